@@ -1,0 +1,308 @@
+// Element-wise / layout kernels (K7, K12, K14 of SURVEY.md section 2.9).
+// Device activations are NHWC bf16; the public layout is NCHW fp32
+// (reference: src/layer/layer.h:33-54), so the two converters below sit at the
+// API boundary (input copy, extract/predict copy-out, flatten).
+#include "common.cuh"
+
+namespace cxn {
+
+// ---------------------------------------------------------------- layout
+// src fp32 [N][C][HW] -> dst bf16 [N][HW][ldc] (channels innermost, ldc >= C)
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int N, int C, int HW,
+                                    int ldc) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z;
+  const int hw0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const float* s = src + (long long)n * C * HW;
+  bf16* d = dst + (long long)n * HW * ldc;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, hw = hw0 + threadIdx.x;
+    tile[i][threadIdx.x] = (c < C && hw < HW) ? s[(long long)c * HW + hw] : 0.0f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int hw = hw0 + i, c = c0 + threadIdx.x;
+    if (hw < HW && c < C) d[(long long)hw * ldc + c] = __float2bfloat16(tile[threadIdx.x][i]);
+  }
+}
+// src bf16 [N][HW][ldc] -> dst fp32 [N][C][HW]
+__global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ src, float* __restrict__ dst, int N, int C, int HW,
+                                    int ldc) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z;
+  const int hw0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const bf16* s = src + (long long)n * HW * ldc;
+  float* d = dst + (long long)n * C * HW;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int hw = hw0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (c < C && hw < HW) ? __bfloat162float(s[(long long)hw * ldc + c]) : 0.0f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, hw = hw0 + threadIdx.x;
+    if (hw < HW && c < C) d[(long long)c * HW + hw] = tile[threadIdx.x][i];
+  }
+}
+// bf16 [N][HW][ldc_in] <-> bf16 [N][C][ld_hw] (flatten in reference (c,h,w) order and its inverse)
+template <bool kToChw>
+__global__ void bf16_transpose_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, int C, int HW,
+                                      long long src_img, long long dst_img, int ld_hwc, int ld_chw) {
+  __shared__ bf16 tile[32][34];
+  const int n = blockIdx.z;
+  const int hw0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const bf16* s = src + (long long)n * src_img;
+  bf16* d = dst + (long long)n * dst_img;
+  if (kToChw) {
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+      const int hw = hw0 + i, c = c0 + threadIdx.x;
+      tile[i][threadIdx.x] = (c < C && hw < HW) ? s[(long long)hw * ld_hwc + c] : __float2bfloat16(0.0f);
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+      const int c = c0 + i, hw = hw0 + threadIdx.x;
+      if (hw < HW && c < C) d[(long long)c * ld_chw + hw] = tile[threadIdx.x][i];
+    }
+  } else {
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+      const int c = c0 + i, hw = hw0 + threadIdx.x;
+      tile[i][threadIdx.x] = (c < C && hw < HW) ? s[(long long)c * ld_chw + hw] : __float2bfloat16(0.0f);
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+      const int hw = hw0 + i, c = c0 + threadIdx.x;
+      if (hw < HW && c < C) d[(long long)hw * ld_hwc + c] = tile[threadIdx.x][i];
+    }
+  }
+}
+
+// ---------------------------------------------------------------- 2-D strided helpers
+// Activations are 2-D [rows][ld] with `cols` valid entries per row.
+template <typename TS, typename TD>
+__global__ void copy2d_kernel(const TS* __restrict__ src, long long lds, TD* __restrict__ dst, long long ldd,
+                              long long rows, int cols, int accumulate) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols;
+    const int c = (int)(i - r * cols);
+    float v = (float)src[r * lds + c];
+    if (accumulate) v += (float)dst[r * ldd + c];
+    dst[r * ldd + c] = (TD)v;
+  }
+}
+
+// ---------------------------------------------------------------- activations
+// op: 0 relu, 1 sigmoid, 2 tanh, 3 xelu(b)          (reference src/layer/op.h:27-73)
+__device__ __forceinline__ float act_fwd(int op, float a, float b) {
+  switch (op) {
+    case 0: return fmaxf(a, 0.0f);
+    case 1: return 1.0f / (1.0f + __expf(-a));
+    case 2: return tanhf(a);
+    default: return a > 0.0f ? a : a / b;
+  }
+}
+// gradient expressed in terms of the ACTIVATED value y (reference keeps y in the input node)
+__device__ __forceinline__ float act_bwd(int op, float y, float b) {
+  switch (op) {
+    case 0: return y > 0.0f ? 1.0f : 0.0f;
+    case 1: return y * (1.0f - y);
+    case 2: return 1.0f - y * y;
+    default: return y > 0.0f ? 1.0f : 1.0f / b;
+  }
+}
+__global__ void act_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, long long rows, int cols,
+                               long long ld, int op, float b) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols;
+    const long long o = r * ld + (i - r * cols);
+    y[o] = __float2bfloat16(act_fwd(op, __bfloat162float(x[o]), b));
+  }
+}
+// dx = act'(y) * dy
+__global__ void act_bwd_kernel(const bf16* __restrict__ y, const bf16* __restrict__ dy, bf16* __restrict__ dx,
+                               long long rows, int cols, long long ld, int op, float b) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols;
+    const long long o = r * ld + (i - r * cols);
+    dx[o] = __float2bfloat16(act_bwd(op, __bfloat162float(y[o]), b) * __bfloat162float(dy[o]));
+  }
+}
+// contiguous fast path, 8 bf16 per thread
+__global__ void relu_bwd_vec_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dy, uint4* __restrict__ dx,
+                                    long long n8) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    uint4 a = y[i], g = dy[i], o;
+    const __nv_bfloat162* ya = reinterpret_cast<const __nv_bfloat162*>(&a);
+    const __nv_bfloat162* ga = reinterpret_cast<const __nv_bfloat162*>(&g);
+    __nv_bfloat162* oa = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float2 yf = __bfloat1622float2(ya[j]), gf = __bfloat1622float2(ga[j]);
+      oa[j] = __floats2bfloat162_rn(yf.x > 0.0f ? gf.x : 0.0f, yf.y > 0.0f ? gf.y : 0.0f);
+    }
+    dx[i] = o;
+  }
+}
+
+// ---------------------------------------------------------------- dropout
+// mask = (U[0,1) < pkeep) / pkeep, regenerated from (seed, element index) in
+// backward instead of being stored (reference src/layer/dropout_layer-inl.hpp:44-58).
+__global__ void dropout_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, long long rows, int cols,
+                               long long ld, float pkeep, unsigned long long seed,
+                               const unsigned long long* __restrict__ counter) {
+  // `counter` is a device-resident step counter so that a captured CUDA graph
+  // draws a fresh mask on every replay.
+  const unsigned long long offset = counter ? *counter : 0ull;
+  const Philox rng(seed);
+  const long long total = rows * cols;
+  const long long nquads = (total + 3) / 4;
+  const float scale = 1.0f / pkeep;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < nquads;
+       q += (long long)gridDim.x * blockDim.x) {
+    uint32_t r4[4];
+    rng((unsigned long long)q, offset, r4);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long i = q * 4 + j;
+      if (i < total) {
+        const long long r = i / cols;
+        const long long o = r * ld + (i - r * cols);
+        const float m = (u01(r4[j]) < pkeep) ? scale : 0.0f;
+        y[o] = __float2bfloat16(__bfloat162float(x[o]) * m);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------- reductions
+// out[c] (+)= sum_r x[r][c]   (bias gradients: reference fullc_layer-inl.hpp:123-125,
+// convolution_layer-inl.hpp:117-119).  One CTA handles a strip of 32 columns.
+__global__ void colsum_kernel(const bf16* __restrict__ x, long long rows, int cols, long long ld,
+                              float* __restrict__ out, int accumulate) {
+  __shared__ float red[8][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  float acc = 0.0f;
+  if (c < cols) {
+    for (long long r = blockIdx.y * 8 + threadIdx.y; r < rows; r += (long long)gridDim.y * 8)
+      acc += __bfloat162float(x[r * ld + c]);
+  }
+  red[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+    float s = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += red[j][threadIdx.x];
+    if (gridDim.y > 1 || accumulate) atomicAdd(out + c, s);
+    else out[c] = s;
+  }
+}
+
+__global__ void counter_add_kernel(unsigned long long* c, unsigned long long inc) { *c += inc; }
+
+__global__ void fill_f32_kernel(float* __restrict__ p, long long n, float v) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    p[i] = v;
+}
+
+}  // namespace cxn
+
+using namespace cxn;
+
+CXN_API int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C, int HW, int ldc, cudaStream_t st) {
+  if (N <= 0 || C <= 0 || HW <= 0) return 0;
+  dim3 grid(ceil_div(HW, 32), ceil_div(C, 32), N), block(32, 8);
+  nchw_to_nhwc_kernel<<<grid, block, 0, st>>>(src, (bf16*)dst, N, C, HW, ldc);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int N, int C, int HW, int ldc, cudaStream_t st) {
+  if (N <= 0 || C <= 0 || HW <= 0) return 0;
+  dim3 grid(ceil_div(HW, 32), ceil_div(C, 32), N), block(32, 8);
+  nhwc_to_nchw_kernel<<<grid, block, 0, st>>>((const bf16*)src, dst, N, C, HW, ldc);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+// to_chw=1: src [N][HW][ld_hwc] -> dst [N][C][ld_chw];  to_chw=0: the inverse.
+CXN_API int cxn_bf16_hwc_chw(const void* src, void* dst, int N, int C, int HW, long long src_img, long long dst_img,
+                             int ld_hwc, int ld_chw, int to_chw, cudaStream_t st) {
+  if (N <= 0 || C <= 0 || HW <= 0) return 0;
+  dim3 grid(ceil_div(HW, 32), ceil_div(C, 32), N), block(32, 8);
+  if (to_chw)
+    bf16_transpose_kernel<true><<<grid, block, 0, st>>>((const bf16*)src, (bf16*)dst, C, HW, src_img, dst_img, ld_hwc, ld_chw);
+  else
+    bf16_transpose_kernel<false><<<grid, block, 0, st>>>((const bf16*)src, (bf16*)dst, C, HW, src_img, dst_img, ld_hwc, ld_chw);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+// kind: 0 bf16->bf16, 1 f32->bf16, 2 bf16->f32, 3 f32->f32
+CXN_API int cxn_copy2d(const void* src, long long lds, void* dst, long long ldd, long long rows, int cols, int kind,
+                       int accumulate, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  const int g = ew_grid(rows * cols, 256);
+  switch (kind) {
+    case 0: copy2d_kernel<bf16, bf16><<<g, 256, 0, st>>>((const bf16*)src, lds, (bf16*)dst, ldd, rows, cols, accumulate); break;
+    case 1: copy2d_kernel<float, bf16><<<g, 256, 0, st>>>((const float*)src, lds, (bf16*)dst, ldd, rows, cols, accumulate); break;
+    case 2: copy2d_kernel<bf16, float><<<g, 256, 0, st>>>((const bf16*)src, lds, (float*)dst, ldd, rows, cols, accumulate); break;
+    default: copy2d_kernel<float, float><<<g, 256, 0, st>>>((const float*)src, lds, (float*)dst, ldd, rows, cols, accumulate); break;
+  }
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_act_fwd(const void* x, void* y, long long rows, int cols, long long ld, int op, float b,
+                        cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  act_fwd_kernel<<<ew_grid(rows * cols, 256), 256, 0, st>>>((const bf16*)x, (bf16*)y, rows, cols, ld, op, b);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_act_bwd(const void* y, const void* dy, void* dx, long long rows, int cols, long long ld, int op,
+                        float b, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  const long long total = rows * cols;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(dy) |
+                         reinterpret_cast<uintptr_t>(dx)) & 15) == 0;
+  if (op == 0 && ld == cols && (total % 8) == 0 && aligned) {
+    relu_bwd_vec_kernel<<<ew_grid(total / 8, 256), 256, 0, st>>>((const uint4*)y, (const uint4*)dy, (uint4*)dx, total / 8);
+  } else {
+    act_bwd_kernel<<<ew_grid(total, 256), 256, 0, st>>>((const bf16*)y, (const bf16*)dy, (bf16*)dx, rows, cols, ld, op, b);
+  }
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_dropout(const void* x, void* y, long long rows, int cols, long long ld, float pkeep,
+                        unsigned long long seed, const unsigned long long* counter, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  dropout_kernel<<<ew_grid((rows * cols + 3) / 4, 256), 256, 0, st>>>((const bf16*)x, (bf16*)y, rows, cols, ld, pkeep, seed, counter);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_colsum_bf16(const void* x, long long rows, int cols, long long ld, float* out, int accumulate,
+                            cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  int gy = (int)((rows + 255) / 256);
+  const int cap = ceil_div(num_sms() * 4, ceil_div(cols, 32));
+  if (gy > cap) gy = cap;
+  if (gy < 1) gy = 1;
+  if (gy > 1 && !accumulate) {
+    fill_f32_kernel<<<ew_grid(cols, 256), 256, 0, st>>>(out, cols, 0.0f);
+  }
+  dim3 grid(ceil_div(cols, 32), gy), block(32, 8);
+  colsum_kernel<<<grid, block, 0, st>>>((const bf16*)x, rows, cols, ld, out, accumulate);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_fill_f32(float* p, long long n, float v, cudaStream_t st) {
+  if (n <= 0) return 0;
+  fill_f32_kernel<<<ew_grid(n, 256), 256, 0, st>>>(p, n, v);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_counter_add(unsigned long long* counter, unsigned long long inc, cudaStream_t st) {
+  counter_add_kernel<<<1, 1, 0, st>>>(counter, inc);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}

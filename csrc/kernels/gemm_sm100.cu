@@ -1,0 +1,526 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a.
+//
+//   D[z] (M x N) (+)= A[z] (M x K) * B[z]^T (N x K)  (+ bias[z][n]) (relu)
+//
+// bf16 operands, fp32 accumulation in tensor memory.  Either operand may be
+// K-major (row-major [MN][K]) or MN-major (row-major [K][MN]); this covers
+//   fullc / conv forward     : A K-major,  B K-major        (cf. reference
+//   fullc / conv backward-data: A K-major,  B MN-major        src/layer/fullc_layer-inl.hpp:108-129,
+//   fullc / conv backward-wgt : A MN-major, B MN-major         src/layer/convolution_layer-inl.hpp:79-153)
+// without any transposed copies.  The reference does these with cuBLAS SGEMM
+// behind mshadow dot(); nothing here is derived from that code.
+//
+// Structure (persistent, warp specialised, one CTA per SM):
+//   warp 0      : TMA producer  (cp.async.bulk.tensor.3d -> 128B-swizzled smem ring)
+//   warp 1      : tcgen05.mma issuer (one elected lane), owns the TMEM allocation
+//   warps 2..5  : epilogue, tcgen05.ld -> bias/relu/convert -> global
+// Two accumulator stages in TMEM let the epilogue of tile i overlap the
+// main loop of tile i+1.  Split-K tiles reduce with fp32 red.global.add.
+#include "common.cuh"
+#include <mutex>
+#include <unordered_map>
+#include <string.h>
+
+namespace cxn {
+namespace gemm {
+
+constexpr int BM = 128;
+constexpr int BK = 64;           // 64 bf16 = 128 bytes = one swizzle span
+constexpr int UMMA_K = 16;
+constexpr int kThreads = 192;
+constexpr int kAccStages = 2;
+
+enum : int {
+  kFlagRelu = 1,      // max(x,0) after bias
+  kFlagOutBf16 = 2,   // D is bf16 (else fp32)
+  kFlagAtomic = 4,    // fp32 D += partial via red.global.add (split-K or accumulate)
+  kFlagBeta1 = 8,     // fp32 D = D + result (non atomic read-modify-write)
+};
+
+struct Params {
+  int M, N, K;
+  int batch, splits, kb_per_split;
+  void* D;
+  long long ldd, strideD;
+  const float* bias;
+  long long strideBias;
+  int flags;
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kTmemCols = kAccStages * BN;  // 128 / 256 / 512
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must surface as a trap, never as a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  unsigned spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if ((++spins & 1023u) == 0 && clock64() - t0 > 8000000000LL) {
+      printf("[cxxnet_b200 gemm] mbarrier timeout block %d thread %d\n", blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0,
+                                            int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory matrix descriptor, 128B swizzle (cute::UMMA::SmemDescriptor layout)
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t bar_base = smem_base + C::kStages * C::kStageBytes;
+  // barrier layout (8 bytes each): full[S], empty[S], tfull[2], tempty[2], then tmem ptr
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + kAccStages + a); };
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + C::kStages * C::kStageBytes + 8 * (2 * C::kStages + 2 * kAccStages));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int tiles_m = ceil_div(p.M, BM);
+  const int tiles_n = ceil_div(p.N, BN);
+  const int num_kb = ceil_div(p.K, BK);
+  const long long total_tiles = (long long)tiles_m * tiles_n * p.batch * p.splits;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < kAccStages; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32((const void*)tmem_ptr_smem)),
+                 "n"(C::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // =========================== TMA producer ===========================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        long long r = t;
+        const int n_blk = (int)(r % tiles_n); r /= tiles_n;
+        const int m_blk = (int)(r % tiles_m); r /= tiles_m;
+        const int split = (int)(r % p.splits);
+        const int z = (int)(r / p.splits);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(num_kb, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * C::kStageBytes;
+          const uint32_t sb = sa + C::kABytes;
+          mbar_expect_tx(full_bar(stage), C::kStageBytes);
+          if (!A_MN) {
+            tma_load_3d(sa, &tmA, full_bar(stage), kb * BK, m_blk * BM, z);
+          } else {
+#pragma unroll
+            for (int h = 0; h < BM / 64; ++h)
+              tma_load_3d(sa + h * (64 * BK * 2), &tmA, full_bar(stage), m_blk * BM + h * 64, kb * BK, z);
+          }
+          if (!B_MN) {
+            tma_load_3d(sb, &tmB, full_bar(stage), kb * BK, n_blk * BN, z);
+          } else {
+#pragma unroll
+            for (int h = 0; h < BN / 64; ++h)
+              tma_load_3d(sb + h * (64 * BK * 2), &tmB, full_bar(stage), n_blk * BN + h * 64, kb * BK, z);
+          }
+          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // =========================== MMA issuer =============================
+    if (lane == 0) {
+      // instruction descriptor: D=f32, A=B=bf16, majors, N, M
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
+                             ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      constexpr uint32_t kLboMN = 64 * BK * 2;  // next 64-wide MN atom (one TMA box)
+      constexpr uint32_t kSbo = 1024;           // 8 rows x 128 bytes
+      constexpr uint32_t kAStep = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+      constexpr uint32_t kBStep = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        long long r = t / ((long long)tiles_n * tiles_m);
+        const int split = (int)(r % p.splits);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(num_kb, kb0 + p.kb_per_split);
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * C::kStageBytes;
+          const uint32_t sb = sa + C::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t ad = make_desc(sa + k * kAStep, A_MN ? kLboMN : 0u, kSbo);
+            const uint64_t bd = make_desc(sb + k * kBStep, B_MN ? kLboMN : 0u, kSbo);
+            umma_bf16(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
+          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
+        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+    __syncwarp();
+  } else {
+    // =========================== epilogue ===============================
+    const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const bool relu = p.flags & kFlagRelu;
+    const bool out_bf16 = p.flags & kFlagOutBf16;
+    const bool atomic = p.flags & kFlagAtomic;
+    const bool beta1 = p.flags & kFlagBeta1;
+    for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      long long r = t;
+      const int n_blk = (int)(r % tiles_n); r /= tiles_n;
+      const int m_blk = (int)(r % tiles_m); r /= tiles_m;
+      const int split = (int)(r % p.splits);
+      const int z = (int)(r / p.splits);
+      const int kb0 = split * p.kb_per_split;
+      const int kb1 = min(num_kb, kb0 + p.kb_per_split);
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const int row = m_blk * BM + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+      const bool has_work = kb1 > kb0;
+      const float* bias = (p.bias != nullptr && split == 0) ? p.bias + (long long)z * p.strideBias : nullptr;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        const int n0 = n_blk * BN + c0;
+        if (n0 >= p.N) break;  // warp-uniform
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
+        tmem_ld32(taddr, v);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = has_work ? __uint_as_float(v[j]) : 0.0f;
+        const bool full = (n0 + 32 <= p.N);
+        if (bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (full || n0 + j < p.N) f[j] += __ldg(bias + n0 + j);
+        }
+        if (relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+        }
+        const long long off = (long long)z * p.strideD + (long long)row * p.ldd + n0;
+        if (out_bf16) {
+          bf16* d = reinterpret_cast<bf16*>(p.D) + off;
+          if (full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+            uint4* d4 = reinterpret_cast<uint4*>(d);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(f[q * 8 + 0], f[q * 8 + 1]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(f[q * 8 + 2], f[q * 8 + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(f[q * 8 + 4], f[q * 8 + 5]);
+              __nv_bfloat162 h3 = __floats2bfloat162_rn(f[q * 8 + 6], f[q * 8 + 7]);
+              uint4 u;
+              u.x = *reinterpret_cast<uint32_t*>(&h0);
+              u.y = *reinterpret_cast<uint32_t*>(&h1);
+              u.z = *reinterpret_cast<uint32_t*>(&h2);
+              u.w = *reinterpret_cast<uint32_t*>(&h3);
+              d4[q] = u;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (n0 + j < p.N) d[j] = __float2bfloat16(f[j]);
+          }
+        } else {
+          float* d = reinterpret_cast<float*>(p.D) + off;
+          if (atomic) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (full || n0 + j < p.N) atomicAdd(d + j, f[j]);
+          } else if (full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+            float4* d4 = reinterpret_cast<float4*>(d);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              float4 o = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
+              if (beta1) {
+                const float4 c = d4[q];
+                o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
+              }
+              d4[q] = o;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (n0 + j < p.N) d[j] = beta1 ? d[j] + f[j] : f[j];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::kTmemCols)
+                 : "memory");
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr;
+  long long ld, bstride;
+  int rows, cols, batch, mn_major, box_rows;
+  bool operator==(const MapKey& o) const { return memcmp(this, &o, sizeof(MapKey)) == 0; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+    size_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < sizeof(MapKey) / 8; ++i) h = (h ^ w[i]) * 1099511628211ull;
+    return h;
+  }
+};
+
+// Tensor map for one operand.  `mn` = extent along M or N, `k` = reduction extent.
+//   K-major : memory [batch][mn][ld>=k]   box {64 (k), box_rows (mn)}
+//   MN-major: memory [batch][k][ld>=mn]   box {64 (mn), 64 (k)}
+static int make_map(CUtensorMap* out, const void* ptr, int mn, int k, long long ld, int batch, long long bstride,
+                    bool mn_major, int box_rows) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  MapKey key;
+  memset(&key, 0, sizeof(key));
+  key.ptr = ptr; key.ld = ld; key.bstride = bstride; key.rows = mn; key.cols = k; key.batch = batch;
+  key.mn_major = mn_major ? 1 : 0; key.box_rows = box_rows;
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return 0; }
+  }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) { fprintf(stderr, "[cxxnet_b200] cuTensorMapEncodeTiled unavailable\n"); return -2; }
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (ld % 8) || (batch > 1 && (bstride % 8))) {
+    fprintf(stderr, "[cxxnet_b200] gemm operand not 16B aligned (ptr=%p ld=%lld bstride=%lld)\n", ptr, ld, bstride);
+    return -3;
+  }
+  cuuint64_t gdim[3], gstr[2];
+  cuuint32_t box[3], estr[3] = {1, 1, 1};
+  if (!mn_major) {
+    gdim[0] = (cuuint64_t)k; gdim[1] = (cuuint64_t)mn;
+    box[0] = BK; box[1] = (cuuint32_t)box_rows;
+  } else {
+    gdim[0] = (cuuint64_t)mn; gdim[1] = (cuuint64_t)k;
+    box[0] = 64; box[1] = BK;
+  }
+  gdim[2] = (cuuint64_t)batch;
+  box[2] = 1;
+  gstr[0] = (cuuint64_t)ld * 2;
+  gstr[1] = (cuuint64_t)(batch > 1 ? bstride : (long long)ld * (long long)gdim[1]) * 2;
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr, "[cxxnet_b200] cuTensorMapEncodeTiled failed: %d (mn=%d k=%d ld=%lld batch=%d)\n", (int)r, mn, k,
+            ld, batch);
+    return -4;
+  }
+  {
+    std::lock_guard<std::mutex> g(mu);
+    if (cache.size() > 4096) cache.clear();
+    cache[key] = *out;
+  }
+  return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int grid, cudaStream_t st) {
+  using C = Cfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         C::kSmemBytes);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  gemm_kernel<BN, A_MN, B_MN><<<grid, kThreads, C::kSmemBytes, st>>>(ta, tb, p);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace gemm
+}  // namespace cxn
+
+// D[z] = A[z] * B[z]^T.  All leading dimensions / strides are in elements.
+//   a_mn / b_mn: 0 = operand stored [rows=MN][K] (K contiguous), 1 = stored [K][MN] (MN contiguous)
+//   flags: cxn::gemm::kFlag*;  splits: split-K factor (>1 requires kFlagAtomic, fp32 D)
+//   bn: tile width 64/128/256 or 0 = choose.
+CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a_mn, const void* B, long long ldb,
+                          long long strideB, int b_mn, void* D, long long ldd, long long strideD, const float* bias,
+                          long long strideBias, int M, int N, int K, int batch, int splits, int flags, int bn,
+                          cudaStream_t stream) {
+  using namespace cxn;
+  using namespace cxn::gemm;
+  if (M <= 0 || N <= 0 || K <= 0 || batch <= 0) return 0;
+  const int num_kb = ceil_div(K, BK);
+  if (splits < 1) splits = 1;
+  if (splits > num_kb) splits = num_kb;
+  if (splits > 1 && !(flags & kFlagAtomic)) return -5;
+  if ((flags & kFlagAtomic) && (flags & kFlagOutBf16)) return -6;
+  int kbps = ceil_div(num_kb, splits);
+  splits = ceil_div(num_kb, kbps);
+  const int sms = num_sms();
+  if (bn == 0) {
+    auto tiles = [&](int b) { return (long long)ceil_div(M, BM) * ceil_div(N, b) * batch * splits; };
+    if (N > 128 && tiles(256) >= sms) bn = 256;
+    else if (N > 64 && tiles(128) >= sms) bn = 128;
+    else bn = (N > 64 && tiles(64) > 2LL * sms) ? 128 : 64;
+  }
+  Params p;
+  p.M = M; p.N = N; p.K = K; p.batch = batch; p.splits = splits; p.kb_per_split = kbps;
+  p.D = D; p.ldd = ldd; p.strideD = strideD; p.bias = bias; p.strideBias = strideBias; p.flags = flags;
+  CUtensorMap ta, tb;
+  int rc = make_map(&ta, A, M, K, lda, batch, strideA, a_mn != 0, BM);
+  if (rc) return rc;
+  rc = make_map(&tb, B, N, K, ldb, batch, strideB, b_mn != 0, bn);
+  if (rc) return rc;
+  const long long total = (long long)ceil_div(M, BM) * ceil_div(N, bn) * batch * splits;
+  const int grid = (int)(total < sms ? total : sms);
+#define CXN_DISPATCH(BN_)                                                                      \
+  if (!a_mn && !b_mn) return launch<BN_, false, false>(ta, tb, p, grid, stream);              \
+  if (!a_mn && b_mn) return launch<BN_, false, true>(ta, tb, p, grid, stream);                \
+  if (a_mn && b_mn) return launch<BN_, true, true>(ta, tb, p, grid, stream);                  \
+  return launch<BN_, true, false>(ta, tb, p, grid, stream);
+  if (bn == 256) { CXN_DISPATCH(256) }
+  if (bn == 128) { CXN_DISPATCH(128) }
+  { CXN_DISPATCH(64) }
+#undef CXN_DISPATCH
+}

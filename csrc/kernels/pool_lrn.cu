@@ -1,0 +1,263 @@
+// Pooling (K8/K9) and local response normalisation (K10/K11) on NHWC bf16.
+//
+// Pooling semantics (reference src/layer/pooling_layer-inl.hpp:45-106): windows start at
+// o*stride and are clipped at the border, output size is
+// min(H-k+s-1, H-1)/s+1, avg divides by the full k*k, and max-unpool sends the
+// gradient to EVERY input equal to the pooled maximum.
+// LRN (reference src/layer/lrn_layer-inl.hpp:53-75):
+//   norm = knorm + alpha/n * sum_{|j-c|<=n/2} x_j^2 ;  y = x * norm^-beta
+//   dx = g*norm^-beta - 2*beta*alpha/n * x * sum_window( g*x*norm^(-beta-1) )
+#include "common.cuh"
+
+namespace cxn {
+
+struct PoolGeom {
+  int N, H, W, C, K_y, K_x, stride, OH, OW;
+  int mode;   // 0 max, 1 sum, 2 avg
+  int relu;   // relu_max_pooling: relu applied to the input first
+};
+
+template <int V>
+__global__ void pool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, PoolGeom g) {
+  const int cv = g.C / V;
+  const long long total = (long long)g.N * g.OH * g.OW * cv;
+  const float scale = g.mode == 2 ? 1.0f / (g.K_y * g.K_x) : 1.0f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    long long r = i;
+    const int c = (int)(r % cv) * V; r /= cv;
+    const int ow = (int)(r % g.OW); r /= g.OW;
+    const int oh = (int)(r % g.OH);
+    const int n = (int)(r / g.OH);
+    const int y0 = oh * g.stride, y1 = min(y0 + g.K_y, g.H);
+    const int x0 = ow * g.stride, x1 = min(x0 + g.K_x, g.W);
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = g.mode == 0 ? -INFINITY : 0.0f;
+    for (int yy = y0; yy < y1; ++yy)
+      for (int xx = x0; xx < x1; ++xx) {
+        const bf16* s = x + (((long long)n * g.H + yy) * g.W + xx) * g.C + c;
+        float f[V];
+        if (V == 8) {
+          const uint4 v = *reinterpret_cast<const uint4*>(s);
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 t = __bfloat1622float2(h[j]);
+            f[2 * j] = t.x; f[2 * j + 1] = t.y;
+          }
+        } else {
+          f[0] = __bfloat162float(*s);
+        }
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          const float a = g.relu ? fmaxf(f[j], 0.0f) : f[j];
+          acc[j] = g.mode == 0 ? fmaxf(acc[j], a) : acc[j] + a;
+        }
+      }
+    bf16* d = y + (((long long)n * g.OH + oh) * g.OW + ow) * g.C + c;
+    if (V == 8) {
+      uint4 o;
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(acc[2 * j] * scale, acc[2 * j + 1] * scale);
+      *reinterpret_cast<uint4*>(d) = o;
+    } else {
+      *d = __float2bfloat16(acc[0] * scale);
+    }
+  }
+}
+
+// dx[n][y][x][c] = sum over covering windows of  partial(x, pooled) * dy   (* 1/k^2 for avg)
+// With relu fused, x is compared after relu and the result is masked by x>0.
+template <int V>
+__global__ void pool_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ y, const bf16* __restrict__ dy,
+                                bf16* __restrict__ dx, PoolGeom g) {
+  const int cv = g.C / V;
+  const long long total = (long long)g.N * g.H * g.W * cv;
+  const float scale = g.mode == 2 ? 1.0f / (g.K_y * g.K_x) : 1.0f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    long long r = i;
+    const int c = (int)(r % cv) * V; r /= cv;
+    const int xx = (int)(r % g.W); r /= g.W;
+    const int yy = (int)(r % g.H);
+    const int n = (int)(r / g.H);
+    const int py0 = yy < g.K_y ? 0 : (yy - g.K_y + g.stride) / g.stride;
+    const int px0 = xx < g.K_x ? 0 : (xx - g.K_x + g.stride) / g.stride;
+    const int py1 = min((yy + g.stride) / g.stride, g.OH);
+    const int px1 = min((xx + g.stride) / g.stride, g.OW);
+    const long long xoff = (((long long)n * g.H + yy) * g.W + xx) * g.C + c;
+    float xv[V], acc[V];
+    if (V == 8) {
+      const uint4 v = *reinterpret_cast<const uint4*>(x + xoff);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 t = __bfloat1622float2(h[j]);
+        xv[2 * j] = t.x; xv[2 * j + 1] = t.y;
+      }
+    } else {
+      xv[0] = __bfloat162float(x[xoff]);
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      if (g.relu) xv[j] = fmaxf(xv[j], 0.0f);
+      acc[j] = 0.0f;
+    }
+    for (int py = py0; py < py1; ++py)
+      for (int px = px0; px < px1; ++px) {
+        const long long poff = (((long long)n * g.OH + py) * g.OW + px) * g.C + c;
+        float pv[V], gv[V];
+        if (V == 8) {
+          const uint4 a = *reinterpret_cast<const uint4*>(y + poff);
+          const uint4 b = *reinterpret_cast<const uint4*>(dy + poff);
+          const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
+          const __nv_bfloat162* hb = reinterpret_cast<const __nv_bfloat162*>(&b);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 t = __bfloat1622float2(ha[j]), u = __bfloat1622float2(hb[j]);
+            pv[2 * j] = t.x; pv[2 * j + 1] = t.y;
+            gv[2 * j] = u.x; gv[2 * j + 1] = u.y;
+          }
+        } else {
+          pv[0] = __bfloat162float(y[poff]);
+          gv[0] = __bfloat162float(dy[poff]);
+        }
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          if (g.mode == 0) acc[j] += (xv[j] == pv[j]) ? gv[j] : 0.0f;
+          else acc[j] += gv[j];
+        }
+      }
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      acc[j] *= scale;
+      if (g.relu) acc[j] = xv[j] > 0.0f ? acc[j] : 0.0f;
+    }
+    if (V == 8) {
+      uint4 o;
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+      *reinterpret_cast<uint4*>(dx + xoff) = o;
+    } else {
+      dx[xoff] = __float2bfloat16(acc[0]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ LRN
+// One warp per pixel; the pixel's channel vector lives in shared memory.
+__global__ void lrn_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, long long pixels, int C, int nsize,
+                               float salpha, float beta, float knorm) {
+  extern __shared__ float sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  float* xs = sm + warp * C;
+  const int half = nsize / 2;
+  for (long long p = (long long)blockIdx.x * wpb + warp; p < pixels; p += (long long)gridDim.x * wpb) {
+    const bf16* xp = x + p * C;
+    for (int c = lane; c < C; c += 32) xs[c] = __bfloat162float(xp[c]);
+    __syncwarp();
+    for (int c = lane; c < C; c += 32) {
+      const int lo = max(0, c - half), hi = min(C, c + half + 1);
+      float s = 0.0f;
+      for (int j = lo; j < hi; ++j) s += xs[j] * xs[j];
+      const float norm = s * salpha + knorm;
+      y[p * C + c] = __float2bfloat16(xs[c] * __powf(norm, -beta));
+    }
+    __syncwarp();
+  }
+}
+__global__ void lrn_bwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, bf16* __restrict__ dx,
+                               long long pixels, int C, int nsize, float salpha, float beta, float knorm) {
+  extern __shared__ float sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  float* xs = sm + warp * 3 * C;
+  float* nb = xs + C;   // norm^-beta
+  float* ts = nb + C;   // g * x * norm^(-beta-1)
+  const int half = nsize / 2;
+  for (long long p = (long long)blockIdx.x * wpb + warp; p < pixels; p += (long long)gridDim.x * wpb) {
+    for (int c = lane; c < C; c += 32) xs[c] = __bfloat162float(x[p * C + c]);
+    __syncwarp();
+    for (int c = lane; c < C; c += 32) {
+      const int lo = max(0, c - half), hi = min(C, c + half + 1);
+      float s = 0.0f;
+      for (int j = lo; j < hi; ++j) s += xs[j] * xs[j];
+      const float norm = s * salpha + knorm;
+      const float pb = __powf(norm, -beta);
+      const float g = __bfloat162float(dy[p * C + c]);
+      nb[c] = pb;
+      ts[c] = g * xs[c] * pb / norm;
+    }
+    __syncwarp();
+    for (int c = lane; c < C; c += 32) {
+      const int lo = max(0, c - half), hi = min(C, c + half + 1);
+      float s = 0.0f;
+      for (int j = lo; j < hi; ++j) s += ts[j];
+      const float g = __bfloat162float(dy[p * C + c]);
+      dx[p * C + c] = __float2bfloat16(g * nb[c] - 2.0f * beta * salpha * s * xs[c]);
+    }
+    __syncwarp();
+  }
+}
+
+}  // namespace cxn
+
+using namespace cxn;
+
+static inline bool pool_vec(const void* a, const void* b, int C) {
+  return (C % 8 == 0) && (((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0);
+}
+
+CXN_API int cxn_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int ky, int kx, int stride, int OH,
+                         int OW, int mode, int relu, cudaStream_t st) {
+  PoolGeom g{N, H, W, C, ky, kx, stride, OH, OW, mode, relu};
+  if ((long long)N * OH * OW * C <= 0) return 0;
+  if (pool_vec(x, y, C))
+    pool_fwd_kernel<8><<<ew_grid((long long)N * OH * OW * (C / 8), 256, 16), 256, 0, st>>>((const bf16*)x, (bf16*)y, g);
+  else
+    pool_fwd_kernel<1><<<ew_grid((long long)N * OH * OW * C, 256, 16), 256, 0, st>>>((const bf16*)x, (bf16*)y, g);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, int ky,
+                         int kx, int stride, int OH, int OW, int mode, int relu, cudaStream_t st) {
+  PoolGeom g{N, H, W, C, ky, kx, stride, OH, OW, mode, relu};
+  if ((long long)N * H * W * C <= 0) return 0;
+  const bool v = pool_vec(x, y, C) && pool_vec(dy, dx, C);
+  if (v)
+    pool_bwd_kernel<8><<<ew_grid((long long)N * H * W * (C / 8), 256, 16), 256, 0, st>>>(
+        (const bf16*)x, (const bf16*)y, (const bf16*)dy, (bf16*)dx, g);
+  else
+    pool_bwd_kernel<1><<<ew_grid((long long)N * H * W * C, 256, 16), 256, 0, st>>>(
+        (const bf16*)x, (const bf16*)y, (const bf16*)dy, (bf16*)dx, g);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_lrn_fwd(const void* x, void* y, long long pixels, int C, int nsize, float alpha, float beta,
+                        float knorm, cudaStream_t st) {
+  if (pixels <= 0 || C <= 0) return 0;
+  const int threads = 256, wpb = threads / 32;
+  const size_t smem = (size_t)wpb * C * sizeof(float);
+  if (smem > 48 * 1024) return -7;
+  long long blocks = ceil_div_ll(pixels, wpb);
+  const long long cap = (long long)num_sms() * 8;
+  lrn_fwd_kernel<<<(int)(blocks < cap ? blocks : cap), threads, smem, st>>>((const bf16*)x, (bf16*)y, pixels, C, nsize,
+                                                                              alpha / nsize, beta, knorm);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_lrn_bwd(const void* x, const void* dy, void* dx, long long pixels, int C, int nsize, float alpha,
+                        float beta, float knorm, cudaStream_t st) {
+  if (pixels <= 0 || C <= 0) return 0;
+  const int threads = 128, wpb = threads / 32;
+  const size_t smem = (size_t)wpb * 3 * C * sizeof(float);
+  if (smem > 48 * 1024) return -7;
+  long long blocks = ceil_div_ll(pixels, wpb);
+  const long long cap = (long long)num_sms() * 8;
+  lrn_bwd_kernel<<<(int)(blocks < cap ? blocks : cap), threads, smem, st>>>((const bf16*)x, (const bf16*)dy, (bf16*)dx,
+                                                                              pixels, C, nsize, alpha / nsize, beta, knorm);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}

@@ -1,0 +1,478 @@
+"""Per-device graph executor.
+
+Functional parity with reference ``NeuralNet<xpu>`` (``src/nnet/neural_net-inl.hpp:23-297``): nodes,
+connections, updaters; ``forward``, ``backprop``, model save / load, batch-size adjustment.
+
+Backends
+--------
+``ref``   every layer runs its reference math on fp32 NCHW torch tensors (CPU or CUDA), with
+          the reference's in-place node reuse; one ``Updater`` object per (layer, tag).
+``b200``  NHWC bf16 nodes with separate gradient buffers, native sm_100a kernels for the hot
+          layers, a layout bridge for the rest, all weights in a ``ParamArena`` updated by one
+          fused multi-tensor kernel (or, multi-GPU, by the fused reduce-scatter + update +
+          all-gather kernel of ``parallel/exchange.py``).  ReLU layers that directly follow a
+          conv / fullc are folded into the GEMM epilogue.
+"""
+from __future__ import annotations
+
+import io
+from typing import BinaryIO, Dict, List, Optional
+
+import numpy as np
+import torch
+
+from . import netconfig as nc
+from . import ops
+from .layers import LabelInfo, Layer, Node, create_layer
+from .layers import native
+from .layers.native import _ParamBinding
+from .netconfig import NetConfig
+from .updaters import UpdaterParam, create_updater
+
+
+class Connection:
+    __slots__ = ("type", "layer", "nodes_in", "nodes_out", "native")
+
+    def __init__(self):
+        self.type = 0
+        self.layer: Optional[Layer] = None
+        self.nodes_in: List[Node] = []
+        self.nodes_out: List[Node] = []
+        self.native = False
+
+
+class NeuralNet:
+    def __init__(self, cfg: NetConfig, max_batch: int, seed: int, device: torch.device, backend: str = "ref",
+                 silent: int = 0, world_size: int = 1, rank: int = 0, arena_alloc=None):
+        self.cfg = cfg
+        self.max_batch = max_batch
+        self.seed = seed
+        self.device = device
+        self.backend = backend
+        self.silent = silent
+        self.world_size, self.rank = world_size, rank
+        self.rng = torch.Generator()
+        self.rng.manual_seed(seed)
+        self.label_info = LabelInfo(cfg.label_name_map)
+        self.nodes: List[Node] = []
+        self.connections: List[Connection] = []
+        self.updaters: List[list] = []
+        # b200 state
+        self.arena = None
+        self.arena_alloc = arena_alloc
+        self.exchange = None
+        self.accumulate_grads = False
+        self.num_sms = 148
+        self.step_counter = None
+        self.in_stage = None
+        if backend == "b200":
+            ops.lib()  # fail loudly if the kernel library is missing
+            self.num_sms = torch.cuda.get_device_properties(device).multi_processor_count
+            self.step_counter = torch.zeros(1, dtype=torch.int64, device=device)
+
+    # ------------------------------------------------------------------ structure
+    def _init_net(self) -> None:
+        cfg = self.cfg
+        self.nodes = [Node(cfg.node_names[i], i) for i in range(cfg.num_nodes)]
+        c, h, w = cfg.input_shape
+        self.nodes[0].shape = [self.max_batch, c, h, w]
+        for i in range(cfg.extra_data_num):
+            es = cfg.extra_shape
+            self.nodes[i + 1].shape = [self.max_batch, es[i * 3], es[i * 3 + 1], es[i * 3 + 2]]
+        self.connections = []
+        for i, info in enumerate(cfg.layers):
+            c_ = Connection()
+            c_.type = info.type
+            c_.nodes_in = [self.nodes[j] for j in info.nindex_in]
+            c_.nodes_out = [self.nodes[j] for j in info.nindex_out]
+            if info.type == nc.kSharedLayer:
+                assert 0 <= info.primary_layer_index < len(self.connections), \
+                    "shared layer primary_layer_index exceed bound"
+                c_.layer = self.connections[info.primary_layer_index].layer
+                if not c_.layer.allow_sharing:
+                    raise ValueError("some layer you set shared do not allow sharing")
+            else:
+                c_.layer = create_layer(info.type)
+                c_.layer.rng = self.rng
+                c_.layer.label_info = self.label_info
+                c_.layer.layer_index = i
+                c_.layer.device = self.device
+            self.connections.append(c_)
+
+    def _config_connections(self) -> None:
+        for i, c in enumerate(self.connections):
+            if c.type == nc.kSharedLayer:
+                continue
+            for k, v in self.cfg.defcfg:
+                c.layer.set_param(k, v)
+            for k, v in self.cfg.layercfg[i]:
+                c.layer.set_param(k, v)
+
+    def _init_connections(self) -> None:
+        for c in self.connections:
+            c.layer.init_connection(c.nodes_in, c.nodes_out)
+            if c.type != nc.kSharedLayer:
+                c.layer.nodes_in, c.layer.nodes_out = c.nodes_in, c.nodes_out
+
+    def init_model(self) -> None:
+        self._init_net()
+        self._config_connections()
+        for i, c in enumerate(self.connections):
+            if self.silent == 0:
+                nm = self.cfg.layers[i].name
+                print("Initializing layer: %s" % (nm if nm else str(i)))
+        self._init_connections()
+        for c in self.connections:
+            if c.type != nc.kSharedLayer:
+                c.layer.init_model()
+                self._layer_to_device(c.layer)
+
+    def _layer_to_device(self, layer: Layer) -> None:
+        layer.device = self.device
+        for tag, w, g in layer.weights():
+            if w is not None:
+                layer.rebind(tag, w.to(self.device), g.to(self.device))
+        if hasattr(layer, "master"):
+            self._layer_to_device(layer.master)
+            self._layer_to_device(layer.slave)
+        if getattr(layer, "wmat", None) is not None and not layer.weights():
+            layer.wmat = layer.wmat.to(self.device)  # fixconn
+
+    def save_model(self, fo: BinaryIO) -> None:
+        self.sync_weights_from_device()
+        for c in self.connections:
+            if c.type != nc.kSharedLayer:
+                c.layer.save_model(fo)
+
+    def load_model(self, fi: BinaryIO) -> None:
+        self._init_net()
+        self._config_connections()
+        for c in self.connections:
+            if c.type != nc.kSharedLayer:
+                c.layer.load_model(fi)
+                self._layer_to_device(c.layer)
+        self._init_connections()
+
+    def copy_layer(self, index: int, fi: BinaryIO) -> None:
+        """finetune: load one layer's weights from a stream (reference ``neural_net-inl.hpp`` CopyLayer)."""
+        self.sync_weights_from_device()
+        layer = self.connections[index].layer
+        old = dict((t, (w, g)) for t, w, g in layer.weights())
+        layer.load_model(fi)
+        for t, w, g in layer.weights():
+            if t in old and old[t][0] is not None and old[t][0].shape == w.shape:
+                old[t][0].copy_(w.to(old[t][0].device))
+                layer.rebind(t, old[t][0], old[t][1])
+            else:
+                layer.rebind(t, w.to(self.device), g.to(self.device))
+        self.sync_weights_to_device()
+
+    # ------------------------------------------------------------------ updaters / nodes
+    def init_updaters(self) -> None:
+        cfg = self.cfg
+        if self.backend == "b200":
+            self._setup_b200()
+            return
+        self.updaters = []
+        for i, c in enumerate(self.connections):
+            out = []
+            if c.type != nc.kSharedLayer:
+                for tag, w, g in c.layer.weights():
+                    u = create_updater(cfg.updater_type, w, g, tag)
+                    for k, v in cfg.defcfg:
+                        u.set_param(k, v)
+                    for k, v in cfg.layercfg[i]:
+                        u.set_param(k, v)
+                    if self.silent:
+                        u.param.silent = 1
+                    u.init()
+                    out.append(u)
+            self.updaters.append(out)
+
+    def init_nodes(self) -> None:
+        for n in self.nodes:
+            if self.silent == 0:
+                print("node[%s].shape: %d,%d,%d,%d" % ((n.name,) + tuple(n.shape)))
+
+    # ------------------------------------------------------------------ b200 setup
+    def _setup_b200(self) -> None:
+        from .parallel.arena import ParamArena
+        cfg = self.cfg
+        consumers: Dict[int, int] = {}
+        for c in self.connections:
+            for n in c.nodes_in:
+                if not (c.layer.self_loop and n in c.nodes_out):
+                    consumers[n.index] = consumers.get(n.index, 0) + 1
+        producer: Dict[int, Connection] = {}
+        # a layer object used by several connections keeps per-layer scratch (im2col buffers),
+        # so weight-shared layers run through the bridge
+        shared = set(id(c.layer) for c in self.connections if c.type == nc.kSharedLayer)
+        for c in self.connections:
+            c.native = bool(c.layer.has_b200) and id(c.layer) not in shared
+            if c.native and hasattr(c.layer, "b200_supported"):
+                c.native = bool(c.layer.b200_supported())
+            if not c.layer.self_loop:
+                for n in c.nodes_out:
+                    producer[n.index] = c
+            if isinstance(c.layer, native._NativeLoss) and c.native:
+                c.nodes_in[0].loss_input = True
+        # node buffers
+        for n in self.nodes:
+            b, ch, h, w = n.shape
+            n.shape[0] = self.max_batch
+            rows = self.max_batch if n.is_mat else self.max_batch * h * w
+            cols = w if n.is_mat else ch
+            ld = ops.round_up(cols, 8) if n.is_mat else cols
+            n.act = ops.DevMat(rows, cols, ld, device=self.device)
+            n.grad = ops.DevMat(rows, cols, ld, device=self.device)
+            if n.loss_input:
+                n.f32 = torch.zeros((self.max_batch, ops.round_up(cols, 4)), dtype=torch.float32, device=self.device)
+        # relu folding / aliasing
+        for c in self.connections:
+            l = c.layer
+            if c.native and isinstance(l, native._NativeAct) and l.alias_ok and c.type != nc.kSharedLayer:
+                x, y = c.nodes_in[0], c.nodes_out[0]
+                if x is y or consumers.get(x.index, 0) != 1 or y.loss_input or x.loss_input:
+                    continue
+                y.act, y.grad = x.act, x.grad
+                y.alias_of = x
+                p = producer.get(x.index)
+                if (p is not None and p.native and isinstance(l, native.ReluLayer)
+                        and isinstance(p.layer, (native.FullConnectLayer, native.ConvolutionLayer))
+                        and consumers.get(x.index, 0) == 1):
+                    p.layer.fuse_relu = True
+                    l.fused = True
+        # parameter arena
+        self.arena = ParamArena(self.device, cfg.updater_type, alloc=self.arena_alloc)
+        self._seg_of = {}
+        for i, c in enumerate(self.connections):
+            if c.type == nc.kSharedLayer:
+                continue
+            for tag, w, g in c.layer.weights():
+                up = UpdaterParam(tag)
+                b1, b2 = 0.1, 0.001
+                for k, v in list(cfg.defcfg) + list(cfg.layercfg[i]):
+                    up.set_param(k, v)
+                    if k == "beta1": b1 = float(v)
+                    if k == "beta2": b2 = float(v)
+                shadow = c.layer.b200_shadow(tag) if (c.native and hasattr(c.layer, "b200_shadow")) else None
+                if shadow is not None:
+                    rows, cols, sld = shadow
+                else:
+                    rows, cols, sld = 1, w.numel(), 0
+                s = self.arena.add(c.layer, i, tag, rows, cols, sld, up, b1, b2)
+                self._seg_of[(i, tag)] = s
+        self.arena.finalize()
+        self._bind_arena()
+        for c in self.connections:
+            if c.native and c.type != nc.kSharedLayer:
+                c.layer.b200_setup(self)
+        c0, h0, w0 = cfg.input_shape
+        self.in_stage = torch.zeros((self.max_batch, c0, h0, w0), dtype=torch.float32, device=self.device)
+        self.extra_stage = [torch.zeros(tuple(self.nodes[i + 1].shape), dtype=torch.float32, device=self.device)
+                            for i in range(cfg.extra_data_num)]
+        if self.world_size > 1:
+            from .parallel.exchange import GradExchange
+            self.exchange = GradExchange(self)
+
+    def _bind_arena(self) -> None:
+        """copy layer weights (reference layout) into the arena and hand views back to the layers."""
+        a = self.arena
+        for (i, tag), s in self._seg_of.items():
+            c = self.connections[i]
+            layer = c.layer
+            w_ref = dict((t, w) for t, w, _ in layer.weights())[tag]
+            wv, gv = a.w_view(s), a.g_view(s)
+            if c.native:
+                wv.copy_(layer.weight_to_internal(tag, w_ref.to(self.device)).reshape(-1))
+                layer.bind[tag] = _ParamBinding(wv, gv, a.shadow_view(s), s.shadow_ld, s.rows, s.cols)
+            else:
+                if w_ref.data_ptr() != wv.data_ptr():
+                    wv.copy_(w_ref.reshape(-1))
+                layer.rebind(tag, wv.view(w_ref.shape), gv.view(w_ref.shape))
+        a.refresh_shadow()
+
+    def sync_weights_from_device(self) -> None:
+        """arena (internal layout) -> layer tensors (checkpoint layout) for native layers."""
+        if self.arena is None:
+            return
+        for (i, tag), s in self._seg_of.items():
+            c = self.connections[i]
+            if not c.native:
+                continue
+            layer = c.layer
+            w_ref = dict((t, w) for t, w, _ in layer.weights())[tag]
+            internal = self.arena.w_view(s)
+            w_ref.copy_(layer.weight_from_internal(tag, internal).reshape(w_ref.shape))
+
+    def sync_weights_to_device(self) -> None:
+        if self.arena is not None:
+            self._bind_arena()
+
+    # ------------------------------------------------------------------ layout bridge (b200)
+    def _node_load(self, n: Node, grad: bool = False) -> torch.Tensor:
+        b, c, h, w = n.shape
+        if n.loss_input and not grad:
+            return n.f32[:b, :w].reshape(b, 1, 1, w).clone()
+        m = n.grad if grad else n.act
+        if n.is_mat:
+            return m.t[:b, :w].float().reshape(b, 1, 1, w)
+        return m.t[:b * h * w, :c].reshape(b, h, w, c).permute(0, 3, 1, 2).float().contiguous()
+
+    def _node_store(self, n: Node, t: torch.Tensor, grad: bool = False) -> None:
+        b, c, h, w = n.shape
+        if n.loss_input and not grad:
+            n.f32[:b, :w].copy_(t.reshape(b, w))
+            return
+        m = n.grad if grad else n.act
+        if n.is_mat:
+            m.t[:b, :w].copy_(t.reshape(b, w))
+        else:
+            m.t[:b * h * w, :c].copy_(t.permute(0, 2, 3, 1).reshape(b * h * w, c))
+
+    def _bridge_forward(self, c: Connection, is_train: bool) -> None:
+        for n in c.nodes_in:
+            n.data = self._node_load(n)
+        c.layer.forward(is_train, c.nodes_in, c.nodes_out)
+        for n in set(c.nodes_in + c.nodes_out):
+            self._node_store(n, n.data)
+            n.data = None
+
+    def _bridge_backprop(self, c: Connection, prop_grad: bool) -> None:
+        if c.layer.self_loop:
+            for n in c.nodes_in:
+                n.data = self._node_load(n, grad=True)
+        else:
+            for n in c.nodes_in:
+                n.data = self._node_load(n)
+            for n in c.nodes_out:
+                n.data = self._node_load(n, grad=True)
+        c.layer.backprop(prop_grad, c.nodes_in, c.nodes_out)
+        if prop_grad or c.layer.self_loop:
+            for n in c.nodes_in:
+                self._node_store(n, n.data, grad=True)
+        for n in set(c.nodes_in + c.nodes_out):
+            n.data = None
+
+    # ------------------------------------------------------------------ execution
+    def adjust_batch_size(self, b: int) -> None:
+        assert self.max_batch >= b, "cannot set batch size larger than max batch"
+        if b != self.nodes[0].shape[0]:
+            for n in self.nodes:
+                n.shape[0] = b
+            for c in self.connections:
+                c.layer.on_batch_size_changed(c.nodes_in, c.nodes_out)
+
+    def set_input(self, batch: torch.Tensor, extra: Optional[List[torch.Tensor]] = None) -> None:
+        """copy one (already device-sliced) host batch into node 0 (+ extra data nodes)."""
+        b = batch.shape[0]
+        self.adjust_batch_size(b)
+        extra = extra or []
+        if self.backend == "ref":
+            self.nodes[0].data = batch.to(self.device, non_blocking=True).float().reshape(self.nodes[0].shape)
+            for i, e in enumerate(extra):
+                self.nodes[i + 1].data = e.to(self.device, non_blocking=True).float().reshape(self.nodes[i + 1].shape)
+            return
+        self._stage_in(self.nodes[0], self.in_stage, batch)
+        for i, e in enumerate(extra):
+            self._stage_in(self.nodes[i + 1], self.extra_stage[i], e)
+
+    def _stage_in(self, n: Node, stage: torch.Tensor, batch: torch.Tensor) -> None:
+        b, c, h, w = n.shape
+        st = stage[:b]
+        st.copy_(batch.reshape(st.shape), non_blocking=True)
+        L = ops.lib()
+        if n.is_mat:
+            ops.check(L.cxn_copy2d(st.data_ptr(), w, n.act.ptr, n.act.ld, b, w, 1, 0, ops.stream()), "copy2d")
+        else:
+            ops.check(L.cxn_nchw_f32_to_nhwc_bf16(st.data_ptr(), n.act.ptr, b, c, h * w, n.act.ld, ops.stream()),
+                      "nchw_to_nhwc")
+
+    def forward(self, is_train: bool) -> None:
+        if self.backend == "ref":
+            for c in self.connections:
+                c.layer.forward(is_train, c.nodes_in, c.nodes_out)
+            return
+        if self.exchange is not None:
+            self.exchange.wait_all()
+        for c in self.connections:
+            if c.native:
+                c.layer.b200_forward(self, is_train)
+            else:
+                self._bridge_forward(c, is_train)
+
+    def backprop(self, prop_to_input: bool, need_update: bool, epoch: int) -> None:
+        n = len(self.connections)
+        if self.backend == "ref":
+            for i in range(n - 1, -1, -1):
+                c = self.connections[i]
+                c.layer.backprop(i != 0 or prop_to_input, c.nodes_in, c.nodes_out)
+                if need_update:
+                    for u in self.updaters[i]:
+                        u.update(epoch)
+            return
+        if need_update:
+            self.arena.refresh_hyper(epoch)
+        for i in range(n - 1, -1, -1):
+            c = self.connections[i]
+            prop = i != 0 or prop_to_input
+            if c.native:
+                c.layer.b200_backprop(self, prop)
+            else:
+                self._bridge_backprop(c, prop)
+            if need_update and self.exchange is not None:
+                self.exchange.layer_done(i)
+        if need_update and self.exchange is None:
+            self.arena.update()
+        ops.check(ops.lib().cxn_counter_add(self.step_counter.data_ptr(), 1, ops.stream()), "counter_add")
+
+    def update_all(self, epoch: int) -> None:
+        if self.backend == "ref":
+            for us in self.updaters:
+                for u in us:
+                    u.update(epoch)
+        else:
+            self.arena.refresh_hyper(epoch)
+            self.arena.update()
+
+    def start_round(self, r: int) -> None:
+        for us in self.updaters:
+            for u in us:
+                u.start_round(r)
+        if self.arena is not None:
+            for s in self.arena.segments:
+                s.param.round = r
+
+    # ------------------------------------------------------------------ access
+    def copy_node_data(self, node_id: int) -> torch.Tensor:
+        """fp32 (b,c,h,w) copy of a node on the device."""
+        n = self.nodes[node_id]
+        if self.backend == "ref":
+            return n.data.reshape(n.shape).clone()
+        return self._node_load(n)
+
+    def _find_weight(self, layer_index: int, tag: str):
+        layer = self.connections[layer_index].layer
+        for t, w, g in layer.weights():
+            if t == tag:
+                return layer, w
+        return layer, None
+
+    def get_weight(self, layer_index: int, tag: str):
+        """(2-D flattened weight, original shape) - reference ``visitor.h:25-91`` GetWeightVisitor."""
+        self.sync_weights_from_device()
+        _, w = self._find_weight(layer_index, tag)
+        if w is None:
+            return None, []
+        shape = list(w.shape)
+        return w.reshape(shape[0], -1).detach().cpu().clone(), shape
+
+    def set_weight(self, layer_index: int, weight: torch.Tensor, tag: str) -> None:
+        self.sync_weights_from_device()
+        _, w = self._find_weight(layer_index, tag)
+        if w is None:
+            return
+        if weight.numel() != w.numel():
+            raise ValueError("SetWeight: weight size mismatch")
+        w.copy_(weight.reshape(w.shape).to(w.device))
+        self.sync_weights_to_device()

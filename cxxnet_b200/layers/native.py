@@ -1,0 +1,378 @@
+"""Native sm_100a (``b200`` backend) implementations of the hot layers.
+
+Activations are NHWC bf16 (``ops.DevMat``), weights are fp32 masters in the parameter arena
+(``parallel/arena.py``) with a bf16 shadow that the tcgen05 GEMM reads through TMA.  Each
+class extends the reference-math class from ``zoo.py`` and adds ``b200_*`` methods; the
+reference methods stay available as the oracle.  Kernel inventory: SURVEY.md section 2.9.
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import ops
+from ..ops import DevMat
+from . import zoo
+from .base import Node
+
+
+def _rows(node: Node) -> int:
+    b, c, h, w = node.shape
+    return b if node.is_mat else b * h * w
+
+
+class _ParamBinding:
+    """Arena views handed to a native layer for one tag."""
+    __slots__ = ("w", "g", "shadow", "shadow_ld", "rows", "cols")
+
+    def __init__(self, w, g, shadow, shadow_ld, rows, cols):
+        self.w, self.g, self.shadow, self.shadow_ld, self.rows, self.cols = w, g, shadow, shadow_ld, rows, cols
+
+
+# ----------------------------------------------------------------------------- fullc
+class FullConnectLayer(zoo.FullConnectLayer):
+    """K5/K6: three tcgen05 GEMMs, bias (+ReLU) fused into the forward epilogue."""
+    has_b200 = True
+
+    def __init__(self):
+        super().__init__()
+        self.fuse_relu = False
+        self.bind = {}
+
+    def b200_shadow(self, tag):
+        p = self.param
+        if tag == "wmat":
+            return (p.num_hidden, p.num_input_node, ops.round_up(p.num_input_node, 8))
+        return None
+
+    def b200_forward(self, ex, is_train):
+        p = self.param
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        b = x.shape[0]
+        W = self.bind["wmat"]
+        bias = self.bind["bias"].w.data_ptr() if p.no_bias == 0 else None
+        flags = ops.GEMM_RELU if self.fuse_relu else 0
+        if y.loss_input:
+            dptr, ldd = y.f32.data_ptr(), y.f32.shape[1]
+        else:
+            dptr, ldd = y.act.ptr, y.act.ld
+            flags |= ops.GEMM_OUT_BF16
+        ops.gemm(x.act.ptr, x.act.ld, 0, 0, W.shadow.data_ptr(), W.shadow_ld, 0, 0, dptr, ldd, 0, bias, 0,
+                 b, p.num_hidden, p.num_input_node, flags=flags)
+
+    def b200_backprop(self, ex, prop_grad):
+        p = self.param
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        b = x.shape[0]
+        W = self.bind["wmat"]
+        gy = y.grad
+        if self.fullc_gather == 0 or ex.world_size == 1:
+            # gW (nout x nin) += gy^T . x   : A = gy stored [K=b][M=nout], B = x stored [K=b][N=nin]
+            ops.gemm(gy.ptr, gy.ld, 0, 1, x.act.ptr, x.act.ld, 0, 1, W.g.data_ptr(), p.num_input_node, 0, None, 0,
+                     p.num_hidden, p.num_input_node, b, flags=ops.GEMM_BETA1 if ex.accumulate_grads else 0)
+        if p.no_bias == 0:
+            ops.check(ops.lib().cxn_colsum_bf16(gy.ptr, b, p.num_hidden, gy.ld, self.bind["bias"].g.data_ptr(),
+                                                 1 if ex.accumulate_grads else 0, ops.stream()), "colsum")
+        if prop_grad:
+            # gx (b x nin) = gy (b x nout) . W (nout x nin) : B = W stored [K=nout][N=nin]
+            ops.gemm(gy.ptr, gy.ld, 0, 0, W.shadow.data_ptr(), W.shadow_ld, 0, 1, x.grad.ptr, x.grad.ld, 0, None, 0,
+                     b, p.num_input_node, p.num_hidden, flags=ops.GEMM_OUT_BF16)
+
+
+# ----------------------------------------------------------------------------- conv
+class ConvolutionLayer(zoo.ConvolutionLayer):
+    """K1-K4: NHWC patch gather + tcgen05 GEMM per group (batched over groups in one launch).
+
+    Internal weight layout is ``(g, oc/g, kh, kw, ic/g)`` (channels innermost, matching the
+    NHWC gather); ``weight_to_internal`` / ``weight_from_internal`` convert to and from the
+    checkpoint layout ``(g, oc/g, ic/g*kh*kw)``.
+    """
+    has_b200 = True
+
+    def __init__(self):
+        super().__init__()
+        self.fuse_relu = False
+        self.bind = {}
+        self.col = None
+
+    def b200_supported(self):
+        p = self.param
+        return (p.num_channel // p.num_group) % 8 == 0
+
+    def _geom(self):
+        p = self.param
+        g = p.num_group
+        icg = p.num_input_channel // g
+        kg = icg * p.kernel_height * p.kernel_width
+        return g, icg, p.num_channel // g, kg, ops.round_up(kg, 8)
+
+    def weight_to_internal(self, tag, w):
+        if tag != "wmat":
+            return w
+        p = self.param
+        g, icg, ocg, kg, _ = self._geom()
+        return w.reshape(g, ocg, icg, p.kernel_height, p.kernel_width).permute(0, 1, 3, 4, 2).reshape(g, ocg, kg)
+
+    def weight_from_internal(self, tag, w):
+        if tag != "wmat":
+            return w
+        p = self.param
+        g, icg, ocg, kg, _ = self._geom()
+        return w.reshape(g, ocg, p.kernel_height, p.kernel_width, icg).permute(0, 1, 4, 2, 3).reshape(g, ocg, kg)
+
+    def b200_shadow(self, tag):
+        if tag == "wmat":
+            g, icg, ocg, kg, kpad = self._geom()
+            return (g * ocg, kg, kpad)
+        return None
+
+    def b200_setup(self, ex):
+        g, icg, ocg, kg, kpad = self._geom()
+        y = self.nodes_out[0]
+        max_rows = ex.max_batch * y.shape[2] * y.shape[3]
+        self.col = torch.empty((g * max_rows * kpad,), dtype=torch.bfloat16, device=ex.device)
+
+    def _im2col_args(self, x, y, rows, kpad):
+        p = self.param
+        b, c, h, w = x.shape
+        return (b, h, w, c, p.num_group, p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x,
+                y.shape[2], y.shape[3], kpad, rows * kpad)
+
+    def b200_forward(self, ex, is_train):
+        p = self.param
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        g, icg, ocg, kg, kpad = self._geom()
+        rows = _rows(y)
+        L = ops.lib()
+        ops.check(L.cxn_im2col_nhwc(x.act.ptr, self.col.data_ptr(), *self._im2col_args(x, y, rows, kpad),
+                                    ops.stream()), "im2col")
+        W = self.bind["wmat"]
+        bias = self.bind["bias"].w.data_ptr() if p.no_bias == 0 else None
+        flags = ops.GEMM_OUT_BF16 | (ops.GEMM_RELU if self.fuse_relu else 0)
+        ops.gemm(self.col.data_ptr(), kpad, rows * kpad, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 0,
+                 y.act.ptr, y.act.ld, ocg, bias, ocg, rows, ocg, kg, batch=g, flags=flags)
+
+    def b200_backprop(self, ex, prop_grad):
+        p = self.param
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        g, icg, ocg, kg, kpad = self._geom()
+        rows = _rows(y)
+        gy = y.grad
+        L = ops.lib()
+        W = self.bind["wmat"]
+        if p.no_bias == 0:
+            ops.check(L.cxn_colsum_bf16(gy.ptr, rows, p.num_channel, gy.ld, self.bind["bias"].g.data_ptr(),
+                                        1 if ex.accumulate_grads else 0, ops.stream()), "colsum")
+        # gW[g] (ocg x kg) += gy[g]^T (ocg x rows) . col[g] (rows x kg); split-K over the pixel dimension
+        kb = (rows + 63) // 64
+        tiles = ((ocg + 127) // 128) * ((kg + 127) // 128) * g
+        splits = max(1, min(kb // 4 if kb >= 8 else 1, (2 * ex.num_sms + tiles - 1) // tiles))
+        if not ex.accumulate_grads:
+            ops.check(L.cxn_fill_f32(W.g.data_ptr(), W.g.numel(), 0.0, ops.stream()), "fill")
+        ops.gemm(gy.ptr, gy.ld, ocg, 1, self.col.data_ptr(), kpad, rows * kpad, 1, W.g.data_ptr(), kg, ocg * kg,
+                 None, 0, ocg, kg, rows, batch=g, splits=splits, flags=ops.GEMM_ATOMIC)
+        if prop_grad:
+            # dcol[g] (rows x kg) = gy[g] (rows x ocg) . W[g] (ocg x kg)  -> col buffer, then scatter
+            ops.gemm(gy.ptr, gy.ld, ocg, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 1, self.col.data_ptr(), kpad,
+                     rows * kpad, None, 0, rows, kg, ocg, batch=g, flags=ops.GEMM_OUT_BF16)
+            ops.check(L.cxn_col2im_nhwc(self.col.data_ptr(), x.grad.ptr, *self._im2col_args(x, y, rows, kpad),
+                                        ops.stream()), "col2im")
+
+
+# ----------------------------------------------------------------------------- activations
+class _NativeAct:
+    has_b200 = True
+    act_op = ops.ACT_RELU
+    alias_ok = False    # out node may share the in node's buffers (sign-preserving activations)
+    fused = False       # forward folded into the producing GEMM epilogue
+
+    def _b(self):
+        return getattr(self, "b", 1.0)
+
+    def b200_forward(self, ex, is_train):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        if self.fused:
+            return
+        rows = _rows(x)
+        L = ops.lib()
+        ops.check(L.cxn_act_fwd(x.act.ptr, x.act.ptr, rows, x.act.cols, x.act.ld, self.act_op, self._b(),
+                                ops.stream()), "act_fwd")
+        if y.act.ptr != x.act.ptr:
+            ops.check(L.cxn_copy2d(x.act.ptr, x.act.ld, y.act.ptr, y.act.ld, rows, x.act.cols, 0, 0, ops.stream()),
+                      "copy2d")
+
+    def b200_backprop(self, ex, prop_grad):
+        if not prop_grad:
+            return
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        rows = _rows(x)
+        ops.check(ops.lib().cxn_act_bwd(x.act.ptr, y.grad.ptr, x.grad.ptr, rows, x.act.cols, x.act.ld, self.act_op,
+                                        self._b(), ops.stream()), "act_bwd")
+
+
+class ReluLayer(_NativeAct, zoo.ReluLayer):
+    act_op = ops.ACT_RELU
+    alias_ok = True
+
+
+class SigmoidLayer(_NativeAct, zoo.SigmoidLayer):
+    act_op = ops.ACT_SIGMOID
+
+
+class TanhLayer(_NativeAct, zoo.TanhLayer):
+    act_op = ops.ACT_TANH
+
+
+class XeluLayer(_NativeAct, zoo.XeluLayer):
+    act_op = ops.ACT_XELU
+    alias_ok = True
+
+
+# ----------------------------------------------------------------------------- pooling / lrn
+class _NativePool:
+    has_b200 = True
+    pool_mode = ops.POOL_MAX
+
+    def _args(self):
+        p = self.param
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        b, c, h, w = x.shape
+        return (b, h, w, c, p.kernel_height, p.kernel_width, p.stride, y.shape[2], y.shape[3], self.pool_mode,
+                1 if self.fused_relu else 0)
+
+    def b200_forward(self, ex, is_train):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        ops.check(ops.lib().cxn_pool_fwd(x.act.ptr, y.act.ptr, *self._args(), ops.stream()), "pool_fwd")
+        if self.fused_relu:  # reference applies relu in place on the input node
+            ops.check(ops.lib().cxn_act_fwd(x.act.ptr, x.act.ptr, _rows(x), x.act.cols, x.act.ld, ops.ACT_RELU, 1.0,
+                                            ops.stream()), "act_fwd")
+
+    def b200_backprop(self, ex, prop_grad):
+        if not prop_grad:
+            return
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        ops.check(ops.lib().cxn_pool_bwd(x.act.ptr, y.act.ptr, y.grad.ptr, x.grad.ptr, *self._args(), ops.stream()),
+                  "pool_bwd")
+
+
+class MaxPoolingLayer(_NativePool, zoo.MaxPoolingLayer):
+    pool_mode = ops.POOL_MAX
+
+
+class SumPoolingLayer(_NativePool, zoo.SumPoolingLayer):
+    pool_mode = ops.POOL_SUM
+
+
+class AvgPoolingLayer(_NativePool, zoo.AvgPoolingLayer):
+    pool_mode = ops.POOL_AVG
+
+
+class ReluMaxPoolingLayer(_NativePool, zoo.ReluMaxPoolingLayer):
+    pool_mode = ops.POOL_MAX
+
+
+class LRNLayer(zoo.LRNLayer):
+    """K10/K11: one warp per pixel, channel vector in shared memory; norm is recomputed in
+    backward instead of being stored."""
+    has_b200 = True
+
+    def b200_supported(self):
+        return not self.nodes_in[0].is_mat and self.nodes_in[0].shape[1] * 4 * 3 * 4 <= 48 * 1024
+
+    def b200_forward(self, ex, is_train):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        ops.check(ops.lib().cxn_lrn_fwd(x.act.ptr, y.act.ptr, _rows(x), x.shape[1], self.nsize, self.alpha,
+                                        self.beta, self.knorm, ops.stream()), "lrn_fwd")
+
+    def b200_backprop(self, ex, prop_grad):
+        if not prop_grad:
+            return
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        ops.check(ops.lib().cxn_lrn_bwd(x.act.ptr, y.grad.ptr, x.grad.ptr, _rows(x), x.shape[1], self.nsize,
+                                        self.alpha, self.beta, self.knorm, ops.stream()), "lrn_bwd")
+
+
+# ----------------------------------------------------------------------------- flatten / dropout
+class FlattenLayer(zoo.FlattenLayer):
+    """NHWC -> (c,h,w)-ordered rows, so fullc weights keep the checkpoint's column order."""
+    has_b200 = True
+
+    def _run(self, src, dst, to_chw):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        b, c, h, w = x.shape
+        if x.is_mat:
+            ops.check(ops.lib().cxn_copy2d(src.ptr, src.ld, dst.ptr, dst.ld, b, w, 0, 0, ops.stream()), "copy2d")
+            return
+        hw = h * w
+        if to_chw:
+            ops.check(ops.lib().cxn_bf16_hwc_chw(src.ptr, dst.ptr, b, c, hw, hw * c, dst.ld, c, hw, 1, ops.stream()),
+                      "flatten")
+        else:
+            ops.check(ops.lib().cxn_bf16_hwc_chw(src.ptr, dst.ptr, b, c, hw, src.ld, hw * c, c, hw, 0, ops.stream()),
+                      "unflatten")
+
+    def b200_forward(self, ex, is_train):
+        self._run(self.nodes_in[0].act, self.nodes_out[0].act, True)
+
+    def b200_backprop(self, ex, prop_grad):
+        if prop_grad:
+            self._run(self.nodes_out[0].grad, self.nodes_in[0].grad, False)
+
+
+class DropoutLayer(zoo.DropoutLayer):
+    """K12: Philox mask regenerated from (seed, device step counter); nothing is stored."""
+    has_b200 = True
+
+    def _apply(self, ex, m):
+        n = self.nodes_out[0]
+        seed = (ex.seed * 1000003 + self.layer_index * 7919 + 12345) & 0xFFFFFFFFFFFFFFFF
+        ops.check(ops.lib().cxn_dropout(m.ptr, m.ptr, _rows(n), m.cols, m.ld, self.pkeep, seed,
+                                        ex.step_counter.data_ptr(), ops.stream()), "dropout")
+
+    def b200_forward(self, ex, is_train):
+        if is_train:
+            self._apply(ex, self.nodes_out[0].act)
+
+    def b200_backprop(self, ex, prop_grad):
+        if prop_grad:
+            self._apply(ex, self.nodes_out[0].grad)
+
+
+# ----------------------------------------------------------------------------- losses
+class _NativeLoss:
+    """K13: softmax / sigmoid in place on the fp32 loss node, gradient on device."""
+    has_b200 = True
+    loss_kind = 0       # 0 softmax (class-index label), 1 dense label
+    transform = "none"
+
+    def b200_forward(self, ex, is_train):
+        n = self.nodes_in[0]
+        b, cols = n.shape[0], n.shape[3]
+        L = ops.lib()
+        if self.transform == "softmax":
+            ops.check(L.cxn_softmax_rows(n.f32.data_ptr(), b, cols, n.f32.shape[1], ops.stream()), "softmax")
+        elif self.transform == "sigmoid":
+            ops.check(L.cxn_sigmoid_rows(n.f32.data_ptr(), b, cols, n.f32.shape[1], ops.stream()), "sigmoid")
+
+    def b200_backprop(self, ex, prop_grad):
+        n = self.nodes_in[0]
+        b, cols = n.shape[0], n.shape[3]
+        label = self.label_info.fields[self.target_index]
+        if self.loss_kind == 1 and label.shape[1] != cols:
+            raise ValueError("%s: label size mismatch" % self.type_name)
+        ops.check(ops.lib().cxn_loss_grad(n.f32.data_ptr(), n.f32.shape[1], label.data_ptr(), label.stride(0),
+                                          n.grad.ptr, n.grad.ld, b, cols, self.scale(), self.loss_kind, ops.stream()),
+                  "loss_grad")
+
+
+class SoftmaxLayer(_NativeLoss, zoo.SoftmaxLayer):
+    loss_kind = 0
+    transform = "softmax"
+
+
+class L2LossLayer(_NativeLoss, zoo.L2LossLayer):
+    loss_kind = 1
+
+
+class MultiLogisticLayer(_NativeLoss, zoo.MultiLogisticLayer):
+    loss_kind = 1
+    transform = "sigmoid"

@@ -1,0 +1,145 @@
+"""Flat parameter arenas for the b200 backend.
+
+Every ``(layer, tag)`` weight of a net becomes one *segment* of three flat fp32 device
+buffers - weights ``w``, gradients ``g``, optimiser state ``m`` (``m2`` for adam) - plus a
+bf16 *shadow* buffer holding the GEMM-ready copy of matrix weights (rows padded to 8
+elements for TMA).  Segments are laid out in layer order and aligned to the update chunk, so
+that
+
+* one kernel launch applies sgd / nag / adam to every weight (``cxn_update``, K15), and
+* a layer bucket is a contiguous byte range - exactly what the fused
+  reduce-scatter + update + all-gather kernel (K17, ``parallel/exchange.py``) exchanges over
+  NVLink, in place of the reference's per-key parameter server
+  (reference ``src/updater/async_updater-inl.hpp:94-127``, key = layer*4 + tag
+  ``updater.h:150-173``).
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, List, Optional
+
+import numpy as np
+import torch
+
+from .. import ops
+from ..updaters import UpdaterParam
+
+SEG_DTYPE = np.dtype([
+    ("start", "<i8"), ("n", "<i8"), ("shadow_off", "<i8"), ("cols", "<i4"), ("shadow_ld", "<i4"),
+    ("lr", "<f4"), ("wd", "<f4"), ("momentum", "<f4"), ("clip", "<f4"),
+    ("adam_lr_t", "<f4"), ("beta1", "<f4"), ("beta2", "<f4"), ("pad", "<f4"),
+])
+
+
+class Segment:
+    __slots__ = ("layer_index", "tag", "start", "n", "rows", "cols", "shadow_off", "shadow_ld", "param", "layer",
+                 "beta1", "beta2")
+
+
+class ParamArena:
+    def __init__(self, device: torch.device, updater_type: str,
+                 alloc: Optional[Callable[[int, torch.dtype], torch.Tensor]] = None):
+        self.device = device
+        self.updater_type = updater_type
+        self.kind = {"sgd": ops.UPD_SGD, "nag": ops.UPD_NAG, "adam": ops.UPD_ADAM}[updater_type]
+        self.segments: List[Segment] = []
+        self._alloc = alloc or (lambda n, dt: torch.zeros(n, dtype=dt, device=device))
+        self.chunk = ops.lib().cxn_update_chunk()
+        assert ops.lib().cxn_segment_bytes() == SEG_DTYPE.itemsize
+        self.total = 0
+        self.shadow_total = 0
+        self.w = self.g = self.m = self.m2 = self.shadow = None
+        self.seg_host = None
+        self.seg_dev = None
+        self.chunk_seg = None
+        self.nchunks = 0
+
+    # ------------------------------------------------------------------ layout
+    def add(self, layer, layer_index: int, tag: str, rows: int, cols: int, shadow_ld: int, param: UpdaterParam,
+            beta1: float = 0.1, beta2: float = 0.001) -> Segment:
+        s = Segment()
+        s.layer, s.layer_index, s.tag = layer, layer_index, tag
+        s.rows, s.cols, s.n = rows, cols, rows * cols
+        s.start = self.total
+        self.total += ops.round_up(s.n, self.chunk)
+        s.shadow_ld = shadow_ld
+        if shadow_ld > 0:
+            s.shadow_off = self.shadow_total
+            self.shadow_total += ops.round_up(rows * shadow_ld, 128)
+        else:
+            s.shadow_off = -1
+        s.param, s.beta1, s.beta2 = param, beta1, beta2
+        self.segments.append(s)
+        return s
+
+    def finalize(self) -> None:
+        n = max(self.total, self.chunk)
+        self.w = self._alloc(n, torch.float32)
+        self.g = self._alloc(n, torch.float32)
+        self.m = self._alloc(n, torch.float32)
+        self.m2 = self._alloc(n, torch.float32) if self.kind == ops.UPD_ADAM else None
+        self.shadow = self._alloc(max(self.shadow_total, 128), torch.bfloat16)
+        self.nchunks = self.total // self.chunk
+        cs = np.zeros(max(self.nchunks, 1), dtype=np.int32)
+        for i, s in enumerate(self.segments):
+            cs[s.start // self.chunk:(s.start + ops.round_up(s.n, self.chunk)) // self.chunk] = i
+        self.chunk_seg = torch.from_numpy(cs).to(self.device)
+        self.seg_host = torch.zeros(max(len(self.segments), 1) * SEG_DTYPE.itemsize, dtype=torch.uint8)
+        if self.device.type == "cuda":
+            self.seg_host = self.seg_host.pin_memory()
+        self.seg_dev = torch.zeros_like(self.seg_host, device=self.device)
+        self.refresh_hyper(0)
+
+    # ------------------------------------------------------------------ views
+    def w_view(self, s: Segment) -> torch.Tensor:
+        return self.w[s.start:s.start + s.n]
+
+    def g_view(self, s: Segment) -> torch.Tensor:
+        return self.g[s.start:s.start + s.n]
+
+    def shadow_view(self, s: Segment) -> Optional[torch.Tensor]:
+        if s.shadow_off < 0:
+            return None
+        return self.shadow[s.shadow_off:s.shadow_off + s.rows * s.shadow_ld]
+
+    def chunk_range(self, seg_begin: int, seg_end: int):
+        """chunk interval covering segments [seg_begin, seg_end)."""
+        a = self.segments[seg_begin].start // self.chunk
+        last = self.segments[seg_end - 1]
+        b = (last.start + ops.round_up(last.n, self.chunk)) // self.chunk
+        return a, b
+
+    # ------------------------------------------------------------------ per-step hyper parameters
+    def refresh_hyper(self, epoch: int) -> None:
+        """Evaluate every segment's schedule for update number ``epoch`` and stage the table
+        (reference ``src/updater/param.h:76-94`` ScheduleEpoch)."""
+        arr = np.zeros(max(len(self.segments), 1), dtype=SEG_DTYPE)
+        for i, s in enumerate(self.segments):
+            p = s.param
+            p.schedule_epoch(epoch)
+            arr[i]["start"], arr[i]["n"], arr[i]["shadow_off"] = s.start, s.n, s.shadow_off
+            arr[i]["cols"], arr[i]["shadow_ld"] = max(s.cols, 1), s.shadow_ld
+            arr[i]["lr"], arr[i]["wd"], arr[i]["momentum"], arr[i]["clip"] = p.learning_rate, p.wd, p.momentum, p.clip_gradient
+            if self.kind == ops.UPD_ADAM:
+                fix1 = 1.0 - (1.0 - s.beta1) ** (epoch + 1)
+                fix2 = 1.0 - (1.0 - s.beta2) ** (epoch + 1)
+                arr[i]["adam_lr_t"] = p.base_lr * np.sqrt(fix2) / fix1
+                arr[i]["beta1"], arr[i]["beta2"] = s.beta1, s.beta2
+        self.seg_host.numpy()[:] = np.frombuffer(arr.tobytes(), dtype=np.uint8)
+        self.seg_dev.copy_(self.seg_host, non_blocking=True)
+
+    # ------------------------------------------------------------------ kernels
+    def update(self, chunk_begin: int = 0, chunk_end: Optional[int] = None) -> None:
+        chunk_end = self.nchunks if chunk_end is None else chunk_end
+        if chunk_end <= chunk_begin:
+            return
+        ops.check(ops.lib().cxn_update(
+            self.w.data_ptr(), self.g.data_ptr(), self.m.data_ptr(),
+            self.m2.data_ptr() if self.m2 is not None else None, self.shadow.data_ptr(),
+            self.seg_dev.data_ptr(), self.chunk_seg.data_ptr(), chunk_begin, chunk_end,
+            self.kind, ops.stream()), "cxn_update")
+
+    def refresh_shadow(self) -> None:
+        if self.nchunks:
+            ops.check(ops.lib().cxn_refresh_shadow(self.w.data_ptr(), self.shadow.data_ptr(), self.seg_dev.data_ptr(),
+                                                   self.chunk_seg.data_ptr(), self.nchunks, ops.stream()),
+                      "cxn_refresh_shadow")

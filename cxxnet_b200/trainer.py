@@ -1,0 +1,363 @@
+"""Net trainer: the ``INetTrainer`` surface (reference ``src/nnet/nnet.h:18-92``), implemented in the
+one-process-per-GPU model.
+
+Parity with ``CXXNetThreadTrainer`` (reference ``src/nnet/nnet_impl-inl.hpp:16-455``):
+
+* ``dev`` parser (``cpu``, ``gpu``, ``gpu:0,1,2``, ``gpu:0-3``), ``batch_size`` is the GLOBAL
+  batch split ``ceil(batch/ndev)`` per device (``:147``), surplus devices dropped (``:344-354``);
+* ``update_period`` gradient accumulation, ``eval_train`` train metrics, ``metric`` /
+  ``metric[label,node]`` sets, ``seed``, ``param_server``;
+* ``update`` / ``predict`` / ``extract_feature`` / ``evaluate`` / ``get_weight`` /
+  ``set_weight`` / ``save_model`` / ``load_model`` / ``copy_model_from``.
+
+Where the reference runs one pthread per GPU inside one process and exchanges gradients
+through mshadow-ps, here each rank of a ``torch.distributed`` job owns one device and its
+slice ``[rank*step, (rank+1)*step)`` of every global batch; gradients are exchanged by the
+fused NVLink kernel (``parallel/exchange.py``).  A single process given several devices
+re-launches itself with one worker per device (``parallel/launch.py``).
+"""
+from __future__ import annotations
+
+import io
+import os
+import re
+import sys
+from typing import BinaryIO, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import model_io as mio
+from .config import ConfigPairs
+from .executor import NeuralNet
+from .io.data import DataBatch, IIterator
+from .metrics import MetricSet
+from .netconfig import NetConfig
+
+
+def parse_devices(val: str) -> Tuple[str, List[int]]:
+    """``cpu`` | ``gpu`` | ``gpu:0,1,2`` | ``gpu:0-3`` (reference ``nnet_impl-inl.hpp:32-51``)."""
+    kind = "gpu" if val.startswith("gpu") else "cpu"
+    devs: List[int] = []
+    if ":" in val:
+        spec = val.split(":", 1)[1]
+        m = re.match(r"^(\d+)-(\d+)$", spec)
+        if m:
+            devs = list(range(int(m.group(1)), int(m.group(2)) + 1))
+        else:
+            for p in spec.split(","):
+                if p:
+                    devs.append(int(p))
+    return kind, devs
+
+
+class NetTrainer:
+    def __init__(self, net_type: int = 0):
+        self.net_type = net_type
+        self.cfg: ConfigPairs = []
+        self.net_cfg = NetConfig()
+        self.batch_size = 100
+        self.update_period = 1
+        self.sample_counter = 0
+        self.eval_train = 1
+        self.epoch_counter = 0
+        self.seed = 0
+        self.silent = 0
+        self.type_pserver = "UNSPECIFIED"
+        self.dev_kind = "cpu"
+        self.devices: List[int] = []
+        self.backend_override: Optional[str] = None
+        self.metric = MetricSet()
+        self.train_metric = MetricSet()
+        self.eval_nodes: List[Tuple[str, int]] = []
+        self.eval_req: List[int] = []
+        self.net: Optional[NeuralNet] = None
+        self.rank, self.world_size = 0, 1
+        self.step = 0
+        self._stage = None
+
+    # ------------------------------------------------------------------ configuration
+    def set_param(self, name: str, val: str) -> None:
+        if name == "dev":
+            self.dev_kind, self.devices = parse_devices(val)
+        if name == "batch_size": self.batch_size = int(val)
+        if name == "update_period": self.update_period = int(val)
+        if name == "eval_train": self.eval_train = int(val)
+        if name == "seed": self.seed = int(val)
+        if name == "silent": self.silent = int(val)
+        if name == "param_server": self.type_pserver = val
+        if name == "backend": self.backend_override = val
+        if name.startswith("metric"):
+            m = re.match(r"metric\[([^,]+),([^\]]+)\]", name)
+            if m:
+                self.metric.add_metric(val, m.group(1))
+                self.train_metric.add_metric(val, m.group(1))
+                self.eval_nodes.append((m.group(2), 0))
+            else:
+                # anything else, including ``metric[label]``, evaluates field "label" on the
+                # last node, as the reference's sscanf does (nnet_impl-inl.hpp:57-67)
+                self.metric.add_metric(val, "label")
+                self.train_metric.add_metric(val, "label")
+                self.eval_nodes.append(("", -1))
+        self.cfg.append((name, val))
+
+    # ------------------------------------------------------------------ device / process layout
+    def _resolve_devices(self) -> None:
+        import torch.distributed as dist
+        if self.type_pserver == "dist":
+            raise ValueError("param_server=dist (ps-lite multi-node) is not supported; "
+                             "use a torch.distributed launch over NVLink instead")
+        if dist.is_available() and dist.is_initialized():
+            self.world_size, self.rank = dist.get_world_size(), dist.get_rank()
+        ndev = max(len(self.devices), 1)
+        if self.world_size > 1:
+            ndev = self.world_size
+        step = max((self.batch_size + ndev - 1) // ndev, 1)
+        used = ndev
+        while step * (used - 1) >= self.batch_size and used > 1:
+            used -= 1
+        if used < ndev and self.silent == 0 and self.rank == 0:
+            print("Warning: The number of devices is induce mini-batch=%u\n"
+                  "We can equally use %u devices to cover the batch_size" % (step, used))
+        self.step = step
+        self.active_ranks = used
+        if self.dev_kind == "gpu":
+            if not torch.cuda.is_available():
+                raise RuntimeError("dev=gpu requested but no CUDA device is available")
+            if self.world_size > 1:
+                local = int(os.environ.get("LOCAL_RANK", self.rank))
+                idx = self.devices[local] if local < len(self.devices) else local
+            else:
+                idx = self.devices[0] if self.devices else torch.cuda.current_device()
+                if len(self.devices) > 1:
+                    raise RuntimeError(
+                        "dev lists %d GPUs but this is a single process: launch with "
+                        "`python -m cxxnet_b200.parallel.launch` / torchrun (one rank per GPU)" % len(self.devices))
+            torch.cuda.set_device(idx)
+            self.device = torch.device("cuda", idx)
+            self.backend = self.backend_override or "b200"
+        else:
+            self.device = torch.device("cpu")
+            self.backend = "ref"
+        if self.backend not in ("ref", "b200"):
+            raise ValueError("unknown backend %s" % self.backend)
+
+    def _init_net(self) -> None:
+        assert self.net is None, "net must be empty before this"
+        self.net_cfg.configure(self.cfg)
+        self._resolve_devices()
+        self.net = NeuralNet(self.net_cfg, self.step, self.rank + self.seed * 100, self.device, self.backend,
+                             silent=self.silent or self.rank != 0, world_size=self.world_size, rank=self.rank)
+        if self.silent == 0 and self.rank == 0:
+            print("finish initialization with %d devices" % max(self.world_size, 1))
+        self.eval_req = []
+        for name, flag in self.eval_nodes:
+            if flag < 0:
+                self.eval_req.append(self.net_cfg.num_nodes - 1)
+            else:
+                if name not in self.net_cfg.node_name_map:
+                    raise ValueError("Cannot find node name: %s\n" % name)
+                self.eval_req.append(self.net_cfg.node_name_map[name])
+
+    def _finish_init(self) -> None:
+        self.net.init_updaters()
+        self.net.init_nodes()
+
+    # ------------------------------------------------------------------ model
+    def init_model(self) -> None:
+        self._init_net()
+        if self.world_size > 1:
+            # every rank draws the same initial weights (the reference serialises device 0's model
+            # to the others, nnet_impl-inl.hpp:70-81); the exchange re-broadcasts rank 0's arena.
+            self.net.rng.manual_seed(self.seed * 100)
+        self.net.init_model()
+        self._finish_init()
+        if self.net.exchange is not None:
+            self.net.exchange.broadcast_weights()
+
+    def save_model(self, fo: BinaryIO) -> None:
+        self.net_cfg.save_net(fo)
+        mio.write_i64(fo, self.epoch_counter)
+        blob = io.BytesIO()
+        self.net.save_model(blob)
+        mio.write_str(fo, blob.getvalue())
+
+    def load_model(self, fi: BinaryIO) -> None:
+        self.net_cfg.load_net(fi)
+        self.epoch_counter = mio.read_i64(fi)
+        self.net = None
+        self._init_net()
+        blob = mio.read_bytes(fi)
+        self.net.load_model(io.BytesIO(blob))
+        self._finish_init()
+
+    def copy_model_from(self, fi: BinaryIO) -> None:
+        """finetune: copy layers whose names match (reference ``nnet_impl-inl.hpp:101-134``)."""
+        self.net = None
+        self.init_model()
+        old_cfg = NetConfig()
+        old_cfg.load_net(fi)
+        mio.read_i64(fi)
+        self.epoch_counter = 0
+        old_net = NeuralNet(old_cfg, 1, 0, torch.device("cpu"), "ref", silent=1)
+        old_net.load_model(io.BytesIO(mio.read_bytes(fi)))
+        for i, ol in enumerate(old_cfg.layers):
+            for j, nl in enumerate(self.net_cfg.layers):
+                if ol.name == nl.name and ol.name != "":
+                    print("Copying layer %s" % ol.name)
+                    buf = io.BytesIO()
+                    old_net.connections[i].layer.save_model(buf)
+                    buf.seek(0)
+                    self.net.copy_layer(j, buf)
+
+    def start_round(self, r: int) -> None:
+        self.net.start_round(r)
+
+    # ------------------------------------------------------------------ batch slicing
+    def _slice(self, n: int) -> Tuple[int, int]:
+        begin = min(self.rank * self.step, n)
+        end = min((self.rank + 1) * self.step, n)
+        return begin, end
+
+    def _label_fields(self, label: torch.Tensor, begin: int, end: int, device) -> List[torch.Tensor]:
+        out = []
+        for a, b in self.net_cfg.label_range:
+            out.append(label[begin:end, a:b].to(device, non_blocking=True).float().contiguous())
+        return out
+
+    def _as_tensor(self, x) -> torch.Tensor:
+        if isinstance(x, torch.Tensor):
+            return x
+        return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+
+    # ------------------------------------------------------------------ training
+    def update(self, batch: DataBatch) -> None:
+        """one mini-batch: forward, backprop, (every ``update_period`` calls) weight update
+        (reference ``nnet_impl-inl.hpp:141-185``)."""
+        net = self.net
+        need_update = (self.sample_counter + 1) % self.update_period == 0
+        data = self._as_tensor(batch.data)
+        label = self._as_tensor(batch.label)
+        begin, end = self._slice(batch.batch_size)
+        net.label_info.fields = self._label_fields(label, begin, end, self.device)
+        net.accumulate_grads = self.sample_counter != 0
+        net.set_input(data[begin:end], [self._as_tensor(e)[begin:end] for e in batch.extra_data])
+        net.forward(True)
+        if self.eval_train != 0 and self.eval_req:
+            scores = [self._scores2d(net.copy_node_data(i)) for i in self.eval_req]
+            self.train_metric.add_eval(scores, net.label_info.fields, self.net_cfg.label_name_map)
+        net.backprop(False, need_update, self.epoch_counter)
+        self.sample_counter += 1
+        if self.sample_counter >= self.update_period:
+            self.sample_counter = 0
+            self.epoch_counter += 1
+
+    @staticmethod
+    def _scores2d(t: torch.Tensor) -> torch.Tensor:
+        return t.reshape(t.shape[0], -1)
+
+    # ------------------------------------------------------------------ inference
+    def _forward_to(self, node_ids: List[int], batch: DataBatch) -> List[torch.Tensor]:
+        """forward and return the requested nodes as host fp32 (batch_size, c, h, w) tensors
+        assembled over all ranks (reference ``nnet_impl-inl.hpp:300-325``)."""
+        net = self.net
+        data = self._as_tensor(batch.data)
+        begin, end = self._slice(batch.batch_size)
+        net.set_input(data[begin:end], [self._as_tensor(e)[begin:end] for e in batch.extra_data])
+        net.forward(False)
+        outs = []
+        for nid in node_ids:
+            t = net.copy_node_data(nid)
+            if self.world_size > 1:
+                t = self._gather_rows(t, batch.batch_size)
+            outs.append(t)
+        return outs
+
+    def _gather_rows(self, t: torch.Tensor, total: int) -> torch.Tensor:
+        import torch.distributed as dist
+        full = torch.zeros((self.world_size * self.step,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        pad = torch.zeros((self.step,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        pad[: t.shape[0]] = t
+        dist.all_gather_into_tensor(full, pad)
+        return full[:total]
+
+    def predict(self, batch: DataBatch) -> np.ndarray:
+        """argmax (or the raw value when the output width is 1) per instance (reference ``:186-199``)."""
+        last = len(self.net.nodes) - 1
+        (t,) = self._forward_to([last], batch)
+        t = t.reshape(t.shape[0], -1)
+        if t.shape[1] != 1:
+            mx = t.max(dim=1, keepdim=True).values
+            pred = (t == mx).float().argmax(dim=1).float()
+        else:
+            pred = t[:, 0]
+        return pred.cpu().numpy().astype(np.float32)
+
+    def node_id_from_name(self, node_name: str) -> int:
+        m = re.match(r"top\[-(\d+)\]", node_name)
+        nnode = len(self.net.nodes)
+        if m:
+            offset = int(m.group(1))
+            if not (1 <= offset <= nnode):
+                raise ValueError("ExtractFeature: offset must be within num_node range")
+            return nnode - offset
+        if node_name not in self.net_cfg.node_name_map:
+            raise ValueError("ExtractFeature: Cannot find node name: %s" % node_name)
+        return self.net_cfg.node_name_map[node_name]
+
+    def extract_feature(self, batch: DataBatch, node_name: str) -> np.ndarray:
+        (t,) = self._forward_to([self.node_id_from_name(node_name)], batch)
+        return t.cpu().numpy().astype(np.float32)
+
+    def evaluate(self, iter_eval: Optional[IIterator], data_name: str) -> str:
+        ret = ""
+        if self.eval_train != 0:
+            self._reduce_metric(self.train_metric)
+            ret += self.train_metric.print("train")
+            self.train_metric.clear()
+        if iter_eval is None:
+            return ret
+        self.metric.clear()
+        iter_eval.before_first()
+        while iter_eval.next():
+            batch = iter_eval.value()
+            outs = self._forward_to(self.eval_req, batch)
+            n = batch.batch_size - batch.num_batch_padd
+            label = self._as_tensor(batch.label)
+            fields = [label[:n, a:b].float() for a, b in self.net_cfg.label_range]
+            scores = [o[:n].reshape(n, -1) for o in outs]
+            self.metric.add_eval(scores, fields, self.net_cfg.label_name_map)
+        ret += self.metric.print(data_name)
+        return ret
+
+    def _reduce_metric(self, ms: MetricSet) -> None:
+        if self.world_size <= 1:
+            return
+        import torch.distributed as dist
+        for e in ms.evals:
+            s = e.sum_metric if e.sum_metric is not None else torch.zeros((), dtype=torch.float64, device=self.device)
+            v = torch.stack([s.to(self.device).double(), torch.tensor(float(e.cnt_inst), dtype=torch.float64,
+                                                                       device=self.device)])
+            dist.all_reduce(v)
+            e.sum_metric, e.cnt_inst = v[0], int(v[1].item())
+
+    # ------------------------------------------------------------------ weights
+    def set_weight(self, weight, layer_name: str, tag: str) -> None:
+        if tag not in ("bias", "wmat"):
+            raise ValueError("NNet.SetWeight: weight tag can only be bias or wmat")
+        idx = self.net_cfg.get_layer_index(layer_name)
+        self.net.set_weight(idx, self._as_tensor(weight), tag)
+
+    def get_weight(self, layer_name: str, tag: str):
+        if tag not in ("bias", "wmat"):
+            raise ValueError("NNet.GetWeight: weight tag can only be bias or wmat")
+        idx = self.net_cfg.get_layer_index(layer_name)
+        w, shape = self.net.get_weight(idx, tag)
+        if w is None:
+            return None, []
+        return w.numpy(), shape
+
+
+def create_net(net_type: int = 0) -> NetTrainer:
+    """reference ``nnet.h:99-100`` CreateNet."""
+    return NetTrainer(net_type)

@@ -1,0 +1,107 @@
+"""tcgen05 GEMM (csrc/kernels/gemm_sm100.cu) against a plain PyTorch fp32 reference."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk(rows, cols, ld, batch=1, scale=1.0):
+    t = torch.zeros(batch, rows, ld, dtype=torch.bfloat16, device="cuda")
+    t[:, :, :cols] = (torch.randn(batch, rows, cols, device="cuda") * scale).to(torch.bfloat16)
+    return t
+
+
+def _run(M, N, K, a_mn, b_mn, batch=1, splits=1, relu=False, bias=False, out_bf16=True, atomic=False, beta1=False,
+         bn=0):
+    from cxxnet_b200 import ops
+    r8 = lambda x: ops.round_up(x, 8)
+    torch.manual_seed(M * 7 + N * 3 + K)
+    if a_mn:
+        A = _mk(K, M, r8(M), batch)          # stored [K][M]
+        Af = A[:, :, :M].float().transpose(1, 2)
+        lda, sa = r8(M), K * r8(M)
+    else:
+        A = _mk(M, K, r8(K), batch)
+        Af = A[:, :, :K].float()
+        lda, sa = r8(K), M * r8(K)
+    if b_mn:
+        B = _mk(K, N, r8(N), batch)          # stored [K][N]
+        Bf = B[:, :, :N].float().transpose(1, 2)
+        ldb, sb = r8(N), K * r8(N)
+    else:
+        B = _mk(N, K, r8(K), batch)
+        Bf = B[:, :, :K].float()
+        ldb, sb = r8(K), N * r8(K)
+    ref = torch.bmm(Af, Bf.transpose(1, 2))
+    bias_t = None
+    if bias:
+        bias_t = torch.randn(batch, N, device="cuda")
+        ref = ref + bias_t[:, None, :]
+    if relu:
+        ref = torch.relu(ref)
+    ldd = r8(N)
+    flags = 0
+    if relu: flags |= ops.GEMM_RELU
+    if out_bf16:
+        D = torch.zeros(batch, M, ldd, dtype=torch.bfloat16, device="cuda")
+        flags |= ops.GEMM_OUT_BF16
+    else:
+        D = torch.randn(batch, M, ldd, device="cuda") if (atomic or beta1) else torch.zeros(batch, M, ldd, device="cuda")
+        if atomic or beta1:
+            ref = ref + D[:, :, :N]
+        if atomic: flags |= ops.GEMM_ATOMIC
+        if beta1: flags |= ops.GEMM_BETA1
+    ops.gemm(A.data_ptr(), lda, sa, int(a_mn), B.data_ptr(), ldb, sb, int(b_mn), D.data_ptr(), ldd, M * ldd,
+             bias_t.data_ptr() if bias else None, N, M, N, K, batch=batch, splits=splits, flags=flags, bn=bn)
+    torch.cuda.synchronize()
+    got = D[:, :, :N].float()
+    tol = 2e-2 * max(1.0, float(ref.abs().max())) if out_bf16 else 2e-3 * max(1.0, float(ref.abs().max()))
+    err = float((got - ref).abs().max())
+    assert err <= tol, "M=%d N=%d K=%d a_mn=%d b_mn=%d batch=%d splits=%d: err %g > tol %g" % (
+        M, N, K, a_mn, b_mn, batch, splits, err, tol)
+    if D.shape[2] > N:
+        assert float(D[:, :, N:].abs().max()) == 0.0 or (atomic or beta1), "wrote outside the valid columns"
+
+
+@pytest.mark.parametrize("bn", [64, 128, 256])
+def test_gemm_tn_basic(bn):
+    _run(256, 256, 512, False, False, bn=bn)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (100, 10, 784), (300, 200, 72), (256, 4096, 1024), (1000, 96, 363),
+                                   (129, 257, 65)])
+def test_gemm_tn_shapes(M, N, K):
+    _run(M, N, K, False, False, bias=True, relu=True)
+    _run(M, N, K, False, False, out_bf16=False)
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 512, 128), (100, 784, 100), (333, 72, 96)])
+def test_gemm_k_major_a_mn_major_b(M, N, K):
+    _run(M, N, K, False, True)
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 256), (100, 784, 100), (96, 363, 3000), (10, 100, 100)])
+def test_gemm_mn_major_both(M, N, K):
+    _run(M, N, K, True, True, out_bf16=False)
+    _run(M, N, K, True, True, out_bf16=False, beta1=True)
+
+
+def test_gemm_mn_major_a_k_major_b():
+    _run(192, 160, 320, True, False)
+
+
+def test_gemm_batched_groups():
+    _run(500, 128, 1200, False, False, batch=2, bias=True, relu=True)
+    _run(128, 1200, 500, True, True, batch=2, out_bf16=False)
+
+
+@pytest.mark.parametrize("splits", [2, 5, 16])
+def test_gemm_split_k_atomic(splits):
+    _run(96, 363, 8192, True, True, splits=splits, out_bf16=False, atomic=True)
+    _run(128, 1728, 4096, True, True, batch=2, splits=splits, out_bf16=False, atomic=True)
+
+
+def test_gemm_many_tiles_persistent():
+    # more tiles than SMs: exercises the persistent loop and both TMEM accumulator stages
+    _run(128 * 20, 128 * 12, 256, False, False, bn=128)
+    _run(128 * 40, 256, 192, False, False, bn=64, bias=True)
