@@ -8,9 +8,13 @@
 
 #define CXN_API extern "C" __attribute__((visibility("default")))
 
+// Number of kernel launches issued by this library in this process (bench.py reports it).
+extern "C" unsigned long long cxn_launch_counter_;
+
 // Every launcher returns 0 on success or a cudaError_t / negative framework error.
 #define CXN_CHECK_LAUNCH()                                                     \
   do {                                                                         \
+    ++cxn_launch_counter_;                                                     \
     cudaError_t e__ = cudaGetLastError();                                      \
     if (e__ != cudaSuccess) {                                                  \
       fprintf(stderr, "[cxxnet_b200] %s:%d launch failed: %s\n", __FILE__,     \

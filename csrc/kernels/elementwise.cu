@@ -212,6 +212,9 @@ __global__ void fill_f32_kernel(float* __restrict__ p, long long n, float v) {
 
 using namespace cxn;
 
+extern "C" { unsigned long long cxn_launch_counter_ = 0; }
+CXN_API unsigned long long cxn_launch_count() { return cxn_launch_counter_; }
+
 CXN_API int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C, int HW, int ldc, cudaStream_t st) {
   if (N <= 0 || C <= 0 || HW <= 0) return 0;
   dim3 grid(ceil_div(HW, 32), ceil_div(C, 32), N), block(32, 8);

@@ -467,6 +467,18 @@ class NeuralNet:
         shape = list(w.shape)
         return w.reshape(shape[0], -1).detach().cpu().clone(), shape
 
+    def get_grad(self, layer_index: int, tag: str) -> Optional[torch.Tensor]:
+        """accumulated weight gradient in the checkpoint layout (testing / debugging aid)."""
+        c = self.connections[layer_index]
+        for t, w, g in c.layer.weights():
+            if t != tag:
+                continue
+            if self.arena is not None and c.native:
+                s = self._seg_of[(layer_index, tag)]
+                return c.layer.weight_from_internal(tag, self.arena.g_view(s)).reshape(w.shape).detach().clone()
+            return g.detach().clone()
+        return None
+
     def set_weight(self, layer_index: int, weight: torch.Tensor, tag: str) -> None:
         self.sync_weights_from_device()
         _, w = self._find_weight(layer_index, tag)

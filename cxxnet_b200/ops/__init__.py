@@ -77,10 +77,16 @@ def lib():
     _sig(L.cxn_update, [P, P, P, P, P, P, P, LL, LL, I, P])
     _sig(L.cxn_refresh_shadow, [P, P, P, P, LL, P])
     _sig(L.cxn_counter_add, [P, ULL, P])
+    L.cxn_launch_count.restype = c_ulonglong
     L.cxn_segment_bytes.restype = c_int
     L.cxn_update_chunk.restype = c_int
     _lib = L
     return L
+
+
+def launch_count() -> int:
+    """kernel launches issued by the native library so far in this process."""
+    return int(lib().cxn_launch_count())
 
 
 def stream() -> int:

@@ -1,0 +1,185 @@
+"""Net-level differential tests: every native sm_100a layer against the reference-math backend
+(the `pairtest` idea of reference src/layer/pairtest_layer-inl.hpp applied to whole nets)."""
+import pytest
+import torch
+
+from util import compare_backends, make_batch
+
+pytestmark = pytest.mark.gpu
+
+HEAD = """
+batch_size = %d
+input_shape = %s
+eta = 0.1
+momentum = 0.9
+random_type = xavier
+metric = error
+"""
+
+
+def _conf(body, batch, shape):
+    return "netconfig=start\n" + body + "\nnetconfig=end\n" + HEAD % (batch, shape)
+
+
+def test_mlp_sigmoid_softmax():
+    body = """
+layer[+1] = fullc:fc1
+  nhidden = 100
+layer[+1] = sigmoid
+layer[+1] = fullc:fc2
+  nhidden = 10
+layer[+0] = softmax
+"""
+    compare_backends(_conf(body, 100, "1,1,784"), make_batch((100, 1, 1, 784)))
+
+
+def test_fullc_relu_fused_tanh_l2():
+    body = """
+layer[+1] = fullc:fc1
+  nhidden = 264
+layer[+1] = relu
+layer[+1] = fullc:fc2
+  nhidden = 72
+layer[+1] = tanh
+layer[+1] = fullc:fc3
+  nhidden = 5
+layer[+0] = l2_loss
+  target = vec
+"""
+    compare_backends(_conf(body, 37, "1,1,300") + "label_vec[0,5) = vec\n", make_batch((37, 1, 1, 300), dense_label=5))
+
+
+def test_conv_stride_pad_pool_flatten():
+    body = """
+layer[+1] = conv:cv1
+  kernel_size = 3
+  pad = 1
+  stride = 2
+  nchannel = 32
+layer[+1] = max_pooling
+  kernel_size = 3
+  stride = 2
+layer[+1] = flatten
+layer[+1] = fullc:fc1
+  nhidden = 10
+layer[+0] = softmax
+"""
+    # bf16 activations create exact ties inside max-pool windows (every tied input receives the
+    # gradient, as in the reference's unpool), so gradients below a max-pool carry more noise
+    compare_backends(_conf(body, 20, "1,28,28"), make_batch((20, 1, 28, 28)), check_nodes=[1, 2, 4], tol_grad=0.12)
+
+
+def test_conv_groups_relu_lrn():
+    body = """
+layer[+1] = conv:cv1
+  kernel_size = 5
+  stride = 2
+  nchannel = 16
+layer[+1] = relu
+layer[+1] = max_pooling
+  kernel_size = 3
+  stride = 2
+layer[+1] = lrn
+  local_size = 5
+  alpha = 0.001
+  beta = 0.75
+  knorm = 1
+layer[+1] = conv:cv2
+  kernel_size = 3
+  pad = 1
+  ngroup = 2
+  nchannel = 32
+layer[+1] = relu
+layer[+1] = conv:cv3
+  kernel_size = 3
+  pad = 1
+  ngroup = 2
+  nchannel = 48
+layer[+1] = relu
+layer[+1] = avg_pooling
+  kernel_size = 2
+  stride = 2
+layer[+1] = flatten
+layer[+1] = fullc:fc1
+  nhidden = 7
+layer[+0] = multi_logistic
+  target = vec
+"""
+    compare_backends(_conf(body, 6, "3,37,37") + "label_vec[0,7) = vec\n", make_batch((6, 3, 37, 37), dense_label=7),
+                     tol_grad=0.12)
+
+
+def test_pool_variants_and_xelu():
+    body = """
+layer[+1] = conv:cv1
+  kernel_size = 3
+  nchannel = 8
+layer[+1] = xelu
+  b = 4
+layer[+1] = sum_pooling
+  kernel_size = 2
+  stride = 2
+layer[+1] = conv:cv2
+  kernel_size = 2
+  nchannel = 16
+layer[+1] = relu_max_pooling
+  kernel_size = 3
+  stride = 2
+layer[+1] = flatten
+layer[+1] = fullc:fc1
+  nhidden = 4
+layer[+0] = softmax
+"""
+    compare_backends(_conf(body, 5, "2,19,19"), make_batch((5, 2, 19, 19), nclass=4), tol_grad=0.15)
+
+
+def test_bridged_layers_bn_prelu_concat_split():
+    body = """
+layer[0->1] = conv:cv1
+  kernel_size = 3
+  pad = 1
+  nchannel = 8
+layer[1->2] = batch_norm:bn1
+layer[2->3] = prelu:pr1
+layer[3->4,5] = split
+layer[4->6] = conv:cv2
+  kernel_size = 3
+  pad = 1
+  nchannel = 8
+layer[5->7] = conv:cv3
+  kernel_size = 1
+  nchannel = 8
+layer[6,7->8] = ch_concat
+layer[8->9] = flatten
+layer[9->10] = fullc:fc1
+  nhidden = 6
+layer[10->10] = softmax
+"""
+    compare_backends(_conf(body, 4, "3,9,9") + "eps = 1e-5\n", make_batch((4, 3, 9, 9), nclass=6), tol_grad=8e-2,
+                     skip=("grad[0:bias]",))  # analytically zero: batch_norm removes the conv bias
+
+
+def test_update_matches_reference_sgd_step():
+    """weights after 3 sgd steps (momentum, wd, per-tag lr) agree with the reference backend."""
+    from util import copy_weights, make_trainer, rel_err
+    body = """
+layer[+1] = fullc:fc1
+  nhidden = 64
+layer[+1] = relu
+layer[+1] = fullc:fc2
+  nhidden = 10
+layer[+0] = softmax
+"""
+    conf = _conf(body, 32, "1,1,50") + "wmat:wd = 0.001\nbias:lr = 0.2\n"
+    ref = make_trainer(conf, dev="gpu:0", backend="ref")
+    b2 = make_trainer(conf, dev="gpu:0", backend="b200")
+    copy_weights(ref, b2)
+    for s in range(3):
+        batch = make_batch((32, 1, 1, 50), seed=s)
+        ref.update(batch)
+        b2.update(batch)
+    for name in ("fc1", "fc2"):
+        for tag in ("wmat", "bias"):
+            wr, _ = ref.get_weight(name, tag)
+            wb, _ = b2.get_weight(name, tag)
+            assert rel_err(torch.from_numpy(wr), torch.from_numpy(wb)) < 2e-2, (name, tag)
