@@ -1,0 +1,579 @@
+// Implicit-GEMM convolution on tcgen05 / TMEM for sm_100a (K1-K3 of SURVEY.md section 2.9).
+//
+// No im2col buffer exists: the patch matrix is gathered straight from the NHWC bf16
+// activation tensor into 128B-swizzled shared memory by four producer warps with
+// cp.async (zero-fill for padding), while the dense operand arrives by TMA.
+//
+//   FPROP  y[n,oh,ow, g*Ng + j]  = sum_{kh,kw,c} x[n, oh*s-p+kh, ow*s-p+kw, g*Cg + c] * W[g][j][kh][kw][c]
+//          A = gathered patches (K-major, rows = output pixels), B = W via TMA (K-major)
+//          epilogue: + bias, optional ReLU, bf16 NHWC store.
+//          The same kernel computes backward-data of stride-1 convolutions: gather from dy with
+//          the spatially flipped, channel-transposed filter (cxn_conv_flip_weights).
+//   WGRAD  dW[g][j][kh][kw][c] += sum_{n,oh,ow} dy[n,oh,ow, g*Ng + j] * x[n, oh*s-p+kh, ow*s-p+kw, g*Cg + c]
+//          A = dy via TMA (MN-major), B = gathered patches (MN-major: rows = pixels = reduction),
+//          split-K over pixels, fp32 red.global.add epilogue.
+//
+// Reference behaviour being reproduced: src/layer/convolution_layer-inl.hpp:79-153 (im2col in
+// chunks + one SGEMM per group + col2im); semantics (cross-correlation, zero padding, groups)
+// are identical, the algorithm is not.
+//
+// Warp roles (10 warps, persistent, one CTA per SM):
+//   0 TMA producer | 1 MMA issuer + TMEM owner | 2-5 epilogue | 6-9 gather producers
+// The gather granule is 16 bytes (8 channels) when Cg % 8 == 0, or 8 bytes (one 4-channel
+// pixel) for the 3-channel input layer stored with a channel pitch of 4.
+#include "tc_common.cuh"
+#include <mutex>
+#include <string.h>
+
+namespace cxn {
+namespace igemm {
+
+using namespace cxn::tc;
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int UMMA_K = 16;
+constexpr int kThreads = 320;
+constexpr int kGatherWarp0 = 6;
+constexpr int kGatherThreads = 128;
+constexpr int kAccStages = 2;
+constexpr int kMaxGranules = 2048;  // gather table entries (K / granule)
+
+struct Params {
+  // gathered tensor (NHWC, pixel stride Cs elements)
+  const bf16* src;
+  int N, H, W, Cs;
+  int Cg;          // channels per group as laid out in K (4 in the padded-RGB mode)
+  int KH, KW, stride, pad_y, pad_x;
+  int OH, OW;      // pixel grid enumerated by the GEMM rows
+  int G;
+  int Kg;          // KH*KW*Cg
+  int gran;        // elements per gather granule: 8 or 4
+  int Ng;          // dense-operand extent per group (output channels)
+  int bn;          // tile width actually used (multiple of 16, <= BNMAX)
+  // output
+  void* D;
+  long long ldd, strideD;   // strideD: per-group offset (elements)
+  const float* bias;        // [G*Ng] or null
+  int relu;
+  // wgrad
+  int splits, kb_per_split;
+};
+
+struct GatherEntry { int off; short kh, kw; };
+
+template <int BNMAX>
+struct Cfg {
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BNMAX * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = BNMAX >= 256 ? 4 : 6;
+  static constexpr int kTmemCols = kAccStages * BNMAX;
+  static constexpr int kTableBytes = kMaxGranules * 8;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kTableBytes;
+};
+
+template <int BNMAX, bool WGRAD>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
+  using C = Cfg<BNMAX>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t bar_base = smem_base + C::kStages * C::kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + kAccStages + a); };
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + C::kStages * C::kStageBytes + 8 * (2 * C::kStages + 2 * kAccStages));
+  GatherEntry* table = reinterpret_cast<GatherEntry*>(smem_gen + C::kStages * C::kStageBytes + 256);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const long long rows = (long long)p.N * p.OH * p.OW;
+
+  // GEMM view.  FPROP: M = rows (gathered), N = Ng, K = Kg.   WGRAD: M = Ng, N = Kg (gathered), K = rows.
+  const long long gm = WGRAD ? p.Ng : rows;
+  const int gn = WGRAD ? p.Kg : p.Ng;
+  const long long gk = WGRAD ? rows : p.Kg;
+  const int tiles_m = (int)ceil_div_ll(gm, BM);
+  const int tiles_n = ceil_div(gn, p.bn);
+  const int num_kb = (int)ceil_div_ll(gk, BK);
+  const int splits = WGRAD ? p.splits : 1;
+  const int kbps = WGRAD ? p.kb_per_split : num_kb;
+  const long long total_tiles = (long long)tiles_m * tiles_n * p.G * splits;
+
+  // gather table: granule index -> (element offset of the tap inside the image, kh, kw)
+  const int ngran = p.Kg / p.gran;
+  for (int i = threadIdx.x; i < ngran; i += blockDim.x) {
+    const int k = i * p.gran;
+    const int pos = k / p.Cg, c0 = k - pos * p.Cg;
+    const int kh = pos / p.KW, kw = pos - kh * p.KW;
+    GatherEntry e;
+    e.off = (kh * p.W + kw) * p.Cs + c0;
+    e.kh = (short)kh;
+    e.kw = (short)kw;
+    table[i] = e;
+  }
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(full_bar(s), 1 + kGatherThreads);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < kAccStages; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmDense) : "memory");
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32((const void*)tmem_ptr_smem)),
+                 "n"(C::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  auto decode_tile = [&](long long t, int& n_blk, int& m_blk, int& split, int& g) {
+    long long r = t;
+    n_blk = (int)(r % tiles_n); r /= tiles_n;
+    m_blk = (int)(r % tiles_m); r /= tiles_m;
+    split = (int)(r % splits);
+    g = (int)(r / splits);
+  };
+
+  if (warp == 0) {
+    // =========================== TMA producer (dense operand) ===========================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        int n_blk, m_blk, split, g;
+        decode_tile(t, n_blk, m_blk, split, g);
+        const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * C::kStageBytes;
+          const uint32_t sb = sa + C::kABytes;
+          if (!WGRAD) {
+            // B = W[g] : K-major box {64 (k), bn (n)}
+            mbar_expect_tx(full_bar(stage), (uint32_t)p.bn * BK * 2);
+            tma_load_3d(sb, &tmDense, full_bar(stage), kb * BK, n_blk * p.bn, g);
+          } else {
+            // A = dy[:, g*Ng + m] : MN-major, two boxes {64 (m), 64 (k)}
+            mbar_expect_tx(full_bar(stage), C::kABytes);
+#pragma unroll
+            for (int h = 0; h < BM / 64; ++h)
+              tma_load_3d(sa + h * (64 * BK * 2), &tmDense, full_bar(stage), m_blk * BM + h * 64, kb * BK, g);
+          }
+          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // =========================== MMA issuer ===========================
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((WGRAD ? 1u : 0u) << 15) |
+                             ((WGRAD ? 1u : 0u) << 16) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      constexpr uint32_t kLboMN = 64 * BK * 2;
+      constexpr uint32_t kSbo = 1024;
+      constexpr uint32_t kStep = WGRAD ? (UMMA_K * 128) : (UMMA_K * 2);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        int n_blk, m_blk, split, g;
+        decode_tile(t, n_blk, m_blk, split, g);
+        const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BNMAX);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          fence_proxy_async();   // cp.async (generic proxy) writes -> tensor-core (async proxy) reads
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * C::kStageBytes;
+          const uint32_t sb = sa + C::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t ad = make_desc(sa + k * kStep, WGRAD ? kLboMN : 0u, kSbo);
+            const uint64_t bd = make_desc(sb + k * kStep, WGRAD ? kLboMN : 0u, kSbo);
+            umma_bf16(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar(stage));
+          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(tfull_bar(acc));
+        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= kGatherWarp0) {
+    // =========================== gather producers ===========================
+    const int tp = threadIdx.x - kGatherWarp0 * 32;   // 0..127
+    int stage = 0;
+    uint32_t phase = 0;
+    const int ohw = p.OH * p.OW;
+    for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      int n_blk, m_blk, split, g;
+      decode_tile(t, n_blk, m_blk, split, g);
+      const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
+      if (!WGRAD) {
+        // one A row (output pixel) per thread
+        const long long row = (long long)m_blk * BM + tp;
+        const bool row_ok = row < rows;
+        int n = 0, oh = 0, ow = 0;
+        if (row_ok) {
+          n = (int)(row / ohw);
+          const int r = (int)(row - (long long)n * ohw);
+          oh = r / p.OW;
+          ow = r - oh * p.OW;
+        }
+        const int ih0 = oh * p.stride - p.pad_y, iw0 = ow * p.stride - p.pad_x;
+        // validity masks over kh / kw (KH, KW <= 32)
+        uint32_t mh = 0, mw = 0;
+        if (row_ok) {
+          for (int kh = 0; kh < p.KH; ++kh) if ((unsigned)(ih0 + kh) < (unsigned)p.H) mh |= 1u << kh;
+          for (int kw = 0; kw < p.KW; ++kw) if ((unsigned)(iw0 + kw) < (unsigned)p.W) mw |= 1u << kw;
+        }
+        const bf16* base = p.src + (((long long)n * p.H + ih0) * p.W + iw0) * p.Cs + (long long)g * p.Cg;
+        const uint32_t sw = (uint32_t)(tp & 7);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t dst = smem_base + stage * C::kStageBytes + tp * 128;
+          if (p.gran == 8) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int gi = kb * 8 + j;
+              bool ok = gi < ngran;
+              GatherEntry e = table[ok ? gi : 0];
+              ok = ok && ((mh >> e.kh) & (mw >> e.kw) & 1u);
+              cp_async_16(dst + ((j ^ sw) << 4), ok ? (const void*)(base + e.off) : (const void*)p.src, ok);
+            }
+          } else {
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+              const int gi = kb * 16 + q;
+              bool ok = gi < ngran;
+              GatherEntry e = table[ok ? gi : 0];
+              ok = ok && ((mh >> e.kh) & (mw >> e.kw) & 1u);
+              cp_async_8(dst + (((q >> 1) ^ sw) << 4) + ((q & 1) << 3),
+                         ok ? (const void*)(base + e.off) : (const void*)p.src, ok);
+            }
+          }
+          cp_async_arrive_noinc(full_bar(stage));
+          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+        }
+      } else {
+        // B tile: 64 pixels (reduction rows) x bn reduction-columns, MN-major atoms of [64 rows][128 B].
+        // thread -> pixel row (tp & 63), and every second 16-byte chunk (tp >> 6).
+        const int r = tp & 63;
+        const int half = tp >> 6;
+        const uint32_t sw = (uint32_t)(r & 7);
+        const int natoms = (p.bn + 63) >> 6;
+        const int gpc = 8 / p.gran;   // granules per 16-byte chunk: 1 or 2
+        for (int kb = kb0; kb < kb1; ++kb) {
+          const long long pix = (long long)kb * BK + r;
+          const bool pix_ok = pix < rows;
+          int n = 0, oh = 0, ow = 0;
+          if (pix_ok) {
+            n = (int)(pix / ohw);
+            const int rr = (int)(pix - (long long)n * ohw);
+            oh = rr / p.OW;
+            ow = rr - oh * p.OW;
+          }
+          const int ih0 = oh * p.stride - p.pad_y, iw0 = ow * p.stride - p.pad_x;
+          uint32_t mh = 0, mw = 0;
+          if (pix_ok) {
+            for (int kh = 0; kh < p.KH; ++kh) if ((unsigned)(ih0 + kh) < (unsigned)p.H) mh |= 1u << kh;
+            for (int kw = 0; kw < p.KW; ++kw) if ((unsigned)(iw0 + kw) < (unsigned)p.W) mw |= 1u << kw;
+          }
+          const bf16* base = p.src + (((long long)n * p.H + ih0) * p.W + iw0) * p.Cs + (long long)g * p.Cg;
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sb = smem_base + stage * C::kStageBytes + C::kABytes;
+          for (int a = 0; a < natoms; ++a) {
+            const uint32_t dst = sb + a * (64 * BK * 2) + r * 128;
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+              const int j = jj * 2 + half;                       // 16-byte chunk inside the atom row
+              const int kcol = n_blk * p.bn + a * 64 + j * 8;    // first reduction-column of the chunk
+              if (p.gran == 8) {
+                const int gi = kcol >> 3;
+                bool ok = gi < ngran;
+                GatherEntry e = table[ok ? gi : 0];
+                ok = ok && ((mh >> e.kh) & (mw >> e.kw) & 1u);
+                cp_async_16(dst + ((j ^ sw) << 4), ok ? (const void*)(base + e.off) : (const void*)p.src, ok);
+              } else {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                  const int gi = (kcol >> 2) + h;
+                  bool ok = gi < ngran;
+                  GatherEntry e = table[ok ? gi : 0];
+                  ok = ok && ((mh >> e.kh) & (mw >> e.kw) & 1u);
+                  cp_async_8(dst + ((j ^ sw) << 4) + (h << 3), ok ? (const void*)(base + e.off) : (const void*)p.src,
+                             ok);
+                }
+              }
+            }
+          }
+          (void)gpc;
+          cp_async_arrive_noinc(full_bar(stage));
+          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else {
+    // =========================== epilogue ===========================
+    const int quad = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      int n_blk, m_blk, split, g;
+      decode_tile(t, n_blk, m_blk, split, g);
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const long long row = (long long)m_blk * BM + quad * 32 + lane;
+      const bool row_ok = row < gm;
+      const float* bias = (!WGRAD && p.bias != nullptr) ? p.bias + (long long)g * p.Ng : nullptr;
+#pragma unroll 1
+      for (int c0 = 0; c0 < p.bn; c0 += 32) {
+        const int n0 = n_blk * p.bn + c0;
+        if (n0 >= gn) break;
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BNMAX + c0);
+        tmem_ld32(taddr, v);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        const int lim = min(32, min(p.bn - c0, gn - n0));   // valid columns in this chunk
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        const long long off = (long long)g * p.strideD + row * p.ldd + n0;
+        if (!WGRAD) {
+          if (bias != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < lim) f[j] += __ldg(bias + n0 + j);
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+          }
+          bf16* d = reinterpret_cast<bf16*>(p.D) + off;
+          if (lim == 32 && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+            uint4* d4 = reinterpret_cast<uint4*>(d);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(f[q * 8 + 0], f[q * 8 + 1]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(f[q * 8 + 2], f[q * 8 + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(f[q * 8 + 4], f[q * 8 + 5]);
+              __nv_bfloat162 h3 = __floats2bfloat162_rn(f[q * 8 + 6], f[q * 8 + 7]);
+              uint4 u;
+              u.x = *reinterpret_cast<uint32_t*>(&h0);
+              u.y = *reinterpret_cast<uint32_t*>(&h1);
+              u.z = *reinterpret_cast<uint32_t*>(&h2);
+              u.w = *reinterpret_cast<uint32_t*>(&h3);
+              d4[q] = u;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < lim) d[j] = __float2bfloat16(f[j]);
+          }
+        } else {
+          float* d = reinterpret_cast<float*>(p.D) + off;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < lim) atomicAdd(d + j, f[j]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::kTmemCols)
+                 : "memory");
+  }
+}
+
+// W[g][oc][kh][kw][ic] (ld_in) -> Wt[g][ic][KH-1-kh][KW-1-kw][oc] (ld_out): the filter of the equivalent
+// forward convolution that computes backward-data of a stride-1 convolution.
+__global__ void flip_weights_kernel(const bf16* __restrict__ w, bf16* __restrict__ wt, int G, int ocg, int icg, int KH,
+                                    int KW, int ld_in, int ld_out) {
+  const long long total = (long long)G * ocg * KH * KW * icg;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    long long r = i;
+    const int oc = (int)(r % ocg); r /= ocg;      // fastest in the OUTPUT layout
+    const int kw = (int)(r % KW); r /= KW;
+    const int kh = (int)(r % KH); r /= KH;
+    const int ic = (int)(r % icg);
+    const int g = (int)(r / icg);
+    const bf16 v = w[((long long)g * ocg + oc) * ld_in + ((KH - 1 - kh) * KW + (KW - 1 - kw)) * icg + ic];
+    wt[((long long)g * icg + ic) * ld_out + (kh * KW + kw) * ocg + oc] = v;
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+static int encode3d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1_elems,
+                    uint64_t s2_elems, uint32_t b0, uint32_t b1) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return -2;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) || (s1_elems % 8) || (d2 > 1 && (s2_elems % 8))) {
+    fprintf(stderr, "[cxxnet_b200] conv operand not 16B aligned (ptr=%p s1=%llu s2=%llu)\n", ptr,
+            (unsigned long long)s1_elems, (unsigned long long)s2_elems);
+    return -3;
+  }
+  cuuint64_t gdim[3] = {d0, d1, d2};
+  cuuint64_t gstr[2] = {s1_elems * 2, (d2 > 1 ? s2_elems : s1_elems * d1) * 2};
+  cuuint32_t box[3] = {b0, b1, 1}, estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr, "[cxxnet_b200] conv cuTensorMapEncodeTiled failed: %d\n", (int)r);
+    return -4;
+  }
+  return 0;
+}
+
+template <int BNMAX, bool WGRAD>
+static int launch(const CUtensorMap& tm, const Params& p, int grid, cudaStream_t st) {
+  using C = Cfg<BNMAX>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BNMAX, WGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         C::kSmemBytes);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  conv_igemm_kernel<BNMAX, WGRAD><<<grid, kThreads, C::kSmemBytes, st>>>(tm, p);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+
+static int check_geom(const Params& p) {
+  if (p.KH > 32 || p.KW > 32) return -10;
+  if (p.gran != 8 && p.gran != 4) return -11;
+  if (p.gran == 4 && p.Cg != 4) return -12;
+  if (p.Cg % p.gran) return -13;
+  if (p.Kg / p.gran > kMaxGranules) return -14;
+  if (p.Cs % p.gran || (reinterpret_cast<uintptr_t>(p.src) & (p.gran * 2 - 1))) return -15;
+  return 0;
+}
+
+// pick the tile width: the smallest multiple of 16 that covers n in the fewest tiles
+static int pick_bn(int n, int bnmax) {
+  const int tiles = ceil_div(n, bnmax);
+  int bn = ceil_div(ceil_div(n, tiles), 16) * 16;
+  return bn < 16 ? 16 : bn;
+}
+
+}  // namespace igemm
+}  // namespace cxn
+
+using namespace cxn;
+using namespace cxn::igemm;
+
+// Forward convolution (and stride-1 backward-data with flipped filters).
+//   src  NHWC bf16 [N][H][W][Cs]; group g reads channels [g*Cg, (g+1)*Cg)   (gran 8: Cg % 8 == 0;
+//        gran 4: single group, Cg = Cs = 4 = RGB padded to 4)
+//   w    bf16 [G][Ng][ldw >= KH*KW*Cg] with the reduction ordered (kh, kw, c)
+//   y    NHWC bf16 [N*OH*OW][ldy], group g writes columns [g*Ng, (g+1)*Ng)
+CXN_API int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
+                           long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                           void* y, long long ldy, const float* bias, int relu, cudaStream_t st) {
+  Params p;
+  memset(&p, 0, sizeof(p));
+  p.src = (const bf16*)src; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
+  p.stride = stride; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
+  p.gran = gran; p.Ng = Ng; p.D = y; p.ldd = ldy; p.strideD = Ng; p.bias = bias; p.relu = relu;
+  p.splits = 1; p.kb_per_split = 0;
+  int rc = check_geom(p);
+  if (rc) return rc;
+  const long long rows = (long long)N * OH * OW;
+  if (rows <= 0) return 0;
+  const int bnmax = Ng > 128 ? 256 : 128;
+  p.bn = pick_bn(Ng, bnmax);
+  CUtensorMap tm;
+  rc = encode3d(&tm, w, (uint64_t)p.Kg, (uint64_t)Ng, (uint64_t)G, (uint64_t)ldw, (uint64_t)Ng * ldw, BK, p.bn);
+  if (rc) return rc;
+  const long long tiles = ceil_div_ll(rows, BM) * ceil_div(Ng, p.bn) * G;
+  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  return bnmax == 256 ? launch<256, false>(tm, p, grid, st) : launch<128, false>(tm, p, grid, st);
+}
+
+// Weight gradient: dw[g][j][(kh,kw,c)] += sum_pixels dy[pixel][g*Ng + j] * patch(pixel)[(kh,kw,c)]  (fp32, atomics)
+CXN_API int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
+                           long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                           float* dw, long long lddw, int splits, cudaStream_t st) {
+  Params p;
+  memset(&p, 0, sizeof(p));
+  p.src = (const bf16*)src; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
+  p.stride = stride; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
+  p.gran = gran; p.Ng = Ng; p.D = dw; p.ldd = lddw; p.strideD = (long long)Ng * lddw; p.bias = nullptr; p.relu = 0;
+  int rc = check_geom(p);
+  if (rc) return rc;
+  const long long rows = (long long)N * OH * OW;
+  if (rows <= 0) return 0;
+  const int bnmax = 256;
+  p.bn = pick_bn(p.Kg, bnmax);
+  if (p.bn % 64) p.bn = ceil_div(p.bn, 64) * 64;   // gathered MN-major operand is built from 64-wide atoms
+  const int num_kb = (int)ceil_div_ll(rows, BK);
+  const long long base_tiles = (long long)ceil_div(Ng, BM) * ceil_div(p.Kg, p.bn) * G;
+  if (splits <= 0) {
+    splits = (int)((2LL * num_sms() + base_tiles - 1) / base_tiles);
+    const int max_splits = num_kb / 8 > 0 ? num_kb / 8 : 1;
+    if (splits > max_splits) splits = max_splits;
+  }
+  if (splits > num_kb) splits = num_kb;
+  if (splits < 1) splits = 1;
+  p.kb_per_split = ceil_div(num_kb, splits);
+  p.splits = ceil_div(num_kb, p.kb_per_split);
+  CUtensorMap tm;
+  rc = encode3d(&tm, dy, (uint64_t)Ng, (uint64_t)rows, (uint64_t)G, (uint64_t)lddy, (uint64_t)Ng, 64, BK);
+  if (rc) return rc;
+  const long long tiles = base_tiles * p.splits;
+  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  return launch<256, true>(tm, p, grid, st);
+}
+
+CXN_API int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in,
+                                  int ld_out, cudaStream_t st) {
+  const long long total = (long long)G * ocg * KH * KW * icg;
+  if (total <= 0) return 0;
+  flip_weights_kernel<<<ew_grid(total, 256), 256, 0, st>>>((const bf16*)w, (bf16*)wt, G, ocg, icg, KH, KW, ld_in, ld_out);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}

@@ -25,6 +25,26 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, bf16* __restr
     if (hw < HW && c < C) d[(long long)hw * ldc + c] = __float2bfloat16(tile[threadIdx.x][i]);
   }
 }
+// small-C variant (C <= 4, ldc == 4): one pixel per thread, channel planes read coalesced,
+// one 8-byte store per pixel (pad channels written as zero)
+__global__ void nchw_to_nhwc4_kernel(const float* __restrict__ src, bf16* __restrict__ dst, long long total, int C,
+                                     int HW) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long n = i / HW;
+    const int hw = (int)(i - n * HW);
+    const float* s = src + n * C * HW + hw;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (c < C) v[c] = s[(long long)c * HW];
+    __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&a);
+    o.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(dst + i * 4) = o;
+  }
+}
 // src bf16 [N][HW][ldc] -> dst fp32 [N][C][HW]
 __global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ src, float* __restrict__ dst, int N, int C, int HW,
                                     int ldc) {
@@ -217,6 +237,12 @@ CXN_API unsigned long long cxn_launch_count() { return cxn_launch_counter_; }
 
 CXN_API int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C, int HW, int ldc, cudaStream_t st) {
   if (N <= 0 || C <= 0 || HW <= 0) return 0;
+  if (C <= 4 && ldc == 4 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0) {
+    const long long total = (long long)N * HW;
+    nchw_to_nhwc4_kernel<<<ew_grid(total, 256, 16), 256, 0, st>>>(src, (bf16*)dst, total, C, HW);
+    CXN_CHECK_LAUNCH();
+    return 0;
+  }
   dim3 grid(ceil_div(HW, 32), ceil_div(C, 32), N), block(32, 8);
   nchw_to_nhwc_kernel<<<grid, block, 0, st>>>(src, (bf16*)dst, N, C, HW, ldc);
   CXN_CHECK_LAUNCH();

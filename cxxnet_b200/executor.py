@@ -216,13 +216,21 @@ class NeuralNet:
                     producer[n.index] = c
             if isinstance(c.layer, native._NativeLoss) and c.native:
                 c.nodes_in[0].loss_input = True
+        # kernel-path planning (may ask for a padded channel pitch on the input node)
+        pitch: Dict[int, int] = {}
+        for c in self.connections:
+            if c.native and hasattr(c.layer, "b200_plan"):
+                x = c.nodes_in[0]
+                want = c.layer.b200_plan(self, x.index == 0, consumers.get(x.index, 0) == 1)
+                if want:
+                    pitch[x.index] = want
         # node buffers
         for n in self.nodes:
             b, ch, h, w = n.shape
             n.shape[0] = self.max_batch
             rows = self.max_batch if n.is_mat else self.max_batch * h * w
             cols = w if n.is_mat else ch
-            ld = ops.round_up(cols, 8) if n.is_mat else cols
+            ld = ops.round_up(cols, 8) if n.is_mat else pitch.get(n.index, cols)
             n.act = ops.DevMat(rows, cols, ld, device=self.device)
             n.grad = ops.DevMat(rows, cols, ld, device=self.device)
             if n.loss_input:

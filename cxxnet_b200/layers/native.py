@@ -80,11 +80,19 @@ class FullConnectLayer(zoo.FullConnectLayer):
 
 # ----------------------------------------------------------------------------- conv
 class ConvolutionLayer(zoo.ConvolutionLayer):
-    """K1-K4: NHWC patch gather + tcgen05 GEMM per group (batched over groups in one launch).
+    """K1-K4 on tensor cores.
+
+    Default path: implicit GEMM (``csrc/kernels/conv_igemm_sm100.cu``) - no im2col buffer; the
+    patch operand is gathered by cp.async producer warps, the filter / dy operand arrives by
+    TMA, groups are one batched launch.  Forward fuses bias (+ReLU); backward-data of stride-1
+    convolutions is the same kernel run on dy with flipped filters; backward-weight is the
+    split-K variant with fp32 atomics.  Shapes the implicit kernel does not cover (channel
+    counts that are not a multiple of 8, strided backward-data) use an explicit NHWC patch
+    gather + the plain tcgen05 GEMM.
 
     Internal weight layout is ``(g, oc/g, kh, kw, ic/g)`` (channels innermost, matching the
-    NHWC gather); ``weight_to_internal`` / ``weight_from_internal`` convert to and from the
-    checkpoint layout ``(g, oc/g, ic/g*kh*kw)``.
+    NHWC gather; a 3-channel input is padded to 4); ``weight_to_internal`` /
+    ``weight_from_internal`` convert to and from the checkpoint layout ``(g, oc/g, ic/g*kh*kw)``.
     """
     has_b200 = True
 
@@ -93,15 +101,40 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         self.fuse_relu = False
         self.bind = {}
         self.col = None
+        self.wflip = None
+        self.cin_pad = 0        # 4 when a <=4-channel input is stored with a channel pitch of 4
+        self.igemm_fwd = False
+        self.igemm_dgrad = False
 
     def b200_supported(self):
         p = self.param
         return (p.num_channel // p.num_group) % 8 == 0
 
-    def _geom(self):
+    def b200_plan(self, ex, input_is_node0: bool, sole_consumer: bool):
+        """decide kernel paths (called before buffers and the parameter arena are laid out)."""
         p = self.param
         g = p.num_group
         icg = p.num_input_channel // g
+        small = p.kernel_height <= 32 and p.kernel_width <= 32
+        if icg % 8 == 0 and small and (p.kernel_height * p.kernel_width * icg) // 8 <= 2048:
+            self.igemm_fwd = True
+        elif (g == 1 and p.num_input_channel <= 4 and input_is_node0 and sole_consumer and small):
+            self.igemm_fwd = True
+            self.cin_pad = 4
+        ocg = p.num_channel // g
+        pad_ok = p.kernel_height - 1 - p.pad_y >= 0 and p.kernel_width - 1 - p.pad_x >= 0
+        self.igemm_dgrad = (self.igemm_fwd and p.stride == 1 and ocg % 8 == 0 and pad_ok
+                            and (p.kernel_height * p.kernel_width * ocg) // 8 <= 2048)
+        return self.cin_pad
+
+    def _icg(self):
+        p = self.param
+        return self.cin_pad if self.cin_pad else p.num_input_channel // p.num_group
+
+    def _geom(self):
+        p = self.param
+        g = p.num_group
+        icg = self._icg()
         kg = icg * p.kernel_height * p.kernel_width
         return g, icg, p.num_channel // g, kg, ops.round_up(kg, 8)
 
@@ -110,14 +143,20 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             return w
         p = self.param
         g, icg, ocg, kg, _ = self._geom()
-        return w.reshape(g, ocg, icg, p.kernel_height, p.kernel_width).permute(0, 1, 3, 4, 2).reshape(g, ocg, kg)
+        cin = p.num_input_channel // g
+        w5 = w.reshape(g, ocg, cin, p.kernel_height, p.kernel_width).permute(0, 1, 3, 4, 2)
+        if icg != cin:
+            w5 = torch.nn.functional.pad(w5, (0, icg - cin))
+        return w5.reshape(g, ocg, kg)
 
     def weight_from_internal(self, tag, w):
         if tag != "wmat":
             return w
         p = self.param
         g, icg, ocg, kg, _ = self._geom()
-        return w.reshape(g, ocg, p.kernel_height, p.kernel_width, icg).permute(0, 1, 4, 2, 3).reshape(g, ocg, kg)
+        cin = p.num_input_channel // g
+        w5 = w.reshape(g, ocg, p.kernel_height, p.kernel_width, icg)[..., :cin]
+        return w5.permute(0, 1, 4, 2, 3).reshape(g, ocg, cin * p.kernel_height * p.kernel_width)
 
     def b200_shadow(self, tag):
         if tag == "wmat":
@@ -126,10 +165,15 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         return None
 
     def b200_setup(self, ex):
+        p = self.param
         g, icg, ocg, kg, kpad = self._geom()
         y = self.nodes_out[0]
-        max_rows = ex.max_batch * y.shape[2] * y.shape[3]
-        self.col = torch.empty((g * max_rows * kpad,), dtype=torch.bfloat16, device=ex.device)
+        if not self.igemm_fwd or not self.igemm_dgrad:
+            max_rows = ex.max_batch * y.shape[2] * y.shape[3]
+            self.col = torch.empty((g * max_rows * kpad,), dtype=torch.bfloat16, device=ex.device)
+        if self.igemm_dgrad:
+            self.wflip_ld = ops.round_up(p.kernel_height * p.kernel_width * ocg, 8)
+            self.wflip = torch.zeros((g * icg * self.wflip_ld,), dtype=torch.bfloat16, device=ex.device)
 
     def _im2col_args(self, x, y, rows, kpad):
         p = self.param
@@ -143,10 +187,17 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         g, icg, ocg, kg, kpad = self._geom()
         rows = _rows(y)
         L = ops.lib()
-        ops.check(L.cxn_im2col_nhwc(x.act.ptr, self.col.data_ptr(), *self._im2col_args(x, y, rows, kpad),
-                                    ops.stream()), "im2col")
         W = self.bind["wmat"]
         bias = self.bind["bias"].w.data_ptr() if p.no_bias == 0 else None
+        b, c, h, w = x.shape
+        if self.igemm_fwd:
+            ops.check(L.cxn_conv_fprop(x.act.ptr, b, h, w, x.act.ld, icg, g, 4 if self.cin_pad else 8,
+                                       W.shadow.data_ptr(), kpad, ocg, p.kernel_height, p.kernel_width, p.stride,
+                                       p.pad_y, p.pad_x, y.shape[2], y.shape[3], y.act.ptr, y.act.ld, bias,
+                                       1 if self.fuse_relu else 0, ops.stream()), "conv_fprop")
+            return
+        ops.check(L.cxn_im2col_nhwc(x.act.ptr, self.col.data_ptr(), *self._im2col_args(x, y, rows, kpad),
+                                    ops.stream()), "im2col")
         flags = ops.GEMM_OUT_BF16 | (ops.GEMM_RELU if self.fuse_relu else 0)
         ops.gemm(self.col.data_ptr(), kpad, rows * kpad, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 0,
                  y.act.ptr, y.act.ld, ocg, bias, ocg, rows, ocg, kg, batch=g, flags=flags)
@@ -159,23 +210,41 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         gy = y.grad
         L = ops.lib()
         W = self.bind["wmat"]
+        b, c, h, w = x.shape
         if p.no_bias == 0:
             ops.check(L.cxn_colsum_bf16(gy.ptr, rows, p.num_channel, gy.ld, self.bind["bias"].g.data_ptr(),
                                         1 if ex.accumulate_grads else 0, ops.stream()), "colsum")
-        # gW[g] (ocg x kg) += gy[g]^T (ocg x rows) . col[g] (rows x kg); split-K over the pixel dimension
-        kb = (rows + 63) // 64
-        tiles = ((ocg + 127) // 128) * ((kg + 127) // 128) * g
-        splits = max(1, min(kb // 4 if kb >= 8 else 1, (2 * ex.num_sms + tiles - 1) // tiles))
-        if not ex.accumulate_grads:
-            ops.check(L.cxn_fill_f32(W.g.data_ptr(), W.g.numel(), 0.0, ops.stream()), "fill")
-        ops.gemm(gy.ptr, gy.ld, ocg, 1, self.col.data_ptr(), kpad, rows * kpad, 1, W.g.data_ptr(), kg, ocg * kg,
-                 None, 0, ocg, kg, rows, batch=g, splits=splits, flags=ops.GEMM_ATOMIC)
-        if prop_grad:
-            # dcol[g] (rows x kg) = gy[g] (rows x ocg) . W[g] (ocg x kg)  -> col buffer, then scatter
-            ops.gemm(gy.ptr, gy.ld, ocg, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 1, self.col.data_ptr(), kpad,
-                     rows * kpad, None, 0, rows, kg, ocg, batch=g, flags=ops.GEMM_OUT_BF16)
-            ops.check(L.cxn_col2im_nhwc(self.col.data_ptr(), x.grad.ptr, *self._im2col_args(x, y, rows, kpad),
-                                        ops.stream()), "col2im")
+        # weight gradient (accumulates into the arena gradient, which the updater leaves zeroed)
+        if self.igemm_fwd:
+            ops.check(L.cxn_conv_wgrad(x.act.ptr, b, h, w, x.act.ld, icg, g, 4 if self.cin_pad else 8, gy.ptr, gy.ld,
+                                       ocg, p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x, y.shape[2],
+                                       y.shape[3], W.g.data_ptr(), kg, 0, ops.stream()), "conv_wgrad")
+        else:
+            kb = (rows + 63) // 64
+            tiles = ((ocg + 127) // 128) * ((kg + 127) // 128) * g
+            splits = max(1, min(kb // 4 if kb >= 8 else 1, (2 * ex.num_sms + tiles - 1) // tiles))
+            if prop_grad and not self.igemm_dgrad:
+                pass  # col still holds the forward patches
+            ops.gemm(gy.ptr, gy.ld, ocg, 1, self.col.data_ptr(), kpad, rows * kpad, 1, W.g.data_ptr(), kg, ocg * kg,
+                     None, 0, ocg, kg, rows, batch=g, splits=splits, flags=ops.GEMM_ATOMIC)
+        if not prop_grad:
+            return
+        if self.igemm_dgrad:
+            kh, kw = p.kernel_height, p.kernel_width
+            ops.check(L.cxn_conv_flip_weights(W.shadow.data_ptr(), self.wflip.data_ptr(), g, ocg, icg, kh, kw, kpad,
+                                              self.wflip_ld, ops.stream()), "flip_weights")
+            ops.check(L.cxn_conv_fprop(gy.ptr, b, y.shape[2], y.shape[3], gy.ld, ocg, g, 8, self.wflip.data_ptr(),
+                                       self.wflip_ld, icg, kh, kw, 1, kh - 1 - p.pad_y, kw - 1 - p.pad_x, h, w,
+                                       x.grad.ptr, x.grad.ld, None, 0, ops.stream()), "conv_dgrad")
+            return
+        if self.igemm_fwd:
+            # strided backward-data: explicit dcol = gy . W, then scatter
+            pass
+        ops.gemm(gy.ptr, gy.ld, ocg, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 1, self.col.data_ptr(), kpad,
+                 rows * kpad, None, 0, rows, kg, ocg, batch=g, flags=ops.GEMM_OUT_BF16)
+        ops.check(L.cxn_col2im_nhwc(self.col.data_ptr(), x.grad.ptr, b, h, w, x.act.ld, p.num_group, p.kernel_height,
+                                    p.kernel_width, p.stride, p.pad_y, p.pad_x, y.shape[2], y.shape[3], kpad,
+                                    rows * kpad, ops.stream()), "col2im")
 
 
 # ----------------------------------------------------------------------------- activations

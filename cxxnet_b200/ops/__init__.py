@@ -67,6 +67,9 @@ def lib():
     _sig(L.cxn_fill_f32, [P, LL, F, P])
     _sig(L.cxn_im2col_nhwc, [P, P, I, I, I, I, I, I, I, I, I, I, I, I, I, LL, P])
     _sig(L.cxn_col2im_nhwc, [P, P, I, I, I, I, I, I, I, I, I, I, I, I, I, LL, P])
+    _sig(L.cxn_conv_fprop, [P, I, I, I, I, I, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, P, I, P])
+    _sig(L.cxn_conv_wgrad, [P, I, I, I, I, I, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, I, P])
+    _sig(L.cxn_conv_flip_weights, [P, P, I, I, I, I, I, I, I, P])
     _sig(L.cxn_pool_fwd, [P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(L.cxn_pool_bwd, [P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(L.cxn_lrn_fwd, [P, P, LL, I, I, F, F, F, P])

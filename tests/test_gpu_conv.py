@@ -1,0 +1,98 @@
+"""Implicit-GEMM convolution kernels (csrc/kernels/conv_igemm_sm100.cu) against torch conv2d in
+fp32 on the same bf16-rounded operands."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(t):
+    return t.to(torch.bfloat16)
+
+
+def _case(N, C, H, W, OC, G, KH, KW, stride, pad, relu=True, c_pitch=None):
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    torch.manual_seed(N + C + H + OC)
+    Cs = c_pitch or C
+    icg_int = (Cs if c_pitch else C) // G          # channels per group as laid out in K
+    ocg = OC // G
+    x = _bf(torch.randn(N, H, W, C, device="cuda"))
+    xs = torch.zeros(N, H, W, Cs, dtype=torch.bfloat16, device="cuda")
+    xs[..., :C] = x
+    w = _bf(torch.randn(OC, C // G, KH, KW, device="cuda") * (1.0 / (C // G * KH * KW) ** 0.5))
+    bias = torch.randn(OC, device="cuda")
+    OH, OW = (H + 2 * pad - KH) // stride + 1, (W + 2 * pad - KW) // stride + 1
+    # internal weight layout [G][ocg][kh][kw][icg_int], row pitch padded to 8
+    kg = KH * KW * icg_int
+    kpad = ops.round_up(kg, 8)
+    wi = torch.zeros(G, ocg, KH, KW, icg_int, dtype=torch.bfloat16, device="cuda")
+    wi[..., :C // G] = w.view(G, ocg, C // G, KH, KW).permute(0, 1, 3, 4, 2)
+    wsh = torch.zeros(G * ocg, kpad, dtype=torch.bfloat16, device="cuda")
+    wsh[:, :kg] = wi.reshape(G * ocg, kg)
+    gran = 4 if c_pitch == 4 else 8
+    # ---- forward
+    y = torch.zeros(N * OH * OW, OC, dtype=torch.bfloat16, device="cuda")
+    ops.check(L.cxn_conv_fprop(xs.data_ptr(), N, H, W, Cs, icg_int, G, gran, wsh.data_ptr(), kpad, ocg, KH, KW, stride,
+                               pad, pad, OH, OW, y.data_ptr(), OC, bias.data_ptr(), 1 if relu else 0, ops.stream()),
+              "fprop")
+    xr = x.float().permute(0, 3, 1, 2)
+    ref = F.conv2d(xr, w.float(), bias, stride=stride, padding=pad, groups=G)
+    if relu:
+        ref = torch.relu(ref)
+    got = y.float().view(N, OH, OW, OC).permute(0, 3, 1, 2)
+    err = float((got - ref).abs().max())
+    assert err <= 2e-2 * max(1.0, float(ref.abs().max())), "fprop err %g" % err
+    # ---- weight gradient
+    dy = _bf(torch.randn(N, OH, OW, OC, device="cuda") * 0.1)
+    dw = torch.zeros(G * ocg, kg, dtype=torch.float32, device="cuda")
+    ops.check(L.cxn_conv_wgrad(xs.data_ptr(), N, H, W, Cs, icg_int, G, gran, dy.data_ptr(), OC, ocg, KH, KW, stride,
+                               pad, pad, OH, OW, dw.data_ptr(), kg, 0, ops.stream()), "wgrad")
+    dwr = torch.nn.grad.conv2d_weight(xr, w.shape, dy.float().permute(0, 3, 1, 2), stride=stride, padding=pad, groups=G)
+    gotw = dw.view(G, ocg, KH, KW, icg_int)[..., :C // G].permute(0, 1, 4, 2, 3).reshape(OC, C // G, KH, KW)
+    errw = float((gotw - dwr).abs().max())
+    assert errw <= 5e-3 * max(1.0, float(dwr.abs().max())), "wgrad err %g (max %g)" % (errw, float(dwr.abs().max()))
+    if c_pitch:
+        assert float(dw.view(G, ocg, KH, KW, icg_int)[..., C // G:].abs().max()) == 0.0
+    # ---- backward data (stride 1 only: forward kernel on dy with flipped filters)
+    if stride == 1 and not c_pitch:
+        icg = C // G
+        kf = KH * KW * ocg
+        kfpad = ops.round_up(kf, 8)
+        wt = torch.zeros(G * icg, kfpad, dtype=torch.bfloat16, device="cuda")
+        ops.check(L.cxn_conv_flip_weights(wsh.data_ptr(), wt.data_ptr(), G, ocg, icg, KH, KW, kpad, kfpad, ops.stream()),
+                  "flip")
+        dx = torch.zeros(N * H * W, C, dtype=torch.bfloat16, device="cuda")
+        ops.check(L.cxn_conv_fprop(dy.data_ptr(), N, OH, OW, OC, ocg, G, 8, wt.data_ptr(), kfpad, icg, KH, KW, 1,
+                                   KH - 1 - pad, KW - 1 - pad, H, W, dx.data_ptr(), C, None, 0, ops.stream()), "dgrad")
+        dxr = torch.nn.grad.conv2d_input(xr.shape, w.float(), dy.float().permute(0, 3, 1, 2), stride=1, padding=pad,
+                                         groups=G)
+        gotx = dx.float().view(N, H, W, C).permute(0, 3, 1, 2)
+        errx = float((gotx - dxr).abs().max())
+        assert errx <= 2e-2 * max(1.0, float(dxr.abs().max())), "dgrad err %g" % errx
+    torch.cuda.synchronize()
+
+
+def test_conv_rgb_stride4_pitch4():
+    _case(4, 3, 67, 67, 96, 1, 11, 11, 4, 0, c_pitch=4)          # AlexNet conv1 shape family
+
+
+def test_conv_grouped_5x5():
+    _case(3, 96, 27, 27, 256, 2, 5, 5, 1, 2)                    # AlexNet conv2
+
+
+def test_conv_3x3_wide():
+    _case(5, 256, 13, 13, 384, 1, 3, 3, 1, 1)                   # conv3
+    _case(5, 384, 13, 13, 384, 2, 3, 3, 1, 1)                   # conv4
+    _case(5, 384, 13, 13, 256, 2, 3, 3, 1, 1, relu=False)       # conv5
+
+
+def test_conv_odd_shapes():
+    _case(2, 8, 9, 11, 24, 1, 3, 2, 2, 1)
+    _case(7, 16, 14, 14, 48, 2, 1, 1, 1, 0)
+    _case(1, 48, 21, 21, 96, 1, 3, 3, 1, 1)                      # kaggle_bowl-like
+
+
+def test_conv_many_tiles_persistent():
+    _case(64, 32, 32, 32, 64, 1, 3, 3, 1, 1)                    # 65536 rows: 512 m-tiles over 148 SMs
