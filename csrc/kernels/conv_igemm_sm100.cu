@@ -73,7 +73,7 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kTableBytes;
 };
 
-template <int BNMAX, bool WGRAD>
+template <int BNMAX, bool WGRAD, int GRAN>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
   using C = Cfg<BNMAX>;
@@ -105,9 +105,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
   const long long total_tiles = (long long)tiles_m * tiles_n * p.G * splits;
 
   // gather table: granule index -> (element offset of the tap inside the image, kh, kw)
-  const int ngran = p.Kg / p.gran;
+  const int ngran = p.Kg / GRAN;
   for (int i = threadIdx.x; i < ngran; i += blockDim.x) {
-    const int k = i * p.gran;
+    const int k = i * GRAN;
     const int pos = k / p.Cg, c0 = k - pos * p.Cg;
     const int kh = pos / p.KW, kw = pos - kh * p.KW;
     GatherEntry e;
@@ -219,113 +219,108 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
     __syncwarp();
   } else if (warp >= kGatherWarp0) {
     // =========================== gather producers ===========================
-    const int tp = threadIdx.x - kGatherWarp0 * 32;   // 0..127
+    // Lane mapping: the lanes of one cp.async instruction cover whole 128-byte rows of the
+    // tile (GPR granules per row, RPI = 32/GPR rows per instruction), so every instruction reads
+    // a few contiguous runs of global memory instead of 32 scattered lines.
+    constexpr int GPR = 64 / GRAN;            // granules per 128-byte row: 8 or 16
+    constexpr int RPI = 32 / GPR;             // rows per instruction: 4 or 2
+    constexpr int GBYTES = GRAN * 2;          // 16 or 8
+    const int wl = warp - kGatherWarp0;       // 0..3
+    const int q = lane & (GPR - 1);           // granule inside the row
+    const int rsub = lane / GPR;              // row inside the instruction
+    const uint32_t qoff16 = (GRAN == 8) ? (uint32_t)q : (uint32_t)(q >> 1);
+    const uint32_t qsub = (GRAN == 8) ? 0u : (uint32_t)((q & 1) << 3);
     int stage = 0;
     uint32_t phase = 0;
     const int ohw = p.OH * p.OW;
+    auto decode_pixel = [&](long long pix, bool ok, long long& off, uint32_t& mask) {
+      int n = 0, oh = 0, ow = 0;
+      if (ok) {
+        n = (int)(pix / ohw);
+        const int r = (int)(pix - (long long)n * ohw);
+        oh = r / p.OW;
+        ow = r - oh * p.OW;
+      }
+      const int ih0 = oh * p.stride - p.pad_y, iw0 = ow * p.stride - p.pad_x;
+      uint32_t mh = 0, mw = 0;
+      if (ok) {
+        for (int kh = 0; kh < p.KH; ++kh) if ((unsigned)(ih0 + kh) < (unsigned)p.H) mh |= 1u << kh;
+        for (int kw = 0; kw < p.KW; ++kw) if ((unsigned)(iw0 + kw) < (unsigned)p.W) mw |= 1u << kw;
+      }
+      mask = mh | (mw << 16);
+      off = (((long long)n * p.H + ih0) * p.W + iw0) * p.Cs;
+    };
     for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       int n_blk, m_blk, split, g;
       decode_tile(t, n_blk, m_blk, split, g);
       const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
+      const bf16* gsrc = p.src + (long long)g * p.Cg;
       if (!WGRAD) {
-        // one A row (output pixel) per thread
-        const long long row = (long long)m_blk * BM + tp;
-        const bool row_ok = row < rows;
-        int n = 0, oh = 0, ow = 0;
-        if (row_ok) {
-          n = (int)(row / ohw);
-          const int r = (int)(row - (long long)n * ohw);
-          oh = r / p.OW;
-          ow = r - oh * p.OW;
+        // A tile: 128 output pixels x 64 reduction elements; warp wl owns rows [32*wl, 32*wl+32)
+        constexpr int ITERS = 32 / RPI;       // 8 or 16
+        long long roff[ITERS];
+        uint32_t rmask[ITERS];
+#pragma unroll
+        for (int i = 0; i < ITERS; ++i) {
+          const long long row = (long long)m_blk * BM + wl * 32 + i * RPI + rsub;
+          decode_pixel(row, row < rows, roff[i], rmask[i]);
         }
-        const int ih0 = oh * p.stride - p.pad_y, iw0 = ow * p.stride - p.pad_x;
-        // validity masks over kh / kw (KH, KW <= 32)
-        uint32_t mh = 0, mw = 0;
-        if (row_ok) {
-          for (int kh = 0; kh < p.KH; ++kh) if ((unsigned)(ih0 + kh) < (unsigned)p.H) mh |= 1u << kh;
-          for (int kw = 0; kw < p.KW; ++kw) if ((unsigned)(iw0 + kw) < (unsigned)p.W) mw |= 1u << kw;
-        }
-        const bf16* base = p.src + (((long long)n * p.H + ih0) * p.W + iw0) * p.Cs + (long long)g * p.Cg;
-        const uint32_t sw = (uint32_t)(tp & 7);
         for (int kb = kb0; kb < kb1; ++kb) {
+          const int gi = kb * GPR + q;
+          const bool gok = gi < ngran;
+          const GatherEntry e = table[gok ? gi : 0];
+          const uint32_t sel = gok ? ((1u << e.kh) | (1u << (16 + e.kw))) : 0xFFFFFFFFu;
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          const uint32_t dst = smem_base + stage * C::kStageBytes + tp * 128;
-          if (p.gran == 8) {
+          const uint32_t abase = smem_base + stage * C::kStageBytes;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const int gi = kb * 8 + j;
-              bool ok = gi < ngran;
-              GatherEntry e = table[ok ? gi : 0];
-              ok = ok && ((mh >> e.kh) & (mw >> e.kw) & 1u);
-              cp_async_16(dst + ((j ^ sw) << 4), ok ? (const void*)(base + e.off) : (const void*)p.src, ok);
-            }
-          } else {
-#pragma unroll
-            for (int q = 0; q < 16; ++q) {
-              const int gi = kb * 16 + q;
-              bool ok = gi < ngran;
-              GatherEntry e = table[ok ? gi : 0];
-              ok = ok && ((mh >> e.kh) & (mw >> e.kw) & 1u);
-              cp_async_8(dst + (((q >> 1) ^ sw) << 4) + ((q & 1) << 3),
-                         ok ? (const void*)(base + e.off) : (const void*)p.src, ok);
-            }
+          for (int i = 0; i < ITERS; ++i) {
+            const int rl = wl * 32 + i * RPI + rsub;
+            const bool ok = gok && ((rmask[i] & sel) == sel);
+            const uint32_t dst = abase + rl * 128 + ((qoff16 ^ (uint32_t)(rl & 7)) << 4) + qsub;
+            const void* sp = ok ? (const void*)(gsrc + roff[i] + e.off) : (const void*)p.src;
+            if (GRAN == 8) cp_async_16(dst, sp, ok); else cp_async_8(dst, sp, ok);
           }
           cp_async_arrive_noinc(full_bar(stage));
           if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
         }
       } else {
-        // B tile: 64 pixels (reduction rows) x bn reduction-columns, MN-major atoms of [64 rows][128 B].
-        // thread -> pixel row (tp & 63), and every second 16-byte chunk (tp >> 6).
-        const int r = tp & 63;
-        const int half = tp >> 6;
-        const uint32_t sw = (uint32_t)(r & 7);
+        // B tile: 64 pixels (reduction rows) x bn reduction-columns, MN-major atoms of [64 rows][128 B];
+        // warp wl owns pixel rows [16*wl, 16*wl+16)
+        constexpr int ITERS = 16 / RPI;       // 4 or 8
+        constexpr int MAXATOMS = BNMAX / 64;
         const int natoms = (p.bn + 63) >> 6;
-        const int gpc = 8 / p.gran;   // granules per 16-byte chunk: 1 or 2
+        GatherEntry ent[MAXATOMS];
+        uint32_t sel[MAXATOMS];
+#pragma unroll
+        for (int a = 0; a < MAXATOMS; ++a) {
+          const int gi = (n_blk * p.bn + a * 64) / GRAN + q;
+          const bool gok = (a < natoms) && gi < ngran;
+          ent[a] = table[gok ? gi : 0];
+          sel[a] = gok ? ((1u << ent[a].kh) | (1u << (16 + ent[a].kw))) : 0xFFFFFFFFu;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
-          const long long pix = (long long)kb * BK + r;
-          const bool pix_ok = pix < rows;
-          int n = 0, oh = 0, ow = 0;
-          if (pix_ok) {
-            n = (int)(pix / ohw);
-            const int rr = (int)(pix - (long long)n * ohw);
-            oh = rr / p.OW;
-            ow = rr - oh * p.OW;
+          long long roff[ITERS];
+          uint32_t rmask[ITERS];
+#pragma unroll
+          for (int i = 0; i < ITERS; ++i) {
+            const long long pix = (long long)kb * BK + wl * 16 + i * RPI + rsub;
+            decode_pixel(pix, pix < rows, roff[i], rmask[i]);
           }
-          const int ih0 = oh * p.stride - p.pad_y, iw0 = ow * p.stride - p.pad_x;
-          uint32_t mh = 0, mw = 0;
-          if (pix_ok) {
-            for (int kh = 0; kh < p.KH; ++kh) if ((unsigned)(ih0 + kh) < (unsigned)p.H) mh |= 1u << kh;
-            for (int kw = 0; kw < p.KW; ++kw) if ((unsigned)(iw0 + kw) < (unsigned)p.W) mw |= 1u << kw;
-          }
-          const bf16* base = p.src + (((long long)n * p.H + ih0) * p.W + iw0) * p.Cs + (long long)g * p.Cg;
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sb = smem_base + stage * C::kStageBytes + C::kABytes;
-          for (int a = 0; a < natoms; ++a) {
-            const uint32_t dst = sb + a * (64 * BK * 2) + r * 128;
 #pragma unroll
-            for (int jj = 0; jj < 4; ++jj) {
-              const int j = jj * 2 + half;                       // 16-byte chunk inside the atom row
-              const int kcol = n_blk * p.bn + a * 64 + j * 8;    // first reduction-column of the chunk
-              if (p.gran == 8) {
-                const int gi = kcol >> 3;
-                bool ok = gi < ngran;
-                GatherEntry e = table[ok ? gi : 0];
-                ok = ok && ((mh >> e.kh) & (mw >> e.kw) & 1u);
-                cp_async_16(dst + ((j ^ sw) << 4), ok ? (const void*)(base + e.off) : (const void*)p.src, ok);
-              } else {
+          for (int a = 0; a < MAXATOMS; ++a) {
+            if (a < natoms) {
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                  const int gi = (kcol >> 2) + h;
-                  bool ok = gi < ngran;
-                  GatherEntry e = table[ok ? gi : 0];
-                  ok = ok && ((mh >> e.kh) & (mw >> e.kw) & 1u);
-                  cp_async_8(dst + ((j ^ sw) << 4) + (h << 3), ok ? (const void*)(base + e.off) : (const void*)p.src,
-                             ok);
-                }
+              for (int i = 0; i < ITERS; ++i) {
+                const int rl = wl * 16 + i * RPI + rsub;
+                const bool ok = (rmask[i] & sel[a]) == sel[a];
+                const uint32_t dst = sb + a * (64 * BK * 2) + rl * 128 + ((qoff16 ^ (uint32_t)(rl & 7)) << 4) + qsub;
+                const void* sp = ok ? (const void*)(gsrc + roff[i] + ent[a].off) : (const void*)p.src;
+                if (GRAN == 8) cp_async_16(dst, sp, ok); else cp_async_8(dst, sp, ok);
               }
             }
           }
-          (void)gpc;
           cp_async_arrive_noinc(full_bar(stage));
           if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
         }
@@ -468,23 +463,27 @@ static int encode3d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1,
   return 0;
 }
 
-template <int BNMAX, bool WGRAD>
-static int launch(const CUtensorMap& tm, const Params& p, int grid, cudaStream_t st) {
+template <int BNMAX, bool WGRAD, int GRAN>
+static int launch_g(const CUtensorMap& tm, const Params& p, int grid, cudaStream_t st) {
   using C = Cfg<BNMAX>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BNMAX, WGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         C::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BNMAX, WGRAD, GRAN>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
-  conv_igemm_kernel<BNMAX, WGRAD><<<grid, kThreads, C::kSmemBytes, st>>>(tm, p);
+  conv_igemm_kernel<BNMAX, WGRAD, GRAN><<<grid, kThreads, C::kSmemBytes, st>>>(tm, p);
   CXN_CHECK_LAUNCH();
   return 0;
 }
+template <int BNMAX, bool WGRAD>
+static int launch(const CUtensorMap& tm, const Params& p, int grid, cudaStream_t st) {
+  return p.gran == 8 ? launch_g<BNMAX, WGRAD, 8>(tm, p, grid, st) : launch_g<BNMAX, WGRAD, 4>(tm, p, grid, st);
+}
 
 static int check_geom(const Params& p) {
-  if (p.KH > 32 || p.KW > 32) return -10;
+  if (p.KH > 16 || p.KW > 16) return -10;
   if (p.gran != 8 && p.gran != 4) return -11;
   if (p.gran == 4 && p.Cg != 4) return -12;
   if (p.Cg % p.gran) return -13;

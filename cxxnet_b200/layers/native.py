@@ -115,7 +115,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         p = self.param
         g = p.num_group
         icg = p.num_input_channel // g
-        small = p.kernel_height <= 32 and p.kernel_width <= 32
+        small = p.kernel_height <= 16 and p.kernel_width <= 16
         if icg % 8 == 0 and small and (p.kernel_height * p.kernel_width * icg) // 8 <= 2048:
             self.igemm_fwd = True
         elif (g == 1 and p.num_input_channel <= 4 and input_is_node0 and sole_consumer and small):
