@@ -1,0 +1,303 @@
+// K17 / K19: fused gradient reduce-scatter + sgd/nag/adam update + weight all-gather over
+// NVLink / NVSwitch peer memory, one launch per layer bucket.
+//
+// What the reference does for the same step (src/updater/async_updater-inl.hpp:94-127 with
+// mshadow-ps "local"): every GPU pushes its gradient to a host-staged parameter server, a
+// CPU thread sums, every GPU pulls the sum and runs its own updater kernels (3+ launches per
+// tensor).  Here every rank maps every other rank's parameter arena (CUDA IPC), and ONE
+// kernel per bucket does, with no NCCL call and no separate update kernel:
+//
+//   entry barrier  system-scope flags in peer memory: "my gradients for this bucket are final"
+//   phase 1        rank r owns chunks [r*per, (r+1)*per) of the bucket: 128-bit peer loads of
+//                  every rank's gradient shard, summed in registers (reduce-scatter), the
+//                  updater applied to the owned shard (momentum lives only in the owner),
+//                  the new weights stored into every rank's arena (all-gather, peer stores)
+//   exit barrier   "I have read your gradients and written your weights"
+//   phase 2        local: zero the bucket's gradients, refresh the bf16 GEMM shadow
+//
+// All ranks issue the same bucket sequence on an in-order stream, so the spin waits cannot
+// deadlock; every wait is bounded and traps on timeout.
+#include "common.cuh"
+#include <string.h>
+
+namespace cxn {
+namespace xchg {
+
+constexpr int kMaxRanks = 16;
+constexpr int kMaxSlots = 256;
+constexpr int kChunk = 1024;
+constexpr int kThreads = 256;
+
+struct Segment {   // must match loss_update.cu
+  long long start, n, shadow_off;
+  int cols, shadow_ld;
+  float lr, wd, momentum, clip;
+  float adam_lr_t, beta1, beta2, pad_;
+};
+
+struct Params {
+  char* peers[kMaxRanks];   // base of every rank's symmetric block, as mapped in THIS process
+  long long off_w, off_g, off_m, off_m2, off_shadow, off_flags;   // byte offsets inside a block
+  const Segment* segs;
+  const int* chunk_seg;
+  long long cb, ce;         // bucket = chunks [cb, ce)
+  int rank, nranks, kind;
+  unsigned seq;
+  int slot;
+  unsigned* counter;        // local scratch: CTA completion counter (zero between launches)
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_sys_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_sys_f4(float* p, float4 v) {
+  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ unsigned* flag_ptr(char* base, long long off_flags, int which, int slot, int src) {
+  return reinterpret_cast<unsigned*>(base + off_flags) + ((which * kMaxSlots + slot) * kMaxRanks + src);
+}
+// wait until every rank has published `seq` in local flag row (which, slot)
+__device__ __forceinline__ void wait_all(const Params& p, int which) {
+  if (threadIdx.x < p.nranks) {
+    const unsigned* f = flag_ptr(p.peers[p.rank], p.off_flags, which, p.slot, threadIdx.x);
+    const long long t0 = clock64();
+    unsigned spins = 0;
+    while ((int)(ld_acquire_sys(f) - p.seq) < 0) {
+      __nanosleep(64);
+      if ((++spins & 4095u) == 0 && clock64() - t0 > 20000000000LL) {
+        printf("[cxxnet_b200 exchange] rank %d timed out waiting for rank %d (slot %d phase %d seq %u)\n", p.rank,
+               (int)threadIdx.x, p.slot, which, p.seq);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float clip_grad(float g, float c) {
+  if (g != g) return 0.0f;
+  return fminf(fmaxf(g, -c), c);
+}
+
+__global__ void __launch_bounds__(kThreads) fused_rs_update_ag_kernel(const Params p) {
+  char* self = p.peers[p.rank];
+  // ---------------- entry barrier: every rank's gradients for this bucket are complete
+  if (blockIdx.x == 0 && threadIdx.x < p.nranks)
+    st_release_sys(flag_ptr(p.peers[threadIdx.x], p.off_flags, 0, p.slot, p.rank), p.seq);
+  wait_all(p, 0);
+
+  // ---------------- phase 1: reduce-scatter + update + all-gather on the owned shard
+  const long long nch = p.ce - p.cb;
+  const long long per = (nch + p.nranks - 1) / p.nranks;
+  const long long my0 = p.cb + (long long)p.rank * per;
+  const long long my1 = min(p.ce, my0 + per);
+  float* w = reinterpret_cast<float*>(self + p.off_w);
+  float* m = reinterpret_cast<float*>(self + p.off_m);
+  float* m2 = reinterpret_cast<float*>(self + p.off_m2);
+  for (long long ch = my0 + blockIdx.x; ch < my1; ch += gridDim.x) {
+    const Segment s = p.segs[p.chunk_seg[ch]];
+    const long long e = ch * kChunk + threadIdx.x * 4;
+    const long long rel = e - s.start;
+    if (rel >= s.n) continue;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int r = 0; r < p.nranks; ++r) {
+      const int src = (p.rank + r) % p.nranks;   // start with the local copy, stagger peers
+      const float4 g = ld_sys_f4(reinterpret_cast<const float*>(p.peers[src] + p.off_g) + e);
+      acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
+    }
+    float4 wv = *reinterpret_cast<const float4*>(w + e);
+    float4 mv = *reinterpret_cast<const float4*>(m + e);
+    float4 m2v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.kind == 2) m2v = *reinterpret_cast<const float4*>(m2 + e);
+    float* wp = reinterpret_cast<float*>(&wv);
+    float* gp = reinterpret_cast<float*>(&acc);
+    float* mp = reinterpret_cast<float*>(&mv);
+    float* m2p = reinterpret_cast<float*>(&m2v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (rel + j >= s.n) { wp[j] = 0.f; mp[j] = 0.f; continue; }
+      float gr = gp[j];
+      if (p.kind == 0) {
+        if (s.clip != 0.0f) gr = clip_grad(gr, s.clip);
+        mp[j] = s.momentum * mp[j] - s.lr * (gr + s.wd * wp[j]);
+        wp[j] += mp[j];
+      } else if (p.kind == 1) {
+        const float old = mp[j];
+        mp[j] = s.momentum * old - s.lr * (gr + s.wd * wp[j]);
+        wp[j] += (1.0f + s.momentum) * mp[j] - s.momentum * old;
+      } else {
+        if (s.wd > 0.0f) gr -= s.wd * wp[j];
+        mp[j] += s.beta1 * (gr - mp[j]);
+        m2p[j] += s.beta2 * (gr * gr - m2p[j]);
+        wp[j] -= s.adam_lr_t * (mp[j] / (sqrtf(m2p[j]) + 1e-8f));
+      }
+    }
+    *reinterpret_cast<float4*>(m + e) = mv;
+    if (p.kind == 2) *reinterpret_cast<float4*>(m2 + e) = m2v;
+#pragma unroll 4
+    for (int r = 0; r < p.nranks; ++r) {
+      const int dst = (p.rank + r) % p.nranks;
+      st_sys_f4(reinterpret_cast<float*>(p.peers[dst] + p.off_w) + e, wv);
+    }
+  }
+
+  // ---------------- exit barrier: my reads of peer gradients and writes of peer weights are done
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(p.counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *p.counter = 0u;
+      __threadfence_system();
+      for (int r = 0; r < p.nranks; ++r) st_release_sys(flag_ptr(p.peers[r], p.off_flags, 1, p.slot, p.rank), p.seq);
+    }
+  }
+  wait_all(p, 1);
+
+  // ---------------- phase 2 (local): zero gradients, refresh the bf16 shadow of the bucket
+  float* g = reinterpret_cast<float*>(self + p.off_g);
+  bf16* shadow = reinterpret_cast<bf16*>(self + p.off_shadow);
+  for (long long ch = p.cb + blockIdx.x; ch < p.ce; ch += gridDim.x) {
+    const Segment s = p.segs[p.chunk_seg[ch]];
+    const long long e = ch * kChunk + threadIdx.x * 4;
+    const long long rel = e - s.start;
+    if (rel >= s.n) continue;
+    *reinterpret_cast<float4*>(g + e) = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (s.shadow_off >= 0) {
+      const float4 wv = ld_sys_f4(w + e);
+      const float* wp = reinterpret_cast<const float*>(&wv);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const long long k = rel + j;
+        if (k < s.n) {
+          const long long row = k / s.cols;
+          shadow[s.shadow_off + row * s.shadow_ld + (k - row * s.cols)] = __float2bfloat16(wp[j]);
+        }
+      }
+    }
+  }
+}
+
+// K19: copy [off, off+bytes) of the root's block into every rank's block, then barrier.
+__global__ void __launch_bounds__(kThreads) broadcast_kernel(const Params p, long long off, long long bytes, int root) {
+  if (p.rank == root) {
+    const long long n16 = bytes / 16;
+    const uint4* src = reinterpret_cast<const uint4*>(p.peers[root] + off);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16;
+         i += (long long)gridDim.x * blockDim.x) {
+      const uint4 v = src[i];
+      for (int r = 0; r < p.nranks; ++r)
+        if (r != root) reinterpret_cast<uint4*>(p.peers[r] + off)[i] = v;
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(p.counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *p.counter = 0u;
+      __threadfence_system();
+      for (int r = 0; r < p.nranks; ++r) st_release_sys(flag_ptr(p.peers[r], p.off_flags, 1, p.slot, p.rank), p.seq);
+    }
+  }
+  wait_all(p, 1);
+}
+
+}  // namespace xchg
+}  // namespace cxn
+
+using namespace cxn;
+using namespace cxn::xchg;
+
+CXN_API int cxn_xchg_flag_bytes() { return 2 * kMaxSlots * kMaxRanks * 4; }
+CXN_API int cxn_xchg_max_ranks() { return kMaxRanks; }
+CXN_API int cxn_xchg_max_slots() { return kMaxSlots; }
+
+static int fill_params(Params* p, const unsigned long long* peers, int nranks, int rank, long long off_w,
+                       long long off_g, long long off_m, long long off_m2, long long off_shadow, long long off_flags,
+                       const void* segs, const int* chunk_seg, long long cb, long long ce, int kind, unsigned seq,
+                       int slot, unsigned* counter) {
+  if (nranks < 1 || nranks > kMaxRanks || slot < 0 || slot >= kMaxSlots) return -20;
+  memset(p, 0, sizeof(*p));
+  for (int i = 0; i < nranks; ++i) p->peers[i] = reinterpret_cast<char*>(peers[i]);
+  p->off_w = off_w; p->off_g = off_g; p->off_m = off_m; p->off_m2 = off_m2; p->off_shadow = off_shadow;
+  p->off_flags = off_flags; p->segs = (const Segment*)segs; p->chunk_seg = chunk_seg; p->cb = cb; p->ce = ce;
+  p->rank = rank; p->nranks = nranks; p->kind = kind; p->seq = seq; p->slot = slot; p->counter = counter;
+  return 0;
+}
+
+// One bucket of the fused gradient exchange.  `peers` is a HOST array of nranks block base
+// addresses (this rank's own block at index `rank`).  `grid` CTAs (<= resident capacity; the
+// kernel spins on peer flags, so every CTA must be co-resident).
+CXN_API int cxn_fused_rs_update_ag(const unsigned long long* peers, int nranks, int rank, long long off_w,
+                                   long long off_g, long long off_m, long long off_m2, long long off_shadow,
+                                   long long off_flags, const void* segs, const int* chunk_seg, long long cb,
+                                   long long ce, int kind, unsigned seq, int slot, unsigned* counter, int grid,
+                                   cudaStream_t st) {
+  Params p;
+  int rc = fill_params(&p, peers, nranks, rank, off_w, off_g, off_m, off_m2, off_shadow, off_flags, segs, chunk_seg,
+                       cb, ce, kind, seq, slot, counter);
+  if (rc) return rc;
+  if (ce <= cb) return 0;
+  if (grid < 1) grid = 1;
+  if (grid > num_sms()) grid = num_sms();
+  fused_rs_update_ag_kernel<<<grid, kThreads, 0, st>>>(p);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+
+CXN_API int cxn_symm_broadcast(const unsigned long long* peers, int nranks, int rank, long long off_flags,
+                               long long off, long long bytes, int root, unsigned seq, int slot, unsigned* counter,
+                               int grid, cudaStream_t st) {
+  Params p;
+  int rc = fill_params(&p, peers, nranks, rank, 0, 0, 0, 0, 0, off_flags, nullptr, nullptr, 0, 0, 0, seq, slot, counter);
+  if (rc) return rc;
+  if (bytes % 16) return -21;
+  if (grid < 1) grid = 1;
+  if (grid > num_sms()) grid = num_sms();
+  broadcast_kernel<<<grid, kThreads, 0, st>>>(p, off, bytes, root);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+
+// ------------------------------------------------------------------ CUDA IPC helpers
+CXN_API int cxn_ipc_alloc(unsigned long long bytes, unsigned long long* ptr, unsigned char* handle64) {
+  void* d = nullptr;
+  cudaError_t e = cudaMalloc(&d, bytes);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaMemset(d, 0, bytes);
+  if (e != cudaSuccess) return (int)e;
+  cudaIpcMemHandle_t h;
+  e = cudaIpcGetMemHandle(&h, d);
+  if (e != cudaSuccess) return (int)e;
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64, &h, 64);
+  *ptr = reinterpret_cast<unsigned long long>(d);
+  return 0;
+}
+CXN_API int cxn_ipc_open(const unsigned char* handle64, unsigned long long* ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  void* d = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&d, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) return (int)e;
+  *ptr = reinterpret_cast<unsigned long long>(d);
+  return 0;
+}
+CXN_API int cxn_ipc_close(unsigned long long ptr) { return (int)cudaIpcCloseMemHandle(reinterpret_cast<void*>(ptr)); }
+CXN_API int cxn_ipc_free(unsigned long long ptr) { return (int)cudaFree(reinterpret_cast<void*>(ptr)); }

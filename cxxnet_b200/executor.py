@@ -250,7 +250,9 @@ class NeuralNet:
                         and consumers.get(x.index, 0) == 1):
                     p.layer.fuse_relu = True
                     l.fused = True
-        # parameter arena
+        # parameter arena (in peer-mapped symmetric memory when several ranks train together)
+        self.symm_block = None
+        self.symm_offsets = {}
         self.arena = ParamArena(self.device, cfg.updater_type, alloc=self.arena_alloc)
         self._seg_of = {}
         for i, c in enumerate(self.connections):
@@ -270,6 +272,8 @@ class NeuralNet:
                     rows, cols, sld = 1, w.numel(), 0
                 s = self.arena.add(c.layer, i, tag, rows, cols, sld, up, b1, b2)
                 self._seg_of[(i, tag)] = s
+        if self.world_size > 1 and self.arena_alloc is None:
+            self._alloc_symmetric()
         self.arena.finalize()
         self._bind_arena()
         for c in self.connections:
@@ -282,6 +286,26 @@ class NeuralNet:
         if self.world_size > 1:
             from .parallel.exchange import GradExchange
             self.exchange = GradExchange(self)
+
+    def _alloc_symmetric(self) -> None:
+        """lay the arenas out inside one CUDA-IPC block that every rank maps (parallel/symm.py)."""
+        from .parallel.symm import SymmetricBlock
+        a = self.arena
+        n = max(a.total, a.chunk)
+        nbuf = 4 if a.kind == ops.UPD_ADAM else 3
+        flag_bytes = ops.lib().cxn_xchg_flag_bytes()
+        total = nbuf * (n * 4 + 4096) + max(a.shadow_total, 128) * 2 + 4096 + flag_bytes + 65536
+        self.symm_block = SymmetricBlock(total, self.device)
+        off, _ = self.symm_block.carve(flag_bytes)
+        self.symm_offsets["flags"] = off
+        names = ["w", "g", "m"] + (["m2"] if a.kind == ops.UPD_ADAM else []) + ["shadow"]
+        it = iter(names)
+
+        def alloc(count, dtype):
+            o, t = self.symm_block.alloc(count, dtype)
+            self.symm_offsets[next(it)] = o
+            return t
+        a._alloc = alloc
 
     def _bind_arena(self) -> None:
         """copy layer weights (reference layout) into the arena and hand views back to the layers."""
@@ -401,9 +425,9 @@ class NeuralNet:
             for c in self.connections:
                 c.layer.forward(is_train, c.nodes_in, c.nodes_out)
             return
-        if self.exchange is not None:
-            self.exchange.wait_all()
-        for c in self.connections:
+        for i, c in enumerate(self.connections):
+            if self.exchange is not None:
+                self.exchange.wait_layer(i)   # UpdateWait: this layer's weights from the last exchange
             if c.native:
                 c.layer.b200_forward(self, is_train)
             else:
@@ -417,10 +441,16 @@ class NeuralNet:
                 c.layer.backprop(i != 0 or prop_to_input, c.nodes_in, c.nodes_out)
                 if need_update:
                     for u in self.updaters[i]:
+                        if self.world_size > 1:
+                            # reference-backend data parallelism: plain sum over ranks (gloo / nccl)
+                            import torch.distributed as dist
+                            dist.all_reduce(u.dw)
                         u.update(epoch)
             return
         if need_update:
             self.arena.refresh_hyper(epoch)
+            if self.exchange is not None:
+                self.exchange.begin_step()
         for i in range(n - 1, -1, -1):
             c = self.connections[i]
             prop = i != 0 or prop_to_input

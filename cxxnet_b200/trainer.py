@@ -107,7 +107,9 @@ class NetTrainer:
         if self.type_pserver == "dist":
             raise ValueError("param_server=dist (ps-lite multi-node) is not supported; "
                              "use a torch.distributed launch over NVLink instead")
-        if dist.is_available() and dist.is_initialized():
+        if dist.is_available() and dist.is_initialized() and self.type_pserver != "NONE":
+            # param_server = NONE keeps this trainer private to its process (no gradient exchange),
+            # as in the reference when a single device is used (nnet_impl-inl.hpp:378-381)
             self.world_size, self.rank = dist.get_world_size(), dist.get_rank()
         ndev = max(len(self.devices), 1)
         if self.world_size > 1:
@@ -127,6 +129,8 @@ class NetTrainer:
             if self.world_size > 1:
                 local = int(os.environ.get("LOCAL_RANK", self.rank))
                 idx = self.devices[local] if local < len(self.devices) else local
+            elif self.type_pserver == "NONE" and len(self.devices) <= 1:
+                idx = self.devices[0] if self.devices else torch.cuda.current_device()
             else:
                 idx = self.devices[0] if self.devices else torch.cuda.current_device()
                 if len(self.devices) > 1:

@@ -1,0 +1,65 @@
+"""worker for test_gpu_multi.py: run under torchrun, one rank per GPU.  argv[1] = updater."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+UPD = sys.argv[1] if len(sys.argv) > 1 else "sgd"
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+import torch, torch.distributed as dist
+rank = int(os.environ["RANK"]); world = int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(rank)
+dist.init_process_group("nccl", device_id=torch.device("cuda", rank))
+from util import make_trainer, make_batch, rel_err, copy_weights
+from cxxnet_b200.models import lenet_conf
+from cxxnet_b200.trainer import NetTrainer
+extra = "wmat:wd = 0.001\nupdater = " + UPD + "\n"
+_lenet = lenet_conf
+def lenet_conf(**kw):   # dropout off: masks are a function of the element index, i.e. of the batch split
+    return _lenet(**kw).replace("threshold = 0.5", "threshold = 0.0")
+tr = make_trainer(lenet_conf(batch_size=64, dev="gpu:" + ",".join(str(i) for i in range(world)), extra=extra))
+assert tr.net.exchange is not None and tr.world_size == world
+assert tr.net.exchange.check_replicas() == 0.0
+# single-GPU twin: same weights, whole batch on one device, no exchange
+single = make_trainer(lenet_conf(batch_size=64, dev="gpu:%d" % rank, extra=extra), param_server="NONE")
+assert single.world_size == 1 and single.net.exchange is None
+copy_weights(tr, single)
+# phase A: gradients only (no update): sum over ranks must equal the single-device gradient
+b = make_batch((64, 1, 28, 28), seed=99)
+for t in (tr, single):
+    lo, hi = t._slice(b.batch_size)
+    t.net.label_info.fields = t._label_fields(b.label, lo, hi, t.device)
+    t.net.accumulate_grads = False
+    t.net.set_input(b.data[lo:hi], [])
+    t.net.forward(True)
+    t.net.backprop(False, False, 0)
+torch.cuda.synchronize()
+for i, c in enumerate(tr.net.connections):
+    for tag, w, g in c.layer.weights():
+        gm = tr.net.get_grad(i, tag).clone()
+        dist.all_reduce(gm)
+        gs = single.net.get_grad(i, tag)
+        e = rel_err(gs, gm, floor=1e-7)
+        if rank == 0:
+            print("  grad[%d:%s] rel err %.4g |single| %.4g |multi| %.4g" % (i, tag, e, float(gs.abs().sum()), float(gm.abs().sum())))
+        assert e < 2e-2, (i, tag, e)
+# clear accumulated gradients again
+tr.net.arena.g.zero_(); single.net.arena.g.zero_()
+torch.cuda.synchronize(); dist.barrier()
+for s in range(4):
+    b = make_batch((64, 1, 28, 28), seed=s)
+    tr.update(b)
+    single.update(b)
+torch.cuda.synchronize()
+assert tr.net.exchange.check_replicas() == 0.0, "replicas diverged"
+worst = 0.0
+for name in ("cv1", "fc1", "fc2"):
+    for tag in ("wmat", "bias"):
+        a, _ = tr.get_weight(name, tag)
+        b_, _ = single.get_weight(name, tag)
+        e = rel_err(torch.from_numpy(b_), torch.from_numpy(a))
+        if rank == 0:
+            print("  %s.%s rel err %.4g  |single| %.4g |multi| %.4g" % (name, tag, e, abs(b_).sum(), abs(a).sum()))
+        worst = max(worst, e)
+print("RANK", rank, "worst rel err", worst)
+assert worst < 3e-2, worst
+dist.barrier()
+dist.destroy_process_group()
+print("OK", rank)
