@@ -1,0 +1,119 @@
+#!/usr/bin/env python
+"""BASELINE config 5: fused reduce-scatter + sgd update + all-gather kernel vs NCCL all-reduce +
+separate update, swept over the AlexNet per-layer message sizes.
+
+  torchrun --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 bench/exchange_sweep.py [--grid G]
+
+Device-timed with CUDA events, max over ranks.  Reported bandwidth is the per-GPU NVLink traffic
+of the algorithm, 2*(N-1)/N * bytes (reduce-scatter in + all-gather out), divided by time.
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+SIZES_MB = [0.139, 1.229, 3.539, 2.654, 1.769, 150.995, 67.109, 16.384]
+NAMES = ["conv1", "conv2", "conv3", "conv4", "conv5", "fc6", "fc7", "fc8"]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--grid", type=int, default=0)
+    ap.add_argument("--iters", type=int, default=20)
+    args = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+    from cxxnet_b200 import ops
+    from cxxnet_b200.parallel.arena import ParamArena
+    from cxxnet_b200.parallel.exchange import GradExchange
+    from cxxnet_b200.parallel.symm import SymmetricBlock
+    from cxxnet_b200.updaters import UpdaterParam
+    dev = torch.device("cuda", torch.cuda.current_device())
+
+    class FakeNet:
+        pass
+    net = FakeNet()
+    net.rank, net.world_size, net.device = rank, world, dev
+    arena = ParamArena(dev, "sgd")
+    for i, mb in enumerate(SIZES_MB):
+        n = int(mb * 1e6 / 4)
+        up = UpdaterParam("wmat")
+        up.base_lr = 0.01
+        arena.add(None, i, "wmat", 1, n, 0, up)
+    nn = max(arena.total, arena.chunk)
+    flag_bytes = ops.lib().cxn_xchg_flag_bytes()
+    block = SymmetricBlock(3 * (nn * 4 + 4096) + 4096 + flag_bytes + 65536 + 1024, dev)
+    offs = {}
+    offs["flags"], _ = block.carve(flag_bytes)
+    names = iter(["w", "g", "m", "shadow"])
+
+    def alloc(count, dtype):
+        o, t = block.alloc(count, dtype)
+        offs[next(names)] = o
+        return t
+    arena._alloc = alloc
+    arena.finalize()
+    net.arena, net.symm_block, net.symm_offsets = arena, block, offs
+    ex = GradExchange(net, grid=args.grid)
+    arena.g.normal_()
+    torch.cuda.synchronize()
+    dist.barrier()
+
+    def time_it(fn, iters):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    rows = []
+    for bi, b in enumerate(ex.buckets):
+        n = (b["ce"] - b["cb"]) * arena.chunk
+        nbytes = n * 4
+
+        def fused():
+            ex.begin_step()
+            with torch.cuda.stream(ex.stream):
+                pass
+            ex.layer_done(b["layer"])
+            ex.wait_layer(b["layer"])
+        gview = arena.g[b["cb"] * arena.chunk:b["ce"] * arena.chunk]
+        wview = arena.w[b["cb"] * arena.chunk:b["ce"] * arena.chunk]
+        mview = arena.m[b["cb"] * arena.chunk:b["ce"] * arena.chunk]
+
+        def nccl():
+            dist.all_reduce(gview)
+            mview.mul_(0.9).add_(gview, alpha=-0.01)
+            wview.add_(mview)
+            gview.zero_()
+        tf = time_it(fused, args.iters)
+        tn = time_it(nccl, args.iters)
+        traffic = 2.0 * (world - 1) / world * nbytes
+        rows.append({"layer": NAMES[bi], "MB": nbytes / 1e6, "fused_us": tf * 1e3, "nccl_allreduce_update_us": tn * 1e3,
+                     "fused_GBps_per_dir": traffic / 2 / (tf * 1e-3) / 1e9, "speedup_vs_nccl": tn / tf})
+    if rank == 0:
+        tot_f = sum(r["fused_us"] for r in rows)
+        tot_n = sum(r["nccl_allreduce_update_us"] for r in rows)
+        print(json.dumps({"n_gpus": world, "grid": ex.grid, "rows": rows, "total_fused_us": tot_f,
+                          "total_nccl_us": tot_n}, indent=1))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -57,14 +57,15 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
 }
 __device__ __forceinline__ float4 ld_sys_f4(const float* p) {
   float4 v;
-  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+  // weak 128-bit load that does not allocate in L1: the data was published before the flag
+  // acquire + bar.sync that precede every use, and is read exactly once per launch
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-               : "l"(p)
-               : "memory");
+               : "l"(p));
   return v;
 }
 __device__ __forceinline__ void st_sys_f4(float* p, float4 v) {
-  asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+  asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
                : "memory");
 }
 __device__ __forceinline__ unsigned* flag_ptr(char* base, long long off_flags, int which, int slot, int src) {
@@ -93,6 +94,7 @@ __device__ __forceinline__ float clip_grad(float g, float c) {
   return fminf(fmaxf(g, -c), c);
 }
 
+template <int NR, int U>   // NR: compile-time upper bound on ranks per load group, U: chunks in flight
 __global__ void __launch_bounds__(kThreads) fused_rs_update_ag_kernel(const Params p) {
   char* self = p.peers[p.rank];
   // ---------------- entry barrier: every rank's gradients for this bucket are complete
@@ -108,51 +110,86 @@ __global__ void __launch_bounds__(kThreads) fused_rs_update_ag_kernel(const Para
   float* w = reinterpret_cast<float*>(self + p.off_w);
   float* m = reinterpret_cast<float*>(self + p.off_m);
   float* m2 = reinterpret_cast<float*>(self + p.off_m2);
-  for (long long ch = my0 + blockIdx.x; ch < my1; ch += gridDim.x) {
-    const Segment s = p.segs[p.chunk_seg[ch]];
-    const long long e = ch * kChunk + threadIdx.x * 4;
-    const long long rel = e - s.start;
-    if (rel >= s.n) continue;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-    for (int r = 0; r < p.nranks; ++r) {
-      const int src = (p.rank + r) % p.nranks;   // start with the local copy, stagger peers
-      const float4 g = ld_sys_f4(reinterpret_cast<const float*>(p.peers[src] + p.off_g) + e);
-      acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
-    }
-    float4 wv = *reinterpret_cast<const float4*>(w + e);
-    float4 mv = *reinterpret_cast<const float4*>(m + e);
-    float4 m2v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (p.kind == 2) m2v = *reinterpret_cast<const float4*>(m2 + e);
-    float* wp = reinterpret_cast<float*>(&wv);
-    float* gp = reinterpret_cast<float*>(&acc);
-    float* mp = reinterpret_cast<float*>(&mv);
-    float* m2p = reinterpret_cast<float*>(&m2v);
+  // U chunks per CTA iteration: U * nranks independent 128-bit peer loads in flight per thread
+  // (NVLink round trips are ~2-3 us; bandwidth needs megabytes in flight across the chip)
+  for (long long ch0 = my0 + (long long)blockIdx.x * U; ch0 < my1; ch0 += (long long)gridDim.x * U) {
+    float4 acc[U];
+    bool live[U];
+    long long eoff[U];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      if (rel + j >= s.n) { wp[j] = 0.f; mp[j] = 0.f; continue; }
-      float gr = gp[j];
-      if (p.kind == 0) {
-        if (s.clip != 0.0f) gr = clip_grad(gr, s.clip);
-        mp[j] = s.momentum * mp[j] - s.lr * (gr + s.wd * wp[j]);
-        wp[j] += mp[j];
-      } else if (p.kind == 1) {
-        const float old = mp[j];
-        mp[j] = s.momentum * old - s.lr * (gr + s.wd * wp[j]);
-        wp[j] += (1.0f + s.momentum) * mp[j] - s.momentum * old;
-      } else {
-        if (s.wd > 0.0f) gr -= s.wd * wp[j];
-        mp[j] += s.beta1 * (gr - mp[j]);
-        m2p[j] += s.beta2 * (gr * gr - m2p[j]);
-        wp[j] -= s.adam_lr_t * (mp[j] / (sqrtf(m2p[j]) + 1e-8f));
+    for (int u = 0; u < U; ++u) {
+      const long long ch = ch0 + u;
+      acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      eoff[u] = ch * kChunk + threadIdx.x * 4;
+      live[u] = false;
+      if (ch < my1) {
+        const Segment& sg = p.segs[p.chunk_seg[ch]];
+        live[u] = (eoff[u] - sg.start) < sg.n;
       }
     }
-    *reinterpret_cast<float4*>(m + e) = mv;
-    if (p.kind == 2) *reinterpret_cast<float4*>(m2 + e) = m2v;
-#pragma unroll 4
-    for (int r = 0; r < p.nranks; ++r) {
-      const int dst = (p.rank + r) % p.nranks;
-      st_sys_f4(reinterpret_cast<float*>(p.peers[dst] + p.off_w) + e, wv);
+    // issue every load of a group of up to RG ranks before consuming any of them
+    constexpr int RG = NR;
+    for (int r0 = 0; r0 < p.nranks; r0 += RG) {
+      float4 buf[RG][U];
+#pragma unroll
+      for (int rr = 0; rr < RG; ++rr) {
+        if (r0 + rr < p.nranks) {
+          const int src = (p.rank + r0 + rr) % p.nranks;   // start with the local copy, stagger peers
+          const float* gsrc = reinterpret_cast<const float*>(p.peers[src] + p.off_g);
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+            buf[rr][u] = live[u] ? ld_sys_f4(gsrc + eoff[u]) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+#pragma unroll
+      for (int rr = 0; rr < RG; ++rr) {
+        if (r0 + rr < p.nranks) {
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            acc[u].x += buf[rr][u].x; acc[u].y += buf[rr][u].y; acc[u].z += buf[rr][u].z; acc[u].w += buf[rr][u].w;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!live[u]) continue;
+      const long long e = eoff[u];
+      const Segment s = p.segs[p.chunk_seg[ch0 + u]];
+      const long long rel = e - s.start;
+      float4 wv = *reinterpret_cast<const float4*>(w + e);
+      float4 mv = *reinterpret_cast<const float4*>(m + e);
+      float4 m2v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (p.kind == 2) m2v = *reinterpret_cast<const float4*>(m2 + e);
+      float* wp = reinterpret_cast<float*>(&wv);
+      float* gp = reinterpret_cast<float*>(&acc[u]);
+      float* mp = reinterpret_cast<float*>(&mv);
+      float* m2p = reinterpret_cast<float*>(&m2v);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (rel + j >= s.n) { wp[j] = 0.f; mp[j] = 0.f; continue; }
+        float gr = gp[j];
+        if (p.kind == 0) {
+          if (s.clip != 0.0f) gr = clip_grad(gr, s.clip);
+          mp[j] = s.momentum * mp[j] - s.lr * (gr + s.wd * wp[j]);
+          wp[j] += mp[j];
+        } else if (p.kind == 1) {
+          const float old = mp[j];
+          mp[j] = s.momentum * old - s.lr * (gr + s.wd * wp[j]);
+          wp[j] += (1.0f + s.momentum) * mp[j] - s.momentum * old;
+        } else {
+          if (s.wd > 0.0f) gr -= s.wd * wp[j];
+          mp[j] += s.beta1 * (gr - mp[j]);
+          m2p[j] += s.beta2 * (gr * gr - m2p[j]);
+          wp[j] -= s.adam_lr_t * (mp[j] / (sqrtf(m2p[j]) + 1e-8f));
+        }
+      }
+      *reinterpret_cast<float4*>(m + e) = mv;
+      if (p.kind == 2) *reinterpret_cast<float4*>(m2 + e) = m2v;
+      for (int r = 0; r < p.nranks; ++r) {
+        const int dst = (p.rank + r) % p.nranks;
+        st_sys_f4(reinterpret_cast<float*>(p.peers[dst] + p.off_w) + e, wv);
+      }
     }
   }
 
@@ -256,7 +293,9 @@ CXN_API int cxn_fused_rs_update_ag(const unsigned long long* peers, int nranks, 
   if (ce <= cb) return 0;
   if (grid < 1) grid = 1;
   if (grid > num_sms()) grid = num_sms();
-  fused_rs_update_ag_kernel<<<grid, kThreads, 0, st>>>(p);
+  if (nranks <= 2) fused_rs_update_ag_kernel<2, 4><<<grid, kThreads, 0, st>>>(p);
+  else if (nranks <= 4) fused_rs_update_ag_kernel<4, 4><<<grid, kThreads, 0, st>>>(p);
+  else fused_rs_update_ag_kernel<8, 2><<<grid, kThreads, 0, st>>>(p);
   CXN_CHECK_LAUNCH();
   return 0;
 }

@@ -28,13 +28,13 @@ from .symm import SymmetricBlock
 
 
 class GradExchange:
-    def __init__(self, net, grid: int = 32):
+    def __init__(self, net, grid: int = 0):
         import torch.distributed as dist
         self.net = net
         self.arena = net.arena
         self.rank, self.world = net.rank, net.world_size
         self.device = net.device
-        self.grid = grid
+        self.grid = grid or int(__import__('os').environ.get('CXN_XCHG_GRID', '96'))
         self.seq = 0
         L = ops.lib()
         P, I, LL, U = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_uint
@@ -101,7 +101,7 @@ class GradExchange:
             self.block.peers_c, self.world, self.rank, self.off["w"], self.off["g"], self.off["m"],
             self.off.get("m2", 0), self.off["shadow"], self.off["flags"], a.seg_dev.data_ptr(),
             a.chunk_seg.data_ptr(), b["cb"], b["ce"], a.kind, self.seq, b["slot"], self.counter.data_ptr(),
-            self.grid, self.stream.cuda_stream), "cxn_fused_rs_update_ag")
+            max(1, min(self.grid, (b["ce"] - b["cb"] + 3) // 4)), self.stream.cuda_stream), "cxn_fused_rs_update_ag")
         b["event"].record(self.stream)
         b["pending"] = True
 
