@@ -4,9 +4,15 @@ report their relative error (reference ``src/layer/pairtest_layer-inl.hpp:14-200
 The master runs on the real nodes, the slave on shadow copies; outputs are compared in
 forward, weight gradients and input gradients in backward.  Metric: relative L1 error
 ``sum|m-s| / sum|m|``; a message goes to stderr when it exceeds 1e-5 or is NaN - the run is
-never failed.  ``master:`` / ``slave:`` prefixed keys go to one side only.  (The reference's
-``LoadModel`` calls ``slave->SaveModel``, ``:148``; here the slave is synchronised from the
-master instead.)  Results are also kept in ``self.reports`` so tests can assert on them.
+never failed.  ``master:`` / ``slave:`` prefixed keys go to one side only.  Results are also kept
+in ``self.reports`` so tests can assert on them.
+
+Differences from the reference, on purpose: the reference hands BOTH weight sets to the updater
+(``ApplyVisitor`` visits master and slave, ``:120-123``) and lets them evolve independently; here
+only the master's weights are trained and the slave's are re-synchronised from them before every
+forward, so each step is an independent kernel-vs-kernel comparison.  ``save_model`` writes master
+then slave like the reference (``:143-146``); the reference's ``LoadModel`` calls
+``slave->SaveModel`` (``:147-150``, a bug) - here both are read back.
 """
 from __future__ import annotations
 
@@ -65,7 +71,10 @@ class PairTestLayer(Layer):
                 raise ValueError("PairTestLayer: master and slave disagree on the output shape")
 
     def _sync(self):
-        for (_, mw, _), (_, sw, _) in zip(self.master.weights(), self.slave.weights()):
+        for (_, mw, _), (tag, sw, sg) in zip(self.master.weights(), self.slave.weights()):
+            if sw.device != mw.device:
+                self.slave.rebind(tag, sw.to(mw.device), sg.to(mw.device))
+                sw = dict((t, w) for t, w, _ in self.slave.weights())[tag]
             sw.copy_(mw.reshape(sw.shape))
 
     def init_model(self):
@@ -74,12 +83,12 @@ class PairTestLayer(Layer):
         self._sync()
 
     def save_model(self, fo):
+        self._sync()
         self.master.save_model(fo)
+        self.slave.save_model(fo)
 
     def load_model(self, fi):
-        pos = fi.tell()
         self.master.load_model(fi)
-        fi.seek(pos)
         self.slave.load_model(fi)
 
     def _cmp(self, what: str, m: torch.Tensor, s: torch.Tensor):
@@ -93,6 +102,7 @@ class PairTestLayer(Layer):
                 self.master.type_name, self.slave.type_name, what, rel))
 
     def forward(self, is_train, nodes_in, nodes_out):
+        self._sync()
         for s, n in zip(self.snodes_in, nodes_in):
             s.shape = list(n.shape)
             s.data = n.data.clone()

@@ -1,0 +1,140 @@
+/*
+ * cxxnet_b200 kernel library - C ABI of libcxxnet_b200.so (sm_100a only).
+ *
+ * Every entry point takes raw device pointers and a cudaStream_t, launches asynchronously on
+ * that stream, allocates nothing (unless its comment says otherwise) and returns 0 on success,
+ * a cudaError_t (> 0) or a negative library error.  bf16 tensors are passed as void*.
+ * Activations are NHWC; 2-D matrices are row-major [rows][ld] with `cols` valid entries.
+ * Citations name the reference code whose BEHAVIOUR the kernel reproduces
+ * (paths relative to the cxxnet reference tree).
+ */
+#ifndef CXXNET_B200_H_
+#define CXXNET_B200_H_
+
+#include <cuda_runtime_api.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- GEMM flags --------------------------------------------------------------------------- */
+#define CXN_GEMM_RELU     1  /* max(x,0) after bias                                  */
+#define CXN_GEMM_OUT_BF16 2  /* D is bf16 (else fp32)                                */
+#define CXN_GEMM_ATOMIC   4  /* fp32 D += partial with red.global.add (split-K)      */
+#define CXN_GEMM_BETA1    8  /* fp32 D = D + result (read-modify-write, no atomics)  */
+
+/* K5/K6 + the GEMMs inside K1-K3: D[z] = A[z] * B[z]^T (+bias) on tcgen05 tensor cores, bf16 in,
+ * fp32 accumulate in TMEM, operands by TMA.  a_mn / b_mn = 0: operand stored [MN][K] (K
+ * contiguous); 1: stored [K][MN].  Leading dimensions and strides in elements (multiples of 8).
+ * Reference: dot() calls in src/layer/fullc_layer-inl.hpp:108-129 and
+ * src/layer/convolution_layer-inl.hpp:93-96,135-142 (cuBLAS SGEMM behind mshadow). */
+int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a_mn, const void* B, long long ldb,
+                  long long strideB, int b_mn, void* D, long long ldd, long long strideD, const float* bias,
+                  long long strideBias, int M, int N, int K, int batch, int splits, int flags, int bn,
+                  cudaStream_t stream);
+
+/* K1 (and K2 for stride-1 layers): implicit-GEMM convolution forward, bias (+ReLU) fused.
+ * Reference: src/layer/convolution_layer-inl.hpp:79-105. */
+int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
+                   long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW, void* y,
+                   long long ldy, const float* bias, int relu, cudaStream_t stream);
+/* K3: implicit-GEMM weight gradient, split-K over pixels, fp32 atomics into dw.
+ * Reference: src/layer/convolution_layer-inl.hpp:121-138. */
+int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
+                   long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW, float* dw,
+                   long long lddw, int splits, cudaStream_t stream);
+/* filter flip + channel transpose used to run backward-data as a forward convolution. */
+int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in, int ld_out,
+                          cudaStream_t stream);
+/* explicit NHWC patch gather / scatter (fallback path).  Reference: unpack_patch2col /
+ * pack_col2patch use in src/layer/convolution_layer-inl.hpp:86-92,143-151. */
+int cxn_im2col_nhwc(const void* x, void* col, int N, int H, int W, int C, int G, int KH, int KW, int stride, int pad_y,
+                    int pad_x, int OH, int OW, int ldk, long long gstride, cudaStream_t stream);
+int cxn_col2im_nhwc(const void* col, void* dx, int N, int H, int W, int C, int G, int KH, int KW, int stride,
+                    int pad_y, int pad_x, int OH, int OW, int ldk, long long gstride, cudaStream_t stream);
+
+/* ---- layout (API boundary: public layout is NCHW fp32, src/layer/layer.h:33-54) ------------- */
+int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C, int HW, int ldc, cudaStream_t stream);
+int cxn_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int N, int C, int HW, int ldc, cudaStream_t stream);
+/* flatten in (c,h,w) order and its inverse.  Reference: src/layer/flatten_layer-inl.hpp:10-39. */
+int cxn_bf16_hwc_chw(const void* src, void* dst, int N, int C, int HW, long long src_img, long long dst_img,
+                     int ld_hwc, int ld_chw, int to_chw, cudaStream_t stream);
+/* kind: 0 bf16->bf16, 1 f32->bf16, 2 bf16->f32, 3 f32->f32.  Concat / split copies (K14). */
+int cxn_copy2d(const void* src, long long lds, void* dst, long long ldd, long long rows, int cols, int kind,
+               int accumulate, cudaStream_t stream);
+int cxn_fill_f32(float* p, long long n, float v, cudaStream_t stream);
+
+/* ---- K7 activations: op 0 relu, 1 sigmoid, 2 tanh, 3 xelu(b).  Backward takes the ACTIVATED
+ * value, as the reference keeps it in the input node.  src/layer/op.h:27-73,
+ * src/layer/activation_layer-inl.hpp:28-37, src/layer/xelu_layer-inl.hpp:35-44. */
+int cxn_act_fwd(const void* x, void* y, long long rows, int cols, long long ld, int op, float b, cudaStream_t stream);
+int cxn_act_bwd(const void* y, const void* dy, void* dx, long long rows, int cols, long long ld, int op, float b,
+                cudaStream_t stream);
+/* K12 dropout: y = x * (U<pkeep)/pkeep with a Philox mask regenerated from (seed, *counter).
+ * src/layer/dropout_layer-inl.hpp:44-58. */
+int cxn_dropout(const void* x, void* y, long long rows, int cols, long long ld, float pkeep, unsigned long long seed,
+                const unsigned long long* counter, cudaStream_t stream);
+int cxn_counter_add(unsigned long long* counter, unsigned long long inc, cudaStream_t stream);
+/* K4 bias gradient: out[c] (+)= sum_r x[r][c].  src/layer/fullc_layer-inl.hpp:123-125,
+ * src/layer/convolution_layer-inl.hpp:117-119. */
+int cxn_colsum_bf16(const void* x, long long rows, int cols, long long ld, float* out, int accumulate,
+                    cudaStream_t stream);
+
+/* ---- K8/K9 pooling: mode 0 max, 1 sum, 2 avg; ceil-style output, clipped windows, avg / k*k,
+ * max-unpool to every tie; relu=1 is relu_max_pooling.  src/layer/pooling_layer-inl.hpp:45-106. */
+int cxn_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int ky, int kx, int stride, int OH, int OW,
+                 int mode, int relu, cudaStream_t stream);
+int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, int ky, int kx,
+                 int stride, int OH, int OW, int mode, int relu, cudaStream_t stream);
+/* ---- K10/K11 local response normalisation across channels.  src/layer/lrn_layer-inl.hpp:53-75. */
+int cxn_lrn_fwd(const void* x, void* y, long long pixels, int C, int nsize, float alpha, float beta, float knorm,
+                cudaStream_t stream);
+int cxn_lrn_bwd(const void* x, const void* dy, void* dx, long long pixels, int C, int nsize, float alpha, float beta,
+                float knorm, cudaStream_t stream);
+
+/* ---- K13 loss layers: in-place softmax / sigmoid on the fp32 output node and the gradient
+ * (p - target) * scale as bf16.  kind 0: class-index label, 1: dense label.
+ * src/layer/loss/softmax_layer-inl.hpp:21-32, loss_layer_base-inl.hpp:52-63. */
+int cxn_softmax_rows(float* x, int rows, int cols, long long ld, cudaStream_t stream);
+int cxn_sigmoid_rows(float* x, long long rows, int cols, long long ld, cudaStream_t stream);
+int cxn_loss_grad(const float* p, long long ld, const float* label, long long label_ld, void* g, long long ldg,
+                  long long rows, int cols, float scale, int kind, cudaStream_t stream);
+
+/* ---- K15 updaters on the flat parameter arena: kind 0 sgd, 1 nag, 2 adam; zeroes the gradient
+ * and refreshes the bf16 GEMM shadow in the same pass.  `segs` is an array of 64-byte segment
+ * records (cxn_segment_bytes()), `chunk_seg` maps each cxn_update_chunk()-element chunk to its
+ * segment.  src/updater/{sgd,nag,adam}_updater-inl.hpp. */
+int cxn_segment_bytes(void);
+int cxn_update_chunk(void);
+int cxn_update(float* w, float* g, float* m, float* m2, void* shadow, const void* segs, const int* chunk_seg,
+               long long chunk_begin, long long chunk_end, int kind, cudaStream_t stream);
+int cxn_refresh_shadow(const float* w, void* shadow, const void* segs, const int* chunk_seg, long long nchunks,
+                       cudaStream_t stream);
+
+/* ---- K17/K19 multi-GPU: fused gradient reduce-scatter + update + weight all-gather over
+ * NVLink peer memory, one launch per layer bucket; weight broadcast.  `peers` is a HOST array
+ * of every rank's symmetric-block base address as mapped in the calling process.
+ * src/updater/async_updater-inl.hpp:94-127, src/nnet/nnet_impl-inl.hpp:70-81. */
+int cxn_fused_rs_update_ag(const unsigned long long* peers, int nranks, int rank, long long off_w, long long off_g,
+                           long long off_m, long long off_m2, long long off_shadow, long long off_flags,
+                           const void* segs, const int* chunk_seg, long long chunk_begin, long long chunk_end, int kind,
+                           unsigned seq, int slot, unsigned* counter, int grid, cudaStream_t stream);
+int cxn_symm_broadcast(const unsigned long long* peers, int nranks, int rank, long long off_flags, long long off,
+                       long long bytes, int root, unsigned seq, int slot, unsigned* counter, int grid,
+                       cudaStream_t stream);
+int cxn_xchg_flag_bytes(void);
+int cxn_xchg_max_ranks(void);
+int cxn_xchg_max_slots(void);
+/* CUDA IPC helpers for the symmetric block (these DO allocate / map device memory). */
+int cxn_ipc_alloc(unsigned long long bytes, unsigned long long* ptr, unsigned char* handle64);
+int cxn_ipc_open(const unsigned char* handle64, unsigned long long* ptr);
+int cxn_ipc_close(unsigned long long ptr);
+int cxn_ipc_free(unsigned long long ptr);
+
+/* number of kernel launches issued by this library in this process */
+unsigned long long cxn_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CXXNET_B200_H_ */

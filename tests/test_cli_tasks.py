@@ -1,0 +1,179 @@
+"""task driver: train / continue / pred / extract / finetune, model naming, metric line format
+(reference src/cxxnet_main.cpp), plus pairtest and weight get/set through the trainer."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+CONF = """
+data = train
+iter = mnist
+    path_img = "none"
+    path_label = "none"
+    num_synthetic = 3000
+    shuffle = 1
+iter = end
+eval = test
+iter = mnist
+    path_img = "none"
+    path_label = "none"
+    num_synthetic = 200
+    index_offset = 7
+iter = end
+pred = %(pred)s
+iter = mnist
+    path_img = "none"
+    path_label = "none"
+    num_synthetic = 200
+    index_offset = 7
+iter = end
+netconfig=start
+layer[+1:fc1] = fullc:fc1
+  nhidden = 32
+  init_sigma = 0.01
+layer[+1:sg1] = sigmoid:se1
+layer[sg1->fc2] = fullc:fc2
+  nhidden = 10
+  init_sigma = 0.01
+layer[+0] = softmax
+netconfig=end
+input_shape = 1,1,784
+batch_size = 100
+dev = cpu
+save_model = 1
+num_round = %(rounds)d
+max_round = %(rounds)d
+eta = 0.1
+momentum = 0.9
+metric[label] = error
+model_dir = %(model_dir)s
+silent = 1
+"""
+
+
+def _run(args, cwd):
+    env = dict(os.environ)
+    env["PYTHONPATH"] = ROOT + os.pathsep + env.get("PYTHONPATH", "")
+    r = subprocess.run([sys.executable, "-m", "cxxnet_b200"] + args, cwd=cwd, env=env, stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    return r
+
+
+def test_train_continue_pred_extract_finetune(tmp_path):
+    mdir = tmp_path / "models"
+    conf = tmp_path / "mnist.conf"
+    conf.write_text(CONF % {"rounds": 2, "model_dir": mdir, "pred": tmp_path / "pred.txt"})
+    r = _run([str(conf)], tmp_path)
+    assert sorted(os.listdir(mdir)) == ["0000.model", "0001.model", "0002.model"]
+    lines = [l for l in r.stderr.splitlines() if l.startswith("[")]
+    assert len(lines) == 2
+    m = re.match(r"\[1\]\ttrain-error:([0-9.eE+-]+)\ttest-error:([0-9.eE+-]+)$", lines[0])
+    assert m, lines[0]
+    assert float(re.match(r"\[2\]\ttrain-error:([0-9.eE+-]+)", lines[1]).group(1)) < min(float(m.group(1)), 0.2)
+    # continue=1 picks up after the latest model and trains the remaining rounds
+    r2 = _run([str(conf), "continue=1", "num_round=3", "max_round=3"], tmp_path)
+    assert "Continue training from round 3" in r2.stdout
+    assert "0003.model" in os.listdir(mdir)
+    assert [l for l in r2.stderr.splitlines() if l.startswith("[3]")]
+    # pred: one class id per line, as many as instances
+    _run([str(conf), "task=pred", "model_in=%s" % (mdir / "0003.model")], tmp_path)
+    preds = (tmp_path / "pred.txt").read_text().split()
+    assert len(preds) == 200 and all(p.isdigit() and 0 <= int(p) <= 9 for p in preds)
+    # extract: text rows + meta "nrow,c,h,w"; top[-1] is the softmax output
+    _run([str(conf), "task=extract", "model_in=%s" % (mdir / "0003.model"), "extract_node_name=top[-1]",
+          "output_format=txt"], tmp_path)
+    rows = (tmp_path / "pred.txt").read_text().strip().split("\n")
+    assert len(rows) == 200 and len(rows[0].split()) == 10
+    assert abs(sum(float(v) for v in rows[0].split()) - 1.0) < 1e-4
+    assert (tmp_path / "pred.txt.meta").read_text().strip() == "200,1,1,10"
+    _run([str(conf), "task=extract", "model_in=%s" % (mdir / "0003.model"), "extract_node_name=sg1",
+          "output_format=bin"], tmp_path)
+    assert os.path.getsize(tmp_path / "pred.txt") == 200 * 32 * 4
+    # finetune: layers with matching names are copied, epoch counter restarts
+    ft = tmp_path / "ft.conf"
+    ft.write_text((CONF % {"rounds": 1, "model_dir": tmp_path / "ft_models", "pred": tmp_path / "p2.txt"})
+                  .replace("fullc:fc2", "fullc:newhead"))
+    r3 = _run([str(ft), "task=finetune", "model_in=%s" % (mdir / "0003.model")], tmp_path)
+    assert "Copying layer fc1" in r3.stdout and "Copying layer newhead" not in r3.stdout
+
+
+def test_test_io_mode_runs_pipeline_only(tmp_path):
+    conf = tmp_path / "c.conf"
+    conf.write_text(CONF % {"rounds": 1, "model_dir": tmp_path / "m", "pred": tmp_path / "p.txt"})
+    r = _run([str(conf), "test_io=1", "silent=0"], tmp_path)
+    assert "start I/O test" in r.stdout and "train-error" not in r.stderr
+
+
+def test_pairtest_layer_reports_zero_error_for_identical_implementations(capsys):
+    from util import make_batch, make_trainer
+    conf = """
+netconfig=start
+layer[+1] = pairtest-conv-conv:pc
+  kernel_size = 3
+  nchannel = 4
+  pad = 1
+layer[+1] = pairtest-relu-relu
+layer[+1] = flatten
+layer[+1] = pairtest-fullc-fullc:pf
+  nhidden = 5
+layer[+0] = softmax
+netconfig=end
+input_shape = 2,6,6
+batch_size = 4
+dev = cpu
+eta = 0.1
+metric = error
+"""
+    tr = make_trainer(conf)
+    for s in range(2):
+        tr.update(make_batch((4, 2, 6, 6), nclass=5, seed=s))
+    reports = []
+    for c in tr.net.connections:
+        reports += getattr(c.layer, "reports", [])
+    assert len(reports) >= 10 and max(r[1] for r in reports) <= 1e-6
+    assert "PairTest" not in capsys.readouterr().err
+    # a deliberately different slave is reported (never fails the run)
+    tr2 = make_trainer(conf.replace("pairtest-relu-relu", "pairtest-relu-tanh"))
+    tr2.update(make_batch((4, 2, 6, 6), nclass=5))
+    assert "PairTest[relu-tanh]" in capsys.readouterr().err
+
+
+def test_get_set_weight_roundtrip_and_update_period():
+    from cxxnet_b200.models import mlp_conf
+    from util import make_batch, make_trainer
+    tr = make_trainer(mlp_conf(dev="cpu"))
+    w, shape = tr.get_weight("fc1", "wmat")
+    assert shape == [100, 784] and w.shape == (100, 784)
+    tr.set_weight(np.zeros_like(w), "fc1", "wmat")
+    assert float(np.abs(tr.get_weight("fc1", "wmat")[0]).max()) == 0.0
+    tr.set_weight(w, "fc1", "wmat")
+    assert np.array_equal(tr.get_weight("fc1", "wmat")[0], w)
+    with pytest.raises(ValueError):
+        tr.get_weight("fc1", "gamma")
+    # update_period=2: weights move only every second call and equal one step on the summed gradient
+    a = make_trainer(mlp_conf(dev="cpu", batch_size=50, extra="update_period = 2\nmomentum = 0\n"))
+    b = make_trainer(mlp_conf(dev="cpu", batch_size=100, extra="momentum = 0\n"))
+    for name in ("fc1", "fc2"):
+        for tag in ("wmat", "bias"):
+            b.set_weight(a.get_weight(name, tag)[0], name, tag)
+    full = make_batch((100, 1, 1, 784), seed=5)
+    from cxxnet_b200.io.data import DataBatch
+    halves = []
+    for lo in (0, 50):
+        h = DataBatch()
+        h.data, h.label, h.batch_size = full.data[lo:lo + 50], full.label[lo:lo + 50], 50
+        halves.append(h)
+    w0 = a.get_weight("fc2", "wmat")[0].copy()
+    a.update(halves[0])
+    assert np.array_equal(a.get_weight("fc2", "wmat")[0], w0) and a.epoch_counter == 0
+    a.update(halves[1])
+    b.update(full)
+    assert a.epoch_counter == 1
+    assert np.allclose(a.get_weight("fc2", "wmat")[0], b.get_weight("fc2", "wmat")[0], atol=1e-6)
