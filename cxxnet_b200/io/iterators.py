@@ -332,8 +332,10 @@ class ImageBinIterator(IIterator):
         self.rs = np.random.RandomState(0)
         self._q = None
         self._thr = None
+        self.use_native = 1
 
     def set_param(self, name, val):
+        if name == "native_reader": self.use_native = int(val)
         if name == "image_list": self.path_imglst.append(val)
         if name == "image_bin": self.path_imgbin.append(val)
         if name == "image_conf_prefix": self.img_conf_prefix = val
@@ -373,8 +375,31 @@ class ImageBinIterator(IIterator):
             print("ThreadImagePageIterator:image_list=%s, bin=%s" % (",".join(self.path_imglst), ",".join(self.path_imgbin)))
         self.before_first()
 
+    def _records_native(self):
+        """file-order records with the pages streamed by the native reader thread."""
+        from . import native
+        rd = native.PageReader(list(self.path_imgbin), 4)
+        try:
+            for fi in range(len(self.path_imglst)):
+                with open(self.path_imglst[fi]) as fl:
+                    for ln in fl:
+                        t = ln.split()
+                        if not t:
+                            continue
+                        blob = rd.next()
+                        if blob is None:
+                            return
+                        yield (int(t[0]), np.asarray([float(x) for x in t[1:1 + self.label_width]], dtype=np.float32),
+                               blob)
+        finally:
+            rd.close()
+
     def _records(self):
         """generator of (index, label, blob) in file order, pages read ahead by a worker thread."""
+        from . import native
+        if not (self.two_stage and self.shuffle) and native.lib() is not None and self.use_native:
+            yield from self._records_native()
+            return
         order = list(range(len(self.path_imgbin)))
         if self.two_stage and self.shuffle:
             self.rs.shuffle(order)

@@ -189,3 +189,48 @@ def test_imgbin_worker_sharding(tmp_path, monkeypatch):
     monkeypatch.setenv("PS_RANK", "2")
     it._parse_image_conf()
     assert [os.path.basename(p) for p in it.path_imglst] == ["part07.lst", "part08.lst", "part09.lst"]
+
+
+def test_im2bin_tool_and_native_page_reader(tmp_path):
+    """bin/im2bin packs a list; the native reader thread and the Python reader return the same blobs."""
+    pytest.importorskip("PIL")
+    import subprocess
+    from PIL import Image
+    from cxxnet_b200.io import native
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "bin", "im2bin")
+    if not os.path.exists(exe) or native.lib() is None:
+        import sys
+        sys.path.insert(0, root)
+        import build as _b
+        _b.build_host()
+    imgdir = tmp_path / "imgs"
+    imgdir.mkdir()
+    lines = []
+    for i in range(7):
+        arr = (np.random.RandomState(100 + i).rand(9, 11, 3) * 255).astype(np.uint8)
+        Image.fromarray(arr).save(imgdir / ("i%d.png" % i))
+        lines.append("%d\t%d\ti%d.png\n" % (i, i % 2, i))
+    (tmp_path / "a.lst").write_text("".join(lines))
+    subprocess.check_call([exe, str(tmp_path / "a.lst"), str(imgdir) + "/", str(tmp_path / "a.bin")])
+    assert os.path.getsize(tmp_path / "a.bin") == 64 << 20
+    rd = native.PageReader([str(tmp_path / "a.bin")])
+    blobs = []
+    while True:
+        b = rd.next()
+        if b is None:
+            break
+        blobs.append(b)
+    assert len(blobs) == 7 and blobs[3] == (imgdir / "i3.png").read_bytes()
+    rd.rewind()
+    assert rd.next() == blobs[0]
+    rd.close()
+    outs = []
+    for use_native in (1, 0):
+        it = _mk('iter = imgbin\n image_list = "%s"\n image_bin = "%s"\n native_reader = %d\n batch_size = 7\n input_shape = 3,9,11\n silent = 1\niter = end\n'
+                 % (tmp_path / "a.lst", tmp_path / "a.bin", use_native))
+        it.before_first()
+        assert it.next()
+        outs.append(it.value().data.clone())
+        it.close()
+    assert torch.equal(outs[0], outs[1])
