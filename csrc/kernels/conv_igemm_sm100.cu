@@ -233,6 +233,19 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
     int stage = 0;
     uint32_t phase = 0;
     const int ohw = p.OH * p.OW;
+    // validity of the KH x KW taps of one output pixel as two bit ranges (rows | cols << 16)
+    auto tap_mask = [&](int ih0, int iw0) -> uint32_t {
+      const int h_lo = max(0, -ih0), h_hi = min(p.KH, p.H - ih0);
+      const int w_lo = max(0, -iw0), w_hi = min(p.KW, p.W - iw0);
+      const uint32_t mh = h_hi > h_lo ? ((1u << h_hi) - 1u) & ~((1u << h_lo) - 1u) : 0u;
+      const uint32_t mw = w_hi > w_lo ? ((1u << w_hi) - 1u) & ~((1u << w_lo) - 1u) : 0u;
+      return mh | (mw << 16);
+    };
+    auto pixel_state = [&](int n, int oh, int ow, bool ok, long long& off, uint32_t& mask) {
+      const int ih0 = oh * p.stride - p.pad_y, iw0 = ow * p.stride - p.pad_x;
+      mask = ok ? tap_mask(ih0, iw0) : 0u;
+      off = (((long long)n * p.H + ih0) * p.W + iw0) * p.Cs;
+    };
     auto decode_pixel = [&](long long pix, bool ok, long long& off, uint32_t& mask) {
       int n = 0, oh = 0, ow = 0;
       if (ok) {
@@ -241,14 +254,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
         oh = r / p.OW;
         ow = r - oh * p.OW;
       }
-      const int ih0 = oh * p.stride - p.pad_y, iw0 = ow * p.stride - p.pad_x;
-      uint32_t mh = 0, mw = 0;
-      if (ok) {
-        for (int kh = 0; kh < p.KH; ++kh) if ((unsigned)(ih0 + kh) < (unsigned)p.H) mh |= 1u << kh;
-        for (int kw = 0; kw < p.KW; ++kw) if ((unsigned)(iw0 + kw) < (unsigned)p.W) mw |= 1u << kw;
-      }
-      mask = mh | (mw << 16);
-      off = (((long long)n * p.H + ih0) * p.W + iw0) * p.Cs;
+      pixel_state(n, oh, ow, ok, off, mask);
     };
     for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       int n_blk, m_blk, split, g;
@@ -298,13 +304,32 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
           ent[a] = table[gok ? gi : 0];
           sel[a] = gok ? ((1u << ent[a].kh) | (1u << (16 + ent[a].kw))) : 0xFFFFFFFFu;
         }
+        // pixel coordinates of this thread's rows, advanced by 64 pixels per k-block without divisions
+        int pn[ITERS], poh[ITERS], pow_[ITERS];
+#pragma unroll
+        for (int i = 0; i < ITERS; ++i) {
+          const long long pix = (long long)kb0 * BK + wl * 16 + i * RPI + rsub;
+          pn[i] = (int)(pix / ohw);
+          const int rr = (int)(pix - (long long)pn[i] * ohw);
+          poh[i] = rr / p.OW;
+          pow_[i] = rr - poh[i] * p.OW;
+        }
+        const int adv_n = BK / ohw, adv_r = BK - adv_n * ohw;
+        const int adv_oh = adv_r / p.OW, adv_ow = adv_r - adv_oh * p.OW;
         for (int kb = kb0; kb < kb1; ++kb) {
           long long roff[ITERS];
           uint32_t rmask[ITERS];
 #pragma unroll
           for (int i = 0; i < ITERS; ++i) {
-            const long long pix = (long long)kb * BK + wl * 16 + i * RPI + rsub;
-            decode_pixel(pix, pix < rows, roff[i], rmask[i]);
+            pixel_state(pn[i], poh[i], pow_[i], pn[i] < p.N, roff[i], rmask[i]);
+            // advance to the pixel 64 rows further
+            pow_[i] += adv_ow;
+            int c = pow_[i] >= p.OW;
+            pow_[i] -= c * p.OW;
+            poh[i] += adv_oh + c;
+            c = poh[i] >= p.OH;
+            poh[i] -= c * p.OH;
+            pn[i] += adv_n + c;
           }
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sb = smem_base + stage * C::kStageBytes + C::kABytes;
