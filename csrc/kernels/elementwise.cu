@@ -309,9 +309,19 @@ CXN_API int cxn_dropout(const void* x, void* y, long long rows, int cols, long l
   CXN_CHECK_LAUNCH();
   return 0;
 }
+extern "C" int cxn_colsum_bf16_vec(const void* x, long long rows, int cols, long long ld, float* out, cudaStream_t st);
+
 CXN_API int cxn_colsum_bf16(const void* x, long long rows, int cols, long long ld, float* out, int accumulate,
                             cudaStream_t st) {
   if (rows <= 0 || cols <= 0) return 0;
+  if (cols % 8 == 0 && cols <= 2048 && ld % 8 == 0 && rows >= 1024 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 &&
+      (256 / (cols / 8)) >= 1 && (size_t)(256 / (cols / 8)) * cols * 4 <= 48 * 1024) {
+    if (!accumulate) {
+      fill_f32_kernel<<<ew_grid(cols, 256), 256, 0, st>>>(out, cols, 0.0f);
+      CXN_CHECK_LAUNCH();
+    }
+    return cxn_colsum_bf16_vec(x, rows, cols, ld, out, st);
+  }
   int gy = (int)((rows + 255) / 256);
   const int cap = ceil_div(num_sms() * 4, ceil_div(cols, 32));
   if (gy > cap) gy = cap;

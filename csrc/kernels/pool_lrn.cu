@@ -202,6 +202,115 @@ __global__ void lrn_bwd_kernel(const bf16* __restrict__ x, const bf16* __restric
   }
 }
 
+// ------------------------------------------------------------------ LRN, register version
+// C % 8 == 0 and C <= 256: TPP = C/8 lanes own one pixel, 8 channels (one 16-byte load) each;
+// the +-2 channel halo (local_size <= 5) comes from the neighbouring lanes by shuffle.
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 t = __bfloat1622float2(h[j]);
+    f[2 * j] = t.x; f[2 * j + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 o;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+  return o;
+}
+// e[0..11] = {left lane's v[6], v[7], own v[0..7], right lane's v[0], v[1]} (zero outside the pixel)
+__device__ __forceinline__ void halo2(const float* v, float* e, int lane_in_pix, int tpp) {
+  const float l6 = __shfl_up_sync(0xffffffffu, v[6], 1), l7 = __shfl_up_sync(0xffffffffu, v[7], 1);
+  const float r0 = __shfl_down_sync(0xffffffffu, v[0], 1), r1 = __shfl_down_sync(0xffffffffu, v[1], 1);
+  const bool hl = lane_in_pix > 0, hr = lane_in_pix < tpp - 1;
+  e[0] = hl ? l6 : 0.f; e[1] = hl ? l7 : 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) e[2 + j] = v[j];
+  e[10] = hr ? r0 : 0.f; e[11] = hr ? r1 : 0.f;
+}
+template <bool BWD>
+__global__ void lrn_reg_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, bf16* __restrict__ out,
+                               long long pixels, int C, int half, float salpha, float beta, float knorm) {
+  const int tpp = C >> 3;                 // lanes per pixel
+  const int ppw = 32 / tpp;               // pixels per warp
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / tpp, lip = lane - sub * tpp;
+  const bool active = sub < ppw;
+  const long long warp0 = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long p0 = warp0 * ppw; p0 < pixels; p0 += nwarps * ppw) {
+    const long long pix = p0 + sub;
+    const bool ok = active && pix < pixels;
+    float xv[8], gv[8];
+    uint4 raw = make_uint4(0, 0, 0, 0), rawg = make_uint4(0, 0, 0, 0);
+    if (ok) {
+      raw = *reinterpret_cast<const uint4*>(x + pix * C + lip * 8);
+      if (BWD) rawg = *reinterpret_cast<const uint4*>(dy + pix * C + lip * 8);
+    }
+    unpack8(raw, xv);
+    if (BWD) unpack8(rawg, gv);
+    float sq[8], e[12];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sq[j] = xv[j] * xv[j];
+    halo2(sq, e, lip, tpp);
+    float nb[8], o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = e[2 + j];
+      if (half >= 1) s += e[1 + j] + e[3 + j];
+      if (half >= 2) s += e[j] + e[4 + j];
+      const float norm = s * salpha + knorm;
+      nb[j] = __powf(norm, -beta);
+      if (!BWD) o[j] = xv[j] * nb[j];
+      else sq[j] = gv[j] * xv[j] * nb[j] / norm;      // t = g * x * norm^(-beta-1)
+    }
+    if (BWD) {
+      halo2(sq, e, lip, tpp);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float s = e[2 + j];
+        if (half >= 1) s += e[1 + j] + e[3 + j];
+        if (half >= 2) s += e[j] + e[4 + j];
+        o[j] = gv[j] * nb[j] - 2.0f * beta * salpha * s * xv[j];
+      }
+    }
+    if (ok) *reinterpret_cast<uint4*>(out + pix * C + lip * 8) = pack8(o);
+  }
+}
+
+// ------------------------------------------------------------------ column sums, vectorised
+// out[c] (+)= sum_r x[r][c] for C % 8 == 0: each thread owns 8 channels (16-byte loads) and
+// strides over rows; partial sums are combined through shared memory, one atomic per column per CTA.
+__global__ void colsum_vec_kernel(const bf16* __restrict__ x, long long rows, int cols, long long ld,
+                                  float* __restrict__ out) {
+  extern __shared__ float red[];            // [rows_per_block][cols]
+  const int tpr = cols >> 3;                // threads per row
+  const int rpb = blockDim.x / tpr;         // rows per block iteration
+  const int tr = threadIdx.x / tpr, tc = threadIdx.x - tr * tpr;
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  if (tr < rpb) {
+    for (long long r = (long long)blockIdx.x * rpb + tr; r < rows; r += (long long)gridDim.x * rpb) {
+      const uint4 v = *reinterpret_cast<const uint4*>(x + r * ld + tc * 8);
+      float f[8];
+      unpack8(v, f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[tr * cols + tc * 8 + j] = acc[j];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+    float s = 0.f;
+    for (int r = 0; r < rpb; ++r) s += red[r * cols + c];
+    atomicAdd(out + c, s);
+  }
+}
+
 }  // namespace cxn
 
 using namespace cxn;
@@ -235,9 +344,27 @@ CXN_API int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx,
   CXN_CHECK_LAUNCH();
   return 0;
 }
+static inline bool lrn_reg_ok(const void* a, const void* b, int C, int nsize) {
+  return (C % 8 == 0) && C <= 256 && nsize <= 5 && (nsize & 1) &&
+         (((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0);
+}
+static inline int lrn_reg_grid(long long pixels, int C) {
+  const int ppw = 32 / (C / 8);
+  const long long warps = ceil_div_ll(pixels, ppw);
+  const long long blocks = ceil_div_ll(warps, 8);
+  const long long cap = (long long)num_sms() * 8;
+  return (int)(blocks < cap ? blocks : cap);
+}
+
 CXN_API int cxn_lrn_fwd(const void* x, void* y, long long pixels, int C, int nsize, float alpha, float beta,
                         float knorm, cudaStream_t st) {
   if (pixels <= 0 || C <= 0) return 0;
+  if (lrn_reg_ok(x, y, C, nsize)) {
+    lrn_reg_kernel<false><<<lrn_reg_grid(pixels, C), 256, 0, st>>>((const bf16*)x, nullptr, (bf16*)y, pixels, C, nsize / 2,
+                                                                   alpha / nsize, beta, knorm);
+    CXN_CHECK_LAUNCH();
+    return 0;
+  }
   const int threads = 256, wpb = threads / 32;
   const size_t smem = (size_t)wpb * C * sizeof(float);
   if (smem > 48 * 1024) return -7;
@@ -251,6 +378,12 @@ CXN_API int cxn_lrn_fwd(const void* x, void* y, long long pixels, int C, int nsi
 CXN_API int cxn_lrn_bwd(const void* x, const void* dy, void* dx, long long pixels, int C, int nsize, float alpha,
                         float beta, float knorm, cudaStream_t st) {
   if (pixels <= 0 || C <= 0) return 0;
+  if (lrn_reg_ok(x, dy, C, nsize) && (reinterpret_cast<uintptr_t>(dx) & 15) == 0) {
+    lrn_reg_kernel<true><<<lrn_reg_grid(pixels, C), 256, 0, st>>>((const bf16*)x, (const bf16*)dy, (bf16*)dx, pixels, C,
+                                                                  nsize / 2, alpha / nsize, beta, knorm);
+    CXN_CHECK_LAUNCH();
+    return 0;
+  }
   const int threads = 128, wpb = threads / 32;
   const size_t smem = (size_t)wpb * 3 * C * sizeof(float);
   if (smem > 48 * 1024) return -7;
@@ -258,6 +391,21 @@ CXN_API int cxn_lrn_bwd(const void* x, const void* dy, void* dx, long long pixel
   const long long cap = (long long)num_sms() * 8;
   lrn_bwd_kernel<<<(int)(blocks < cap ? blocks : cap), threads, smem, st>>>((const bf16*)x, (const bf16*)dy, (bf16*)dx,
                                                                               pixels, C, nsize, alpha / nsize, beta, knorm);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+
+// vectorised column sum (bias gradients of conv layers); falls back to the generic kernel in elementwise.cu
+CXN_API int cxn_colsum_bf16_vec(const void* x, long long rows, int cols, long long ld, float* out, cudaStream_t st) {
+  const int tpr = cols / 8;
+  const int threads = 256;
+  const int rpb = threads / tpr;
+  const size_t smem = (size_t)rpb * cols * sizeof(float);
+  long long blocks = ceil_div_ll(rows, (long long)rpb * 8);
+  const long long cap = (long long)num_sms() * 4;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  colsum_vec_kernel<<<(int)blocks, threads, smem, st>>>((const bf16*)x, rows, cols, ld, out);
   CXN_CHECK_LAUNCH();
   return 0;
 }

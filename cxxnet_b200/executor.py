@@ -250,6 +250,16 @@ class NeuralNet:
                         and consumers.get(x.index, 0) == 1):
                     p.layer.fuse_relu = True
                     l.fused = True
+        # fold the backward mask of an aliased ReLU into the pooling layer that consumes it
+        for c in self.connections:
+            l = c.layer
+            if c.native and isinstance(l, native._NativePool):
+                x = c.nodes_in[0]
+                p = producer.get(x.index)
+                if (p is not None and p.native and isinstance(p.layer, native.ReluLayer) and x.alias_of is not None
+                        and consumers.get(x.index, 0) == 1 and x.grad is x.alias_of.grad):
+                    l.mask_relu = True
+                    p.layer.skip_bwd = True
         # parameter arena (in peer-mapped symmetric memory when several ranks train together)
         self.symm_block = None
         self.symm_offsets = {}
@@ -280,7 +290,14 @@ class NeuralNet:
             if c.native and c.type != nc.kSharedLayer:
                 c.layer.b200_setup(self)
         c0, h0, w0 = cfg.input_shape
-        self.in_stage = torch.zeros((self.max_batch, c0, h0, w0), dtype=torch.float32, device=self.device)
+        # two fp32 staging slots filled on a copy stream, so the H2D transfer of batch t+1 overlaps
+        # the compute of batch t
+        self.in_stage = [torch.zeros((self.max_batch, c0, h0, w0), dtype=torch.float32, device=self.device)
+                         for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.stage_free = [torch.cuda.Event(), torch.cuda.Event()]
+        self.stage_ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self.stage_idx = 0
         self.extra_stage = [torch.zeros(tuple(self.nodes[i + 1].shape), dtype=torch.float32, device=self.device)
                             for i in range(cfg.extra_data_num)]
         if self.world_size > 1:
@@ -405,14 +422,31 @@ class NeuralNet:
             for i, e in enumerate(extra):
                 self.nodes[i + 1].data = e.to(self.device, non_blocking=True).float().reshape(self.nodes[i + 1].shape)
             return
-        self._stage_in(self.nodes[0], self.in_stage, batch)
+        self.stage_idx ^= 1
+        slot = self.stage_idx
+        main = torch.cuda.current_stream(self.device)
+        if batch.device.type == "cpu" and batch.is_pinned():
+            st = self.in_stage[slot][:b]
+            self.copy_stream.wait_event(self.stage_free[slot])
+            with torch.cuda.stream(self.copy_stream):
+                st.copy_(batch.reshape(st.shape), non_blocking=True)
+                self.stage_ready[slot].record(self.copy_stream)
+            main.wait_event(self.stage_ready[slot])
+            self._convert_in(self.nodes[0], st)
+        else:
+            self._stage_in(self.nodes[0], self.in_stage[slot], batch)
+        self.stage_free[slot].record(main)
         for i, e in enumerate(extra):
             self._stage_in(self.nodes[i + 1], self.extra_stage[i], e)
 
     def _stage_in(self, n: Node, stage: torch.Tensor, batch: torch.Tensor) -> None:
-        b, c, h, w = n.shape
+        b = n.shape[0]
         st = stage[:b]
         st.copy_(batch.reshape(st.shape), non_blocking=True)
+        self._convert_in(n, st)
+
+    def _convert_in(self, n: Node, st: torch.Tensor) -> None:
+        b, c, h, w = n.shape
         L = ops.lib()
         if n.is_mat:
             ops.check(L.cxn_copy2d(st.data_ptr(), w, n.act.ptr, n.act.ld, b, w, 1, 0, ops.stream()), "copy2d")

@@ -253,6 +253,7 @@ class _NativeAct:
     act_op = ops.ACT_RELU
     alias_ok = False    # out node may share the in node's buffers (sign-preserving activations)
     fused = False       # forward folded into the producing GEMM epilogue
+    skip_bwd = False    # backward mask folded into the consuming pooling layer
 
     def _b(self):
         return getattr(self, "b", 1.0)
@@ -270,7 +271,7 @@ class _NativeAct:
                       "copy2d")
 
     def b200_backprop(self, ex, prop_grad):
-        if not prop_grad:
+        if not prop_grad or self.skip_bwd:
             return
         x, y = self.nodes_in[0], self.nodes_out[0]
         rows = _rows(x)
@@ -300,13 +301,15 @@ class XeluLayer(_NativeAct, zoo.XeluLayer):
 class _NativePool:
     has_b200 = True
     pool_mode = ops.POOL_MAX
+    mask_relu = False   # backward also applies the mask of the ReLU that produced the input node
 
-    def _args(self):
+    def _args(self, bwd=False):
         p = self.param
         x, y = self.nodes_in[0], self.nodes_out[0]
         b, c, h, w = x.shape
+        relu = self.fused_relu or (bwd and self.mask_relu)
         return (b, h, w, c, p.kernel_height, p.kernel_width, p.stride, y.shape[2], y.shape[3], self.pool_mode,
-                1 if self.fused_relu else 0)
+                1 if relu else 0)
 
     def b200_forward(self, ex, is_train):
         x, y = self.nodes_in[0], self.nodes_out[0]
@@ -319,7 +322,7 @@ class _NativePool:
         if not prop_grad:
             return
         x, y = self.nodes_in[0], self.nodes_out[0]
-        ops.check(ops.lib().cxn_pool_bwd(x.act.ptr, y.act.ptr, y.grad.ptr, x.grad.ptr, *self._args(), ops.stream()),
+        ops.check(ops.lib().cxn_pool_bwd(x.act.ptr, y.act.ptr, y.grad.ptr, x.grad.ptr, *self._args(True), ops.stream()),
                   "pool_bwd")
 
 
