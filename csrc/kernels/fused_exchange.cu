@@ -18,6 +18,7 @@
 // All ranks issue the same bucket sequence on an in-order stream, so the spin waits cannot
 // deadlock; every wait is bounded and traps on timeout.
 #include "common.cuh"
+#include <mutex>
 #include <string.h>
 
 namespace cxn {
@@ -281,6 +282,16 @@ static int fill_params(Params* p, const unsigned long long* peers, int nranks, i
 // One bucket of the fused gradient exchange.  `peers` is a HOST array of nranks block base
 // addresses (this rank's own block at index `rank`).  `grid` CTAs (<= resident capacity; the
 // kernel spins on peer flags, so every CTA must be co-resident).
+static int launch_fused(const Params& p, int nranks, int grid, cudaStream_t st) {
+  if (grid < 1) grid = 1;
+  if (grid > num_sms()) grid = num_sms();
+  if (nranks <= 2) fused_rs_update_ag_kernel<2, 4><<<grid, kThreads, 0, st>>>(p);
+  else if (nranks <= 4) fused_rs_update_ag_kernel<4, 4><<<grid, kThreads, 0, st>>>(p);
+  else fused_rs_update_ag_kernel<8, 2><<<grid, kThreads, 0, st>>>(p);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+
 CXN_API int cxn_fused_rs_update_ag(const unsigned long long* peers, int nranks, int rank, long long off_w,
                                    long long off_g, long long off_m, long long off_m2, long long off_shadow,
                                    long long off_flags, const void* segs, const int* chunk_seg, long long cb,
@@ -291,13 +302,75 @@ CXN_API int cxn_fused_rs_update_ag(const unsigned long long* peers, int nranks, 
                        cb, ce, kind, seq, slot, counter);
   if (rc) return rc;
   if (ce <= cb) return 0;
-  if (grid < 1) grid = 1;
-  if (grid > num_sms()) grid = num_sms();
-  if (nranks <= 2) fused_rs_update_ag_kernel<2, 4><<<grid, kThreads, 0, st>>>(p);
-  else if (nranks <= 4) fused_rs_update_ag_kernel<4, 4><<<grid, kThreads, 0, st>>>(p);
-  else fused_rs_update_ag_kernel<8, 2><<<grid, kThreads, 0, st>>>(p);
-  CXN_CHECK_LAUNCH();
-  return 0;
+  return launch_fused(p, nranks, grid, st);
+}
+
+// ------------------------------------------------------------------ entry point without allocation
+// The fused exchange needs one word of scratch per bucket: the counter its CTAs use to find out
+// which of them finished last.  cxn_fused_rs_update_ag takes that word from the caller, which in
+// practice means the caller allocated it.  Some hosts cannot: an inference / training server that
+// hands all device memory to its own pool at start-up (a later cudaMalloc simply fails), or a
+// latency-critical loop that must not hit the implicit device-wide synchronisation of
+// cudaMalloc / cudaFree.  For them the counters below live in the library image itself.
+//
+//   * kNoAllocSlots words = 1 KiB, resident on every GPU that loads the library until exit.
+//   * slot must be < kNoAllocSlots (one word per bucket); larger values are refused.
+//   * The word is cleared on the stream before every launch, so a call never depends on what an
+//     earlier (possibly aborted) call left behind.
+//   * All calls share the array: two calls for the same slot that overlap on the GPU race on
+//     its word.  Calls on one stream, or for different slots, do not.
+//   * The first call on each device resolves the array's device address (cudaGetSymbolAddress
+//     with that device current); make that first call outside any stream capture.
+constexpr int kNoAllocSlots = 256;
+constexpr int kNoAllocMaxDevices = 64;
+static __device__ __align__(256) unsigned g_noalloc_counters[kNoAllocSlots];
+
+CXN_API int cxn_fused_rs_update_ag_noalloc_max_slots() { return kNoAllocSlots; }
+
+CXN_API int cxn_fused_rs_update_ag_noalloc(const unsigned long long* peers, int nranks, int rank, long long off_w,
+                                           long long off_g, long long off_m, long long off_m2, long long off_shadow,
+                                           long long off_flags, const void* segs, const int* chunk_seg, long long cb,
+                                           long long ce, int kind, unsigned seq, int slot, int grid,
+                                           cudaStream_t st) {
+  if (slot < 0 || slot >= kNoAllocSlots) {
+    fprintf(stderr, "[cxxnet_b200] cxn_fused_rs_update_ag_noalloc: slot %d is outside the built-in scratch "
+                    "(%d slots); use cxn_fused_rs_update_ag with caller-provided scratch\n", slot, kNoAllocSlots);
+    return -30;
+  }
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kNoAllocMaxDevices) {
+    fprintf(stderr, "[cxxnet_b200] cxn_fused_rs_update_ag_noalloc: device ordinal %d not supported\n", dev);
+    return -31;
+  }
+  // g_noalloc_counters names a host-side handle here, not a device address: resolve it once per
+  // device, with that device current, and hand the resolved pointer to the kernel.
+  static std::mutex mu;
+  static unsigned* dev_ptr[kNoAllocMaxDevices] = {nullptr};
+  unsigned* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (dev_ptr[dev] == nullptr) {
+      void* sym = nullptr;
+      e = cudaGetSymbolAddress(&sym, g_noalloc_counters);
+      if (e != cudaSuccess) {
+        fprintf(stderr, "[cxxnet_b200] cudaGetSymbolAddress(g_noalloc_counters) failed on device %d: %s\n", dev,
+                cudaGetErrorString(e));
+        return (int)e;
+      }
+      dev_ptr[dev] = static_cast<unsigned*>(sym);
+    }
+    base = dev_ptr[dev];
+  }
+  Params p;
+  int rc = fill_params(&p, peers, nranks, rank, off_w, off_g, off_m, off_m2, off_shadow, off_flags, segs, chunk_seg,
+                       cb, ce, kind, seq, slot, base + slot);
+  if (rc) return rc;
+  if (ce <= cb) return 0;
+  e = cudaMemsetAsync(base + slot, 0, sizeof(unsigned), st);   // the counter must start at zero
+  if (e != cudaSuccess) return (int)e;
+  return launch_fused(p, nranks, grid, st);
 }
 
 CXN_API int cxn_symm_broadcast(const unsigned long long* peers, int nranks, int rank, long long off_flags,

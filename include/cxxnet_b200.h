@@ -119,6 +119,22 @@ int cxn_fused_rs_update_ag(const unsigned long long* peers, int nranks, int rank
                            long long off_m, long long off_m2, long long off_shadow, long long off_flags,
                            const void* segs, const int* chunk_seg, long long chunk_begin, long long chunk_end, int kind,
                            unsigned seq, int slot, unsigned* counter, int grid, cudaStream_t stream);
+/* Same exchange for hosts that must not allocate device memory (no counterpart in the reference).
+ * Meant for a process that hands the whole GPU to its own pool at start-up, so that a later
+ * cudaMalloc by a library fails, and for latency-critical loops that cannot take the device-wide
+ * synchronisation of cudaMalloc / cudaFree.  The per-bucket CTA counter that the entry point above
+ * takes from the caller lives here in a 1 KiB array inside the library image (256 slots, resident
+ * on every GPU that loads the library until exit): `slot` >= cxn_fused_rs_update_ag_noalloc_max_slots()
+ * is refused with an error and nothing is launched.  The slot's word is cleared on `stream` before
+ * each launch.  All calls share the array, so two calls for the same slot that overlap on the GPU
+ * race.  The first call on each device resolves the array's device address; make that call
+ * outside any stream capture.  Calls no cudaMalloc / cudaFree or allocating library routine. */
+int cxn_fused_rs_update_ag_noalloc(const unsigned long long* peers, int nranks, int rank, long long off_w,
+                                   long long off_g, long long off_m, long long off_m2, long long off_shadow,
+                                   long long off_flags, const void* segs, const int* chunk_seg, long long chunk_begin,
+                                   long long chunk_end, int kind, unsigned seq, int slot, int grid,
+                                   cudaStream_t stream);
+int cxn_fused_rs_update_ag_noalloc_max_slots(void);
 int cxn_symm_broadcast(const unsigned long long* peers, int nranks, int rank, long long off_flags, long long off,
                        long long bytes, int root, unsigned seq, int slot, unsigned* counter, int grid,
                        cudaStream_t stream);
