@@ -58,6 +58,8 @@ struct Params {
   int relu;
   // wgrad
   int splits, kb_per_split;
+  // fprop: whole filter panel resident in shared memory (single group, single n-tile, small K*N)
+  int b_resident;
 };
 
 struct GatherEntry { int off; short kh, kw; };
@@ -85,8 +87,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
   auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + kAccStages + a); };
+  const uint32_t bres_bar = bar_base + 8u * (2 * C::kStages + 2 * kAccStages);
   volatile uint32_t* tmem_ptr_smem =
-      reinterpret_cast<volatile uint32_t*>(smem_gen + C::kStages * C::kStageBytes + 8 * (2 * C::kStages + 2 * kAccStages));
+      reinterpret_cast<volatile uint32_t*>(smem_gen + C::kStages * C::kStageBytes + 8 * (2 * C::kStages + 2 * kAccStages + 1));
+  // smem addressing: ring of {A,B} stages, or (resident filter) ring of A stages followed by the panel
+  const bool bres = !WGRAD && p.b_resident;
+  const uint32_t a_stride = bres ? (uint32_t)C::kABytes : (uint32_t)C::kStageBytes;
+  const uint32_t bres_base = smem_base + C::kStages * C::kABytes;
+  const uint32_t bres_kb_bytes = (uint32_t)p.bn * BK * 2;
   GatherEntry* table = reinterpret_cast<GatherEntry*>(smem_gen + C::kStages * C::kStageBytes + 256);
 
   const int warp = threadIdx.x >> 5;
@@ -126,6 +134,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
       mbar_init(tfull_bar(a), 1);
       mbar_init(tempty_bar(a), 4);
     }
+    mbar_init(bres_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmDense) : "memory");
@@ -154,15 +163,22 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      if (bres) {
+        // the whole filter panel, once per CTA
+        mbar_expect_tx(bres_bar, (uint32_t)num_kb * bres_kb_bytes);
+        for (int kb = 0; kb < num_kb; ++kb) tma_load_3d(bres_base + kb * bres_kb_bytes, &tmDense, bres_bar, kb * BK, 0, 0);
+      }
       for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         int n_blk, m_blk, split, g;
         decode_tile(t, n_blk, m_blk, split, g);
         const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          const uint32_t sa = smem_base + stage * C::kStageBytes;
+          const uint32_t sa = smem_base + stage * a_stride;
           const uint32_t sb = sa + C::kABytes;
-          if (!WGRAD) {
+          if (bres) {
+            mbar_arrive(full_bar(stage));   // keeps the arrival count uniform; the operand is already resident
+          } else if (!WGRAD) {
             // B = W[g] : K-major box {64 (k), bn (n)}
             mbar_expect_tx(full_bar(stage), (uint32_t)p.bn * BK * 2);
             tma_load_3d(sb, &tmDense, full_bar(stage), kb * BK, n_blk * p.bn, g);
@@ -190,6 +206,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      if (bres) mbar_wait(bres_bar, 0);
       for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         int n_blk, m_blk, split, g;
         decode_tile(t, n_blk, m_blk, split, g);
@@ -201,8 +218,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
           mbar_wait(full_bar(stage), phase);
           fence_proxy_async();   // cp.async (generic proxy) writes -> tensor-core (async proxy) reads
           tc_fence_after();
-          const uint32_t sa = smem_base + stage * C::kStageBytes;
-          const uint32_t sb = sa + C::kABytes;
+          const uint32_t sa = smem_base + stage * a_stride;
+          const uint32_t sb = bres ? bres_base + kb * bres_kb_bytes : sa + C::kABytes;
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t ad = make_desc(sa + k * kStep, WGRAD ? kLboMN : 0u, kSbo);
@@ -277,7 +294,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
           const GatherEntry e = table[gok ? gi : 0];
           const uint32_t sel = gok ? ((1u << e.kh) | (1u << (16 + e.kw))) : 0xFFFFFFFFu;
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          const uint32_t abase = smem_base + stage * C::kStageBytes;
+          const uint32_t abase = smem_base + stage * a_stride;
 #pragma unroll
           for (int i = 0; i < ITERS; ++i) {
             const int rl = wl * 32 + i * RPI + rsub;
@@ -411,9 +428,18 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
           }
         } else {
           float* d = reinterpret_cast<float*>(p.D) + off;
+          if (lim == 32 && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+            // 128-bit reductions: a quarter of the L2 atomic operations of the scalar form
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < lim) atomicAdd(d + j, f[j]);
+            for (int q = 0; q < 8; ++q)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + 4 * q), "f"(f[4 * q]),
+                           "f"(f[4 * q + 1]), "f"(f[4 * q + 2]), "f"(f[4 * q + 3])
+                           : "memory");
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < lim) atomicAdd(d + j, f[j]);
+          }
         }
       }
       tc_fence_before();
@@ -555,6 +581,13 @@ CXN_API int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg,
   if (rc) return rc;
   const long long tiles = ceil_div_ll(rows, BM) * ceil_div(Ng, p.bn) * G;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  // small single-group filters stay resident in shared memory for the whole (persistent) kernel
+  {
+    const int stages = bnmax >= 256 ? 4 : 6;
+    const long long ring_b = (long long)stages * bnmax * BK * 2;             // smem the B slots of the ring would use
+    const long long panel = (long long)ceil_div(p.Kg, BK) * p.bn * BK * 2;
+    p.b_resident = (G == 1 && Ng <= p.bn && panel <= ring_b && tiles > 2LL * grid) ? 1 : 0;
+  }
   return bnmax == 256 ? launch<256, false>(tm, p, grid, st) : launch<128, false>(tm, p, grid, st);
 }
 
@@ -577,9 +610,12 @@ CXN_API int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg,
   const int num_kb = (int)ceil_div_ll(rows, BK);
   const long long base_tiles = (long long)ceil_div(Ng, BM) * ceil_div(p.Kg, p.bn) * G;
   if (splits <= 0) {
-    splits = (int)((2LL * num_sms() + base_tiles - 1) / base_tiles);
+    // aim at ~4 tiles per SM so the round-robin tile assignment stays balanced, but keep at least
+    // 8 k-blocks per tile and never exceed a whole number of waves by a few stragglers
+    splits = (int)((4LL * num_sms()) / base_tiles);
     const int max_splits = num_kb / 8 > 0 ? num_kb / 8 : 1;
     if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
   }
   if (splits > num_kb) splits = num_kb;
   if (splits < 1) splits = 1;

@@ -19,6 +19,7 @@
 // deadlock; every wait is bounded and traps on timeout.
 #include "common.cuh"
 #include <mutex>
+#include <stdlib.h>
 #include <string.h>
 
 namespace cxn {
@@ -28,6 +29,7 @@ constexpr int kMaxRanks = 16;
 constexpr int kMaxSlots = 256;
 constexpr int kChunk = 1024;
 constexpr int kThreads = 256;
+constexpr int kMaxBucketSegs = 8;
 
 struct Segment {   // must match loss_update.cu
   long long start, n, shadow_off;
@@ -46,6 +48,7 @@ struct Params {
   unsigned seq;
   int slot;
   unsigned* counter;        // local scratch: CTA completion counter (zero between launches)
+  int dbg;                  // profiling aid (CXN_XCHG_DBG): 1 skip peer loads, 2 skip peer stores, 4 skip phase 2
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
@@ -95,9 +98,25 @@ __device__ __forceinline__ float clip_grad(float g, float c) {
   return fminf(fmaxf(g, -c), c);
 }
 
+// segment of chunk `ch`: the bucket's few segments are cached in shared memory, so no dependent
+// global loads sit on the critical path of every chunk
+__device__ __forceinline__ int find_seg(const Segment* sseg, int nseg, long long e) {
+  int k = 0;
+#pragma unroll 1
+  for (int i = 1; i < nseg; ++i)
+    if (e >= sseg[i].start) k = i;
+  return k;
+}
+
 template <int NR, int U>   // NR: compile-time upper bound on ranks per load group, U: chunks in flight
-__global__ void __launch_bounds__(kThreads) fused_rs_update_ag_kernel(const Params p) {
+__global__ void __launch_bounds__(kThreads, 4)   // <= 64 registers: must co-reside with the GEMM CTAs it overlaps
+fused_rs_update_ag_kernel(const Params p) {
+  __shared__ Segment sseg[kMaxBucketSegs];
   char* self = p.peers[p.rank];
+  // the segments this bucket covers (contiguous in the table)
+  const int seg_lo = p.chunk_seg[p.cb], seg_hi = p.chunk_seg[p.ce - 1];
+  const int nseg = min(seg_hi - seg_lo + 1, kMaxBucketSegs);
+  if (threadIdx.x < nseg) sseg[threadIdx.x] = p.segs[seg_lo + threadIdx.x];
   // ---------------- entry barrier: every rank's gradients for this bucket are complete
   if (blockIdx.x == 0 && threadIdx.x < p.nranks)
     st_release_sys(flag_ptr(p.peers[threadIdx.x], p.off_flags, 0, p.slot, p.rank), p.seq);
@@ -111,39 +130,32 @@ __global__ void __launch_bounds__(kThreads) fused_rs_update_ag_kernel(const Para
   float* w = reinterpret_cast<float*>(self + p.off_w);
   float* m = reinterpret_cast<float*>(self + p.off_m);
   float* m2 = reinterpret_cast<float*>(self + p.off_m2);
-  // U chunks per CTA iteration: U * nranks independent 128-bit peer loads in flight per thread
-  // (NVLink round trips are ~2-3 us; bandwidth needs megabytes in flight across the chip)
   for (long long ch0 = my0 + (long long)blockIdx.x * U; ch0 < my1; ch0 += (long long)gridDim.x * U) {
     float4 acc[U];
     bool live[U];
-    long long eoff[U];
+    int sidx[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const long long ch = ch0 + u;
+      const long long e = (ch0 + u) * kChunk + threadIdx.x * 4;
       acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      eoff[u] = ch * kChunk + threadIdx.x * 4;
-      live[u] = false;
-      if (ch < my1) {
-        const Segment& sg = p.segs[p.chunk_seg[ch]];
-        live[u] = (eoff[u] - sg.start) < sg.n;
-      }
+      sidx[u] = find_seg(sseg, nseg, e);
+      live[u] = (ch0 + u < my1) && (e - sseg[sidx[u]].start) < sseg[sidx[u]].n;
     }
-    // issue every load of a group of up to RG ranks before consuming any of them
-    constexpr int RG = NR;
-    for (int r0 = 0; r0 < p.nranks; r0 += RG) {
-      float4 buf[RG][U];
+    // issue every load of a group of up to NR ranks before consuming any of them
+    for (int r0 = 0; r0 < p.nranks; r0 += NR) {
+      float4 buf[NR][U];
 #pragma unroll
-      for (int rr = 0; rr < RG; ++rr) {
+      for (int rr = 0; rr < NR; ++rr) {
         if (r0 + rr < p.nranks) {
-          const int src = (p.rank + r0 + rr) % p.nranks;   // start with the local copy, stagger peers
+          const int src = (p.dbg & 1) ? p.rank : (p.rank + r0 + rr) % p.nranks;   // local copy first, peers staggered
           const float* gsrc = reinterpret_cast<const float*>(p.peers[src] + p.off_g);
 #pragma unroll
           for (int u = 0; u < U; ++u)
-            buf[rr][u] = live[u] ? ld_sys_f4(gsrc + eoff[u]) : make_float4(0.f, 0.f, 0.f, 0.f);
+            buf[rr][u] = live[u] ? ld_sys_f4(gsrc + (ch0 + u) * kChunk + threadIdx.x * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
       }
 #pragma unroll
-      for (int rr = 0; rr < RG; ++rr) {
+      for (int rr = 0; rr < NR; ++rr) {
         if (r0 + rr < p.nranks) {
 #pragma unroll
           for (int u = 0; u < U; ++u) {
@@ -155,8 +167,8 @@ __global__ void __launch_bounds__(kThreads) fused_rs_update_ag_kernel(const Para
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (!live[u]) continue;
-      const long long e = eoff[u];
-      const Segment s = p.segs[p.chunk_seg[ch0 + u]];
+      const long long e = (ch0 + u) * kChunk + threadIdx.x * 4;
+      const Segment& s = sseg[sidx[u]];
       const long long rel = e - s.start;
       float4 wv = *reinterpret_cast<const float4*>(w + e);
       float4 mv = *reinterpret_cast<const float4*>(m + e);
@@ -188,7 +200,7 @@ __global__ void __launch_bounds__(kThreads) fused_rs_update_ag_kernel(const Para
       *reinterpret_cast<float4*>(m + e) = mv;
       if (p.kind == 2) *reinterpret_cast<float4*>(m2 + e) = m2v;
       for (int r = 0; r < p.nranks; ++r) {
-        const int dst = (p.rank + r) % p.nranks;
+        const int dst = (p.dbg & 2) ? p.rank : (p.rank + r) % p.nranks;
         st_sys_f4(reinterpret_cast<float*>(p.peers[dst] + p.off_w) + e, wv);
       }
     }
@@ -210,21 +222,45 @@ __global__ void __launch_bounds__(kThreads) fused_rs_update_ag_kernel(const Para
   // ---------------- phase 2 (local): zero gradients, refresh the bf16 shadow of the bucket
   float* g = reinterpret_cast<float*>(self + p.off_g);
   bf16* shadow = reinterpret_cast<bf16*>(self + p.off_shadow);
-  for (long long ch = p.cb + blockIdx.x; ch < p.ce; ch += gridDim.x) {
-    const Segment s = p.segs[p.chunk_seg[ch]];
-    const long long e = ch * kChunk + threadIdx.x * 4;
-    const long long rel = e - s.start;
-    if (rel >= s.n) continue;
-    *reinterpret_cast<float4*>(g + e) = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (s.shadow_off >= 0) {
-      const float4 wv = ld_sys_f4(w + e);
-      const float* wp = reinterpret_cast<const float*>(&wv);
+  constexpr int V = 4;
+  for (long long ch0 = p.cb + (long long)blockIdx.x * V; ch0 < p.ce && !(p.dbg & 4); ch0 += (long long)gridDim.x * V) {
+    float4 wv[V];
+    int sidx[V];
+    bool live[V];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const long long k = rel + j;
-        if (k < s.n) {
-          const long long row = k / s.cols;
-          shadow[s.shadow_off + row * s.shadow_ld + (k - row * s.cols)] = __float2bfloat16(wp[j]);
+    for (int u = 0; u < V; ++u) {
+      const long long e = (ch0 + u) * kChunk + threadIdx.x * 4;
+      sidx[u] = find_seg(sseg, nseg, e);
+      live[u] = (ch0 + u < p.ce) && (e - sseg[sidx[u]].start) < sseg[sidx[u]].n;
+      wv[u] = (live[u] && sseg[sidx[u]].shadow_off >= 0) ? ld_sys_f4(w + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < V; ++u) {
+      if (!live[u]) continue;
+      const long long e = (ch0 + u) * kChunk + threadIdx.x * 4;
+      const Segment& s = sseg[sidx[u]];
+      const long long rel = e - s.start;
+      *reinterpret_cast<float4*>(g + e) = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (s.shadow_off >= 0) {
+        const float* wp = reinterpret_cast<const float*>(&wv[u]);
+        const long long row = rel / s.cols;
+        const long long col = rel - row * s.cols;
+        bf16* dst = shadow + s.shadow_off + row * s.shadow_ld + col;
+        if (col + 3 < s.cols && rel + 3 < s.n && ((reinterpret_cast<uintptr_t>(dst) & 7) == 0)) {
+          __nv_bfloat162 a = __floats2bfloat162_rn(wp[0], wp[1]), b2 = __floats2bfloat162_rn(wp[2], wp[3]);
+          uint2 o;
+          o.x = *reinterpret_cast<uint32_t*>(&a);
+          o.y = *reinterpret_cast<uint32_t*>(&b2);
+          *reinterpret_cast<uint2*>(dst) = o;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const long long k = rel + j;
+            if (k < s.n) {
+              const long long r2 = k / s.cols;
+              shadow[s.shadow_off + r2 * s.shadow_ld + (k - r2 * s.cols)] = __float2bfloat16(wp[j]);
+            }
+          }
         }
       }
     }
@@ -276,6 +312,8 @@ static int fill_params(Params* p, const unsigned long long* peers, int nranks, i
   p->off_w = off_w; p->off_g = off_g; p->off_m = off_m; p->off_m2 = off_m2; p->off_shadow = off_shadow;
   p->off_flags = off_flags; p->segs = (const Segment*)segs; p->chunk_seg = chunk_seg; p->cb = cb; p->ce = ce;
   p->rank = rank; p->nranks = nranks; p->kind = kind; p->seq = seq; p->slot = slot; p->counter = counter;
+  static const int dbg = getenv("CXN_XCHG_DBG") ? atoi(getenv("CXN_XCHG_DBG")) : 0;
+  p->dbg = dbg;
   return 0;
 }
 
@@ -284,10 +322,10 @@ static int fill_params(Params* p, const unsigned long long* peers, int nranks, i
 // kernel spins on peer flags, so every CTA must be co-resident).
 static int launch_fused(const Params& p, int nranks, int grid, cudaStream_t st) {
   if (grid < 1) grid = 1;
-  if (grid > num_sms()) grid = num_sms();
+  if (grid > 2 * num_sms()) grid = 2 * num_sms();
   if (nranks <= 2) fused_rs_update_ag_kernel<2, 4><<<grid, kThreads, 0, st>>>(p);
-  else if (nranks <= 4) fused_rs_update_ag_kernel<4, 4><<<grid, kThreads, 0, st>>>(p);
-  else fused_rs_update_ag_kernel<8, 2><<<grid, kThreads, 0, st>>>(p);
+  else if (nranks <= 4) fused_rs_update_ag_kernel<4, 2><<<grid, kThreads, 0, st>>>(p);
+  else fused_rs_update_ag_kernel<8, 1><<<grid, kThreads, 0, st>>>(p);
   CXN_CHECK_LAUNCH();
   return 0;
 }

@@ -34,7 +34,7 @@ class GradExchange:
         self.arena = net.arena
         self.rank, self.world = net.rank, net.world_size
         self.device = net.device
-        self.grid = grid or int(__import__('os').environ.get('CXN_XCHG_GRID', '96'))
+        self.grid = grid or int(__import__('os').environ.get('CXN_XCHG_GRID', '296'))
         self.seq = 0
         L = ops.lib()
         P, I, LL, U = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_uint
