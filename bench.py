@@ -139,7 +139,10 @@ def run_ours(args, rank, world, local):
     B = args.batch
     tr = NetTrainer()
     dev = "gpu:%d" % local if world == 1 else "gpu:" + ",".join(str(i) for i in range(world))
-    for k, v in parse_config_string(alexnet_conf(batch_size=B, dev=dev, extra=args.extra)):
+    extra = args.extra
+    if world > 1 and "fullc_gather" not in extra:
+        extra += "\nfullc_gather = 1\n"      # the reference's own option for fully connected layers on several GPUs
+    for k, v in parse_config_string(alexnet_conf(batch_size=B, dev=dev, extra=extra)):
         tr.set_param(k, v)
     tr.set_param("silent", "1")
     tr.set_param("eval_train", "1")

@@ -292,6 +292,45 @@ __global__ void __launch_bounds__(kThreads) broadcast_kernel(const Params p, lon
   wait_all(p, 1);
 }
 
+// K18: all-gather of up to two local pieces into every rank's symmetric block, bracketed by the
+// same flag barriers as the fused exchange.  Rank r's piece k lands at dst_off[k] + r * slot_bytes[k]
+// in every block; bytes beyond valid_bytes[k] (a short last batch) are zero-filled.  Used to
+// gather the [activation | output-gradient] rows of a fully connected layer (the reference's
+// fullc_gather, src/updater/async_updater-inl.hpp:67-93) and to publish updated weight shards.
+struct GatherArgs {
+  const char* src[2];
+  long long dst_off[2], slot_bytes[2], valid_bytes[2];
+  int npieces;
+};
+__global__ void __launch_bounds__(kThreads) allgather_kernel(const Params p, const GatherArgs a) {
+  if (blockIdx.x == 0 && threadIdx.x < p.nranks)
+    st_release_sys(flag_ptr(p.peers[threadIdx.x], p.off_flags, 0, p.slot, p.rank), p.seq);
+  wait_all(p, 0);
+  for (int k = 0; k < a.npieces; ++k) {
+    const long long n16 = a.slot_bytes[k] / 16, v16 = a.valid_bytes[k] / 16;
+    const uint4* src = reinterpret_cast<const uint4*>(a.src[k]);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16;
+         i += (long long)gridDim.x * blockDim.x) {
+      const uint4 v = i < v16 ? src[i] : make_uint4(0, 0, 0, 0);
+      for (int r = 0; r < p.nranks; ++r) {
+        const int dst = (p.rank + r) % p.nranks;
+        reinterpret_cast<uint4*>(p.peers[dst] + a.dst_off[k] + (long long)p.rank * a.slot_bytes[k])[i] = v;
+      }
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(p.counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *p.counter = 0u;
+      __threadfence_system();
+      for (int r = 0; r < p.nranks; ++r) st_release_sys(flag_ptr(p.peers[r], p.off_flags, 1, p.slot, p.rank), p.seq);
+    }
+  }
+  wait_all(p, 1);
+}
+
 }  // namespace xchg
 }  // namespace cxn
 
@@ -421,6 +460,28 @@ CXN_API int cxn_symm_broadcast(const unsigned long long* peers, int nranks, int 
   if (grid < 1) grid = 1;
   if (grid > num_sms()) grid = num_sms();
   broadcast_kernel<<<grid, kThreads, 0, st>>>(p, off, bytes, root);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+
+// npieces = 1 or 2; all byte counts multiples of 16; src pointers 16-byte aligned.
+CXN_API int cxn_symm_allgather(const unsigned long long* peers, int nranks, int rank, long long off_flags,
+                               const void* src0, long long dst_off0, long long slot_bytes0, long long valid_bytes0,
+                               const void* src1, long long dst_off1, long long slot_bytes1, long long valid_bytes1,
+                               int npieces, unsigned seq, int slot, unsigned* counter, int grid, cudaStream_t st) {
+  Params p;
+  int rc = fill_params(&p, peers, nranks, rank, 0, 0, 0, 0, 0, off_flags, nullptr, nullptr, 0, 0, 0, seq, slot, counter);
+  if (rc) return rc;
+  if (npieces < 1 || npieces > 2) return -22;
+  GatherArgs a;
+  a.src[0] = (const char*)src0; a.dst_off[0] = dst_off0; a.slot_bytes[0] = slot_bytes0; a.valid_bytes[0] = valid_bytes0;
+  a.src[1] = (const char*)src1; a.dst_off[1] = dst_off1; a.slot_bytes[1] = slot_bytes1; a.valid_bytes[1] = valid_bytes1;
+  a.npieces = npieces;
+  for (int k = 0; k < npieces; ++k)
+    if ((a.slot_bytes[k] % 16) || (a.valid_bytes[k] % 16) || (reinterpret_cast<uintptr_t>(a.src[k]) & 15)) return -21;
+  if (grid < 1) grid = 1;
+  if (grid > num_sms()) grid = num_sms();
+  allgather_kernel<<<grid, kThreads, 0, st>>>(p, a);
   CXN_CHECK_LAUNCH();
   return 0;
 }

@@ -61,6 +61,7 @@ class NeuralNet:
         self.arena = None
         self.arena_alloc = arena_alloc
         self.exchange = None
+        self.need_update = True
         self.accumulate_grads = False
         self.num_sms = 148
         self.step_counter = None
@@ -283,8 +284,11 @@ class NeuralNet:
                 s = self.arena.add(c.layer, i, tag, rows, cols, sld, up, b1, b2)
                 self._seg_of[(i, tag)] = s
         if self.world_size > 1 and self.arena_alloc is None:
+            self._plan_fc_shards()
             self._alloc_symmetric()
         self.arena.finalize()
+        if self.world_size > 1 and self.arena_alloc is None:
+            self._finish_fc_shards()
         self._bind_arena()
         for c in self.connections:
             if c.native and c.type != nc.kSharedLayer:
@@ -304,6 +308,39 @@ class NeuralNet:
             from .parallel.exchange import GradExchange
             self.exchange = GradExchange(self)
 
+    def _plan_fc_shards(self) -> None:
+        """fully connected layers with ``fullc_gather = 1``: row-sharded weight gradient / update."""
+        from .parallel.exchange import FcShard
+        self.fc_shards = {}
+        a = self.arena
+        for i, c in enumerate(self.connections):
+            l = c.layer
+            if not (c.native and isinstance(l, native.FullConnectLayer) and l.fullc_gather
+                    and c.type != nc.kSharedLayer):
+                continue
+            p = l.param
+            nin, nout = p.num_input_node, p.num_hidden
+            rs = ops.round_up((nout + self.world_size - 1) // self.world_size, 8)   # TMA needs 16-byte aligned column offsets
+            if (rs * nin) % a.chunk != 0:
+                continue   # shard boundaries must fall on update chunks; otherwise the plain bucket path is used
+            sh = FcShard()
+            sh.layer_index, sh.layer = i, l
+            sh.rows_per_rank = rs
+            sh.row0 = min(self.rank * rs, nout)
+            sh.my_rows = max(0, min(rs, nout - sh.row0))
+            sh.ld_in, sh.ld_out = c.nodes_in[0].act.ld, c.nodes_out[0].grad.ld
+            sh.wseg = self._seg_of[(i, "wmat")]
+            sh.bseg = self._seg_of.get((i, "bias"))
+            self.fc_shards[i] = sh
+            l.shard = sh
+
+    def _finish_fc_shards(self) -> None:
+        total_rows = self.max_batch * self.world_size
+        for sh in self.fc_shards.values():
+            sh.x_off, x = self.symm_block.alloc(total_rows * sh.ld_in, torch.bfloat16)
+            sh.gy_off, gy = self.symm_block.alloc(total_rows * sh.ld_out, torch.bfloat16)
+            sh.x_all, sh.gy_all = x, gy
+
     def _alloc_symmetric(self) -> None:
         """lay the arenas out inside one CUDA-IPC block that every rank maps (parallel/symm.py)."""
         from .parallel.symm import SymmetricBlock
@@ -312,6 +349,8 @@ class NeuralNet:
         nbuf = 4 if a.kind == ops.UPD_ADAM else 3
         flag_bytes = ops.lib().cxn_xchg_flag_bytes()
         total = nbuf * (n * 4 + 4096) + max(a.shadow_total, 128) * 2 + 4096 + flag_bytes + 65536
+        for sh in getattr(self, "fc_shards", {}).values():
+            total += self.max_batch * self.world_size * (sh.ld_in + sh.ld_out) * 2 + 4096
         self.symm_block = SymmetricBlock(total, self.device)
         off, _ = self.symm_block.carve(flag_bytes)
         self.symm_offsets["flags"] = off
@@ -342,9 +381,12 @@ class NeuralNet:
         a.refresh_shadow()
 
     def sync_weights_from_device(self) -> None:
-        """arena (internal layout) -> layer tensors (checkpoint layout) for native layers."""
+        """arena (internal layout) -> layer tensors (checkpoint layout) for native layers.
+        With sharded fully connected layers this is a collective over all ranks."""
         if self.arena is None:
             return
+        if self.exchange is not None:
+            self.exchange.gather_master()
         for (i, tag), s in self._seg_of.items():
             c = self.connections[i]
             if not c.native:
@@ -481,10 +523,11 @@ class NeuralNet:
                             dist.all_reduce(u.dw)
                         u.update(epoch)
             return
+        self.need_update = need_update
         if need_update:
             self.arena.refresh_hyper(epoch)
-            if self.exchange is not None:
-                self.exchange.begin_step()
+        if self.exchange is not None:
+            self.exchange.begin_step()
         for i in range(n - 1, -1, -1):
             c = self.connections[i]
             prop = i != 0 or prop_to_input

@@ -37,6 +37,7 @@ class FullConnectLayer(zoo.FullConnectLayer):
         super().__init__()
         self.fuse_relu = False
         self.bind = {}
+        self.shard = None     # parallel.exchange.FcShard when trained with fullc_gather on several ranks
 
     def b200_shadow(self, tag):
         p = self.param
@@ -65,7 +66,14 @@ class FullConnectLayer(zoo.FullConnectLayer):
         b = x.shape[0]
         W = self.bind["wmat"]
         gy = y.grad
-        if self.fullc_gather == 0 or ex.world_size == 1:
+        if self.shard is not None and ex.exchange is not None:
+            # fullc_gather: backward-data locally, weight gradient / update row-sharded over the ranks
+            if prop_grad:
+                ops.gemm(gy.ptr, gy.ld, 0, 0, W.shadow.data_ptr(), W.shadow_ld, 0, 1, x.grad.ptr, x.grad.ld, 0, None, 0,
+                         b, p.num_input_node, p.num_hidden, flags=ops.GEMM_OUT_BF16)
+            ex.exchange.fc_backward(self, ex.need_update)
+            return
+        if True:
             # gW (nout x nin) += gy^T . x   : A = gy stored [K=b][M=nout], B = x stored [K=b][N=nin]
             ops.gemm(gy.ptr, gy.ld, 0, 1, x.act.ptr, x.act.ld, 0, 1, W.g.data_ptr(), p.num_input_node, 0, None, 0,
                      p.num_hidden, p.num_input_node, b, flags=ops.GEMM_BETA1 if ex.accumulate_grads else 0)

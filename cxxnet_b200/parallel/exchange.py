@@ -27,14 +27,36 @@ from .. import ops
 from .symm import SymmetricBlock
 
 
+class FcShard:
+    """plan for one fully connected layer trained with ``fullc_gather = 1`` on several ranks."""
+    __slots__ = ("layer_index", "layer", "rows_per_rank", "my_rows", "row0", "x_off", "gy_off", "x_all", "gy_all",
+                 "ld_in", "ld_out", "wseg", "bseg", "slot_gather", "slot_pub", "event", "pending")
+
+
 class GradExchange:
+    """Per-step orchestration of the NVLink exchange.
+
+    * ordinary weighted layers are grouped, in backward order, into buckets of at least
+      ``min_bucket_bytes`` (small conv layers share one launch: at 8 GPUs a launch costs two
+      ~20 us flag barriers regardless of size) and exchanged by ``cxn_fused_rs_update_ag``;
+    * fully connected layers configured with ``fullc_gather = 1`` (reference
+      ``async_updater-inl.hpp:67-93,115-126``) do not exchange their weight gradient at all: the
+      ``[input | output-gradient]`` rows of every rank are all-gathered (a few MB instead of the
+      151 MB fc6 gradient), each rank computes the weight gradient of ITS row shard of W over the
+      whole global batch, updates that shard (momentum lives only there) and publishes the new
+      bf16 weights to every rank.  fp32 masters of foreign shards are refreshed on demand
+      (``gather_master``) for checkpoints / ``get_weight``.
+    """
+
     def __init__(self, net, grid: int = 0):
+        import os
         import torch.distributed as dist
         self.net = net
         self.arena = net.arena
         self.rank, self.world = net.rank, net.world_size
         self.device = net.device
-        self.grid = grid or int(__import__('os').environ.get('CXN_XCHG_GRID', '296'))
+        self.grid = grid or int(os.environ.get("CXN_XCHG_GRID", "296"))
+        self.min_bucket_bytes = int(float(os.environ.get("CXN_XCHG_MIN_BUCKET_MB", "4")) * (1 << 20))
         self.seq = 0
         L = ops.lib()
         P, I, LL, U = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_uint
@@ -42,25 +64,48 @@ class GradExchange:
         L.cxn_fused_rs_update_ag.restype = I
         L.cxn_symm_broadcast.argtypes = [P, I, I, LL, LL, LL, I, U, I, P, I, P]
         L.cxn_symm_broadcast.restype = I
+        L.cxn_symm_allgather.argtypes = [P, I, I, LL, P, LL, LL, LL, P, LL, LL, LL, I, U, I, P, I, P]
+        L.cxn_symm_allgather.restype = I
         if self.world > L.cxn_xchg_max_ranks():
             raise ValueError("too many ranks for the fused exchange")
         self.block: SymmetricBlock = net.symm_block
         self.off = net.symm_offsets
         self.counter = torch.zeros(4, dtype=torch.int32, device=self.device)
-        # buckets: one per weighted layer, in layer order; slot = bucket index
+        self.counter_main = torch.zeros(4, dtype=torch.int32, device=self.device)
         a = self.arena
-        self.buckets: List[Dict] = []
+        self.shards: Dict[int, FcShard] = getattr(net, "fc_shards", {})
+        # buckets over the non-sharded weighted layers, merged in backward order
         by_layer: Dict[int, List[int]] = {}
         for si, s in enumerate(a.segments):
-            by_layer.setdefault(s.layer_index, []).append(si)
-        for li in sorted(by_layer):
+            if s.layer_index not in self.shards:
+                by_layer.setdefault(s.layer_index, []).append(si)
+        self.buckets: List[Dict] = []
+        cur = None
+        for li in sorted(by_layer, reverse=True):
             segs = by_layer[li]
             cb, ce = a.chunk_range(segs[0], segs[-1] + 1)
-            self.buckets.append({"layer": li, "cb": cb, "ce": ce, "slot": len(self.buckets),
-                                 "event": torch.cuda.Event(), "pending": False})
-        if len(self.buckets) + 1 > L.cxn_xchg_max_slots():
+            if cur is not None and cur["cb"] == ce and (cur["ce"] - cur["cb"]) * a.chunk * 4 < self.min_bucket_bytes:
+                cur["cb"] = cb
+                cur["layers"].append(li)
+                cur["trigger"] = li
+            else:
+                cur = {"layers": [li], "trigger": li, "cb": cb, "ce": ce, "event": torch.cuda.Event(),
+                       "pending": False}
+                self.buckets.append(cur)
+        for i, b in enumerate(self.buckets):
+            b["slot"] = i
+        nslots = len(self.buckets)
+        for sh in self.shards.values():
+            sh.slot_gather, sh.slot_pub = nslots, nslots + 1
+            nslots += 2
+            sh.event = torch.cuda.Event()
+            sh.pending = False
+        if nslots + 1 > L.cxn_xchg_max_slots():
             raise ValueError("too many weighted layers for the fused exchange")
-        self.bucket_of_layer = {b["layer"]: b for b in self.buckets}
+        self.bucket_of_layer = {}
+        for b in self.buckets:
+            for li in b["layers"]:
+                self.bucket_of_layer[li] = b
         self.stream = torch.cuda.Stream(device=self.device, priority=-1)
         self.ready = torch.cuda.Event()
         dist.barrier()
@@ -91,7 +136,7 @@ class GradExchange:
     def layer_done(self, layer_index: int) -> None:
         """called right after layer ``layer_index`` finished its backward on the main stream."""
         b = self.bucket_of_layer.get(layer_index)
-        if b is None:
+        if b is None or b["trigger"] != layer_index:
             return
         a = self.arena
         main = torch.cuda.current_stream(self.device)
@@ -111,15 +156,105 @@ class GradExchange:
         if b is not None and b["pending"]:
             torch.cuda.current_stream(self.device).wait_event(b["event"])
             b["pending"] = False
+        sh = self.shards.get(layer_index)
+        if sh is not None and sh.pending:
+            torch.cuda.current_stream(self.device).wait_event(sh.event)
+            sh.pending = False
 
     def wait_all(self) -> None:
         for b in self.buckets:
-            self.wait_layer(b["layer"])
+            self.wait_layer(b["trigger"])
+        for li in self.shards:
+            self.wait_layer(li)
+
+    # ------------------------------------------------------------------ K18: sharded fully connected layers
+    def _allgather(self, pieces, slot, counter, stream) -> None:
+        """pieces: list of (src_ptr, dst_off, slot_bytes, valid_bytes)"""
+        p = list(pieces) + [(None, 0, 0, 0)] * (2 - len(pieces))
+        ops.check(ops.lib().cxn_symm_allgather(
+            self.block.peers_c, self.world, self.rank, self.off["flags"],
+            p[0][0], p[0][1], p[0][2], p[0][3], p[1][0], p[1][1], p[1][2], p[1][3], len(pieces),
+            self.seq, slot, counter.data_ptr(), 64, stream), "cxn_symm_allgather")
+
+    def fc_backward(self, layer, need_update: bool) -> None:
+        """weight-gradient path of a sharded fully connected layer; called from the layer's backward on
+        the main stream, after its backward-data GEMM has been issued."""
+        net, a = self.net, self.arena
+        sh = self.shards[layer.layer_index]
+        x, y = layer.nodes_in[0], layer.nodes_out[0]
+        b = x.shape[0]
+        step = net.max_batch
+        main = torch.cuda.current_stream(self.device)
+        # 1. gather [x | gy] rows of every rank (zero-filled up to `step` rows per rank)
+        self._allgather([(x.act.ptr, sh.x_off, step * sh.ld_in * 2, b * sh.ld_in * 2),
+                         (y.grad.ptr, sh.gy_off, step * sh.ld_out * 2, b * sh.ld_out * 2)],
+                        sh.slot_gather, self.counter_main, main.cuda_stream)
+        total_b = step * self.world
+        p = layer.param
+        nin, nout = p.num_input_node, p.num_hidden
+        # 2. everything else runs on the exchange stream, overlapped with the rest of backward
+        self.ready.record(main)
+        self.stream.wait_event(self.ready)
+        with torch.cuda.stream(self.stream):
+            acc = net.accumulate_grads
+            if sh.my_rows > 0:
+                # gW[row0:row0+my_rows] = GY_all[:, shard]^T . X_all  over the global batch
+                gy_ptr = sh.gy_all.data_ptr() + sh.row0 * 2
+                g_ptr = a.g.data_ptr() + (sh.wseg.start + sh.row0 * nin) * 4
+                ops.gemm(gy_ptr, sh.ld_out, 0, 1, sh.x_all.data_ptr(), sh.ld_in, 0, 1, g_ptr, nin, 0, None, 0,
+                         sh.my_rows, nin, total_b, flags=ops.GEMM_BETA1 if acc else 0)
+            if sh.bseg is not None:
+                ops.check(ops.lib().cxn_colsum_bf16(sh.gy_all.data_ptr(), total_b, nout, sh.ld_out,
+                                                     a.g.data_ptr() + sh.bseg.start * 4, 1 if acc else 0,
+                                                     ops.stream()), "colsum")
+            if need_update:
+                if sh.my_rows > 0:
+                    e0 = sh.wseg.start + sh.row0 * nin
+                    a.update(e0 // a.chunk, (e0 + sh.my_rows * nin + a.chunk - 1) // a.chunk)
+                if sh.bseg is not None:
+                    a.update(sh.bseg.start // a.chunk, (sh.bseg.start + sh.bseg.n + a.chunk - 1) // a.chunk)
+                # 3. publish the updated bf16 rows to every rank
+                sld = sh.wseg.shadow_ld
+                src = a.shadow.data_ptr() + (sh.wseg.shadow_off + sh.row0 * sld) * 2
+                dst = self.off["shadow"] + sh.wseg.shadow_off * 2
+                self._allgather([(src, dst, sh.rows_per_rank * sld * 2, sh.my_rows * sld * 2)],
+                                sh.slot_pub, self.counter, self.stream.cuda_stream)
+            sh.event.record(self.stream)
+            sh.pending = True
+
+    def gather_master(self) -> None:
+        """refresh the fp32 masters of foreign weight shards from their owners (collective)."""
+        if not self.shards:
+            return
+        import torch.distributed as dist
+        from .symm import _RawCudaBuffer
+        self.wait_all()
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+        a = self.arena
+        for sh in self.shards.values():
+            nin = sh.layer.param.num_input_node
+            nout = sh.layer.param.num_hidden
+            for r in range(self.world):
+                if r == self.rank:
+                    continue
+                row0 = r * sh.rows_per_rank
+                rows = max(0, min(sh.rows_per_rank, nout - row0))
+                if rows == 0:
+                    continue
+                e0 = sh.wseg.start + row0 * nin
+                nbytes = rows * nin * 4
+                holder = _RawCudaBuffer(self.block.peer_ptrs[r] + self.off["w"] + e0 * 4, nbytes)
+                peer = torch.as_tensor(holder, device=self.device).view(torch.float32)
+                a.w[e0:e0 + rows * nin].copy_(peer)
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
 
     def check_replicas(self) -> float:
         """max |w_rank - w_rank0| over all weights (the reference's ``test_on_server`` idea)."""
         import torch.distributed as dist
         self.wait_all()
+        self.gather_master()
         ref = self.arena.w.clone()
         dist.broadcast(ref, 0)
         d = (self.arena.w - ref).abs().max()

@@ -138,6 +138,12 @@ int cxn_fused_rs_update_ag_noalloc_max_slots(void);
 int cxn_symm_broadcast(const unsigned long long* peers, int nranks, int rank, long long off_flags, long long off,
                        long long bytes, int root, unsigned seq, int slot, unsigned* counter, int grid,
                        cudaStream_t stream);
+/* K18: all-gather of one or two local pieces into every rank's block (fullc_gather rows, weight
+ * shards), with entry / exit flag barriers.  src/updater/async_updater-inl.hpp:67-93,115-126. */
+int cxn_symm_allgather(const unsigned long long* peers, int nranks, int rank, long long off_flags, const void* src0,
+                       long long dst_off0, long long slot_bytes0, long long valid_bytes0, const void* src1,
+                       long long dst_off1, long long slot_bytes1, long long valid_bytes1, int npieces, unsigned seq,
+                       int slot, unsigned* counter, int grid, cudaStream_t stream);
 int cxn_xchg_flag_bytes(void);
 int cxn_xchg_max_ranks(void);
 int cxn_xchg_max_slots(void);

@@ -14,7 +14,38 @@ extra = "wmat:wd = 0.001\nupdater = " + UPD + "\n"
 _lenet = lenet_conf
 def lenet_conf(**kw):   # dropout off: masks are a function of the element index, i.e. of the batch split
     return _lenet(**kw).replace("threshold = 0.5", "threshold = 0.0")
+MODE = sys.argv[2] if len(sys.argv) > 2 else "lenet"
+if MODE == "gather":
+    # fully connected net whose first layer can be row-sharded (fullc_gather = 1): nin = 1024
+    def lenet_conf(batch_size=64, dev="gpu", extra=""):
+        return """
+netconfig=start
+layer[+1] = fullc:cv1
+  nhidden = 96
+  fullc_gather = 1
+layer[+1] = relu
+layer[+1] = fullc:fc1
+  nhidden = 40
+layer[+1] = sigmoid
+layer[+1] = fullc:fc2
+  nhidden = 10
+layer[+0] = softmax
+netconfig=end
+input_shape = 1,1,1024
+batch_size = %d
+dev = %s
+random_type = xavier
+eta = 0.1
+momentum = 0.9
+metric = error
+%s
+""" % (batch_size, dev, extra)
+    SHAPE = (64, 1, 1, 1024)
+else:
+    SHAPE = (64, 1, 28, 28)
 tr = make_trainer(lenet_conf(batch_size=64, dev="gpu:" + ",".join(str(i) for i in range(world)), extra=extra))
+if MODE == "gather":
+    assert len(tr.net.fc_shards) == 1, "first layer should be sharded"
 assert tr.net.exchange is not None and tr.world_size == world
 assert tr.net.exchange.check_replicas() == 0.0
 # single-GPU twin: same weights, whole batch on one device, no exchange
@@ -22,7 +53,7 @@ single = make_trainer(lenet_conf(batch_size=64, dev="gpu:%d" % rank, extra=extra
 assert single.world_size == 1 and single.net.exchange is None
 copy_weights(tr, single)
 # phase A: gradients only (no update): sum over ranks must equal the single-device gradient
-b = make_batch((64, 1, 28, 28), seed=99)
+b = make_batch(SHAPE, seed=99)
 for t in (tr, single):
     lo, hi = t._slice(b.batch_size)
     t.net.label_info.fields = t._label_fields(b.label, lo, hi, t.device)
@@ -34,7 +65,8 @@ torch.cuda.synchronize()
 for i, c in enumerate(tr.net.connections):
     for tag, w, g in c.layer.weights():
         gm = tr.net.get_grad(i, tag).clone()
-        dist.all_reduce(gm)
+        if not (i in getattr(tr.net, "fc_shards", {}) and tag == "bias"):
+            dist.all_reduce(gm)      # (a sharded layer's bias gradient is already the full-batch sum on every rank)
         gs = single.net.get_grad(i, tag)
         e = rel_err(gs, gm, floor=1e-7)
         if rank == 0:
@@ -44,7 +76,7 @@ for i, c in enumerate(tr.net.connections):
 tr.net.arena.g.zero_(); single.net.arena.g.zero_()
 torch.cuda.synchronize(); dist.barrier()
 for s in range(4):
-    b = make_batch((64, 1, 28, 28), seed=s)
+    b = make_batch(SHAPE, seed=s)
     tr.update(b)
     single.update(b)
 torch.cuda.synchronize()

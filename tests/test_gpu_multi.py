@@ -18,8 +18,8 @@ def _run(nproc, script_args, timeout=300):
 
 
 @pytest.mark.skipif(torch.cuda.is_available() and torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("updater", ["sgd", "nag"])
-def test_fused_exchange_matches_single_gpu(updater):
+@pytest.mark.parametrize("updater,mode", [("sgd", "lenet"), ("nag", "lenet"), ("sgd", "gather")])
+def test_fused_exchange_matches_single_gpu(updater, mode):
     script = os.path.join(ROOT, "tests", "mp_exchange_worker.py")
-    r = _run(2, [script, updater])
+    r = _run(2, [script, updater, mode])
     assert r.returncode == 0 and r.stdout.count("OK") == 2, r.stdout[-4000:]
