@@ -1,8 +1,13 @@
 // Implicit-GEMM convolution on tcgen05 / TMEM for sm_100a (K1-K3 of SURVEY.md section 2.9).
 //
-// No im2col buffer exists: the patch matrix is gathered straight from the NHWC bf16
-// activation tensor into 128B-swizzled shared memory by four producer warps with
-// cp.async (zero-fill for padding), while the dense operand arrives by TMA.
+// No im2col buffer exists: the patch matrix goes straight from the NHWC bf16 activation tensor
+// into 128B-swizzled shared memory, the dense operand arrives by (tiled) TMA.  Two ways to fetch
+// the patches:
+//   ATMA   im2col-mode TMA (cuTensorMapEncodeIm2col): one instruction per k-block loads 128/256
+//          output positions x 64 channels through one filter tap, padding = out-of-bounds zero
+//          fill.  Needs channels-per-group % 64 == 0.  No thread touches the data.
+//   gather four producer warps issue cp.async (zero-fill for padding) from a per-CTA gather table;
+//          any channels-per-group % 8 == 0, and the 4-channel-pitch RGB input.
 //
 //   FPROP  y[n,oh,ow, g*Ng + j]  = sum_{kh,kw,c} x[n, oh*s-p+kh, ow*s-p+kw, g*Cg + c] * W[g][j][kh][kw][c]
 //          A = gathered patches (K-major, rows = output pixels), B = W via TMA (K-major)
@@ -36,8 +41,7 @@ constexpr int UMMA_K = 16;
 constexpr int kThreads = 320;
 constexpr int kGatherWarp0 = 6;
 constexpr int kGatherThreads = 128;
-constexpr int kAccStages = 2;
-constexpr int kMaxGranules = 2048;  // gather table entries (K / granule)
+constexpr int kMaxGranules = 1024;  // gather table entries (K / granule)
 
 struct Params {
   // gathered tensor (NHWC, pixel stride Cs elements)
@@ -60,42 +64,69 @@ struct Params {
   int splits, kb_per_split;
   // fprop: whole filter panel resident in shared memory (single group, single n-tile, small K*N)
   int b_resident;
+  int stages;      // depth of the shared-memory ring actually used (<= Cfg::kMaxStages)
+  int tap_inner;   // fprop, Cg % 64 == 0: visit the k-blocks channel-chunk outer / filter tap inner
+  int l1_alloc;    // gather with cp.async.ca (neighbouring taps then hit in L1) instead of .cg
+  long long* prof; // [grid][16] cycle counters of the warp roles (builds with -DCXN_IGEMM_PROF only)
+  int dbg;         // timing experiments only (results are garbage): 1 skip the gather, 2 skip the TMA loads, 4 skip the MMAs
 };
+
+#ifdef CXN_IGEMM_PROF
+constexpr bool kProf = true;
+#else
+constexpr bool kProf = false;
+#endif
 
 struct GatherEntry { int off; short kh, kw; };
 
-template <int BNMAX>
+// MH = number of 128-row accumulator halves of one tile (fprop only): with MH = 2 a CTA computes a
+// 256-row tile with two MMAs per k-step that share the filter tile, halving the filter's L2 traffic.
+template <int BNMAX, int MH>
 struct Cfg {
-  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kAHalfBytes = BM * BK * 2;
+  static constexpr int kABytes = MH * kAHalfBytes;
   static constexpr int kBBytes = BNMAX * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = BNMAX >= 256 ? 4 : 6;
-  static constexpr int kTmemCols = kAccStages * BNMAX;
   static constexpr int kTableBytes = kMaxGranules * 8;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kTableBytes;
+  static constexpr int kFixedBytes = 1024 + 256 + kTableBytes;
+  static constexpr int kMaxStagesFit = (232448 - kFixedBytes) / kStageBytes;
+  static constexpr int kMaxStages = kMaxStagesFit > 6 ? 6 : kMaxStagesFit;
+  static constexpr int kAccStages = (2 * MH * BNMAX <= 512) ? 2 : 1;
+  static constexpr int kTmemCols = kAccStages * MH * BNMAX;
+  static constexpr int smem_bytes(int stages) { return stages * kStageBytes + kFixedBytes; }
 };
 
-template <int BNMAX, bool WGRAD, int GRAN>
+template <int BNMAX, bool WGRAD, int GRAN, int MH, bool ATMA>
 __global__ void __launch_bounds__(kThreads, 1)
-conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
-  using C = Cfg<BNMAX>;
+conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_constant__ CUtensorMap tmPatch,
+                  const Params p) {
+  using C = Cfg<BNMAX, MH>;
+  static_assert(!(WGRAD && MH != 1), "row-paired tiles are a forward-convolution feature");
+  static_assert(!(ATMA && GRAN != 8), "im2col TMA needs 64-channel chunks");
+  // With ATMA the TMA / MMA warps run warp-uniform and elect the issuing lane (as the GEMM does);
+  // with the gather producers alive the single-lane form is faster (fewer pollers on the barriers
+  // the 128 gather threads arrive on).
+  constexpr bool UNI = ATMA;
+  constexpr int kAccStages = C::kAccStages;
+  constexpr int BMT = BM * MH;               // tile rows
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-  const uint32_t bar_base = smem_base + C::kStages * C::kStageBytes;
+  const int nst = p.stages;
+  const uint32_t bar_base = smem_base + nst * C::kStageBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
-  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + a); };
-  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + kAccStages + a); };
-  const uint32_t bres_bar = bar_base + 8u * (2 * C::kStages + 2 * kAccStages);
+  auto empty_bar = [&](int s) { return bar_base + 8u * (nst + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * nst + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * nst + kAccStages + a); };
+  const uint32_t bres_bar = bar_base + 8u * (2 * nst + 2 * kAccStages);
   volatile uint32_t* tmem_ptr_smem =
-      reinterpret_cast<volatile uint32_t*>(smem_gen + C::kStages * C::kStageBytes + 8 * (2 * C::kStages + 2 * kAccStages + 1));
+      reinterpret_cast<volatile uint32_t*>(smem_gen + nst * C::kStageBytes + 8 * (2 * nst + 2 * kAccStages + 1));
   // smem addressing: ring of {A,B} stages, or (resident filter) ring of A stages followed by the panel
   const bool bres = !WGRAD && p.b_resident;
   const uint32_t a_stride = bres ? (uint32_t)C::kABytes : (uint32_t)C::kStageBytes;
-  const uint32_t bres_base = smem_base + C::kStages * C::kABytes;
+  const uint32_t bres_base = smem_base + nst * C::kABytes;
   const uint32_t bres_kb_bytes = (uint32_t)p.bn * BK * 2;
-  GatherEntry* table = reinterpret_cast<GatherEntry*>(smem_gen + C::kStages * C::kStageBytes + 256);
+  GatherEntry* table = reinterpret_cast<GatherEntry*>(smem_gen + nst * C::kStageBytes + 256);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -105,7 +136,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
   const long long gm = WGRAD ? p.Ng : rows;
   const int gn = WGRAD ? p.Kg : p.Ng;
   const long long gk = WGRAD ? rows : p.Kg;
-  const int tiles_m = (int)ceil_div_ll(gm, BM);
+  const int tiles_m = (int)ceil_div_ll(gm, BMT);
   const int tiles_n = ceil_div(gn, p.bn);
   const int num_kb = (int)ceil_div_ll(gk, BK);
   const int splits = WGRAD ? p.splits : 1;
@@ -114,7 +145,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
 
   // gather table: granule index -> (element offset of the tap inside the image, kh, kw)
   const int ngran = p.Kg / GRAN;
-  for (int i = threadIdx.x; i < ngran; i += blockDim.x) {
+  for (int i = threadIdx.x; !ATMA && i < ngran; i += blockDim.x) {
     const int k = i * GRAN;
     const int pos = k / p.Cg, c0 = k - pos * p.Cg;
     const int kh = pos / p.KW, kw = pos - kh * p.KW;
@@ -126,8 +157,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
   }
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < C::kStages; ++s) {
-      mbar_init(full_bar(s), 1 + kGatherThreads);
+    for (int s = 0; s < nst; ++s) {
+      mbar_init(full_bar(s), ATMA ? 1 : 1 + kGatherThreads);
       mbar_init(empty_bar(s), 1);
     }
     for (int a = 0; a < kAccStages; ++a) {
@@ -137,7 +168,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
     mbar_init(bres_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 0 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmDense) : "memory");
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmDense) : "memory");
+    if (ATMA) asm volatile("prefetch.tensormap [%0];" ::"l"(&tmPatch) : "memory");
+  }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
                      smem_u32((const void*)tmem_ptr_smem)),
@@ -150,6 +184,35 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
+  // k-block visiting order.  Tap-inner (fprop, Cg % 64 == 0): consecutive k-blocks read the same 64
+  // channels through neighbouring filter taps, i.e. the same pixels shifted by one - those re-reads
+  // then hit in L1 instead of going back to L2.  Both operands just visit their k-blocks permuted.
+  const int taps = p.KH * p.KW, cpk = p.Cg >> 6;
+  auto phys_kb = [&](int kb) -> int {
+    if (WGRAD || !p.tap_inner) return kb;
+    const int chunk = kb / taps, tap = kb - chunk * taps;
+    return tap * cpk + chunk;
+  };
+
+  auto wait_bar = [&](uint32_t bar, uint32_t parity) { mbar_wait(bar, parity); };
+  auto issue = [&]() -> bool { return UNI ? elect_one() : true; };   // UNI: all lanes run the loop, one issues
+  // role profiling: cycles spent inside waits / phases, accumulated per CTA
+  const bool prof_on = kProf && p.prof != nullptr;
+  long long pw0 = 0, pw1 = 0, pw2 = 0;
+  const long long prof_t0 = prof_on ? clock64() : 0;
+  auto timed_wait = [&](uint32_t bar, uint32_t parity, long long& accum) {
+    if (prof_on) {
+      const long long t = clock64();
+      wait_bar(bar, parity);
+      accum += clock64() - t;
+    } else {
+      wait_bar(bar, parity);
+    }
+  };
+  auto prof_store = [&](int slot, long long v) {
+    if (prof_on && lane == 0) p.prof[(long long)blockIdx.x * 16 + slot] = v;
+  };
+
   auto decode_tile = [&](long long t, int& n_blk, int& m_blk, int& split, int& g) {
     long long r = t;
     n_blk = (int)(r % tiles_n); r /= tiles_n;
@@ -159,81 +222,142 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
   };
 
   if (warp == 0) {
-    // =========================== TMA producer (dense operand) ===========================
-    if (lane == 0) {
+    // =========================== TMA producer ===========================
+    // dense operand always; with ATMA also the patch operand (im2col mode)
+    if (UNI || lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      if (bres) {
+      if (bres && issue()) {
         // the whole filter panel, once per CTA
         mbar_expect_tx(bres_bar, (uint32_t)num_kb * bres_kb_bytes);
         for (int kb = 0; kb < num_kb; ++kb) tma_load_3d(bres_base + kb * bres_kb_bytes, &tmDense, bres_bar, kb * BK, 0, 0);
       }
+      if (UNI) __syncwarp();
+      const int ohw = p.OH * p.OW;
       for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         int n_blk, m_blk, split, g;
         decode_tile(t, n_blk, m_blk, split, g);
         const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
+        // ATMA fprop: base output position of the tile -> (w, h, n) of its tap-(0,0) input pixel
+        int pn = 0, pw = 0, ph = 0;
+        if (ATMA && !WGRAD) {
+          const long long m0 = (long long)m_blk * BMT;
+          pn = (int)(m0 / ohw);
+          const int r = (int)(m0 - (long long)pn * ohw);
+          const int oh = r / p.OW;
+          pw = (r - oh * p.OW) * p.stride - p.pad_x;
+          ph = oh * p.stride - p.pad_y;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(empty_bar(stage), phase ^ 1u);
+          timed_wait(empty_bar(stage), phase ^ 1u, pw0);
           const uint32_t sa = smem_base + stage * a_stride;
           const uint32_t sb = sa + C::kABytes;
-          if (bres) {
-            mbar_arrive(full_bar(stage));   // keeps the arrival count uniform; the operand is already resident
-          } else if (!WGRAD) {
-            // B = W[g] : K-major box {64 (k), bn (n)}
-            mbar_expect_tx(full_bar(stage), (uint32_t)p.bn * BK * 2);
-            tma_load_3d(sb, &tmDense, full_bar(stage), kb * BK, n_blk * p.bn, g);
-          } else {
-            // A = dy[:, g*Ng + m] : MN-major, two boxes {64 (m), 64 (k)}
-            mbar_expect_tx(full_bar(stage), C::kABytes);
+          if (issue()) {
+            if (p.dbg & 2) {
+              mbar_arrive(full_bar(stage));
+            } else if (!WGRAD) {
+              const int pk = phys_kb(kb);
+              uint32_t tx = bres ? 0u : (uint32_t)p.bn * BK * 2;
+              if (ATMA) tx += (uint32_t)C::kABytes;
+              if (tx) mbar_expect_tx(full_bar(stage), tx); else mbar_arrive(full_bar(stage));
+              if (ATMA) {
+                // A = patches: BMT output positions x 64 channels through tap (kh, kw)
+                const int tap = pk / cpk, chunk = pk - tap * cpk;
+                const int kh = tap / p.KW, kw = tap - kh * p.KW;
+                tma_load_im2col_4d(sa, &tmPatch, full_bar(stage), g * p.Cg + chunk * 64, pw, ph, pn, kw, kh);
+              }
+              // B = W[g] : K-major box {64 (k), bn (n)}
+              if (!bres) tma_load_3d(sb, &tmDense, full_bar(stage), pk * BK, n_blk * p.bn, g);
+            } else {
+              // A = dy[:, g*Ng + m] : MN-major, two boxes {64 (m), 64 (k)}
+              uint32_t tx = (uint32_t)C::kABytes;
+              int natoms_ld = 0;
+              if (ATMA) {
+                natoms_ld = min((p.bn + 63) >> 6, (p.Kg - n_blk * p.bn + 63) >> 6);
+                tx += (uint32_t)natoms_ld * (64 * BK * 2);
+              }
+              mbar_expect_tx(full_bar(stage), tx);
 #pragma unroll
-            for (int h = 0; h < BM / 64; ++h)
-              tma_load_3d(sa + h * (64 * BK * 2), &tmDense, full_bar(stage), m_blk * BM + h * 64, kb * BK, g);
+              for (int h = 0; h < BM / 64; ++h)
+                tma_load_3d(sa + h * (64 * BK * 2), &tmDense, full_bar(stage), m_blk * BM + h * 64, kb * BK, g);
+              if (ATMA) {
+                // B = patches, MN-major: per 64-column atom (one tap, 64 channels) the 64 pixels of this k-block
+                const long long pix0 = (long long)kb * BK;
+                const int n = (int)(pix0 / ohw);
+                const int r = (int)(pix0 - (long long)n * ohw);
+                const int oh = r / p.OW;
+                const int w0 = (r - oh * p.OW) * p.stride - p.pad_x, h0 = oh * p.stride - p.pad_y;
+                for (int a = 0; a < natoms_ld; ++a) {
+                  const int n0 = n_blk * p.bn + a * 64;
+                  const int tap = n0 / p.Cg, c0 = n0 - tap * p.Cg;
+                  const int kh = tap / p.KW, kw = tap - kh * p.KW;
+                  tma_load_im2col_4d(sb + a * (64 * BK * 2), &tmPatch, full_bar(stage), g * p.Cg + c0, w0, h0, n, kw, kh);
+                }
+              }
+            }
           }
-          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+          if (UNI) __syncwarp();
+          if (++stage == nst) { stage = 0; phase ^= 1u; }
         }
       }
+      prof_store(0, pw0);
+      prof_store(1, prof_on ? clock64() - prof_t0 : 0);
     }
     __syncwarp();
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
-    if (lane == 0) {
+    if (UNI || lane == 0) {
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((WGRAD ? 1u : 0u) << 15) |
                              ((WGRAD ? 1u : 0u) << 16) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
       constexpr uint32_t kLboMN = 64 * BK * 2;
       constexpr uint32_t kSbo = 1024;
       constexpr uint32_t kStep = WGRAD ? (UMMA_K * 128) : (UMMA_K * 2);
+      // descriptor = constant high word | (address >> 4): stepping along K only touches the low word
+      const uint64_t desc_hi = make_desc(0, WGRAD ? kLboMN : 0u, kSbo);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      if (bres) mbar_wait(bres_bar, 0);
+      if (bres) wait_bar(bres_bar, 0);
       for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         int n_blk, m_blk, split, g;
         decode_tile(t, n_blk, m_blk, split, g);
         const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
-        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        timed_wait(tempty_bar(acc), acc_phase ^ 1u, pw1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BNMAX);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * MH * BNMAX);
         for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(full_bar(stage), phase);
-          fence_proxy_async();   // cp.async (generic proxy) writes -> tensor-core (async proxy) reads
+          timed_wait(full_bar(stage), phase, pw0);
+          if (!ATMA) fence_proxy_async();   // cp.async (generic proxy) writes -> tensor-core (async proxy) reads
           tc_fence_after();
           const uint32_t sa = smem_base + stage * a_stride;
-          const uint32_t sb = bres ? bres_base + kb * bres_kb_bytes : sa + C::kABytes;
+          const uint32_t sb = bres ? bres_base + phys_kb(kb) * bres_kb_bytes : sa + C::kABytes;
+          if (issue()) {
+            const uint64_t a0 = desc_hi | (uint64_t)((sa >> 4) & 0x3FFF), b0 = desc_hi | (uint64_t)((sb >> 4) & 0x3FFF);
+            if (!(p.dbg & 4)) {
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t ad = make_desc(sa + k * kStep, WGRAD ? kLboMN : 0u, kSbo);
-            const uint64_t bd = make_desc(sb + k * kStep, WGRAD ? kLboMN : 0u, kSbo);
-            umma_bf16(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+              for (int k = 0; k < BK / UMMA_K; ++k) {
+#pragma unroll
+                for (int h = 0; h < MH; ++h)
+                  umma_bf16(d_tmem + (uint32_t)(h * BNMAX), a0 + (uint64_t)((h * C::kAHalfBytes + k * kStep) >> 4),
+                            b0 + (uint64_t)((k * kStep) >> 4), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+              }
+            }
+            umma_commit(empty_bar(stage));
+            if (kb == kb1 - 1) umma_commit(tfull_bar(acc));
           }
-          umma_commit(empty_bar(stage));
-          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+          if (UNI) __syncwarp();
+          if (++stage == nst) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(tfull_bar(acc));
         if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
       }
+      prof_store(2, pw0);
+      prof_store(3, pw1);
+      prof_store(4, prof_on ? clock64() - prof_t0 : 0);
     }
     __syncwarp();
+  } else if (ATMA && warp >= kGatherWarp0) {
+    // im2col TMA fetches the patches: nothing to gather
   } else if (warp >= kGatherWarp0) {
     // =========================== gather producers ===========================
     // Lane mapping: the lanes of one cp.async instruction cover whole 128-byte rows of the
@@ -278,33 +402,43 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
       decode_tile(t, n_blk, m_blk, split, g);
       const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
       const bf16* gsrc = p.src + (long long)g * p.Cg;
+      const long long tset = prof_on ? clock64() : 0;
       if (!WGRAD) {
-        // A tile: 128 output pixels x 64 reduction elements; warp wl owns rows [32*wl, 32*wl+32)
-        constexpr int ITERS = 32 / RPI;       // 8 or 16
+        // A tile: MH halves of 128 output pixels x 64 reduction elements; warp wl owns rows
+        // [32*wl, 32*wl+32) of every half
+        constexpr int ITERS1 = 32 / RPI;      // 8 or 16
+        constexpr int ITERS = ITERS1 * MH;
         long long roff[ITERS];
         uint32_t rmask[ITERS];
 #pragma unroll
         for (int i = 0; i < ITERS; ++i) {
-          const long long row = (long long)m_blk * BM + wl * 32 + i * RPI + rsub;
+          const int rl = (i / ITERS1) * BM + wl * 32 + (i % ITERS1) * RPI + rsub;
+          const long long row = (long long)m_blk * BMT + rl;
           decode_pixel(row, row < rows, roff[i], rmask[i]);
         }
+        if (prof_on) pw1 += clock64() - tset;
         for (int kb = kb0; kb < kb1; ++kb) {
-          const int gi = kb * GPR + q;
+          const int gi = phys_kb(kb) * GPR + q;
           const bool gok = gi < ngran;
           const GatherEntry e = table[gok ? gi : 0];
           const uint32_t sel = gok ? ((1u << e.kh) | (1u << (16 + e.kw))) : 0xFFFFFFFFu;
-          mbar_wait(empty_bar(stage), phase ^ 1u);
+          timed_wait(empty_bar(stage), phase ^ 1u, pw0);
           const uint32_t abase = smem_base + stage * a_stride;
 #pragma unroll
           for (int i = 0; i < ITERS; ++i) {
-            const int rl = wl * 32 + i * RPI + rsub;
+            const int rl = (i / ITERS1) * BM + wl * 32 + (i % ITERS1) * RPI + rsub;   // half*128 + row: 128 B per row
             const bool ok = gok && ((rmask[i] & sel) == sel);
             const uint32_t dst = abase + rl * 128 + ((qoff16 ^ (uint32_t)(rl & 7)) << 4) + qsub;
             const void* sp = ok ? (const void*)(gsrc + roff[i] + e.off) : (const void*)p.src;
-            if (GRAN == 8) cp_async_16(dst, sp, ok); else cp_async_8(dst, sp, ok);
+            if (p.dbg & 1) continue;
+            if (GRAN == 8) {
+              if (p.l1_alloc) cp_async_16_ca(dst, sp, ok); else cp_async_16(dst, sp, ok);
+            } else {
+              cp_async_8(dst, sp, ok);
+            }
           }
           cp_async_arrive_noinc(full_bar(stage));
-          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+          if (++stage == nst) { stage = 0; phase ^= 1u; }
         }
       } else {
         // B tile: 64 pixels (reduction rows) x bn reduction-columns, MN-major atoms of [64 rows][128 B];
@@ -348,7 +482,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
             poh[i] -= c * p.OH;
             pn[i] += adv_n + c;
           }
-          mbar_wait(empty_bar(stage), phase ^ 1u);
+          timed_wait(empty_bar(stage), phase ^ 1u, pw0);
           const uint32_t sb = smem_base + stage * C::kStageBytes + C::kABytes;
 #pragma unroll
           for (int a = 0; a < MAXATOMS; ++a) {
@@ -364,9 +498,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
             }
           }
           cp_async_arrive_noinc(full_bar(stage));
-          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+          if (++stage == nst) { stage = 0; phase ^= 1u; }
         }
       }
+    }
+    if (wl == 0) {
+      prof_store(5, pw0);
+      prof_store(6, pw1);
+      prof_store(7, prof_on ? clock64() - prof_t0 : 0);
     }
   } else {
     // =========================== epilogue ===========================
@@ -376,17 +515,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
     for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       int n_blk, m_blk, split, g;
       decode_tile(t, n_blk, m_blk, split, g);
-      mbar_wait(tfull_bar(acc), acc_phase);
+      timed_wait(tfull_bar(acc), acc_phase, pw0);
+      const long long tbody = prof_on ? clock64() : 0;
       tc_fence_after();
-      const long long row = (long long)m_blk * BM + quad * 32 + lane;
-      const bool row_ok = row < gm;
       const float* bias = (!WGRAD && p.bias != nullptr) ? p.bias + (long long)g * p.Ng : nullptr;
 #pragma unroll 1
-      for (int c0 = 0; c0 < p.bn; c0 += 32) {
+      for (int hc = 0; hc < MH * BNMAX; hc += 32) {
+        const int h = hc / BNMAX, c0 = hc - h * BNMAX;
+        if (c0 >= p.bn) continue;
+        const long long row = (long long)m_blk * BMT + h * BM + quad * 32 + lane;
+        const bool row_ok = row < gm;
         const int n0 = n_blk * p.bn + c0;
-        if (n0 >= gn) break;
+        if (n0 >= gn) continue;
         uint32_t v[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BNMAX + c0);
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * MH * BNMAX + hc);
         tmem_ld32(taddr, v);
         tmem_ld_wait();
         if (!row_ok) continue;
@@ -445,7 +587,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const Params p) {
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (prof_on) pw1 += clock64() - tbody;
       if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+    if (quad == 2) {   // warp 2
+      prof_store(8, pw0);
+      prof_store(9, pw1);
+      prof_store(10, prof_on ? clock64() - prof_t0 : 0);
     }
   }
 
@@ -514,23 +662,99 @@ static int encode3d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1,
   return 0;
 }
 
-template <int BNMAX, bool WGRAD, int GRAN>
-static int launch_g(const CUtensorMap& tm, const Params& p, int grid, cudaStream_t st) {
-  using C = Cfg<BNMAX>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BNMAX, WGRAD, GRAN>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
-    if (e != cudaSuccess) return (int)e;
-    attr_set = true;
+// tuning knobs (cxn_conv_tune): 0 = automatic
+static int g_tune_mh = 0;          // 1 / 2: force the number of 128-row halves per forward tile
+static int g_tune_stages = 0;      // force the ring depth
+static int g_tune_l1 = -1;         // 0 / 1: gather through L1 (.ca)
+static int g_tune_tap_inner = -1;  // 0 / 1: tap-inner k-block order
+static int g_tune_bnmax = 0;       // 128 / 256: force the forward tile-width class
+static int g_tune_dbg = 0;         // timing experiments (Params::dbg)
+static int g_tune_atma = -1;       // 0 / 1: fetch the patches with im2col-mode TMA
+static long long* g_prof = nullptr;
+
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeIm2colFn get_encode_im2col() {
+  static EncodeIm2colFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* q = nullptr;
+    cudaDriverEntryPointQueryResult r;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &q, cudaEnableDefault, &r) == cudaSuccess &&
+        r == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeIm2colFn>(q);
+  });
+  return fn;
+}
+
+// Can the patch operand of this problem come through an im2col tensor map?
+static bool atma_ok(const Params& p) {
+  if (p.gran != 8 || p.Cg % 64 || p.KH * p.KW < 1) return false;
+  if (p.pad_x > 127 || p.pad_y > 127 || p.KW - 1 - p.pad_x > 127 || p.KH - 1 - p.pad_y > 127) return false;
+  if (p.stride < 1 || p.stride > 8) return false;
+  // the map enumerates floor((W + 2 pad - KW) / stride) + 1 positions per row: must be the caller's grid
+  if ((p.W + 2 * p.pad_x - p.KW) / p.stride + 1 != p.OW || (p.H + 2 * p.pad_y - p.KH) / p.stride + 1 != p.OH) return false;
+  if (p.W + 2 * p.pad_x < p.KW || p.H + 2 * p.pad_y < p.KH) return false;
+  if ((reinterpret_cast<uintptr_t>(p.src) & 15) || (p.Cs % 8)) return false;
+  return get_encode_im2col() != nullptr;
+}
+
+// NHWC activation tensor as an im2col tensor map: `pixels` output positions x 64 channels per load
+static int encode_im2col(CUtensorMap* out, const Params& p, int pixels) {
+  EncodeIm2colFn enc = get_encode_im2col();
+  if (!enc) return -2;
+  cuuint64_t gdim[4] = {(cuuint64_t)p.Cs, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
+  cuuint64_t gstr[3] = {(cuuint64_t)p.Cs * 2, (cuuint64_t)p.W * p.Cs * 2, (cuuint64_t)p.H * p.W * p.Cs * 2};
+  // bounding box of the tap-(0,0) pixel: [-pad, extent + pad - (K-1))
+  int lower[2] = {-p.pad_x, -p.pad_y};
+  int upper[2] = {p.pad_x - (p.KW - 1), p.pad_y - (p.KH - 1)};
+  cuuint32_t estr[4] = {1, (cuuint32_t)p.stride, (cuuint32_t)p.stride, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<bf16*>(p.src), gdim, gstr, lower, upper, 64,
+                   (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr, "[cxxnet_b200] cuTensorMapEncodeIm2col failed: %d\n", (int)r);
+    return -5;
   }
-  conv_igemm_kernel<BNMAX, WGRAD, GRAN><<<grid, kThreads, C::kSmemBytes, st>>>(tm, p);
+  return 0;
+}
+
+template <int BNMAX, bool WGRAD, int GRAN, int MH, bool ATMA>
+static int launch_g(const CUtensorMap& tm, const CUtensorMap& tmp, const Params& p, int grid, cudaStream_t st) {
+  using C = Cfg<BNMAX, MH>;
+  if (p.stages < 2 || p.stages > C::kMaxStages) return -20;
+  const int smem = C::smem_bytes(p.stages);
+  static int max_set = 0, carve_set = -1;
+  if (smem > max_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BNMAX, WGRAD, GRAN, MH, ATMA>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    max_set = smem;
+  }
+  // leave what the ring does not need to L1: the gathered operand re-reads pixels through it
+  int carve = (int)(((long long)smem + 1024) * 100 / (228 * 1024)) + 1;
+  if (carve > 100) carve = 100;
+  if (carve != carve_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BNMAX, WGRAD, GRAN, MH, ATMA>,
+                                         cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+    if (e != cudaSuccess) return (int)e;
+    carve_set = carve;
+  }
+  conv_igemm_kernel<BNMAX, WGRAD, GRAN, MH, ATMA><<<grid, kThreads, smem, st>>>(tm, tmp, p);
   CXN_CHECK_LAUNCH();
   return 0;
 }
-template <int BNMAX, bool WGRAD>
-static int launch(const CUtensorMap& tm, const Params& p, int grid, cudaStream_t st) {
-  return p.gran == 8 ? launch_g<BNMAX, WGRAD, 8>(tm, p, grid, st) : launch_g<BNMAX, WGRAD, 4>(tm, p, grid, st);
+// atma: the patch operand comes through `tmp` (im2col map), otherwise through the gather warps
+template <int BNMAX, bool WGRAD, int MH>
+static int launch(const CUtensorMap& tm, const CUtensorMap& tmp, bool atma, const Params& p, int grid, cudaStream_t st) {
+  if (p.gran == 8) {
+    if (atma) return launch_g<BNMAX, WGRAD, 8, MH, true>(tm, tmp, p, grid, st);
+    return launch_g<BNMAX, WGRAD, 8, MH, false>(tm, tmp, p, grid, st);
+  }
+  if (MH == 1 && !atma) return launch_g<BNMAX, WGRAD, 4, 1, false>(tm, tmp, p, grid, st);
+  return -21;
 }
 
 static int check_geom(const Params& p) {
@@ -574,21 +798,71 @@ CXN_API int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg,
   if (rc) return rc;
   const long long rows = (long long)N * OH * OW;
   if (rows <= 0) return 0;
-  const int bnmax = Ng > 128 ? 256 : 128;
+  // Tile shape: row-paired tiles (256 x <=128, two accumulators sharing the filter tile) when one
+  // n-tile covers the group's outputs and there is enough work to fill the machine with them -
+  // the filter tile is then read half as often; otherwise 128 x <=256.
+  int mh = 1, bnmax = Ng > 128 ? 256 : 128;
+  if (gran == 8 && Ng <= 128) {
+    const long long t2 = ceil_div_ll(rows, 2 * BM) * G;
+    if (t2 >= 2LL * num_sms()) mh = 2;
+  }
+  if (g_tune_mh && gran == 8) { mh = g_tune_mh; if (mh == 1) bnmax = Ng > 128 ? 256 : 128; }
+  if (g_tune_bnmax) bnmax = g_tune_bnmax;
   p.bn = pick_bn(Ng, bnmax);
+  // optional: tap-inner k-block order + L1-allocating gather (neighbouring taps re-read the same pixels).
+  // Measured neutral to slower on AlexNet shapes, so both stay off unless asked for.
+  p.tap_inner = (g_tune_tap_inner > 0 && gran == 8 && Cg % 64 == 0 && KH * KW > 1) ? 1 : 0;
+  p.l1_alloc = (g_tune_l1 > 0 && gran == 8) ? 1 : 0;
+  p.dbg = g_tune_dbg;
+  p.prof = g_prof;
+  const int stage_bytes = (mh * BM + bnmax) * BK * 2;
+  int max_st = (232448 - (1024 + 256 + kMaxGranules * 8)) / stage_bytes;
+  if (max_st > 6) max_st = 6;
+  p.stages = g_tune_stages ? g_tune_stages : max_st;
   CUtensorMap tm;
   rc = encode3d(&tm, w, (uint64_t)p.Kg, (uint64_t)Ng, (uint64_t)G, (uint64_t)ldw, (uint64_t)Ng * ldw, BK, p.bn);
   if (rc) return rc;
-  const long long tiles = ceil_div_ll(rows, BM) * ceil_div(Ng, p.bn) * G;
+  const long long tiles = ceil_div_ll(rows, mh * BM) * ceil_div(Ng, p.bn) * G;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   // small single-group filters stay resident in shared memory for the whole (persistent) kernel
   {
-    const int stages = bnmax >= 256 ? 4 : 6;
-    const long long ring_b = (long long)stages * bnmax * BK * 2;             // smem the B slots of the ring would use
     const long long panel = (long long)ceil_div(p.Kg, BK) * p.bn * BK * 2;
+    const long long ring_b = (long long)p.stages * bnmax * BK * 2;           // smem the B slots of the ring would use
     p.b_resident = (G == 1 && Ng <= p.bn && panel <= ring_b && tiles > 2LL * grid) ? 1 : 0;
   }
-  return bnmax == 256 ? launch<256, false>(tm, p, grid, st) : launch<128, false>(tm, p, grid, st);
+  bool atma = atma_ok(p);
+  if (g_tune_atma >= 0) atma = atma && g_tune_atma;
+  CUtensorMap tmp = tm;
+  if (atma) {
+    rc = encode_im2col(&tmp, p, mh * BM);
+    if (rc) return rc;
+  }
+  if (mh == 2) return bnmax == 256 ? launch<256, false, 2>(tm, tmp, atma, p, grid, st) : launch<128, false, 2>(tm, tmp, atma, p, grid, st);
+  return bnmax == 256 ? launch<256, false, 1>(tm, tmp, atma, p, grid, st) : launch<128, false, 1>(tm, tmp, atma, p, grid, st);
+}
+
+// Tuning / experiment knobs; value 0 (or -1 for the switches) restores the automatic choice.
+//   0: row halves per forward tile   1: ring stages   2: gather through L1   3: tap-inner order   4: tile-width class
+// Role profiling of the forward kernel: buf = device array of [148][16] int64 (null switches it off).
+// slots: 0 TMA wait-empty, 1 TMA total | 2 MMA wait-full, 3 MMA wait-tmem-empty, 4 MMA total |
+// 5 gather wait-empty, 6 gather tile setup, 7 gather total | 8 epilogue wait-tmem-full, 9 epilogue body, 10 total
+CXN_API int cxn_conv_set_prof(void* buf) {
+  g_prof = (long long*)buf;
+  return 0;
+}
+
+CXN_API int cxn_conv_tune(int key, int value) {
+  switch (key) {
+    case 0: g_tune_mh = value; break;
+    case 1: g_tune_stages = value; break;
+    case 2: g_tune_l1 = value; break;
+    case 3: g_tune_tap_inner = value; break;
+    case 4: g_tune_bnmax = value; break;
+    case 5: g_tune_dbg = value; break;
+    case 6: g_tune_atma = value; break;
+    default: return -1;
+  }
+  return 0;
 }
 
 // Weight gradient: dw[g][j][(kh,kw,c)] += sum_pixels dy[pixel][g*Ng + j] * patch(pixel)[(kh,kw,c)]  (fp32, atomics)
@@ -626,7 +900,17 @@ CXN_API int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg,
   if (rc) return rc;
   const long long tiles = base_tiles * p.splits;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
-  return launch<256, true>(tm, p, grid, st);
+  p.stages = g_tune_stages ? g_tune_stages : 4;
+  p.dbg = g_tune_dbg;
+  p.prof = g_prof;
+  bool atma = atma_ok(p);
+  if (g_tune_atma >= 0) atma = atma && g_tune_atma;
+  CUtensorMap tmp = tm;
+  if (atma) {
+    rc = encode_im2col(&tmp, p, BK);
+    if (rc) return rc;
+  }
+  return launch<256, true, 1>(tm, tmp, atma, p, grid, st);
 }
 
 CXN_API int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in,

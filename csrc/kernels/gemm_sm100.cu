@@ -112,21 +112,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   if (warp == 0) {
     // =========================== TMA producer ===========================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        long long r = t;
-        const int n_blk = (int)(r % tiles_n); r /= tiles_n;
-        const int m_blk = (int)(r % tiles_m); r /= tiles_m;
-        const int split = (int)(r % p.splits);
-        const int z = (int)(r / p.splits);
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(num_kb, kb0 + p.kb_per_split);
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(empty_bar(stage), phase ^ 1u);
-          const uint32_t sa = smem_base + stage * C::kStageBytes;
-          const uint32_t sb = sa + C::kABytes;
+    // the whole warp walks the schedule, one elected lane issues (see elect_one in tc_common.cuh)
+    int stage = 0;
+    uint32_t phase = 0;
+    for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      long long r = t;
+      const int n_blk = (int)(r % tiles_n); r /= tiles_n;
+      const int m_blk = (int)(r % tiles_m); r /= tiles_m;
+      const int split = (int)(r % p.splits);
+      const int z = (int)(r / p.splits);
+      const int kb0 = split * p.kb_per_split;
+      const int kb1 = min(num_kb, kb0 + p.kb_per_split);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait_warp(empty_bar(stage), phase ^ 1u);
+        const uint32_t sa = smem_base + stage * C::kStageBytes;
+        const uint32_t sb = sa + C::kABytes;
+        if (elect_one()) {
           mbar_expect_tx(full_bar(stage), C::kStageBytes);
           if (!A_MN) {
             tma_load_3d(sa, &tmA, full_bar(stage), kb * BK, m_blk * BM, z);
@@ -142,52 +143,55 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             for (int h = 0; h < BN / 64; ++h)
               tma_load_3d(sb + h * (64 * BK * 2), &tmB, full_bar(stage), n_blk * BN + h * 64, kb * BK, z);
           }
-          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
         }
+        __syncwarp();
+        if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
       }
     }
-    __syncwarp();
   } else if (warp == 1) {
     // =========================== MMA issuer =============================
-    if (lane == 0) {
-      // instruction descriptor: D=f32, A=B=bf16, majors, N, M
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
-                             ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-      constexpr uint32_t kLboMN = 64 * BK * 2;  // next 64-wide MN atom (one TMA box)
-      constexpr uint32_t kSbo = 1024;           // 8 rows x 128 bytes
-      constexpr uint32_t kAStep = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);
-      constexpr uint32_t kBStep = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
-      int stage = 0;
-      uint32_t phase = 0;
-      int acc = 0;
-      uint32_t acc_phase = 0;
-      for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        long long r = t / ((long long)tiles_n * tiles_m);
-        const int split = (int)(r % p.splits);
-        const int kb0 = split * p.kb_per_split;
-        const int kb1 = min(num_kb, kb0 + p.kb_per_split);
-        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+    // warp-uniform loop, one elected lane issues the MMAs and their commits
+    // instruction descriptor: D=f32, A=B=bf16, majors, N, M
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
+                           ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    constexpr uint32_t kLboMN = 64 * BK * 2;  // next 64-wide MN atom (one TMA box)
+    constexpr uint32_t kSbo = 1024;           // 8 rows x 128 bytes
+    constexpr uint32_t kAStep = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+    constexpr uint32_t kBStep = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+    // descriptor = constant high part | (address >> 4): stepping along K only adds to the low word
+    const uint64_t adesc_hi = make_desc(0, A_MN ? kLboMN : 0u, kSbo);
+    const uint64_t bdesc_hi = make_desc(0, B_MN ? kLboMN : 0u, kSbo);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      long long r = t / ((long long)tiles_n * tiles_m);
+      const int split = (int)(r % p.splits);
+      const int kb0 = split * p.kb_per_split;
+      const int kb1 = min(num_kb, kb0 + p.kb_per_split);
+      mbar_wait_warp(tempty_bar(acc), acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait_warp(full_bar(stage), phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(full_bar(stage), phase);
-          tc_fence_after();
-          const uint32_t sa = smem_base + stage * C::kStageBytes;
-          const uint32_t sb = sa + C::kABytes;
+        const uint32_t sa = smem_base + stage * C::kStageBytes;
+        const uint32_t sb = sa + C::kABytes;
+        if (elect_one()) {
+          const uint64_t a0 = adesc_hi | (uint64_t)((sa >> 4) & 0x3FFF), b0 = bdesc_hi | (uint64_t)((sb >> 4) & 0x3FFF);
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t ad = make_desc(sa + k * kAStep, A_MN ? kLboMN : 0u, kSbo);
-            const uint64_t bd = make_desc(sb + k * kBStep, B_MN ? kLboMN : 0u, kSbo);
-            umma_bf16(d_tmem, ad, bd, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          }
-          umma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
-          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma_bf16(d_tmem, a0 + (uint64_t)((k * kAStep) >> 4), b0 + (uint64_t)((k * kBStep) >> 4), idesc,
+                      (kb > kb0 || k > 0) ? 1u : 0u);
+          umma_commit(empty_bar(stage));                   // frees the smem slot when these MMAs retire
+          if (kb == kb1 - 1) umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
         }
-        umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
-        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+        __syncwarp();
+        if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
       }
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
     }
-    __syncwarp();
   } else {
     // =========================== epilogue ===============================
     const int quad = warp & 3;  // TMEM lane quadrant this warp may read
@@ -205,7 +209,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int z = (int)(r / p.splits);
       const int kb0 = split * p.kb_per_split;
       const int kb1 = min(num_kb, kb0 + p.kb_per_split);
-      mbar_wait(tfull_bar(acc), acc_phase);
+      mbar_wait_warp(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const int row = m_blk * BM + quad * 32 + lane;
       const bool row_ok = row < p.M;

@@ -41,12 +41,38 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
   }
 }
+// Warp-level wait: one lane polls (32 lanes polling are 32 requests to the barrier unit, which
+// also has to serve the producers' arrivals), the warp reconverges behind it.
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
+  if ((threadIdx.x & 31) == 0) mbar_wait(bar, parity);
+  __syncwarp();
+}
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0,
                                             int c1, int c2) {
   asm volatile(
       "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
       " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
       "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+// One lane of a fully converged warp (the same lane every time).  Code that issues TMA / tcgen05
+// instructions runs warp-uniform and guards the issue with this: a `lane == 0` branch makes ptxas
+// wrap every such instruction (its operands live in uniform registers) in a per-lane waterfall loop.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+// im2col-mode TMA: `pixels` consecutive output positions (walking w, then h, then n inside the
+// map's bounding box, with the map's traversal stride) x the map's channel box, read through the
+// filter tap (off_w, off_h); out-of-image positions are zero-filled = the convolution's padding.
+__device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c, int w,
+                                                   int h, int n, int off_w, int off_h) {
+  const unsigned short ow = (unsigned short)off_w, oh = (unsigned short)off_h;
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(ow), "h"(oh)
       : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -93,6 +119,11 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
 __device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, bool valid) {
   const int sz = valid ? 16 : 0;   // src-size 0 => the 16 destination bytes are zero-filled
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
+}
+// 16-byte copy that allocates in L1 (.ca): used when neighbouring filter taps re-read the same pixels
+__device__ __forceinline__ void cp_async_16_ca(uint32_t dst, const void* src, bool valid) {
+  const uint32_t sz = valid ? 16u : 0u;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
 }
 __device__ __forceinline__ void cp_async_8(uint32_t dst, const void* src, bool valid) {
   const int sz = valid ? 8 : 0;

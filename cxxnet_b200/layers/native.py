@@ -124,7 +124,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         g = p.num_group
         icg = p.num_input_channel // g
         small = p.kernel_height <= 16 and p.kernel_width <= 16
-        if icg % 8 == 0 and small and (p.kernel_height * p.kernel_width * icg) // 8 <= 2048:
+        if icg % 8 == 0 and small and (p.kernel_height * p.kernel_width * icg) // 8 <= 1024:
             self.igemm_fwd = True
         elif (g == 1 and p.num_input_channel <= 4 and input_is_node0 and sole_consumer and small):
             self.igemm_fwd = True
@@ -132,7 +132,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         ocg = p.num_channel // g
         pad_ok = p.kernel_height - 1 - p.pad_y >= 0 and p.kernel_width - 1 - p.pad_x >= 0
         self.igemm_dgrad = (self.igemm_fwd and p.stride == 1 and ocg % 8 == 0 and pad_ok
-                            and (p.kernel_height * p.kernel_width * ocg) // 8 <= 2048)
+                            and (p.kernel_height * p.kernel_width * ocg) // 8 <= 1024)
         return self.cin_pad
 
     def _icg(self):

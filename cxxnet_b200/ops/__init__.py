@@ -70,6 +70,8 @@ def lib():
     _sig(L.cxn_conv_fprop, [P, I, I, I, I, I, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, P, I, P])
     _sig(L.cxn_conv_wgrad, [P, I, I, I, I, I, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, I, P])
     _sig(L.cxn_conv_flip_weights, [P, P, I, I, I, I, I, I, I, P])
+    _sig(L.cxn_conv_tune, [I, I])
+    _sig(L.cxn_conv_set_prof, [P])
     _sig(L.cxn_pool_fwd, [P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(L.cxn_pool_bwd, [P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(L.cxn_lrn_fwd, [P, P, LL, I, I, F, F, F, P])
