@@ -18,7 +18,7 @@ def timeit(fn, iters=20):
         fn()
     ts = []
     for _ in range(iters):
-        flush.zero_()                       # evict L2 between timed launches
+        flush.max()                         # evict L2 with clean lines (a write would leave dirty lines to drain)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); fn(); e1.record()
         torch.cuda.synchronize()

@@ -65,10 +65,8 @@ struct Params {
   // fprop: whole filter panel resident in shared memory (single group, single n-tile, small K*N)
   int b_resident;
   int stages;      // depth of the shared-memory ring actually used (<= Cfg::kMaxStages)
-  int tap_inner;   // fprop, Cg % 64 == 0: visit the k-blocks channel-chunk outer / filter tap inner
-  int l1_alloc;    // gather with cp.async.ca (neighbouring taps then hit in L1) instead of .cg
   long long* prof; // [grid][16] cycle counters of the warp roles (builds with -DCXN_IGEMM_PROF only)
-  int dbg;         // timing experiments only (results are garbage): 1 skip the gather, 2 skip the TMA loads, 4 skip the MMAs
+  int dbg;         // timing experiments only (results are garbage): 2 skip the TMA loads, 4 skip the MMAs
 };
 
 #ifdef CXN_IGEMM_PROF
@@ -184,15 +182,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
-  // k-block visiting order.  Tap-inner (fprop, Cg % 64 == 0): consecutive k-blocks read the same 64
-  // channels through neighbouring filter taps, i.e. the same pixels shifted by one - those re-reads
-  // then hit in L1 instead of going back to L2.  Both operands just visit their k-blocks permuted.
-  const int taps = p.KH * p.KW, cpk = p.Cg >> 6;
-  auto phys_kb = [&](int kb) -> int {
-    if (WGRAD || !p.tap_inner) return kb;
-    const int chunk = kb / taps, tap = kb - chunk * taps;
-    return tap * cpk + chunk;
-  };
+  const int cpk = p.Cg >> 6;   // 64-channel chunks per filter tap (ATMA)
 
   auto wait_bar = [&](uint32_t bar, uint32_t parity) { mbar_wait(bar, parity); };
   auto issue = [&]() -> bool { return UNI ? elect_one() : true; };   // UNI: all lanes run the loop, one issues
@@ -256,7 +246,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
             if (p.dbg & 2) {
               mbar_arrive(full_bar(stage));
             } else if (!WGRAD) {
-              const int pk = phys_kb(kb);
+              const int pk = kb;
               uint32_t tx = bres ? 0u : (uint32_t)p.bn * BK * 2;
               if (ATMA) tx += (uint32_t)C::kABytes;
               if (tx) mbar_expect_tx(full_bar(stage), tx); else mbar_arrive(full_bar(stage));
@@ -331,7 +321,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
           if (!ATMA) fence_proxy_async();   // cp.async (generic proxy) writes -> tensor-core (async proxy) reads
           tc_fence_after();
           const uint32_t sa = smem_base + stage * a_stride;
-          const uint32_t sb = bres ? bres_base + phys_kb(kb) * bres_kb_bytes : sa + C::kABytes;
+          const uint32_t sb = bres ? bres_base + kb * bres_kb_bytes : sa + C::kABytes;
           if (issue()) {
             const uint64_t a0 = desc_hi | (uint64_t)((sa >> 4) & 0x3FFF), b0 = desc_hi | (uint64_t)((sb >> 4) & 0x3FFF);
             if (!(p.dbg & 4)) {
@@ -418,7 +408,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
         }
         if (prof_on) pw1 += clock64() - tset;
         for (int kb = kb0; kb < kb1; ++kb) {
-          const int gi = phys_kb(kb) * GPR + q;
+          const int gi = kb * GPR + q;
           const bool gok = gi < ngran;
           const GatherEntry e = table[gok ? gi : 0];
           const uint32_t sel = gok ? ((1u << e.kh) | (1u << (16 + e.kw))) : 0xFFFFFFFFu;
@@ -430,12 +420,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
             const bool ok = gok && ((rmask[i] & sel) == sel);
             const uint32_t dst = abase + rl * 128 + ((qoff16 ^ (uint32_t)(rl & 7)) << 4) + qsub;
             const void* sp = ok ? (const void*)(gsrc + roff[i] + e.off) : (const void*)p.src;
-            if (p.dbg & 1) continue;
-            if (GRAN == 8) {
-              if (p.l1_alloc) cp_async_16_ca(dst, sp, ok); else cp_async_16(dst, sp, ok);
-            } else {
-              cp_async_8(dst, sp, ok);
-            }
+            if (GRAN == 8) cp_async_16(dst, sp, ok); else cp_async_8(dst, sp, ok);
           }
           cp_async_arrive_noinc(full_bar(stage));
           if (++stage == nst) { stage = 0; phase ^= 1u; }
@@ -665,8 +650,6 @@ static int encode3d(CUtensorMap* out, const void* ptr, uint64_t d0, uint64_t d1,
 // tuning knobs (cxn_conv_tune): 0 = automatic
 static int g_tune_mh = 0;          // 1 / 2: force the number of 128-row halves per forward tile
 static int g_tune_stages = 0;      // force the ring depth
-static int g_tune_l1 = -1;         // 0 / 1: gather through L1 (.ca)
-static int g_tune_tap_inner = -1;  // 0 / 1: tap-inner k-block order
 static int g_tune_bnmax = 0;       // 128 / 256: force the forward tile-width class
 static int g_tune_dbg = 0;         // timing experiments (Params::dbg)
 static int g_tune_atma = -1;       // 0 / 1: fetch the patches with im2col-mode TMA
@@ -726,21 +709,12 @@ static int launch_g(const CUtensorMap& tm, const CUtensorMap& tmp, const Params&
   using C = Cfg<BNMAX, MH>;
   if (p.stages < 2 || p.stages > C::kMaxStages) return -20;
   const int smem = C::smem_bytes(p.stages);
-  static int max_set = 0, carve_set = -1;
+  static int max_set = 0;
   if (smem > max_set) {
     cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BNMAX, WGRAD, GRAN, MH, ATMA>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return (int)e;
     max_set = smem;
-  }
-  // leave what the ring does not need to L1: the gathered operand re-reads pixels through it
-  int carve = (int)(((long long)smem + 1024) * 100 / (228 * 1024)) + 1;
-  if (carve > 100) carve = 100;
-  if (carve != carve_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BNMAX, WGRAD, GRAN, MH, ATMA>,
-                                         cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-    if (e != cudaSuccess) return (int)e;
-    carve_set = carve;
   }
   conv_igemm_kernel<BNMAX, WGRAD, GRAN, MH, ATMA><<<grid, kThreads, smem, st>>>(tm, tmp, p);
   CXN_CHECK_LAUNCH();
@@ -809,10 +783,6 @@ CXN_API int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg,
   if (g_tune_mh && gran == 8) { mh = g_tune_mh; if (mh == 1) bnmax = Ng > 128 ? 256 : 128; }
   if (g_tune_bnmax) bnmax = g_tune_bnmax;
   p.bn = pick_bn(Ng, bnmax);
-  // optional: tap-inner k-block order + L1-allocating gather (neighbouring taps re-read the same pixels).
-  // Measured neutral to slower on AlexNet shapes, so both stay off unless asked for.
-  p.tap_inner = (g_tune_tap_inner > 0 && gran == 8 && Cg % 64 == 0 && KH * KW > 1) ? 1 : 0;
-  p.l1_alloc = (g_tune_l1 > 0 && gran == 8) ? 1 : 0;
   p.dbg = g_tune_dbg;
   p.prof = g_prof;
   const int stage_bytes = (mh * BM + bnmax) * BK * 2;
@@ -855,8 +825,8 @@ CXN_API int cxn_conv_tune(int key, int value) {
   switch (key) {
     case 0: g_tune_mh = value; break;
     case 1: g_tune_stages = value; break;
-    case 2: g_tune_l1 = value; break;
-    case 3: g_tune_tap_inner = value; break;
+    case 2: break;   // (was: gather through L1; removed - no gain and it cost the gather loop a branch)
+    case 3: break;   // (was: tap-inner k-block order; removed - measured slower)
     case 4: g_tune_bnmax = value; break;
     case 5: g_tune_dbg = value; break;
     case 6: g_tune_atma = value; break;

@@ -68,6 +68,189 @@ __global__ void pool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y
   }
 }
 
+// ---- fast paths: 8 channels per thread, one image per blockIdx.y, windows fully unrolled so
+// that every load of a thread is in flight before the first use (the generic kernels below walk
+// the window with dependent loads and 64-bit index divisions).
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 t = __bfloat1622float2(h[j]);
+    f[2 * j] = t.x; f[2 * j + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 o;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+  return o;
+}
+
+// forward, window <= KMAX x KMAX
+template <int KMAX>
+__global__ void __launch_bounds__(256) pool_fwd_img_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, PoolGeom g) {
+  const int cv = g.C >> 3;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= g.OH * g.OW * cv) return;
+  const int pix = idx / cv, c = (idx - pix * cv) << 3;
+  const int oh = pix / g.OW, ow = pix - oh * g.OW;
+  const int n = blockIdx.y;
+  const int y0 = oh * g.stride, x0 = ow * g.stride;
+  const bf16* base = x + (((long long)n * g.H + y0) * g.W + x0) * g.C + c;
+  uint4 v[KMAX][KMAX];
+  bool ok[KMAX][KMAX];
+#pragma unroll
+  for (int a = 0; a < KMAX; ++a)
+#pragma unroll
+    for (int b = 0; b < KMAX; ++b) {
+      ok[a][b] = a < g.K_y && b < g.K_x && y0 + a < g.H && x0 + b < g.W;
+      v[a][b] = ok[a][b] ? *reinterpret_cast<const uint4*>(base + ((long long)a * g.W + b) * g.C) : make_uint4(0, 0, 0, 0);
+    }
+  bf16* dst = y + (((long long)n * g.OH + oh) * g.OW + ow) * g.C + c;
+  if (g.mode == 0) {
+    // max pooling in packed bf16 (exact): 4 instructions per window instead of 8 converts + 8 max
+    const __nv_bfloat162 ninf = __float2bfloat162_rn(-INFINITY);
+    __nv_bfloat162 m[4] = {ninf, ninf, ninf, ninf};
+#pragma unroll
+    for (int a = 0; a < KMAX; ++a)
+#pragma unroll
+      for (int b = 0; b < KMAX; ++b) {
+        if (!ok[a][b]) continue;
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[a][b]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) m[j] = __hmax2(m[j], h[j]);
+      }
+    if (g.relu) {
+      const __nv_bfloat162 z = __float2bfloat162_rn(0.0f);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) m[j] = __hmax2(m[j], z);
+    }
+    uint4 o;
+    __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ho[j] = m[j];
+    *reinterpret_cast<uint4*>(dst) = o;
+    return;
+  }
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
+#pragma unroll
+  for (int a = 0; a < KMAX; ++a)
+#pragma unroll
+    for (int b = 0; b < KMAX; ++b) {
+      if (!ok[a][b]) continue;
+      float f[8];
+      unpack8(v[a][b], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += g.relu ? fmaxf(f[j], 0.0f) : f[j];
+    }
+  const float scale = g.mode == 2 ? 1.0f / (g.K_y * g.K_x) : 1.0f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] *= scale;
+  *reinterpret_cast<uint4*>(dst) = pack8(acc);
+}
+
+// backward, at most 2 x 2 windows cover an input pixel (K <= 2 * stride).
+// A thread owns U vectors a block-width apart and issues their x loads (the DRAM stream) up
+// front: one 16-byte miss per thread in flight is ~12 KB per SM, a quarter of what HBM needs.
+template <int U>
+__global__ void __launch_bounds__(256) pool_bwd_img_kernel(const bf16* __restrict__ x, const bf16* __restrict__ y,
+                                                           const bf16* __restrict__ dy, bf16* __restrict__ dx, PoolGeom g) {
+  const int cv = g.C >> 3;
+  const int per_img = g.H * g.W * cv;
+  const int n = blockIdx.y;
+  const int idx0 = blockIdx.x * (blockDim.x * U) + threadIdx.x;
+  const long long img = (long long)n * g.H * g.W * g.C;
+  uint4 xr[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int idx = idx0 + u * blockDim.x;
+    xr[u] = idx < per_img ? *reinterpret_cast<const uint4*>(x + img + (long long)idx * 8) : make_uint4(0, 0, 0, 0);
+  }
+  const float scale = g.mode == 2 ? 1.0f / (g.K_y * g.K_x) : 1.0f;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const int idx = idx0 + u * blockDim.x;
+    if (idx >= per_img) break;
+    const int pix = idx / cv, c = (idx - pix * cv) << 3;
+    const int yy = pix / g.W, xx = pix - yy * g.W;
+    const int py0 = yy < g.K_y ? 0 : (yy - g.K_y + g.stride) / g.stride;
+    const int px0 = xx < g.K_x ? 0 : (xx - g.K_x + g.stride) / g.stride;
+    const int py1 = min(yy / g.stride + 1, g.OH);
+    const int px1 = min(xx / g.stride + 1, g.OW);
+    const long long pbase = (((long long)n * g.OH + py0) * g.OW + px0) * g.C + c;
+    uint4 pv[2][2], gv[2][2];
+    bool ok[2][2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        ok[a][b] = py0 + a < py1 && px0 + b < px1;
+        const long long o = pbase + ((long long)a * g.OW + b) * g.C;
+        pv[a][b] = ok[a][b] && g.mode == 0 ? *reinterpret_cast<const uint4*>(y + o) : make_uint4(0, 0, 0, 0);
+        gv[a][b] = ok[a][b] ? *reinterpret_cast<const uint4*>(dy + o) : make_uint4(0, 0, 0, 0);
+      }
+    if (g.mode == 0) {
+      // max pooling in packed bf16: mask = (x == pooled) as 1.0 / 0.0, acc += mask * dy.  At most
+      // four terms, almost always one, so bf16 accumulation costs nothing measurable.
+      const __nv_bfloat162 z = __float2bfloat162_rn(0.0f);
+      const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&xr[u]);
+      __nv_bfloat162 xm[4], am[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        xm[j] = g.relu ? __hmax2(hx[j], z) : hx[j];
+        am[j] = z;
+      }
+#pragma unroll
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          if (!ok[a][b]) continue;
+          const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&pv[a][b]);
+          const __nv_bfloat162* hg = reinterpret_cast<const __nv_bfloat162*>(&gv[a][b]);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) am[j] = __hfma2(__heq2(xm[j], hp[j]), hg[j], am[j]);
+        }
+      if (g.relu) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) am[j] = __hmul2(am[j], __hgt2(hx[j], z));
+      }
+      uint4 o;
+      __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ho[j] = am[j];
+      *reinterpret_cast<uint4*>(dx + img + (long long)idx * 8) = o;
+      continue;
+    }
+    float xv[8], acc[8];
+    unpack8(xr[u], xv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (g.relu) xv[j] = fmaxf(xv[j], 0.0f);
+      acc[j] = 0.0f;
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        if (!ok[a][b]) continue;
+        float p[8], gr[8];
+        unpack8(pv[a][b], p);
+        unpack8(gv[a][b], gr);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += (g.mode != 0 || xv[j] == p[j]) ? gr[j] : 0.0f;
+      }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      acc[j] *= scale;
+      if (g.relu) acc[j] = xv[j] > 0.0f ? acc[j] : 0.0f;
+    }
+    *reinterpret_cast<uint4*>(dx + img + (long long)idx * 8) = pack8(acc);
+  }
+}
+
 // dx[n][y][x][c] = sum over covering windows of  partial(x, pooled) * dy   (* 1/k^2 for avg)
 // With relu fused, x is compared after relu and the result is masked by x>0.
 template <int V>
@@ -205,21 +388,6 @@ __global__ void lrn_bwd_kernel(const bf16* __restrict__ x, const bf16* __restric
 // ------------------------------------------------------------------ LRN, register version
 // C % 8 == 0 and C <= 256: TPP = C/8 lanes own one pixel, 8 channels (one 16-byte load) each;
 // the +-2 channel halo (local_size <= 5) comes from the neighbouring lanes by shuffle.
-__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
-  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const float2 t = __bfloat1622float2(h[j]);
-    f[2 * j] = t.x; f[2 * j + 1] = t.y;
-  }
-}
-__device__ __forceinline__ uint4 pack8(const float* f) {
-  uint4 o;
-  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-  for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
-  return o;
-}
 // e[0..11] = {left lane's v[6], v[7], own v[0..7], right lane's v[0], v[1]} (zero outside the pixel)
 __device__ __forceinline__ void halo2(const float* v, float* e, int lane_in_pix, int tpp) {
   const float l6 = __shfl_up_sync(0xffffffffu, v[6], 1), l7 = __shfl_up_sync(0xffffffffu, v[7], 1);
@@ -323,7 +491,12 @@ CXN_API int cxn_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int
                          int OW, int mode, int relu, cudaStream_t st) {
   PoolGeom g{N, H, W, C, ky, kx, stride, OH, OW, mode, relu};
   if ((long long)N * OH * OW * C <= 0) return 0;
-  if (pool_vec(x, y, C))
+  const bool small = pool_vec(x, y, C) && N <= 65535 && (long long)OH * OW * (C / 8) < (1LL << 30);
+  if (small && ky <= 2 && kx <= 2)
+    pool_fwd_img_kernel<2><<<dim3((unsigned)ceil_div_ll((long long)OH * OW * (C / 8), 256), N), 256, 0, st>>>((const bf16*)x, (bf16*)y, g);
+  else if (small && ky <= 3 && kx <= 3)
+    pool_fwd_img_kernel<3><<<dim3((unsigned)ceil_div_ll((long long)OH * OW * (C / 8), 256), N), 256, 0, st>>>((const bf16*)x, (bf16*)y, g);
+  else if (pool_vec(x, y, C))
     pool_fwd_kernel<8><<<ew_grid((long long)N * OH * OW * (C / 8), 256, 16), 256, 0, st>>>((const bf16*)x, (bf16*)y, g);
   else
     pool_fwd_kernel<1><<<ew_grid((long long)N * OH * OW * C, 256, 16), 256, 0, st>>>((const bf16*)x, (bf16*)y, g);
@@ -335,7 +508,10 @@ CXN_API int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx,
   PoolGeom g{N, H, W, C, ky, kx, stride, OH, OW, mode, relu};
   if ((long long)N * H * W * C <= 0) return 0;
   const bool v = pool_vec(x, y, C) && pool_vec(dy, dx, C);
-  if (v)
+  if (v && N <= 65535 && ky <= 2 * stride && kx <= 2 * stride && (long long)H * W * (C / 8) < (1LL << 30))
+    pool_bwd_img_kernel<4><<<dim3((unsigned)ceil_div_ll((long long)H * W * (C / 8), 256 * 4), N), 256, 0, st>>>(
+        (const bf16*)x, (const bf16*)y, (const bf16*)dy, (bf16*)dx, g);
+  else if (v)
     pool_bwd_kernel<8><<<ew_grid((long long)N * H * W * (C / 8), 256, 16), 256, 0, st>>>(
         (const bf16*)x, (const bf16*)y, (const bf16*)dy, (bf16*)dx, g);
   else

@@ -120,11 +120,6 @@ __device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, bool 
   const int sz = valid ? 16 : 0;   // src-size 0 => the 16 destination bytes are zero-filled
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
 }
-// 16-byte copy that allocates in L1 (.ca): used when neighbouring filter taps re-read the same pixels
-__device__ __forceinline__ void cp_async_16_ca(uint32_t dst, const void* src, bool valid) {
-  const uint32_t sz = valid ? 16u : 0u;
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
-}
 __device__ __forceinline__ void cp_async_8(uint32_t dst, const void* src, bool valid) {
   const int sz = valid ? 8 : 0;
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");

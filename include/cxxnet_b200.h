@@ -47,8 +47,8 @@ int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg, int G, 
 int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in, int ld_out,
                           cudaStream_t stream);
 /* experiment / tuning knobs of the implicit-GEMM convolution (0, or -1 for switches, = automatic):
- * key 0 row halves per forward tile (1|2), 1 ring stages, 2 gather through L1 (0|1),
- * 3 tap-inner k-block order (0|1), 4 forward tile-width class (128|256), 5 timing-experiment bits,
+ * key 0 row halves per forward tile (1|2), 1 ring stages, 2 unused,
+ * 3 unused, 4 forward tile-width class (128|256), 5 timing-experiment bits,
  * 6 im2col-mode TMA for the patch operand (0|1).  No reference counterpart. */
 int cxn_conv_tune(int key, int value);
 /* per-role cycle counters of the forward implicit-GEMM kernel: buf = device int64 [148][16], NULL = off */
