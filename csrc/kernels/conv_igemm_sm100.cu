@@ -48,7 +48,7 @@ struct Params {
   const bf16* src;
   int N, H, W, Cs;
   int Cg;          // channels per group as laid out in K (4 in the padded-RGB mode)
-  int KH, KW, stride, pad_y, pad_x;
+  int KH, KW, stride_y, stride_x, pad_y, pad_x;
   int OH, OW;      // pixel grid enumerated by the GEMM rows
   int G;
   int Kg;          // KH*KW*Cg
@@ -62,6 +62,7 @@ struct Params {
   int relu;
   // wgrad
   int splits, kb_per_split;
+  int mask_period, mask_valid;   // wgrad: columns n with n % period >= valid are not accumulated (0 = off)
   // fprop: whole filter panel resident in shared memory (single group, single n-tile, small K*N)
   int b_resident;
   int stages;      // depth of the shared-memory ring actually used (<= Cfg::kMaxStages)
@@ -235,8 +236,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
           pn = (int)(m0 / ohw);
           const int r = (int)(m0 - (long long)pn * ohw);
           const int oh = r / p.OW;
-          pw = (r - oh * p.OW) * p.stride - p.pad_x;
-          ph = oh * p.stride - p.pad_y;
+          pw = (r - oh * p.OW) * p.stride_x - p.pad_x;
+          ph = oh * p.stride_y - p.pad_y;
         }
         for (int kb = kb0; kb < kb1; ++kb) {
           timed_wait(empty_bar(stage), phase ^ 1u, pw0);
@@ -276,7 +277,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
                 const int n = (int)(pix0 / ohw);
                 const int r = (int)(pix0 - (long long)n * ohw);
                 const int oh = r / p.OW;
-                const int w0 = (r - oh * p.OW) * p.stride - p.pad_x, h0 = oh * p.stride - p.pad_y;
+                const int w0 = (r - oh * p.OW) * p.stride_x - p.pad_x, h0 = oh * p.stride_y - p.pad_y;
                 for (int a = 0; a < natoms_ld; ++a) {
                   const int n0 = n_blk * p.bn + a * 64;
                   const int tap = n0 / p.Cg, c0 = n0 - tap * p.Cg;
@@ -373,7 +374,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
       return mh | (mw << 16);
     };
     auto pixel_state = [&](int n, int oh, int ow, bool ok, long long& off, uint32_t& mask) {
-      const int ih0 = oh * p.stride - p.pad_y, iw0 = ow * p.stride - p.pad_x;
+      const int ih0 = oh * p.stride_y - p.pad_y, iw0 = ow * p.stride_x - p.pad_x;
       mask = ok ? tap_mask(ih0, iw0) : 0u;
       off = (((long long)n * p.H + ih0) * p.W + iw0) * p.Cs;
     };
@@ -558,14 +559,16 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
           if (lim == 32 && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
             // 128-bit reductions: a quarter of the L2 atomic operations of the scalar form
 #pragma unroll
-            for (int q = 0; q < 8; ++q)
+            for (int q = 0; q < 8; ++q) {
+              if (p.mask_period && (n0 + 4 * q) % p.mask_period >= p.mask_valid) continue;   // structural zeros (4-aligned)
               asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + 4 * q), "f"(f[4 * q]),
                            "f"(f[4 * q + 1]), "f"(f[4 * q + 2]), "f"(f[4 * q + 3])
                            : "memory");
+            }
           } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
-              if (j < lim) atomicAdd(d + j, f[j]);
+              if (j < lim && !(p.mask_period && (n0 + j) % p.mask_period >= p.mask_valid)) atomicAdd(d + j, f[j]);
           }
         }
       }
@@ -676,9 +679,9 @@ static EncodeIm2colFn get_encode_im2col() {
 static bool atma_ok(const Params& p) {
   if (p.gran != 8 || p.Cg % 64 || p.KH * p.KW < 1) return false;
   if (p.pad_x > 127 || p.pad_y > 127 || p.KW - 1 - p.pad_x > 127 || p.KH - 1 - p.pad_y > 127) return false;
-  if (p.stride < 1 || p.stride > 8) return false;
+  if (p.stride_x < 1 || p.stride_x > 8 || p.stride_y < 1 || p.stride_y > 8) return false;
   // the map enumerates floor((W + 2 pad - KW) / stride) + 1 positions per row: must be the caller's grid
-  if ((p.W + 2 * p.pad_x - p.KW) / p.stride + 1 != p.OW || (p.H + 2 * p.pad_y - p.KH) / p.stride + 1 != p.OH) return false;
+  if ((p.W + 2 * p.pad_x - p.KW) / p.stride_x + 1 != p.OW || (p.H + 2 * p.pad_y - p.KH) / p.stride_y + 1 != p.OH) return false;
   if (p.W + 2 * p.pad_x < p.KW || p.H + 2 * p.pad_y < p.KH) return false;
   if ((reinterpret_cast<uintptr_t>(p.src) & 15) || (p.Cs % 8)) return false;
   return get_encode_im2col() != nullptr;
@@ -693,7 +696,7 @@ static int encode_im2col(CUtensorMap* out, const Params& p, int pixels) {
   // bounding box of the tap-(0,0) pixel: [-pad, extent + pad - (K-1))
   int lower[2] = {-p.pad_x, -p.pad_y};
   int upper[2] = {p.pad_x - (p.KW - 1), p.pad_y - (p.KH - 1)};
-  cuuint32_t estr[4] = {1, (cuuint32_t)p.stride, (cuuint32_t)p.stride, 1};
+  cuuint32_t estr[4] = {1, (cuuint32_t)p.stride_x, (cuuint32_t)p.stride_y, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<bf16*>(p.src), gdim, gstr, lower, upper, 64,
                    (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -765,7 +768,7 @@ CXN_API int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg,
   Params p;
   memset(&p, 0, sizeof(p));
   p.src = (const bf16*)src; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
-  p.stride = stride; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
+  p.stride_y = stride & 0xFFFF; p.stride_x = (stride >> 16) ? (stride >> 16) : p.stride_y; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
   p.gran = gran; p.Ng = Ng; p.D = y; p.ldd = ldy; p.strideD = Ng; p.bias = bias; p.relu = relu;
   p.splits = 1; p.kb_per_split = 0;
   int rc = check_geom(p);
@@ -836,13 +839,16 @@ CXN_API int cxn_conv_tune(int key, int value) {
 }
 
 // Weight gradient: dw[g][j][(kh,kw,c)] += sum_pixels dy[pixel][g*Ng + j] * patch(pixel)[(kh,kw,c)]  (fp32, atomics)
-CXN_API int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
-                           long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
-                           float* dw, long long lddw, int splits, cudaStream_t st) {
+CXN_API int cxn_conv_wgrad_masked(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
+                                  long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                                  float* dw, long long lddw, int splits, int mask_period, int mask_valid,
+                                  cudaStream_t st) {
   Params p;
   memset(&p, 0, sizeof(p));
+  if (mask_period && ((mask_period | mask_valid) & 3)) return -16;
+  p.mask_period = mask_period; p.mask_valid = mask_valid;
   p.src = (const bf16*)src; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
-  p.stride = stride; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
+  p.stride_y = stride & 0xFFFF; p.stride_x = (stride >> 16) ? (stride >> 16) : p.stride_y; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
   p.gran = gran; p.Ng = Ng; p.D = dw; p.ldd = lddw; p.strideD = (long long)Ng * lddw; p.bias = nullptr; p.relu = 0;
   int rc = check_geom(p);
   if (rc) return rc;
@@ -890,4 +896,11 @@ CXN_API int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int i
   flip_weights_kernel<<<ew_grid(total, 256), 256, 0, st>>>((const bf16*)w, (bf16*)wt, G, ocg, icg, KH, KW, ld_in, ld_out);
   CXN_CHECK_LAUNCH();
   return 0;
+}
+
+CXN_API int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
+                           long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                           float* dw, long long lddw, int splits, cudaStream_t st) {
+  return cxn_conv_wgrad_masked(src, N, H, W, Cs, Cg, G, gran, dy, lddy, Ng, KH, KW, stride, pad_y, pad_x, OH, OW, dw, lddw,
+                               splits, 0, 0, st);
 }

@@ -45,6 +45,33 @@ __global__ void nchw_to_nhwc4_kernel(const float* __restrict__ src, bf16* __rest
     *reinterpret_cast<uint2*>(dst + i * 4) = o;
   }
 }
+// C <= 4 with an even row pitch Wp >= W (pixel pitch 4): one thread converts a pixel pair and
+// stores it as 16 bytes; pixels at x >= W are written as zero.  This is the layout the first
+// convolution reads as [H][Wp/2] super-pixels of 8 channels (see ConvolutionLayer pair mode).
+__global__ void nchw_to_nhwc4_pitched_kernel(const float* __restrict__ src, bf16* __restrict__ dst, long long total,
+                                             int C, int H, int W, int Wp) {
+  const int wp2 = Wp >> 1;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / wp2;             // n * H + y
+    const int j = (int)(i - row * wp2);
+    const long long n = row / H;
+    const int y = (int)(row - n * H);
+    const float* s = src + (n * C * H + y) * (long long)W + 2 * j;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (c < C) {
+        if (2 * j < W) v[c] = s[(long long)c * H * W];
+        if (2 * j + 1 < W) v[4 + c] = s[(long long)c * H * W + 1];
+      }
+    uint4 o;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+    *reinterpret_cast<uint4*>(dst + i * 8) = o;
+  }
+}
 // src bf16 [N][HW][ldc] -> dst fp32 [N][C][HW]
 __global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ src, float* __restrict__ dst, int N, int C, int HW,
                                     int ldc) {
@@ -245,6 +272,14 @@ CXN_API int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C,
   }
   dim3 grid(ceil_div(HW, 32), ceil_div(C, 32), N), block(32, 8);
   nchw_to_nhwc_kernel<<<grid, block, 0, st>>>(src, (bf16*)dst, N, C, HW, ldc);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_nchw_f32_to_nhwc4_pitched(const float* src, void* dst, int N, int C, int H, int W, int Wp, cudaStream_t st) {
+  if (N <= 0 || C <= 0 || H <= 0 || W <= 0) return 0;
+  if (C > 4 || (Wp & 1) || Wp < W || (reinterpret_cast<uintptr_t>(dst) & 15)) return -1;
+  const long long total = (long long)N * H * (Wp / 2);
+  nchw_to_nhwc4_pitched_kernel<<<ew_grid(total, 256, 16), 256, 0, st>>>(src, (bf16*)dst, total, C, H, W, Wp);
   CXN_CHECK_LAUNCH();
   return 0;
 }

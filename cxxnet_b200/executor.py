@@ -223,13 +223,15 @@ class NeuralNet:
             if c.native and hasattr(c.layer, "b200_plan"):
                 x = c.nodes_in[0]
                 want = c.layer.b200_plan(self, x.index == 0, consumers.get(x.index, 0) == 1)
+                if isinstance(want, tuple):          # (channel pitch, row pitch in pixels)
+                    want, x.wpitch = want
                 if want:
                     pitch[x.index] = want
         # node buffers
         for n in self.nodes:
             b, ch, h, w = n.shape
             n.shape[0] = self.max_batch
-            rows = self.max_batch if n.is_mat else self.max_batch * h * w
+            rows = self.max_batch if n.is_mat else self.max_batch * h * (n.wpitch or w)
             cols = w if n.is_mat else ch
             ld = ops.round_up(cols, 8) if n.is_mat else pitch.get(n.index, cols)
             n.act = ops.DevMat(rows, cols, ld, device=self.device)
@@ -408,7 +410,8 @@ class NeuralNet:
         m = n.grad if grad else n.act
         if n.is_mat:
             return m.t[:b, :w].float().reshape(b, 1, 1, w)
-        return m.t[:b * h * w, :c].reshape(b, h, w, c).permute(0, 3, 1, 2).float().contiguous()
+        wp = n.wpitch or w
+        return m.t[:b * h * wp, :c].reshape(b, h, wp, c)[:, :, :w].permute(0, 3, 1, 2).float().contiguous()
 
     def _node_store(self, n: Node, t: torch.Tensor, grad: bool = False) -> None:
         b, c, h, w = n.shape
@@ -419,7 +422,8 @@ class NeuralNet:
         if n.is_mat:
             m.t[:b, :w].copy_(t.reshape(b, w))
         else:
-            m.t[:b * h * w, :c].copy_(t.permute(0, 2, 3, 1).reshape(b * h * w, c))
+            wp = n.wpitch or w
+            m.t[:b * h * wp].reshape(b, h, wp, -1)[:, :, :w, :c].copy_(t.permute(0, 2, 3, 1))
 
     def _bridge_forward(self, c: Connection, is_train: bool) -> None:
         for n in c.nodes_in:
@@ -492,6 +496,9 @@ class NeuralNet:
         L = ops.lib()
         if n.is_mat:
             ops.check(L.cxn_copy2d(st.data_ptr(), w, n.act.ptr, n.act.ld, b, w, 1, 0, ops.stream()), "copy2d")
+        elif n.wpitch:
+            ops.check(L.cxn_nchw_f32_to_nhwc4_pitched(st.data_ptr(), n.act.ptr, b, c, h, w, n.wpitch, ops.stream()),
+                      "nchw_to_nhwc4_pitched")
         else:
             ops.check(L.cxn_nchw_f32_to_nhwc_bf16(st.data_ptr(), n.act.ptr, b, c, h * w, n.act.ld, ops.stream()),
                       "nchw_to_nhwc")

@@ -29,7 +29,7 @@ from .. import model_io as mio
 class Node:
     """One activation node of the graph."""
 
-    __slots__ = ("shape", "data", "name", "index", "act", "grad", "f32", "alias_of", "loss_input")
+    __slots__ = ("shape", "data", "name", "index", "act", "grad", "f32", "alias_of", "loss_input", "wpitch")
 
     def __init__(self, name: str = "", index: int = 0):
         self.shape: List[int] = [0, 0, 0, 0]  # (b, c, h, w)
@@ -42,6 +42,7 @@ class Node:
         self.f32 = None    # fp32 [b, ld] buffer for loss nodes
         self.alias_of = None
         self.loss_input = False
+        self.wpitch = 0    # b200: pixels per stored image row when it differs from shape[3] (0 = dense)
 
     @property
     def is_mat(self) -> bool:

@@ -7,6 +7,8 @@ reference methods stay available as the oracle.  Kernel inventory: SURVEY.md sec
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from .. import ops
@@ -111,6 +113,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         self.col = None
         self.wflip = None
         self.cin_pad = 0        # 4 when a <=4-channel input is stored with a channel pitch of 4
+        self.pair = False       # cin_pad input read as [H][Wp/2] super-pixels of 8 channels (two pixels each)
         self.igemm_fwd = False
         self.igemm_dgrad = False
 
@@ -129,22 +132,43 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         elif (g == 1 and p.num_input_channel <= 4 and input_is_node0 and sole_consumer and small):
             self.igemm_fwd = True
             self.cin_pad = 4
+            # Pixel pairs: with an even stride and no horizontal padding every filter row starts on an even
+            # pixel, so the image (stored with an even row pitch) reads as super-pixels of two pixels = 8
+            # channels = one 16-byte granule, filter width ceil(kw/2), stride_x / 2.  Half the gather
+            # instructions of the 8-byte (one pixel) granule form; the odd filter column, if any, is a
+            # structural zero of the internal weight layout.
+            self.pair = p.stride % 2 == 0 and p.pad_x == 0 and os.environ.get("CXN_CONV_PAIR", "1") != "0"
         ocg = p.num_channel // g
         pad_ok = p.kernel_height - 1 - p.pad_y >= 0 and p.kernel_width - 1 - p.pad_x >= 0
         self.igemm_dgrad = (self.igemm_fwd and p.stride == 1 and ocg % 8 == 0 and pad_ok
                             and (p.kernel_height * p.kernel_width * ocg) // 8 <= 1024)
+        if self.pair:
+            return (self.cin_pad, ops.round_up(self.nodes_in[0].shape[3], 2))
         return self.cin_pad
 
     def _icg(self):
         p = self.param
         return self.cin_pad if self.cin_pad else p.num_input_channel // p.num_group
 
+    def _kw2(self):
+        return (self.param.kernel_width + 1) // 2
+
     def _geom(self):
         p = self.param
         g = p.num_group
         icg = self._icg()
         kg = icg * p.kernel_height * p.kernel_width
+        if self.pair:
+            kg = 8 * p.kernel_height * self._kw2()
         return g, icg, p.num_channel // g, kg, ops.round_up(kg, 8)
+
+    def _gather_args(self, x):
+        """(H, W, pixel pitch, channels per group, granule, KW, stride, pad_x) as the implicit-GEMM kernel sees the input"""
+        p = self.param
+        b, c, h, w = x.shape
+        if self.pair:
+            return (h, x.wpitch // 2, 8, 8, 8, self._kw2(), p.stride | ((p.stride // 2) << 16), 0)
+        return (h, w, x.act.ld, self._icg(), 4 if self.cin_pad else 8, p.kernel_width, p.stride, p.pad_x)
 
     def weight_to_internal(self, tag, w):
         if tag != "wmat":
@@ -155,6 +179,8 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         w5 = w.reshape(g, ocg, cin, p.kernel_height, p.kernel_width).permute(0, 1, 3, 4, 2)
         if icg != cin:
             w5 = torch.nn.functional.pad(w5, (0, icg - cin))
+        if self.pair:
+            w5 = torch.nn.functional.pad(w5, (0, 0, 0, 2 * self._kw2() - p.kernel_width))   # zero odd filter column
         return w5.reshape(g, ocg, kg)
 
     def weight_from_internal(self, tag, w):
@@ -163,7 +189,8 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         p = self.param
         g, icg, ocg, kg, _ = self._geom()
         cin = p.num_input_channel // g
-        w5 = w.reshape(g, ocg, p.kernel_height, p.kernel_width, icg)[..., :cin]
+        kw = 2 * self._kw2() if self.pair else p.kernel_width
+        w5 = w.reshape(g, ocg, p.kernel_height, kw, icg)[:, :, :, :p.kernel_width, :cin]
         return w5.permute(0, 1, 4, 2, 3).reshape(g, ocg, cin * p.kernel_height * p.kernel_width)
 
     def b200_shadow(self, tag):
@@ -199,9 +226,10 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         bias = self.bind["bias"].w.data_ptr() if p.no_bias == 0 else None
         b, c, h, w = x.shape
         if self.igemm_fwd:
-            ops.check(L.cxn_conv_fprop(x.act.ptr, b, h, w, x.act.ld, icg, g, 4 if self.cin_pad else 8,
-                                       W.shadow.data_ptr(), kpad, ocg, p.kernel_height, p.kernel_width, p.stride,
-                                       p.pad_y, p.pad_x, y.shape[2], y.shape[3], y.act.ptr, y.act.ld, bias,
+            gh, gw, gcs, gcg, gran, gkw, gstride, gpad_x = self._gather_args(x)
+            ops.check(L.cxn_conv_fprop(x.act.ptr, b, gh, gw, gcs, gcg, g, gran,
+                                       W.shadow.data_ptr(), kpad, ocg, p.kernel_height, gkw, gstride,
+                                       p.pad_y, gpad_x, y.shape[2], y.shape[3], y.act.ptr, y.act.ld, bias,
                                        1 if self.fuse_relu else 0, ops.stream()), "conv_fprop")
             return
         ops.check(L.cxn_im2col_nhwc(x.act.ptr, self.col.data_ptr(), *self._im2col_args(x, y, rows, kpad),
@@ -224,9 +252,13 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
                                         1 if ex.accumulate_grads else 0, ops.stream()), "colsum")
         # weight gradient (accumulates into the arena gradient, which the updater leaves zeroed)
         if self.igemm_fwd:
-            ops.check(L.cxn_conv_wgrad(x.act.ptr, b, h, w, x.act.ld, icg, g, 4 if self.cin_pad else 8, gy.ptr, gy.ld,
-                                       ocg, p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x, y.shape[2],
-                                       y.shape[3], W.g.data_ptr(), kg, 0, ops.stream()), "conv_wgrad")
+            gh, gw, gcs, gcg, gran, gkw, gstride, gpad_x = self._gather_args(x)
+            # pair mode: the odd filter column is a structural zero - its gradient (real pixels!) must not accumulate
+            mask = (8 * gkw, 4 * p.kernel_width) if self.pair and p.kernel_width % 2 else (0, 0)
+            ops.check(L.cxn_conv_wgrad_masked(x.act.ptr, b, gh, gw, gcs, gcg, g, gran, gy.ptr, gy.ld,
+                                              ocg, p.kernel_height, gkw, gstride, p.pad_y, gpad_x, y.shape[2],
+                                              y.shape[3], W.g.data_ptr(), kg, 0, mask[0], mask[1], ops.stream()),
+                      "conv_wgrad")
         else:
             kb = (rows + 63) // 64
             tiles = ((ocg + 127) // 128) * ((kg + 127) // 128) * g
@@ -250,8 +282,10 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             pass
         ops.gemm(gy.ptr, gy.ld, ocg, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 1, self.col.data_ptr(), kpad,
                  rows * kpad, None, 0, rows, kg, ocg, batch=g, flags=ops.GEMM_OUT_BF16)
-        ops.check(L.cxn_col2im_nhwc(self.col.data_ptr(), x.grad.ptr, b, h, w, x.act.ld, p.num_group, p.kernel_height,
-                                    p.kernel_width, p.stride, p.pad_y, p.pad_x, y.shape[2], y.shape[3], kpad,
+        # pair mode: (kh, kw2, 8) columns are (kh, 2*kw2, 4) in the pixel domain of the pitched image
+        cw, ckw = (x.wpitch, 2 * self._kw2()) if self.pair else (w, p.kernel_width)
+        ops.check(L.cxn_col2im_nhwc(self.col.data_ptr(), x.grad.ptr, b, h, cw, x.act.ld, p.num_group, p.kernel_height,
+                                    ckw, p.stride, p.pad_y, p.pad_x, y.shape[2], y.shape[3], kpad,
                                     rows * kpad, ops.stream()), "col2im")
 
 

@@ -44,6 +44,12 @@ int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg, int G, 
                    long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW, float* dw,
                    long long lddw, int splits, cudaStream_t stream);
 /* filter flip + channel transpose used to run backward-data as a forward convolution. */
+/* cxn_conv_wgrad that leaves columns n with (n % mask_period) >= mask_valid untouched (structural zeros of a
+ * padded filter layout; both multiples of 4, 0 = no mask).  In every conv entry point `stride` may carry an
+ * anisotropic stride as stride_y | (stride_x << 16). */
+int cxn_conv_wgrad_masked(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
+                          long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                          float* dw, long long lddw, int splits, int mask_period, int mask_valid, cudaStream_t stream);
 int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in, int ld_out,
                           cudaStream_t stream);
 /* experiment / tuning knobs of the implicit-GEMM convolution (0, or -1 for switches, = automatic):
@@ -62,6 +68,8 @@ int cxn_col2im_nhwc(const void* col, void* dx, int N, int H, int W, int C, int G
 
 /* ---- layout (API boundary: public layout is NCHW fp32, src/layer/layer.h:33-54) ------------- */
 int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C, int HW, int ldc, cudaStream_t stream);
+/* C <= 4 input image -> NHWC bf16 with pixel pitch 4 and an even row pitch Wp >= W (pad pixels zero) */
+int cxn_nchw_f32_to_nhwc4_pitched(const float* src, void* dst, int N, int C, int H, int W, int Wp, cudaStream_t stream);
 int cxn_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int N, int C, int HW, int ldc, cudaStream_t stream);
 /* flatten in (c,h,w) order and its inverse.  Reference: src/layer/flatten_layer-inl.hpp:10-39. */
 int cxn_bf16_hwc_chw(const void* src, void* dst, int N, int C, int HW, long long src_img, long long dst_img,

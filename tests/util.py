@@ -49,7 +49,8 @@ def copy_weights(src: NetTrainer, dst: NetTrainer) -> None:
             dst.net.set_weight(i, ws, tag)
 
 
-def compare_backends(conf: str, batch: DataBatch, tol_out=2e-2, tol_grad=4e-2, check_nodes=None, skip=()):
+def compare_backends(conf: str, batch: DataBatch, tol_out=2e-2, tol_grad=4e-2, check_nodes=None, skip=(),
+                     return_trainers=False):
     """one forward/backward on the reference backend (fp32, CUDA) and on the b200 backend with
     identical weights and data; returns dict of relative L1 errors and asserts tolerances."""
     ref = make_trainer(conf, dev="gpu:0", backend="ref")
@@ -81,4 +82,6 @@ def compare_backends(conf: str, batch: DataBatch, tol_out=2e-2, tol_grad=4e-2, c
             continue
         tol = tol_out if k.startswith("node") else tol_grad
         assert v == v and v <= tol, "%s: relative error %g > %g (all: %s)" % (k, v, tol, errs)
+    if return_trainers:
+        return errs, ref, b2
     return errs
