@@ -32,7 +32,7 @@ def main():
     shapes = [("fc6 fwd b256", 256, 4096, 9216, 0, 0), ("fc6 fwd b32", 32, 4096, 9216, 0, 0),
               ("fc7 fwd b256", 256, 4096, 4096, 0, 0), ("fc8 fwd b256", 256, 1000, 4096, 0, 0),
               ("fc6 dgrad b256", 256, 9216, 4096, 0, 1), ("fc6 wgrad b256", 4096, 9216, 256, 1, 1),
-              ("fc6 wgrad b32", 4096, 9216, 32, 1, 1), ("square 4096", 4096, 4096, 4096, 0, 0),
+              ("fc6 wgrad b32", 4096, 9216, 32, 1, 1), ("fc6 dgrad b32", 32, 9216, 4096, 0, 1), ("fc7 fwd b32", 32, 4096, 4096, 0, 0), ("square 4096", 4096, 4096, 4096, 0, 0),
               ("square 8192", 8192, 8192, 8192, 0, 0)]
     for name, M, N, K, amn, bmn in shapes:
         A = torch.randn((K, M) if amn else (M, K), device="cuda").to(torch.bfloat16)
@@ -41,18 +41,18 @@ def main():
         D = torch.zeros(M, N, device="cuda", dtype=torch.float32 if wgrad else torch.bfloat16)
         flags = 0 if wgrad else ops.GEMM_OUT_BF16
         res = {"shape": name, "M": M, "N": N, "K": K}
-        for bn in (64, 128, 256):
+        for bn in (0, 64, 128, 256):
             def run(bn=bn):
                 ops.gemm(A.data_ptr(), A.shape[1], 0, amn, B.data_ptr(), B.shape[1], 0, bmn, D.data_ptr(), N, 0, None, 0,
                          M, N, K, flags=flags, bn=bn)
-            res["bn%d_us" % bn] = timeit(run)
+            res[("bn%d_us" % bn) if bn else "auto_us"] = round(timeit(run), 1)
         Af = A.t() if amn else A
         Bf = B if bmn else B.t()
 
         def ref():
             torch.matmul(Af, Bf)
-        res["cublas_us"] = timeit(ref)
-        best = min(res["bn64_us"], res["bn128_us"], res["bn256_us"])
+        res["cublas_us"] = round(timeit(ref), 1)
+        best = min(res["auto_us"], res["bn64_us"], res["bn128_us"], res["bn256_us"])
         res["best_tflops"] = 2.0 * M * N * K / best / 1e6
         res["best_GBps"] = (A.numel() * 2 + B.numel() * 2 + D.numel() * D.element_size()) / best / 1e3
         rows.append(res)

@@ -124,7 +124,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int kb0 = split * p.kb_per_split;
       const int kb1 = min(num_kb, kb0 + p.kb_per_split);
       for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait_warp(empty_bar(stage), phase ^ 1u);
+        mbar_wait(empty_bar(stage), phase ^ 1u);
         const uint32_t sa = smem_base + stage * C::kStageBytes;
         const uint32_t sb = sa + C::kABytes;
         if (elect_one()) {
@@ -170,11 +170,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int split = (int)(r % p.splits);
       const int kb0 = split * p.kb_per_split;
       const int kb1 = min(num_kb, kb0 + p.kb_per_split);
-      mbar_wait_warp(tempty_bar(acc), acc_phase ^ 1u);
+      mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
       for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait_warp(full_bar(stage), phase);
+        mbar_wait(full_bar(stage), phase);
         tc_fence_after();
         const uint32_t sa = smem_base + stage * C::kStageBytes;
         const uint32_t sb = sa + C::kABytes;
@@ -209,7 +209,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int z = (int)(r / p.splits);
       const int kb0 = split * p.kb_per_split;
       const int kb1 = min(num_kb, kb0 + p.kb_per_split);
-      mbar_wait_warp(tfull_bar(acc), acc_phase);
+      mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const int row = m_blk * BM + quad * 32 + lane;
       const bool row_ok = row < p.M;
@@ -262,7 +262,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
         } else {
           float* d = reinterpret_cast<float*>(p.D) + off;
-          if (atomic) {
+          if (atomic && full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+            // 128-bit reductions: a quarter of the L2 atomic operations of the scalar form
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + 4 * q), "f"(f[4 * q]),
+                           "f"(f[4 * q + 1]), "f"(f[4 * q + 2]), "f"(f[4 * q + 3])
+                           : "memory");
+          } else if (atomic) {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
               if (full || n0 + j < p.N) atomicAdd(d + j, f[j]);
@@ -297,6 +304,35 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::kTmemCols)
                  : "memory");
+  }
+}
+
+// Second half of an internally split GEMM: D = act(ws + bias) (+ D), ws (fp32 [M][ldw]) is left zeroed
+// for the next call.
+__global__ void splitk_finish_kernel(float* __restrict__ ws, int ldw, void* __restrict__ D, long long ldd,
+                                     const float* __restrict__ bias, int M, int N, int flags) {
+  const int nq = ldw >> 2;
+  const long long total = (long long)M * nq;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int row = (int)(i / nq), c = (int)(i - (long long)row * nq) << 2;
+    float4* w4 = reinterpret_cast<float4*>(ws + (long long)row * ldw + c);
+    const float4 v = *w4;
+    *w4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    float f[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (c + j >= N) continue;
+      if (bias != nullptr) f[j] += __ldg(bias + c + j);
+      if (flags & kFlagRelu) f[j] = fmaxf(f[j], 0.0f);
+      const long long o = (long long)row * ldd + c + j;
+      if (flags & kFlagOutBf16) {
+        reinterpret_cast<bf16*>(D)[o] = __float2bfloat16(f[j]);
+      } else {
+        float* d = reinterpret_cast<float*>(D) + o;
+        *d = (flags & kFlagBeta1) ? *d + f[j] : f[j];
+      }
+    }
   }
 }
 
@@ -399,6 +435,27 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p,
   return 0;
 }
 
+// fp32 scratch of the internally split GEMMs: one zeroed buffer per (device, stream), grown on demand
+static float* splitk_workspace(size_t bytes, cudaStream_t st) {
+  struct Ws { float* p; size_t n; };
+  static std::mutex mu;
+  static std::unordered_map<uint64_t, Ws> map;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const uint64_t key = ((uint64_t)dev << 56) ^ (uint64_t)(uintptr_t)st;
+  std::lock_guard<std::mutex> g(mu);
+  Ws& w = map[key];
+  if (w.n < bytes) {
+    if (w.p) cudaFree(w.p);
+    w.p = nullptr; w.n = 0;
+    const size_t want = bytes < (4u << 20) ? (4u << 20) : bytes;
+    if (cudaMalloc(&w.p, want) != cudaSuccess) { w.p = nullptr; return nullptr; }
+    if (cudaMemsetAsync(w.p, 0, want, st) != cudaSuccess) return nullptr;
+    w.n = want;
+  }
+  return w.p;
+}
+
 }  // namespace gemm
 }  // namespace cxn
 
@@ -418,13 +475,49 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   if (splits > num_kb) splits = num_kb;
   if (splits > 1 && !(flags & kFlagAtomic)) return -5;
   if ((flags & kFlagAtomic) && (flags & kFlagOutBf16)) return -6;
+  const int sms = num_sms();
+  // Skinny problems (few output tiles, long K - the fully connected layers at any batch size) are
+  // split along K internally: partial tiles meet in a zeroed fp32 scratch through vector
+  // reductions and a second small kernel applies bias / activation / conversion.  More CTAs pull
+  // on the weight stream, and wider tiles re-read the activations less often.
+  static const bool auto_split = getenv("CXN_GEMM_NO_AUTOSPLIT") == nullptr;
+  // (measured: worth it only while even 64-wide tiles would leave a quarter of the SMs idle)
+  const long long tiles64 = (long long)ceil_div(M, BM) * ceil_div(N, 64);
+  if (auto_split && splits == 1 && batch == 1 && bn == 0 && !(flags & kFlagAtomic) && num_kb >= 16 &&
+      tiles64 * 4 < 3LL * sms) {
+    int best_bn = 0, best_splits = 1;
+    const int cand[3] = {256, 128, 64};
+    for (int ci = 0; ci < 3; ++ci) {
+      const int b = cand[ci];
+      if (b > 64 && N <= b / 2) continue;
+      const long long t = (long long)ceil_div(M, BM) * ceil_div(N, b);
+      if (t >= sms) break;                       // enough tiles without splitting
+      int sp = (int)(sms / t);
+      if (sp > num_kb / 8) sp = num_kb / 8;      // keep at least 8 k-blocks per split
+      if (sp < 2) continue;
+      if (t * sp >= (3 * sms) / 4 || ci == 2) { best_bn = b; best_splits = sp; break; }
+    }
+    const int ldw = (N + 3) & ~3;
+    const size_t ws_bytes = (size_t)M * ldw * sizeof(float);
+    if (best_bn && ws_bytes <= (64u << 20)) {
+      float* ws = splitk_workspace(ws_bytes, stream);
+      if (ws != nullptr) {
+        int rc = cxn_gemm_bf16(A, lda, strideA, a_mn, B, ldb, strideB, b_mn, ws, ldw, 0, nullptr, 0, M, N, K, 1, best_splits,
+                               kFlagAtomic, best_bn, stream);
+        if (rc) return rc;
+        const long long quads = (long long)M * (ldw >> 2);
+        splitk_finish_kernel<<<ew_grid(quads, 256), 256, 0, stream>>>(ws, ldw, D, ldd, bias, M, N, flags);
+        CXN_CHECK_LAUNCH();
+        return 0;
+      }
+    }
+  }
   int kbps = ceil_div(num_kb, splits);
   splits = ceil_div(num_kb, kbps);
-  const int sms = num_sms();
   if (bn == 0) {
     auto tiles = [&](int b) { return (long long)ceil_div(M, BM) * ceil_div(N, b) * batch * splits; };
     if (N > 128 && tiles(256) >= sms) bn = 256;
-    else if (N > 64 && tiles(128) >= sms) bn = 128;
+    else if (N > 64 && tiles(128) * 4 >= 3LL * sms) bn = 128;
     else bn = (N > 64 && tiles(64) > 2LL * sms) ? 128 : 64;
   }
   Params p;
