@@ -595,20 +595,23 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
 }
 
 // W[g][oc][kh][kw][ic] (ld_in) -> Wt[g][ic][KH-1-kh][KW-1-kw][oc] (ld_out): the filter of the equivalent
-// forward convolution that computes backward-data of a stride-1 convolution.
-__global__ void flip_weights_kernel(const bf16* __restrict__ w, bf16* __restrict__ wt, int G, int ocg, int icg, int KH,
-                                    int KW, int ld_in, int ld_out) {
-  const long long total = (long long)G * ocg * KH * KW * icg;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    long long r = i;
-    const int oc = (int)(r % ocg); r /= ocg;      // fastest in the OUTPUT layout
-    const int kw = (int)(r % KW); r /= KW;
-    const int kh = (int)(r % KH); r /= KH;
-    const int ic = (int)(r % icg);
-    const int g = (int)(r / icg);
-    const bf16 v = w[((long long)g * ocg + oc) * ld_in + ((KH - 1 - kh) * KW + (KW - 1 - kw)) * icg + ic];
-    wt[((long long)g * icg + ic) * ld_out + (kh * KW + kw) * ocg + oc] = v;
+// forward convolution that computes backward-data of a stride-1 convolution.  Per (group, tap) this is
+// the transpose of an ocg x icg block: 32 x 32 tiles through shared memory, both sides coalesced.
+__global__ void flip_weights_kernel(const bf16* __restrict__ w, bf16* __restrict__ wt, int ocg, int icg, int taps,
+                                    int ld_in, int ld_out) {
+  __shared__ bf16 tile[32][33];
+  const int g = blockIdx.z / taps, t = blockIdx.z - g * taps;
+  const int oc0 = blockIdx.y * 32, ic0 = blockIdx.x * 32;
+  const bf16* src = w + (long long)g * ocg * ld_in + (long long)t * icg;
+  bf16* dst = wt + (long long)g * icg * ld_out + (long long)(taps - 1 - t) * ocg;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int oc = oc0 + i, ic = ic0 + threadIdx.x;
+    tile[i][threadIdx.x] = (oc < ocg && ic < icg) ? src[(long long)oc * ld_in + ic] : __float2bfloat16(0.0f);
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int ic = ic0 + i, oc = oc0 + threadIdx.x;
+    if (ic < icg && oc < ocg) dst[(long long)ic * ld_out + oc] = tile[threadIdx.x][i];
   }
 }
 
@@ -893,7 +896,9 @@ CXN_API int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int i
                                   int ld_out, cudaStream_t st) {
   const long long total = (long long)G * ocg * KH * KW * icg;
   if (total <= 0) return 0;
-  flip_weights_kernel<<<ew_grid(total, 256), 256, 0, st>>>((const bf16*)w, (bf16*)wt, G, ocg, icg, KH, KW, ld_in, ld_out);
+  if ((long long)G * KH * KW > 65535) return -1;
+  dim3 grid(ceil_div(icg, 32), ceil_div(ocg, 32), G * KH * KW), block(32, 8);
+  flip_weights_kernel<<<grid, block, 0, st>>>((const bf16*)w, (bf16*)wt, ocg, icg, KH * KW, ld_in, ld_out);
   CXN_CHECK_LAUNCH();
   return 0;
 }

@@ -199,6 +199,7 @@ class NeuralNet:
     def _setup_b200(self) -> None:
         from .parallel.arena import ParamArena
         cfg = self.cfg
+        ops.set_device_index(self.device.index if self.device.index is not None else torch.cuda.current_device())
         consumers: Dict[int, int] = {}
         for c in self.connections:
             for n in c.nodes_in:
