@@ -261,6 +261,8 @@ using namespace cxn;
 
 extern "C" { unsigned long long cxn_launch_counter_ = 0; }
 CXN_API unsigned long long cxn_launch_count() { return cxn_launch_counter_; }
+// launches replayed from a captured CUDA graph never pass through this library's entry points
+CXN_API unsigned long long cxn_launch_count_add(unsigned long long n) { return cxn_launch_counter_ += n; }
 
 CXN_API int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C, int HW, int ldc, cudaStream_t st) {
   if (N <= 0 || C <= 0 || HW <= 0) return 0;

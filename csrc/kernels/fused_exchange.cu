@@ -46,6 +46,7 @@ struct Params {
   long long cb, ce;         // bucket = chunks [cb, ce)
   int rank, nranks, kind;
   unsigned seq;
+  const unsigned* seq_dev;  // optional device word added to seq when the kernel starts (cxn_xchg_set_epoch_ptr)
   int slot;
   unsigned* counter;        // local scratch: CTA completion counter (zero between launches)
   int dbg;                  // profiling aid (CXN_XCHG_DBG): 1 skip peer loads, 2 skip peer stores, 4 skip phase 2
@@ -76,21 +77,28 @@ __device__ __forceinline__ unsigned* flag_ptr(char* base, long long off_flags, i
   return reinterpret_cast<unsigned*>(base + off_flags) + ((which * kMaxSlots + slot) * kMaxRanks + src);
 }
 // wait until every rank has published `seq` in local flag row (which, slot)
-__device__ __forceinline__ void wait_all(const Params& p, int which) {
+__device__ __forceinline__ void wait_all(const Params& p, int which, unsigned seq) {
   if (threadIdx.x < p.nranks) {
     const unsigned* f = flag_ptr(p.peers[p.rank], p.off_flags, which, p.slot, threadIdx.x);
     const long long t0 = clock64();
     unsigned spins = 0;
-    while ((int)(ld_acquire_sys(f) - p.seq) < 0) {
+    while ((int)(ld_acquire_sys(f) - seq) < 0) {
       __nanosleep(64);
       if ((++spins & 4095u) == 0 && clock64() - t0 > 20000000000LL) {
         printf("[cxxnet_b200 exchange] rank %d timed out waiting for rank %d (slot %d phase %d seq %u)\n", p.rank,
-               (int)threadIdx.x, p.slot, which, p.seq);
+               (int)threadIdx.x, p.slot, which, seq);
         __trap();
       }
     }
   }
   __syncthreads();
+}
+
+// Sequence number of this launch.  The host part is constant per captured CUDA graph; the device
+// part is a step counter the training loop bumps on the main stream before a step's first exchange
+// launch (and never while one is in flight), so replaying a graph still advances the barriers.
+__device__ __forceinline__ unsigned launch_seq(const Params& p) {
+  return p.seq + (p.seq_dev != nullptr ? *reinterpret_cast<const volatile unsigned*>(p.seq_dev) : 0u);
 }
 
 __device__ __forceinline__ float clip_grad(float g, float c) {
@@ -111,6 +119,7 @@ __device__ __forceinline__ int find_seg(const Segment* sseg, int nseg, long long
 template <int NR, int U>   // NR: compile-time upper bound on ranks per load group, U: chunks in flight
 __global__ void __launch_bounds__(kThreads, 4)   // <= 64 registers: must co-reside with the GEMM CTAs it overlaps
 fused_rs_update_ag_kernel(const Params p) {
+  const unsigned seq = launch_seq(p);
   __shared__ Segment sseg[kMaxBucketSegs];
   char* self = p.peers[p.rank];
   // the segments this bucket covers (contiguous in the table)
@@ -119,8 +128,8 @@ fused_rs_update_ag_kernel(const Params p) {
   if (threadIdx.x < nseg) sseg[threadIdx.x] = p.segs[seg_lo + threadIdx.x];
   // ---------------- entry barrier: every rank's gradients for this bucket are complete
   if (blockIdx.x == 0 && threadIdx.x < p.nranks)
-    st_release_sys(flag_ptr(p.peers[threadIdx.x], p.off_flags, 0, p.slot, p.rank), p.seq);
-  wait_all(p, 0);
+    st_release_sys(flag_ptr(p.peers[threadIdx.x], p.off_flags, 0, p.slot, p.rank), seq);
+  wait_all(p, 0, seq);
 
   // ---------------- phase 1: reduce-scatter + update + all-gather on the owned shard
   const long long nch = p.ce - p.cb;
@@ -214,10 +223,10 @@ fused_rs_update_ag_kernel(const Params p) {
     if (prev == gridDim.x - 1) {
       *p.counter = 0u;
       __threadfence_system();
-      for (int r = 0; r < p.nranks; ++r) st_release_sys(flag_ptr(p.peers[r], p.off_flags, 1, p.slot, p.rank), p.seq);
+      for (int r = 0; r < p.nranks; ++r) st_release_sys(flag_ptr(p.peers[r], p.off_flags, 1, p.slot, p.rank), seq);
     }
   }
-  wait_all(p, 1);
+  wait_all(p, 1, seq);
 
   // ---------------- phase 2 (local): zero gradients, refresh the bf16 shadow of the bucket
   float* g = reinterpret_cast<float*>(self + p.off_g);
@@ -269,6 +278,7 @@ fused_rs_update_ag_kernel(const Params p) {
 
 // K19: copy [off, off+bytes) of the root's block into every rank's block, then barrier.
 __global__ void __launch_bounds__(kThreads) broadcast_kernel(const Params p, long long off, long long bytes, int root) {
+  const unsigned seq = launch_seq(p);
   if (p.rank == root) {
     const long long n16 = bytes / 16;
     const uint4* src = reinterpret_cast<const uint4*>(p.peers[root] + off);
@@ -286,10 +296,10 @@ __global__ void __launch_bounds__(kThreads) broadcast_kernel(const Params p, lon
     if (prev == gridDim.x - 1) {
       *p.counter = 0u;
       __threadfence_system();
-      for (int r = 0; r < p.nranks; ++r) st_release_sys(flag_ptr(p.peers[r], p.off_flags, 1, p.slot, p.rank), p.seq);
+      for (int r = 0; r < p.nranks; ++r) st_release_sys(flag_ptr(p.peers[r], p.off_flags, 1, p.slot, p.rank), seq);
     }
   }
-  wait_all(p, 1);
+  wait_all(p, 1, seq);
 }
 
 // K18: all-gather of up to two local pieces into every rank's symmetric block, bracketed by the
@@ -303,9 +313,10 @@ struct GatherArgs {
   int npieces;
 };
 __global__ void __launch_bounds__(kThreads) allgather_kernel(const Params p, const GatherArgs a) {
+  const unsigned seq = launch_seq(p);
   if (blockIdx.x == 0 && threadIdx.x < p.nranks)
-    st_release_sys(flag_ptr(p.peers[threadIdx.x], p.off_flags, 0, p.slot, p.rank), p.seq);
-  wait_all(p, 0);
+    st_release_sys(flag_ptr(p.peers[threadIdx.x], p.off_flags, 0, p.slot, p.rank), seq);
+  wait_all(p, 0, seq);
   for (int k = 0; k < a.npieces; ++k) {
     const long long n16 = a.slot_bytes[k] / 16, v16 = a.valid_bytes[k] / 16;
     const uint4* src = reinterpret_cast<const uint4*>(a.src[k]);
@@ -325,10 +336,10 @@ __global__ void __launch_bounds__(kThreads) allgather_kernel(const Params p, con
     if (prev == gridDim.x - 1) {
       *p.counter = 0u;
       __threadfence_system();
-      for (int r = 0; r < p.nranks; ++r) st_release_sys(flag_ptr(p.peers[r], p.off_flags, 1, p.slot, p.rank), p.seq);
+      for (int r = 0; r < p.nranks; ++r) st_release_sys(flag_ptr(p.peers[r], p.off_flags, 1, p.slot, p.rank), seq);
     }
   }
-  wait_all(p, 1);
+  wait_all(p, 1, seq);
 }
 
 }  // namespace xchg
@@ -336,6 +347,14 @@ __global__ void __launch_bounds__(kThreads) allgather_kernel(const Params p, con
 
 using namespace cxn;
 using namespace cxn::xchg;
+
+// Device word (4-byte aligned, lives as long as exchanges are launched) whose value every exchange
+// kernel adds to its `seq` argument; NULL (the default) = the argument alone.  One GPU per process.
+static const unsigned* g_epoch_ptr = nullptr;
+CXN_API int cxn_xchg_set_epoch_ptr(const void* dev_word) {
+  g_epoch_ptr = reinterpret_cast<const unsigned*>(dev_word);
+  return 0;
+}
 
 CXN_API int cxn_xchg_flag_bytes() { return 2 * kMaxSlots * kMaxRanks * 4; }
 CXN_API int cxn_xchg_max_ranks() { return kMaxRanks; }
@@ -351,6 +370,7 @@ static int fill_params(Params* p, const unsigned long long* peers, int nranks, i
   p->off_w = off_w; p->off_g = off_g; p->off_m = off_m; p->off_m2 = off_m2; p->off_shadow = off_shadow;
   p->off_flags = off_flags; p->segs = (const Segment*)segs; p->chunk_seg = chunk_seg; p->cb = cb; p->ce = ce;
   p->rank = rank; p->nranks = nranks; p->kind = kind; p->seq = seq; p->slot = slot; p->counter = counter;
+  p->seq_dev = g_epoch_ptr;
   static const int dbg = getenv("CXN_XCHG_DBG") ? atoi(getenv("CXN_XCHG_DBG")) : 0;
   p->dbg = dbg;
   return 0;

@@ -435,25 +435,55 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p,
   return 0;
 }
 
-// fp32 scratch of the internally split GEMMs: one zeroed buffer per (device, stream), grown on demand
+// fp32 scratch of the internally split GEMMs: one zeroed buffer per device, grown on demand (never
+// while a stream is capturing - the first, eager, steps size it).  Different streams using it are
+// ordered through an event; inside a stream capture neither the wait nor the record is issued (the
+// capture begins after a device synchronisation and its streams are ordered by the graph itself).
+struct SplitWs {
+  float* p = nullptr;
+  size_t n = 0;
+  cudaEvent_t ev = nullptr;
+  cudaStream_t last = nullptr;
+  bool used = false;
+};
+static std::mutex g_ws_mu;
+static SplitWs g_ws[64];
+
+static bool stream_capturing(cudaStream_t st) {
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) return false;
+  return cs != cudaStreamCaptureStatusNone;
+}
+
 static float* splitk_workspace(size_t bytes, cudaStream_t st) {
-  struct Ws { float* p; size_t n; };
-  static std::mutex mu;
-  static std::unordered_map<uint64_t, Ws> map;
   int dev = 0;
   cudaGetDevice(&dev);
-  const uint64_t key = ((uint64_t)dev << 56) ^ (uint64_t)(uintptr_t)st;
-  std::lock_guard<std::mutex> g(mu);
-  Ws& w = map[key];
+  if (dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> g(g_ws_mu);
+  SplitWs& w = g_ws[dev];
+  const bool capturing = stream_capturing(st);
   if (w.n < bytes) {
-    if (w.p) cudaFree(w.p);
+    if (capturing) return nullptr;            // cannot allocate now: the caller falls back to the unsplit kernel
+    if (w.p) { cudaDeviceSynchronize(); cudaFree(w.p); }
     w.p = nullptr; w.n = 0;
-    const size_t want = bytes < (4u << 20) ? (4u << 20) : bytes;
+    const size_t want = bytes < (16u << 20) ? (16u << 20) : bytes;
     if (cudaMalloc(&w.p, want) != cudaSuccess) { w.p = nullptr; return nullptr; }
     if (cudaMemsetAsync(w.p, 0, want, st) != cudaSuccess) return nullptr;
     w.n = want;
+    if (!w.ev) cudaEventCreateWithFlags(&w.ev, cudaEventDisableTiming);
+    w.last = st; w.used = false;
   }
+  if (!capturing && w.used && w.last != st && w.ev) cudaStreamWaitEvent(st, w.ev, 0);
   return w.p;
+}
+static void splitk_release(cudaStream_t st) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return;
+  std::lock_guard<std::mutex> g(g_ws_mu);
+  SplitWs& w = g_ws[dev];
+  if (!stream_capturing(st) && w.ev) cudaEventRecord(w.ev, st);
+  w.last = st; w.used = true;
 }
 
 }  // namespace gemm
@@ -508,6 +538,7 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
         const long long quads = (long long)M * (ldw >> 2);
         splitk_finish_kernel<<<ew_grid(quads, 256), 256, 0, stream>>>(ws, ldw, D, ldd, bias, M, N, flags);
         CXN_CHECK_LAUNCH();
+        splitk_release(stream);
         return 0;
       }
     }

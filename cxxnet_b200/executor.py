@@ -301,6 +301,8 @@ class NeuralNet:
         # the compute of batch t
         self.in_stage = [torch.zeros((self.max_batch, c0, h0, w0), dtype=torch.float32, device=self.device)
                          for _ in range(2)]
+        self.hyper_prepared = False
+        self.hyper_slot = 0
         self.copy_stream = torch.cuda.Stream(device=self.device)
         self.stage_free = [torch.cuda.Event(), torch.cuda.Event()]
         self.stage_ready = [torch.cuda.Event(), torch.cuda.Event()]
@@ -469,22 +471,39 @@ class NeuralNet:
             for i, e in enumerate(extra):
                 self.nodes[i + 1].data = e.to(self.device, non_blocking=True).float().reshape(self.nodes[i + 1].shape)
             return
+        slot = self.stage_input(batch)
+        self.convert_staged(slot)
+        self.release_stage(slot)
+        for i, e in enumerate(extra):
+            self._stage_in(self.nodes[i + 1], self.extra_stage[i], e)
+
+    # The three parts of set_input for node 0, separately callable: a training step captured into a
+    # CUDA graph contains only the middle one (the staging buffers are persistent, one graph per slot).
+    def stage_input(self, batch: torch.Tensor) -> int:
+        """copy the batch into the next staging slot (pinned host memory goes through the copy stream,
+        overlapping the step still running) and make the main stream wait for it; returns the slot"""
+        b = batch.shape[0]
         self.stage_idx ^= 1
         slot = self.stage_idx
         main = torch.cuda.current_stream(self.device)
+        st = self.in_stage[slot][:b]
         if batch.device.type == "cpu" and batch.is_pinned():
-            st = self.in_stage[slot][:b]
             self.copy_stream.wait_event(self.stage_free[slot])
             with torch.cuda.stream(self.copy_stream):
                 st.copy_(batch.reshape(st.shape), non_blocking=True)
                 self.stage_ready[slot].record(self.copy_stream)
             main.wait_event(self.stage_ready[slot])
-            self._convert_in(self.nodes[0], st)
         else:
-            self._stage_in(self.nodes[0], self.in_stage[slot], batch)
-        self.stage_free[slot].record(main)
-        for i, e in enumerate(extra):
-            self._stage_in(self.nodes[i + 1], self.extra_stage[i], e)
+            st.copy_(batch.reshape(st.shape), non_blocking=True)
+        return slot
+
+    def convert_staged(self, slot: int) -> None:
+        """staging slot (fp32 NCHW) -> node 0 in the backend's layout"""
+        n = self.nodes[0]
+        self._convert_in(n, self.in_stage[slot][:n.shape[0]])
+
+    def release_stage(self, slot: int) -> None:
+        self.stage_free[slot].record(torch.cuda.current_stream(self.device))
 
     def _stage_in(self, n: Node, stage: torch.Tensor, batch: torch.Tensor) -> None:
         b = n.shape[0]
@@ -533,7 +552,10 @@ class NeuralNet:
             return
         self.need_update = need_update
         if need_update:
-            self.arena.refresh_hyper(epoch)
+            if self.hyper_prepared:          # the host half already ran (captured step)
+                self.arena.upload_hyper(self.hyper_slot)
+            else:
+                self.arena.refresh_hyper(epoch)
         if self.exchange is not None:
             self.exchange.begin_step()
         for i in range(n - 1, -1, -1):

@@ -23,7 +23,12 @@ class Metric:
         self.clear()
 
     def clear(self) -> None:
-        self.sum_metric = None  # device scalar (float64)
+        # the accumulator is a persistent device scalar updated in place: a training step captured into
+        # a CUDA graph keeps adding to the same address on replay
+        if getattr(self, "sum_metric", None) is not None:
+            self.sum_metric.zero_()
+        else:
+            self.sum_metric = None  # device scalar (float64), created by the first add_eval
         self.cnt_inst = 0
 
     def add_eval(self, pred: torch.Tensor, label: torch.Tensor) -> None:
@@ -31,7 +36,10 @@ class Metric:
         if pred.shape[0] == 0:
             return
         v = self.calc(pred.float(), label.to(pred.device).float()).double().sum()
-        self.sum_metric = v if self.sum_metric is None else self.sum_metric + v
+        if self.sum_metric is None or self.sum_metric.device != v.device:
+            self.sum_metric = v.clone()
+        else:
+            self.sum_metric.add_(v)
         self.cnt_inst += int(pred.shape[0])
 
     def calc(self, pred, label) -> torch.Tensor:

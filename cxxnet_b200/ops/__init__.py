@@ -85,6 +85,8 @@ def lib():
     _sig(L.cxn_refresh_shadow, [P, P, P, P, LL, P])
     _sig(L.cxn_counter_add, [P, ULL, P])
     L.cxn_launch_count.restype = c_ulonglong
+    L.cxn_launch_count_add.restype = c_ulonglong
+    L.cxn_launch_count_add.argtypes = [c_ulonglong]
     L.cxn_segment_bytes.restype = c_int
     L.cxn_update_chunk.restype = c_int
     _lib = L

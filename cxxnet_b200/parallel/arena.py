@@ -83,10 +83,13 @@ class ParamArena:
         for i, s in enumerate(self.segments):
             cs[s.start // self.chunk:(s.start + ops.round_up(s.n, self.chunk)) // self.chunk] = i
         self.chunk_seg = torch.from_numpy(cs).to(self.device)
-        self.seg_host = torch.zeros(max(len(self.segments), 1) * SEG_DTYPE.itemsize, dtype=torch.uint8)
+        self._hyper_raw = [None, None]       # bytes last written to each pinned staging buffer
+        self._hyper_copied = [None, None]    # events: the device has consumed the staging buffer
+        self._hyper_slot = 0
+        self.seg_host = [torch.zeros(max(len(self.segments), 1) * SEG_DTYPE.itemsize, dtype=torch.uint8) for _ in range(2)]
         if self.device.type == "cuda":
-            self.seg_host = self.seg_host.pin_memory()
-        self.seg_dev = torch.zeros_like(self.seg_host, device=self.device)
+            self.seg_host = [t.pin_memory() for t in self.seg_host]
+        self.seg_dev = torch.zeros_like(self.seg_host[0], device=self.device)
         self.refresh_hyper(0)
 
     # ------------------------------------------------------------------ views
@@ -109,9 +112,13 @@ class ParamArena:
         return a, b
 
     # ------------------------------------------------------------------ per-step hyper parameters
-    def refresh_hyper(self, epoch: int) -> None:
-        """Evaluate every segment's schedule for update number ``epoch`` and stage the table
-        (reference ``src/updater/param.h:76-94`` ScheduleEpoch)."""
+    def prepare_hyper(self, epoch: int, slot: int = 0) -> bool:
+        """Host half: evaluate every segment's schedule for update number ``epoch`` (reference
+        ``src/updater/param.h:76-94`` ScheduleEpoch) and, if the table differs from what pinned
+        staging buffer ``slot`` holds, rewrite that buffer.  Before rewriting, wait until the
+        device has consumed its previous contents (the H2D copy is asynchronous, and a captured
+        graph re-reads the same pinned address on every replay).  Two slots used alternately let
+        the host run one step ahead of the device.  Returns whether the buffer was rewritten."""
         arr = np.zeros(max(len(self.segments), 1), dtype=SEG_DTYPE)
         for i, s in enumerate(self.segments):
             p = s.param
@@ -124,8 +131,31 @@ class ParamArena:
                 fix2 = 1.0 - (1.0 - s.beta2) ** (epoch + 1)
                 arr[i]["adam_lr_t"] = p.base_lr * np.sqrt(fix2) / fix1
                 arr[i]["beta1"], arr[i]["beta2"] = s.beta1, s.beta2
-        self.seg_host.numpy()[:] = np.frombuffer(arr.tobytes(), dtype=np.uint8)
-        self.seg_dev.copy_(self.seg_host, non_blocking=True)
+        raw = arr.tobytes()
+        if raw == self._hyper_raw[slot]:
+            return False
+        if self._hyper_copied[slot] is not None:
+            self._hyper_copied[slot].synchronize()
+        self.seg_host[slot].numpy()[:] = np.frombuffer(raw, dtype=np.uint8)
+        self._hyper_raw[slot] = raw
+        return True
+
+    def upload_hyper(self, slot: int = 0) -> None:
+        """Device half (stream ordered, capturable): pinned table ``slot`` -> device table."""
+        self.seg_dev.copy_(self.seg_host[slot], non_blocking=True)
+        if not torch.cuda.is_current_stream_capturing():
+            self.mark_hyper_consumed(slot)
+
+    def mark_hyper_consumed(self, slot: int = 0) -> None:
+        """the pinned table ``slot`` may be rewritten once the stream reaches this point"""
+        if self._hyper_copied[slot] is None:
+            self._hyper_copied[slot] = torch.cuda.Event()
+        self._hyper_copied[slot].record()
+
+    def refresh_hyper(self, epoch: int) -> None:
+        self._hyper_slot ^= 1
+        self.prepare_hyper(epoch, self._hyper_slot)
+        self.upload_hyper(self._hyper_slot)
 
     # ------------------------------------------------------------------ kernels
     def update(self, chunk_begin: int = 0, chunk_end: Optional[int] = None) -> None:

@@ -66,6 +66,8 @@ class GradExchange:
         L.cxn_symm_broadcast.restype = I
         L.cxn_symm_allgather.argtypes = [P, I, I, LL, P, LL, LL, LL, P, LL, LL, LL, I, U, I, P, I, P]
         L.cxn_symm_allgather.restype = I
+        L.cxn_xchg_set_epoch_ptr.argtypes = [P]
+        L.cxn_xchg_set_epoch_ptr.restype = I
         if self.world > L.cxn_xchg_max_ranks():
             raise ValueError("too many ranks for the fused exchange")
         self.block: SymmetricBlock = net.symm_block
@@ -108,6 +110,11 @@ class GradExchange:
                 self.bucket_of_layer[li] = b
         self.stream = torch.cuda.Stream(device=self.device, priority=-1)
         self.ready = torch.cuda.Event()
+        # Per-step part of every kernel's sequence number: a device word bumped on the main stream at the
+        # start of each backward pass (begin_step).  The host part `self.seq` only moves outside steps, so
+        # a step captured into a CUDA graph replays with advancing barriers.
+        self.epoch = torch.zeros(1, dtype=torch.int64, device=self.device)
+        L.cxn_xchg_set_epoch_ptr(self.epoch.data_ptr())
         dist.barrier()
 
     # ------------------------------------------------------------------ K19
@@ -131,7 +138,9 @@ class GradExchange:
 
     # ------------------------------------------------------------------ K17
     def begin_step(self) -> None:
-        self.seq += 1
+        # every exchange kernel of the previous step has been waited for by this step's forward pass (or
+        # by the join at the end of a captured step), so nothing in flight reads the word while it changes
+        ops.check(ops.lib().cxn_counter_add(self.epoch.data_ptr(), 1, ops.stream()), "counter_add")
 
     def layer_done(self, layer_index: int) -> None:
         """called right after layer ``layer_index`` finished its backward on the main stream."""

@@ -28,6 +28,7 @@ import numpy as np
 import torch
 
 from . import model_io as mio
+from . import ops
 from .config import ConfigPairs
 from .executor import NeuralNet
 from .io.data import DataBatch, IIterator
@@ -75,6 +76,15 @@ class NetTrainer:
         self.rank, self.world_size = 0, 1
         self.step = 0
         self._stage = None
+        # cuda_graph = 1: after a few eager steps one training step (forward, metric, backward, gradient
+        # exchange, update) is captured into a CUDA graph per input staging slot and replayed; the host
+        # then only stages the batch and launches one graph per step
+        self.cuda_graph = 0
+        self.graph_warmup = 3
+        self._graphs = {}            # staging slot -> (torch.cuda.CUDAGraph, launches inside)
+        self._graph_rows = -1
+        self._graph_steps = 0
+        self._graph_labels: Optional[List[torch.Tensor]] = None
 
     # ------------------------------------------------------------------ configuration
     def set_param(self, name: str, val: str) -> None:
@@ -87,6 +97,7 @@ class NetTrainer:
         if name == "silent": self.silent = int(val)
         if name == "param_server": self.type_pserver = val
         if name == "backend": self.backend_override = val
+        if name == "cuda_graph": self.cuda_graph = int(val)
         if name.startswith("metric"):
             m = re.match(r"metric\[([^,]+),([^\]]+)\]", name)
             if m:
@@ -239,6 +250,9 @@ class NetTrainer:
         """one mini-batch: forward, backprop, (every ``update_period`` calls) weight update
         (reference ``nnet_impl-inl.hpp:141-185``)."""
         net = self.net
+        if self.cuda_graph and self._graph_applicable(batch):
+            self._update_graph(batch)
+            return
         need_update = (self.sample_counter + 1) % self.update_period == 0
         data = self._as_tensor(batch.data)
         label = self._as_tensor(batch.label)
@@ -255,6 +269,96 @@ class NetTrainer:
         if self.sample_counter >= self.update_period:
             self.sample_counter = 0
             self.epoch_counter += 1
+
+    # ------------------------------------------------------------------ captured training step
+    def _graph_applicable(self, batch: DataBatch) -> bool:
+        net = self.net
+        if net is None or net.backend != "b200" or self.update_period != 1 or batch.extra_data:
+            return False
+        begin, end = self._slice(batch.batch_size)
+        # only full-size slices are replayed (a smaller last batch takes the eager path)
+        return end - begin == net.max_batch
+
+    def _step_body(self, slot: int) -> None:
+        """the part of a training step that lives inside the graph"""
+        net = self.net
+        net.convert_staged(slot)
+        net.forward(True)
+        if self.eval_train != 0 and self.eval_req:
+            scores = [self._scores2d(net.copy_node_data(i)) for i in self.eval_req]
+            self.train_metric.add_eval(scores, net.label_info.fields, self.net_cfg.label_name_map)
+        net.backprop(False, True, self.epoch_counter)
+        if net.exchange is not None:
+            net.exchange.wait_all()          # join the exchange stream: the step is one unit
+
+    def _update_graph(self, batch: DataBatch) -> None:
+        net = self.net
+        data = self._as_tensor(batch.data)
+        label = self._as_tensor(batch.label)
+        begin, end = self._slice(batch.batch_size)
+        rows = end - begin
+        net.adjust_batch_size(rows)
+        # persistent label fields (the loss layers and the metric read these addresses)
+        if self._graph_labels is None:
+            self._graph_labels = [torch.zeros((rows, b - a), dtype=torch.float32, device=self.device)
+                                  for a, b in self.net_cfg.label_range]
+        for t, (a, b) in zip(self._graph_labels, self.net_cfg.label_range):
+            t.copy_(label[begin:end, a:b], non_blocking=True)
+        net.label_info.fields = self._graph_labels
+        net.accumulate_grads = False
+        slot = net.stage_input(data[begin:end])
+        # host half of the per-step hyper parameters (rewrites the pinned table only when it changed)
+        net.arena.prepare_hyper(self.epoch_counter, slot)
+        net.hyper_prepared, net.hyper_slot = True, slot
+        try:
+            entry = self._graphs.get(slot)
+            if entry is not None:
+                g, launches, cnt = entry
+                g.replay()
+                ops.lib().cxn_launch_count_add(launches)
+                for e in self.train_metric.evals:
+                    e.cnt_inst += cnt
+            elif self._graph_steps < self.graph_warmup:
+                self._step_body(slot)
+            else:
+                try:
+                    self._capture(slot, rows)
+                except Exception as exc:      # a layer that cannot be captured (host round trips): stay eager
+                    import warnings
+                    warnings.warn("cuda_graph: capture failed (%r), continuing without graphs" % (exc,))
+                    self.cuda_graph = 0
+                    self._graphs.clear()
+                    torch.cuda.synchronize(self.device)
+                    self._step_body(slot)
+        finally:
+            net.hyper_prepared = False
+        net.arena.mark_hyper_consumed(slot)
+        net.release_stage(slot)
+        self._graph_steps += 1
+        self.epoch_counter += 1
+
+    def _capture(self, slot: int, rows: int) -> None:
+        """capture one step for this staging slot; the capture itself does not execute, so the step is
+        replayed once right away"""
+        net = self.net
+        if net.exchange is not None:
+            net.exchange.wait_all()
+        torch.cuda.synchronize(self.device)
+        before = ops.launch_count()
+        cnt0 = [e.cnt_inst for e in self.train_metric.evals]
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._step_body(slot)
+        launches = ops.launch_count() - before
+        cnt = (self.train_metric.evals[0].cnt_inst - cnt0[0]) if self.train_metric.evals else 0
+        for e, c in zip(self.train_metric.evals, cnt0):
+            e.cnt_inst = c
+        self._graphs[slot] = (g, launches, cnt)
+        ops.lib().cxn_launch_count_add(-launches & 0xFFFFFFFFFFFFFFFF)   # the captured launches did not run
+        g.replay()
+        ops.lib().cxn_launch_count_add(launches)
+        for e in self.train_metric.evals:
+            e.cnt_inst += cnt
 
     @staticmethod
     def _scores2d(t: torch.Tensor) -> torch.Tensor:
@@ -343,7 +447,11 @@ class NetTrainer:
             v = torch.stack([s.to(self.device).double(), torch.tensor(float(e.cnt_inst), dtype=torch.float64,
                                                                        device=self.device)])
             dist.all_reduce(v)
-            e.sum_metric, e.cnt_inst = v[0], int(v[1].item())
+            if e.sum_metric is not None:
+                e.sum_metric.copy_(v[0])          # in place: a captured training step accumulates into this tensor
+            else:
+                e.sum_metric = v[0].clone()
+            e.cnt_inst = int(v[1].item())
 
     # ------------------------------------------------------------------ weights
     def set_weight(self, weight, layer_name: str, tag: str) -> None:

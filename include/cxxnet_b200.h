@@ -159,6 +159,9 @@ int cxn_symm_allgather(const unsigned long long* peers, int nranks, int rank, lo
                        long long dst_off0, long long slot_bytes0, long long valid_bytes0, const void* src1,
                        long long dst_off1, long long slot_bytes1, long long valid_bytes1, int npieces, unsigned seq,
                        int slot, unsigned* counter, int grid, cudaStream_t stream);
+/* optional device word added to the `seq` argument of every exchange kernel at kernel start (so that a
+ * captured CUDA graph advances the flag barriers on replay); NULL = off.  No reference counterpart. */
+int cxn_xchg_set_epoch_ptr(const void* dev_word);
 int cxn_xchg_flag_bytes(void);
 int cxn_xchg_max_ranks(void);
 int cxn_xchg_max_slots(void);
@@ -170,6 +173,7 @@ int cxn_ipc_free(unsigned long long ptr);
 
 /* number of kernel launches issued by this library in this process */
 unsigned long long cxn_launch_count(void);
+unsigned long long cxn_launch_count_add(unsigned long long n);   /* account for kernels replayed from a CUDA graph */
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,77 @@
+"""`cuda_graph = 1`: a training step captured into a CUDA graph must train exactly like the eager
+step (same kernels, same order), keep the train metric's device accumulator and host count going,
+and fall back to the eager path for a short last batch."""
+import pytest
+import torch
+
+from util import copy_weights, make_batch, make_trainer, rel_err
+
+pytestmark = pytest.mark.gpu
+
+CONF = """
+netconfig=start
+layer[+1] = conv:cv1
+  kernel_size = 5
+  stride = 2
+  nchannel = 16
+layer[+1] = relu
+layer[+1] = max_pooling
+  kernel_size = 3
+  stride = 2
+layer[+1] = conv:cv2
+  kernel_size = 3
+  pad = 1
+  nchannel = 64
+layer[+1] = relu
+layer[+1] = conv:cv3
+  kernel_size = 3
+  pad = 1
+  nchannel = 32
+layer[+1] = flatten
+layer[+0] = dropout
+  threshold = 0.5
+layer[+1] = fullc:fc1
+  nhidden = 10
+layer[+0] = softmax
+netconfig=end
+batch_size = 16
+input_shape = 3,33,33
+eta = 0.05
+momentum = 0.9
+wd = 0.0005
+random_type = xavier
+metric = error
+eval_train = 1
+dev = gpu:0
+"""
+
+
+def test_captured_step_trains_like_eager_step():
+    eager = make_trainer(CONF)
+    graph = make_trainer(CONF, cuda_graph=1)
+    copy_weights(eager, graph)
+    batches = [make_batch((16, 3, 33, 33), seed=s, pin=True) for s in range(3)]
+    steps = 12
+    for i in range(steps):
+        b = batches[i % 3]
+        eager.update(b)
+        graph.update(b)
+    torch.cuda.synchronize()
+    assert len(graph._graphs) == 2, "one captured graph per input staging slot"
+    for i, c in enumerate(eager.net.connections):
+        for tag, _, _ in c.layer.weights():
+            we, _ = eager.net.get_weight(i, tag)
+            wg, _ = graph.net.get_weight(i, tag)
+            # the weight-gradient kernels reduce with atomics, so the two runs agree to rounding only
+            assert rel_err(we, wg) < 2e-2, "layer %d %s diverged" % (i, tag)
+    me, mg = eager.train_metric.evals[0], graph.train_metric.evals[0]
+    assert me.cnt_inst == mg.cnt_inst == steps * 16
+    assert abs(me.get() - mg.get()) <= 0.1
+    # a short last batch takes the eager path and the graphs stay valid afterwards
+    short = make_batch((16, 3, 33, 33), seed=9)
+    short.batch_size = 11
+    graph.update(short)
+    graph.update(batches[0])
+    torch.cuda.synchronize()
+    assert mg.cnt_inst == steps * 16 + 11 + 16
+    assert graph.epoch_counter == steps + 2
