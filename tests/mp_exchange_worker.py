@@ -15,6 +15,7 @@ _lenet = lenet_conf
 def lenet_conf(**kw):   # dropout off: masks are a function of the element index, i.e. of the batch split
     return _lenet(**kw).replace("threshold = 0.5", "threshold = 0.0")
 MODE = sys.argv[2] if len(sys.argv) > 2 else "lenet"
+GRAPH = len(sys.argv) > 3 and sys.argv[3] == "graph"     # multi-GPU trainer replays captured steps
 if MODE == "gather":
     # fully connected net whose first layer can be row-sharded (fullc_gather = 1): nin = 1024
     def lenet_conf(batch_size=64, dev="gpu", extra=""):
@@ -43,7 +44,8 @@ metric = error
     SHAPE = (64, 1, 1, 1024)
 else:
     SHAPE = (64, 1, 28, 28)
-tr = make_trainer(lenet_conf(batch_size=64, dev="gpu:" + ",".join(str(i) for i in range(world)), extra=extra))
+tr = make_trainer(lenet_conf(batch_size=64, dev="gpu:" + ",".join(str(i) for i in range(world)),
+                             extra=extra + ("cuda_graph = 1\n" if GRAPH else "")))
 if MODE == "gather":
     assert len(tr.net.fc_shards) == 1, "first layer should be sharded"
 assert tr.net.exchange is not None and tr.world_size == world
@@ -75,11 +77,13 @@ for i, c in enumerate(tr.net.connections):
 # clear accumulated gradients again
 tr.net.arena.g.zero_(); single.net.arena.g.zero_()
 torch.cuda.synchronize(); dist.barrier()
-for s in range(4):
+for s in range(9 if GRAPH else 4):
     b = make_batch(SHAPE, seed=s)
     tr.update(b)
     single.update(b)
 torch.cuda.synchronize()
+if GRAPH:
+    assert len(tr._graphs) == 2, "expected one captured graph per staging slot, got %d" % len(tr._graphs)
 assert tr.net.exchange.check_replicas() == 0.0, "replicas diverged"
 worst = 0.0
 for name in ("cv1", "fc1", "fc2"):
