@@ -28,17 +28,17 @@ _NATIVE = {
     nc.kSoftmax: native.SoftmaxLayer,
     nc.kL2Loss: native.L2LossLayer,
     nc.kMultiLogistic: native.MultiLogisticLayer,
+    nc.kBias: native.BiasLayer,
+    nc.kConcat: native.ConcatLayer,
+    nc.kChConcat: native.ChConcatLayer,
+    nc.kSplit: native.SplitLayer,
+    nc.kPRelu: native.PReluLayer,
+    nc.kBatchNorm: native.BatchNormLayer,
 }
 
 _REF_ONLY = {
-    nc.kBias: zoo.BiasLayer,
-    nc.kConcat: zoo.ConcatLayer,
-    nc.kChConcat: zoo.ChConcatLayer,
-    nc.kSplit: zoo.SplitLayer,
     nc.kInsanity: zoo.InsanityLayer,
     nc.kInsanityPooling: zoo.InsanityPoolingLayer,
-    nc.kPRelu: zoo.PReluLayer,
-    nc.kBatchNorm: zoo.BatchNormLayer,
     nc.kFixConnect: zoo.FixConnectLayer,
 }
 

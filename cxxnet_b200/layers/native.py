@@ -490,3 +490,160 @@ class L2LossLayer(_NativeLoss, zoo.L2LossLayer):
 class MultiLogisticLayer(_NativeLoss, zoo.MultiLogisticLayer):
     loss_kind = 1
     transform = "sigmoid"
+
+
+# ----------------------------------------------------------------------------- bias / prelu / batch norm
+def _mat_view(node, m):
+    """(rows, cols, ld) of a node's activation or gradient matrix: channels are the columns"""
+    return _rows(node), m.cols, m.ld
+
+
+class BiasLayer(zoo.BiasLayer):
+    """self-loop bias on a matrix node; gradient = column sums (csrc/kernels/misc_layers.cu)."""
+    has_b200 = True
+
+    def __init__(self):
+        super().__init__()
+        self.bind = {}
+
+    def b200_forward(self, ex, is_train):
+        x = self.nodes_in[0]
+        rows, cols, ld = _mat_view(x, x.act)
+        ops.check(ops.lib().cxn_bias_add(x.act.ptr, x.act.ptr, rows, cols, ld, self.bind["bias"].w.data_ptr(), ops.stream()),
+                  "bias_add")
+
+    def b200_backprop(self, ex, prop_grad):
+        x = self.nodes_in[0]
+        rows, cols, ld = _mat_view(x, x.grad)
+        ops.check(ops.lib().cxn_colsum_bf16(x.grad.ptr, rows, cols, ld, self.bind["bias"].g.data_ptr(),
+                                             1 if ex.accumulate_grads else 0, ops.stream()), "colsum")
+
+
+class PReluLayer(zoo.PReluLayer):
+    """per-channel learned slope; the training-time slope noise is a Philox stream regenerated in backward"""
+    has_b200 = True
+
+    def __init__(self):
+        super().__init__()
+        self.bind = {}
+
+    def _seed(self, ex):
+        return (ex.seed * 1000003 + self.layer_index * 7919 + 4242) & 0xFFFFFFFFFFFFFFFF
+
+    def b200_forward(self, ex, is_train):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        rows, cols, ld = _mat_view(x, x.act)
+        self._noise = float(self.random) if is_train else 0.0
+        ops.check(ops.lib().cxn_prelu_fwd(x.act.ptr, y.act.ptr, rows, cols, ld, y.act.ld, self.bind["bias"].w.data_ptr(),
+                                          self._noise, self._seed(ex), ex.step_counter.data_ptr(), ops.stream()), "prelu_fwd")
+
+    def b200_backprop(self, ex, prop_grad):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        rows, cols, ld = _mat_view(x, x.act)
+        b = self.bind["bias"]
+        if not ex.accumulate_grads:
+            ops.check(ops.lib().cxn_fill_f32(b.g.data_ptr(), b.g.numel(), 0.0, ops.stream()), "fill")
+        ops.check(ops.lib().cxn_prelu_bwd(x.act.ptr, y.grad.ptr, x.grad.ptr if prop_grad else None, rows, cols, ld, y.grad.ld,
+                                          b.w.data_ptr(), b.g.data_ptr(), getattr(self, "_noise", 0.0), self._seed(ex),
+                                          ex.step_counter.data_ptr(), ops.stream()), "prelu_bwd")
+
+
+class BatchNormLayer(zoo.BatchNormLayer):
+    """mini-batch statistics in training and at test time (as the reference); one column reduction per
+    pass plus element-wise kernels with per-channel coefficients.  Unlike the reference the input node
+    keeps its value (the reference overwrites it with the normalised activations); xhat lives in a
+    private buffer."""
+    has_b200 = True
+
+    def __init__(self):
+        super().__init__()
+        self.bind = {}
+
+    def b200_setup(self, ex):
+        x = self.nodes_in[0]
+        C = x.act.cols
+        self.xhat = DevMat(x.act.t.shape[0], C, x.act.ld, device=ex.device)
+        self.scratch = torch.zeros(5 * C, dtype=torch.float32, device=ex.device)
+        self.mean = torch.zeros(C, dtype=torch.float32, device=ex.device)
+        self.istd = torch.zeros(C, dtype=torch.float32, device=ex.device)
+
+    def b200_forward(self, ex, is_train):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        rows, C, ld = _mat_view(x, x.act)
+        ops.check(ops.lib().cxn_batchnorm_fwd(x.act.ptr, y.act.ptr, self.xhat.ptr if is_train else None, rows, C, ld, y.act.ld,
+                                              self.xhat.ld, self.bind["wmat"].w.data_ptr(), self.bind["bias"].w.data_ptr(),
+                                              float(self.eps), self.scratch.data_ptr(), self.mean.data_ptr(),
+                                              self.istd.data_ptr(), ops.stream()), "batchnorm_fwd")
+
+    def b200_backprop(self, ex, prop_grad):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        rows, C, ld = _mat_view(x, x.act)
+        gs, gb = self.bind["wmat"].g, self.bind["bias"].g
+        if not ex.accumulate_grads:
+            ops.check(ops.lib().cxn_fill_f32(gs.data_ptr(), C, 0.0, ops.stream()), "fill")
+            ops.check(ops.lib().cxn_fill_f32(gb.data_ptr(), C, 0.0, ops.stream()), "fill")
+        ops.check(ops.lib().cxn_batchnorm_bwd(y.grad.ptr, self.xhat.ptr, x.grad.ptr, rows, C, y.grad.ld, self.xhat.ld, x.grad.ld,
+                                              self.bind["wmat"].w.data_ptr(), self.istd.data_ptr(), gs.data_ptr(),
+                                              gb.data_ptr(), self.scratch.data_ptr(), 1 if prop_grad else 0, ops.stream()),
+                  "batchnorm_bwd")
+
+
+# ----------------------------------------------------------------------------- split / concat
+class SplitLayer(zoo.SplitLayer):
+    """1 -> n copies forward, sum of the n gradients backward (strided bf16 copies)"""
+    has_b200 = True
+
+    def b200_forward(self, ex, is_train):
+        x = self.nodes_in[0]
+        rows, cols, ld = _mat_view(x, x.act)
+        for n in self.nodes_out:
+            ops.check(ops.lib().cxn_copy2d(x.act.ptr, ld, n.act.ptr, n.act.ld, rows, cols, 0, 0, ops.stream()), "copy2d")
+
+    def b200_backprop(self, ex, prop_grad):
+        if not prop_grad:
+            return
+        x = self.nodes_in[0]
+        rows, cols, ld = _mat_view(x, x.grad)
+        for k, n in enumerate(self.nodes_out):
+            ops.check(ops.lib().cxn_copy2d(n.grad.ptr, n.grad.ld, x.grad.ptr, ld, rows, cols, 0, 1 if k else 0, ops.stream()),
+                      "copy2d")
+
+
+class _NativeConcat:
+    """concatenation along the innermost stored dimension: the columns of matrix nodes (`concat`) or
+    the channels of NHWC nodes (`ch_concat`) - in both cases column ranges of the [rows][C] matrices"""
+    has_b200 = True
+
+    def b200_supported(self):
+        mats = all(n.is_mat for n in self.nodes_in)
+        return mats if self.dim == 3 else not any(n.is_mat for n in self.nodes_in)
+
+    def _copy(self, grad: bool):
+        y = self.nodes_out[0]
+        ym = y.grad if grad else y.act
+        rows = _rows(y)
+        off = 0
+        for n in self.nodes_in:
+            m = n.grad if grad else n.act
+            yptr = ym.ptr + off * 2
+            if grad:
+                ops.check(ops.lib().cxn_copy2d(yptr, ym.ld, m.ptr, m.ld, rows, m.cols, 0, 0, ops.stream()), "copy2d")
+            else:
+                ops.check(ops.lib().cxn_copy2d(m.ptr, m.ld, yptr, ym.ld, rows, m.cols, 0, 0, ops.stream()), "copy2d")
+            off += m.cols
+
+    def b200_forward(self, ex, is_train):
+        self._copy(False)
+
+    def b200_backprop(self, ex, prop_grad):
+        if prop_grad:
+            self._copy(True)
+
+
+class ConcatLayer(_NativeConcat, zoo.ConcatLayer):
+    pass
+
+
+class ChConcatLayer(_NativeConcat, zoo.ChConcatLayer):
+    pass
+

@@ -73,6 +73,11 @@ def lib():
     _sig(L.cxn_nchw_f32_to_nhwc4_pitched, [P, P, I, I, I, I, I, P])
     _sig(L.cxn_conv_flip_weights, [P, P, I, I, I, I, I, I, I, P])
     _sig(L.cxn_conv_tune, [I, I])
+    _sig(L.cxn_bias_add, [P, P, LL, I, LL, P, P])
+    _sig(L.cxn_batchnorm_fwd, [P, P, P, LL, I, LL, LL, LL, P, P, F, P, P, P, P])
+    _sig(L.cxn_batchnorm_bwd, [P, P, P, LL, I, LL, LL, LL, P, P, P, P, P, I, P])
+    _sig(L.cxn_prelu_fwd, [P, P, LL, I, LL, LL, P, F, ULL, P, P])
+    _sig(L.cxn_prelu_bwd, [P, P, P, LL, I, LL, LL, P, P, F, ULL, P, P])
     _sig(L.cxn_conv_set_prof, [P])
     _sig(L.cxn_pool_fwd, [P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(L.cxn_pool_bwd, [P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])

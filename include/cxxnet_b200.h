@@ -97,6 +97,23 @@ int cxn_colsum_bf16(const void* x, long long rows, int cols, long long ld, float
 
 /* ---- K8/K9 pooling: mode 0 max, 1 sum, 2 avg; ceil-style output, clipped windows, avg / k*k,
  * max-unpool to every tie; relu=1 is relu_max_pooling.  src/layer/pooling_layer-inl.hpp:45-106. */
+/* ---- bias / prelu / batch_norm (csrc/kernels/misc_layers.cu); matrices are bf16 [rows][ld], channels = columns.
+ * reference: src/layer/bias_layer-inl.hpp, prelu_layer-inl.hpp, batch_norm_layer-inl.hpp */
+int cxn_bias_add(const void* x, void* y, long long rows, int cols, long long ld, const float* bias, cudaStream_t stream);
+/* scratch: 2*C floats; mean / istd: C floats each, kept for backward; xhat may be NULL (evaluation) */
+int cxn_batchnorm_fwd(const void* x, void* y, void* xhat, long long rows, int C, long long ldx, long long ldy,
+                      long long ldxhat, const float* slope, const float* bias, float eps, float* scratch, float* mean,
+                      float* istd, cudaStream_t stream);
+/* gslope += sum dy*xhat, gbias += sum dy, dx = slope*istd*(dy - mean(dy) - xhat*mean(dy*xhat)); scratch: 5*C floats */
+int cxn_batchnorm_bwd(const void* dy, const void* xhat, void* dx, long long rows, int C, long long lddy, long long ldxhat,
+                      long long lddx, const float* slope, const float* istd, float* gslope, float* gbias, float* scratch,
+                      int prop_grad, cudaStream_t stream);
+/* y = x > 0 ? x : x * clamp(slope[c] * (1 + u*2*noise - noise), 0, 1), u from Philox(seed, *counter) */
+int cxn_prelu_fwd(const void* x, void* y, long long rows, int cols, long long ldx, long long ldy, const float* slope,
+                  float noise, unsigned long long seed, const unsigned long long* counter, cudaStream_t stream);
+int cxn_prelu_bwd(const void* x, const void* dy, void* dx, long long rows, int cols, long long ldx, long long ldg,
+                  const float* slope, float* gslope, float noise, unsigned long long seed,
+                  const unsigned long long* counter, cudaStream_t stream);
 int cxn_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int ky, int kx, int stride, int OH, int OW,
                  int mode, int relu, cudaStream_t stream);
 int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, int ky, int kx,

@@ -160,7 +160,7 @@ layer[+0] = softmax
     compare_backends(_conf(body, 5, "2,19,19"), make_batch((5, 2, 19, 19), nclass=4), tol_grad=0.15)
 
 
-def test_bridged_layers_bn_prelu_concat_split():
+def test_bn_prelu_split_ch_concat_on_images():
     body = """
 layer[0->1] = conv:cv1
   kernel_size = 3
@@ -184,6 +184,30 @@ layer[10->10] = softmax
 """
     compare_backends(_conf(body, 4, "3,9,9") + "eps = 1e-5\n", make_batch((4, 3, 9, 9), nclass=6), tol_grad=8e-2,
                      skip=("grad[0:bias]",))  # analytically zero: batch_norm removes the conv bias
+
+
+def test_bias_bn_prelu_split_concat_on_matrices():
+    body = """
+layer[0->1] = fullc:fc1
+  nhidden = 32
+  no_bias = 1
+layer[1->1] = bias:b1
+  init_bias = 0.3
+layer[1->2] = batch_norm:bn1
+layer[2->3] = prelu:pr1
+layer[3->4,5] = split
+layer[4->6] = fullc:fa
+  nhidden = 16
+layer[5->7] = fullc:fb
+  nhidden = 24
+layer[6,7->8] = concat
+layer[8->9] = fullc:fc2
+  nhidden = 6
+layer[9->9] = softmax
+"""
+    errs, ref, b2 = compare_backends(_conf(body, 24, "1,1,40") + "eps = 1e-5\n", make_batch((24, 1, 1, 40), nclass=6),
+                                     tol_grad=8e-2, skip=("grad[1:bias]",), return_trainers=True)  # bn removes the bias
+    assert all(c.native for c in b2.net.connections), "every layer of this net has a native implementation"
 
 
 def test_update_matches_reference_sgd_step():
