@@ -66,6 +66,10 @@ struct Params {
   // fprop: whole filter panel resident in shared memory (single group, single n-tile, small K*N)
   int b_resident;
   int stages;      // depth of the shared-memory ring actually used (<= Cfg::kMaxStages)
+  int ring_bytes;  // shared memory before the barriers: stages * stage bytes, or (resident filter) A ring + panel
+  // optional strided view for the im2col tensor map (elements; 0 = the dense NHWC tensor): channel
+  // extent per position, row stride, image stride.  Cs stays the stride between positions.
+  long long view_cdim, view_row, view_img;
   long long* prof; // [grid][16] cycle counters of the warp roles (builds with -DCXN_IGEMM_PROF only)
   int dbg;         // timing experiments only (results are garbage): 2 skip the TMA loads, 4 skip the MMAs
 };
@@ -112,20 +116,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const int nst = p.stages;
-  const uint32_t bar_base = smem_base + nst * C::kStageBytes;
+  const uint32_t bar_base = smem_base + (uint32_t)p.ring_bytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (nst + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * nst + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * nst + kAccStages + a); };
   const uint32_t bres_bar = bar_base + 8u * (2 * nst + 2 * kAccStages);
   volatile uint32_t* tmem_ptr_smem =
-      reinterpret_cast<volatile uint32_t*>(smem_gen + nst * C::kStageBytes + 8 * (2 * nst + 2 * kAccStages + 1));
+      reinterpret_cast<volatile uint32_t*>(smem_gen + p.ring_bytes + 8 * (2 * nst + 2 * kAccStages + 1));
   // smem addressing: ring of {A,B} stages, or (resident filter) ring of A stages followed by the panel
   const bool bres = !WGRAD && p.b_resident;
   const uint32_t a_stride = bres ? (uint32_t)C::kABytes : (uint32_t)C::kStageBytes;
   const uint32_t bres_base = smem_base + nst * C::kABytes;
   const uint32_t bres_kb_bytes = (uint32_t)p.bn * BK * 2;
-  GatherEntry* table = reinterpret_cast<GatherEntry*>(smem_gen + nst * C::kStageBytes + 256);
+  GatherEntry* table = reinterpret_cast<GatherEntry*>(smem_gen + p.ring_bytes + 256);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -687,6 +691,7 @@ static bool atma_ok(const Params& p) {
   if ((p.W + 2 * p.pad_x - p.KW) / p.stride_x + 1 != p.OW || (p.H + 2 * p.pad_y - p.KH) / p.stride_y + 1 != p.OH) return false;
   if (p.W + 2 * p.pad_x < p.KW || p.H + 2 * p.pad_y < p.KH) return false;
   if ((reinterpret_cast<uintptr_t>(p.src) & 15) || (p.Cs % 8)) return false;
+  if (p.view_cdim && ((p.view_row % 8) || (p.view_img % 8) || p.view_cdim < p.G * p.Cg)) return false;
   return get_encode_im2col() != nullptr;
 }
 
@@ -696,6 +701,12 @@ static int encode_im2col(CUtensorMap* out, const Params& p, int pixels) {
   if (!enc) return -2;
   cuuint64_t gdim[4] = {(cuuint64_t)p.Cs, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
   cuuint64_t gstr[3] = {(cuuint64_t)p.Cs * 2, (cuuint64_t)p.W * p.Cs * 2, (cuuint64_t)p.H * p.W * p.Cs * 2};
+  if (p.view_cdim) {
+    // positions may overlap in memory (channel extent larger than the stride between positions)
+    gdim[0] = (cuuint64_t)p.view_cdim;
+    gstr[1] = (cuuint64_t)p.view_row * 2;
+    gstr[2] = (cuuint64_t)p.view_img * 2;
+  }
   // bounding box of the tap-(0,0) pixel: [-pad, extent + pad - (K-1))
   int lower[2] = {-p.pad_x, -p.pad_y};
   int upper[2] = {p.pad_x - (p.KW - 1), p.pad_y - (p.KH - 1)};
@@ -714,7 +725,9 @@ template <int BNMAX, bool WGRAD, int GRAN, int MH, bool ATMA>
 static int launch_g(const CUtensorMap& tm, const CUtensorMap& tmp, const Params& p, int grid, cudaStream_t st) {
   using C = Cfg<BNMAX, MH>;
   if (p.stages < 2 || p.stages > C::kMaxStages) return -20;
-  const int smem = C::smem_bytes(p.stages);
+  if (p.ring_bytes < p.stages * (p.b_resident ? C::kABytes : C::kStageBytes) || (p.ring_bytes & 1023)) return -22;
+  const int smem = p.ring_bytes + C::kFixedBytes;
+  if (smem > 232448) return -23;
   static int max_set = 0;
   if (smem > max_set) {
     cudaError_t e = cudaFuncSetAttribute(conv_igemm_kernel<BNMAX, WGRAD, GRAN, MH, ATMA>,
@@ -765,11 +778,13 @@ using namespace cxn::igemm;
 //        gran 4: single group, Cg = Cs = 4 = RGB padded to 4)
 //   w    bf16 [G][Ng][ldw >= KH*KW*Cg] with the reduction ordered (kh, kw, c)
 //   y    NHWC bf16 [N*OH*OW][ldy], group g writes columns [g*Ng, (g+1)*Ng)
-CXN_API int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
+static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
                            long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
-                           void* y, long long ldy, const float* bias, int relu, cudaStream_t st) {
+                           void* y, long long ldy, const float* bias, int relu, long long view_cdim, long long view_row,
+                           long long view_img, cudaStream_t st) {
   Params p;
   memset(&p, 0, sizeof(p));
+  p.view_cdim = view_cdim; p.view_row = view_row; p.view_img = view_img;
   p.src = (const bf16*)src; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
   p.stride_y = stride & 0xFFFF; p.stride_x = (stride >> 16) ? (stride >> 16) : p.stride_y; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
   p.gran = gran; p.Ng = Ng; p.D = y; p.ldd = ldy; p.strideD = Ng; p.bias = bias; p.relu = relu;
@@ -800,21 +815,40 @@ CXN_API int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg,
   if (rc) return rc;
   const long long tiles = ceil_div_ll(rows, mh * BM) * ceil_div(Ng, p.bn) * G;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
-  // small single-group filters stay resident in shared memory for the whole (persistent) kernel
-  {
-    const long long panel = (long long)ceil_div(p.Kg, BK) * p.bn * BK * 2;
-    const long long ring_b = (long long)p.stages * bnmax * BK * 2;           // smem the B slots of the ring would use
-    p.b_resident = (G == 1 && Ng <= p.bn && panel <= ring_b && tiles > 2LL * grid) ? 1 : 0;
+  // Small single-group filters stay resident in shared memory for the whole (persistent) kernel: the
+  // ring then holds only the patch operand.  Prefer that over row-paired tiles when it only fits with
+  // 128-row tiles - no filter traffic at all beats half the filter traffic.
+  p.b_resident = 0;
+  p.ring_bytes = p.stages * stage_bytes;
+  if (G == 1 && Ng <= p.bn && tiles > 2LL * grid) {
+    const long long panel = ((long long)ceil_div(p.Kg, BK) * p.bn * BK * 2 + 1023) & ~1023LL;
+    const long long budget = 232448 - (1024 + 256 + kMaxGranules * 8);
+    for (int try_mh = mh; try_mh >= 1 && !p.b_resident; --try_mh) {
+      if (g_tune_mh && try_mh != mh) break;
+      const long long a_bytes = (long long)try_mh * BM * BK * 2;
+      int st_fit = (int)((budget - panel) / a_bytes);
+      if (st_fit > 6) st_fit = 6;
+      if (g_tune_stages && st_fit > g_tune_stages) st_fit = g_tune_stages;
+      if (panel < budget && st_fit >= 3) {
+        mh = try_mh;
+        p.stages = st_fit;
+        p.b_resident = 1;
+        p.ring_bytes = (int)(st_fit * a_bytes + panel);
+      }
+    }
   }
+  const long long tiles_final = ceil_div_ll(rows, mh * BM) * ceil_div(Ng, p.bn) * G;
+  const int grid_final = (int)(tiles_final < num_sms() ? tiles_final : num_sms());
   bool atma = atma_ok(p);
-  if (g_tune_atma >= 0) atma = atma && g_tune_atma;
+  if (g_tune_atma >= 0 && !p.view_cdim) atma = atma && g_tune_atma;
+  if (p.view_cdim && !atma) return -17;    // a strided view only exists as a tensor map
   CUtensorMap tmp = tm;
   if (atma) {
     rc = encode_im2col(&tmp, p, mh * BM);
     if (rc) return rc;
   }
-  if (mh == 2) return bnmax == 256 ? launch<256, false, 2>(tm, tmp, atma, p, grid, st) : launch<128, false, 2>(tm, tmp, atma, p, grid, st);
-  return bnmax == 256 ? launch<256, false, 1>(tm, tmp, atma, p, grid, st) : launch<128, false, 1>(tm, tmp, atma, p, grid, st);
+  if (mh == 2) return bnmax == 256 ? launch<256, false, 2>(tm, tmp, atma, p, grid_final, st) : launch<128, false, 2>(tm, tmp, atma, p, grid_final, st);
+  return bnmax == 256 ? launch<256, false, 1>(tm, tmp, atma, p, grid_final, st) : launch<128, false, 1>(tm, tmp, atma, p, grid_final, st);
 }
 
 // Tuning / experiment knobs; value 0 (or -1 for the switches) restores the automatic choice.
@@ -842,12 +876,13 @@ CXN_API int cxn_conv_tune(int key, int value) {
 }
 
 // Weight gradient: dw[g][j][(kh,kw,c)] += sum_pixels dy[pixel][g*Ng + j] * patch(pixel)[(kh,kw,c)]  (fp32, atomics)
-CXN_API int cxn_conv_wgrad_masked(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
-                                  long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
-                                  float* dw, long long lddw, int splits, int mask_period, int mask_valid,
-                                  cudaStream_t st) {
+static int conv_wgrad_impl(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
+                           long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                           float* dw, long long lddw, int splits, int mask_period, int mask_valid, long long view_cdim,
+                           long long view_row, long long view_img, cudaStream_t st) {
   Params p;
   memset(&p, 0, sizeof(p));
+  p.view_cdim = view_cdim; p.view_row = view_row; p.view_img = view_img;
   if (mask_period && ((mask_period | mask_valid) & 3)) return -16;
   p.mask_period = mask_period; p.mask_valid = mask_valid;
   p.src = (const bf16*)src; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
@@ -880,16 +915,53 @@ CXN_API int cxn_conv_wgrad_masked(const void* src, int N, int H, int W, int Cs, 
   const long long tiles = base_tiles * p.splits;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   p.stages = g_tune_stages ? g_tune_stages : 4;
+  p.ring_bytes = p.stages * (BM + 256) * BK * 2;
   p.dbg = g_tune_dbg;
   p.prof = g_prof;
   bool atma = atma_ok(p);
-  if (g_tune_atma >= 0) atma = atma && g_tune_atma;
+  if (g_tune_atma >= 0 && !p.view_cdim) atma = atma && g_tune_atma;
+  if (p.view_cdim && !atma) return -17;
   CUtensorMap tmp = tm;
   if (atma) {
     rc = encode_im2col(&tmp, p, BK);
     if (rc) return rc;
   }
   return launch<256, true, 1>(tm, tmp, atma, p, grid, st);
+}
+
+// ---- public entry points
+CXN_API int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
+                           long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                           void* y, long long ldy, const float* bias, int relu, cudaStream_t st) {
+  return conv_fprop_impl(src, N, H, W, Cs, Cg, G, gran, w, ldw, Ng, KH, KW, stride, pad_y, pad_x, OH, OW, y, ldy, bias, relu,
+                         0, 0, 0, st);
+}
+// The same over a strided view of the input: position (n, h, w) starts at src + n*img_stride + h*row_stride + w*Cs and
+// exposes `cdim` >= G*Cg contiguous elements (positions may overlap in memory).  Only the im2col-TMA route can read
+// such a view (Cg % 64 == 0 etc., else -17).  Used by the first layer: a filter row of a 4-channel-pitch image is
+// one contiguous run, so "16 pixels x 4 channels" is a 64-channel position every `stride` pixels.
+CXN_API int cxn_conv_fprop_view(const void* src, int N, int H, int W, int Cs, int Cg, int G, const void* w, long long ldw,
+                                int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW, void* y,
+                                long long ldy, const float* bias, int relu, long long cdim, long long row_stride,
+                                long long img_stride, cudaStream_t st) {
+  if (cdim <= 0) return -18;
+  return conv_fprop_impl(src, N, H, W, Cs, Cg, G, 8, w, ldw, Ng, KH, KW, stride, pad_y, pad_x, OH, OW, y, ldy, bias, relu,
+                         cdim, row_stride, img_stride, st);
+}
+CXN_API int cxn_conv_wgrad_masked(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
+                                  long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                                  float* dw, long long lddw, int splits, int mask_period, int mask_valid,
+                                  cudaStream_t st) {
+  return conv_wgrad_impl(src, N, H, W, Cs, Cg, G, gran, dy, lddy, Ng, KH, KW, stride, pad_y, pad_x, OH, OW, dw, lddw, splits,
+                         mask_period, mask_valid, 0, 0, 0, st);
+}
+CXN_API int cxn_conv_wgrad_view(const void* src, int N, int H, int W, int Cs, int Cg, int G, const void* dy, long long lddy,
+                                int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW, float* dw,
+                                long long lddw, int splits, int mask_period, int mask_valid, long long cdim,
+                                long long row_stride, long long img_stride, cudaStream_t st) {
+  if (cdim <= 0) return -18;
+  return conv_wgrad_impl(src, N, H, W, Cs, Cg, G, 8, dy, lddy, Ng, KH, KW, stride, pad_y, pad_x, OH, OW, dw, lddw, splits,
+                         mask_period, mask_valid, cdim, row_stride, img_stride, st);
 }
 
 CXN_API int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in,

@@ -233,6 +233,8 @@ class NeuralNet:
             b, ch, h, w = n.shape
             n.shape[0] = self.max_batch
             rows = self.max_batch if n.is_mat else self.max_batch * h * (n.wpitch or w)
+            if n.wpitch:
+                rows += 64     # zeroed slack: the last span of the last image row reads a few pixels past the image
             cols = w if n.is_mat else ch
             ld = ops.round_up(cols, 8) if n.is_mat else pitch.get(n.index, cols)
             n.act = ops.DevMat(rows, cols, ld, device=self.device)

@@ -114,6 +114,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         self.wflip = None
         self.cin_pad = 0        # 4 when a <=4-channel input is stored with a channel pitch of 4
         self.pair = False       # cin_pad input read as [H][Wp/2] super-pixels of 8 channels (two pixels each)
+        self.span = False       # cin_pad input read through im2col TMA as overlapping 16-pixel (64-channel) positions
         self.igemm_fwd = False
         self.igemm_dgrad = False
 
@@ -138,6 +139,12 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             # instructions of the 8-byte (one pixel) granule form; the odd filter column, if any, is a
             # structural zero of the internal weight layout.
             self.pair = p.stride % 2 == 0 and p.pad_x == 0 and os.environ.get("CXN_CONV_PAIR", "1") != "0"
+            # Spans: a filter row of the pitch-4 image is one contiguous run, so "16 pixels x 4 channels" is a
+            # 64-channel position that starts every `stride` pixels (positions overlap in memory - a tensor map
+            # does not mind).  That makes the layer a kh x 1 convolution over 64 channels which im2col-mode TMA
+            # fetches without a single gather instruction; filter columns kw..15 are structural zeros.
+            self.span = (self.pair and p.kernel_width <= 16 and p.kernel_height <= 16
+                         and os.environ.get("CXN_CONV_SPAN", "1") != "0")
         ocg = p.num_channel // g
         pad_ok = p.kernel_height - 1 - p.pad_y >= 0 and p.kernel_width - 1 - p.pad_x >= 0
         self.igemm_dgrad = (self.igemm_fwd and p.stride == 1 and ocg % 8 == 0 and pad_ok
@@ -160,6 +167,8 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         kg = icg * p.kernel_height * p.kernel_width
         if self.pair:
             kg = 8 * p.kernel_height * self._kw2()
+        if self.span:
+            kg = 64 * p.kernel_height
         return g, icg, p.num_channel // g, kg, ops.round_up(kg, 8)
 
     def _gather_args(self, x):
@@ -179,7 +188,9 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         w5 = w.reshape(g, ocg, cin, p.kernel_height, p.kernel_width).permute(0, 1, 3, 4, 2)
         if icg != cin:
             w5 = torch.nn.functional.pad(w5, (0, icg - cin))
-        if self.pair:
+        if self.span:
+            w5 = torch.nn.functional.pad(w5, (0, 0, 0, 16 - p.kernel_width))                # zero filter columns kw..15
+        elif self.pair:
             w5 = torch.nn.functional.pad(w5, (0, 0, 0, 2 * self._kw2() - p.kernel_width))   # zero odd filter column
         return w5.reshape(g, ocg, kg)
 
@@ -189,7 +200,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         p = self.param
         g, icg, ocg, kg, _ = self._geom()
         cin = p.num_input_channel // g
-        kw = 2 * self._kw2() if self.pair else p.kernel_width
+        kw = 16 if self.span else (2 * self._kw2() if self.pair else p.kernel_width)
         w5 = w.reshape(g, ocg, p.kernel_height, kw, icg)[:, :, :, :p.kernel_width, :cin]
         return w5.permute(0, 1, 4, 2, 3).reshape(g, ocg, cin * p.kernel_height * p.kernel_width)
 
@@ -225,6 +236,13 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         W = self.bind["wmat"]
         bias = self.bind["bias"].w.data_ptr() if p.no_bias == 0 else None
         b, c, h, w = x.shape
+        if self.span:
+            wp = x.wpitch
+            ops.check(L.cxn_conv_fprop_view(x.act.ptr, b, h, y.shape[3], p.stride * 4, 64, 1, W.shadow.data_ptr(), kpad, ocg,
+                                            p.kernel_height, 1, p.stride | (1 << 16), p.pad_y, 0, y.shape[2], y.shape[3],
+                                            y.act.ptr, y.act.ld, bias, 1 if self.fuse_relu else 0, 64, wp * 4, h * wp * 4,
+                                            ops.stream()), "conv_fprop_view")
+            return
         if self.igemm_fwd:
             gh, gw, gcs, gcg, gran, gkw, gstride, gpad_x = self._gather_args(x)
             ops.check(L.cxn_conv_fprop(x.act.ptr, b, gh, gw, gcs, gcg, g, gran,
@@ -251,7 +269,13 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             ops.check(L.cxn_colsum_bf16(gy.ptr, rows, p.num_channel, gy.ld, self.bind["bias"].g.data_ptr(),
                                         1 if ex.accumulate_grads else 0, ops.stream()), "colsum")
         # weight gradient (accumulates into the arena gradient, which the updater leaves zeroed)
-        if self.igemm_fwd:
+        if self.span:
+            wp = x.wpitch
+            ops.check(L.cxn_conv_wgrad_view(x.act.ptr, b, h, y.shape[3], p.stride * 4, 64, 1, gy.ptr, gy.ld, ocg,
+                                            p.kernel_height, 1, p.stride | (1 << 16), p.pad_y, 0, y.shape[2], y.shape[3],
+                                            W.g.data_ptr(), kg, 0, 64, 4 * p.kernel_width, 64, wp * 4, h * wp * 4,
+                                            ops.stream()), "conv_wgrad_view")
+        elif self.igemm_fwd:
             gh, gw, gcs, gcg, gran, gkw, gstride, gpad_x = self._gather_args(x)
             # pair mode: the odd filter column is a structural zero - its gradient (real pixels!) must not accumulate
             mask = (8 * gkw, 4 * p.kernel_width) if self.pair and p.kernel_width % 2 else (0, 0)
@@ -283,7 +307,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         ops.gemm(gy.ptr, gy.ld, ocg, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 1, self.col.data_ptr(), kpad,
                  rows * kpad, None, 0, rows, kg, ocg, batch=g, flags=ops.GEMM_OUT_BF16)
         # pair mode: (kh, kw2, 8) columns are (kh, 2*kw2, 4) in the pixel domain of the pitched image
-        cw, ckw = (x.wpitch, 2 * self._kw2()) if self.pair else (w, p.kernel_width)
+        cw, ckw = (x.wpitch, 16 if self.span else 2 * self._kw2()) if self.pair else (w, p.kernel_width)
         ops.check(L.cxn_col2im_nhwc(self.col.data_ptr(), x.grad.ptr, b, h, cw, x.act.ld, p.num_group, p.kernel_height,
                                     ckw, p.stride, p.pad_y, p.pad_x, y.shape[2], y.shape[3], kpad,
                                     rows * kpad, ops.stream()), "col2im")

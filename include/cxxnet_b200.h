@@ -50,6 +50,18 @@ int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg, int G, 
 int cxn_conv_wgrad_masked(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
                           long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
                           float* dw, long long lddw, int splits, int mask_period, int mask_valid, cudaStream_t stream);
+/* Convolution over a strided view of the input: position (n,h,w) starts at src + n*img_stride + h*row_stride + w*Cs
+ * and exposes `cdim` >= G*Cg contiguous elements (positions may overlap in memory).  Only the im2col-TMA route can
+ * read such a view (Cg % 64 == 0 ..., else -17).  The first layer uses it: 16 pixels x 4 channels of a pitch-4 image
+ * are one 64-channel position every `stride` pixels, which turns an 11x11x3 filter into an 11x1x64 one. */
+int cxn_conv_fprop_view(const void* src, int N, int H, int W, int Cs, int Cg, int G, const void* w, long long ldw, int Ng,
+                        int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW, void* y, long long ldy,
+                        const float* bias, int relu, long long cdim, long long row_stride, long long img_stride,
+                        cudaStream_t stream);
+int cxn_conv_wgrad_view(const void* src, int N, int H, int W, int Cs, int Cg, int G, const void* dy, long long lddy, int Ng,
+                        int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW, float* dw, long long lddw,
+                        int splits, int mask_period, int mask_valid, long long cdim, long long row_stride,
+                        long long img_stride, cudaStream_t stream);
 int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in, int ld_out,
                           cudaStream_t stream);
 /* experiment / tuning knobs of the implicit-GEMM convolution (0, or -1 for switches, = automatic):

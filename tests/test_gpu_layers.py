@@ -69,10 +69,13 @@ layer[+0] = softmax
     compare_backends(_conf(body, 20, "1,28,28"), make_batch((20, 1, 28, 28)), check_nodes=[1, 2, 4], tol_grad=0.12)
 
 
+@pytest.mark.parametrize("span", [1, 0])
 @pytest.mark.parametrize("k,stride,shape", [(11, 4, (3, 67, 67)), (4, 2, (3, 30, 31)), (3, 2, (1, 21, 20))])
-def test_conv_first_layer_pixel_pairs(k, stride, shape):
-    """first layer, <= 4 input channels, even stride, no padding: the image is read as pixel pairs
-    (16-byte granules) with the filter's odd column as a structural zero of the weight layout"""
+def test_conv_first_layer_spans_and_pixel_pairs(k, stride, shape, span, monkeypatch):
+    """first layer, <= 4 input channels, even stride, no padding.  span=1: 16-pixel x 4-channel runs of the
+    pitch-4 image are 64-channel positions fetched by im2col-mode TMA; span=0: pixel pairs (16-byte gather
+    granules).  Either way the unused filter columns are structural zeros of the internal weight layout."""
+    monkeypatch.setenv("CXN_CONV_SPAN", str(span))
     body = """
 layer[+1] = conv:cv1
   kernel_size = %d
@@ -88,12 +91,13 @@ layer[+0] = softmax
     errs, ref, b2 = compare_backends(_conf(body, 9, shp), make_batch((9,) + shape), return_trainers=True,
                                     tol_grad=0.1)   # bias gradients are sums of cancelling bf16 terms
     layer = b2.net.connections[0].layer
-    assert layer.pair
-    if k % 2:
+    assert layer.pair and layer.span == bool(span)
+    kw_eff = 16 if layer.span else 2 * ((k + 1) // 2)
+    if kw_eff > k:
         # the structural zeros must not collect gradient (their patch values are real pixels)
-        g = layer.bind["wmat"].g.reshape(24, k, k + 1, 4)
+        g = layer.bind["wmat"].g.reshape(24, k, kw_eff, 4)
         assert float(g[:, :, k:, :].abs().max()) == 0.0
-        assert float(g[:, :, :k, :3].abs().max()) > 0.0
+        assert float(g[:, :, :k, :shape[0]].abs().max()) > 0.0
 
 
 def test_conv_groups_relu_lrn():
