@@ -60,6 +60,8 @@ struct Params {
   long long ldd, strideD;   // strideD: per-group offset (elements)
   const float* bias;        // [G*Ng] or null
   int relu;
+  const bf16* mask;         // optional [rows][ldd] tensor: outputs whose mask element is <= 0 are written as zero
+                            // (backward-data folding the ReLU that precedes this layer in the forward pass)
   // wgrad
   int splits, kb_per_split;
   int mask_period, mask_valid;   // wgrad: columns n with n % period >= valid are not accumulated (0 = off)
@@ -537,6 +539,26 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
           }
+          if (p.mask != nullptr) {
+            const bf16* mk = p.mask + off;
+            if (lim == 32 && ((reinterpret_cast<uintptr_t>(mk) & 15) == 0)) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const uint4 mv = *reinterpret_cast<const uint4*>(mk + 8 * q);
+                const __nv_bfloat162* mh2 = reinterpret_cast<const __nv_bfloat162*>(&mv);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                  const float2 m2 = __bfloat1622float2(mh2[t]);
+                  if (!(m2.x > 0.0f)) f[q * 8 + 2 * t] = 0.0f;
+                  if (!(m2.y > 0.0f)) f[q * 8 + 2 * t + 1] = 0.0f;
+                }
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j < lim && !(__bfloat162float(mk[j]) > 0.0f)) f[j] = 0.0f;
+            }
+          }
           bf16* d = reinterpret_cast<bf16*>(p.D) + off;
           if (lim == 32 && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
             uint4* d4 = reinterpret_cast<uint4*>(d);
@@ -780,14 +802,15 @@ using namespace cxn::igemm;
 //   y    NHWC bf16 [N*OH*OW][ldy], group g writes columns [g*Ng, (g+1)*Ng)
 static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
                            long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
-                           void* y, long long ldy, const float* bias, int relu, long long view_cdim, long long view_row,
-                           long long view_img, cudaStream_t st) {
+                           void* y, long long ldy, const float* bias, int relu, const void* mask, long long view_cdim,
+                           long long view_row, long long view_img, cudaStream_t st) {
   Params p;
   memset(&p, 0, sizeof(p));
   p.view_cdim = view_cdim; p.view_row = view_row; p.view_img = view_img;
   p.src = (const bf16*)src; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
   p.stride_y = stride & 0xFFFF; p.stride_x = (stride >> 16) ? (stride >> 16) : p.stride_y; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
   p.gran = gran; p.Ng = Ng; p.D = y; p.ldd = ldy; p.strideD = Ng; p.bias = bias; p.relu = relu;
+  p.mask = (const bf16*)mask;
   p.splits = 1; p.kb_per_split = 0;
   int rc = check_geom(p);
   if (rc) return rc;
@@ -934,7 +957,15 @@ CXN_API int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg,
                            long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
                            void* y, long long ldy, const float* bias, int relu, cudaStream_t st) {
   return conv_fprop_impl(src, N, H, W, Cs, Cg, G, gran, w, ldw, Ng, KH, KW, stride, pad_y, pad_x, OH, OW, y, ldy, bias, relu,
-                         0, 0, 0, st);
+                         nullptr, 0, 0, 0, st);
+}
+// cxn_conv_fprop whose outputs are zeroed where mask[row][col] <= 0 (mask: bf16, laid out like y).  Backward-data of a
+// layer whose input went through a ReLU: dx = (x > 0) * (dy conv flipped W) in one kernel.
+CXN_API int cxn_conv_fprop_masked(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
+                                  long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                                  void* y, long long ldy, const void* mask, cudaStream_t st) {
+  return conv_fprop_impl(src, N, H, W, Cs, Cg, G, gran, w, ldw, Ng, KH, KW, stride, pad_y, pad_x, OH, OW, y, ldy, nullptr, 0,
+                         mask, 0, 0, 0, st);
 }
 // The same over a strided view of the input: position (n, h, w) starts at src + n*img_stride + h*row_stride + w*Cs and
 // exposes `cdim` >= G*Cg contiguous elements (positions may overlap in memory).  Only the im2col-TMA route can read
@@ -946,7 +977,7 @@ CXN_API int cxn_conv_fprop_view(const void* src, int N, int H, int W, int Cs, in
                                 long long img_stride, cudaStream_t st) {
   if (cdim <= 0) return -18;
   return conv_fprop_impl(src, N, H, W, Cs, Cg, G, 8, w, ldw, Ng, KH, KW, stride, pad_y, pad_x, OH, OW, y, ldy, bias, relu,
-                         cdim, row_stride, img_stride, st);
+                         nullptr, cdim, row_stride, img_stride, st);
 }
 CXN_API int cxn_conv_wgrad_masked(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,
                                   long long lddy, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,

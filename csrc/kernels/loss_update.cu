@@ -70,7 +70,8 @@ struct Segment {
   int cols;               // row length of the 2-D view (for the padded shadow)
   int shadow_ld;
   float lr, wd, momentum, clip;   // refreshed every step
-  float adam_lr_t, beta1, beta2, pad_;
+  float adam_lr_t, beta1, beta2;
+  int flags;              // bit 0: the producer overwrites this gradient every step - the updater need not zero it
 };
 constexpr int kChunk = 1024;
 
@@ -124,7 +125,7 @@ __global__ void update_kernel(float* __restrict__ w, float* __restrict__ g, floa
       *reinterpret_cast<float4*>(w + e) = wv;
       *reinterpret_cast<float4*>(m + e) = mv;
       if (kind == 2) *reinterpret_cast<float4*>(m2 + e) = m2v;
-      *reinterpret_cast<float4*>(g + e) = make_float4(0, 0, 0, 0);
+      if (!(s.flags & 1)) *reinterpret_cast<float4*>(g + e) = make_float4(0, 0, 0, 0);
       if (s.shadow_off >= 0) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {

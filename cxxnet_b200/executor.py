@@ -266,6 +266,17 @@ class NeuralNet:
                         and consumers.get(x.index, 0) == 1 and x.grad is x.alias_of.grad):
                     l.mask_relu = True
                     p.layer.skip_bwd = True
+        # ... or into the backward-data kernel of the convolution that consumes it
+        for c in self.connections:
+            l = c.layer
+            if c.native and isinstance(l, native.ConvolutionLayer) and l.igemm_dgrad:
+                x = c.nodes_in[0]
+                p = producer.get(x.index)
+                if (p is not None and p.native and isinstance(p.layer, native.ReluLayer) and x.alias_of is not None
+                        and consumers.get(x.index, 0) == 1 and x.grad is x.alias_of.grad and not p.layer.skip_bwd
+                        and x.act.ld == x.grad.ld):
+                    l.mask_relu_in = True
+                    p.layer.skip_bwd = True
         # parameter arena (in peer-mapped symmetric memory when several ranks train together)
         self.symm_block = None
         self.symm_offsets = {}
@@ -287,6 +298,12 @@ class NeuralNet:
                 else:
                     rows, cols, sld = 1, w.numel(), 0
                 s = self.arena.add(c.layer, i, tag, rows, cols, sld, up, b1, b2)
+                # gradients that their producer overwrites on the first micro-step (GEMM with beta = 0, column
+                # sums without accumulation) need no zeroing by the updater; convolution weight gradients are
+                # accumulated with atomics and do
+                s.nozero = bool(c.native and ((isinstance(c.layer, native.FullConnectLayer) and tag == "wmat") or
+                                              (isinstance(c.layer, (native.FullConnectLayer, native.ConvolutionLayer))
+                                               and tag == "bias")))
                 self._seg_of[(i, tag)] = s
         if self.world_size > 1 and self.arena_alloc is None:
             self._plan_fc_shards()

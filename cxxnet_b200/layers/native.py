@@ -114,6 +114,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         self.wflip = None
         self.cin_pad = 0        # 4 when a <=4-channel input is stored with a channel pitch of 4
         self.pair = False       # cin_pad input read as [H][Wp/2] super-pixels of 8 channels (two pixels each)
+        self.mask_relu_in = False   # backward-data also applies the mask of the ReLU that produced the input node
         self.span = False       # cin_pad input read through im2col TMA as overlapping 16-pixel (64-channel) positions
         self.igemm_fwd = False
         self.igemm_dgrad = False
@@ -297,9 +298,10 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             kh, kw = p.kernel_height, p.kernel_width
             ops.check(L.cxn_conv_flip_weights(W.shadow.data_ptr(), self.wflip.data_ptr(), g, ocg, icg, kh, kw, kpad,
                                               self.wflip_ld, ops.stream()), "flip_weights")
-            ops.check(L.cxn_conv_fprop(gy.ptr, b, y.shape[2], y.shape[3], gy.ld, ocg, g, 8, self.wflip.data_ptr(),
-                                       self.wflip_ld, icg, kh, kw, 1, kh - 1 - p.pad_y, kw - 1 - p.pad_x, h, w,
-                                       x.grad.ptr, x.grad.ld, None, 0, ops.stream()), "conv_dgrad")
+            ops.check(L.cxn_conv_fprop_masked(gy.ptr, b, y.shape[2], y.shape[3], gy.ld, ocg, g, 8, self.wflip.data_ptr(),
+                                              self.wflip_ld, icg, kh, kw, 1, kh - 1 - p.pad_y, kw - 1 - p.pad_x, h, w,
+                                              x.grad.ptr, x.grad.ld, x.act.ptr if self.mask_relu_in else None,
+                                              ops.stream()), "conv_dgrad")
             return
         if self.igemm_fwd:
             # strided backward-data: explicit dcol = gy . W, then scatter

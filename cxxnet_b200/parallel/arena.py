@@ -26,13 +26,13 @@ from ..updaters import UpdaterParam
 SEG_DTYPE = np.dtype([
     ("start", "<i8"), ("n", "<i8"), ("shadow_off", "<i8"), ("cols", "<i4"), ("shadow_ld", "<i4"),
     ("lr", "<f4"), ("wd", "<f4"), ("momentum", "<f4"), ("clip", "<f4"),
-    ("adam_lr_t", "<f4"), ("beta1", "<f4"), ("beta2", "<f4"), ("pad", "<f4"),
+    ("adam_lr_t", "<f4"), ("beta1", "<f4"), ("beta2", "<f4"), ("flags", "<i4"),
 ])
 
 
 class Segment:
     __slots__ = ("layer_index", "tag", "start", "n", "rows", "cols", "shadow_off", "shadow_ld", "param", "layer",
-                 "beta1", "beta2")
+                 "beta1", "beta2", "nozero")
 
 
 class ParamArena:
@@ -68,6 +68,7 @@ class ParamArena:
         else:
             s.shadow_off = -1
         s.param, s.beta1, s.beta2 = param, beta1, beta2
+        s.nozero = False
         self.segments.append(s)
         return s
 
@@ -126,6 +127,7 @@ class ParamArena:
             arr[i]["start"], arr[i]["n"], arr[i]["shadow_off"] = s.start, s.n, s.shadow_off
             arr[i]["cols"], arr[i]["shadow_ld"] = max(s.cols, 1), s.shadow_ld
             arr[i]["lr"], arr[i]["wd"], arr[i]["momentum"], arr[i]["clip"] = p.learning_rate, p.wd, p.momentum, p.clip_gradient
+            arr[i]["flags"] = 1 if s.nozero else 0    # the producing kernel overwrites this gradient: no need to zero it
             if self.kind == ops.UPD_ADAM:
                 fix1 = 1.0 - (1.0 - s.beta1) ** (epoch + 1)
                 fix2 = 1.0 - (1.0 - s.beta2) ** (epoch + 1)

@@ -62,6 +62,11 @@ int cxn_conv_wgrad_view(const void* src, int N, int H, int W, int Cs, int Cg, in
                         int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW, float* dw, long long lddw,
                         int splits, int mask_period, int mask_valid, long long cdim, long long row_stride,
                         long long img_stride, cudaStream_t stream);
+/* cxn_conv_fprop (no bias / activation) whose outputs are zeroed where mask[row][col] <= 0; mask is bf16 laid out
+ * like y.  Backward-data of a layer whose input went through a ReLU, in one kernel. */
+int cxn_conv_fprop_masked(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
+                          long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
+                          void* y, long long ldy, const void* mask, cudaStream_t stream);
 int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in, int ld_out,
                           cudaStream_t stream);
 /* experiment / tuning knobs of the implicit-GEMM convolution (0, or -1 for switches, = automatic):
