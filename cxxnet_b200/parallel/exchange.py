@@ -21,6 +21,8 @@ from __future__ import annotations
 import ctypes
 from typing import Dict, List, Optional
 
+import os
+
 import torch
 
 from .. import ops
@@ -113,6 +115,8 @@ class GradExchange:
         # Per-step part of every kernel's sequence number: a device word bumped on the main stream at the
         # start of each backward pass (begin_step).  The host part `self.seq` only moves outside steps, so
         # a step captured into a CUDA graph replays with advancing barriers.
+        # timing experiments only (results are wrong): comma list of conv | gather | publish | fcgemm
+        self._skip = set(filter(None, os.environ.get("CXN_XCHG_SKIP", "").split(",")))
         self.epoch = torch.zeros(1, dtype=torch.int64, device=self.device)
         L.cxn_xchg_set_epoch_ptr(self.epoch.data_ptr())
         dist.barrier()
@@ -145,7 +149,7 @@ class GradExchange:
     def layer_done(self, layer_index: int) -> None:
         """called right after layer ``layer_index`` finished its backward on the main stream."""
         b = self.bucket_of_layer.get(layer_index)
-        if b is None or b["trigger"] != layer_index:
+        if b is None or b["trigger"] != layer_index or "conv" in self._skip:
             return
         a = self.arena
         main = torch.cuda.current_stream(self.device)
@@ -194,19 +198,23 @@ class GradExchange:
         b = x.shape[0]
         step = net.max_batch
         main = torch.cuda.current_stream(self.device)
-        # 1. gather [x | gy] rows of every rank (zero-filled up to `step` rows per rank)
-        self._allgather([(x.act.ptr, sh.x_off, step * sh.ld_in * 2, b * sh.ld_in * 2),
-                         (y.grad.ptr, sh.gy_off, step * sh.ld_out * 2, b * sh.ld_out * 2)],
-                        sh.slot_gather, self.counter_main, main.cuda_stream)
         total_b = step * self.world
         p = layer.param
         nin, nout = p.num_input_node, p.num_hidden
-        # 2. everything else runs on the exchange stream, overlapped with the rest of backward
+        # Everything runs on the exchange stream, overlapped with the rest of backward.  The stream waits
+        # for this rank's backward-data GEMM; the gather's entry barrier therefore also tells every rank
+        # that all of them are done reading this layer's weights, which the publish below overwrites.
         self.ready.record(main)
         self.stream.wait_event(self.ready)
         with torch.cuda.stream(self.stream):
+            # 1. gather [x | gy] rows of every rank (zero-filled up to `step` rows per rank); neither buffer
+            #    is written again before this layer's next forward, which waits for this stream
+            if "gather" not in self._skip:
+                self._allgather([(x.act.ptr, sh.x_off, step * sh.ld_in * 2, b * sh.ld_in * 2),
+                                 (y.grad.ptr, sh.gy_off, step * sh.ld_out * 2, b * sh.ld_out * 2)],
+                                sh.slot_gather, self.counter, self.stream.cuda_stream)
             acc = net.accumulate_grads
-            if sh.my_rows > 0:
+            if sh.my_rows > 0 and "fcgemm" not in self._skip:
                 # gW[row0:row0+my_rows] = GY_all[:, shard]^T . X_all  over the global batch
                 gy_ptr = sh.gy_all.data_ptr() + sh.row0 * 2
                 g_ptr = a.g.data_ptr() + (sh.wseg.start + sh.row0 * nin) * 4
@@ -226,8 +234,9 @@ class GradExchange:
                 sld = sh.wseg.shadow_ld
                 src = a.shadow.data_ptr() + (sh.wseg.shadow_off + sh.row0 * sld) * 2
                 dst = self.off["shadow"] + sh.wseg.shadow_off * 2
-                self._allgather([(src, dst, sh.rows_per_rank * sld * 2, sh.my_rows * sld * 2)],
-                                sh.slot_pub, self.counter, self.stream.cuda_stream)
+                if "publish" not in self._skip:
+                    self._allgather([(src, dst, sh.rows_per_rank * sld * 2, sh.my_rows * sld * 2)],
+                                    sh.slot_pub, self.counter, self.stream.cuda_stream)
             sh.event.record(self.stream)
             sh.pending = True
 
