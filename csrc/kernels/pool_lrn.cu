@@ -251,6 +251,59 @@ __global__ void __launch_bounds__(256) pool_bwd_img_kernel(const bf16* __restric
   }
 }
 
+// Max-pool backward, at most 2 x 2 covering windows, division-free indexing: threadIdx.x = channel
+// vector, threadIdx.y = pixel inside the row segment, blockIdx = (row segment, row, image).  SH = log2 of
+// the stride when it is a power of two (else -1: generic division).
+template <int SH>
+__global__ void __launch_bounds__(256) pool_bwd_row_kernel(const bf16* __restrict__ x, const bf16* __restrict__ y,
+                                                           const bf16* __restrict__ dy, bf16* __restrict__ dx, PoolGeom g) {
+  const int xx = blockIdx.x * blockDim.y + threadIdx.y;
+  if (xx >= g.W) return;
+  const int yy = blockIdx.y, n = blockIdx.z, c = threadIdx.x << 3;
+  auto div_s = [&](int v) { return SH >= 0 ? (v >> SH) : v / g.stride; };
+  const int py0 = yy < g.K_y ? 0 : div_s(yy - g.K_y + g.stride);
+  const int px0 = xx < g.K_x ? 0 : div_s(xx - g.K_x + g.stride);
+  const int py1 = min(div_s(yy) + 1, g.OH);
+  const int px1 = min(div_s(xx) + 1, g.OW);
+  const long long xoff = (((long long)n * g.H + yy) * g.W + xx) * g.C + c;
+  const uint4 xr = *reinterpret_cast<const uint4*>(x + xoff);
+  const long long pbase = (((long long)n * g.OH + py0) * g.OW + px0) * g.C + c;
+  const bool ok01 = px0 + 1 < px1, ok10 = py0 + 1 < py1;
+  const bool okv[4] = {py0 < py1 && px0 < px1, py0 < py1 && ok01, ok10 && px0 < px1, ok10 && ok01};
+  const long long offv[4] = {0, (long long)g.C, (long long)g.OW * g.C, (long long)(g.OW + 1) * g.C};
+  uint4 pv[4], gv[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    pv[k] = okv[k] ? *reinterpret_cast<const uint4*>(y + pbase + offv[k]) : make_uint4(0, 0, 0, 0);
+    gv[k] = okv[k] ? *reinterpret_cast<const uint4*>(dy + pbase + offv[k]) : make_uint4(0, 0, 0, 0);
+  }
+  const __nv_bfloat162 z = __float2bfloat162_rn(0.0f);
+  const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&xr);
+  __nv_bfloat162 xm[4], am[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    xm[j] = g.relu ? __hmax2(hx[j], z) : hx[j];
+    am[j] = z;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    // an invalid window contributes dy = 0 (its loads were replaced by zeros), so no branch is needed
+    const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&pv[k]);
+    const __nv_bfloat162* hg = reinterpret_cast<const __nv_bfloat162*>(&gv[k]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) am[j] = __hfma2(__heq2(xm[j], hp[j]), hg[j], am[j]);
+  }
+  if (g.relu) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) am[j] = __hmul2(am[j], __hgt2(hx[j], z));
+  }
+  uint4 o;
+  __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) ho[j] = am[j];
+  *reinterpret_cast<uint4*>(dx + xoff) = o;
+}
+
 // dx[n][y][x][c] = sum over covering windows of  partial(x, pooled) * dy   (* 1/k^2 for avg)
 // With relu fused, x is compared after relu and the result is masked by x>0.
 template <int V>
@@ -408,43 +461,58 @@ __global__ void lrn_reg_kernel(const bf16* __restrict__ x, const bf16* __restric
   const bool active = sub < ppw;
   const long long warp0 = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
   const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
-  for (long long p0 = warp0 * ppw; p0 < pixels; p0 += nwarps * ppw) {
-    const long long pix = p0 + sub;
-    const bool ok = active && pix < pixels;
-    float xv[8], gv[8];
-    uint4 raw = make_uint4(0, 0, 0, 0), rawg = make_uint4(0, 0, 0, 0);
-    if (ok) {
-      raw = *reinterpret_cast<const uint4*>(x + pix * C + lip * 8);
-      if (BWD) rawg = *reinterpret_cast<const uint4*>(dy + pix * C + lip * 8);
-    }
-    unpack8(raw, xv);
-    if (BWD) unpack8(rawg, gv);
-    float sq[8], e[12];
+  // two pixels per thread and iteration, both loads issued before the arithmetic of the first: one
+  // 16-byte load in flight per thread is not enough outstanding bytes to cover HBM latency
+  constexpr int U = 2;
+  for (long long p0 = warp0 * ppw; p0 < pixels; p0 += U * nwarps * ppw) {
+    uint4 raw[U], rawg[U];
+    bool ok[U];
+    long long pixu[U];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) sq[j] = xv[j] * xv[j];
-    halo2(sq, e, lip, tpp);
-    float nb[8], o[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float s = e[2 + j];
-      if (half >= 1) s += e[1 + j] + e[3 + j];
-      if (half >= 2) s += e[j] + e[4 + j];
-      const float norm = s * salpha + knorm;
-      nb[j] = __powf(norm, -beta);
-      if (!BWD) o[j] = xv[j] * nb[j];
-      else sq[j] = gv[j] * xv[j] * nb[j] / norm;      // t = g * x * norm^(-beta-1)
+    for (int u = 0; u < U; ++u) {
+      pixu[u] = p0 + u * nwarps * ppw + sub;
+      ok[u] = active && pixu[u] < pixels;
+      raw[u] = make_uint4(0, 0, 0, 0);
+      rawg[u] = make_uint4(0, 0, 0, 0);
+      if (ok[u]) {
+        raw[u] = *reinterpret_cast<const uint4*>(x + pixu[u] * C + lip * 8);
+        if (BWD) rawg[u] = *reinterpret_cast<const uint4*>(dy + pixu[u] * C + lip * 8);
+      }
     }
-    if (BWD) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (p0 + u * nwarps * ppw >= pixels) break;      // warp-uniform: the shuffles below stay converged
+      float xv[8], gv[8];
+      unpack8(raw[u], xv);
+      if (BWD) unpack8(rawg[u], gv);
+      float sq[8], e[12];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sq[j] = xv[j] * xv[j];
       halo2(sq, e, lip, tpp);
+      float nb[8], o[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float s = e[2 + j];
         if (half >= 1) s += e[1 + j] + e[3 + j];
         if (half >= 2) s += e[j] + e[4 + j];
-        o[j] = gv[j] * nb[j] - 2.0f * beta * salpha * s * xv[j];
+        const float norm = s * salpha + knorm;
+        const float l2 = __log2f(norm);
+        nb[j] = exp2f(-beta * l2);                                      // norm^-beta
+        if (!BWD) o[j] = xv[j] * nb[j];
+        else sq[j] = gv[j] * xv[j] * exp2f((-beta - 1.0f) * l2);        // t = g * x * norm^(-beta-1)
       }
+      if (BWD) {
+        halo2(sq, e, lip, tpp);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float s = e[2 + j];
+          if (half >= 1) s += e[1 + j] + e[3 + j];
+          if (half >= 2) s += e[j] + e[4 + j];
+          o[j] = gv[j] * nb[j] - 2.0f * beta * salpha * s * xv[j];
+        }
+      }
+      if (ok[u]) *reinterpret_cast<uint4*>(out + pixu[u] * C + lip * 8) = pack8(o);
     }
-    if (ok) *reinterpret_cast<uint4*>(out + pix * C + lip * 8) = pack8(o);
   }
 }
 
@@ -508,7 +576,17 @@ CXN_API int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx,
   PoolGeom g{N, H, W, C, ky, kx, stride, OH, OW, mode, relu};
   if ((long long)N * H * W * C <= 0) return 0;
   const bool v = pool_vec(x, y, C) && pool_vec(dy, dx, C);
-  if (v && N <= 65535 && ky <= 2 * stride && kx <= 2 * stride && (long long)H * W * (C / 8) < (1LL << 30))
+  if (v && mode == 0 && N <= 65535 && H <= 65535 && ky <= 2 * stride && kx <= 2 * stride && C / 8 <= 256) {
+    // max pooling: one thread per (pixel, 8 channels) with 2-D thread indexing
+    const int cv = C / 8;
+    const int py = 256 / cv > 0 ? 256 / cv : 1;
+    dim3 block(cv, py), grid(ceil_div(W, py), H, N);
+    const bf16 *xp = (const bf16*)x, *yp = (const bf16*)y, *gp = (const bf16*)dy;
+    if (stride == 1) pool_bwd_row_kernel<0><<<grid, block, 0, st>>>(xp, yp, gp, (bf16*)dx, g);
+    else if (stride == 2) pool_bwd_row_kernel<1><<<grid, block, 0, st>>>(xp, yp, gp, (bf16*)dx, g);
+    else if (stride == 4) pool_bwd_row_kernel<2><<<grid, block, 0, st>>>(xp, yp, gp, (bf16*)dx, g);
+    else pool_bwd_row_kernel<-1><<<grid, block, 0, st>>>(xp, yp, gp, (bf16*)dx, g);
+  } else if (v && N <= 65535 && ky <= 2 * stride && kx <= 2 * stride && (long long)H * W * (C / 8) < (1LL << 30))
     pool_bwd_img_kernel<4><<<dim3((unsigned)ceil_div_ll((long long)H * W * (C / 8), 256 * 4), N), 256, 0, st>>>(
         (const bf16*)x, (const bf16*)y, (const bf16*)dy, (bf16*)dx, g);
   else if (v)
