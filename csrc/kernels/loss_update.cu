@@ -32,6 +32,45 @@ __global__ void softmax_rows_kernel(float* __restrict__ x, int rows, int cols, l
   const float inv = 1.0f / s;
   for (int c = lane; c < cols; c += 32) r[c] *= inv;
 }
+// Error metric on the device (reference src/utils/metric.h:92-121 runs this loop on the host after a
+// D2H copy): one warp per row finds the first maximum of the scores (strict '>' scan), compares it with
+// the label and adds the number of wrong rows to a double accumulator.  cols == 1: score > 0 is class 1.
+__global__ void metric_error_kernel(const float* __restrict__ p, long long ld, const float* __restrict__ label,
+                                    long long label_ld, int rows, int cols, double* __restrict__ accum) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  float wrong = 0.0f;
+  if (warp < rows) {
+    const float* r = p + (long long)warp * ld;
+    int best;
+    if (cols == 1) {
+      best = r[0] > 0.0f ? 1 : 0;
+    } else {
+      float m = -INFINITY;
+      int mi = 0x7fffffff;
+      for (int c = lane; c < cols; c += 32) {
+        const float v = r[c];
+        if (v > m) { m = v; mi = c; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float om = __shfl_xor_sync(0xffffffffu, m, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, mi, o);
+        if (om > m || (om == m && oi < mi)) { m = om; mi = oi; }
+      }
+      best = mi;
+    }
+    wrong = (best != (int)label[(long long)warp * label_ld]) ? 1.0f : 0.0f;
+  }
+  // one atomic per block
+  __shared__ float part[8];
+  if (lane == 0) part[threadIdx.x >> 5] = wrong;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.0f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += part[i];
+    if (t != 0.0f) atomicAdd(accum, (double)t);
+  }
+}
 __global__ void sigmoid_rows_kernel(float* __restrict__ x, long long rows, int cols, long long ld) {
   const long long total = rows * cols;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -163,6 +202,14 @@ using namespace cxn;
 CXN_API int cxn_softmax_rows(float* x, int rows, int cols, long long ld, cudaStream_t st) {
   if (rows <= 0 || cols <= 0) return 0;
   softmax_rows_kernel<<<ceil_div(rows * 32, 256), 256, 0, st>>>(x, rows, cols, ld);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+// accum (double, device) += number of rows whose first-maximum class differs from label[row][0]
+CXN_API int cxn_metric_error(const float* p, long long ld, const float* label, long long label_ld, int rows, int cols,
+                             double* accum, cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  metric_error_kernel<<<ceil_div(rows * 32, 256), 256, 0, st>>>(p, ld, label, label_ld, rows, cols, accum);
   CXN_CHECK_LAUNCH();
   return 0;
 }

@@ -251,6 +251,49 @@ __global__ void __launch_bounds__(256) pool_bwd_img_kernel(const bf16* __restric
   }
 }
 
+// Max-pool forward with the same division-free 2-D thread indexing (window <= KMAX x KMAX)
+template <int KMAX>
+__global__ void __launch_bounds__(256) pool_fwd_row_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, PoolGeom g) {
+  const int ow = blockIdx.x * blockDim.y + threadIdx.y;
+  if (ow >= g.OW) return;
+  const int oh = blockIdx.y, n = blockIdx.z, c = threadIdx.x << 3;
+  const int y0 = oh * g.stride, x0 = ow * g.stride;
+  const bf16* base = x + (((long long)n * g.H + y0) * g.W + x0) * g.C + c;
+  const __nv_bfloat162 ninf = __float2bfloat162_rn(-INFINITY);
+  uint4 v[KMAX][KMAX];
+#pragma unroll
+  for (int a = 0; a < KMAX; ++a)
+#pragma unroll
+    for (int b = 0; b < KMAX; ++b) {
+      const bool ok = a < g.K_y && b < g.K_x && y0 + a < g.H && x0 + b < g.W;
+      if (ok) {
+        v[a][b] = *reinterpret_cast<const uint4*>(base + ((long long)a * g.W + b) * g.C);
+      } else {
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v[a][b]);
+        h[0] = h[1] = h[2] = h[3] = ninf;
+      }
+    }
+  __nv_bfloat162 m[4] = {ninf, ninf, ninf, ninf};
+#pragma unroll
+  for (int a = 0; a < KMAX; ++a)
+#pragma unroll
+    for (int b = 0; b < KMAX; ++b) {
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[a][b]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) m[j] = __hmax2(m[j], h[j]);
+    }
+  if (g.relu) {
+    const __nv_bfloat162 z = __float2bfloat162_rn(0.0f);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) m[j] = __hmax2(m[j], z);
+  }
+  uint4 o;
+  __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) ho[j] = m[j];
+  *reinterpret_cast<uint4*>(y + (((long long)n * g.OH + oh) * g.OW + ow) * g.C + c) = o;
+}
+
 // Max-pool backward, at most 2 x 2 covering windows, division-free indexing: threadIdx.x = channel
 // vector, threadIdx.y = pixel inside the row segment, blockIdx = (row segment, row, image).  SH = log2 of
 // the stride when it is a power of two (else -1: generic division).
@@ -560,7 +603,13 @@ CXN_API int cxn_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int
   PoolGeom g{N, H, W, C, ky, kx, stride, OH, OW, mode, relu};
   if ((long long)N * OH * OW * C <= 0) return 0;
   const bool small = pool_vec(x, y, C) && N <= 65535 && (long long)OH * OW * (C / 8) < (1LL << 30);
-  if (small && ky <= 2 && kx <= 2)
+  if (small && mode == 0 && ky <= 3 && kx <= 3 && OH <= 65535 && C / 8 <= 256) {
+    const int cv = C / 8;
+    const int py = 256 / cv > 0 ? 256 / cv : 1;
+    dim3 block(cv, py), grid(ceil_div(OW, py), OH, N);
+    if (ky <= 2 && kx <= 2) pool_fwd_row_kernel<2><<<grid, block, 0, st>>>((const bf16*)x, (bf16*)y, g);
+    else pool_fwd_row_kernel<3><<<grid, block, 0, st>>>((const bf16*)x, (bf16*)y, g);
+  } else if (small && ky <= 2 && kx <= 2)
     pool_fwd_img_kernel<2><<<dim3((unsigned)ceil_div_ll((long long)OH * OW * (C / 8), 256), N), 256, 0, st>>>((const bf16*)x, (bf16*)y, g);
   else if (small && ky <= 3 && kx <= 3)
     pool_fwd_img_kernel<3><<<dim3((unsigned)ceil_div_ll((long long)OH * OW * (C / 8), 256), N), 256, 0, st>>>((const bf16*)x, (bf16*)y, g);

@@ -86,6 +86,7 @@ def lib():
     _sig(L.cxn_pool_bwd, [P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(L.cxn_lrn_fwd, [P, P, LL, I, I, F, F, F, P])
     _sig(L.cxn_lrn_bwd, [P, P, P, LL, I, I, F, F, F, P])
+    _sig(L.cxn_metric_error, [P, LL, P, LL, I, I, P, P])
     _sig(L.cxn_softmax_rows, [P, I, I, LL, P])
     _sig(L.cxn_sigmoid_rows, [P, LL, I, LL, P])
     _sig(L.cxn_loss_grad, [P, LL, P, LL, P, LL, LL, I, F, I, P])

@@ -261,14 +261,38 @@ class NetTrainer:
         net.accumulate_grads = self.sample_counter != 0
         net.set_input(data[begin:end], [self._as_tensor(e)[begin:end] for e in batch.extra_data])
         net.forward(True)
-        if self.eval_train != 0 and self.eval_req:
-            scores = [self._scores2d(net.copy_node_data(i)) for i in self.eval_req]
-            self.train_metric.add_eval(scores, net.label_info.fields, self.net_cfg.label_name_map)
+        self._eval_train()
         net.backprop(False, need_update, self.epoch_counter)
         self.sample_counter += 1
         if self.sample_counter >= self.update_period:
             self.sample_counter = 0
             self.epoch_counter += 1
+
+    def _eval_train(self) -> None:
+        """running train metric on the forward pass just done.  `error` on a native loss node is one kernel
+        that accumulates into the metric's device scalar; anything else goes through the torch reductions."""
+        if self.eval_train == 0 or not self.eval_req:
+            return
+        net = self.net
+        fields, fmap = net.label_info.fields, self.net_cfg.label_name_map
+        ms = self.train_metric
+        fast = net.backend == "b200" and all(
+            type(e).__name__ == "MetricError" and f in fmap and net.nodes[nid].loss_input and net.nodes[nid].f32 is not None
+            and fields[fmap[f]].is_cuda and fields[fmap[f]].dtype == torch.float32 and fields[fmap[f]].is_contiguous()
+            for e, f, nid in zip(ms.evals, ms.label_fields, self.eval_req))
+        if not fast:
+            scores = [self._scores2d(net.copy_node_data(i)) for i in self.eval_req]
+            ms.add_eval(scores, fields, fmap)
+            return
+        for e, f, nid in zip(ms.evals, ms.label_fields, self.eval_req):
+            n = net.nodes[nid]
+            rows, cols = n.shape[0], n.shape[3]
+            lab = fields[fmap[f]]
+            if e.sum_metric is None or e.sum_metric.device != n.f32.device:
+                e.sum_metric = torch.zeros((), dtype=torch.float64, device=n.f32.device)
+            ops.check(ops.lib().cxn_metric_error(n.f32.data_ptr(), n.f32.shape[1], lab.data_ptr(), lab.shape[1], rows, cols,
+                                                 e.sum_metric.data_ptr(), ops.stream()), "metric_error")
+            e.cnt_inst += rows
 
     # ------------------------------------------------------------------ captured training step
     def _graph_applicable(self, batch: DataBatch) -> bool:
@@ -284,9 +308,7 @@ class NetTrainer:
         net = self.net
         net.convert_staged(slot)
         net.forward(True)
-        if self.eval_train != 0 and self.eval_req:
-            scores = [self._scores2d(net.copy_node_data(i)) for i in self.eval_req]
-            self.train_metric.add_eval(scores, net.label_info.fields, self.net_cfg.label_name_map)
+        self._eval_train()
         net.backprop(False, True, self.epoch_counter)
         if net.exchange is not None:
             net.exchange.wait_all()          # join the exchange stream: the step is one unit

@@ -144,6 +144,10 @@ int cxn_lrn_bwd(const void* x, const void* dy, void* dx, long long pixels, int C
 /* ---- K13 loss layers: in-place softmax / sigmoid on the fp32 output node and the gradient
  * (p - target) * scale as bf16.  kind 0: class-index label, 1: dense label.
  * src/layer/loss/softmax_layer-inl.hpp:21-32, loss_layer_base-inl.hpp:52-63. */
+/* error metric on the device: accum (double) += #rows whose first-maximum score index != (int)label[row*label_ld]
+ * (cols == 1: score > 0 is class 1).  Reference: src/utils/metric.h:92-121 (host loop after a D2H copy). */
+int cxn_metric_error(const float* p, long long ld, const float* label, long long label_ld, int rows, int cols,
+                     double* accum, cudaStream_t stream);
 int cxn_softmax_rows(float* x, int rows, int cols, long long ld, cudaStream_t stream);
 int cxn_sigmoid_rows(float* x, long long rows, int cols, long long ld, cudaStream_t stream);
 int cxn_loss_grad(const float* p, long long ld, const float* label, long long label_ld, void* g, long long ldg,

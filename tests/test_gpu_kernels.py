@@ -237,3 +237,34 @@ def test_arena_update_kernel_matches_reference_updaters(kind):
             if s.shadow_off >= 0:
                 sh = arena.shadow_view(s).view(s.rows, s.shadow_ld)[:, :s.cols]
                 assert torch.equal(sh, arena.w_view(s).view(s.rows, s.cols).to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("rows,cols", [(256, 1000), (37, 10), (64, 1), (5, 33)])
+def test_metric_error_kernel_counts_first_maximum_mismatches(rows, cols):
+    """the fused error metric against the reference rule (first maximum wins; width 1: score > 0 is class 1)"""
+    g = torch.Generator().manual_seed(rows * 131 + cols)
+    scores = torch.randn(rows, cols, generator=g)
+    if cols > 4:
+        scores[:, 3] = scores[:, 1]                      # exact ties: the first maximum must win
+        scores[: rows // 2, 1] = 10.0
+        scores[: rows // 2, 3] = 10.0
+    nclass = max(cols, 2)
+    label = torch.randint(0, nclass, (rows, 1), generator=g).float()
+    ld = (cols + 3) // 4 * 4
+    p = torch.zeros(rows, ld, device="cuda")
+    p[:, :cols] = scores.cuda()
+    lab = label.cuda()
+    acc = torch.zeros((), dtype=torch.float64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    for _ in range(2):                                   # accumulates
+        assert L.cxn_metric_error(p.data_ptr(), ld, lab.data_ptr(), 1, rows, cols, acc.data_ptr(), st) == 0
+    torch.cuda.synchronize()
+    if cols == 1:
+        pred = (scores[:, 0] > 0).long()
+    else:
+        mx = scores.max(dim=1, keepdim=True).values
+        pred = (scores == mx).float().argmax(dim=1)
+    expect = 2.0 * float((pred != label[:, 0].long()).sum())
+    assert float(acc.item()) == expect
