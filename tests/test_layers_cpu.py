@@ -241,3 +241,28 @@ def test_weight_init_modes():
         layer.init_connection([a], [b])
         layer.init_model()
         assert layer.wmat.shape == (40, 50) and chk(layer.wmat), rt
+
+
+@pytest.mark.parametrize("mode,kw,kw_eff", [("plain", 11, 11), ("pair", 11, 12), ("span", 11, 16), ("pair", 4, 4), ("span", 3, 16)])
+def test_native_conv_first_layer_weight_layouts_round_trip(mode, kw, kw_eff):
+    """internal weight layouts of the native first convolution (channel pitch 4; pixel pairs; 16-pixel
+    spans): checkpoint layout -> internal -> checkpoint is the identity and the added filter columns /
+    the fourth channel are structural zeros"""
+    from cxxnet_b200.layers import native
+    l = native.ConvolutionLayer()
+    for k, v in (("nchannel", "24"), ("kernel_size", str(kw)), ("stride", "2")):
+        l.set_param(k, v)
+    l.param.num_input_channel = 3
+    l.cin_pad = 4
+    l.pair = mode in ("pair", "span")
+    l.span = mode == "span"
+    torch.manual_seed(3)
+    w = torch.randn(24, 3 * kw * kw)
+    wi = l.weight_to_internal("wmat", w)
+    assert wi.shape == (1, 24, kw * kw_eff * 4)
+    w5 = wi.reshape(24, kw, kw_eff, 4)
+    assert float(w5[:, :, kw:, :].abs().sum()) == 0.0 and float(w5[..., 3].abs().sum()) == 0.0
+    # (oc, c, kh, kw) of the checkpoint is (oc, kh, kw, c) inside
+    assert torch.equal(w5[:, :, :kw, :3], w.reshape(24, 3, kw, kw).permute(0, 2, 3, 1))
+    back = l.weight_from_internal("wmat", wi)
+    assert torch.equal(back.reshape(24, -1), w)
