@@ -83,6 +83,7 @@ constexpr bool kProf = false;
 #endif
 
 struct GatherEntry { int off; short kh, kw; };
+constexpr int kHostFixedBytes = 1024 + 256 + kMaxGranules * 8 + 4 * 32 * 36 * 4;   // = Cfg::kFixedBytes
 
 // MH = number of 128-row accumulator halves of one tile (fprop only): with MH = 2 a CTA computes a
 // 256-row tile with two MMAs per k-step that share the filter tile, halving the filter's L2 traffic.
@@ -93,7 +94,9 @@ struct Cfg {
   static constexpr int kBBytes = BNMAX * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTableBytes = kMaxGranules * 8;
-  static constexpr int kFixedBytes = 1024 + 256 + kTableBytes;
+  // epilogue staging (weight gradient): per epilogue warp a 32 x 32 fp32 chunk, rows padded to 36 floats
+  static constexpr int kStageOutBytes = 4 * 32 * 36 * 4;
+  static constexpr int kFixedBytes = 1024 + 256 + kTableBytes + kStageOutBytes;
   static constexpr int kMaxStagesFit = (232448 - kFixedBytes) / kStageBytes;
   static constexpr int kMaxStages = kMaxStagesFit > 6 ? 6 : kMaxStagesFit;
   static constexpr int kAccStages = (2 * MH * BNMAX <= 512) ? 2 : 1;
@@ -132,6 +135,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
   const uint32_t bres_base = smem_base + nst * C::kABytes;
   const uint32_t bres_kb_bytes = (uint32_t)p.bn * BK * 2;
   GatherEntry* table = reinterpret_cast<GatherEntry*>(smem_gen + p.ring_bytes + 256);
+  float* stage_out = reinterpret_cast<float*>(smem_gen + p.ring_bytes + 256 + C::kTableBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -523,8 +527,37 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * MH * BNMAX + hc);
         tmem_ld32(taddr, v);
         tmem_ld_wait();
-        if (!row_ok) continue;
         const int lim = min(32, min(p.bn - c0, gn - n0));   // valid columns in this chunk
+        if (WGRAD && lim == 32 && (p.ldd & 3) == 0 && (p.strideD & 3) == 0 &&
+            (reinterpret_cast<uintptr_t>(p.D) & 15) == 0) {
+          // Transpose through shared memory: a thread owns an accumulator row, so direct reductions put
+          // 32 rows x 16 bytes into every instruction; staged, an instruction covers four complete
+          // 128-byte row segments.
+          float* sm = stage_out + quad * (32 * 36);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            *reinterpret_cast<float4*>(sm + lane * 36 + 4 * q) =
+                make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
+                            __uint_as_float(v[4 * q + 3]));
+          __syncwarp();
+          const int rsub = lane >> 3, cq = (lane & 7) * 4;
+          const long long row0 = (long long)m_blk * BMT + h * BM + quad * 32;
+          float* dbase = reinterpret_cast<float*>(p.D) + (long long)g * p.strideD + n0 + cq;
+          const bool col_ok = !(p.mask_period && (n0 + cq) % p.mask_period >= p.mask_valid);   // structural zeros (4-aligned)
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + rsub;
+            if (col_ok && row0 + r < gm) {
+              const float4 o4 = *reinterpret_cast<const float4*>(sm + r * 36 + cq);
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dbase + (row0 + r) * p.ldd), "f"(o4.x),
+                           "f"(o4.y), "f"(o4.z), "f"(o4.w)
+                           : "memory");
+            }
+          }
+          __syncwarp();
+          continue;
+        }
+        if (!row_ok) continue;
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
@@ -830,7 +863,7 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   p.dbg = g_tune_dbg;
   p.prof = g_prof;
   const int stage_bytes = (mh * BM + bnmax) * BK * 2;
-  int max_st = (232448 - (1024 + 256 + kMaxGranules * 8)) / stage_bytes;
+  int max_st = (232448 - kHostFixedBytes) / stage_bytes;
   if (max_st > 6) max_st = 6;
   p.stages = g_tune_stages ? g_tune_stages : max_st;
   CUtensorMap tm;
@@ -845,7 +878,7 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   p.ring_bytes = p.stages * stage_bytes;
   if (G == 1 && Ng <= p.bn && tiles > 2LL * grid) {
     const long long panel = ((long long)ceil_div(p.Kg, BK) * p.bn * BK * 2 + 1023) & ~1023LL;
-    const long long budget = 232448 - (1024 + 256 + kMaxGranules * 8);
+    const long long budget = 232448 - kHostFixedBytes;
     for (int try_mh = mh; try_mh >= 1 && !p.b_resident; --try_mh) {
       if (g_tune_mh && try_mh != mh) break;
       const long long a_bytes = (long long)try_mh * BM * BK * 2;

@@ -54,7 +54,10 @@ struct Cfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kTmemCols = kAccStages * BN;  // 128 / 256 / 512
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  // epilogue staging: per epilogue warp a 32 x 32 fp32 chunk, rows padded to 36 floats (conflict-free
+  // 128-bit shared accesses both ways)
+  static constexpr int kStageOutBytes = 4 * 32 * 36 * 4;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kStageOutBytes;
 };
 
 using namespace cxn::tc;
@@ -77,6 +80,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  float* stage_out = reinterpret_cast<float*>(smem_gen + C::kStages * C::kStageBytes + 256);
 
   const int tiles_m = ceil_div(p.M, BM);
   const int tiles_n = ceil_div(p.N, BN);
@@ -223,11 +227,46 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
         tmem_ld32(taddr, v);
         tmem_ld_wait();
+        const bool full = (n0 + 32 <= p.N);
+        // fp32 results (weight gradients) go through a shared-memory transpose: a thread owns a row of the
+        // accumulator, so direct stores put 32 rows x 16 bytes into every instruction; staged, each
+        // instruction writes four complete 128-byte row segments.
+        if (!out_bf16 && !atomic && full && bias == nullptr && !relu && (p.ldd & 3) == 0 &&
+            ((reinterpret_cast<uintptr_t>(p.D) & 15) == 0) && (p.strideD & 3) == 0) {
+          float* sm = stage_out + (warp - 2) * (32 * 36);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            float4 o4;
+            o4.x = has_work ? __uint_as_float(v[4 * q]) : 0.0f;
+            o4.y = has_work ? __uint_as_float(v[4 * q + 1]) : 0.0f;
+            o4.z = has_work ? __uint_as_float(v[4 * q + 2]) : 0.0f;
+            o4.w = has_work ? __uint_as_float(v[4 * q + 3]) : 0.0f;
+            *reinterpret_cast<float4*>(sm + lane * 36 + 4 * q) = o4;
+          }
+          __syncwarp();
+          const int rsub = lane >> 3, cq = (lane & 7) * 4;
+          float* dbase = reinterpret_cast<float*>(p.D) + (long long)z * p.strideD + n0 + cq;
+          const int row0 = m_blk * BM + quad * 32;
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + rsub;
+            if (row0 + r < p.M) {
+              float4 o4 = *reinterpret_cast<const float4*>(sm + r * 36 + cq);
+              float4* dp = reinterpret_cast<float4*>(dbase + (long long)(row0 + r) * p.ldd);
+              if (beta1) {
+                const float4 c4 = *dp;
+                o4.x += c4.x; o4.y += c4.y; o4.z += c4.z; o4.w += c4.w;
+              }
+              *dp = o4;
+            }
+          }
+          __syncwarp();
+          continue;
+        }
         if (!row_ok) continue;
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = has_work ? __uint_as_float(v[j]) : 0.0f;
-        const bool full = (n0 + 32 <= p.N);
         if (bias != nullptr) {
 #pragma unroll
           for (int j = 0; j < 32; ++j)
