@@ -48,7 +48,10 @@ __global__ void nchw_to_nhwc4_kernel(const float* __restrict__ src, bf16* __rest
 // C <= 4 with an even row pitch Wp >= W (pixel pitch 4): one thread converts a pixel pair and
 // stores it as 16 bytes; pixels at x >= W are written as zero.  This is the layout the first
 // convolution reads as [H][Wp/2] super-pixels of 8 channels (see ConvolutionLayer pair mode).
-__global__ void nchw_to_nhwc4_pitched_kernel(const float* __restrict__ src, bf16* __restrict__ dst, long long total,
+__device__ __forceinline__ float ld_as_float(const float* p) { return *p; }
+__device__ __forceinline__ float ld_as_float(const bf16* p) { return __bfloat162float(*p); }
+template <typename TS>
+__global__ void nchw_to_nhwc4_pitched_kernel(const TS* __restrict__ src, bf16* __restrict__ dst, long long total,
                                              int C, int H, int W, int Wp) {
   const int wp2 = Wp >> 1;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -57,13 +60,13 @@ __global__ void nchw_to_nhwc4_pitched_kernel(const float* __restrict__ src, bf16
     const int j = (int)(i - row * wp2);
     const long long n = row / H;
     const int y = (int)(row - n * H);
-    const float* s = src + (n * C * H + y) * (long long)W + 2 * j;
+    const TS* s = src + (n * C * H + y) * (long long)W + 2 * j;
     float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int c = 0; c < 4; ++c)
       if (c < C) {
-        if (2 * j < W) v[c] = s[(long long)c * H * W];
-        if (2 * j + 1 < W) v[4 + c] = s[(long long)c * H * W + 1];
+        if (2 * j < W) v[c] = ld_as_float(s + (long long)c * H * W);
+        if (2 * j + 1 < W) v[4 + c] = ld_as_float(s + (long long)c * H * W + 1);
       }
     uint4 o;
     __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
@@ -281,7 +284,16 @@ CXN_API int cxn_nchw_f32_to_nhwc4_pitched(const float* src, void* dst, int N, in
   if (N <= 0 || C <= 0 || H <= 0 || W <= 0) return 0;
   if (C > 4 || (Wp & 1) || Wp < W || (reinterpret_cast<uintptr_t>(dst) & 15)) return -1;
   const long long total = (long long)N * H * (Wp / 2);
-  nchw_to_nhwc4_pitched_kernel<<<ew_grid(total, 256, 16), 256, 0, st>>>(src, (bf16*)dst, total, C, H, W, Wp);
+  nchw_to_nhwc4_pitched_kernel<float><<<ew_grid(total, 256, 16), 256, 0, st>>>(src, (bf16*)dst, total, C, H, W, Wp);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+// the same from a bf16 NCHW source (a data pipeline that ships half the bytes over PCIe)
+CXN_API int cxn_nchw_bf16_to_nhwc4_pitched(const void* src, void* dst, int N, int C, int H, int W, int Wp, cudaStream_t st) {
+  if (N <= 0 || C <= 0 || H <= 0 || W <= 0) return 0;
+  if (C > 4 || (Wp & 1) || Wp < W || (reinterpret_cast<uintptr_t>(dst) & 15)) return -1;
+  const long long total = (long long)N * H * (Wp / 2);
+  nchw_to_nhwc4_pitched_kernel<bf16><<<ew_grid(total, 256, 16), 256, 0, st>>>((const bf16*)src, (bf16*)dst, total, C, H, W, Wp);
   CXN_CHECK_LAUNCH();
   return 0;
 }

@@ -320,6 +320,10 @@ class NeuralNet:
         # the compute of batch t
         self.in_stage = [torch.zeros((self.max_batch, c0, h0, w0), dtype=torch.float32, device=self.device)
                          for _ in range(2)]
+        # bf16 batches (a data pipeline that ships half the bytes over PCIe) get their own pair of slots,
+        # allocated when the first one arrives
+        self.in_stage_bf16 = None
+        self.stage_dtype = [torch.float32, torch.float32]
         self.hyper_prepared = False
         self.hyper_slot = 0
         self.copy_stream = torch.cuda.Stream(device=self.device)
@@ -505,7 +509,13 @@ class NeuralNet:
         self.stage_idx ^= 1
         slot = self.stage_idx
         main = torch.cuda.current_stream(self.device)
-        st = self.in_stage[slot][:b]
+        if batch.dtype == torch.bfloat16:
+            if self.in_stage_bf16 is None:
+                self.in_stage_bf16 = [torch.zeros_like(t, dtype=torch.bfloat16) for t in self.in_stage]
+            st = self.in_stage_bf16[slot][:b]
+        else:
+            st = self.in_stage[slot][:b]
+        self.stage_dtype[slot] = st.dtype
         if batch.device.type == "cpu" and batch.is_pinned():
             self.copy_stream.wait_event(self.stage_free[slot])
             with torch.cuda.stream(self.copy_stream):
@@ -519,7 +529,16 @@ class NeuralNet:
     def convert_staged(self, slot: int) -> None:
         """staging slot (fp32 NCHW) -> node 0 in the backend's layout"""
         n = self.nodes[0]
-        self._convert_in(n, self.in_stage[slot][:n.shape[0]])
+        b = n.shape[0]
+        if self.stage_dtype[slot] == torch.bfloat16:
+            src = self.in_stage_bf16[slot][:b]
+            if n.wpitch and not n.is_mat:
+                _, c, h, w = n.shape
+                ops.check(ops.lib().cxn_nchw_bf16_to_nhwc4_pitched(src.data_ptr(), n.act.ptr, b, c, h, w, n.wpitch,
+                                                                   ops.stream()), "nchw_bf16_to_nhwc4_pitched")
+                return
+            self.in_stage[slot][:b].copy_(src)      # other layouts: widen on the device, then the fp32 path
+        self._convert_in(n, self.in_stage[slot][:b])
 
     def release_stage(self, slot: int) -> None:
         self.stage_free[slot].record(torch.cuda.current_stream(self.device))

@@ -42,8 +42,8 @@ class DataBatch:
         self.data: Optional[torch.Tensor] = None
         self.extra_data: List[torch.Tensor] = []
 
-    def alloc_dense(self, shape, batch_size, label_width, pin=False):
-        self.data = torch.zeros(tuple(shape), dtype=torch.float32)
+    def alloc_dense(self, shape, batch_size, label_width, pin=False, dtype=torch.float32):
+        self.data = torch.zeros(tuple(shape), dtype=dtype)
         self.label = torch.zeros((batch_size, label_width), dtype=torch.float32)
         if pin and torch.cuda.is_available():
             self.data = self.data.pin_memory()
@@ -52,8 +52,8 @@ class DataBatch:
         self.batch_size = batch_size
 
     def copy_from(self, o: "DataBatch"):
-        if self.data is None or self.data.shape != o.data.shape:
-            self.alloc_dense(o.data.shape, o.batch_size, o.label.shape[1], pin=True)
+        if self.data is None or self.data.shape != o.data.shape or self.data.dtype != o.data.dtype:
+            self.alloc_dense(o.data.shape, o.batch_size, o.label.shape[1], pin=True, dtype=o.data.dtype)
         self.data.copy_(o.data)
         self.label.copy_(o.label)
         if o.inst_index is not None:

@@ -706,9 +706,15 @@ class BatchAdaptIterator(IIterator):
         self.test_skipread = 0
         self.head = 1
         self.out = DataBatch()
+        self.input_dtype = "fp32"     # bf16: batches leave the iterator as bf16 (half the H2D bytes; the b200
+        self._half = None             # backend computes in bf16 anyway).  Not a reference option.
 
     def set_param(self, name, val):
         self.base.set_param(name, val)
+        if name == "input_dtype":
+            if val not in ("fp32", "bf16"):
+                raise ValueError("input_dtype must be fp32 or bf16")
+            self.input_dtype = val
         if name == "batch_size": self.batch_size = int(val)
         if name == "input_shape": self.shape = tuple(int(x) for x in val.split(","))
         if name == "label_width": self.label_width = int(val)
@@ -721,6 +727,11 @@ class BatchAdaptIterator(IIterator):
         self.out.alloc_dense((self.batch_size,) + tuple(self.shape), self.batch_size, self.label_width, pin=True)
         self._data_np = self.out.data.numpy()
         self._label_np = self.out.label.numpy()
+        if self.input_dtype == "bf16":
+            self._half = DataBatch()
+            self._half.alloc_dense((self.batch_size,) + tuple(self.shape), self.batch_size, self.label_width, pin=True,
+                                   dtype=torch.bfloat16)
+            self._half.label, self._half.inst_index = self.out.label, self.out.inst_index
 
     def before_first(self):
         if self.round_batch == 0 or self.num_overflow == 0:
@@ -767,6 +778,11 @@ class BatchAdaptIterator(IIterator):
 
     def value(self):
         assert self.head == 0, "must call Next to get value"
+        if self._half is not None:
+            self._half.data.copy_(self.out.data)      # fp32 -> bf16 on the producer side
+            self._half.batch_size, self._half.num_batch_padd = self.out.batch_size, self.out.num_batch_padd
+            self._half.extra_data = self.out.extra_data
+            return self._half
         return self.out
 
 

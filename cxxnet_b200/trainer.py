@@ -333,7 +333,8 @@ class NetTrainer:
         net.arena.prepare_hyper(self.epoch_counter, slot)
         net.hyper_prepared, net.hyper_slot = True, slot
         try:
-            entry = self._graphs.get(slot)
+            gkey = (slot, net.stage_dtype[slot])
+            entry = self._graphs.get(gkey)
             if entry is not None:
                 g, launches, cnt = entry
                 g.replay()
@@ -344,7 +345,7 @@ class NetTrainer:
                 self._step_body(slot)
             else:
                 try:
-                    self._capture(slot, rows)
+                    self._capture(slot, rows, gkey)
                 except Exception as exc:      # a layer that cannot be captured (host round trips): stay eager
                     import warnings
                     warnings.warn("cuda_graph: capture failed (%r), continuing without graphs" % (exc,))
@@ -359,7 +360,7 @@ class NetTrainer:
         self._graph_steps += 1
         self.epoch_counter += 1
 
-    def _capture(self, slot: int, rows: int) -> None:
+    def _capture(self, slot: int, rows: int, gkey) -> None:
         """capture one step for this staging slot; the capture itself does not execute, so the step is
         replayed once right away"""
         net = self.net
@@ -375,7 +376,7 @@ class NetTrainer:
         cnt = (self.train_metric.evals[0].cnt_inst - cnt0[0]) if self.train_metric.evals else 0
         for e, c in zip(self.train_metric.evals, cnt0):
             e.cnt_inst = c
-        self._graphs[slot] = (g, launches, cnt)
+        self._graphs[gkey] = (g, launches, cnt)
         ops.lib().cxn_launch_count_add(-launches & 0xFFFFFFFFFFFFFFFF)   # the captured launches did not run
         g.replay()
         ops.lib().cxn_launch_count_add(launches)

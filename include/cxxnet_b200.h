@@ -87,6 +87,7 @@ int cxn_col2im_nhwc(const void* col, void* dx, int N, int H, int W, int C, int G
 int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C, int HW, int ldc, cudaStream_t stream);
 /* C <= 4 input image -> NHWC bf16 with pixel pitch 4 and an even row pitch Wp >= W (pad pixels zero) */
 int cxn_nchw_f32_to_nhwc4_pitched(const float* src, void* dst, int N, int C, int H, int W, int Wp, cudaStream_t stream);
+int cxn_nchw_bf16_to_nhwc4_pitched(const void* src, void* dst, int N, int C, int H, int W, int Wp, cudaStream_t stream);
 int cxn_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int N, int C, int HW, int ldc, cudaStream_t stream);
 /* flatten in (c,h,w) order and its inverse.  Reference: src/layer/flatten_layer-inl.hpp:10-39. */
 int cxn_bf16_hwc_chw(const void* src, void* dst, int N, int C, int HW, long long src_img, long long dst_img,

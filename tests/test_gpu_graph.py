@@ -75,3 +75,29 @@ def test_captured_step_trains_like_eager_step():
     torch.cuda.synchronize()
     assert mg.cnt_inst == steps * 16 + 11 + 16
     assert graph.epoch_counter == steps + 2
+
+
+def test_bf16_batches_train_exactly_like_fp32_batches():
+    """a bf16 batch is the fp32 batch rounded on the host instead of on the device: same bits reach the
+    first layer, so the two runs may differ only through the atomics of the weight-gradient kernels"""
+    a = make_trainer(CONF, cuda_graph=1)
+    b = make_trainer(CONF, cuda_graph=1)
+    copy_weights(a, b)
+    batches = [make_batch((16, 3, 33, 33), seed=s, pin=True) for s in range(3)]
+    halves = []
+    for x in batches:
+        h = make_batch((16, 3, 33, 33), seed=0, pin=True)
+        h.data = x.data.to(torch.bfloat16).pin_memory()
+        h.label = x.label
+        halves.append(h)
+    for i in range(8):
+        a.update(batches[i % 3])
+        b.update(halves[i % 3])
+    torch.cuda.synchronize()
+    assert b.net.in_stage_bf16 is not None and len(b._graphs) == 2
+    for i, c in enumerate(a.net.connections):
+        for tag, _, _ in c.layer.weights():
+            wa, _ = a.net.get_weight(i, tag)
+            wb, _ = b.net.get_weight(i, tag)
+            assert rel_err(wa, wb) < 2e-2, "layer %d %s diverged" % (i, tag)
+    assert a.train_metric.evals[0].cnt_inst == b.train_metric.evals[0].cnt_inst == 8 * 16

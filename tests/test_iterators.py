@@ -234,3 +234,18 @@ def test_im2bin_tool_and_native_page_reader(tmp_path):
         outs.append(it.value().data.clone())
         it.close()
     assert torch.equal(outs[0], outs[1])
+
+
+def test_input_dtype_bf16_batches_through_the_thread_buffer():
+    """`input_dtype = bf16`: batches leave the chain as bf16 tensors holding the rounded fp32 values
+    (half the host-to-device bytes); labels and indices are untouched"""
+    want = [(b.data.clone(), b.label.clone(), b.inst_index.copy()) for b in _mk(SYN % "")]
+    cfg = (SYN % "  input_dtype = bf16").replace("iter = end", "iter = threadbuffer\niter = end")
+    it = create_iterator(parse_config_string(cfg))
+    it.init()
+    got = [(b.data.clone(), b.label.clone(), b.inst_index.copy()) for b in it]
+    it.close()
+    assert len(got) == len(want)
+    for (d, l, i), (wd, wl, wi) in zip(got, want):
+        assert d.dtype == torch.bfloat16 and torch.equal(d, wd.to(torch.bfloat16))
+        assert torch.equal(l, wl) and (i == wi).all()
