@@ -20,13 +20,12 @@ SHAPES = [("conv2 fprop", 27, 96, 2, 256, 5, 2), ("conv3 fprop", 13, 256, 1, 384
           ("conv4 fprop", 13, 384, 2, 384, 3, 1), ("conv5 fprop", 13, 384, 2, 256, 3, 1),
           ("conv2 dgrad", 27, 256, 2, 96, 5, 2), ("conv3 dgrad", 13, 384, 1, 256, 3, 1),
           ("conv4 dgrad", 13, 384, 2, 384, 3, 1), ("conv5 dgrad", 13, 256, 2, 384, 3, 1)]
-CONFIGS = [("gather mh1 deep", dict(atma=0, mh=1, l1=0, tap=0, stages=-1)),
-           ("tma mh1 natural", dict(atma=1, mh=1, tap=0, stages=-1)),
-           ("tma mh1 tap-inner", dict(atma=1, mh=1, tap=1, stages=-1)),
-           ("tma mh2x128 st4", dict(atma=1, mh=2, tap=0, stages=4, bn=128)),
-           ("tma mh2x256 st3", dict(atma=1, mh=2, tap=0, stages=3, bn=256)),
-           ("tma mh2x256 st3 tap-inner", dict(atma=1, mh=2, tap=1, stages=3, bn=256)),
-           ("auto", dict(atma=-1, mh=0, l1=-1, tap=-1, stages=0))]
+CONFIGS = [("gather 128-row", dict(atma=0, mh=1, stages=-1)),
+           ("gather 256-row", dict(atma=0, mh=2, bn=128)),
+           ("tma 128-row", dict(atma=1, mh=1, stages=-1)),
+           ("tma 256x128", dict(atma=1, mh=2, stages=4, bn=128)),
+           ("tma 256x256", dict(atma=1, mh=2, stages=3, bn=256)),
+           ("auto", dict(atma=-1, mh=0, stages=0))]
 WCONFIGS = [("gather", dict(atma=0)), ("tma", dict(atma=1))]
 
 
@@ -36,8 +35,6 @@ def set_knobs(c, ocg):
     if st == -1:
         st = 4 if ocg > 128 else 6
     L.cxn_conv_tune(1, st)
-    L.cxn_conv_tune(2, c.get("l1", -1))
-    L.cxn_conv_tune(3, c.get("tap", -1))
     L.cxn_conv_tune(4, c.get("bn", 0))
     L.cxn_conv_tune(5, c.get("dbg", 0))
     L.cxn_conv_tune(6, c.get("atma", -1))

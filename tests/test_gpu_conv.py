@@ -96,3 +96,21 @@ def test_conv_odd_shapes():
 
 def test_conv_many_tiles_persistent():
     _case(64, 32, 32, 32, 64, 1, 3, 3, 1, 1)                    # 65536 rows: 512 m-tiles over 148 SMs
+
+
+@pytest.mark.parametrize("atma", [1, 0])
+def test_conv_im2col_tma_and_gather_routes_agree_with_reference(atma):
+    """channels-per-group % 64 == 0 takes the im2col-mode TMA route by default; the same problems through the
+    gather warps (cxn_conv_tune key 6) must give the same answers.  Strides, asymmetric kernels, padding
+    larger than one, groups, row counts that are not a multiple of the tile."""
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    L.cxn_conv_tune(6, atma)
+    try:
+        _case(3, 64, 17, 19, 48, 1, 3, 3, 2, 1)                  # stride 2, odd extents, M tail
+        _case(2, 128, 12, 12, 64, 2, 5, 3, 1, 2)                 # groups of 64 channels, 5x3 filter, pad 2
+        _case(1, 192, 7, 7, 32, 1, 1, 1, 1, 0)                   # 1x1, 49 rows only
+        _case(9, 64, 20, 20, 128, 1, 4, 4, 4, 0, relu=False)     # stride = kernel (no overlap)
+        _case(40, 64, 13, 13, 96, 1, 3, 3, 1, 1)                 # enough rows for the row-paired (256-row) tiles
+    finally:
+        L.cxn_conv_tune(6, -1)
