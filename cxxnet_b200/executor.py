@@ -566,6 +566,8 @@ class NeuralNet:
             for c in self.connections:
                 c.layer.forward(is_train, c.nodes_in, c.nodes_out)
             return
+        if self.exchange is not None:
+            self.exchange.publish_pending()
         for i, c in enumerate(self.connections):
             if self.exchange is not None:
                 self.exchange.wait_layer(i)   # UpdateWait: this layer's weights from the last exchange

@@ -117,6 +117,14 @@ class GradExchange:
         # a step captured into a CUDA graph replays with advancing barriers.
         # timing experiments only (results are wrong): comma list of conv | gather | publish | fcgemm
         self._skip = set(filter(None, os.environ.get("CXN_XCHG_SKIP", "").split(",")))
+        # The bf16 rows a rank owns are published to the other ranks at the START of the next forward pass
+        # (on the exchange stream, under the convolution layers) instead of at the end of backward, where the
+        # transfer competed with the convolution buckets for NVLink and was not hidden (8 GPUs: 181 us).
+        # Measured: 8 GPUs 1.016 -> 0.957 ms/step, 4 GPUs 1.184 -> 1.149, but 2 GPUs 1.616 -> 1.687 (half of all
+        # fully connected weights then cross one link while the first convolutions run), hence world >= 4.
+        env = os.environ.get("CXN_XCHG_DEFER_PUBLISH")
+        self.defer_publish = (env != "0") if env is not None else self.world >= 4
+        self._pending_pub: List[FcShard] = []
         self.epoch = torch.zeros(1, dtype=torch.int64, device=self.device)
         L.cxn_xchg_set_epoch_ptr(self.epoch.data_ptr())
         dist.barrier()
@@ -230,15 +238,46 @@ class GradExchange:
                     a.update(e0 // a.chunk, (e0 + sh.my_rows * nin + a.chunk - 1) // a.chunk)
                 if sh.bseg is not None:
                     a.update(sh.bseg.start // a.chunk, (sh.bseg.start + sh.bseg.n + a.chunk - 1) // a.chunk)
-                # 3. publish the updated bf16 rows to every rank
-                sld = sh.wseg.shadow_ld
-                src = a.shadow.data_ptr() + (sh.wseg.shadow_off + sh.row0 * sld) * 2
-                dst = self.off["shadow"] + sh.wseg.shadow_off * 2
-                if "publish" not in self._skip:
-                    self._allgather([(src, dst, sh.rows_per_rank * sld * 2, sh.my_rows * sld * 2)],
-                                    sh.slot_pub, self.counter, self.stream.cuda_stream)
+                # 3. publish the updated bf16 rows to every rank (now, or at the start of the next forward)
+                if self.defer_publish:
+                    if sh not in self._pending_pub:
+                        self._pending_pub.append(sh)
+                else:
+                    self._publish(sh)
             sh.event.record(self.stream)
             sh.pending = True
+
+    def _publish(self, sh) -> None:
+        """all-gather of this rank's updated bf16 rows of one sharded layer (exchange stream)"""
+        a = self.arena
+        sld = sh.wseg.shadow_ld
+        src = a.shadow.data_ptr() + (sh.wseg.shadow_off + sh.row0 * sld) * 2
+        dst = self.off["shadow"] + sh.wseg.shadow_off * 2
+        if "publish" not in self._skip:
+            self._allgather([(src, dst, sh.rows_per_rank * sld * 2, sh.my_rows * sld * 2)],
+                            sh.slot_pub, self.counter, self.stream.cuda_stream)
+
+    def publish_pending(self) -> None:
+        """called at the start of every forward pass: launch the deferred publishes on the exchange stream;
+        the forward of each sharded layer waits for its own (wait_layer).  Every rank has long passed the
+        gather barrier of the step that produced these rows, i.e. nobody still reads the old ones."""
+        if not self._pending_pub:
+            return
+        main = torch.cuda.current_stream(self.device)
+        self.ready.record(main)
+        self.stream.wait_event(self.ready)
+        with torch.cuda.stream(self.stream):
+            for sh in self._pending_pub:
+                self._publish(sh)
+                sh.event.record(self.stream)
+                sh.pending = True
+        self._pending_pub = []
+
+    def after_replayed_step(self) -> None:
+        """a replayed CUDA graph ran the sharded updates without touching host state: their rows are
+        unpublished until the next forward pass (replayed or eager) does it"""
+        if self.defer_publish:
+            self._pending_pub = [sh for sh in self.shards.values()]
 
     def gather_master(self) -> None:
         """refresh the fp32 masters of foreign weight shards from their owners (collective)."""

@@ -341,6 +341,8 @@ class NetTrainer:
                 ops.lib().cxn_launch_count_add(launches)
                 for e in self.train_metric.evals:
                     e.cnt_inst += cnt
+                if net.exchange is not None:
+                    net.exchange.after_replayed_step()
             elif self._graph_steps < self.graph_warmup:
                 self._step_body(slot)
             else:
@@ -366,6 +368,7 @@ class NetTrainer:
         net = self.net
         if net.exchange is not None:
             net.exchange.wait_all()
+            net.exchange.after_replayed_step()     # the captured forward must contain the deferred publishes
         torch.cuda.synchronize(self.device)
         before = ops.launch_count()
         cnt0 = [e.cnt_inst for e in self.train_metric.evals]
@@ -382,6 +385,8 @@ class NetTrainer:
         ops.lib().cxn_launch_count_add(launches)
         for e in self.train_metric.evals:
             e.cnt_inst += cnt
+        if net.exchange is not None:
+            net.exchange.after_replayed_step()
 
     @staticmethod
     def _scores2d(t: torch.Tensor) -> torch.Tensor:
