@@ -112,6 +112,8 @@ int cxn_counter_add(unsigned long long* counter, unsigned long long inc, cudaStr
  * src/layer/convolution_layer-inl.hpp:117-119. */
 int cxn_colsum_bf16(const void* x, long long rows, int cols, long long ld, float* out, int accumulate,
                     cudaStream_t stream);
+/* the vectorised kernel behind cxn_colsum_bf16 (cols % 8 == 0, 16-byte aligned rows): out[c] += sum_r x[r][c] */
+int cxn_colsum_bf16_vec(const void* x, long long rows, int cols, long long ld, float* out, cudaStream_t stream);
 
 /* ---- K8/K9 pooling: mode 0 max, 1 sum, 2 avg; ceil-style output, clipped windows, avg / k*k,
  * max-unpool to every tie; relu=1 is relu_max_pooling.  src/layer/pooling_layer-inl.hpp:45-106. */
