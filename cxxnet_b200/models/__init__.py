@@ -209,9 +209,15 @@ batch_size = %(batch)d
 dev = %(dev)s
 updater = %(updater)s
 random_type = xavier
-eta = 0.01
+init_sigma = 0.01
 momentum = 0.9
-wd = 0.0005
+wmat:lr  = 0.001
+wmat:wd  = 0.0005
+bias:wd  = 0.000
+bias:lr  = 0.002
+lr:schedule = expdecay
+lr:gamma = 0.1
+lr:step = 20000
 metric = error
 metric = logloss
 %(extra)s
