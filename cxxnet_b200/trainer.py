@@ -80,6 +80,7 @@ class NetTrainer:
         # exchange, update) is captured into a CUDA graph per input staging slot and replayed; the host
         # then only stages the batch and launches one graph per step
         self.cuda_graph = 0
+        self.test_on_server = 0
         self.graph_warmup = 3
         self._graphs = {}            # staging slot -> (torch.cuda.CUDAGraph, launches inside)
         self._graph_rows = -1
@@ -98,6 +99,13 @@ class NetTrainer:
         if name == "param_server": self.type_pserver = val
         if name == "backend": self.backend_override = val
         if name == "cuda_graph": self.cuda_graph = int(val)
+        # reference async_updater-inl.hpp:148-153: replicate the weights on the server and assert equality every
+        # round.  Here: every round all ranks compare their replicas with rank 0's (collective).
+        if name == "test_on_server": self.test_on_server = int(val)
+        # Parameter-server tuning keys of the reference (async_updater-inl.hpp:155-184, fullc_layer-inl.hpp) that
+        # have nothing to act on here - there is no server, pulls are not deferred, arrays are not chunked by
+        # the transport: accepted and ignored, like every key a consumer does not know.
+        #   pull_at_backprop, bigarray_bound, update_on_server, init_on_worker, force_contiguous
         if name.startswith("metric"):
             m = re.match(r"metric\[([^,]+),([^\]]+)\]", name)
             if m:
@@ -227,6 +235,11 @@ class NetTrainer:
 
     def start_round(self, r: int) -> None:
         self.net.start_round(r)
+        ex = getattr(self.net, "exchange", None)
+        if self.test_on_server and ex is not None:
+            d = ex.check_replicas()
+            if d != 0.0:
+                raise RuntimeError("test_on_server: weight replicas differ from rank 0 by up to %g at round %d" % (d, r))
 
     # ------------------------------------------------------------------ batch slicing
     def _slice(self, n: int) -> Tuple[int, int]:

@@ -136,3 +136,13 @@ def test_layer_type_ids_and_pairtest_encoding():
     assert nc.get_layer_type("pairtest-conv-conv") == 1024 * 10 + 10
     with pytest.raises(ConfigError):
         nc.get_layer_type("nonsense")
+
+
+def test_parameter_server_tuning_keys_are_accepted():
+    """keys of the reference's async updater that have nothing to act on here must not be errors"""
+    from cxxnet_b200.trainer import NetTrainer
+    tr = NetTrainer()
+    for k, v in (("pull_at_backprop", "0"), ("bigarray_bound", "1000000"), ("update_on_server", "0"),
+                 ("init_on_worker", "1"), ("force_contiguous", "1"), ("test_on_server", "1")):
+        tr.set_param(k, v)
+    assert tr.test_on_server == 1
