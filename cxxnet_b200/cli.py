@@ -328,6 +328,9 @@ class LearnTask:
                     err.write(line + "\n")
                     err.flush()
             elapsed = int(time.time() - start)
+            report = self.net_trainer.timing_report()
+            if report and self.rank == 0:
+                print("\n" + report)
             self.save_model()
         if not self.silent and self.rank == 0:
             print("\nupdating end, %d sec in all" % elapsed)

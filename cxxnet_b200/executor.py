@@ -45,6 +45,7 @@ class NeuralNet:
     def __init__(self, cfg: NetConfig, max_batch: int, seed: int, device: torch.device, backend: str = "ref",
                  silent: int = 0, world_size: int = 1, rank: int = 0, arena_alloc=None):
         self.cfg = cfg
+        self.timer = None        # utils.timing.LayerTimer when `layer_timing = 1`
         self.max_batch = max_batch
         self.seed = seed
         self.device = device
@@ -562,26 +563,37 @@ class NeuralNet:
                       "nchw_to_nhwc")
 
     def forward(self, is_train: bool) -> None:
+        tm = self.timer
         if self.backend == "ref":
-            for c in self.connections:
+            for i, c in enumerate(self.connections):
+                t0 = tm.begin() if tm else None
                 c.layer.forward(is_train, c.nodes_in, c.nodes_out)
+                if tm:
+                    tm.end("f", i, t0)
             return
         if self.exchange is not None:
             self.exchange.publish_pending()
         for i, c in enumerate(self.connections):
             if self.exchange is not None:
                 self.exchange.wait_layer(i)   # UpdateWait: this layer's weights from the last exchange
+            t0 = tm.begin() if tm else None
             if c.native:
                 c.layer.b200_forward(self, is_train)
             else:
                 self._bridge_forward(c, is_train)
+            if tm:
+                tm.end("f", i, t0)
 
     def backprop(self, prop_to_input: bool, need_update: bool, epoch: int) -> None:
         n = len(self.connections)
+        tm = self.timer
         if self.backend == "ref":
             for i in range(n - 1, -1, -1):
                 c = self.connections[i]
+                t0 = tm.begin() if tm else None
                 c.layer.backprop(i != 0 or prop_to_input, c.nodes_in, c.nodes_out)
+                if tm:
+                    tm.end("b", i, t0)
                 if need_update:
                     for u in self.updaters[i]:
                         if self.world_size > 1:
@@ -601,10 +613,13 @@ class NeuralNet:
         for i in range(n - 1, -1, -1):
             c = self.connections[i]
             prop = i != 0 or prop_to_input
+            t0 = tm.begin() if tm else None
             if c.native:
                 c.layer.b200_backprop(self, prop)
             else:
                 self._bridge_backprop(c, prop)
+            if tm:
+                tm.end("b", i, t0)
             if need_update and self.exchange is not None:
                 self.exchange.layer_done(i)
         if need_update and self.exchange is None:

@@ -81,6 +81,7 @@ class NetTrainer:
         # then only stages the batch and launches one graph per step
         self.cuda_graph = 0
         self.test_on_server = 0
+        self.layer_timing = 0
         self.graph_warmup = 3
         self._graphs = {}            # staging slot -> (torch.cuda.CUDAGraph, launches inside)
         self._graph_rows = -1
@@ -102,6 +103,7 @@ class NetTrainer:
         # reference async_updater-inl.hpp:148-153: replicate the weights on the server and assert equality every
         # round.  Here: every round all ranks compare their replicas with rank 0's (collective).
         if name == "test_on_server": self.test_on_server = int(val)
+        if name == "layer_timing": self.layer_timing = int(val)     # per-layer timers, see utils/timing.py
         # Parameter-server tuning keys of the reference (async_updater-inl.hpp:155-184, fullc_layer-inl.hpp) that
         # have nothing to act on here - there is no server, pulls are not deferred, arrays are not chunked by
         # the transport: accepted and ignored, like every key a consumer does not know.
@@ -171,6 +173,13 @@ class NetTrainer:
         self._resolve_devices()
         self.net = NeuralNet(self.net_cfg, self.step, self.rank + self.seed * 100, self.device, self.backend,
                              silent=self.silent or self.rank != 0, world_size=self.world_size, rank=self.rank)
+        if self.layer_timing:
+            from .utils.timing import LayerTimer
+            def names():
+                return ["%s:%s" % (c.layer.type_name, self.net_cfg.layers[i].name or i)
+                        for i, c in enumerate(self.net.connections)]
+            self.net.timer = LayerTimer(names, self.device.type == "cuda")
+            self.cuda_graph = 0          # a captured step cannot be bracketed
         if self.silent == 0 and self.rank == 0:
             print("finish initialization with %d devices" % max(self.world_size, 1))
         self.eval_req = []
@@ -240,6 +249,16 @@ class NetTrainer:
             d = ex.check_replicas()
             if d != 0.0:
                 raise RuntimeError("test_on_server: weight replicas differ from rank 0 by up to %g at round %d" % (d, r))
+
+    def timing_report(self, reset: bool = True) -> str:
+        """per-layer forward / backward time since the last report (`layer_timing = 1`), else an empty string"""
+        tm = self.net.timer if self.net is not None else None
+        if tm is None:
+            return ""
+        text = tm.report()
+        if reset:
+            tm.reset()
+        return text
 
     # ------------------------------------------------------------------ batch slicing
     def _slice(self, n: int) -> Tuple[int, int]:

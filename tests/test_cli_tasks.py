@@ -177,3 +177,16 @@ def test_get_set_weight_roundtrip_and_update_period():
     b.update(full)
     assert a.epoch_counter == 1
     assert np.allclose(a.get_weight("fc2", "wmat")[0], b.get_weight("fc2", "wmat")[0], atol=1e-6)
+
+
+def test_layer_timing_reports_every_layer(tmp_path):
+    """`layer_timing = 1`: a forward / backward table per round on stdout, one row per layer"""
+    conf = tmp_path / "mnist.conf"
+    conf.write_text(CONF % {"rounds": 1, "model_dir": tmp_path / "models", "pred": tmp_path / "pred.txt"})
+    r = _run([str(conf), "layer_timing=1"], tmp_path)
+    assert "layer timing (mean us per step" in r.stdout
+    rows = [l for l in r.stdout.splitlines() if re.match(r"\s+\d+ (fullc|sigmoid|softmax):", l)]
+    assert len(rows) == 4, r.stdout
+    fwd = [float(l.split()[2]) for l in rows]
+    bwd = [float(l.split()[3]) for l in rows]
+    assert all(v > 0 for v in fwd) and all(v > 0 for v in bwd)

@@ -91,3 +91,16 @@ def test_cli_trains_with_captured_steps_and_bf16_batches(tmp_path):
     ref = (tmp_path / "pred.txt").read_text().split()
     assert len(fast) == len(ref) == 200
     assert sum(a != b for a, b in zip(fast, ref)) <= 4      # bf16 vs fp32 may flip a borderline instance
+
+
+def test_cli_layer_timing_on_the_gpu(tmp_path):
+    """`layer_timing = 1` brackets every layer with CUDA events (and runs eagerly: a captured step
+    cannot be bracketed)"""
+    conf = tmp_path / "conv.conf"
+    conf.write_text(CONF % {"model_dir": tmp_path / "models", "pred": tmp_path / "pred.txt"})
+    r = _run([str(conf), "layer_timing=1", "num_round=1", "max_round=1"], tmp_path)
+    assert "layer timing (mean us per step" in r.stdout
+    rows = [l for l in r.stdout.splitlines() if re.match(r"\s+\d+ (conv|relu|max_pooling|flatten|fullc|dropout|softmax):", l)]
+    assert len(rows) == 9, r.stdout
+    conv = [l for l in rows if " conv:" in l][0].split()
+    assert float(conv[2]) > 0 and float(conv[3]) > 0
