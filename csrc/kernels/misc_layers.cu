@@ -208,9 +208,60 @@ __global__ void prelu_kernel(const bf16* __restrict__ x, const bf16* __restrict_
   }
 }
 
+// ---------------------------------------------------------------- insanity (randomised leaky ReLU)
+// reference src/layer/insanity_layer-inl.hpp:13-102: y = x > 0 ? x : x / s, s ~ U[lb, ub) per element while
+// training, (lb + ub) / 2 otherwise; backward multiplies dy by 1 or 1 / s with the same s (Philox stream
+// regenerated from (seed, step counter), nothing stored).
+template <bool BWD>
+__global__ void insanity_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, bf16* __restrict__ out,
+                                long long rows, int cols, long long ldx, long long ldo, float lb, float ub, int random,
+                                unsigned long long seed, const unsigned long long* __restrict__ counter) {
+  const unsigned long long offset = counter ? *counter : 0ull;
+  const Philox rng(seed);
+  const long long total = rows * cols;
+  const long long nquads = (total + 3) / 4;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < nquads;
+       q += (long long)gridDim.x * blockDim.x) {
+    uint32_t r4[4] = {0, 0, 0, 0};
+    if (random) rng((unsigned long long)q, offset, r4);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long i = q * 4 + j;
+      if (i >= total) break;
+      const long long r = i / cols;
+      const int c = (int)(i - r * cols);
+      const float s = random ? u01(r4[j]) * (ub - lb) + lb : 0.5f * (lb + ub);
+      const float xv = __bfloat162float(x[r * ldx + c]);
+      float o;
+      if (!BWD) o = xv > 0.0f ? xv : xv / s;
+      else o = (xv > 0.0f ? 1.0f : 1.0f / s) * __bfloat162float(dy[r * ldo + c]);
+      out[r * ldo + c] = __float2bfloat16(o);
+    }
+  }
+}
+
 }  // namespace cxn
 
 using namespace cxn;
+
+CXN_API int cxn_insanity_fwd(const void* x, void* y, long long rows, int cols, long long ldx, long long ldy, float lb,
+                             float ub, int random, unsigned long long seed, const unsigned long long* counter,
+                             cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  insanity_kernel<false><<<ew_grid((rows * cols + 3) / 4, 256), 256, 0, st>>>((const bf16*)x, nullptr, (bf16*)y, rows, cols,
+                                                                               ldx, ldy, lb, ub, random, seed, counter);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+CXN_API int cxn_insanity_bwd(const void* x, const void* dy, void* dx, long long rows, int cols, long long ldx, long long ldg,
+                             float lb, float ub, int random, unsigned long long seed, const unsigned long long* counter,
+                             cudaStream_t st) {
+  if (rows <= 0 || cols <= 0) return 0;
+  insanity_kernel<true><<<ew_grid((rows * cols + 3) / 4, 256), 256, 0, st>>>((const bf16*)x, (const bf16*)dy, (bf16*)dx, rows,
+                                                                              cols, ldx, ldg, lb, ub, random, seed, counter);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
 
 // x[r][c] += bias[c]  (in place allowed)
 CXN_API int cxn_bias_add(const void* x, void* y, long long rows, int cols, long long ld, const float* bias, cudaStream_t st) {

@@ -34,12 +34,12 @@ _NATIVE = {
     nc.kSplit: native.SplitLayer,
     nc.kPRelu: native.PReluLayer,
     nc.kBatchNorm: native.BatchNormLayer,
+    nc.kInsanity: native.InsanityLayer,
+    nc.kFixConnect: native.FixConnectLayer,
 }
 
 _REF_ONLY = {
-    nc.kInsanity: zoo.InsanityLayer,
     nc.kInsanityPooling: zoo.InsanityPoolingLayer,
-    nc.kFixConnect: zoo.FixConnectLayer,
 }
 
 

@@ -673,3 +673,67 @@ class ConcatLayer(_NativeConcat, zoo.ConcatLayer):
 class ChConcatLayer(_NativeConcat, zoo.ChConcatLayer):
     pass
 
+
+# ----------------------------------------------------------------------------- insanity / fixconn
+class InsanityLayer(zoo.InsanityLayer):
+    """randomised leaky ReLU: the per-element divisor is a Philox stream regenerated in backward.  Unlike
+    the reference the input node keeps its value (the reference overwrites it with the output)."""
+    has_b200 = True
+
+    @property
+    def graph_unsafe(self):
+        # [lb, ub] move on the host while the calm-down schedule is active: a captured step would freeze them
+        return self.sat_end > self.sat_start
+
+    def _seed(self, ex):
+        return (ex.seed * 1000003 + self.layer_index * 7919 + 977) & 0xFFFFFFFFFFFFFFFF
+
+    def b200_forward(self, ex, is_train):
+        self._advance()
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        rows, cols, ld = _mat_view(x, x.act)
+        self._random = 1 if is_train else 0
+        ops.check(ops.lib().cxn_insanity_fwd(x.act.ptr, y.act.ptr, rows, cols, ld, y.act.ld, float(self.lb), float(self.ub),
+                                             self._random, self._seed(ex), ex.step_counter.data_ptr(), ops.stream()),
+                  "insanity_fwd")
+
+    def b200_backprop(self, ex, prop_grad):
+        if not prop_grad:
+            return
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        rows, cols, ld = _mat_view(x, x.act)
+        ops.check(ops.lib().cxn_insanity_bwd(x.act.ptr, y.grad.ptr, x.grad.ptr, rows, cols, ld, y.grad.ld, float(self.lb),
+                                             float(self.ub), getattr(self, "_random", 0), self._seed(ex),
+                                             ex.step_counter.data_ptr(), ops.stream()), "insanity_bwd")
+
+
+class FixConnectLayer(zoo.FixConnectLayer):
+    """fixed (file-given, untrained) connection matrix: two tcgen05 GEMMs on a bf16 copy of the weights"""
+    has_b200 = True
+
+    def b200_setup(self, ex):
+        nout, nin = self.wmat.shape
+        self.w_ld = ops.round_up(nin, 8)
+        self.w_bf16 = torch.zeros((nout, self.w_ld), dtype=torch.bfloat16, device=ex.device)
+        self.w_bf16[:, :nin] = self.wmat.to(ex.device)
+
+    def b200_forward(self, ex, is_train):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        b = x.shape[0]
+        nout, nin = self.wmat.shape
+        if y.loss_input:
+            dptr, ldd, flags = y.f32.data_ptr(), y.f32.shape[1], 0
+        else:
+            dptr, ldd, flags = y.act.ptr, y.act.ld, ops.GEMM_OUT_BF16
+        ops.gemm(x.act.ptr, x.act.ld, 0, 0, self.w_bf16.data_ptr(), self.w_ld, 0, 0, dptr, ldd, 0, None, 0, b, nout, nin,
+                 flags=flags)
+
+    def b200_backprop(self, ex, prop_grad):
+        if not prop_grad:
+            return
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        b = x.shape[0]
+        nout, nin = self.wmat.shape
+        ops.gemm(y.grad.ptr, y.grad.ld, 0, 0, self.w_bf16.data_ptr(), self.w_ld, 0, 1, x.grad.ptr, x.grad.ld, 0, None, 0,
+                 b, nin, nout, flags=ops.GEMM_OUT_BF16)
+

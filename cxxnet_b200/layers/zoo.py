@@ -420,7 +420,8 @@ class InsanityLayer(Layer):
         self._check_11(nodes_in, nodes_out, "InsanityLayer")
         nodes_out[0].shape = list(nodes_in[0].shape)
 
-    def forward(self, is_train, nodes_in, nodes_out):
+    def _advance(self):
+        """the calm-down schedule of [lb, ub], evaluated once per forward pass (reference :49-60)"""
         if not self.inited:
             self.inited = True
             d = self.ub - (self.ub + self.lb) / 2.0
@@ -430,6 +431,9 @@ class InsanityLayer(Layer):
             self.ub -= self.delta * self.step
             self.lb += self.delta * self.step
             self.step += 1
+
+    def forward(self, is_train, nodes_in, nodes_out):
+        self._advance()
         x = nodes_in[0].data
         if is_train:
             mask = torch.rand(x.shape, generator=self.rng).to(x.device) * (self.ub - self.lb) + self.lb

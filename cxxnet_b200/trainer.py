@@ -85,6 +85,7 @@ class NetTrainer:
         self.graph_warmup = 3
         self._graphs = {}            # staging slot -> (torch.cuda.CUDAGraph, launches inside)
         self._graph_rows = -1
+        self._graph_unsafe = None
         self._graph_steps = 0
         self._graph_labels: Optional[List[torch.Tensor]] = None
 
@@ -330,6 +331,10 @@ class NetTrainer:
     def _graph_applicable(self, batch: DataBatch) -> bool:
         net = self.net
         if net is None or net.backend != "b200" or self.update_period != 1 or batch.extra_data:
+            return False
+        if self._graph_unsafe is None:     # layers whose kernel arguments change on the host between steps
+            self._graph_unsafe = any(getattr(c.layer, "graph_unsafe", False) or not c.native for c in net.connections)
+        if self._graph_unsafe:
             return False
         begin, end = self._slice(batch.batch_size)
         # only full-size slices are replayed (a smaller last batch takes the eager path)

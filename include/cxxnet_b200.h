@@ -134,6 +134,13 @@ int cxn_prelu_fwd(const void* x, void* y, long long rows, int cols, long long ld
 int cxn_prelu_bwd(const void* x, const void* dy, void* dx, long long rows, int cols, long long ldx, long long ldg,
                   const float* slope, float* gslope, float noise, unsigned long long seed,
                   const unsigned long long* counter, cudaStream_t stream);
+/* insanity (randomised leaky ReLU): y = x > 0 ? x : x / s, s ~ U[lb,ub) per element when `random`, else (lb+ub)/2;
+ * backward regenerates s.  Reference: src/layer/insanity_layer-inl.hpp:13-102 */
+int cxn_insanity_fwd(const void* x, void* y, long long rows, int cols, long long ldx, long long ldy, float lb, float ub,
+                     int random, unsigned long long seed, const unsigned long long* counter, cudaStream_t stream);
+int cxn_insanity_bwd(const void* x, const void* dy, void* dx, long long rows, int cols, long long ldx, long long ldg,
+                     float lb, float ub, int random, unsigned long long seed, const unsigned long long* counter,
+                     cudaStream_t stream);
 int cxn_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int ky, int kx, int stride, int OH, int OW,
                  int mode, int relu, cudaStream_t stream);
 int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, int ky, int kx,

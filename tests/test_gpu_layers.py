@@ -238,3 +238,32 @@ layer[+0] = softmax
             wr, _ = ref.get_weight(name, tag)
             wb, _ = b2.get_weight(name, tag)
             assert rel_err(torch.from_numpy(wr), torch.from_numpy(wb)) < 2e-2, (name, tag)
+
+
+def test_insanity_and_fixconn_native(tmp_path):
+    """insanity with lb == ub is a deterministic leaky ReLU (x / lb below zero), so the Philox stream of the
+    native kernel and torch's generator in the reference math give the same answer; fixconn multiplies by a
+    file-given sparse matrix and passes gradients through it"""
+    import random
+    rnd = random.Random(5)
+    nout, nin = 24, 40
+    entries = sorted({(rnd.randrange(nout), rnd.randrange(nin)) for _ in range(300)})
+    wfile = tmp_path / "fix.txt"
+    wfile.write_text("%d %d %d\n" % (nout, nin, len(entries)) +
+                     "\n".join("%d %d %.4f" % (r, c, rnd.uniform(-1, 1)) for r, c in entries) + "\n")
+    body = """
+layer[0->1] = fullc:fc1
+  nhidden = 40
+layer[1->2] = insanity:in1
+  lb = 4
+  ub = 4
+layer[2->3] = fixconn:fx1
+  nhidden = 24
+  fixconn_weight = %s
+layer[3->4] = fullc:fc2
+  nhidden = 6
+layer[4->4] = softmax
+""" % wfile
+    errs, ref, b2 = compare_backends(_conf(body, 20, "1,1,30"), make_batch((20, 1, 1, 30), nclass=6), tol_grad=8e-2,
+                                     return_trainers=True)
+    assert all(c.native for c in b2.net.connections)
