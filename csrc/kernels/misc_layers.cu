@@ -240,9 +240,58 @@ __global__ void insanity_kernel(const bf16* __restrict__ x, const bf16* __restri
   }
 }
 
+// ---------------------------------------------------------------- insanity pooling: random displacement
+// reference src/layer/insanity_pooling_layer-inl.hpp:63-94: while training, every element of the pooling
+// input is read from itself (probability `keep`) or from its upper / lower / left / right neighbour
+// ((1 - keep) / 4 each, clamped at the border); the max pooling then runs on that displaced copy.
+// src[n][y][x][c] = in[n][y'][x'][c], (y', x') chosen by u ~ U[0,1) from Philox(seed, *counter).
+__global__ void insanity_displace_kernel(const bf16* __restrict__ in, bf16* __restrict__ out, int N, int H, int W, int C,
+                                         long long ld, float keep, unsigned long long seed,
+                                         const unsigned long long* __restrict__ counter) {
+  const unsigned long long offset = counter ? *counter : 0ull;
+  const Philox rng(seed);
+  const long long total = (long long)N * H * W * C;
+  const long long nquads = (total + 3) / 4;
+  const float delta = (1.0f - keep) * 0.25f;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < nquads;
+       q += (long long)gridDim.x * blockDim.x) {
+    uint32_t r4[4];
+    rng((unsigned long long)q, offset, r4);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long i = q * 4 + j;
+      if (i >= total) break;
+      long long r = i;
+      const int c = (int)(r % C); r /= C;
+      const int x = (int)(r % W); r /= W;
+      const int y = (int)(r % H);
+      const long long n = r / H;
+      const float u = u01(r4[j]);
+      int ys = y, xs = x;
+      if (u >= keep) {
+        if (u < keep + delta) ys = max(y - 1, 0);
+        else if (u < keep + 2.0f * delta) ys = min(y + 1, H - 1);
+        else if (u < keep + 3.0f * delta) xs = max(x - 1, 0);
+        else xs = min(x + 1, W - 1);
+      }
+      out[((n * H + y) * W + x) * ld + c] = in[((n * H + ys) * W + xs) * ld + c];
+    }
+  }
+}
+
 }  // namespace cxn
 
 using namespace cxn;
+
+CXN_API int cxn_insanity_displace(const void* in, void* out, int N, int H, int W, int C, long long ld, float keep,
+                                  unsigned long long seed, const unsigned long long* counter, cudaStream_t st) {
+  const long long total = (long long)N * H * W * C;
+  if (total <= 0) return 0;
+  insanity_displace_kernel<<<ew_grid((total + 3) / 4, 256), 256, 0, st>>>((const bf16*)in, (bf16*)out, N, H, W, C, ld, keep,
+                                                                           seed, counter);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
 
 CXN_API int cxn_insanity_fwd(const void* x, void* y, long long rows, int cols, long long ldx, long long ldy, float lb,
                              float ub, int random, unsigned long long seed, const unsigned long long* counter,

@@ -260,7 +260,7 @@ class NeuralNet:
         # fold the backward mask of an aliased ReLU into the pooling layer that consumes it
         for c in self.connections:
             l = c.layer
-            if c.native and isinstance(l, native._NativePool):
+            if c.native and isinstance(l, native._NativePool) and not isinstance(l, native.InsanityPoolingLayer):
                 x = c.nodes_in[0]
                 p = producer.get(x.index)
                 if (p is not None and p.native and isinstance(p.layer, native.ReluLayer) and x.alias_of is not None

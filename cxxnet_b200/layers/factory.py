@@ -36,11 +36,10 @@ _NATIVE = {
     nc.kBatchNorm: native.BatchNormLayer,
     nc.kInsanity: native.InsanityLayer,
     nc.kFixConnect: native.FixConnectLayer,
+    nc.kInsanityPooling: native.InsanityPoolingLayer,
 }
 
-_REF_ONLY = {
-    nc.kInsanityPooling: zoo.InsanityPoolingLayer,
-}
+_REF_ONLY = {}
 
 
 def create_layer(type_id: int) -> Layer:

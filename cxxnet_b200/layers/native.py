@@ -674,6 +674,41 @@ class ChConcatLayer(_NativeConcat, zoo.ChConcatLayer):
     pass
 
 
+class InsanityPoolingLayer(_NativePool, zoo.InsanityPoolingLayer):
+    """max pooling over a randomly displaced copy of the input (training only): one gather kernel writes the
+    displaced copy, the ordinary pooling kernels run on it forward and backward.  As in the reference the
+    backward pass hands the gradient to the displaced positions' slots, not back to their sources."""
+    pool_mode = ops.POOL_MAX
+
+    def b200_setup(self, ex):
+        x = self.nodes_in[0]
+        self.src = DevMat(x.act.t.shape[0], x.act.cols, x.act.ld, device=ex.device)
+        self._displaced = False
+
+    def _seed(self, ex):
+        return (ex.seed * 1000003 + self.layer_index * 7919 + 31337) & 0xFFFFFFFFFFFFFFFF
+
+    def b200_forward(self, ex, is_train):
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        b, c, h, w = x.shape
+        self._displaced = bool(is_train)
+        src = x.act
+        if is_train:
+            ops.check(ops.lib().cxn_insanity_displace(x.act.ptr, self.src.ptr, b, h, w, c, x.act.ld, float(self.p_keep),
+                                                      self._seed(ex), ex.step_counter.data_ptr(), ops.stream()),
+                      "insanity_displace")
+            src = self.src
+        ops.check(ops.lib().cxn_pool_fwd(src.ptr, y.act.ptr, *self._args(), ops.stream()), "pool_fwd")
+
+    def b200_backprop(self, ex, prop_grad):
+        if not prop_grad:
+            return
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        src = self.src if self._displaced else x.act
+        ops.check(ops.lib().cxn_pool_bwd(src.ptr, y.act.ptr, y.grad.ptr, x.grad.ptr, *self._args(True), ops.stream()),
+                  "pool_bwd")
+
+
 # ----------------------------------------------------------------------------- insanity / fixconn
 class InsanityLayer(zoo.InsanityLayer):
     """randomised leaky ReLU: the per-element divisor is a Philox stream regenerated in backward.  Unlike

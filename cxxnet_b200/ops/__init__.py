@@ -84,6 +84,7 @@ def lib():
     _sig(L.cxn_prelu_bwd, [P, P, P, LL, I, LL, LL, P, P, F, ULL, P, P])
     _sig(L.cxn_insanity_fwd, [P, P, LL, I, LL, LL, F, F, I, ULL, P, P])
     _sig(L.cxn_insanity_bwd, [P, P, P, LL, I, LL, LL, F, F, I, ULL, P, P])
+    _sig(L.cxn_insanity_displace, [P, P, I, I, I, I, LL, F, ULL, P, P])
     _sig(L.cxn_conv_set_prof, [P])
     _sig(L.cxn_pool_fwd, [P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(L.cxn_pool_bwd, [P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])

@@ -141,6 +141,10 @@ int cxn_insanity_fwd(const void* x, void* y, long long rows, int cols, long long
 int cxn_insanity_bwd(const void* x, const void* dy, void* dx, long long rows, int cols, long long ldx, long long ldg,
                      float lb, float ub, int random, unsigned long long seed, const unsigned long long* counter,
                      cudaStream_t stream);
+/* insanity pooling: out[n][y][x][c] = in at (y,x) with probability keep, else at the upper / lower / left / right
+ * neighbour ((1-keep)/4 each, clamped); NHWC bf16 with pixel pitch ld.  Reference: insanity_pooling_layer-inl.hpp:63-94 */
+int cxn_insanity_displace(const void* in, void* out, int N, int H, int W, int C, long long ld, float keep,
+                          unsigned long long seed, const unsigned long long* counter, cudaStream_t stream);
 int cxn_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int ky, int kx, int stride, int OH, int OW,
                  int mode, int relu, cudaStream_t stream);
 int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, int ky, int kx,

@@ -267,3 +267,49 @@ layer[4->4] = softmax
     errs, ref, b2 = compare_backends(_conf(body, 20, "1,1,30"), make_batch((20, 1, 1, 30), nclass=6), tol_grad=8e-2,
                                      return_trainers=True)
     assert all(c.native for c in b2.net.connections)
+
+
+def test_insanity_pooling_native():
+    """keep = 1 never displaces, so training mode must equal plain max pooling on both backends; the
+    displacement kernel itself is checked against its definition: every output element is the input at the
+    same position or at one of its four (clamped) neighbours, with roughly the configured frequencies"""
+    body = """
+layer[+1] = conv:cv1
+  kernel_size = 3
+  pad = 1
+  nchannel = 16
+layer[+1] = insanity_max_pooling
+  kernel_size = 3
+  stride = 2
+  keep = 1.0
+layer[+1] = flatten
+layer[+1] = fullc:fc1
+  nhidden = 10
+layer[+0] = softmax
+"""
+    errs, ref, b2 = compare_backends(_conf(body, 8, "3,15,15"), make_batch((8, 3, 15, 15)), tol_grad=0.12,
+                                     return_trainers=True)
+    assert all(c.native for c in b2.net.connections)
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    N, H, W, C = 3, 9, 11, 16
+    x = torch.arange(N * H * W * C, device="cuda", dtype=torch.float32).reshape(N, H, W, C)
+    # values identify their source position: keep them exactly representable in bf16 by using small integers
+    pos = (torch.arange(H, device="cuda").view(1, H, 1, 1) * 16 + torch.arange(W, device="cuda").view(1, 1, W, 1)).expand(N, H, W, C)
+    xin = pos.to(torch.bfloat16).contiguous()
+    out = torch.zeros_like(xin)
+    counter = torch.zeros(1, dtype=torch.int64, device="cuda")
+    assert L.cxn_insanity_displace(xin.data_ptr(), out.data_ptr(), N, H, W, C, C, 0.6, 12345, counter.data_ptr(),
+                                   torch.cuda.current_stream().cuda_stream) == 0
+    torch.cuda.synchronize()
+    o = out.float().long()
+    ys, xs = o // 16, o % 16
+    y0 = torch.arange(H, device="cuda").view(1, H, 1, 1).expand(N, H, W, C)
+    x0 = torch.arange(W, device="cuda").view(1, 1, W, 1).expand(N, H, W, C)
+    dy, dx = ys - y0, xs - x0
+    assert bool(((dy.abs() + dx.abs()) <= 1).all())                       # itself or a direct neighbour
+    interior = (y0 > 0) & (y0 < H - 1) & (x0 > 0) & (x0 < W - 1)
+    kept = float(((dy == 0) & (dx == 0) & interior).sum()) / float(interior.sum())
+    assert 0.5 < kept < 0.7                                                 # keep = 0.6
+    up = float(((dy == -1) & interior).sum()) / float(interior.sum())
+    assert 0.06 < up < 0.14                                                 # (1 - keep) / 4 = 0.1
