@@ -70,7 +70,13 @@ class LearnTask:
             self.task_train()
         if self.task == "pred":
             self.task_predict()
-        if self.task == "extract":
+        if self.task in ("extract", "extract_feature"):
+            self.task_extract_feature()
+        if self.task == "pred_raw":
+            # Documented by the reference (doc/tasks.md, example/kaggle_bowl/pred.conf) although its driver never
+            # dispatches it (cxxnet_main.cpp:77-79): one text row of raw top-node outputs per instance.
+            self.extract_node_name = self.extract_node_name or "top[-1]"
+            self.output_format = 1
             self.task_extract_feature()
         self.close()
         return 0
@@ -207,13 +213,13 @@ class LearnTask:
                 continue
             if name == "iter" and val == "end":
                 assert flag != 0, "wrong configuration file"
-                if flag == 1 and self.task != "pred":
+                if flag == 1 and self.task in ("train", "finetune"):
                     assert self.itr_train is None, "can only have one data"
                     self.itr_train = create_iterator(itcfg)
-                if flag == 2 and self.task != "pred":
+                if flag == 2 and self.task in ("train", "finetune"):
                     self.itr_evals.append(create_iterator(itcfg))
                     self.eval_names.append(evname)
-                if flag == 3 and self.task in ("pred", "pred_raw", "extract"):
+                if flag == 3 and self.task in ("pred", "pred_raw", "extract", "extract_feature"):
                     assert self.itr_pred is None, "can only have one data:test"
                     self.itr_pred = create_iterator(itcfg)
                 flag = 0

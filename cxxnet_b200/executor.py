@@ -43,7 +43,8 @@ class Connection:
 
 class NeuralNet:
     def __init__(self, cfg: NetConfig, max_batch: int, seed: int, device: torch.device, backend: str = "ref",
-                 silent: int = 0, world_size: int = 1, rank: int = 0, arena_alloc=None):
+                 silent: int = 0, world_size: int = 1, rank: int = 0, arena_alloc=None,
+                 exchange_kind: str = "nvlink"):
         self.cfg = cfg
         self.timer = None        # utils.timing.LayerTimer when `layer_timing = 1`
         self.max_batch = max_batch
@@ -52,6 +53,9 @@ class NeuralNet:
         self.backend = backend
         self.silent = silent
         self.world_size, self.rank = world_size, rank
+        # "nvlink": fused kernels over peer-mapped memory (parallel/exchange.py); "collective": torch.distributed
+        # all-reduce + local update for ranks without peer access (parallel/dist_exchange.py)
+        self.exchange_kind = exchange_kind
         self.rng = torch.Generator()
         self.rng.manual_seed(seed)
         self.label_info = LabelInfo(cfg.label_name_map)
@@ -306,11 +310,12 @@ class NeuralNet:
                                               (isinstance(c.layer, (native.FullConnectLayer, native.ConvolutionLayer))
                                                and tag == "bias")))
                 self._seg_of[(i, tag)] = s
-        if self.world_size > 1 and self.arena_alloc is None:
+        peer_mapped = self.world_size > 1 and self.arena_alloc is None and self.exchange_kind == "nvlink"
+        if peer_mapped:
             self._plan_fc_shards()
             self._alloc_symmetric()
         self.arena.finalize()
-        if self.world_size > 1 and self.arena_alloc is None:
+        if peer_mapped:
             self._finish_fc_shards()
         self._bind_arena()
         for c in self.connections:
@@ -333,7 +338,10 @@ class NeuralNet:
         self.stage_idx = 0
         self.extra_stage = [torch.zeros(tuple(self.nodes[i + 1].shape), dtype=torch.float32, device=self.device)
                             for i in range(cfg.extra_data_num)]
-        if self.world_size > 1:
+        if self.world_size > 1 and self.exchange_kind == "collective":
+            from .parallel.dist_exchange import CollectiveExchange
+            self.exchange = CollectiveExchange(self)
+        elif self.world_size > 1:
             from .parallel.exchange import GradExchange
             self.exchange = GradExchange(self)
 

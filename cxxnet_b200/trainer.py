@@ -126,13 +126,25 @@ class NetTrainer:
     # ------------------------------------------------------------------ device / process layout
     def _resolve_devices(self) -> None:
         import torch.distributed as dist
+        self.exchange_kind = "nvlink"
         if self.type_pserver == "dist":
-            raise ValueError("param_server=dist (ps-lite multi-node) is not supported; "
-                             "use a torch.distributed launch over NVLink instead")
+            # The reference's multi-node mode (ps-lite servers, example/MNIST/mpi.conf).  Here: the ranks of a
+            # torch.distributed job launched over several nodes, exchanging through collectives
+            # (parallel/dist_exchange.py) instead of peer-mapped memory.
+            if not (dist.is_available() and dist.is_initialized()):
+                raise ValueError("param_server=dist needs a torch.distributed job: launch one rank per device "
+                                 "with torchrun (--nnodes N --nproc-per-node G) and run `python -m cxxnet_b200 conf`")
+            self.exchange_kind = "collective"
         if dist.is_available() and dist.is_initialized() and self.type_pserver != "NONE":
             # param_server = NONE keeps this trainer private to its process (no gradient exchange),
             # as in the reference when a single device is used (nnet_impl-inl.hpp:378-381)
             self.world_size, self.rank = dist.get_world_size(), dist.get_rank()
+        if self.world_size > 1 and self.dev_kind == "gpu" and self.exchange_kind == "nvlink":
+            from .parallel.dist_exchange import ranks_share_one_host
+            # peer-mapped memory exists inside one machine only; CXN_EXCHANGE=collective selects the library
+            # path on one node too (the arm the fused kernels are compared against)
+            if os.environ.get("CXN_EXCHANGE", "") == "collective" or not ranks_share_one_host():
+                self.exchange_kind = "collective"
         ndev = max(len(self.devices), 1)
         if self.world_size > 1:
             ndev = self.world_size
@@ -173,7 +185,10 @@ class NetTrainer:
         self.net_cfg.configure(self.cfg)
         self._resolve_devices()
         self.net = NeuralNet(self.net_cfg, self.step, self.rank + self.seed * 100, self.device, self.backend,
-                             silent=self.silent or self.rank != 0, world_size=self.world_size, rank=self.rank)
+                             silent=self.silent or self.rank != 0, world_size=self.world_size, rank=self.rank,
+                             exchange_kind=self.exchange_kind)
+        if self.world_size > 1 and self.exchange_kind == "collective":
+            self.cuda_graph = 0          # library collectives stay outside captured steps
         if self.layer_timing:
             from .utils.timing import LayerTimer
             def names():

@@ -15,6 +15,10 @@ _lenet = lenet_conf
 def lenet_conf(**kw):   # dropout off: masks are a function of the element index, i.e. of the batch split
     return _lenet(**kw).replace("threshold = 0.5", "threshold = 0.0")
 MODE = sys.argv[2] if len(sys.argv) > 2 else "lenet"
+COLLECTIVE = MODE == "collective"       # torch.distributed all-reduce + local update instead of the fused kernels
+if COLLECTIVE:
+    os.environ["CXN_EXCHANGE"] = "collective"
+    MODE = "lenet"
 GRAPH = len(sys.argv) > 3 and sys.argv[3] == "graph"     # multi-GPU trainer replays captured steps
 if MODE == "gather":
     # fully connected net whose first layer can be row-sharded (fullc_gather = 1): nin = 1024
@@ -49,6 +53,8 @@ tr = make_trainer(lenet_conf(batch_size=64, dev="gpu:" + ",".join(str(i) for i i
 if MODE == "gather":
     assert len(tr.net.fc_shards) == 1, "first layer should be sharded"
 assert tr.net.exchange is not None and tr.world_size == world
+assert (type(tr.net.exchange).__name__ == "CollectiveExchange") == COLLECTIVE
+os.environ.pop("CXN_EXCHANGE", None)
 assert tr.net.exchange.check_replicas() == 0.0
 # single-GPU twin: same weights, whole batch on one device, no exchange
 single = make_trainer(lenet_conf(batch_size=64, dev="gpu:%d" % rank, extra=extra), param_server="NONE")

@@ -96,6 +96,11 @@ def test_train_continue_pred_extract_finetune(tmp_path):
     _run([str(conf), "task=extract", "model_in=%s" % (mdir / "0003.model"), "extract_node_name=sg1",
           "output_format=bin"], tmp_path)
     assert os.path.getsize(tmp_path / "pred.txt") == 200 * 32 * 4
+    # pred_raw (documented by the reference, dispatched here): one text row of raw outputs per instance
+    _run([str(conf), "task=pred_raw", "model_in=%s" % (mdir / "0003.model")], tmp_path)
+    raw = (tmp_path / "pred.txt").read_text().strip().split("\n")
+    assert len(raw) == 200 and len(raw[0].split()) == 10
+    assert [int(np.argmax([float(v) for v in ln.split()])) for ln in raw] == [int(p) for p in preds]
     # finetune: layers with matching names are copied, epoch counter restarts
     ft = tmp_path / "ft.conf"
     ft.write_text((CONF % {"rounds": 1, "model_dir": tmp_path / "ft_models", "pred": tmp_path / "p2.txt"})

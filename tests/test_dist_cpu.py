@@ -4,6 +4,8 @@ import os
 import subprocess
 import sys
 
+import pytest
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 WORKER = r'''
@@ -15,7 +17,7 @@ rank = dist.get_rank()
 from util import make_trainer, make_batch
 from cxxnet_b200.models import mlp_conf
 conf = mlp_conf(dev="cpu", batch_size=60, extra="wmat:wd = 0.01\n")
-tr = make_trainer(conf)
+tr = make_trainer(conf%(over)s)
 assert tr.world_size == 2 and tr.step == 30
 single = make_trainer(conf, param_server="NONE")
 assert single.world_size == 1 and single.step == 60
@@ -38,12 +40,38 @@ print("OK", rank)
 '''
 
 
-def test_two_gloo_ranks_match_single_process(tmp_path):
+@pytest.mark.parametrize("pserver", ["local", "dist"])
+def test_two_gloo_ranks_match_single_process(tmp_path, pserver):
+    """`param_server = dist` (the reference's multi-node key) selects the collective exchange; on the CPU backend
+    both settings sum the gradients with an all-reduce."""
     script = tmp_path / "w.py"
-    script.write_text(WORKER % {"root": ROOT})
+    script.write_text(WORKER % {"root": ROOT, "over": "" if pserver == "local" else ', param_server="dist"'})
     env = dict(os.environ)
     env["MASTER_ADDR"] = "127.0.0.1"
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-                        "--master-addr", "127.0.0.1", "--master-port", "29633", str(script)], env=env,
+                        "--master-addr", "127.0.0.1", "--master-port", "29633" if pserver == "local" else "29634", str(script)], env=env,
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     assert r.returncode == 0 and r.stdout.count("OK") == 2, r.stdout[-3000:]
+
+
+def test_param_server_dist_needs_a_process_group():
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.models import mlp_conf
+    from cxxnet_b200.trainer import NetTrainer
+    tr = NetTrainer()
+    for k, v in parse_config_string(mlp_conf(dev="cpu", batch_size=10)):
+        tr.set_param(k, v)
+    tr.set_param("param_server", "dist")
+    with pytest.raises(ValueError, match="torchrun"):
+        tr.init_model()
+
+
+def test_host_detection_reads_the_launcher_environment(monkeypatch):
+    from cxxnet_b200.parallel.dist_exchange import ranks_share_one_host
+    monkeypatch.setenv("WORLD_SIZE", "16")
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "8")
+    assert not ranks_share_one_host()
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "16")
+    assert ranks_share_one_host()
+    monkeypatch.delenv("LOCAL_WORLD_SIZE")
+    assert ranks_share_one_host()

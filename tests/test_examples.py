@@ -26,6 +26,7 @@ def test_example_conf_builds(path):
         if not in_iter:
             tr.set_param(k, v)
     tr.set_param("dev", "cpu")
+    tr.set_param("param_server", "local")      # dist.conf asks for a multi-node job
     tr.set_param("batch_size", "2")
     tr.set_param("silent", "1")
     tr.init_model()
@@ -34,3 +35,40 @@ def test_example_conf_builds(path):
     assert nparam > 0
     if path.endswith("ImageNet.conf"):
         assert nparam == 60965224          # AlexNet
+
+
+def test_mnist_python_api_example_runs(tmp_path):
+    """examples/MNIST/mnist.py: the tour of the Python API (surrogate data, CPU)."""
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "MNIST", "mnist.py"), "cpu"], cwd=tmp_path,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert "predict: sum|iter - ndarray| = 0.0" in r.stdout
+    assert "reloaded model agrees: True" in r.stdout
+    assert os.path.exists(tmp_path / "models" / "python_api.model")
+
+
+def test_kaggle_resize_and_submission_scripts(tmp_path):
+    """gen_train.py / gen_img_list.py / make_submission.py on a two-class toy tree"""
+    import subprocess
+    import sys
+    from PIL import Image
+    kb = os.path.join(ROOT, "examples", "kaggle_bowl")
+    for cls in ("acantharia", "copepod"):
+        os.makedirs(tmp_path / "raw" / cls)
+        for i in range(3):
+            Image.new("L", (30 + i, 20)).save(tmp_path / "raw" / cls / ("%s_%d.jpg" % (cls, i)))
+    (tmp_path / "sample.csv").write_text("image,acantharia,copepod\nx.jpg,0.5,0.5\n")
+    run = lambda *a: subprocess.run([sys.executable] + [str(x) for x in a], cwd=tmp_path, check=True, timeout=120)
+    run(os.path.join(kb, "gen_train.py"), str(tmp_path / "raw") + "/", str(tmp_path / "small") + "/", 48)
+    assert Image.open(tmp_path / "small" / "copepod" / "copepod_2.jpg").size == (48, 48)
+    run(os.path.join(kb, "gen_img_list.py"), "train", tmp_path / "sample.csv", str(tmp_path / "small") + "/",
+        tmp_path / "train.lst")
+    rows = [ln.split("\t") for ln in (tmp_path / "train.lst").read_text().strip().split("\n")]
+    assert len(rows) == 6 and sorted(r[1] for r in rows) == ["0"] * 3 + ["1"] * 3
+    (tmp_path / "probs.txt").write_text("".join("0.25 0.75 \n" for _ in rows))
+    run(os.path.join(kb, "make_submission.py"), tmp_path / "sample.csv", tmp_path / "train.lst",
+        tmp_path / "probs.txt", tmp_path / "out.csv")
+    out = (tmp_path / "out.csv").read_text().strip().split("\n")
+    assert out[0] == "image,acantharia,copepod" and len(out) == 7 and out[1].endswith(",0.25,0.75")

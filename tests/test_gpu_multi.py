@@ -24,3 +24,12 @@ def test_fused_exchange_matches_single_gpu(updater, mode, graph):
     script = os.path.join(ROOT, "tests", "mp_exchange_worker.py")
     r = _run(2, [script, updater, mode] + ([graph] if graph else []))
     assert r.returncode == 0 and r.stdout.count("OK") == 2, r.stdout[-4000:]
+
+
+@pytest.mark.skipif(torch.cuda.is_available() and torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.skipif(os.environ.get("CXN_TEST_COLLECTIVE", "0") != "1",
+                    reason="collective (param_server = dist) exchange on GPUs: opt-in with CXN_TEST_COLLECTIVE=1")
+def test_collective_exchange_matches_single_gpu():
+    script = os.path.join(ROOT, "tests", "mp_exchange_worker.py")
+    r = _run(2, [script, "sgd", "collective"])
+    assert r.returncode == 0 and r.stdout.count("OK") == 2, r.stdout[-4000:]
