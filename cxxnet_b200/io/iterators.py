@@ -25,8 +25,15 @@ from .data import DataBatch, DataInst, IIterator
 PAGE_INTS = 64 << 18  # BinaryPage: 64 Mi ints... 64<<18 ints = 64 MiB (reference src/utils/io.h:257)
 
 
-def _decode_image(buf: bytes) -> np.ndarray:
-    """bytes -> float32 RGB planar (3,h,w), as the reference's imdecode + BGR->RGB split."""
+def _decode_image(buf: bytes, native_first: bool = True) -> np.ndarray:
+    """bytes -> float32 RGB planar (3,h,w), as the reference's imdecode + BGR->RGB split.  JPEGs go through the
+    native decoder (csrc/runtime/jpeg_decoder.cpp, the counterpart of the reference's utils/decoder.h); other
+    formats, and JPEG variants it does not cover, through OpenCV or Pillow."""
+    if native_first and os.environ.get("CXN_NATIVE_JPEG", "1") != "0":
+        from . import native
+        arr = native.jpeg_decode(buf)
+        if arr is not None:
+            return arr
     try:
         import cv2
         arr = cv2.imdecode(np.frombuffer(buf, dtype=np.uint8), 1)
@@ -429,11 +436,29 @@ class ImageBinIterator(IIterator):
 
     def _producer(self, q, stop):
         try:
+            if self.two_stage:
+                # imgbinx decode stage: groups of blobs are decoded by native worker threads (GIL released)
+                from . import native
+                group = []
+
+                def flush():
+                    imgs = native.jpeg_decode_many([r[2] for r in group]) if native.lib() is not None \
+                        else [None] * len(group)
+                    for r, im in zip(group, imgs):
+                        q.put((r[0], r[1], im if im is not None else _decode_image(r[2], native_first=False)))
+                    group.clear()
+                for rec in self._records():
+                    if stop.is_set():
+                        return
+                    group.append(rec)
+                    if len(group) >= 32:
+                        flush()
+                flush()
+                return
             for rec in self._records():
                 if stop.is_set():
                     return
-                item = (rec[0], rec[1], _decode_image(rec[2])) if self.two_stage else rec
-                q.put(item)
+                q.put(rec)
         finally:
             q.put(None)
 
