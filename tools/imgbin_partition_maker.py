@@ -1,14 +1,33 @@
 #!/usr/bin/env python
-"""Write a Makefile that shards an image list into <= N MB ``.lst`` / ``.bin`` partitions packed by
-``im2bin`` (same options and output as the reference's ``tools/imgbin-partition-maker.py``)."""
+"""Shard an image list into partitions of bounded packed size and write the Makefile that packs every
+partition with ``im2bin`` (run it with ``make -f Gen.mk -j``).  Same command line as the reference's
+``tools/imgbin-partition-maker.py``; the ``imgbin`` iterator reads the parts back through
+``image_conf_prefix`` / ``image_conf_ids``.
+
+A partition is closed when the next image would push its packed size (image bytes plus the 4-byte entries of
+the page's offset table) past ``--partition_size`` MB, so no ``.bin`` exceeds the bound."""
 import argparse
 import os
 import random
 import sys
 
 
+def plan_partitions(entries, sizes, limit_bytes):
+    """greedy split of `entries` (list lines) into consecutive groups whose packed size stays <= limit."""
+    groups, cur, used = [], [], 0
+    for line, nbytes in zip(entries, sizes):
+        cost = nbytes + 4                      # blob + its slot in the offset table
+        if cur and used + cost + 8 > limit_bytes:
+            groups.append(cur)
+            cur, used = [], 0
+        cur.append(line)
+        used += cost
+    if cur:
+        groups.append(cur)
+    return groups
+
+
 def main(argv=None):
-    random.seed(888)
     ap = argparse.ArgumentParser(description="Generate a Makefile to make partition imgbin files")
     ap.add_argument("--img_list", required=True, help="path to list of all images")
     ap.add_argument("--img_root", required=True, help="prefix path to the file path in img_list")
@@ -19,35 +38,25 @@ def main(argv=None):
     ap.add_argument("--out", required=True, help="output folder for image bins and lists")
     ap.add_argument("--makefile", default="Gen.mk", help="name of the generated Makefile")
     args = ap.parse_args(argv)
+
     with open(args.img_list) as f:
-        lst = [ln for ln in f if ln.strip()]
+        entries = [ln if ln.endswith("\n") else ln + "\n" for ln in f if ln.strip()]
     if args.shuffle == "1":
-        random.shuffle(lst)
-    out = args.out if args.out.endswith("/") else args.out + "/"
-    os.makedirs(out, exist_ok=True)
-    limit = int(args.partition_size) << 20
-    objs, cmds = [], []
-    fw, sz, img_cnt, cnt = None, 0, 1, 1
-    for item in lst:
-        if fw is None or sz + 10240 > limit:
-            lst_name = out + (args.prefix % cnt) + ".lst"
-            bin_name = out + (args.prefix % cnt) + ".bin"
-            objs.append(bin_name)
-            if fw is not None:
-                fw.close()
-            fw = open(lst_name, "w")
-            cmds.append("%s: %s\n\t%s %s %s %s" % (bin_name, lst_name, args.im2bin, lst_name, args.img_root, bin_name))
-            sz, img_cnt = 0, 1
-            cnt += 1
-        path = item.rstrip("\n").split("\t")[2]
-        sz += os.path.getsize(args.img_root + path) + (img_cnt + 2) * 4
-        fw.write(item)
-        img_cnt += 1
-    if fw is not None:
-        fw.close()
-    with open(args.makefile, "w") as fo:
-        fo.write("all: " + " ".join(objs) + "\n")
-        fo.write("\n\n".join(cmds) + "\n")
+        random.Random(888).shuffle(entries)
+    sizes = [os.path.getsize(args.img_root + e.rstrip("\n").split("\t")[2]) for e in entries]
+    out_dir = os.path.join(args.out, "")
+    os.makedirs(out_dir, exist_ok=True)
+
+    rules = []
+    for number, group in enumerate(plan_partitions(entries, sizes, int(args.partition_size) << 20), start=1):
+        stem = out_dir + (args.prefix % number)
+        with open(stem + ".lst", "w") as fl:
+            fl.writelines(group)
+        rules.append((stem + ".bin", stem + ".lst"))
+    with open(args.makefile, "w") as mk:
+        mk.write("all: %s\n" % " ".join(target for target, _ in rules))
+        for target, source in rules:
+            mk.write("\n%s: %s\n\t%s %s %s %s\n" % (target, source, args.im2bin, source, args.img_root, target))
     return 0
 
 
