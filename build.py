@@ -75,14 +75,14 @@ def build_kernels(force=False, verbose=False):
 def build_host(force=False, verbose=False):
     os.makedirs(LIBDIR, exist_ok=True)
     cxx = os.environ.get("CXX", "g++")
-    flags = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread"]
+    flags = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-pthread", "-ffp-contract=off"]
     out = []
     io_srcs = sorted(glob.glob(os.path.join(ROOT, "csrc", "runtime", "*.cpp")))
     io_hdrs = glob.glob(os.path.join(ROOT, "csrc", "runtime", "*.h"))
     if io_srcs:
         target = os.path.join(LIBDIR, "libcxxnet_io.so")
         if force or _newer(target, io_srcs + io_hdrs):
-            _run([cxx] + flags + ["-shared", "-o", target] + io_srcs + ["-lz"], verbose)
+            _run([cxx] + flags + ["-O3", "-shared", "-o", target] + io_srcs + ["-lz"], verbose)
         out.append(target)
     capi = sorted(glob.glob(os.path.join(ROOT, "csrc", "capi", "*.cpp")))
     if capi:

@@ -1,0 +1,122 @@
+// Decode + augment + batch assembly on native worker threads: the per-instance work of the reference's
+// imgbinx decode thread (src/io/iter_thread_imbin_x-inl.hpp:18-395), AugmentIterator::SetData
+// (src/io/iter_augment_proc-inl.hpp:98-162) and BatchAdaptIterator (src/io/iter_batch_proc-inl.hpp:16-133),
+// done for a whole batch in one call.  The caller (cxxnet_b200/io/iterators.py) draws the random decisions
+// in instance order - so results do not depend on the number of threads - and hands over encoded images;
+// each worker decodes one image (jpeg_decoder.cpp) and writes its crop, mean-subtracted, jittered, mirrored
+// and scaled, straight into that instance's slot of the (pinned) batch buffer, as fp32 or bf16.
+//
+//   mean_mode 0: out = v * scale                                   (no mean configured)
+//             1: out = ((v - mean[c]) * contrast + illum) * scale  (mean_value: one number per channel)
+//             2: mean image of the decoded size, subtracted before the crop / mirror
+//             3: mean image of the crop size, subtracted after the crop / mirror
+// The arithmetic is single precision in this order, the same as the NumPy path it replaces.
+#include <atomic>
+#include <cstdint>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+extern "C" int cxnio_jpeg_info(const uint8_t* buf, size_t n, int* width, int* height, int* components);
+extern "C" int cxnio_jpeg_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, int width, int height);
+
+extern "C" {
+
+struct CxnioAugItem {
+  const uint8_t* buf;     // encoded image, or NULL when `pixels` is given
+  uint64_t size;
+  const float* pixels;    // already decoded planar float image (channels x src_h x src_w), or NULL
+  int32_t src_h, src_w;   // size of the decoded image (checked against the file)
+  int32_t y0, x0;         // crop origin
+  int32_t flip;           // mirror horizontally
+  float contrast, illum;
+};
+
+static inline uint16_t F32ToBf16(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return uint16_t((u >> 16) | 0x40);      // NaN stays NaN
+  u += 0x7fffu + ((u >> 16) & 1u);                                              // round to nearest even
+  return uint16_t(u >> 16);
+}
+
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__)
+#define CXNIO_CLONES __attribute__((target_clones("avx2", "default")))
+#else
+#define CXNIO_CLONES
+#endif
+
+// one instance: src (C x sh x sw planar float) -> dst slot
+CXNIO_CLONES static int AugmentOne(const float* src, int C, int sh, int sw, const CxnioAugItem& it, int H, int W, int mean_mode,
+                      const float* mean, int mean_h, int mean_w, float scale, void* dst, int dst_bf16) {
+  if (it.y0 < 0 || it.x0 < 0 || it.y0 + H > sh || it.x0 + W > sw) return -10;
+  if (mean_mode == 2 && (mean_h != sh || mean_w != sw)) return -11;
+  if (mean_mode == 3 && (mean_h != H || mean_w != W)) return -11;
+  float* df = static_cast<float*>(dst);
+  uint16_t* dh = static_cast<uint16_t*>(dst);
+  const float contrast = it.contrast, illum = it.illum;
+  for (int c = 0; c < C; ++c) {
+    for (int y = 0; y < H; ++y) {
+      const float* srow = src + (size_t(c) * sh + it.y0 + y) * sw + it.x0;
+      const float* mrow = nullptr;
+      if (mean_mode == 2) mrow = mean + (size_t(c) * sh + it.y0 + y) * sw + it.x0;
+      if (mean_mode == 3) mrow = mean + (size_t(c) * H + y) * W;
+      const size_t o = (size_t(c) * H + y) * W;
+      for (int x = 0; x < W; ++x) {
+        const int xs = it.flip ? W - 1 - x : x;
+        float v = srow[xs];
+        if (mean_mode == 1) v = (v - mean[c]) * contrast + illum;
+        else if (mean_mode == 2) v = (v - mrow[xs]) * contrast + illum;
+        else if (mean_mode == 3) v = (v - mrow[x]) * contrast + illum;
+        v = v * scale;
+        if (dst_bf16) dh[o + x] = F32ToBf16(v); else df[o + x] = v;
+      }
+    }
+  }
+  return 0;
+}
+
+// status[i]: 0 ok, < 0 this instance was not written (undecodable here, size mismatch, crop outside the image)
+int cxnio_decode_augment_batch(const CxnioAugItem* items, int n, int C, int H, int W, int mean_mode, const float* mean,
+                               int mean_h, int mean_w, float scale, void* dst, int dst_bf16, int* status,
+                               int nthreads) {
+  if (n <= 0) return 0;
+  if (nthreads < 1) nthreads = 1;
+  if (nthreads > n) nthreads = n;
+  const size_t inst = size_t(C) * H * W * (dst_bf16 ? 2 : 4);
+  std::atomic<int> next{0};
+  auto work = [&]() {
+    std::vector<float> tmp;
+    for (;;) {
+      const int i = next.fetch_add(1);
+      if (i >= n) return;
+      const CxnioAugItem& it = items[i];
+      void* slot = static_cast<char*>(dst) + inst * i;
+      if (it.pixels) {
+        status[i] = AugmentOne(it.pixels, C, it.src_h, it.src_w, it, H, W, mean_mode, mean, mean_h, mean_w, scale,
+                               slot, dst_bf16);
+        continue;
+      }
+      int w = 0, h = 0, comps = 0;
+      int r = cxnio_jpeg_info(it.buf, it.size, &w, &h, &comps);
+      if (r == 0 && (w != it.src_w || h != it.src_h || C != 3)) r = -12;
+      if (r == 0) {
+        tmp.resize(size_t(3) * h * w);
+        r = cxnio_jpeg_decode_planar_f32(it.buf, it.size, tmp.data(), w, h);
+      }
+      if (r == 0) r = AugmentOne(tmp.data(), C, h, w, it, H, W, mean_mode, mean, mean_h, mean_w, scale, slot, dst_bf16);
+      status[i] = r;
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < nthreads; ++t) pool.emplace_back(work);
+  work();
+  for (auto& t : pool) t.join();
+  int bad = 0;
+  for (int i = 0; i < n; ++i) bad += status[i] != 0;
+  return bad;
+}
+
+int cxnio_aug_item_bytes() { return int(sizeof(CxnioAugItem)); }
+
+}  // extern "C"

@@ -38,6 +38,21 @@ struct HuffTable {
   int32_t maxcode[18];     // largest code of each length, left-aligned to 16 bits, +1
   int32_t valoff[17];      // symbol index = code + valoff[len]
   uint8_t syms[256];
+  // AC tables only: 9-bit prefix -> (value << 8) | (run << 4) | (code bits + magnitude bits) when a whole
+  // run/size code and its magnitude bits fit into the prefix, else 0
+  int16_t fast_ac[512];
+  void BuildFastAc() {
+    for (int i = 0; i < 512; ++i) {
+      fast_ac[i] = 0;
+      const int len = fast_len[i];
+      if (!len) continue;
+      const int rs = fast_sym[i], run = rs >> 4, mag = rs & 15;
+      if (mag == 0 || len + mag > 9) continue;
+      int v = ((i << len) & 511) >> (9 - mag);
+      if (v < (1 << (mag - 1))) v += 1 - (1 << mag);
+      if (v >= -128 && v <= 127) fast_ac[i] = int16_t(v * 256 + run * 16 + len + mag);
+    }
+  }
   bool Build(const uint8_t counts[16], const uint8_t* symbols, int nsym) {
     memcpy(syms, symbols, nsym);
     memset(fast_len, 0, sizeof(fast_len));
@@ -117,44 +132,82 @@ struct Component {
 static const float kAanScale[8] = {1.0f, 1.387039845f, 1.306562965f, 1.175875602f, 1.0f, 0.785694958f, 0.541196100f,
                                    0.275899379f};
 
-// one 8-point pass of the Arai-Agui-Nakajima inverse DCT (5 multiplications), stride `st` between elements
-static inline void Idct8(const float* in, int st, float* o) {
-  float t0 = in[0], t1 = in[2 * st], t2 = in[4 * st], t3 = in[6 * st];
-  float t10 = t0 + t2, t11 = t0 - t2;
-  float t13 = t1 + t3, t12 = (t1 - t3) * 1.414213562f - t13;
-  t0 = t10 + t13; t3 = t10 - t13; t1 = t11 + t12; t2 = t11 - t12;
-  float t4 = in[st], t5 = in[3 * st], t6 = in[5 * st], t7 = in[7 * st];
-  const float z13 = t6 + t5, z10 = t6 - t5, z11 = t4 + t7, z12 = t4 - t7;
-  t7 = z11 + z13;
-  t11 = (z11 - z13) * 1.414213562f;
-  const float z5 = (z10 + z12) * 1.847759065f;
-  t10 = 1.082392200f * z12 - z5;
-  t12 = -2.613125930f * z10 + z5;
-  t6 = t12 - t7; t5 = t11 - t6; t4 = t10 + t5;
-  o[0] = t0 + t7; o[7] = t0 - t7; o[1] = t1 + t6; o[6] = t1 - t6;
-  o[2] = t2 + t5; o[5] = t2 - t5; o[4] = t3 + t4; o[3] = t3 - t4;
+// Hot loops are compiled twice (AVX2 and baseline x86-64) and chosen at load time.
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__)
+#define CXNIO_CLONES __attribute__((target_clones("avx2", "default")))
+#else
+#define CXNIO_CLONES
+#endif
+
+// Eight 8-point inverse DCTs side by side (Arai-Agui-Nakajima, 5 multiplications each): element k of
+// transform `lane` is in[k * 8 + lane], results go to out[k * 8 + lane]; the lane loop vectorises.
+static inline void Idct8Lanes(const float* in, float* out) {
+  for (int l = 0; l < 8; ++l) {
+    float t0 = in[l], t1 = in[16 + l], t2 = in[32 + l], t3 = in[48 + l];
+    float t10 = t0 + t2, t11 = t0 - t2;
+    float t13 = t1 + t3, t12 = (t1 - t3) * 1.414213562f - t13;
+    t0 = t10 + t13; t3 = t10 - t13; t1 = t11 + t12; t2 = t11 - t12;
+    float t4 = in[8 + l], t5 = in[24 + l], t6 = in[40 + l], t7 = in[56 + l];
+    const float z13 = t6 + t5, z10 = t6 - t5, z11 = t4 + t7, z12 = t4 - t7;
+    t7 = z11 + z13;
+    t11 = (z11 - z13) * 1.414213562f;
+    const float z5 = (z10 + z12) * 1.847759065f;
+    t10 = 1.082392200f * z12 - z5;
+    t12 = -2.613125930f * z10 + z5;
+    t6 = t12 - t7; t5 = t11 - t6; t4 = t10 + t5;
+    out[l] = t0 + t7; out[56 + l] = t0 - t7; out[8 + l] = t1 + t6; out[48 + l] = t1 - t6;
+    out[16 + l] = t2 + t5; out[40 + l] = t2 - t5; out[32 + l] = t3 + t4; out[24 + l] = t3 - t4;
+  }
 }
 
 // 8x8 inverse DCT of coefficients already multiplied by their (AAN-scaled) quantisation steps, natural order
-// -> samples, level shift +128, clamp
-static void Idct8x8(const float* in, uint8_t* out, int stride) {
-  float tmp[64], col[8];
-  for (int u = 0; u < 8; ++u) {
-    if (in[8 + u] == 0 && in[16 + u] == 0 && in[24 + u] == 0 && in[32 + u] == 0 && in[40 + u] == 0 &&
-        in[48 + u] == 0 && in[56 + u] == 0) {
-      for (int y = 0; y < 8; ++y) tmp[y * 8 + u] = in[u];
-      continue;
-    }
-    Idct8(in + u, 8, col);
-    for (int y = 0; y < 8; ++y) tmp[y * 8 + u] = col[y];
+// -> samples, level shift +128, clamp.  `dc_only`: every AC coefficient is zero.
+CXNIO_CLONES static void Idct8x8(const float* in, uint8_t* out, int stride, bool dc_only) {
+  if (dc_only) {
+    int v = int(in[0] + 128.5f + 1024.0f) - 1024;
+    v = v < 0 ? 0 : (v > 255 ? 255 : v);
+    for (int y = 0; y < 8; ++y) memset(out + y * stride, v, 8);
+    return;
   }
+  float a[64], b[64];
+  Idct8Lanes(in, a);                                   // along v for every column u: a[y * 8 + u]
+  for (int y = 0; y < 8; ++y)
+    for (int u = 0; u < 8; ++u) b[u * 8 + y] = a[y * 8 + u];
+  Idct8Lanes(b, a);                                    // along u for every row y: a[x * 8 + y]
   for (int y = 0; y < 8; ++y) {
-    Idct8(tmp + y * 8, 1, col);
     uint8_t* o = out + y * stride;
     for (int x = 0; x < 8; ++x) {
-      const int v = int(col[x] + 128.5f + 1024.0f) - 1024;      // floor for the value range of interest
+      int v = int(a[x * 8 + y] + 128.5f + 1024.0f) - 1024;      // floor for the value range of interest
       o[x] = uint8_t(v < 0 ? 0 : (v > 255 ? 255 : v));
     }
+  }
+}
+
+// one row of YCbCr samples -> interleaved RGB bytes (libjpeg's fixed-point constants)
+CXNIO_CLONES static void YccRowToRgb(const uint8_t* yy, const uint8_t* cb, const uint8_t* cr, uint8_t* px, int width) {
+  for (int x = 0; x < width; ++x) {
+    const int Y = yy[x], u = cb[x] - 128, v = cr[x] - 128;
+    int r = Y + ((91881 * v + 32768) >> 16);
+    int g = Y + ((-22554 * u - 46802 * v + 32768) >> 16);
+    int b = Y + ((116130 * u + 32768) >> 16);
+    r = r < 0 ? 0 : (r > 255 ? 255 : r);
+    g = g < 0 ? 0 : (g > 255 ? 255 : g);
+    b = b < 0 ? 0 : (b > 255 ? 255 : b);
+    px[3 * x] = uint8_t(r); px[3 * x + 1] = uint8_t(g); px[3 * x + 2] = uint8_t(b);
+  }
+}
+
+// one row of YCbCr samples -> three planar float rows
+CXNIO_CLONES static void YccRowToPlanar(const uint8_t* yy, const uint8_t* cb, const uint8_t* cr, float* o0, float* o1,
+                                        float* o2, int width) {
+  for (int x = 0; x < width; ++x) {
+    const int Y = yy[x], u = cb[x] - 128, v = cr[x] - 128;
+    int r = Y + ((91881 * v + 32768) >> 16);
+    int g = Y + ((-22554 * u - 46802 * v + 32768) >> 16);
+    int b = Y + ((116130 * u + 32768) >> 16);
+    o0[x] = float(r < 0 ? 0 : (r > 255 ? 255 : r));
+    o1[x] = float(g < 0 ? 0 : (g > 255 ? 255 : g));
+    o2[x] = float(b < 0 ? 0 : (b > 255 ? 255 : b));
   }
 }
 
@@ -258,6 +311,7 @@ class Decoder {
         if (nsym > 256 || p + 17 + nsym > end) return kCorrupt;
         HuffTable& h = tc ? ac_[th] : dc_[th];
         if (!h.Build(p + 1, p + 17, nsym)) return kCorrupt;
+        if (tc) h.BuildFastAc();
         p += 17 + nsym;
       }
     } else if (m == 0xDD) {     // restart interval
@@ -315,7 +369,7 @@ class Decoder {
   }
 
   // ---------------------------------------------------------------- sequential block
-  int DecodeBlockSeq(BitReader& br, Component& c, float* deq) {
+  int DecodeBlockSeq(BitReader& br, Component& c, float* deq, bool* dc_only) {
     const HuffTable& hd = dc_[c.td];
     const HuffTable& ha = ac_[c.ta];
     const float* q = qf_[c.tq];
@@ -324,7 +378,19 @@ class Decoder {
     if (t < 0 || t > 15) return kCorrupt;
     c.pred += br.Extend(t);
     deq[0] = float(c.pred) * q[0];
+    *dc_only = true;
     for (int k = 1; k < 64;) {
+      if (br.nbits < 16) br.Fill();
+      const int fast = ha.fast_ac[br.Peek(9)];
+      if (fast) {               // code and magnitude bits together in the 9-bit window
+        k += (fast >> 4) & 15;
+        if (k > 63) return kCorrupt;
+        br.Skip(fast & 15);
+        const int z = kZigzag[k++];
+        deq[z] = float(fast >> 8) * q[z];
+        *dc_only = false;
+        continue;
+      }
       int rs = br.Decode(ha);
       if (rs < 0) return kCorrupt;
       const int r = rs >> 4, s = rs & 15;
@@ -337,6 +403,7 @@ class Decoder {
       if (k > 63) return kCorrupt;
       const int z = kZigzag[k++];
       deq[z] = float(br.Extend(s)) * q[z];
+      *dc_only = false;
     }
     return kOk;
   }
@@ -452,6 +519,7 @@ class Decoder {
     eobrun_ = 0;
     int todo = restart_interval_ ? restart_interval_ : 0x7fffffff;
     float deq[64];
+    bool dc_only = false;
     int rc = kOk;
     auto restart_check = [&]() -> bool {      // returns false when the scan's data ended
       if (--todo > 0) return true;
@@ -477,8 +545,8 @@ class Decoder {
             int16_t* blk = c.coef.data() + (size_t(by) * c.bw + bx) * 64;
             rc = ss == 0 ? DecodeBlockProgDC(br, c, blk, ah, al) : DecodeBlockProgAC(br, c, blk, ss, se, ah, al);
           } else {
-            rc = DecodeBlockSeq(br, c, deq);
-            if (rc == kOk) Idct8x8(deq, c.plane.data() + (size_t(by) * 8 * c.bw + bx) * 8, c.bw * 8);
+            rc = DecodeBlockSeq(br, c, deq, &dc_only);
+            if (rc == kOk) Idct8x8(deq, c.plane.data() + (size_t(by) * 8 * c.bw + bx) * 8, c.bw * 8, dc_only);
           }
           if (rc != kOk) break;
           if (!restart_check()) { by = nby; break; }
@@ -494,8 +562,8 @@ class Decoder {
                 if (progressive_) {
                   rc = DecodeBlockProgDC(br, c, c.coef.data() + (size_t(by) * c.bw + bx) * 64, ah, al);
                 } else {
-                  rc = DecodeBlockSeq(br, c, deq);
-                  if (rc == kOk) Idct8x8(deq, c.plane.data() + (size_t(by) * 8 * c.bw + bx) * 8, c.bw * 8);
+                  rc = DecodeBlockSeq(br, c, deq, &dc_only);
+                  if (rc == kOk) Idct8x8(deq, c.plane.data() + (size_t(by) * 8 * c.bw + bx) * 8, c.bw * 8, dc_only);
                 }
                 if (rc != kOk) break;
               }
@@ -522,8 +590,12 @@ class Decoder {
       for (int by = 0; by < c.bh; ++by)
         for (int bx = 0; bx < c.bw; ++bx) {
           const int16_t* blk = c.coef.data() + (size_t(by) * c.bw + bx) * 64;
-          for (int k = 0; k < 64; ++k) deq[k] = float(blk[k]) * q[k];
-          Idct8x8(deq, c.plane.data() + (size_t(by) * 8 * c.bw + bx) * 8, c.bw * 8);
+          bool dc_only = true;
+          for (int k = 0; k < 64; ++k) {
+            deq[k] = float(blk[k]) * q[k];
+            if (k && blk[k]) dc_only = false;
+          }
+          Idct8x8(deq, c.plane.data() + (size_t(by) * 8 * c.bw + bx) * 8, c.bw * 8, dc_only);
         }
     }
   }
@@ -599,25 +671,20 @@ class Decoder {
         UpsampledRow(comp_[2], y, cr, colsum);
       }
       uint8_t* px = line.data();
+      float* o0 = planar ? planar + size_t(y) * width : nullptr;
+      if (ncomp == 3 && !is_rgb) {
+        if (rgb) YccRowToRgb(yy, cb, cr, rgb + size_t(y) * width * 3, width);
+        if (planar) YccRowToPlanar(yy, cb, cr, o0, o0 + plane, o0 + 2 * plane, width);
+        continue;
+      }
       if (ncomp == 1) {
         for (int x = 0; x < width; ++x) px[3 * x] = px[3 * x + 1] = px[3 * x + 2] = yy[x];
-      } else if (is_rgb) {
-        for (int x = 0; x < width; ++x) { px[3 * x] = yy[x]; px[3 * x + 1] = cb[x]; px[3 * x + 2] = cr[x]; }
       } else {
-        for (int x = 0; x < width; ++x) {
-          const int Y = yy[x], u = cb[x] - 128, v = cr[x] - 128;
-          px[3 * x] = Clamp(Y + ((91881 * v + 32768) >> 16));
-          px[3 * x + 1] = Clamp(Y + ((-22554 * u - 46802 * v + 32768) >> 16));
-          px[3 * x + 2] = Clamp(Y + ((116130 * u + 32768) >> 16));
-        }
+        for (int x = 0; x < width; ++x) { px[3 * x] = yy[x]; px[3 * x + 1] = cb[x]; px[3 * x + 2] = cr[x]; }
       }
       if (rgb) memcpy(rgb + size_t(y) * width * 3, px, size_t(width) * 3);
-      if (planar) {
-        float* o0 = planar + size_t(y) * width;
-        float* o1 = o0 + plane;
-        float* o2 = o1 + plane;
-        for (int x = 0; x < width; ++x) { o0[x] = px[3 * x]; o1[x] = px[3 * x + 1]; o2[x] = px[3 * x + 2]; }
-      }
+      if (planar)
+        for (int x = 0; x < width; ++x) { o0[x] = px[3 * x]; o0[plane + x] = px[3 * x + 1]; o0[2 * plane + x] = px[3 * x + 2]; }
     }
   }
 };

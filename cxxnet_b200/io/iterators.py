@@ -327,6 +327,7 @@ class ImageBinIterator(IIterator):
 
     def __init__(self, two_stage: bool):
         self.two_stage = two_stage
+        self.raw_mode = False    # see next_raw
         self.silent = 0
         self.label_width = 1
         self.shuffle = 0
@@ -436,7 +437,7 @@ class ImageBinIterator(IIterator):
 
     def _producer(self, q, stop):
         try:
-            if self.two_stage:
+            if self.two_stage and not self.raw_mode:
                 # imgbinx decode stage: groups of blobs are decoded by native worker threads (GIL released)
                 from . import native
                 group = []
@@ -486,8 +487,19 @@ class ImageBinIterator(IIterator):
             return False
         idx, lab, payload = item
         self.out.index, self.out.label = idx, lab
-        self.out.data = payload if self.two_stage else _decode_image(payload)
+        self.out.data = payload if (self.two_stage and not self.raw_mode) else _decode_image(payload)
         return True
+
+    def next_raw(self):
+        """(index, label, encoded bytes) of the next record, or None at the end; needs ``raw_mode`` (set
+        before ``before_first``), in which the producer thread hands over blobs without decoding them - the
+        batch stage then decodes a whole batch on native worker threads"""
+        assert self.raw_mode, "next_raw needs raw_mode"
+        item = self._q.get()
+        if item is None:
+            self._q.put(None)
+            return None
+        return item
 
     def value(self):
         return self.out
@@ -637,6 +649,66 @@ class AugmentIterator(IIterator):
     def close(self):
         self.base.close()
 
+    # ---- the random decisions of one instance, drawn in the reference's order (iter_augment_proc-inl.hpp:98-162)
+    def mean_mode(self) -> int:
+        """0 none, 1 mean_value per channel, 2 / 3 mean image (decided per instance by its size: 2 when the
+        image has the mean image's size - subtract, then crop - else 3: crop, then subtract)"""
+        if self.mean_r > 0 or self.mean_g > 0 or self.mean_b > 0:
+            return 1
+        if not self.meanfile_ready or not self.name_meanimg:
+            return 0
+        return 2
+
+    def draw_params(self, src_h: int, src_w: int):
+        """(y0, x0, flip, contrast, illum) for a decoded image of the given size"""
+        c, H, W = self.shape
+        assert src_h >= H and src_w >= W, "Data size must be bigger than the input size to net."
+        yy, xx = src_h - H, src_w - W
+        if self.rand_crop != 0 and (yy != 0 or xx != 0):
+            yy, xx = self.rnd.next_uint32(yy + 1), self.rnd.next_uint32(xx + 1)
+        else:
+            yy, xx = yy // 2, xx // 2
+        if src_h != H and self.crop_y_start != -1: yy = self.crop_y_start
+        if src_w != W and self.crop_x_start != -1: xx = self.crop_x_start
+        contrast = self.rnd.next_double() * self.max_random_contrast * 2 - self.max_random_contrast + 1
+        illum = self.rnd.next_double() * self.max_random_illumination * 2 - self.max_random_illumination
+        flip = self.rand_mirror != 0 and self.rnd.next_double() < 0.5
+        if self.mean_mode() != 0:
+            flip = flip or self.mirror == 1
+        return yy, xx, bool(flip), contrast, illum
+
+    def apply_params(self, data: np.ndarray, params) -> np.ndarray:
+        """NumPy statement of the per-instance arithmetic (also the oracle of the native batch path)"""
+        yy, xx, flip, contrast, illum = params
+        c, H, W = self.shape
+
+        def crop(t):
+            return t[:, yy:yy + H, xx:xx + W]
+        mode = self.mean_mode()
+        if mode == 1:
+            data = data.copy()
+            data[0] -= self.mean_b
+            if data.shape[0] > 2:
+                data[1] -= self.mean_g
+                data[2] -= self.mean_r
+            img = crop(data * contrast + illum)
+            if flip:
+                img = img[:, :, ::-1]
+        elif mode == 0:
+            img = crop(data)
+            if flip:
+                img = img[:, :, ::-1]
+        elif data.shape == self.meanimg.shape:
+            img = crop((data - self.meanimg) * contrast + illum)
+            if flip:
+                img = img[:, :, ::-1]
+        else:
+            img = crop(data)
+            if flip:
+                img = img[:, :, ::-1]
+            img = (img - self.meanimg) * contrast + illum
+        return np.ascontiguousarray(img * self.scale, dtype=np.float32)
+
     def _set_data(self, d: DataInst):
         self.out.label, self.out.index = d.label, d.index
         data = self.aug.process(d.data, self.rnd)
@@ -644,46 +716,7 @@ class AugmentIterator(IIterator):
         if H == 1:
             self.out.data = (data * self.scale).astype(np.float32)
             return
-        assert data.shape[1] >= H and data.shape[2] >= W, "Data size must be bigger than the input size to net."
-        yy, xx = data.shape[1] - H, data.shape[2] - W
-        if self.rand_crop != 0 and (yy != 0 or xx != 0):
-            yy, xx = self.rnd.next_uint32(yy + 1), self.rnd.next_uint32(xx + 1)
-        else:
-            yy, xx = yy // 2, xx // 2
-        if data.shape[1] != H and self.crop_y_start != -1: yy = self.crop_y_start
-        if data.shape[2] != W and self.crop_x_start != -1: xx = self.crop_x_start
-        contrast = self.rnd.next_double() * self.max_random_contrast * 2 - self.max_random_contrast + 1
-        illum = self.rnd.next_double() * self.max_random_illumination * 2 - self.max_random_illumination
-
-        def crop(t):
-            return t[:, yy:yy + H, xx:xx + W]
-        if self.mean_r > 0 or self.mean_g > 0 or self.mean_b > 0:
-            data = data.copy()
-            data[0] -= self.mean_b
-            if data.shape[0] > 2:
-                data[1] -= self.mean_g
-                data[2] -= self.mean_r
-            flip = (self.rand_mirror != 0 and self.rnd.next_double() < 0.5) or self.mirror == 1
-            img = crop(data * contrast + illum)
-        elif not self.meanfile_ready or not self.name_meanimg:
-            flip = self.rand_mirror != 0 and self.rnd.next_double() < 0.5
-            img = crop(data)
-        else:
-            flip = (self.rand_mirror != 0 and self.rnd.next_double() < 0.5) or self.mirror == 1
-            if data.shape == self.meanimg.shape:
-                img = crop((data - self.meanimg) * contrast + illum)
-                if flip:
-                    img = img[:, :, ::-1]
-                    flip = False
-            else:
-                img = crop(data)
-                if flip:
-                    img = img[:, :, ::-1]
-                    flip = False
-                img = (img - self.meanimg) * contrast + illum
-        if flip:
-            img = img[:, :, ::-1]
-        self.out.data = np.ascontiguousarray(img * self.scale, dtype=np.float32)
+        self.out.data = self.apply_params(data, self.draw_params(data.shape[1], data.shape[2]))
 
     def next(self):
         if not self.base.next():
@@ -733,6 +766,10 @@ class BatchAdaptIterator(IIterator):
         self.out = DataBatch()
         self.input_dtype = "fp32"     # bf16: batches leave the iterator as bf16 (half the H2D bytes; the b200
         self._half = None             # backend computes in bf16 anyway).  Not a reference option.
+        self.native_pipeline = 1      # decode + augment + batch assembly on native threads where applicable
+        self.decode_threads = 0       # 0 = min(8, cores)
+        self._native = False
+        self._pending = []            # native path: records of the batch being assembled
 
     def set_param(self, name, val):
         self.base.set_param(name, val)
@@ -746,9 +783,30 @@ class BatchAdaptIterator(IIterator):
         if name == "round_batch": self.round_batch = int(val)
         if name == "silent": self.silent = int(val)
         if name == "test_skipread": self.test_skipread = int(val)
+        if name == "native_pipeline": self.native_pipeline = int(val)
+        if name == "decode_threads": self.decode_threads = int(val)
+
+    def _plan_native(self) -> bool:
+        """The fused native batch path (csrc/runtime/batch_pipeline.cpp) applies when the chain below is
+        imgbin(x) -> augment without the affine group, on 3-channel images, and the library is built."""
+        from . import native
+        aug = self.base
+        if not (self.native_pipeline and isinstance(aug, AugmentIterator) and isinstance(aug.base, ImageBinIterator)):
+            return False
+        if native.lib() is None or not hasattr(native.lib(), "cxnio_decode_augment_batch"):
+            return False
+        if aug.aug.need_process() or len(self.shape) != 3 or self.shape[0] != 3 or self.shape[1] == 1:
+            return False
+        if aug.mean_mode() == 2 and (aug.meanimg is None or aug.meanimg.shape[0] != 3):
+            return False
+        return True
 
     def init(self):
         self.base.init()
+        self._native = self._plan_native()
+        if self._native:
+            self.base.base.raw_mode = True
+            self.base.base.before_first()      # restart the producer thread so that it hands over encoded records
         self.out.alloc_dense((self.batch_size,) + tuple(self.shape), self.batch_size, self.label_width, pin=True)
         self._data_np = self.out.data.numpy()
         self._label_np = self.out.label.numpy()
@@ -773,6 +831,58 @@ class BatchAdaptIterator(IIterator):
         self.out.inst_index[top] = d.index
         self._data_np[top] = d.data.reshape(self._data_np.shape[1:])
 
+    # the two ways of taking one instance from below: decoded and augmented by the Python stages, or - native
+    # path - as an encoded record that is only noted; _flush_native then processes the whole batch at once
+    def _take(self, top) -> bool:
+        if not self._native:
+            if not self.base.next():
+                return False
+            self._put(top, self.base.value())
+            return True
+        rec = self.base.base.next_raw()
+        if rec is None:
+            return False
+        self._label_np[top, :] = rec[1][: self.label_width]
+        self.out.inst_index[top] = rec[0]
+        self._pending.append((top, rec[2]))
+        return True
+
+    def _flush_native(self) -> None:
+        """decode + augment every noted record into its batch slot (native worker threads)"""
+        if not self._pending:
+            return
+        from . import native
+        aug = self.base
+        items, fallback = [], {}
+        for top, blob in self._pending:
+            info = native.jpeg_info(blob)
+            pixels = None
+            if info is None:                               # not a JPEG the native decoder takes
+                pixels = _decode_image(blob, native_first=False)
+                h, w = pixels.shape[1], pixels.shape[2]
+            else:
+                w, h = info[0], info[1]
+            items.append((blob, pixels, h, w) + tuple(aug.draw_params(h, w)))
+        mode = aug.mean_mode()
+        mean = None
+        if mode == 1:
+            mean = np.asarray([aug.mean_b, aug.mean_g, aug.mean_r], dtype=np.float32)
+        elif mode == 2:
+            mean = aug.meanimg
+        to_half = self._half is not None
+        dst = self._half.data if to_half else self.out.data
+        first = self._pending[0][0]
+        assert [t for t, _ in self._pending] == list(range(first, first + len(items)))
+        status = native.decode_augment_batch(items, self.shape, mode, mean, aug.scale, dst[first:first + len(items)],
+                                             to_half, self.decode_threads)
+        for k, st in enumerate(status):
+            if st != 0:                                    # e.g. a damaged file: the library decoders get a try
+                blob, pixels, h, w = items[k][:4]
+                data = pixels if pixels is not None else _decode_image(blob, native_first=False)
+                res = torch.from_numpy(aug.apply_params(data, items[k][4:]))
+                dst[first + k].copy_(res)
+        self._pending = []
+
     def next(self):
         self.out.num_batch_padd = 0
         if self.test_skipread != 0 and self.head == 0:
@@ -781,28 +891,33 @@ class BatchAdaptIterator(IIterator):
         if self.num_overflow != 0:
             return False
         top = 0
-        while self.base.next():
-            self._put(top, self.base.value())
+        while self._take(top):
             top += 1
             if top >= self.batch_size:
+                self._flush_native()
                 return True
         if top != 0:
             if self.round_batch != 0:
                 self.num_overflow = 0
                 self.base.before_first()
                 while top < self.batch_size:
-                    assert self.base.next(), "number of input must be bigger than batch size"
-                    self._put(top, self.base.value())
+                    assert self._take(top), "number of input must be bigger than batch size"
                     top += 1
                     self.num_overflow += 1
                 self.out.num_batch_padd = self.num_overflow
             else:
                 self.out.num_batch_padd = self.batch_size - top
+            self._flush_native()
             return True
         return False
 
     def value(self):
         assert self.head == 0, "must call Next to get value"
+        if self._half is not None and self._native:
+            # the native path wrote bf16 straight into the pinned half-precision batch
+            self._half.batch_size, self._half.num_batch_padd = self.out.batch_size, self.out.num_batch_padd
+            self._half.extra_data = self.out.extra_data
+            return self._half
         if self._half is not None:
             self._half.data.copy_(self.out.data)      # fp32 -> bf16 on the producer side
             self._half.batch_size, self._half.num_batch_padd = self.out.batch_size, self.out.num_batch_padd

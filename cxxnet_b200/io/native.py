@@ -32,8 +32,21 @@ def lib():
             L.cxnio_jpeg_decode_many.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_char_p),
                                                  ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(ctypes.c_void_p),
                                                  IP, IP, IP, ctypes.c_int]
+        if hasattr(L, "cxnio_decode_augment_batch"):
+            L.cxnio_decode_augment_batch.argtypes = [
+                ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_int,
+                ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+            assert L.cxnio_aug_item_bytes() == ctypes.sizeof(AugItem)
         _lib = L
     return _lib
+
+
+class AugItem(ctypes.Structure):
+    """one instance of ``cxnio_decode_augment_batch`` (``csrc/runtime/batch_pipeline.cpp`` CxnioAugItem)"""
+    _fields_ = [("buf", ctypes.c_char_p), ("size", ctypes.c_uint64), ("pixels", ctypes.c_void_p),
+                ("src_h", ctypes.c_int32), ("src_w", ctypes.c_int32), ("y0", ctypes.c_int32), ("x0", ctypes.c_int32),
+                ("flip", ctypes.c_int32), ("contrast", ctypes.c_float), ("illum", ctypes.c_float)]
 
 
 class PageReader:
@@ -121,3 +134,61 @@ def jpeg_decode_many(bufs: List[bytes], nthreads: int = 0) -> list:
     for j, i in enumerate(idx):
         outs[i] = arrs[j] if st[j] == 0 else None
     return outs
+
+
+def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, dst_bf16: bool,
+                         nthreads: int = 0) -> List[int]:
+    """Decode, crop, mean-subtract, jitter, mirror and scale ``len(items)`` images into the rows of ``dst``
+    (a contiguous torch tensor [n, 3, H, W], fp32 or bf16) on native worker threads.
+
+    items: tuples ``(encoded bytes, decoded planar float array or None, src_h, src_w, y0, x0, flip, contrast,
+    illum)``; ``mean_mode`` 0 none / 1 per-channel values / 2 mean image (per instance: subtracted before the
+    crop when it has the decoded size, after it when it has the crop size).  Returns one status per item
+    (0 = written)."""
+    import numpy as np
+    n = len(items)
+    c, H, W = shape
+    arr = (AugItem * n)()
+    keep = []
+    mean_h = mean_w = 0
+    mean_ptr = None
+    if mean is not None:
+        mean = np.ascontiguousarray(mean, dtype=np.float32)
+        mean_ptr = mean.ctypes.data
+        if mean_mode == 2:
+            mean_h, mean_w = mean.shape[1], mean.shape[2]
+    status = (ctypes.c_int * n)()
+    # a mean image is used in one of two ways depending on the instance's decoded size: split the batch
+    groups = {}
+    for i, (blob, pixels, h, w, y0, x0, flip, contrast, illum) in enumerate(items):
+        a = arr[i]
+        if pixels is not None:
+            pixels = np.ascontiguousarray(pixels, dtype=np.float32)
+            keep.append(pixels)
+            a.buf, a.size, a.pixels = None, 0, pixels.ctypes.data
+        else:
+            a.buf, a.size, a.pixels = blob, len(blob), None
+        a.src_h, a.src_w, a.y0, a.x0, a.flip = h, w, y0, x0, 1 if flip else 0
+        a.contrast, a.illum = contrast, illum
+        mode = mean_mode
+        if mean_mode == 2 and (h, w) != (mean_h, mean_w):
+            mode = 3
+        groups.setdefault(mode, []).append(i)
+    assert dst.is_contiguous() and tuple(dst.shape[1:]) == (c, H, W) and dst.shape[0] >= n
+    inst_bytes = c * H * W * (2 if dst_bf16 else 4)
+    nthreads = nthreads or min(8, os.cpu_count() or 1)
+    for mode, idx in groups.items():
+        # contiguous runs of instances that share a mode go down in one call
+        run_start = 0
+        while run_start < len(idx):
+            run_end = run_start
+            while run_end + 1 < len(idx) and idx[run_end + 1] == idx[run_end] + 1:
+                run_end += 1
+            i0, cnt = idx[run_start], run_end - run_start + 1
+            lib().cxnio_decode_augment_batch(
+                ctypes.addressof(arr) + i0 * ctypes.sizeof(AugItem), cnt, c, H, W, mode, mean_ptr,
+                mean_h if mode == 2 else H, mean_w if mode == 2 else W, scale,
+                dst.data_ptr() + i0 * inst_bytes, 1 if dst_bf16 else 0,
+                ctypes.cast(ctypes.addressof(status) + 4 * i0, ctypes.POINTER(ctypes.c_int)), nthreads)
+            run_start = run_end + 1
+    return list(status)

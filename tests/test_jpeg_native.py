@@ -107,3 +107,131 @@ def test_imgbin_iterators_decode_jpeg_pages(tmp_path):
         assert [r[0] for r in rows[:6]] == [0, 1, 2, 3, 4, 5]
         for idx, data in rows[:6]:
             assert np.abs(data.astype(np.int32) - _reference(bufs[idx])).max() <= 3
+
+
+def _jpeg_bin(tmp_path, n=11, w=30, h=28):
+    from cxxnet_b200.io.iterators import BinaryPage
+    page, lines = BinaryPage(), []
+    for i in range(n):
+        if i == 4:                               # one PNG among the JPEGs: decoded by the library path
+            b = io.BytesIO()
+            _picture(w, h, seed=i).save(b, "PNG")
+            blob = b.getvalue()
+        else:
+            blob = _encode(_picture(w, h, seed=i), quality=88, subsampling=i % 3, progressive=(i % 2 == 0))
+        assert page.push(blob)
+        lines.append("%d\t%d\timg%d\n" % (i, i % 5, i))
+    (tmp_path / "j.lst").write_text("".join(lines))
+    (tmp_path / "j.bin").write_bytes(bytes(page.raw))
+
+
+@pytest.mark.parametrize("mean", ["none", "value", "image"])
+@pytest.mark.parametrize("dtype", ["fp32", "bf16"])
+def test_native_batch_pipeline_equals_python_stages(tmp_path, mean, dtype):
+    """decode + augment + batch assembly on native threads (csrc/runtime/batch_pipeline.cpp) produces the batches
+    of the Python iterator stages bit for bit: same random decisions, same single-precision arithmetic"""
+    import torch
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.io.data import create_iterator
+    _jpeg_bin(tmp_path)
+    extra = {"none": "", "value": " mean_value = 100,110,120\n",
+             "image": ' image_mean = "%s"\n' % (tmp_path / "mean.bin")}[mean]
+
+    def batches(native_pipeline, kind):
+        it = create_iterator(parse_config_string(
+            'iter = %s\n image_list = "%s"\n image_bin = "%s"\n batch_size = 4\n input_shape = 3,24,26\n'
+            ' rand_crop = 1\n rand_mirror = 1\n max_random_contrast = 0.2\n max_random_illumination = 6\n'
+            ' divideby = 64\n round_batch = 1\n seed_data = 5\n silent = 1\n input_dtype = %s\n native_pipeline = %d\n'
+            ' decode_threads = 3\n%siter = end\n'
+            % (kind, tmp_path / "j.lst", tmp_path / "j.bin", dtype, native_pipeline, extra)))
+        it.init()
+        assert it._native == bool(native_pipeline)
+        out = []
+        for _ in range(2):                       # two passes: the wrap-around of round_batch included
+            it.before_first()
+            while it.next():
+                b = it.value()
+                out.append((b.data.clone(), b.label.clone(), b.inst_index.copy(), b.num_batch_padd))
+        it.close()
+        return out
+
+    if mean == "image":
+        batches(0, "imgbin")                     # the first use computes and caches the mean image (and draws while doing so)
+        assert (tmp_path / "mean.bin").exists()
+    want = batches(0, "imgbin")
+    for kind in ("imgbin", "imgbinx"):
+        got = batches(1, kind)
+        assert len(got) == len(want) == 6
+        for (d0, l0, i0, p0), (d1, l1, i1, p1) in zip(want, got):
+            assert d1.dtype == (torch.bfloat16 if dtype == "bf16" else torch.float32)
+            assert torch.equal(d0, d1) and torch.equal(l0, l1) and list(i0) == list(i1) and p0 == p1
+
+
+def test_native_augment_modes_against_numpy_statement():
+    """every mean mode of cxnio_decode_augment_batch on decoded pixels and on JPEG bytes, mirrored or not,
+    against AugmentIterator.apply_params"""
+    import torch
+    from cxxnet_b200.io.iterators import AugmentIterator, SyntheticInstIterator
+    rs = np.random.RandomState(3)
+    H, W = 20, 22
+    for mode_name in ("none", "value", "mean_full", "mean_crop"):
+        aug = AugmentIterator(SyntheticInstIterator())
+        aug.shape = (3, H, W)
+        aug.scale = 1.0 / 32
+        if mode_name == "value":
+            aug.mean_b, aug.mean_g, aug.mean_r = 90.0, 100.0, 110.0
+        if mode_name.startswith("mean_"):
+            aug.name_meanimg, aug.meanfile_ready = "x", True
+            aug.meanimg = (rs.rand(3, 26, 30) * 255).astype(np.float32) if mode_name == "mean_full" \
+                else (rs.rand(3, H, W) * 255).astype(np.float32)
+        items, want = [], []
+        for i in range(6):
+            blob = _encode(_picture(30, 26, seed=20 + i), quality=90)
+            pixels = native.jpeg_decode(blob)
+            params = (i % 5, (2 * i) % 7, i % 2 == 1, 1.0 + 0.03 * i, 2.0 - i)
+            items.append((blob, pixels if i % 3 == 0 else None, 26, 30) + params)
+            want.append(aug.apply_params(pixels, params))
+        mode = aug.mean_mode()
+        mean = {0: None, 1: np.asarray([90.0, 100.0, 110.0], np.float32), 2: aug.meanimg}[mode]
+        for bf16 in (False, True):
+            dst = torch.zeros((6, 3, H, W), dtype=torch.bfloat16 if bf16 else torch.float32)
+            st = native.decode_augment_batch(items, (3, H, W), mode, mean, aug.scale, dst, bf16, 2)
+            assert st == [0] * 6
+            ref = torch.from_numpy(np.stack(want))
+            assert torch.equal(dst, ref.to(dst.dtype)), mode_name
+    # a crop that leaves the image is reported, not written
+    dst = torch.zeros((1, 3, H, W))
+    bad = [(blob, None, 26, 30, 10, 0, False, 1.0, 0.0)]
+    assert native.decode_augment_batch(bad, (3, H, W), 0, None, 1.0, dst, False, 1) != [0]
+
+
+def test_decoder_survives_mutated_inputs_under_sanitizers(tmp_path):
+    """tools/jpeg_fuzz.cpp built with ASAN + UBSAN: damaged files may be rejected, never crash or over-read"""
+    import os
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cxx = shutil.which("g++")
+    if cxx is None:
+        pytest.skip("no g++")
+    exe = tmp_path / "jpeg_fuzz"
+    r = subprocess.run([cxx, "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined",
+                        "-fno-sanitize-recover=undefined", "-pthread", "-o", str(exe),
+                        os.path.join(root, "tools", "jpeg_fuzz.cpp"),
+                        os.path.join(root, "csrc", "runtime", "jpeg_decoder.cpp")],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    if r.returncode != 0 and "sanitize" in r.stdout:
+        pytest.skip("sanitizer runtime not available: " + r.stdout[-200:])
+    assert r.returncode == 0, r.stdout[-2000:]
+    seeds = []
+    for i, kw in enumerate([dict(quality=90), dict(quality=80, progressive=True),
+                            dict(quality=70, subsampling=2, restart_marker_blocks=2),
+                            dict(quality=95, subsampling=1, progressive=True)]):
+        p = tmp_path / ("seed%d.jpg" % i)
+        p.write_bytes(_encode(_picture(52, 40, seed=i), **kw))
+        seeds.append(str(p))
+    r = subprocess.run([str(exe), "1500"] + seeds, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                       timeout=600)
+    assert r.returncode == 0 and "decoded" in r.stdout, r.stdout[-3000:]
+    decoded = int(r.stdout.split("decoded")[1].split()[0])
+    assert decoded > 100          # the mutations are mild enough that a good share still decodes
