@@ -200,7 +200,7 @@ def run_ours(args, rank, world, local):
     out = {
         "metric": METRIC, "value": B * args.steps / (ms / 1e3), "unit": "images/sec", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
+        "scaling": args.scaling, "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
         "config": {"model": "AlexNet (example/ImageNet/ImageNet.conf)", "global_batch": B, "input": "3x227x227 (bf16 NCHW batches from the iterator, fp32 labels)",
                    "per_gpu_batch": hi - lo, "parallelism": "dp%d" % world, "updater": "sgd momentum 0.9 wd 5e-4",
                    "l2": "no flush: per-step working set (activations + im2col + 244 MB weights) far exceeds "
@@ -266,7 +266,7 @@ def run_library(args, rank, world, local):
     ms = timed(step, args.steps, world)
     return {"metric": METRIC, "value": B * args.steps / (ms / 1e3), "unit": "images/sec", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "library",
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "library",
             "config": {"model": "AlexNet", "global_batch": B, "parallelism": "dp%d" % world,
                        "note": "stock PyTorch cuDNN/cuBLAS + NCCL all-reduce + torch SGD (library baseline B3)"}}
 
@@ -278,6 +278,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "library"])
     ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong (default, the reference's semantics): --batch is the global batch, split over the "
+                         "GPUs; weak: --batch images per GPU, global batch = batch x GPUs (secondary series)")
     ap.add_argument("--extra", default="", help="extra config lines for the ours arm, ';' separated")
     args = ap.parse_args()
     args.extra = args.extra.replace(";", "\n")
@@ -290,6 +293,8 @@ def main():
                               "and is absent offline; see DESIGN.md section 'Reference arm'"}))
         return 0
     rank, world, local = dist_setup(args.gpus)
+    if args.scaling == "weak":
+        args.batch *= world
     out = run_ours(args, rank, world, local) if args.impl == "ours" else run_library(args, rank, world, local)
     if rank == 0:
         print(json.dumps(out))
