@@ -653,6 +653,267 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
   }
 }
 
+// ===================================================================================================
+// Cluster variant of the forward kernel (opt-in: cxn_conv_tune(7, 2) or CXN_CONV_CLUSTER=2).
+// Two CTAs of a cluster work on two different 128/256-row pixel tiles of the SAME output columns, so they
+// need the same filter tile: each fetches one half of it (bn/2 filter rows x 64) and multicasts it into
+// both CTAs' rings - the filter crosses L2->SM once per pair instead of once per CTA.  The patches come
+// by im2col-mode TMA into the CTA's own ring (no gather warps: 6 warps).  The tensor map of the multicast
+// load covers this GPU's weights only.
+//
+// Protocol per ring stage: full barrier (1 arrival + bytes) = own patch tile + both filter halves;
+// empty barrier (2 arrivals) = tcgen05.commit of BOTH CTAs' MMA warps (multicast commit), because a
+// producer writes into its peer's stage as well as its own.  Both CTAs run the same (n, group, k) loop,
+// so the barriers of a pair advance in lock step; every wait is bounded (mbar_wait traps).
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_3d_mc(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
+                                               int c2, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"(mask)
+      : "memory");
+}
+
+constexpr int kClusterThreads = 192;   // warp 0 TMA | warp 1 MMA + TMEM | warps 2-5 epilogue
+
+template <int BNMAX, int MH>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kClusterThreads, 1)
+conv_fprop_cluster_kernel(const __grid_constant__ CUtensorMap tmHalf, const __grid_constant__ CUtensorMap tmPatch,
+                          const Params p) {
+  using C = Cfg<BNMAX, MH>;
+  constexpr int kAccStages = C::kAccStages;
+  constexpr int BMT = BM * MH;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int nst = p.stages;
+  const uint32_t bar_base = smem_base + (uint32_t)p.ring_bytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (nst + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * nst + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * nst + kAccStages + a); };
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + p.ring_bytes + 8 * (2 * nst + 2 * kAccStages + 1));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t crank = cluster_ctarank();
+  const long long rows = (long long)p.N * p.OH * p.OW;
+  const int tiles_m = (int)ceil_div_ll(rows, BMT);
+  const int pairs_m = (tiles_m + 1) >> 1;
+  const int tiles_n = ceil_div(p.Ng, p.bn);
+  const int num_kb = ceil_div(p.Kg, BK);
+  const long long total_pairs = (long long)pairs_m * tiles_n * p.G;
+  const long long cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+  const int half_rows = p.bn >> 1;               // filter rows each CTA of the pair fetches
+  const int cpk = p.Cg >> 6;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < nst; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 2);
+    }
+    for (int a = 0; a < kAccStages; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmHalf) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmPatch) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32((const void*)tmem_ptr_smem)),
+                 "n"(C::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();          // the peer's barriers exist before anything of ours can reach them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  auto decode_pair = [&](long long t, int& n_blk, int& m_blk, int& g) {
+    n_blk = (int)(t % tiles_n);
+    const long long r = t / tiles_n;
+    m_blk = 2 * (int)(r % pairs_m) + (int)crank;
+    g = (int)(r / pairs_m);
+  };
+
+  if (warp == 0) {
+    // =========================== TMA producer ===========================
+    int stage = 0;
+    uint32_t phase = 0;
+    const int ohw = p.OH * p.OW;
+    for (long long t = cluster_id; t < total_pairs; t += num_clusters) {
+      int n_blk, m_blk, g;
+      decode_pair(t, n_blk, m_blk, g);
+      // an odd tile count leaves the last pair with one real tile: its partner recomputes that tile
+      // (same loads, so the pair stays in lock step) and stores nothing
+      const int m_ld = m_blk < tiles_m ? m_blk : tiles_m - 1;
+      const long long m0 = (long long)m_ld * BMT;
+      const int pn = (int)(m0 / ohw);
+      const int r = (int)(m0 - (long long)pn * ohw);
+      const int oh = r / p.OW;
+      const int pw = (r - oh * p.OW) * p.stride_x - p.pad_x;
+      const int ph = oh * p.stride_y - p.pad_y;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait_warp(empty_bar(stage), phase ^ 1u);
+        const uint32_t sa = smem_base + stage * (uint32_t)C::kStageBytes;
+        const uint32_t sb = sa + C::kABytes;
+        if (elect_one()) {
+          mbar_expect_tx(full_bar(stage), (uint32_t)C::kABytes + (uint32_t)p.bn * BK * 2);
+          const int tap = kb / cpk, chunk = kb - tap * cpk;
+          const int kh = tap / p.KW, kw = tap - kh * p.KW;
+          tma_load_im2col_4d(sa, &tmPatch, full_bar(stage), g * p.Cg + chunk * 64, pw, ph, pn, kw, kh);
+          tma_load_3d_mc(sb + crank * (uint32_t)half_rows * 128u, &tmHalf, full_bar(stage), kb * BK,
+                         n_blk * p.bn + (int)crank * half_rows, g, (uint16_t)0x3);
+        }
+        __syncwarp();
+        if (++stage == nst) { stage = 0; phase ^= 1u; }
+      }
+    }
+    // tail: every stage we (or the peer) filled has been released by BOTH MMA warps before this CTA may
+    // leave - the peer's last commits target our barriers
+    for (int i = 0; i < nst; ++i) {
+      mbar_wait_warp(empty_bar(stage), phase ^ 1u);
+      if (++stage == nst) { stage = 0; phase ^= 1u; }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA issuer ===========================
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    constexpr uint32_t kSbo = 1024;
+    constexpr uint32_t kStep = UMMA_K * 2;
+    const uint64_t desc_hi = make_desc(0, 0u, kSbo);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (long long t = cluster_id; t < total_pairs; t += num_clusters) {
+      mbar_wait_warp(tempty_bar(acc), acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * MH * BNMAX);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait_warp(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t sa = smem_base + stage * (uint32_t)C::kStageBytes;
+        const uint32_t sb = sa + C::kABytes;
+        if (elect_one()) {
+          const uint64_t a0 = desc_hi | (uint64_t)((sa >> 4) & 0x3FFF), b0 = desc_hi | (uint64_t)((sb >> 4) & 0x3FFF);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+#pragma unroll
+            for (int h = 0; h < MH; ++h)
+              umma_bf16(d_tmem + (uint32_t)(h * BNMAX), a0 + (uint64_t)((h * C::kAHalfBytes + k * kStep) >> 4),
+                        b0 + (uint64_t)((k * kStep) >> 4), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_mc(empty_bar(stage), (uint16_t)0x3);     // frees this stage in both CTAs
+          if (kb == num_kb - 1) umma_commit(tfull_bar(acc));
+        }
+        __syncwarp();
+        if (++stage == nst) { stage = 0; phase ^= 1u; }
+      }
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  } else {
+    // =========================== epilogue ===========================
+    const int quad = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (long long t = cluster_id; t < total_pairs; t += num_clusters) {
+      int n_blk, m_blk, g;
+      decode_pair(t, n_blk, m_blk, g);
+      mbar_wait_warp(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const float* bias = p.bias != nullptr ? p.bias + (long long)g * p.Ng : nullptr;
+#pragma unroll 1
+      for (int hc = 0; hc < MH * BNMAX; hc += 32) {
+        const int h = hc / BNMAX, c0 = hc - h * BNMAX;
+        if (c0 >= p.bn) continue;
+        const long long row = (long long)m_blk * BMT + h * BM + quad * 32 + lane;
+        const int n0 = n_blk * p.bn + c0;
+        if (n0 >= p.Ng) continue;
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * MH * BNMAX + hc);
+        tmem_ld32(taddr, v);
+        tmem_ld_wait();
+        if (row >= rows) continue;
+        const int lim = min(32, min(p.bn - c0, p.Ng - n0));
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        const long long off = (long long)g * p.strideD + row * p.ldd + n0;
+        if (bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < lim) f[j] += __ldg(bias + n0 + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+        }
+        if (p.mask != nullptr) {
+          const bf16* mk = p.mask + off;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < lim && !(__bfloat162float(mk[j]) > 0.0f)) f[j] = 0.0f;
+        }
+        bf16* d = reinterpret_cast<bf16*>(p.D) + off;
+        if (lim == 32 && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+          uint4* d4 = reinterpret_cast<uint4*>(d);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(f[q * 8 + 0], f[q * 8 + 1]);
+            __nv_bfloat162 h1 = __floats2bfloat162_rn(f[q * 8 + 2], f[q * 8 + 3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(f[q * 8 + 4], f[q * 8 + 5]);
+            __nv_bfloat162 h3 = __floats2bfloat162_rn(f[q * 8 + 6], f[q * 8 + 7]);
+            uint4 u;
+            u.x = *reinterpret_cast<uint32_t*>(&h0);
+            u.y = *reinterpret_cast<uint32_t*>(&h1);
+            u.z = *reinterpret_cast<uint32_t*>(&h2);
+            u.w = *reinterpret_cast<uint32_t*>(&h3);
+            d4[q] = u;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < lim) d[j] = __float2bfloat16(f[j]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();          // nobody leaves while the peer may still signal our barriers or fill our ring
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::kTmemCols)
+                 : "memory");
+  }
+}
+
 // W[g][oc][kh][kw][ic] (ld_in) -> Wt[g][ic][KH-1-kh][KW-1-kw][oc] (ld_out): the filter of the equivalent
 // forward convolution that computes backward-data of a stride-1 convolution.  Per (group, tap) this is
 // the transpose of an ocg x icg block: 32 x 32 tiles through shared memory, both sides coalesced.
@@ -718,6 +979,8 @@ static int g_tune_stages = 0;      // force the ring depth
 static int g_tune_bnmax = 0;       // 128 / 256: force the forward tile-width class
 static int g_tune_dbg = 0;         // timing experiments (Params::dbg)
 static int g_tune_atma = -1;       // 0 / 1: fetch the patches with im2col-mode TMA
+static int g_tune_cluster = -1;    // 2: forward layers on the im2col-TMA route run as CTA pairs that share the
+                                   // filter tile by multicast (conv_fprop_cluster_kernel); -1 = read CXN_CONV_CLUSTER
 static long long* g_prof = nullptr;
 
 typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -793,6 +1056,31 @@ static int launch_g(const CUtensorMap& tm, const CUtensorMap& tmp, const Params&
   conv_igemm_kernel<BNMAX, WGRAD, GRAN, MH, ATMA><<<grid, kThreads, smem, st>>>(tm, tmp, p);
   CXN_CHECK_LAUNCH();
   return 0;
+}
+template <int BNMAX, int MH>
+static int launch_cluster(const CUtensorMap& tm_half, const CUtensorMap& tmp, const Params& p, int grid, cudaStream_t st) {
+  using C = Cfg<BNMAX, MH>;
+  if (p.stages < 2 || p.stages > C::kMaxStages || (grid & 1)) return -20;
+  if (p.ring_bytes < p.stages * C::kStageBytes || (p.ring_bytes & 1023)) return -22;
+  const int smem = p.ring_bytes + C::kFixedBytes;
+  if (smem > 232448) return -23;
+  static int max_set = 0;
+  if (smem > max_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_fprop_cluster_kernel<BNMAX, MH>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    max_set = smem;
+  }
+  conv_fprop_cluster_kernel<BNMAX, MH><<<grid, kClusterThreads, smem, st>>>(tm_half, tmp, p);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+static int cluster_mode() {
+  if (g_tune_cluster < 0) {
+    const char* e = getenv("CXN_CONV_CLUSTER");
+    g_tune_cluster = e ? atoi(e) : 0;
+  }
+  return g_tune_cluster;
 }
 // atma: the patch operand comes through `tmp` (im2col map), otherwise through the gather warps
 template <int BNMAX, bool WGRAD, int MH>
@@ -903,12 +1191,26 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
     rc = encode_im2col(&tmp, p, mh * BM);
     if (rc) return rc;
   }
+  const long long tiles_m = ceil_div_ll(rows, mh * BM);
+  if (cluster_mode() == 2 && atma && !p.b_resident && tiles_m >= 2 && num_sms() >= 2) {
+    // CTA pairs on two pixel tiles of the same output columns: each fetches half of the filter tile and
+    // multicasts it to both (tensor map over this GPU's weights)
+    CUtensorMap tmh;
+    rc = encode3d(&tmh, w, (uint64_t)p.Kg, (uint64_t)Ng, (uint64_t)G, (uint64_t)ldw, (uint64_t)Ng * ldw, BK, p.bn / 2);
+    if (rc) return rc;
+    const long long pairs = ((tiles_m + 1) / 2) * ceil_div(Ng, p.bn) * G;
+    const long long max_clusters = num_sms() / 2;
+    const int grid_c = 2 * (int)(pairs < max_clusters ? pairs : max_clusters);
+    if (mh == 2) return bnmax == 256 ? launch_cluster<256, 2>(tmh, tmp, p, grid_c, st) : launch_cluster<128, 2>(tmh, tmp, p, grid_c, st);
+    return bnmax == 256 ? launch_cluster<256, 1>(tmh, tmp, p, grid_c, st) : launch_cluster<128, 1>(tmh, tmp, p, grid_c, st);
+  }
   if (mh == 2) return bnmax == 256 ? launch<256, false, 2>(tm, tmp, atma, p, grid_final, st) : launch<128, false, 2>(tm, tmp, atma, p, grid_final, st);
   return bnmax == 256 ? launch<256, false, 1>(tm, tmp, atma, p, grid_final, st) : launch<128, false, 1>(tm, tmp, atma, p, grid_final, st);
 }
 
 // Tuning / experiment knobs; value 0 (or -1 for the switches) restores the automatic choice.
 //   0: row halves per forward tile   1: ring stages   2: gather through L1   3: tap-inner order   4: tile-width class
+//   5: timing experiments   6: im2col TMA on / off   7: 2 = CTA-pair clusters with a multicast filter tile (forward)
 // Role profiling of the forward kernel: buf = device array of [148][16] int64 (null switches it off).
 // slots: 0 TMA wait-empty, 1 TMA total | 2 MMA wait-full, 3 MMA wait-tmem-empty, 4 MMA total |
 // 5 gather wait-empty, 6 gather tile setup, 7 gather total | 8 epilogue wait-tmem-full, 9 epilogue body, 10 total
@@ -926,6 +1228,7 @@ CXN_API int cxn_conv_tune(int key, int value) {
     case 4: g_tune_bnmax = value; break;
     case 5: g_tune_dbg = value; break;
     case 6: g_tune_atma = value; break;
+    case 7: g_tune_cluster = value; break;
     default: return -1;
   }
   return 0;

@@ -1,5 +1,7 @@
 """Implicit-GEMM convolution kernels (csrc/kernels/conv_igemm_sm100.cu) against torch conv2d in
 fp32 on the same bf16-rounded operands."""
+import os
+
 import pytest
 import torch
 import torch.nn.functional as F
@@ -114,3 +116,23 @@ def test_conv_im2col_tma_and_gather_routes_agree_with_reference(atma):
         _case(40, 64, 13, 13, 96, 1, 3, 3, 1, 1)                 # enough rows for the row-paired (256-row) tiles
     finally:
         L.cxn_conv_tune(6, -1)
+
+
+@pytest.mark.skipif(os.environ.get("CXN_TEST_CLUSTER", "0") != "1",
+                    reason="CTA-pair cluster route (multicast filter tile): written without access to a GPU, "
+                           "opt-in with CXN_TEST_CLUSTER=1 until it has been run on hardware")
+def test_conv_cluster_pairs_share_the_filter_tile():
+    """cxn_conv_tune(7, 2): forward layers on the im2col-TMA route run as clusters of two CTAs that fetch half of
+    the filter tile each and multicast it to both.  Odd and even tile counts, groups, two tile widths, the
+    row-paired tiles, and the backward-data use of the same kernel."""
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    L.cxn_conv_tune(7, 2)
+    try:
+        _case(5, 256, 13, 13, 384, 1, 3, 3, 1, 1)                # conv3: 7 m-tiles (odd) x 2 n-tiles
+        _case(5, 384, 13, 13, 384, 2, 3, 3, 1, 1)                # conv4: groups
+        _case(6, 64, 16, 16, 128, 1, 3, 3, 1, 1)                 # 12 m-tiles (even), one n-tile
+        _case(40, 64, 13, 13, 96, 1, 3, 3, 1, 1)                 # row-paired (256-row) tiles
+        _case(64, 64, 32, 32, 64, 1, 3, 3, 1, 1)                 # many pairs per cluster (persistent loop)
+    finally:
+        L.cxn_conv_tune(7, 0)
