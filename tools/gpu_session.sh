@@ -1,0 +1,44 @@
+#!/bin/bash
+# One GPU-box session in the order that yields evidence even if the call is cut short:
+#   tests -> bench line -> launch list -> one full ncu capture of the top kernel.
+# Usage (from the repository root, through the remote runner):
+#   gpurun --timeout 1500 -- 'bash tools/gpu_session.sh'            # 1 GPU
+#   gpurun --gpus 2 --timeout 1500 -- 'bash tools/gpu_session.sh 2'  # also the 2-GPU tests and bench
+# Everything lands in gpurun_out/ (scratch); copy what should be judged into profiles/.
+# Opt-in experiments that have not yet run on hardware (each under its own timeout, failures do not stop the rest):
+#   CXN_TEST_CLUSTER=1      CTA-pair cluster convolution (tests/test_gpu_conv.py)
+#   CXN_TEST_COLLECTIVE=1   torch.distributed exchange on GPUs (tests/test_gpu_multi.py, needs 2 GPUs)
+set -u
+N=${1:-1}
+OUT=gpurun_out
+mkdir -p $OUT
+python build.py > $OUT/build.log 2>&1 || { tail -20 $OUT/build.log; exit 1; }
+
+echo "== pytest -m gpu"
+timeout 1200 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1
+echo "pytest exit $?"; tail -3 $OUT/pytest_gpu.log
+
+echo "== opt-in experiments"
+CXN_TEST_CLUSTER=1 timeout 300 python -m pytest tests/test_gpu_conv.py -q -k cluster > $OUT/pytest_cluster.log 2>&1
+echo "cluster conv exit $?"; tail -3 $OUT/pytest_cluster.log
+if [ "$N" -ge 2 ]; then
+  CXN_TEST_COLLECTIVE=1 timeout 300 python -m pytest tests/test_gpu_multi.py -q -k collective > $OUT/pytest_collective.log 2>&1
+  echo "collective exchange exit $?"; tail -3 $OUT/pytest_collective.log
+fi
+
+echo "== bench"
+timeout 600 python bench.py --gpus 1 --steps 20 --warmup 5 > $OUT/bench_1.json 2> $OUT/bench_1.err && cat $OUT/bench_1.json
+if [ "$N" -ge 2 ]; then
+  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29555 \
+      bench.py --gpus $N --steps 30 --warmup 5 > $OUT/bench_$N.json 2> $OUT/bench_$N.err && cat $OUT/bench_$N.json
+fi
+
+echo "== launch list (eager steps, so that every kernel is visible)"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv \
+    python bench.py --steps 2 --warmup 3 --extra "cuda_graph = 0" > $OUT/ncu_launches.log 2>&1
+python tools/launch_profile.py $OUT/launches.csv > $OUT/step_launches.txt 2>&1 && head -30 $OUT/step_launches.txt
+
+echo "== full capture of the convolution kernels of one step"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:conv_ -c 14 -o $OUT/conv_full \
+    python bench.py --steps 1 --warmup 3 --extra "cuda_graph = 0" > $OUT/ncu_full.log 2>&1
+ls -la $OUT | tail -12
