@@ -72,8 +72,15 @@ int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int 
 /* experiment / tuning knobs of the implicit-GEMM convolution (0, or -1 for switches, = automatic):
  * key 0 row halves per forward tile (1|2), 1 ring stages, 2 unused,
  * 3 unused, 4 forward tile-width class (128|256), 5 timing-experiment bits,
- * 6 im2col-mode TMA for the patch operand (0|1).  No reference counterpart. */
+ * 6 im2col-mode TMA for the patch operand (0|1), 7 = 2: forward layers on the im2col-TMA route run as clusters of
+ * two CTAs that multicast the filter tile to each other (also CXN_CONV_CLUSTER=2).  No reference counterpart. */
 int cxn_conv_tune(int key, int value);
+/* hardware probe, not on any training path (csrc/kernels/probe_sm100.cu): one tcgen05.mma whose 128B-swizzled
+ * operand starts `shift_rows` rows (0..32) into a shared-memory patch; out = device float [128][16];
+ * base_offset_mode 0 | 1 = descriptor base-offset field left 0 | set from the start address.
+ * cxn_probe_expected(m, n, shift_rows) is the value out[m][n] should hold.  No reference counterpart. */
+int cxn_probe_shifted_desc(float* out, int shift_rows, int base_offset_mode, cudaStream_t stream);
+float cxn_probe_expected(int m, int n, int shift_rows);
 /* per-role cycle counters of the forward implicit-GEMM kernel: buf = device int64 [148][16], NULL = off */
 int cxn_conv_set_prof(void* buf);
 /* explicit NHWC patch gather / scatter (fallback path).  Reference: unpack_patch2col /
