@@ -87,6 +87,18 @@ def pack(list_path: str, root: str, out_path: str, silent: bool = True) -> int:
     return int(L.cxnio_pack(list_path.encode(), root.encode(), out_path.encode(), 1 if silent else 0))
 
 
+def default_threads() -> int:
+    """worker threads of a native batch call: this process's share of the cores (one process per GPU, so
+    cores / ranks on this node), between 1 and 32"""
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        pass
+    ranks = max(int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1), 1)
+    return max(1, min(32, cores // ranks))
+
+
 # ---------------------------------------------------------------------------------------------- JPEG
 def jpeg_info(buf: bytes):
     """(width, height, components) of a JPEG the native decoder can handle, else None."""
@@ -130,7 +142,7 @@ def jpeg_decode_many(bufs: List[bytes], nthreads: int = 0) -> list:
     cw = (ctypes.c_int * n)(*[infos[i][0] for i in idx])
     ch = (ctypes.c_int * n)(*[infos[i][1] for i in idx])
     st = (ctypes.c_int * n)()
-    lib().cxnio_jpeg_decode_many(n, cb, cs, co, cw, ch, st, nthreads or min(8, os.cpu_count() or 1))
+    lib().cxnio_jpeg_decode_many(n, cb, cs, co, cw, ch, st, nthreads or default_threads())
     for j, i in enumerate(idx):
         outs[i] = arrs[j] if st[j] == 0 else None
     return outs
@@ -176,7 +188,7 @@ def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, 
         groups.setdefault(mode, []).append(i)
     assert dst.is_contiguous() and tuple(dst.shape[1:]) == (c, H, W) and dst.shape[0] >= n
     inst_bytes = c * H * W * (2 if dst_bf16 else 4)
-    nthreads = nthreads or min(8, os.cpu_count() or 1)
+    nthreads = nthreads or default_threads()
     for mode, idx in groups.items():
         # contiguous runs of instances that share a mode go down in one call
         run_start = 0

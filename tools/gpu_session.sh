@@ -21,6 +21,8 @@ echo "pytest exit $?"; tail -3 $OUT/pytest_gpu.log
 echo "== opt-in experiments"
 CXN_TEST_CLUSTER=1 timeout 300 python -m pytest tests/test_gpu_conv.py -q -k cluster > $OUT/pytest_cluster.log 2>&1
 echo "cluster conv exit $?"; tail -3 $OUT/pytest_cluster.log
+timeout 120 python bench/desc_probe.py > $OUT/desc_probe.txt 2>&1
+echo "descriptor probe exit $?"; tail -18 $OUT/desc_probe.txt
 if [ "$N" -ge 2 ]; then
   CXN_TEST_COLLECTIVE=1 timeout 300 python -m pytest tests/test_gpu_multi.py -q -k collective > $OUT/pytest_collective.log 2>&1
   echo "collective exchange exit $?"; tail -3 $OUT/pytest_collective.log
