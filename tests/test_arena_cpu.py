@@ -1,0 +1,82 @@
+"""Host side of the parameter arenas (cxxnet_b200/parallel/arena.py) without a GPU: segment layout on update-chunk
+boundaries, the chunk -> segment map the kernels index, and the per-step hyper-parameter table (schedules, per-tag
+values, adam's bias-corrected rate, the no-zero flag) that is staged for the multi-tensor update / exchange kernels."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from cxxnet_b200 import ops
+from cxxnet_b200.updaters import UpdaterParam
+
+pytestmark = pytest.mark.skipif(not ops.available(), reason="kernel library not built")
+
+
+def _param(tag, **kv):
+    p = UpdaterParam(tag)
+    for k, v in kv.items():
+        p.set_param(k.replace("__", ":"), str(v))
+    return p
+
+
+def _arena(kind="sgd"):
+    from cxxnet_b200.parallel.arena import ParamArena
+    a = ParamArena(torch.device("cpu"), kind)
+    s0 = a.add(None, 0, "wmat", 96, 363, 368, _param("wmat", lr=0.01, wd=0.0005, lr__schedule="expdecay",
+                                                       lr__gamma=0.1, lr__step=100))
+    s1 = a.add(None, 0, "bias", 1, 96, 0, _param("bias", lr=0.02, wd=0.0))
+    s2 = a.add(None, 3, "wmat", 10, 4096, 4096, _param("wmat", lr=0.01, momentum=0.5, clip_gradient=2.0))
+    s1.nozero = True
+    a.upload_hyper = lambda slot=0: None          # the device half (pinned table -> device) needs a GPU
+    a.finalize()
+    return a, (s0, s1, s2)
+
+
+def test_segments_sit_on_update_chunks_and_map_back():
+    from cxxnet_b200.parallel.arena import SEG_DTYPE
+    a, (s0, s1, s2) = _arena()
+    ch = a.chunk
+    assert ch > 0 and all(s.start % ch == 0 for s in (s0, s1, s2))
+    assert s0.start == 0 and s1.start == ops.round_up(96 * 363, ch) and s2.start == s1.start + ops.round_up(96, ch)
+    assert a.total == s2.start + ops.round_up(10 * 4096, ch) and a.nchunks == a.total // ch
+    cs = a.chunk_seg.numpy()
+    assert cs.shape[0] == a.nchunks
+    for i, s in enumerate((s0, s1, s2)):
+        lo, hi = s.start // ch, (s.start + ops.round_up(s.n, ch)) // ch
+        assert (cs[lo:hi] == i).all()
+    assert a.chunk_range(0, 2) == (0, s2.start // ch) and a.chunk_range(2, 3) == (s2.start // ch, a.nchunks)
+    # shadow (bf16, GEMM-ready) rows are padded to their leading dimension; vectors have none
+    assert s0.shadow_off == 0 and s1.shadow_off == -1 and s2.shadow_off == ops.round_up(96 * 368, 128)
+    assert a.w.numel() >= a.total and a.shadow.numel() >= s2.shadow_off + 10 * 4096
+    assert a.w_view(s1).numel() == 96 and a.shadow_view(s1) is None
+    assert SEG_DTYPE.itemsize == ops.lib().cxn_segment_bytes()
+
+
+def test_hyper_table_follows_schedules_and_tags():
+    from cxxnet_b200.parallel.arena import SEG_DTYPE
+    a, (s0, s1, s2) = _arena()
+    assert a.prepare_hyper(0, 0) is True
+    t = np.frombuffer(a.seg_host[0].numpy().tobytes(), dtype=SEG_DTYPE)
+    assert t[0]["start"] == 0 and t[0]["n"] == 96 * 363 and t[0]["cols"] == 363 and t[0]["shadow_ld"] == 368
+    assert np.isclose(t[0]["lr"], 0.01) and np.isclose(t[0]["wd"], 0.0005) and np.isclose(t[0]["momentum"], 0.9)
+    assert np.isclose(t[1]["lr"], 0.02) and t[1]["wd"] == 0.0 and t[1]["flags"] == 1 and t[0]["flags"] == 0
+    assert np.isclose(t[2]["momentum"], 0.5) and np.isclose(t[2]["clip"], 2.0) and t[2]["shadow_off"] == s2.shadow_off
+    assert a.prepare_hyper(0, 0) is False                     # unchanged table: the pinned buffer is left alone
+    assert a.prepare_hyper(250, 1) is True                    # expdecay: 0.01 * 0.1 ** (250 / 100)
+    t = np.frombuffer(a.seg_host[1].numpy().tobytes(), dtype=SEG_DTYPE)
+    assert np.isclose(t[0]["lr"], 0.01 * 0.1 ** 2.5, rtol=1e-5) and np.isclose(t[1]["lr"], 0.02)
+    a.prepare_hyper(10 ** 9, 0)                               # clamped at lr:minimum_lr
+    t = np.frombuffer(a.seg_host[0].numpy().tobytes(), dtype=SEG_DTYPE)
+    assert np.isclose(t[0]["lr"], 1e-5)
+
+
+def test_adam_table_carries_the_bias_corrected_rate():
+    from cxxnet_b200.parallel.arena import SEG_DTYPE
+    a, _ = _arena("adam")
+    assert a.m2 is not None and a.kind == ops.UPD_ADAM
+    a.prepare_hyper(4, 0)
+    t = np.frombuffer(a.seg_host[0].numpy().tobytes(), dtype=SEG_DTYPE)
+    b1, b2 = 0.1, 0.001
+    want = 0.02 * np.sqrt(1 - (1 - b2) ** 5) / (1 - (1 - b1) ** 5)
+    assert np.isclose(t[1]["adam_lr_t"], want, rtol=1e-5) and np.isclose(t[1]["beta1"], b1) and np.isclose(t[1]["beta2"], b2)
