@@ -15,6 +15,7 @@ that
 """
 from __future__ import annotations
 
+import math
 from typing import Callable, Dict, List, Optional
 
 import numpy as np
@@ -52,6 +53,7 @@ class ParamArena:
         self.seg_dev = None
         self.chunk_seg = None
         self.nchunks = 0
+        self._hyper_arr = None
 
     # ------------------------------------------------------------------ layout
     def add(self, layer, layer_index: int, tag: str, rows: int, cols: int, shadow_ld: int, param: UpdaterParam,
@@ -120,19 +122,27 @@ class ParamArena:
         device has consumed its previous contents (the H2D copy is asynchronous, and a captured
         graph re-reads the same pinned address on every replay).  Two slots used alternately let
         the host run one step ahead of the device.  Returns whether the buffer was rewritten."""
-        arr = np.zeros(max(len(self.segments), 1), dtype=SEG_DTYPE)
-        for i, s in enumerate(self.segments):
-            p = s.param
-            p.schedule_epoch(epoch)
-            arr[i]["start"], arr[i]["n"], arr[i]["shadow_off"] = s.start, s.n, s.shadow_off
-            arr[i]["cols"], arr[i]["shadow_ld"] = max(s.cols, 1), s.shadow_ld
-            arr[i]["lr"], arr[i]["wd"], arr[i]["momentum"], arr[i]["clip"] = p.learning_rate, p.wd, p.momentum, p.clip_gradient
-            arr[i]["flags"] = 1 if s.nozero else 0    # the producing kernel overwrites this gradient: no need to zero it
+        arr = self._hyper_arr
+        if arr is None:
+            # the fields that never change are filled once; a step only rewrites the scheduled columns
+            arr = self._hyper_arr = np.zeros(max(len(self.segments), 1), dtype=SEG_DTYPE)
+            for i, s in enumerate(self.segments):
+                arr[i]["start"], arr[i]["n"], arr[i]["shadow_off"] = s.start, s.n, s.shadow_off
+                arr[i]["cols"], arr[i]["shadow_ld"] = max(s.cols, 1), s.shadow_ld
+                arr[i]["beta1"], arr[i]["beta2"] = (s.beta1, s.beta2) if self.kind == ops.UPD_ADAM else (0.0, 0.0)
+        segs = self.segments
+        if segs:
+            for s in segs:
+                s.param.schedule_epoch(epoch)
+            n = len(segs)
+            arr["lr"][:n] = [s.param.learning_rate for s in segs]
+            arr["wd"][:n] = [s.param.wd for s in segs]
+            arr["momentum"][:n] = [s.param.momentum for s in segs]
+            arr["clip"][:n] = [s.param.clip_gradient for s in segs]
+            arr["flags"][:n] = [1 if s.nozero else 0 for s in segs]   # the producing kernel overwrites this gradient
             if self.kind == ops.UPD_ADAM:
-                fix1 = 1.0 - (1.0 - s.beta1) ** (epoch + 1)
-                fix2 = 1.0 - (1.0 - s.beta2) ** (epoch + 1)
-                arr[i]["adam_lr_t"] = p.base_lr * np.sqrt(fix2) / fix1
-                arr[i]["beta1"], arr[i]["beta2"] = s.beta1, s.beta2
+                arr["adam_lr_t"][:n] = [s.param.base_lr * math.sqrt(1.0 - (1.0 - s.beta2) ** (epoch + 1))
+                                        / (1.0 - (1.0 - s.beta1) ** (epoch + 1)) for s in segs]
         raw = arr.tobytes()
         if raw == self._hyper_raw[slot]:
             return False
