@@ -228,10 +228,16 @@ class LearnTask:
                 defcfg.append((name, val))
             else:
                 itcfg.append((name, val))
+        world = int(os.environ.get("WORLD_SIZE", "1")) if "RANK" in os.environ else 1
         for it in [self.itr_train, self.itr_pred] + self.itr_evals:
             if it is not None:
                 for k, v in defcfg:
                     it.set_param(k, v)
+                if world > 1:
+                    # every rank walks the whole data set but only uses its rows of each batch: let the batch stage
+                    # skip the decoding of the others (io/iterators.py BatchAdaptIterator)
+                    it.set_param("slice_world", str(world))
+                    it.set_param("slice_rank", str(self.rank))
                 it.init()
 
     def close(self) -> None:

@@ -770,6 +770,7 @@ class BatchAdaptIterator(IIterator):
         self.decode_threads = 0       # 0 = min(8, cores)
         self._native = False
         self._pending = []            # native path: records of the batch being assembled
+        self.slice_world, self.slice_rank = 1, 0
 
     def set_param(self, name, val):
         self.base.set_param(name, val)
@@ -785,6 +786,11 @@ class BatchAdaptIterator(IIterator):
         if name == "test_skipread": self.test_skipread = int(val)
         if name == "native_pipeline": self.native_pipeline = int(val)
         if name == "decode_threads": self.decode_threads = int(val)
+        # one process per GPU: rank r of w only uses rows [r*ceil(B/w), (r+1)*ceil(B/w)) of every batch (trainer.py
+        # _slice), so the native path decodes just those; the other rows of `data` are left as they are.  Set by the
+        # task driver; labels, indices and the random decisions are still produced for every row.
+        if name == "slice_world": self.slice_world = max(int(val), 1)
+        if name == "slice_rank": self.slice_rank = int(val)
 
     def _plan_native(self) -> bool:
         """The fused native batch path (csrc/runtime/batch_pipeline.cpp) applies when the chain below is
@@ -853,7 +859,9 @@ class BatchAdaptIterator(IIterator):
             return
         from . import native
         aug = self.base
-        items, fallback = [], {}
+        step = (self.batch_size + self.slice_world - 1) // self.slice_world
+        lo, hi = min(self.slice_rank * step, self.batch_size), min((self.slice_rank + 1) * step, self.batch_size)
+        items, tops = [], []
         for top, blob in self._pending:
             info = native.jpeg_info(blob)
             pixels = None
@@ -862,7 +870,13 @@ class BatchAdaptIterator(IIterator):
                 h, w = pixels.shape[1], pixels.shape[2]
             else:
                 w, h = info[0], info[1]
-            items.append((blob, pixels, h, w) + tuple(aug.draw_params(h, w)))
+            params = tuple(aug.draw_params(h, w))          # drawn for every row: the stream of random decisions
+            if lo <= top < hi:                             # does not depend on how the batch is split over ranks
+                items.append((blob, pixels, h, w) + params)
+                tops.append(top)
+        self._pending = []
+        if not items:
+            return
         mode = aug.mean_mode()
         mean = None
         if mode == 1:
@@ -871,8 +885,8 @@ class BatchAdaptIterator(IIterator):
             mean = aug.meanimg
         to_half = self._half is not None
         dst = self._half.data if to_half else self.out.data
-        first = self._pending[0][0]
-        assert [t for t, _ in self._pending] == list(range(first, first + len(items)))
+        first = tops[0]
+        assert tops == list(range(first, first + len(items)))
         status = native.decode_augment_batch(items, self.shape, mode, mean, aug.scale, dst[first:first + len(items)],
                                              to_half, self.decode_threads)
         for k, st in enumerate(status):
@@ -881,7 +895,6 @@ class BatchAdaptIterator(IIterator):
                 data = pixels if pixels is not None else _decode_image(blob, native_first=False)
                 res = torch.from_numpy(aug.apply_params(data, items[k][4:]))
                 dst[first + k].copy_(res)
-        self._pending = []
 
     def next(self):
         self.out.num_batch_padd = 0

@@ -235,3 +235,37 @@ def test_decoder_survives_mutated_inputs_under_sanitizers(tmp_path):
     assert r.returncode == 0 and "decoded" in r.stdout, r.stdout[-3000:]
     decoded = int(r.stdout.split("decoded")[1].split()[0])
     assert decoded > 100          # the mutations are mild enough that a good share still decodes
+
+
+def test_rank_slice_decodes_only_the_rows_a_rank_uses(tmp_path):
+    """slice_world / slice_rank (set by the task driver in multi-process runs): the rows of a rank's slice are those
+    of the unsliced batch, the random decisions do not depend on the split, the other rows are not decoded"""
+    import torch
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.io.data import create_iterator
+    _jpeg_bin(tmp_path, n=12)
+
+    def batches(extra):
+        it = create_iterator(parse_config_string(
+            'iter = imgbin\n image_list = "%s"\n image_bin = "%s"\n batch_size = 6\n input_shape = 3,24,26\n'
+            ' rand_crop = 1\n rand_mirror = 1\n mean_value = 100,110,120\n seed_data = 9\n silent = 1\n%siter = end\n'
+            % (tmp_path / "j.lst", tmp_path / "j.bin", extra)))
+        it.init()
+        it.before_first()
+        out = []
+        while it.next():
+            b = it.value()
+            out.append((b.data.clone(), b.label.clone(), b.inst_index.copy()))
+            b.data.fill_(-777.0)                  # marks the rows the next batch leaves alone
+        it.close()
+        return out
+
+    full = batches("")
+    assert len(full) == 2
+    for rank in range(3):                         # 3 ranks: rows [0,2) [2,4) [4,6)
+        part = batches(" slice_world = 3\n slice_rank = %d\n" % rank)
+        for (d0, l0, i0), (d1, l1, i1) in zip(full, part):
+            lo, hi = 2 * rank, 2 * rank + 2
+            assert torch.equal(d0[lo:hi], d1[lo:hi]) and torch.equal(l0, l1) and list(i0) == list(i1)
+        other = [r for r in range(6) if not 2 * rank <= r < 2 * rank + 2]
+        assert bool((part[1][0][other] == -777.0).all())       # second batch: untouched rows still hold the marker
