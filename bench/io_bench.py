@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Host data-pipeline throughput: imgbin pages of 256x256 JPEGs -> augmented 3x227x227 batches.
 
-  python bench/io_bench.py [--n 512] [--batch 128] [--threads 0]
+  python bench/io_bench.py [--n 2048] [--batch 256] [--threads 0]
 
 Compares the Python iterator stages (`native_pipeline = 0`) with the fused native batch path
 (csrc/runtime/batch_pipeline.cpp: JPEG decode + crop / mean / jitter / mirror / scale + batch assembly on worker
@@ -20,8 +20,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=512)
-    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--n", type=int, default=2048)
+    ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--threads", type=int, default=0)
     args = ap.parse_args()
     from PIL import Image
