@@ -792,7 +792,7 @@ class BatchAdaptIterator(IIterator):
         if name == "slice_world": self.slice_world = max(int(val), 1)
         if name == "slice_rank": self.slice_rank = int(val)
 
-    def _plan_native(self) -> bool:
+    def _native_chain(self) -> bool:
         """The fused native batch path (csrc/runtime/batch_pipeline.cpp) applies when the chain below is
         imgbin(x) -> augment without the affine group, on 3-channel images, and the library is built."""
         from . import native
@@ -801,18 +801,18 @@ class BatchAdaptIterator(IIterator):
             return False
         if native.lib() is None or not hasattr(native.lib(), "cxnio_decode_augment_batch"):
             return False
-        if aug.aug.need_process() or len(self.shape) != 3 or self.shape[0] != 3 or self.shape[1] == 1:
-            return False
-        if aug.mean_mode() == 2 and (aug.meanimg is None or aug.meanimg.shape[0] != 3):
-            return False
-        return True
+        return not (aug.aug.need_process() or len(self.shape) != 3 or self.shape[0] != 3 or self.shape[1] == 1)
 
     def init(self):
-        self.base.init()
-        self._native = self._plan_native()
-        if self._native:
+        chain = self._native_chain()
+        if chain:
+            # the source hands over encoded records from its first pass on (whoever reads it through next()
+            # - the mean-image pass - gets them decoded on the spot), so no restart is needed later and a
+            # shuffled source visits the data in the same order as without the native path
             self.base.base.raw_mode = True
-            self.base.base.before_first()      # restart the producer thread so that it hands over encoded records
+        self.base.init()
+        aug = self.base
+        self._native = chain and not (aug.mean_mode() == 2 and (aug.meanimg is None or aug.meanimg.shape[0] != 3))
         self.out.alloc_dense((self.batch_size,) + tuple(self.shape), self.batch_size, self.label_width, pin=True)
         self._data_np = self.out.data.numpy()
         self._label_np = self.out.label.numpy()

@@ -269,3 +269,34 @@ def test_rank_slice_decodes_only_the_rows_a_rank_uses(tmp_path):
             assert torch.equal(d0[lo:hi], d1[lo:hi]) and torch.equal(l0, l1) and list(i0) == list(i1)
         other = [r for r in range(6) if not 2 * rank <= r < 2 * rank + 2]
         assert bool((part[1][0][other] == -777.0).all())       # second batch: untouched rows still hold the marker
+
+
+def test_native_path_keeps_the_order_of_a_shuffled_source_behind_a_thread_buffer(tmp_path):
+    """imgbinx with shuffle = 1 wrapped in threadbuffer: the native batch path visits the data in the same
+    (shuffled) order and produces the same batches as the Python stages, over two passes"""
+    import torch
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.io.data import create_iterator
+    _jpeg_bin(tmp_path, n=13)
+
+    def run(native_pipeline):
+        it = create_iterator(parse_config_string(
+            'iter = imgbinx\n image_list = "%s"\n image_bin = "%s"\n shuffle = 1\n batch_size = 4\n'
+            ' input_shape = 3,24,26\n rand_crop = 1\n rand_mirror = 1\n mean_value = 1,2,3\n round_batch = 1\n'
+            ' silent = 1\n native_pipeline = %d\niter = threadbuffer\n silent = 1\niter = end\n'
+            % (tmp_path / "j.lst", tmp_path / "j.bin", native_pipeline)))
+        it.init()
+        out = []
+        for _ in range(2):
+            it.before_first()
+            while it.next():
+                b = it.value()
+                out.append((b.data.clone(), [int(i) for i in b.inst_index], b.num_batch_padd))
+        it.close()
+        return out
+
+    a, b = run(0), run(1)
+    assert len(a) == len(b) > 4
+    assert [x[1] for x in a] != [sorted(x[1]) for x in a]        # the order really is shuffled
+    for (d0, i0, p0), (d1, i1, p1) in zip(a, b):
+        assert i0 == i1 and p0 == p1 and torch.equal(d0, d1)
