@@ -300,3 +300,84 @@ def test_native_path_keeps_the_order_of_a_shuffled_source_behind_a_thread_buffer
     assert [x[1] for x in a] != [sorted(x[1]) for x in a]        # the order really is shuffled
     for (d0, i0, p0), (d1, i1, p1) in zip(a, b):
         assert i0 == i1 and p0 == p1 and torch.equal(d0, d1)
+
+
+def test_command_line_trains_from_packed_jpegs(tmp_path):
+    """files -> bin/im2bin -> `iter = imgbin` (native reader, decoder and batch path) -> task driver on the CPU
+    backend: a two-class problem (bright / dark images) is learnt, and `task = pred` reads the same pages"""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    im2bin = os.path.join(root, "bin", "im2bin")
+    if not os.path.exists(im2bin):
+        pytest.skip("bin/im2bin not built")
+    rs = np.random.RandomState(0)
+    os.makedirs(tmp_path / "img")
+    lines = []
+    for i in range(60):
+        cls = i % 2
+        a = np.clip(rs.randn(20, 22, 3) * 20 + (70 if cls == 0 else 180), 0, 255).astype(np.uint8)
+        Image.fromarray(a).save(tmp_path / "img" / ("%03d.jpg" % i), quality=90)
+        lines.append("%d\t%d\timg/%03d.jpg\n" % (i, cls, i))
+    (tmp_path / "all.lst").write_text("".join(lines))
+    subprocess.run([im2bin, str(tmp_path / "all.lst"), str(tmp_path) + "/", str(tmp_path / "all.bin")], check=True,
+                   stdout=subprocess.PIPE, timeout=120)
+    conf = tmp_path / "net.conf"
+    conf.write_text('''
+data = train
+iter = imgbin
+  image_list = "%(d)s/all.lst"
+  image_bin = "%(d)s/all.bin"
+  rand_crop = 1
+  rand_mirror = 1
+  mean_value = 128,128,128
+  divideby = 64
+iter = threadbuffer
+iter = end
+eval = val
+iter = imgbin
+  image_list = "%(d)s/all.lst"
+  image_bin = "%(d)s/all.bin"
+  mean_value = 128,128,128
+  divideby = 64
+iter = end
+pred = %(d)s/pred.txt
+iter = imgbin
+  image_list = "%(d)s/all.lst"
+  image_bin = "%(d)s/all.bin"
+  mean_value = 128,128,128
+  divideby = 64
+iter = end
+netconfig = start
+layer[+1] = flatten
+layer[+1] = fullc:fc
+  nhidden = 2
+  init_sigma = 0.01
+layer[+0] = softmax
+netconfig = end
+input_shape = 3,16,16
+batch_size = 20
+round_batch = 1
+dev = cpu
+eta = 0.05
+momentum = 0.9
+metric = error
+num_round = 3
+max_round = 3
+model_dir = %(d)s/models
+silent = 1
+''' % {"d": tmp_path})
+    env = dict(os.environ)
+    env["PYTHONPATH"] = root + os.pathsep + env.get("PYTHONPATH", "")
+    r = subprocess.run([sys.executable, "-m", "cxxnet_b200", str(conf)], cwd=tmp_path, env=env, stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    last = [ln for ln in r.stderr.splitlines() if ln.startswith("[3]")][0]
+    assert float(last.split("val-error:")[1].split()[0]) == 0.0, last
+    r = subprocess.run([sys.executable, "-m", "cxxnet_b200", str(conf), "task=pred",
+                        "model_in=%s/models/0003.model" % tmp_path], cwd=tmp_path, env=env, stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    preds = [int(float(x)) for x in (tmp_path / "pred.txt").read_text().split()]
+    assert preds == [i % 2 for i in range(60)]
