@@ -981,6 +981,8 @@ static int g_tune_dbg = 0;         // timing experiments (Params::dbg)
 static int g_tune_atma = -1;       // 0 / 1: fetch the patches with im2col-mode TMA
 static int g_tune_cluster = -1;    // 2: forward layers on the im2col-TMA route run as CTA pairs that share the
                                    // filter tile by multicast (conv_fprop_cluster_kernel); -1 = read CXN_CONV_CLUSTER
+static int g_tune_fill = -1;       // 1: forward layers with fewer tiles than SMs take narrower column tiles until
+                                   // the grid fills the machine (small per-GPU batches); -1 = read CXN_CONV_FILL
 static long long* g_prof = nullptr;
 
 typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -1148,6 +1150,18 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   if (g_tune_mh && gran == 8) { mh = g_tune_mh; if (mh == 1) bnmax = Ng > 128 ? 256 : 128; }
   if (g_tune_bnmax) bnmax = g_tune_bnmax;
   p.bn = pick_bn(Ng, bnmax);
+  if (g_tune_fill < 0) {
+    const char* e = getenv("CXN_CONV_FILL");
+    g_tune_fill = e ? atoi(e) : 0;
+  }
+  if (g_tune_fill == 1) {
+    // under one wave of tiles: halve the tile width (not below 64 columns) while that adds CTAs
+    while (p.bn >= 128 && ceil_div_ll(rows, mh * BM) * ceil_div(Ng, p.bn) * G < num_sms()) {
+      const int nb = pick_bn(Ng, p.bn / 2);
+      if (nb >= p.bn || nb < 64) break;
+      p.bn = nb;
+    }
+  }
   p.dbg = g_tune_dbg;
   p.prof = g_prof;
   const int stage_bytes = (mh * BM + bnmax) * BK * 2;
@@ -1211,6 +1225,7 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
 // Tuning / experiment knobs; value 0 (or -1 for the switches) restores the automatic choice.
 //   0: row halves per forward tile   1: ring stages   2: gather through L1   3: tap-inner order   4: tile-width class
 //   5: timing experiments   6: im2col TMA on / off   7: 2 = CTA-pair clusters with a multicast filter tile (forward)
+//   8: 1 = narrower column tiles when the forward grid would not fill the machine
 // Role profiling of the forward kernel: buf = device array of [148][16] int64 (null switches it off).
 // slots: 0 TMA wait-empty, 1 TMA total | 2 MMA wait-full, 3 MMA wait-tmem-empty, 4 MMA total |
 // 5 gather wait-empty, 6 gather tile setup, 7 gather total | 8 epilogue wait-tmem-full, 9 epilogue body, 10 total
@@ -1229,6 +1244,7 @@ CXN_API int cxn_conv_tune(int key, int value) {
     case 5: g_tune_dbg = value; break;
     case 6: g_tune_atma = value; break;
     case 7: g_tune_cluster = value; break;
+    case 8: g_tune_fill = value; break;
     default: return -1;
   }
   return 0;

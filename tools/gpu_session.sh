@@ -35,6 +35,10 @@ if [ "$N" -ge 2 ]; then
       bench.py --gpus $N --steps 30 --warmup 5 > $OUT/bench_$N.json 2> $OUT/bench_$N.err && cat $OUT/bench_$N.json
 fi
 
+echo "== small-batch A/B (what one GPU computes in the 8-GPU run)"
+timeout 300 python bench.py --batch 32 --steps 30 --warmup 5 > $OUT/bench_b32.json 2>/dev/null && python -c "import json;d=json.load(open('$OUT/bench_b32.json'));print('batch 32:', round(d['ms_per_step'],4), 'ms')"
+CXN_CONV_FILL=1 timeout 300 python bench.py --batch 32 --steps 30 --warmup 5 > $OUT/bench_b32_fill.json 2>/dev/null && python -c "import json;d=json.load(open('$OUT/bench_b32_fill.json'));print('batch 32, CXN_CONV_FILL=1:', round(d['ms_per_step'],4), 'ms')"
+
 echo "== launch list (eager steps, so that every kernel is visible)"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv \
     python bench.py --steps 2 --warmup 3 --extra "cuda_graph = 0" > $OUT/ncu_launches.log 2>&1
