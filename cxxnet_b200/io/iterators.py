@@ -232,6 +232,7 @@ class ImageIterator(IIterator):
         self.shuffle = 0
         self.label_width = 1
         self.path_imglst = self.path_imgdir = ""
+        self.raw_mode = False    # next_raw() hands over the file's bytes; the batch stage decodes (native threads)
         self.out = DataInst()
 
     def set_param(self, name, val):
@@ -261,6 +262,15 @@ class ImageIterator(IIterator):
         self.data_index = 0
         if self.shuffle:
             self.rs.shuffle(self.order)
+
+    def next_raw(self):
+        """(index, label, encoded bytes) of the next image, or None at the end (see ImageBinIterator.next_raw)"""
+        if self.data_index >= len(self.order):
+            return None
+        i = self.order[self.data_index]
+        self.data_index += 1
+        with open(self.path_imgdir + self.filenames[i], "rb") as f:
+            return self.index_list[i], np.asarray(self.labels[i], dtype=np.float32), f.read()
 
     def next(self):
         if self.data_index >= len(self.order):
@@ -797,7 +807,8 @@ class BatchAdaptIterator(IIterator):
         imgbin(x) -> augment without the affine group, on 3-channel images, and the library is built."""
         from . import native
         aug = self.base
-        if not (self.native_pipeline and isinstance(aug, AugmentIterator) and isinstance(aug.base, ImageBinIterator)):
+        if not (self.native_pipeline and isinstance(aug, AugmentIterator)
+                and isinstance(aug.base, (ImageBinIterator, ImageIterator))):
             return False
         if native.lib() is None or not hasattr(native.lib(), "cxnio_decode_augment_batch"):
             return False

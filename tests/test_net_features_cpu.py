@@ -166,6 +166,21 @@ def test_img_iterator_reads_list_and_files(tmp_path):
     ref = np.asarray(Image.open(tmp_path / "im2.jpg").convert("RGB")).transpose(2, 0, 1).astype(np.float32)
     assert np.abs(seen[2][2] - ref).max() <= 3                                             # JPEG: as libjpeg
     assert padds == [0, 0, 1]                                  # 5 images, batches of 2, wrapped around
+    assert it._native                                          # files are decoded by the native batch path ...
+
+    def crops(native_pipeline):
+        jt = create_iterator(parse_config_string(
+            'iter = img\n image_list = "%s"\n image_root = "%s/"\n label_width = 2\n batch_size = 2\n'
+            ' input_shape = 3,7,8\n rand_crop = 1\n rand_mirror = 1\n mean_value = 9,8,7\n round_batch = 1\n'
+            ' native_pipeline = %d\n silent = 1\niter = end\n' % (tmp_path / "l.lst", tmp_path, native_pipeline)))
+        jt.init()
+        jt.before_first()
+        got = []
+        while jt.next():
+            got.append(jt.value().data.clone())
+        return got
+    a, b = crops(0), crops(1)                                  # ... with the results of the Python stages
+    assert len(a) == len(b) == 3 and all(torch.equal(x, y) for x, y in zip(a, b))
 
 
 def test_affine_augmenter_rotation_and_crop():
