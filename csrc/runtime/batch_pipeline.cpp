@@ -12,6 +12,7 @@
 //             3: mean image of the crop size, subtracted after the crop / mirror
 // The arithmetic is single precision in this order, the same as the NumPy path it replaces.
 #include <atomic>
+#include <cmath>
 #include <cstdint>
 #include <cstring>
 #include <thread>
@@ -30,6 +31,14 @@ struct CxnioAugItem {
   int32_t y0, x0;         // crop origin
   int32_t flip;           // mirror horizontally
   float contrast, illum;
+  // optional affine stage (reference src/io/image_augmenter-inl.hpp: rotation / shear / scale / aspect): the crop is
+  // taken from a virtual warp_h x warp_w image V(y, x) = bilinear(decoded image at (ai[0..2] . (x, y, 1),
+  // ai[3..5] . (x, y, 1))), positions outside the decoded image reading `fill`; (y0, x0) then refer to the
+  // input_shape window of V that starts at (warp_y, warp_x)
+  int32_t affine;
+  int32_t warp_h, warp_w, warp_y, warp_x;
+  float fill;
+  double ai[6];
 };
 
 static inline uint16_t F32ToBf16(float f) {
@@ -76,6 +85,49 @@ CXNIO_CLONES static int AugmentOne(const float* src, int C, int sh, int sw, cons
   return 0;
 }
 
+// the H x W window at (wy, wx) of the affine-warped image, channel by channel, into `out` (C x H x W)
+CXNIO_CLONES static void WarpWindow(const float* src, int C, int sh, int sw, const CxnioAugItem& it, int H, int W,
+                                    float* out) {
+  const double a00 = it.ai[0], a01 = it.ai[1], a02 = it.ai[2], a10 = it.ai[3], a11 = it.ai[4], a12 = it.ai[5];
+  const float fill = it.fill;
+  for (int y = 0; y < H; ++y) {
+    const int yy = it.warp_y + y;
+    for (int x = 0; x < W; ++x) {
+      const int xx = it.warp_x + x;
+      const double sx = a00 * xx + a01 * yy + a02, sy = a10 * xx + a11 * yy + a12;
+      const double fxd = std::floor(sx), fyd = std::floor(sy);
+      const long x0 = long(fxd), y0 = long(fyd);
+      const float fx = float(sx - fxd), fy = float(sy - fyd);
+      const bool okx0 = x0 >= 0 && x0 < sw, okx1 = x0 + 1 >= 0 && x0 + 1 < sw;
+      const bool oky0 = y0 >= 0 && y0 < sh, oky1 = y0 + 1 >= 0 && y0 + 1 < sh;
+      const float w00 = (1 - fx), w01 = fx;
+      for (int c = 0; c < C; ++c) {
+        const float* pl = src + size_t(c) * sh * sw;
+        const float t00 = (oky0 && okx0) ? pl[y0 * sw + x0] : fill;
+        const float t01 = (oky0 && okx1) ? pl[y0 * sw + x0 + 1] : fill;
+        const float t10 = (oky1 && okx0) ? pl[(y0 + 1) * sw + x0] : fill;
+        const float t11 = (oky1 && okx1) ? pl[(y0 + 1) * sw + x0 + 1] : fill;
+        // the NumPy statement's order: ((t00 (1-fx) (1-fy) + t01 fx (1-fy)) + t10 (1-fx) fy) + t11 fx fy
+        const float v = ((t00 * w00 * (1 - fy) + t01 * w01 * (1 - fy)) + t10 * w00 * fy) + t11 * w01 * fy;
+        out[(size_t(c) * H + y) * W + x] = v;
+      }
+    }
+  }
+}
+
+// crop / mean / jitter / mirror / scale of one decoded image, through the affine stage when the item asks for it
+static int ProcessOne(const float* src, int C, int sh, int sw, const CxnioAugItem& it, int H, int W, int mean_mode,
+                      const float* mean, int mean_h, int mean_w, float scale, void* dst, int dst_bf16,
+                      std::vector<float>& win) {
+  if (!it.affine)
+    return AugmentOne(src, C, sh, sw, it, H, W, mean_mode, mean, mean_h, mean_w, scale, dst, dst_bf16);
+  if (it.warp_y < 0 || it.warp_x < 0 || it.warp_y + H > it.warp_h || it.warp_x + W > it.warp_w || it.y0 || it.x0)
+    return -13;
+  win.resize(size_t(C) * H * W);
+  WarpWindow(src, C, sh, sw, it, H, W, win.data());
+  return AugmentOne(win.data(), C, H, W, it, H, W, mean_mode, mean, mean_h, mean_w, scale, dst, dst_bf16);
+}
+
 // status[i]: 0 ok, < 0 this instance was not written (undecodable here, size mismatch, crop outside the image)
 int cxnio_decode_augment_batch(const CxnioAugItem* items, int n, int C, int H, int W, int mean_mode, const float* mean,
                                int mean_h, int mean_w, float scale, void* dst, int dst_bf16, int* status,
@@ -86,15 +138,15 @@ int cxnio_decode_augment_batch(const CxnioAugItem* items, int n, int C, int H, i
   const size_t inst = size_t(C) * H * W * (dst_bf16 ? 2 : 4);
   std::atomic<int> next{0};
   auto work = [&]() {
-    std::vector<float> tmp;
+    std::vector<float> tmp, win;
     for (;;) {
       const int i = next.fetch_add(1);
       if (i >= n) return;
       const CxnioAugItem& it = items[i];
       void* slot = static_cast<char*>(dst) + inst * i;
       if (it.pixels) {
-        status[i] = AugmentOne(it.pixels, C, it.src_h, it.src_w, it, H, W, mean_mode, mean, mean_h, mean_w, scale,
-                               slot, dst_bf16);
+        status[i] = ProcessOne(it.pixels, C, it.src_h, it.src_w, it, H, W, mean_mode, mean, mean_h, mean_w, scale,
+                               slot, dst_bf16, win);
         continue;
       }
       int w = 0, h = 0, comps = 0;
@@ -104,7 +156,7 @@ int cxnio_decode_augment_batch(const CxnioAugItem* items, int n, int C, int H, i
         tmp.resize(size_t(3) * h * w);
         r = cxnio_jpeg_decode_planar_f32(it.buf, it.size, tmp.data(), w, h);
       }
-      if (r == 0) r = AugmentOne(tmp.data(), C, h, w, it, H, W, mean_mode, mean, mean_h, mean_w, scale, slot, dst_bf16);
+      if (r == 0) r = ProcessOne(tmp.data(), C, h, w, it, H, W, mean_mode, mean, mean_h, mean_w, scale, slot, dst_bf16, win);
       status[i] = r;
     }
   };

@@ -555,10 +555,11 @@ class ImageAugmenter:
             return True
         return self.min_crop_size > 0 and self.max_crop_size > 0
 
-    def process(self, data: np.ndarray, rnd: RandomSampler) -> np.ndarray:
-        if not self.need_process():
-            return data
-        c, rows, cols = data.shape
+    def draw(self, rows: int, cols: int, rnd: RandomSampler):
+        """the random decisions of one warp for a rows x cols image, in the reference's order: returns
+        (Ai, new_h, new_w, y, x, cropped) - the inverse affine map as a 3x3 float64 matrix, the size of the warped
+        image, and the origin of the input_shape crop taken from it (cropped is False when the warped image is
+        smaller than input_shape and is passed on whole)"""
         s = rnd.next_double() * self.max_shear_ratio * 2 - self.max_shear_ratio
         angle = rnd.next_uint32(self.max_rotate_angle * 2) - self.max_rotate_angle
         if self.rotate > 0:
@@ -576,14 +577,25 @@ class ImageAugmenter:
         M[0, 2] = (new_w - (M[0, 0] * cols + M[0, 1] * rows)) / 2
         M[1, 2] = (new_h - (M[1, 0] * cols + M[1, 1] * rows)) / 2
         # dst(x,y) = src(M^-1 [x,y,1])
-        A = np.vstack([M, [0, 0, 1]])
-        Ai = np.linalg.inv(A)
+        Ai = np.linalg.inv(np.vstack([M, [0, 0, 1]]))
+        y, x = new_h - self.shape[2], new_w - self.shape[1]
+        if y < 0 or x < 0:
+            return Ai, new_h, new_w, 0, 0, False
+        if self.rand_crop != 0:
+            y, x = rnd.next_uint32(y + 1), rnd.next_uint32(x + 1)
+        else:
+            y, x = y // 2, x // 2
+        return Ai, new_h, new_w, y, x, True
+
+    def warp(self, data: np.ndarray, params) -> np.ndarray:
+        """bilinear inverse-mapped resample of `data` (c, rows, cols) with the decisions of `draw`"""
+        Ai, new_h, new_w, y, x, cropped = params
+        c, rows, cols = data.shape
         ys, xs = np.mgrid[0:new_h, 0:new_w]
         sx = Ai[0, 0] * xs + Ai[0, 1] * ys + Ai[0, 2]
         sy = Ai[1, 0] * xs + Ai[1, 1] * ys + Ai[1, 2]
         x0, y0 = np.floor(sx).astype(int), np.floor(sy).astype(int)
         fx, fy = (sx - x0).astype(np.float32), (sy - y0).astype(np.float32)
-        out = np.zeros((c, new_h, new_w), dtype=np.float32)
 
         def tap(yy, xx):
             ok = (yy >= 0) & (yy < rows) & (xx >= 0) & (xx < cols)
@@ -591,14 +603,14 @@ class ImageAugmenter:
             return np.where(ok[None], v, float(self.fill_value))
         out = (tap(y0, x0) * (1 - fx) * (1 - fy) + tap(y0, x0 + 1) * fx * (1 - fy)
                + tap(y0 + 1, x0) * (1 - fx) * fy + tap(y0 + 1, x0 + 1) * fx * fy).astype(np.float32)
-        y, x = new_h - self.shape[2], new_w - self.shape[1]
-        if y < 0 or x < 0:
+        if not cropped:
             return out
-        if self.rand_crop != 0:
-            y, x = rnd.next_uint32(y + 1), rnd.next_uint32(x + 1)
-        else:
-            y, x = y // 2, x // 2
         return out[:, y:y + self.shape[2], x:x + self.shape[1]]
+
+    def process(self, data: np.ndarray, rnd: RandomSampler) -> np.ndarray:
+        if not self.need_process():
+            return data
+        return self.warp(data, self.draw(data.shape[1], data.shape[2], rnd))
 
 
 class AugmentIterator(IIterator):
@@ -804,7 +816,7 @@ class BatchAdaptIterator(IIterator):
 
     def _native_chain(self) -> bool:
         """The fused native batch path (csrc/runtime/batch_pipeline.cpp) applies when the chain below is
-        imgbin(x) -> augment without the affine group, on 3-channel images, and the library is built."""
+        img / imgbin(x) -> augment on 3-channel images, and the library is built."""
         from . import native
         aug = self.base
         if not (self.native_pipeline and isinstance(aug, AugmentIterator)
@@ -812,7 +824,7 @@ class BatchAdaptIterator(IIterator):
             return False
         if native.lib() is None or not hasattr(native.lib(), "cxnio_decode_augment_batch"):
             return False
-        return not (aug.aug.need_process() or len(self.shape) != 3 or self.shape[0] != 3 or self.shape[1] == 1)
+        return not (len(self.shape) != 3 or self.shape[0] != 3 or self.shape[1] == 1)
 
     def init(self):
         chain = self._native_chain()
@@ -881,9 +893,18 @@ class BatchAdaptIterator(IIterator):
                 h, w = pixels.shape[1], pixels.shape[2]
             else:
                 w, h = info[0], info[1]
-            params = tuple(aug.draw_params(h, w))          # drawn for every row: the stream of random decisions
-            if lo <= top < hi:                             # does not depend on how the batch is split over ranks
-                items.append((blob, pixels, h, w) + params)
+            # drawn for every row: the stream of random decisions does not depend on how the batch is split over ranks
+            affine = None
+            if aug.aug.need_process():
+                Ai, new_h, new_w, wy, wx, cropped = aug.aug.draw(h, w, aug.rnd)
+                if not cropped:
+                    raise ValueError("Data size must be bigger than the input size to net.")
+                affine = (Ai, new_h, new_w, wy, wx, float(aug.aug.fill_value))
+                params = tuple(aug.draw_params(self.shape[1], self.shape[2]))
+            else:
+                params = tuple(aug.draw_params(h, w))
+            if lo <= top < hi:
+                items.append((blob, pixels, h, w) + params + (affine,))
                 tops.append(top)
         self._pending = []
         if not items:
@@ -904,7 +925,10 @@ class BatchAdaptIterator(IIterator):
             if st != 0:                                    # e.g. a damaged file: the library decoders get a try
                 blob, pixels, h, w = items[k][:4]
                 data = pixels if pixels is not None else _decode_image(blob, native_first=False)
-                res = torch.from_numpy(aug.apply_params(data, items[k][4:]))
+                if items[k][9] is not None:
+                    Ai, new_h, new_w, wy, wx, _ = items[k][9]
+                    data = aug.aug.warp(data, (Ai, new_h, new_w, wy, wx, True))
+                res = torch.from_numpy(aug.apply_params(data, items[k][4:9]))
                 dst[first + k].copy_(res)
 
     def next(self):

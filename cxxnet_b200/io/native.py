@@ -46,7 +46,10 @@ class AugItem(ctypes.Structure):
     """one instance of ``cxnio_decode_augment_batch`` (``csrc/runtime/batch_pipeline.cpp`` CxnioAugItem)"""
     _fields_ = [("buf", ctypes.c_char_p), ("size", ctypes.c_uint64), ("pixels", ctypes.c_void_p),
                 ("src_h", ctypes.c_int32), ("src_w", ctypes.c_int32), ("y0", ctypes.c_int32), ("x0", ctypes.c_int32),
-                ("flip", ctypes.c_int32), ("contrast", ctypes.c_float), ("illum", ctypes.c_float)]
+                ("flip", ctypes.c_int32), ("contrast", ctypes.c_float), ("illum", ctypes.c_float),
+                ("affine", ctypes.c_int32), ("warp_h", ctypes.c_int32), ("warp_w", ctypes.c_int32),
+                ("warp_y", ctypes.c_int32), ("warp_x", ctypes.c_int32), ("fill", ctypes.c_float),
+                ("ai", ctypes.c_double * 6)]
 
 
 class PageReader:
@@ -154,7 +157,8 @@ def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, 
     (a contiguous torch tensor [n, 3, H, W], fp32 or bf16) on native worker threads.
 
     items: tuples ``(encoded bytes, decoded planar float array or None, src_h, src_w, y0, x0, flip, contrast,
-    illum)``; ``mean_mode`` 0 none / 1 per-channel values / 2 mean image (per instance: subtracted before the
+    illum[, affine])`` where ``affine`` is None or ``(Ai, warp_h, warp_w, warp_y, warp_x, fill)`` as drawn by
+    ``ImageAugmenter.draw`` (the crop is then taken from the warped image); ``mean_mode`` 0 none / 1 per-channel values / 2 mean image (per instance: subtracted before the
     crop when it has the decoded size, after it when it has the crop size).  Returns one status per item
     (0 = written)."""
     import numpy as np
@@ -172,8 +176,15 @@ def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, 
     status = (ctypes.c_int * n)()
     # a mean image is used in one of two ways depending on the instance's decoded size: split the batch
     groups = {}
-    for i, (blob, pixels, h, w, y0, x0, flip, contrast, illum) in enumerate(items):
+    for i, item in enumerate(items):
+        blob, pixels, h, w, y0, x0, flip, contrast, illum = item[:9]
+        affine = item[9] if len(item) > 9 else None
         a = arr[i]
+        if affine is not None:
+            Ai, a.warp_h, a.warp_w, a.warp_y, a.warp_x, a.fill = affine
+            a.affine = 1
+            for k in range(6):
+                a.ai[k] = float(Ai[k // 3, k % 3])
         if pixels is not None:
             pixels = np.ascontiguousarray(pixels, dtype=np.float32)
             keep.append(pixels)
@@ -183,7 +194,8 @@ def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, 
         a.src_h, a.src_w, a.y0, a.x0, a.flip = h, w, y0, x0, 1 if flip else 0
         a.contrast, a.illum = contrast, illum
         mode = mean_mode
-        if mean_mode == 2 and (h, w) != (mean_h, mean_w):
+        eff = (H, W) if affine is not None else (h, w)      # after the affine stage the instance has the crop's size
+        if mean_mode == 2 and eff != (mean_h, mean_w):
             mode = 3
         groups.setdefault(mode, []).append(i)
     assert dst.is_contiguous() and tuple(dst.shape[1:]) == (c, H, W) and dst.shape[0] >= n

@@ -381,3 +381,37 @@ silent = 1
     assert r.returncode == 0, r.stdout + r.stderr
     preds = [int(float(x)) for x in (tmp_path / "pred.txt").read_text().split()]
     assert preds == [i % 2 for i in range(60)]
+
+
+def test_native_affine_stage_equals_the_numpy_warp(tmp_path):
+    """rotation / shear / aspect / scale (the kaggle bowl augmentation) on the native batch path: same random
+    decisions, same bilinear arithmetic, bit-identical batches"""
+    import torch
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.io.data import create_iterator
+    _jpeg_bin(tmp_path, n=10, w=48, h=48)
+
+    def batches(native_pipeline, extra):
+        it = create_iterator(parse_config_string(
+            'iter = imgbin\n image_list = "%s"\n image_bin = "%s"\n batch_size = 5\n input_shape = 3,40,40\n'
+            ' rand_crop = 1\n rand_mirror = 1\n max_rotate_angle = 180\n max_aspect_ratio = 0.5\n'
+            ' max_shear_ratio = 0.3\n min_crop_size = 32\n max_crop_size = 48\n seed_data = 4\n silent = 1\n'
+            ' native_pipeline = %d\n%siter = end\n' % (tmp_path / "j.lst", tmp_path / "j.bin", native_pipeline, extra)))
+        it.init()
+        assert it._native == bool(native_pipeline)
+        out = []
+        it.before_first()
+        while it.next():
+            out.append(it.value().data.clone())
+        it.close()
+        return out
+
+    for extra in ("", " mean_value = 90,100,110\n divideby = 32\n max_random_contrast = 0.1\n",
+                  ' image_mean = "%s"\n fill_value = 0\n' % (tmp_path / "m.bin")):
+        if "image_mean" in extra:
+            batches(0, extra)                       # first use creates the mean image
+        a, b = batches(0, extra), batches(1, extra)
+        assert len(a) == len(b) == 2
+        for x, y in zip(a, b):
+            assert torch.equal(x, y), float((x - y).abs().max())
+    assert float(a[0].std()) > 1.0
