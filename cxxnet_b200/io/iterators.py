@@ -649,7 +649,10 @@ class AugmentIterator(IIterator):
         if name == "max_random_contrast": self.max_random_contrast = float(val)
         if name == "max_random_illumination": self.max_random_illumination = float(val)
         if name == "mean_value":
-            self.mean_b, self.mean_g, self.mean_r = [float(x) for x in val.split(",")]
+            vals = [float(x) for x in val.split(",")]
+            if len(vals) == 1:             # one number for every plane (single-channel nets)
+                vals = vals * 3
+            self.mean_b, self.mean_g, self.mean_r = vals
         self.aug.set_param(name, val)
 
     def init(self):
@@ -733,7 +736,13 @@ class AugmentIterator(IIterator):
 
     def _set_data(self, d: DataInst):
         self.out.label, self.out.index = d.label, d.index
-        data = self.aug.process(d.data, self.rnd)
+        data = d.data
+        if self.shape[0] == 1 and data.ndim == 3 and data.shape[0] == 3:
+            # a single-channel net fed by an image source (decoders always deliver three planes; a grey-scale
+            # file has them equal): the mean of the planes.  Not in the reference, whose image sources are
+            # three-channel only.
+            data = data.mean(axis=0, keepdims=True, dtype=np.float32)
+        data = self.aug.process(data, self.rnd)
         c, H, W = self.shape
         if H == 1:
             self.out.data = (data * self.scale).astype(np.float32)

@@ -221,3 +221,28 @@ def test_partition_maker_writes_parts_and_makefile(tmp_path):
     assert sum(len((tmp_path / "out" / p).read_text().splitlines()) for p in parts) == 6
     mk = (tmp_path / "Gen.mk").read_text()
     assert mk.startswith("all: ") and mk.count("im2bin ") == 3 and "part001.bin" in mk
+
+
+def test_single_channel_net_reads_image_sources(tmp_path):
+    """input_shape = 1,h,w over an image source: grey-scale files arrive as one plane"""
+    pytest.importorskip("PIL")
+    from PIL import Image
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.io.data import create_iterator
+    lines = []
+    arrs = []
+    for i in range(4):
+        a = (np.random.RandomState(i).rand(12, 14) * 255).astype(np.uint8)
+        arrs.append(a)
+        Image.fromarray(a, mode="L").save(tmp_path / ("g%d.png" % i))
+        lines.append("%d\t%d\tg%d.png\n" % (i, i % 2, i))
+    (tmp_path / "g.lst").write_text("".join(lines))
+    it = create_iterator(parse_config_string(
+        'iter = img\n image_list = "%s"\n image_root = "%s/"\n batch_size = 2\n input_shape = 1,12,14\n'
+        ' mean_value = 10\n silent = 1\niter = end\n' % (tmp_path / "g.lst", tmp_path)))
+    it.init()
+    it.before_first()
+    assert it.next()
+    b = it.value()
+    assert tuple(b.data.shape) == (2, 1, 12, 14)
+    assert np.allclose(b.data[1, 0].numpy(), arrs[1].astype(np.float32) - 10.0)
