@@ -5,7 +5,7 @@
 
 Compares the Python iterator stages (`native_pipeline = 0`) with the fused native batch path
 (csrc/runtime/batch_pipeline.cpp: JPEG decode + crop / mean / jitter / mirror / scale + batch assembly on worker
-threads), fp32 and bf16 batches.  CPU only; prints images/s."""
+threads), fp32 and bf16 batches, and pages of pre-decoded raw records (`im2bin ... raw=1`).  CPU only; prints images/s."""
 import argparse
 import io
 import os
@@ -41,13 +41,25 @@ def main():
         lines.append("%d\t%d\tx\n" % (i, i % 1000))
     open(os.path.join(tmp, "a.lst"), "w").write("".join(lines))
     open(os.path.join(tmp, "a.bin"), "wb").write(bytes(page.raw))
+    # the same images as pre-decoded raw records (what `im2bin ... raw=1` writes): several pages
+    from cxxnet_b200.io import native
+    with open(os.path.join(tmp, "raw.bin"), "wb") as f:
+        rp = BinaryPage()
+        for i in range(args.n):
+            rec = native.raw_encode(np.asarray(Image.open(io.BytesIO(page.get(i))).convert("RGB")))
+            if not rp.push(rec):
+                f.write(bytes(rp.raw))
+                rp = BinaryPage()
+                assert rp.push(rec)
+        f.write(bytes(rp.raw))
     print("cores: %d" % (os.cpu_count() or 1))
-    for native_pipeline, dtype in ((0, "fp32"), (1, "fp32"), (1, "bf16")):
+    for binfile, native_pipeline, dtype in (("a.bin", 0, "fp32"), ("a.bin", 1, "fp32"), ("a.bin", 1, "bf16"),
+                                           ("raw.bin", 1, "bf16")):
         it = create_iterator(parse_config_string(
-            'iter = imgbin\n image_list = "%s/a.lst"\n image_bin = "%s/a.bin"\n batch_size = %d\n'
+            'iter = imgbin\n image_list = "%s/a.lst"\n image_bin = "%s/%s"\n batch_size = %d\n'
             ' input_shape = 3,227,227\n rand_crop = 1\n rand_mirror = 1\n mean_value = 104,117,123\n silent = 1\n'
             ' native_pipeline = %d\n decode_threads = %d\n input_dtype = %s\niter = end\n'
-            % (tmp, tmp, args.batch, native_pipeline, args.threads, dtype)))
+            % (tmp, tmp, binfile, args.batch, native_pipeline, args.threads, dtype)))
         it.init()
         it.before_first()
         n = 0
@@ -56,7 +68,7 @@ def main():
             n += it.value().batch_size
         dt = time.perf_counter() - t0
         it.close()
-        print("native_pipeline=%d %s: %7.0f images/s (%d images)" % (native_pipeline, dtype, n / dt, n))
+        print("%-8s native_pipeline=%d %s: %7.0f images/s (%d images)" % (binfile, native_pipeline, dtype, n / dt, n))
 
 
 if __name__ == "__main__":

@@ -98,7 +98,7 @@ def build_host(force=False, verbose=False):
     if os.path.exists(tool):
         os.makedirs(os.path.join(ROOT, "bin"), exist_ok=True)
         target = os.path.join(ROOT, "bin", "im2bin")
-        if force or _newer(target, [tool] + io_hdrs):
+        if force or _newer(target, [tool] + io_hdrs + io_srcs):
             _run([cxx] + flags + ["-o", target, "-I", os.path.join(ROOT, "csrc", "runtime"), tool], verbose)
         out.append(target)
     return out

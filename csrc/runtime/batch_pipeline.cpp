@@ -18,8 +18,9 @@
 #include <thread>
 #include <vector>
 
-extern "C" int cxnio_jpeg_info(const uint8_t* buf, size_t n, int* width, int* height, int* components);
-extern "C" int cxnio_jpeg_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, int width, int height);
+// JPEG or pre-decoded raw record (raw_image.cpp)
+extern "C" int cxnio_image_info(const uint8_t* buf, size_t n, int* width, int* height, int* components);
+extern "C" int cxnio_image_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, int width, int height);
 
 extern "C" {
 
@@ -150,11 +151,11 @@ int cxnio_decode_augment_batch(const CxnioAugItem* items, int n, int C, int H, i
         continue;
       }
       int w = 0, h = 0, comps = 0;
-      int r = cxnio_jpeg_info(it.buf, it.size, &w, &h, &comps);
+      int r = cxnio_image_info(it.buf, it.size, &w, &h, &comps);
       if (r == 0 && (w != it.src_w || h != it.src_h || C != 3)) r = -12;
       if (r == 0) {
         tmp.resize(size_t(3) * h * w);
-        r = cxnio_jpeg_decode_planar_f32(it.buf, it.size, tmp.data(), w, h);
+        r = cxnio_image_decode_planar_f32(it.buf, it.size, tmp.data(), w, h);
       }
       if (r == 0) r = ProcessOne(tmp.data(), C, h, w, it, H, W, mean_mode, mean, mean_h, mean_w, scale, slot, dst_bf16, win);
       status[i] = r;

@@ -7,6 +7,7 @@
 // C ABI (used by cxxnet_b200/io/native.py through ctypes):
 //   void* cxnio_reader_open(const char** paths, int npaths, int nbuffers)
 //   int   cxnio_reader_next(void* h, const void** blob, unsigned long long* size)  1 = blob, 0 = end of data
+//   int   cxnio_reader_next_page(void* h, void* dst)   next whole 64 MiB page into caller memory, 0 = end of data
 //   void  cxnio_reader_rewind(void* h)          restart from the first file
 //   void  cxnio_reader_close(void* h)
 //   int   cxnio_pack(...)                        im2bin: see tools/im2bin.cpp
@@ -49,6 +50,25 @@ class PageReader {
       full_.pop_front();
       top_ = 0;
     }
+  }
+  // the next whole page copied into caller-owned memory (kPageBytes): records can then be handed out as views of
+  // that buffer with no per-record copy and no lifetime tie to this reader.  Not to be mixed with Next() in a pass.
+  bool NextPage(void* dst) {
+    std::unique_lock<std::mutex> lk(mu_);
+    if (cur_) {
+      free_.push_back(std::move(cur_));
+      cv_free_.notify_one();
+    }
+    cv_full_.wait(lk, [&] { return !full_.empty() || done_; });
+    if (full_.empty()) return false;
+    std::unique_ptr<BinaryPage> pg = std::move(full_.front());
+    full_.pop_front();
+    lk.unlock();
+    memcpy(dst, pg->raw(), BinaryPage::kPageBytes);
+    lk.lock();
+    free_.push_back(std::move(pg));
+    cv_free_.notify_one();
+    return true;
   }
   void Rewind() {
     Stop();
@@ -121,6 +141,7 @@ void* cxnio_reader_open(const char** paths, int npaths, int nbuffers) {
 int cxnio_reader_next(void* h, const void** blob, unsigned long long* size) {
   return static_cast<cxnio::PageReader*>(h)->Next(blob, size) ? 1 : 0;
 }
+int cxnio_reader_next_page(void* h, void* dst) { return static_cast<cxnio::PageReader*>(h)->NextPage(dst) ? 1 : 0; }
 void cxnio_reader_rewind(void* h) { static_cast<cxnio::PageReader*>(h)->Rewind(); }
 void cxnio_reader_close(void* h) { delete static_cast<cxnio::PageReader*>(h); }
 

@@ -28,10 +28,15 @@ PAGE_INTS = 64 << 18  # BinaryPage: 64 Mi ints... 64<<18 ints = 64 MiB (referenc
 def _decode_image(buf: bytes, native_first: bool = True) -> np.ndarray:
     """bytes -> float32 RGB planar (3,h,w), as the reference's imdecode + BGR->RGB split.  JPEGs go through the
     native decoder (csrc/runtime/jpeg_decoder.cpp, the counterpart of the reference's utils/decoder.h); other
-    formats, and JPEG variants it does not cover, through OpenCV or Pillow."""
+    formats, and JPEG variants it does not cover, through OpenCV or Pillow.  Raw records (`im2bin ... raw=1`,
+    csrc/runtime/raw_image.cpp) are unpacked directly."""
+    if buf[:4] == b"CXNR" and len(buf) >= 12:
+        w, h = int.from_bytes(buf[4:6], "little"), int.from_bytes(buf[6:8], "little")
+        px = np.frombuffer(buf, dtype=np.uint8, count=w * h * 3, offset=12).reshape(h, w, 3)
+        return np.ascontiguousarray(px.transpose(2, 0, 1), dtype=np.float32)
     if native_first and os.environ.get("CXN_NATIVE_JPEG", "1") != "0":
         from . import native
-        arr = native.jpeg_decode(buf)
+        arr = native.image_decode(buf)
         if arr is not None:
             return arr
     try:
@@ -307,6 +312,11 @@ class BinaryPage:
         end, beg = int(self.head[r + 2]), int(self.head[r + 1])
         return bytes(self.raw[self.nbytes - end:self.nbytes - beg])
 
+    def view(self, r: int) -> memoryview:
+        """blob r without a copy: a view that keeps the page's buffer alive for as long as it is referenced"""
+        end, beg = int(self.head[r + 2]), int(self.head[r + 1])
+        return memoryview(self.raw)[self.nbytes - end:self.nbytes - beg]
+
     def free_bytes(self) -> int:
         n = self.size()
         return (PAGE_INTS - (n + 2)) * 4 - int(self.head[n + 1])
@@ -397,6 +407,7 @@ class ImageBinIterator(IIterator):
         """file-order records with the pages streamed by the native reader thread."""
         from . import native
         rd = native.PageReader(list(self.path_imgbin), 4)
+        page, r = None, 0
         try:
             for fi in range(len(self.path_imglst)):
                 with open(self.path_imglst[fi]) as fl:
@@ -404,9 +415,15 @@ class ImageBinIterator(IIterator):
                         t = ln.split()
                         if not t:
                             continue
-                        blob = rd.next()
-                        if blob is None:
-                            return
+                        while page is None or r >= page.size():
+                            # a whole page into a buffer of its own; records are views of it (no per-record copy,
+                            # the buffer lives as long as any of its records is referenced)
+                            buf = np.empty(PAGE_INTS * 4, dtype=np.uint8)
+                            if not rd.next_page(buf):
+                                return
+                            page, r = BinaryPage(buf), 0
+                        blob = page.view(r)
+                        r += 1
                         yield (int(t[0]), np.asarray([float(x) for x in t[1:1 + self.label_width]], dtype=np.float32),
                                blob)
         finally:
@@ -439,7 +456,7 @@ class ImageBinIterator(IIterator):
                         t = lines[li]
                         li += 1
                         recs.append((int(t[0]), np.asarray([float(x) for x in t[1:1 + self.label_width]],
-                                                           dtype=np.float32), page.get(r)))
+                                                           dtype=np.float32), page.view(r)))
                     if self.two_stage and self.shuffle:
                         self.rs.shuffle(recs)
                     for rec in recs:
@@ -895,9 +912,9 @@ class BatchAdaptIterator(IIterator):
         lo, hi = min(self.slice_rank * step, self.batch_size), min((self.slice_rank + 1) * step, self.batch_size)
         items, tops = [], []
         for top, blob in self._pending:
-            info = native.jpeg_info(blob)
+            info = native.image_info(blob)
             pixels = None
-            if info is None:                               # not a JPEG the native decoder takes
+            if info is None:                               # neither a JPEG the native decoder takes nor a raw record
                 pixels = _decode_image(blob, native_first=False)
                 h, w = pixels.shape[1], pixels.shape[2]
             else:

@@ -19,19 +19,31 @@ def lib():
         L.cxnio_reader_next.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p),
                                         ctypes.POINTER(ctypes.c_ulonglong)]
         L.cxnio_reader_rewind.argtypes = [ctypes.c_void_p]
+        if hasattr(L, "cxnio_reader_next_page"):
+            L.cxnio_reader_next_page.restype = ctypes.c_int
+            L.cxnio_reader_next_page.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.cxnio_reader_close.argtypes = [ctypes.c_void_p]
         L.cxnio_pack.restype = ctypes.c_longlong
         L.cxnio_pack.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int]
         if hasattr(L, "cxnio_jpeg_info"):
             IP = ctypes.POINTER(ctypes.c_int)
-            L.cxnio_jpeg_info.argtypes = [ctypes.c_char_p, ctypes.c_size_t, IP, IP, IP]
-            L.cxnio_jpeg_decode_planar_f32.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p,
+            L.cxnio_jpeg_info.argtypes = [ctypes.c_void_p, ctypes.c_size_t, IP, IP, IP]
+            L.cxnio_jpeg_decode_planar_f32.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p,
                                                        ctypes.c_int, ctypes.c_int]
-            L.cxnio_jpeg_decode_rgb.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p,
+            L.cxnio_jpeg_decode_rgb.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p,
                                                 ctypes.c_int, ctypes.c_int]
-            L.cxnio_jpeg_decode_many.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_char_p),
+            L.cxnio_jpeg_decode_many.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_void_p),
                                                  ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(ctypes.c_void_p),
                                                  IP, IP, IP, ctypes.c_int]
+        if hasattr(L, "cxnio_image_info"):
+            IP = ctypes.POINTER(ctypes.c_int)
+            L.cxnio_image_info.argtypes = [ctypes.c_void_p, ctypes.c_size_t, IP, IP, IP]
+            L.cxnio_image_decode_planar_f32.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p,
+                                                        ctypes.c_int, ctypes.c_int]
+            L.cxnio_raw_encode.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+            L.cxnio_raw_encode.restype = ctypes.c_size_t
+            L.cxnio_pack_raw.restype = ctypes.c_longlong
+            L.cxnio_pack_raw.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_int]
         if hasattr(L, "cxnio_decode_augment_batch"):
             L.cxnio_decode_augment_batch.argtypes = [
                 ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
@@ -42,9 +54,15 @@ def lib():
     return _lib
 
 
+def _view(buf):
+    """uint8 numpy view of a bytes-like object (no copy); `.ctypes.data` is its address"""
+    import numpy as np
+    return np.frombuffer(buf, dtype=np.uint8)
+
+
 class AugItem(ctypes.Structure):
     """one instance of ``cxnio_decode_augment_batch`` (``csrc/runtime/batch_pipeline.cpp`` CxnioAugItem)"""
-    _fields_ = [("buf", ctypes.c_char_p), ("size", ctypes.c_uint64), ("pixels", ctypes.c_void_p),
+    _fields_ = [("buf", ctypes.c_void_p), ("size", ctypes.c_uint64), ("pixels", ctypes.c_void_p),
                 ("src_h", ctypes.c_int32), ("src_w", ctypes.c_int32), ("y0", ctypes.c_int32), ("x0", ctypes.c_int32),
                 ("flip", ctypes.c_int32), ("contrast", ctypes.c_float), ("illum", ctypes.c_float),
                 ("affine", ctypes.c_int32), ("warp_h", ctypes.c_int32), ("warp_w", ctypes.c_int32),
@@ -68,6 +86,11 @@ class PageReader:
             return None
         return ctypes.string_at(p.value, n.value)
 
+    def next_page(self, dst) -> bool:
+        """the next whole page copied into `dst` (a writable uint8 numpy array of 64 MiB); False at the end"""
+        assert dst.nbytes == 64 << 20
+        return bool(lib().cxnio_reader_next_page(self._h, dst.ctypes.data))
+
     def rewind(self) -> None:
         lib().cxnio_reader_rewind(self._h)
 
@@ -83,10 +106,13 @@ class PageReader:
             pass
 
 
-def pack(list_path: str, root: str, out_path: str, silent: bool = True) -> int:
+def pack(list_path: str, root: str, out_path: str, silent: bool = True, raw: bool = False) -> int:
+    """im2bin; raw = True decodes every (JPEG) file now and stores raw RGB records"""
     L = lib()
     if L is None:
         raise RuntimeError("libcxxnet_io.so is not built")
+    if raw:
+        return int(L.cxnio_pack_raw(list_path.encode(), root.encode(), out_path.encode(), 1 if silent else 0))
     return int(L.cxnio_pack(list_path.encode(), root.encode(), out_path.encode(), 1 if silent else 0))
 
 
@@ -109,9 +135,48 @@ def jpeg_info(buf: bytes):
     if L is None or not hasattr(L, "cxnio_jpeg_info") or buf[:2] != b"\xff\xd8":
         return None
     w, h, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
-    if L.cxnio_jpeg_info(buf, len(buf), ctypes.byref(w), ctypes.byref(h), ctypes.byref(c)) != 0:
+    v = _view(buf)
+    if L.cxnio_jpeg_info(v.ctypes.data, v.size, ctypes.byref(w), ctypes.byref(h), ctypes.byref(c)) != 0:
         return None
     return w.value, h.value, c.value
+
+
+def image_info(buf: bytes):
+    """(width, height, components) of a JPEG or a raw record (``csrc/runtime/raw_image.cpp``) the native pipeline
+    reads, else None"""
+    L = lib()
+    if L is None or not hasattr(L, "cxnio_image_info") or not (buf[:2] == b"\xff\xd8" or buf[:4] == b"CXNR"):
+        return None
+    w, h, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    v = _view(buf)
+    if L.cxnio_image_info(v.ctypes.data, v.size, ctypes.byref(w), ctypes.byref(h), ctypes.byref(c)) != 0:
+        return None
+    return w.value, h.value, c.value
+
+
+def image_decode(buf: bytes):
+    """JPEG or raw record -> float32 RGB planar (3, h, w), or None when the native pipeline does not read it"""
+    import numpy as np
+    info = image_info(buf)
+    if info is None:
+        return None
+    w, h, _ = info
+    out = np.empty((3, h, w), dtype=np.float32)
+    v = _view(buf)
+    if lib().cxnio_image_decode_planar_f32(v.ctypes.data, v.size, out.ctypes.data, w, h) != 0:
+        return None
+    return out
+
+
+def raw_encode(rgb_hwc) -> bytes:
+    """uint8 array (h, w, 3) -> raw record for an imgbin page"""
+    import numpy as np
+    a = np.ascontiguousarray(rgb_hwc, dtype=np.uint8)
+    assert a.ndim == 3 and a.shape[2] == 3
+    out = np.empty(12 + a.size, dtype=np.uint8)
+    n = lib().cxnio_raw_encode(a.ctypes.data, a.shape[1], a.shape[0], out.ctypes.data)
+    assert n == out.size
+    return out.tobytes()
 
 
 def jpeg_decode(buf: bytes):
@@ -123,7 +188,8 @@ def jpeg_decode(buf: bytes):
         return None
     w, h, _ = info
     out = np.empty((3, h, w), dtype=np.float32)
-    if lib().cxnio_jpeg_decode_planar_f32(buf, len(buf), out.ctypes.data, w, h) != 0:
+    v = _view(buf)
+    if lib().cxnio_jpeg_decode_planar_f32(v.ctypes.data, v.size, out.ctypes.data, w, h) != 0:
         return None
     return out
 
@@ -139,7 +205,8 @@ def jpeg_decode_many(bufs: List[bytes], nthreads: int = 0) -> list:
         return outs
     n = len(idx)
     arrs = [np.empty((3, infos[i][1], infos[i][0]), dtype=np.float32) for i in idx]
-    cb = (ctypes.c_char_p * n)(*[bufs[i] for i in idx])
+    views = [_view(bufs[i]) for i in idx]
+    cb = (ctypes.c_void_p * n)(*[v.ctypes.data for v in views])
     cs = (ctypes.c_size_t * n)(*[len(bufs[i]) for i in idx])
     co = (ctypes.c_void_p * n)(*[a.ctypes.data for a in arrs])
     cw = (ctypes.c_int * n)(*[infos[i][0] for i in idx])
@@ -190,7 +257,9 @@ def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, 
             keep.append(pixels)
             a.buf, a.size, a.pixels = None, 0, pixels.ctypes.data
         else:
-            a.buf, a.size, a.pixels = blob, len(blob), None
+            v = _view(blob)
+            keep.append(v)
+            a.buf, a.size, a.pixels = v.ctypes.data, v.size, None
         a.src_h, a.src_w, a.y0, a.x0, a.flip = h, w, y0, x0, 1 if flip else 0
         a.contrast, a.illum = contrast, illum
         mode = mean_mode

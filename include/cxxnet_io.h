@@ -19,6 +19,9 @@ extern "C" {
 void* cxnio_reader_open(const char** paths, int npaths, int nbuffers);
 /* 1 = *blob / *size describe the next record (valid until the next call), 0 = end of data */
 int cxnio_reader_next(void* reader, const void** blob, unsigned long long* size);
+/* the next whole page (64 MiB, layout of csrc/runtime/binary_page.h) copied into caller memory; 1, or 0 at the end.
+ * Use either this or cxnio_reader_next within one pass. */
+int cxnio_reader_next_page(void* reader, void* dst);
 void cxnio_reader_rewind(void* reader);
 void cxnio_reader_close(void* reader);
 /* pack the files of an image list (index <tab> label.. <tab> path, relative to root) into pages; returns the
@@ -33,6 +36,15 @@ int cxnio_jpeg_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, i
 /* `count` images on `nthreads` worker threads; status[i] per image; returns the number of failures */
 int cxnio_jpeg_decode_many(int count, const uint8_t* const* bufs, const size_t* sizes, float* const* outs_chw,
                            const int* widths, const int* heights, int* status, int nthreads);
+
+/* ---- pre-decoded records ("CXNR", LE uint16 width, height, uint8 channels = 3, 3 zero bytes, then interleaved RGB
+ * bytes) next to JPEG: the functions below take either, chosen by the first bytes.  No reference counterpart. */
+int cxnio_image_info(const uint8_t* buf, size_t n, int* width, int* height, int* components);
+int cxnio_image_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, int width, int height);
+/* interleaved RGB bytes -> raw record (out: 12 + width*height*3 bytes); returns the record size, 0 on bad sizes */
+size_t cxnio_raw_encode(const uint8_t* rgb_hwc, int width, int height, uint8_t* out);
+/* cxnio_pack that decodes every (JPEG) file and stores raw records (im2bin ... raw=1) */
+long long cxnio_pack_raw(const char* list_path, const char* root, const char* out_path, int silent);
 
 /* ---- one batch: decode + (affine warp) + crop + mean + contrast / illumination + mirror + scale */
 typedef struct CxnioAugItem {

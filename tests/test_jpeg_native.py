@@ -415,3 +415,53 @@ def test_native_affine_stage_equals_the_numpy_warp(tmp_path):
         for x, y in zip(a, b):
             assert torch.equal(x, y), float((x - y).abs().max())
     assert float(a[0].std()) > 1.0
+
+
+def test_raw_records_skip_the_decoding(tmp_path):
+    """`im2bin ... raw=1` decodes at packing time; the iterators (native batch path and Python stages) read the raw
+    records and deliver exactly what they deliver from the JPEG pages"""
+    import os
+    import subprocess
+    import torch
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.io.data import create_iterator
+    from cxxnet_b200.io.iterators import _decode_image
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    im2bin = os.path.join(root, "bin", "im2bin")
+    if not os.path.exists(im2bin):
+        pytest.skip("bin/im2bin not built")
+    os.makedirs(tmp_path / "img")
+    lines = []
+    for i in range(9):
+        (tmp_path / "img" / ("%d.jpg" % i)).write_bytes(_encode(_picture(30, 28, seed=i), quality=90, progressive=(i % 2 == 1)))
+        lines.append("%d\t%d\timg/%d.jpg\n" % (i, i % 3, i))
+    (tmp_path / "a.lst").write_text("".join(lines))
+    for name, extra in (("jpg.bin", []), ("raw.bin", ["raw=1"])):
+        subprocess.run([im2bin, str(tmp_path / "a.lst"), str(tmp_path) + "/", str(tmp_path / name)] + extra, check=True,
+                       stdout=subprocess.PIPE, timeout=120)
+    assert os.path.getsize(tmp_path / "raw.bin") == os.path.getsize(tmp_path / "jpg.bin") == 64 << 20
+
+    def batches(binfile, native_pipeline):
+        it = create_iterator(parse_config_string(
+            'iter = imgbin\n image_list = "%s"\n image_bin = "%s"\n batch_size = 4\n input_shape = 3,24,26\n rand_crop = 1\n'
+            ' rand_mirror = 1\n mean_value = 100,110,120\n round_batch = 1\n silent = 1\n native_pipeline = %d\niter = end\n'
+            % (tmp_path / "a.lst", tmp_path / binfile, native_pipeline)))
+        it.init()
+        it.before_first()
+        out = []
+        while it.next():
+            out.append(it.value().data.clone())
+        it.close()
+        return out
+    want = batches("jpg.bin", 1)
+    for native_pipeline in (0, 1):
+        got = batches("raw.bin", native_pipeline)
+        assert len(got) == len(want) == 3 and all(torch.equal(a, b) for a, b in zip(want, got))
+    # record round trip through the library and the NumPy reader
+    px = (np.random.RandomState(0).rand(5, 7, 3) * 255).astype(np.uint8)
+    rec = native.raw_encode(px)
+    assert rec[:4] == b"CXNR" and len(rec) == 12 + 5 * 7 * 3 and native.image_info(rec) == (7, 5, 3)
+    want_planar = px.transpose(2, 0, 1).astype(np.float32)
+    assert np.array_equal(native.image_decode(rec), want_planar)
+    assert np.array_equal(_decode_image(rec, native_first=False), want_planar)
+    assert native.image_info(rec[:-1]) is None                       # truncated record
