@@ -99,7 +99,7 @@ def build_host(force=False, verbose=False):
         os.makedirs(os.path.join(ROOT, "bin"), exist_ok=True)
         target = os.path.join(ROOT, "bin", "im2bin")
         if force or _newer(target, [tool] + io_hdrs + io_srcs):
-            _run([cxx] + flags + ["-o", target, "-I", os.path.join(ROOT, "csrc", "runtime"), tool], verbose)
+            _run([cxx] + flags + ["-o", target, "-I", os.path.join(ROOT, "csrc", "runtime"), tool, "-lz"], verbose)
         out.append(target)
     return out
 

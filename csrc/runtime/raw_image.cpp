@@ -8,9 +8,9 @@
 // which the batch stage only has to crop, normalise and convert (memory speed, no entropy decoding).  No
 // counterpart in the reference, whose pages always hold encoded files (tools/im2bin.cpp:6-67).
 //
-//   cxnio_image_info / cxnio_image_decode_planar_f32   JPEG or raw record, chosen by the first bytes
+//   cxnio_image_info / cxnio_image_decode_planar_f32   JPEG, PNG or raw record, chosen by the first bytes
 //   cxnio_raw_encode                                   planar-or-interleaved pixels -> raw record
-//   cxnio_pack_raw                                     im2bin with decoding (JPEG sources only)
+//   cxnio_pack_raw                                     im2bin with decoding (JPEG and PNG sources)
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -22,10 +22,20 @@
 extern "C" int cxnio_jpeg_info(const uint8_t* buf, size_t n, int* width, int* height, int* components);
 extern "C" int cxnio_jpeg_decode_rgb(const uint8_t* buf, size_t n, uint8_t* out_hwc, int width, int height);
 extern "C" int cxnio_jpeg_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, int width, int height);
+extern "C" int cxnio_png_info(const uint8_t* buf, size_t n, int* width, int* height, int* components);
+extern "C" int cxnio_png_decode_rgb(const uint8_t* buf, size_t n, uint8_t* out_hwc, int width, int height);
 
 namespace cxnio {
 constexpr size_t kRawHeader = 12;
 static bool IsRaw(const uint8_t* b, size_t n) { return n >= kRawHeader && memcmp(b, "CXNR", 4) == 0; }
+static bool IsPng(const uint8_t* b, size_t n) { return n >= 8 && memcmp(b, "\x89PNG", 4) == 0; }
+static void HwcToPlanar(const uint8_t* px, size_t plane, float* out_chw) {
+  for (size_t i = 0; i < plane; ++i) {
+    out_chw[i] = float(px[3 * i]);
+    out_chw[plane + i] = float(px[3 * i + 1]);
+    out_chw[2 * plane + i] = float(px[3 * i + 2]);
+  }
+}
 }  // namespace cxnio
 
 extern "C" {
@@ -38,22 +48,23 @@ int cxnio_image_info(const uint8_t* buf, size_t n, int* width, int* height, int*
     *width = w; *height = h; *components = c;
     return 0;
   }
+  if (cxnio::IsPng(buf, n)) return cxnio_png_info(buf, n, width, height, components);
   return cxnio_jpeg_info(buf, n, width, height, components);
 }
 
 int cxnio_image_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, int width, int height) {
+  if (cxnio::IsPng(buf, n)) {
+    std::vector<uint8_t> rgb(size_t(width) * height * 3);
+    const int rp = cxnio_png_decode_rgb(buf, n, rgb.data(), width, height);
+    if (rp == 0) cxnio::HwcToPlanar(rgb.data(), size_t(width) * height, out_chw);
+    return rp;
+  }
   if (!cxnio::IsRaw(buf, n)) return cxnio_jpeg_decode_planar_f32(buf, n, out_chw, width, height);
   int w, h, c;
   const int r = cxnio_image_info(buf, n, &w, &h, &c);
   if (r) return r;
   if (w != width || h != height) return -5;
-  const uint8_t* px = buf + cxnio::kRawHeader;
-  const size_t plane = size_t(w) * h;
-  for (size_t i = 0; i < plane; ++i) {
-    out_chw[i] = float(px[3 * i]);
-    out_chw[plane + i] = float(px[3 * i + 1]);
-    out_chw[2 * plane + i] = float(px[3 * i + 2]);
-  }
+  cxnio::HwcToPlanar(buf + cxnio::kRawHeader, size_t(w) * h, out_chw);
   return 0;
 }
 
@@ -98,9 +109,13 @@ long long cxnio_pack_raw(const char* list_path, const char* root, const char* ou
     fclose(fi);
     if (!ok) return fail("cannot read", path);
     int w, h, c;
-    if (cxnio_jpeg_info(file.data(), file.size(), &w, &h, &c) != 0) return fail("not a JPEG this decoder reads", path);
+    const bool is_png = cxnio::IsPng(file.data(), file.size());
+    if ((is_png ? cxnio_png_info(file.data(), file.size(), &w, &h, &c) : cxnio_jpeg_info(file.data(), file.size(), &w, &h, &c)) != 0)
+      return fail("neither a JPEG nor a PNG this decoder reads", path);
     rgb.resize(size_t(w) * h * 3);
-    if (cxnio_jpeg_decode_rgb(file.data(), file.size(), rgb.data(), w, h) != 0) return fail("damaged JPEG", path);
+    if ((is_png ? cxnio_png_decode_rgb(file.data(), file.size(), rgb.data(), w, h)
+                : cxnio_jpeg_decode_rgb(file.data(), file.size(), rgb.data(), w, h)) != 0)
+      return fail("damaged image", path);
     rec.resize(cxnio::kRawHeader + rgb.size());
     const size_t rsz = cxnio_raw_encode(rgb.data(), w, h, rec.data());
     if (!rsz) return fail("image too large for a raw record", path);

@@ -142,10 +142,11 @@ def jpeg_info(buf: bytes):
 
 
 def image_info(buf: bytes):
-    """(width, height, components) of a JPEG or a raw record (``csrc/runtime/raw_image.cpp``) the native pipeline
-    reads, else None"""
+    """(width, height, components) of a JPEG, a PNG or a raw record (``csrc/runtime/raw_image.cpp``) the native
+    pipeline reads, else None"""
     L = lib()
-    if L is None or not hasattr(L, "cxnio_image_info") or not (buf[:2] == b"\xff\xd8" or buf[:4] == b"CXNR"):
+    if L is None or not hasattr(L, "cxnio_image_info") or not (buf[:2] == b"\xff\xd8" or buf[:4] == b"CXNR"
+                                                                    or buf[:4] == b"\x89PNG"):
         return None
     w, h, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
     v = _view(buf)

@@ -37,8 +37,12 @@ int cxnio_jpeg_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, i
 int cxnio_jpeg_decode_many(int count, const uint8_t* const* bufs, const size_t* sizes, float* const* outs_chw,
                            const int* widths, const int* heights, int* status, int nthreads);
 
+/* ---- PNG (non-interlaced; grey / RGB / palette, bit depths 1-16, alpha dropped); codes as for JPEG */
+int cxnio_png_info(const uint8_t* buf, size_t n, int* width, int* height, int* components);
+int cxnio_png_decode_rgb(const uint8_t* buf, size_t n, uint8_t* out_hwc, int width, int height);
+
 /* ---- pre-decoded records ("CXNR", LE uint16 width, height, uint8 channels = 3, 3 zero bytes, then interleaved RGB
- * bytes) next to JPEG: the functions below take either, chosen by the first bytes.  No reference counterpart. */
+ * bytes) next to JPEG and PNG: the functions below take any of them, chosen by the first bytes.  No reference counterpart. */
 int cxnio_image_info(const uint8_t* buf, size_t n, int* width, int* height, int* components);
 int cxnio_image_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, int width, int height);
 /* interleaved RGB bytes -> raw record (out: 12 + width*height*3 bytes); returns the record size, 0 on bad sizes */

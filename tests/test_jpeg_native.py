@@ -71,6 +71,7 @@ def test_unsupported_inputs_fall_back():
     png = io.BytesIO()
     _picture(20, 10).save(png, "PNG")
     assert native.jpeg_decode(png.getvalue()) is None and native.jpeg_info(b"\xff\xd8\xff") is None
+    assert native.image_decode(png.getvalue()).shape == (3, 10, 20)      # PNG has its own native decoder
     cmyk = _encode(_picture(16, 16).convert("CMYK"), quality=90)
     assert native.jpeg_decode(cmyk) is None                      # four components: left to the library decoders
     truncated = _encode(_picture(64, 64), quality=90)[:200]
@@ -218,7 +219,8 @@ def test_decoder_survives_mutated_inputs_under_sanitizers(tmp_path):
     r = subprocess.run([cxx, "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined",
                         "-fno-sanitize-recover=undefined", "-pthread", "-o", str(exe),
                         os.path.join(root, "tools", "jpeg_fuzz.cpp"),
-                        os.path.join(root, "csrc", "runtime", "jpeg_decoder.cpp")],
+                        os.path.join(root, "csrc", "runtime", "jpeg_decoder.cpp"),
+                        os.path.join(root, "csrc", "runtime", "png_decoder.cpp"), "-lz"],
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
     if r.returncode != 0 and "sanitize" in r.stdout:
         pytest.skip("sanitizer runtime not available: " + r.stdout[-200:])
@@ -229,6 +231,11 @@ def test_decoder_survives_mutated_inputs_under_sanitizers(tmp_path):
                             dict(quality=95, subsampling=1, progressive=True)]):
         p = tmp_path / ("seed%d.jpg" % i)
         p.write_bytes(_encode(_picture(52, 40, seed=i), **kw))
+        seeds.append(str(p))
+    for i, mode in enumerate(["RGB", "P", "LA", "1"]):
+        p = tmp_path / ("seed%d.png" % i)
+        im = _picture(52, 40, seed=i)
+        (im.quantize(colors=17) if mode == "P" else im.convert(mode)).save(p, "PNG")
         seeds.append(str(p))
     r = subprocess.run([str(exe), "1500"] + seeds, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
                        timeout=600)
@@ -465,3 +472,47 @@ def test_raw_records_skip_the_decoding(tmp_path):
     assert np.array_equal(native.image_decode(rec), want_planar)
     assert np.array_equal(_decode_image(rec, native_first=False), want_planar)
     assert native.image_info(rec[:-1]) is None                       # truncated record
+
+
+@pytest.mark.parametrize("mode", ["RGB", "L", "P", "RGBA", "LA", "1", "I;16"])
+def test_png_decoder_matches_pillow(mode):
+    """native PNG path (csrc/runtime/png_decoder.cpp): colour types, palette, alpha dropped, packed bits, every
+    scanline filter (the encoder picks them adaptively on noisy gradients)"""
+    rs = np.random.RandomState(3)
+    for (w, h) in [(31, 17), (64, 40), (5, 3), (1, 1)]:
+        yy, xx = np.mgrid[0:h, 0:w]
+        base = np.clip(np.stack([xx * 255.0 / max(w - 1, 1), yy * 255.0 / max(h - 1, 1), (xx + yy) * 4.0], -1)
+                       + rs.randn(h, w, 3) * 6, 0, 255).astype(np.uint8)
+        im = Image.fromarray(base)
+        if mode == "I;16":
+            im = Image.fromarray((base[:, :, 0].astype(np.uint16) << 8) + 37)
+        elif mode == "P":
+            im = im.quantize(colors=23)
+        else:
+            im = im.convert(mode)
+        b = io.BytesIO()
+        im.save(b, "PNG")
+        buf = b.getvalue()
+        assert native.image_info(buf) == (w, h, 3)
+        got = native.image_decode(buf)
+        if mode == "I;16":
+            want = np.repeat(base[:, :, :1], 3, axis=2)              # high byte of every sample
+        elif mode in ("RGBA", "LA"):
+            want = np.asarray(im.convert("RGBA"))[:, :, :3]          # alpha dropped, not blended
+        else:
+            want = np.asarray(im.convert("RGB"))
+        assert got is not None and np.array_equal(got, want.transpose(2, 0, 1).astype(np.float32)), (mode, w, h)
+
+
+def test_png_interlaced_or_damaged_falls_back():
+    from cxxnet_b200.io.iterators import _decode_image
+    b = io.BytesIO()
+    _picture(20, 10).save(b, "PNG")
+    good = b.getvalue()
+    cut = good[:len(good) // 2]
+    assert native.image_decode(cut) is None
+    flipped = bytearray(good)
+    flipped[len(good) // 2] ^= 0x55
+    out = native.image_decode(bytes(flipped))
+    assert out is None or out.shape == (3, 10, 20)                   # zlib / filter damage is reported, never a crash
+    assert np.array_equal(_decode_image(good), np.asarray(_picture(20, 10)).transpose(2, 0, 1).astype(np.float32))

@@ -1,12 +1,13 @@
 // im2bin: pack an image list into the imgbin BinaryPage format.
 //   usage: im2bin <image.lst> <image_root_dir> <output.bin> [raw=1]
-// Same command line and file format as the reference tool (tools/im2bin.cpp:6-67).  With raw=1 every file (JPEG) is
+// Same command line and file format as the reference tool (tools/im2bin.cpp:6-67).  With raw=1 every file (JPEG or PNG) is
 // decoded now and stored as a raw RGB record (csrc/runtime/raw_image.cpp): about 8x the bytes, no decoding at
 // training time.
 #include <cstdio>
 #include <cstring>
 #include "../csrc/runtime/page_reader.cpp"
 #include "../csrc/runtime/jpeg_decoder.cpp"
+#include "../csrc/runtime/png_decoder.cpp"
 #include "../csrc/runtime/raw_image.cpp"
 
 int main(int argc, char* argv[]) {

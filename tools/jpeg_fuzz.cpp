@@ -1,7 +1,7 @@
-// Mutation fuzzer for the native JPEG decoder (csrc/runtime/jpeg_decoder.cpp).
+// Mutation fuzzer for the native image decoders (csrc/runtime/jpeg_decoder.cpp, png_decoder.cpp).
 //   g++ -O1 -g -std=c++17 -fsanitize=address,undefined -fno-sanitize-recover=undefined -pthread \
-//       -o jpeg_fuzz tools/jpeg_fuzz.cpp csrc/runtime/jpeg_decoder.cpp
-//   ./jpeg_fuzz <iterations per file> a.jpg b.jpg ...
+//       -o jpeg_fuzz tools/jpeg_fuzz.cpp csrc/runtime/jpeg_decoder.cpp csrc/runtime/png_decoder.cpp -lz
+//   ./jpeg_fuzz <iterations per file> a.jpg b.png ...
 // Every iteration flips / overwrites a few bytes of a seed file (and sometimes truncates it), copies the result
 // into an exact-size heap block so that the sanitizer sees any over-read, and decodes it.  The decoder may
 // reject the input; it must not crash, read or write out of bounds, or overflow.  Prints the two counts.
@@ -13,6 +13,8 @@
 
 extern "C" int cxnio_jpeg_info(const uint8_t*, size_t, int*, int*, int*);
 extern "C" int cxnio_jpeg_decode_rgb(const uint8_t*, size_t, uint8_t*, int, int);
+extern "C" int cxnio_png_info(const uint8_t*, size_t, int*, int*, int*);
+extern "C" int cxnio_png_decode_rgb(const uint8_t*, size_t, uint8_t*, int, int);
 
 int main(int argc, char** argv) {
   if (argc < 3) {
@@ -42,9 +44,12 @@ int main(int argc, char** argv) {
       if (rand() % 10 == 0) m.resize(rand() % m.size() + 1);
       std::vector<uint8_t> exact(m);
       int w, h, n;
-      if (cxnio_jpeg_info(exact.data(), exact.size(), &w, &h, &n) != 0 || long(w) * h > 4000000) { ++rejected; continue; }
+      const bool png = seed.size() > 4 && seed[1] == 'P' && seed[2] == 'N' && seed[3] == 'G';
+      if ((png ? cxnio_png_info(exact.data(), exact.size(), &w, &h, &n) : cxnio_jpeg_info(exact.data(), exact.size(), &w, &h, &n)) != 0 ||
+          long(w) * h > 4000000) { ++rejected; continue; }
       std::vector<uint8_t> out(size_t(w) * h * 3);
-      if (cxnio_jpeg_decode_rgb(exact.data(), exact.size(), out.data(), w, h) == 0) ++decoded; else ++rejected;
+      if ((png ? cxnio_png_decode_rgb(exact.data(), exact.size(), out.data(), w, h)
+               : cxnio_jpeg_decode_rgb(exact.data(), exact.size(), out.data(), w, h)) == 0) ++decoded; else ++rejected;
     }
   }
   printf("decoded %ld rejected %ld\n", decoded, rejected);
