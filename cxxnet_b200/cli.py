@@ -318,11 +318,14 @@ class LearnTask:
             if not self.silent and self.rank == 0:
                 print("update round %d" % (self.start_counter - 1), end="", flush=True)
             sample_counter = 0
+            round_t0, n_inst = time.time(), 0
             self.net_trainer.start_round(self.start_counter)
             self.itr_train.before_first()
             while self.itr_train.next():
                 if self.test_io == 0:
                     self.net_trainer.update(self.itr_train.value())
+                else:
+                    n_inst += self.itr_train.value().batch_size
                 sample_counter += 1
                 if sample_counter % self.print_step == 0:
                     elapsed = int(time.time() - start)
@@ -339,6 +342,11 @@ class LearnTask:
                 if self.rank == 0:
                     err.write(line + "\n")
                     err.flush()
+            if self.test_io != 0 and self.rank == 0:
+                # the reference only runs the pipeline; the rate is what one wants to know from such a run
+                dt = max(time.time() - round_t0, 1e-9)
+                print("\nI/O test round %d: %d batches, %d instances in %.2f sec: %.0f instances/sec"
+                      % (self.start_counter - 1, sample_counter, n_inst, dt, n_inst / dt))
             elapsed = int(time.time() - start)
             report = self.net_trainer.timing_report()
             if report and self.rank == 0:

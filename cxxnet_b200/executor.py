@@ -150,14 +150,20 @@ class NeuralNet:
             if c.type != nc.kSharedLayer:
                 c.layer.save_model(fo)
 
-    def load_model(self, fi: BinaryIO) -> None:
+    def load_model(self, fi: BinaryIO, infer_shapes: bool = True) -> None:
+        """``infer_shapes = False`` only reads every layer's stored parameters and weights: enough to copy layers by
+        name (finetune) or to inspect a checkpoint, and possible without the configuration - a stored net does not
+        carry the keys of its weightless layers (pooling windows ...), so its shapes cannot be inferred from the
+        file alone (the reference's finetune path runs the shape inference on the stored net all the same,
+        ``nnet_impl-inl.hpp:101-113``)."""
         self._init_net()
         self._config_connections()
         for c in self.connections:
             if c.type != nc.kSharedLayer:
                 c.layer.load_model(fi)
                 self._layer_to_device(c.layer)
-        self._init_connections()
+        if infer_shapes:
+            self._init_connections()
 
     def copy_layer(self, index: int, fi: BinaryIO) -> None:
         """finetune: load one layer's weights from a stream (reference ``neural_net-inl.hpp`` CopyLayer)."""

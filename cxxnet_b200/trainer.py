@@ -248,7 +248,7 @@ class NetTrainer:
         mio.read_i64(fi)
         self.epoch_counter = 0
         old_net = NeuralNet(old_cfg, 1, 0, torch.device("cpu"), "ref", silent=1)
-        old_net.load_model(io.BytesIO(mio.read_bytes(fi)))
+        old_net.load_model(io.BytesIO(mio.read_bytes(fi)), infer_shapes=False)
         for i, ol in enumerate(old_cfg.layers):
             for j, nl in enumerate(self.net_cfg.layers):
                 if ol.name == nl.name and ol.name != "":

@@ -114,6 +114,7 @@ def test_test_io_mode_runs_pipeline_only(tmp_path):
     conf.write_text(CONF % {"rounds": 1, "model_dir": tmp_path / "m", "pred": tmp_path / "p.txt"})
     r = _run([str(conf), "test_io=1", "silent=0"], tmp_path)
     assert "start I/O test" in r.stdout and "train-error" not in r.stderr
+    assert re.search(r"I/O test round 0: 30 batches, 3000 instances in [0-9.]+ sec: \d+ instances/sec", r.stdout)
 
 
 def test_pairtest_layer_reports_zero_error_for_identical_implementations(capsys):
@@ -195,3 +196,56 @@ def test_layer_timing_reports_every_layer(tmp_path):
     fwd = [float(l.split()[2]) for l in rows]
     bwd = [float(l.split()[3]) for l in rows]
     assert all(v > 0 for v in fwd) and all(v > 0 for v in bwd)
+
+
+CONV_CONF = """
+data = train
+iter = mnist
+    path_img = "none"
+    path_label = "none"
+    num_synthetic = 300
+    input_flat = 0
+iter = end
+netconfig=start
+layer[+1] = conv:cv1
+  kernel_size = 3
+  stride = 2
+  nchannel = 4
+layer[+1] = max_pooling
+  kernel_size = 3
+  stride = 2
+layer[+1] = flatten
+layer[+1] = fullc:%(head)s
+  nhidden = 10
+layer[+0] = softmax
+netconfig=end
+input_shape = 1,28,28
+batch_size = 100
+dev = cpu
+num_round = 1
+max_round = 1
+eta = 0.1
+metric = error
+model_dir = %(model_dir)s
+silent = 1
+"""
+
+
+def test_finetune_and_model_info_on_a_net_with_weightless_layers(tmp_path):
+    """a stored net does not carry its pooling windows: copying layers by name and inspecting the file must not
+    need them"""
+    a = tmp_path / "a.conf"
+    a.write_text(CONV_CONF % {"head": "fc", "model_dir": tmp_path / "m"})
+    _run([str(a)], tmp_path)
+    model = tmp_path / "m" / "0001.model"
+    b = tmp_path / "b.conf"
+    b.write_text(CONV_CONF % {"head": "newhead", "model_dir": tmp_path / "m2"})
+    r = _run([str(b), "task=finetune", "model_in=%s" % model], tmp_path)
+    assert "Copying layer cv1" in r.stdout and "Copying layer newhead" not in r.stdout
+    env = dict(os.environ)
+    env["PYTHONPATH"] = ROOT + os.pathsep + env.get("PYTHONPATH", "")
+    info = subprocess.run([sys.executable, "-m", "cxxnet_b200.tools.model_info", str(model), "--weights"], env=env,
+                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert info.returncode == 0, info.stdout
+    assert "input 1x28x28" in info.stdout and "MaxPooling" in info.stdout and "wmat  (1, 4, 9)" in info.stdout
+    assert "parameters: %d" % (4 * 9 + 4 + 10 * 4 * 6 * 6 + 10) in info.stdout
