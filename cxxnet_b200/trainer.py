@@ -298,6 +298,9 @@ class NetTrainer:
         """one mini-batch: forward, backprop, (every ``update_period`` calls) weight update
         (reference ``nnet_impl-inl.hpp:141-185``)."""
         net = self.net
+        if batch.batch_size > self.batch_size:
+            raise ValueError("update: the batch holds %d instances but the net was built for batch_size = %d"
+                             % (batch.batch_size, self.batch_size))
         if self.cuda_graph and self._graph_applicable(batch):
             self._update_graph(batch)
             return
@@ -449,6 +452,18 @@ class NetTrainer:
         """forward and return the requested nodes as host fp32 (batch_size, c, h, w) tensors
         assembled over all ranks (reference ``nnet_impl-inl.hpp:300-325``)."""
         net = self.net
+        if batch.batch_size > self.batch_size:
+            # more instances than the net was sized for (an ndarray handed to predict / extract): go through it in
+            # pieces of batch_size instead of dropping the rest (the reference stops with an assertion here)
+            pieces = []
+            for lo in range(0, batch.batch_size, self.batch_size):
+                hi = min(lo + self.batch_size, batch.batch_size)
+                part = DataBatch()
+                part.data = self._as_tensor(batch.data)[lo:hi]
+                part.extra_data = [self._as_tensor(e)[lo:hi] for e in batch.extra_data]
+                part.batch_size = hi - lo
+                pieces.append(self._forward_to(node_ids, part))
+            return [torch.cat([p[i] for p in pieces], dim=0) for i in range(len(node_ids))]
         data = self._as_tensor(batch.data)
         begin, end = self._slice(batch.batch_size)
         net.set_input(data[begin:end], [self._as_tensor(e)[begin:end] for e in batch.extra_data])

@@ -98,3 +98,18 @@ def test_c_abi_from_plain_c(tmp_path):
     r = subprocess.run([str(exe), str(tmp_path / "capi.model")], env=env, stdout=subprocess.PIPE,
                        stderr=subprocess.STDOUT, text=True, timeout=300)
     assert r.returncode == 0 and "C ABI OK" in r.stdout, r.stdout[-3000:]
+
+
+def test_predict_takes_more_rows_than_the_batch_size_and_update_refuses():
+    from cxxnet_b200.wrapper import cxxnet
+    net = cxxnet.Net(dev="cpu", cfg=NET)
+    net.set_param("silent", 1)
+    net.init_model()
+    x = np.random.RandomState(0).rand(250, 1, 1, 784).astype(np.float32)
+    whole = net.predict(x)
+    assert whole.shape == (250,)
+    parts = np.concatenate([net.predict(x[:100]), net.predict(x[100:200]), net.predict(x[200:])])
+    assert np.array_equal(whole, parts)
+    assert net.extract(x, "sg1").shape == (250, 1, 1, 24)
+    with pytest.raises(ValueError, match="batch_size"):
+        net.update(x, np.zeros(250, dtype=np.float32))
