@@ -75,3 +75,77 @@ def test_host_detection_reads_the_launcher_environment(monkeypatch):
     assert ranks_share_one_host()
     monkeypatch.delenv("LOCAL_WORLD_SIZE")
     assert ranks_share_one_host()
+
+
+def test_two_ranks_over_packed_jpegs_decode_their_own_rows_and_match_one_process(tmp_path):
+    """task driver under torchrun (gloo) on imgbin data: every rank decodes only its rows of each batch
+    (slice_world / slice_rank), random crops and mirrors included, and the trained weights equal a single process's"""
+    PIL = pytest.importorskip("PIL")
+    import numpy as np
+    from PIL import Image
+    im2bin = os.path.join(ROOT, "bin", "im2bin")
+    if not os.path.exists(im2bin):
+        pytest.skip("bin/im2bin not built")
+    rs = np.random.RandomState(0)
+    os.makedirs(tmp_path / "img")
+    lines = []
+    for i in range(60):
+        cls = i % 2
+        a = np.clip(rs.randn(20, 22, 3) * 20 + (70 if cls == 0 else 180), 0, 255).astype(np.uint8)
+        Image.fromarray(a).save(tmp_path / "img" / ("%03d.jpg" % i), quality=90)
+        lines.append("%d\t%d\timg/%03d.jpg\n" % (i, cls, i))
+    (tmp_path / "all.lst").write_text("".join(lines))
+    subprocess.run([im2bin, "all.lst", "./", "all.bin"], cwd=tmp_path, check=True, stdout=subprocess.PIPE, timeout=120)
+    (tmp_path / "net.conf").write_text("""
+data = train
+iter = imgbin
+  image_list = "all.lst"
+  image_bin = "all.bin"
+  rand_crop = 1
+  rand_mirror = 1
+  mean_value = 128,128,128
+  divideby = 64
+iter = threadbuffer
+iter = end
+eval = val
+iter = imgbin
+  image_list = "all.lst"
+  image_bin = "all.bin"
+  mean_value = 128,128,128
+  divideby = 64
+iter = end
+netconfig = start
+layer[+1] = flatten
+layer[+1] = fullc:fc
+  nhidden = 2
+  init_sigma = 0.01
+layer[+0] = softmax
+netconfig = end
+input_shape = 3,16,16
+batch_size = 20
+round_batch = 1
+dev = cpu
+eta = 0.05
+momentum = 0.9
+metric = error
+num_round = 2
+max_round = 2
+silent = 1
+""")
+    env = dict(os.environ)
+    env["PYTHONPATH"] = ROOT + os.pathsep + env.get("PYTHONPATH", "")
+    env["MASTER_ADDR"] = "127.0.0.1"
+    one = subprocess.run([sys.executable, "-m", "cxxnet_b200", "net.conf", "model_dir=m1"], cwd=tmp_path, env=env,
+                         stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+    assert one.returncode == 0, one.stderr[-2000:]
+    two = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29635", "-m", "cxxnet_b200", "net.conf",
+                          "model_dir=m2"], cwd=tmp_path, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                         text=True, timeout=300)
+    assert two.returncode == 0, two.stderr[-2000:]
+    lines1 = [ln for ln in one.stderr.splitlines() if ln.startswith("[")]
+    lines2 = [ln for ln in two.stderr.splitlines() if ln.startswith("[")]
+    assert lines1 == lines2 and len(lines1) == 2
+    a = np.frombuffer((tmp_path / "m1" / "0002.model").read_bytes()[-1500 * 4:], dtype=np.float32)
+    b = np.frombuffer((tmp_path / "m2" / "0002.model").read_bytes()[-1500 * 4:], dtype=np.float32)
+    assert np.abs(a - b).max() < 1e-5
