@@ -80,3 +80,74 @@ def test_adam_table_carries_the_bias_corrected_rate():
     b1, b2 = 0.1, 0.001
     want = 0.02 * np.sqrt(1 - (1 - b2) ** 5) / (1 - (1 - b1) ** 5)
     assert np.isclose(t[1]["adam_lr_t"], want, rtol=1e-5) and np.isclose(t[1]["beta1"], b1) and np.isclose(t[1]["beta2"], b2)
+
+
+def test_collective_exchange_buckets_and_calls_on_a_mocked_device(monkeypatch):
+    """parallel/dist_exchange.py without a GPU: CUDA streams / events replaced by stand-ins, a one-rank gloo group.
+    Checks the bucket plan (backward order, small layers merged, trigger = lowest layer of the bucket), that a
+    bucket's all-reduce covers exactly its chunk range and is followed by the update of that range, and the waits."""
+    import torch.distributed as dist
+    from cxxnet_b200.parallel import dist_exchange as dx
+    from cxxnet_b200.parallel.arena import ParamArena
+
+    class FakeEvent:
+        def __init__(self, *a, **k): self.recorded = 0
+        def record(self, *a): self.recorded += 1
+
+    class FakeStream:
+        def __init__(self, *a, **k): self.waits = 0
+        def wait_event(self, ev): self.waits += 1
+
+    class FakeCtx:
+        def __init__(self, s): pass
+        def __enter__(self): return self
+        def __exit__(self, *a): return False
+    main = FakeStream()
+    monkeypatch.setattr(torch.cuda, "Event", FakeEvent)
+    monkeypatch.setattr(torch.cuda, "Stream", FakeStream)
+    monkeypatch.setattr(torch.cuda, "stream", FakeCtx)
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda *a, **k: main)
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+    monkeypatch.setenv("CXN_XCHG_MIN_BUCKET_MB", "0.5")
+    if not dist.is_initialized():
+        dist.init_process_group("gloo", init_method="tcp://127.0.0.1:29636", rank=0, world_size=1)
+    try:
+        a = ParamArena(torch.device("cpu"), "sgd")
+        a.upload_hyper = lambda slot=0: None
+        sizes = {0: (96, 363), 4: (256, 1200), 8: (384, 2304), 16: (64, 4096)}      # layer index -> wmat shape
+        for li, (r, c) in sizes.items():
+            a.add(None, li, "wmat", r, c, c, _param("wmat"))
+            a.add(None, li, "bias", 1, r, 0, _param("bias"))
+        a.finalize()
+        a.refresh_shadow = lambda: None
+        updates = []
+        a.update = lambda cb=0, ce=None: updates.append((cb, ce))
+
+        class Net:
+            pass
+        net = Net()
+        net.arena, net.rank, net.world_size, net.device = a, 0, 1, torch.device("cpu")
+        ex = dx.CollectiveExchange(net)
+        # backward order; a bucket closes once it holds >= 0.5 MB: [16] (1 MB), [8] (3.5 MB), [4] (1.2 MB), [0] (0.14 MB)
+        assert [b["layers"] for b in ex.buckets] == [[16], [8], [4], [0]]
+        assert all(b["trigger"] == b["layers"][-1] for b in ex.buckets)
+        cover = sorted((b["cb"], b["ce"]) for b in ex.buckets)
+        assert cover[0][0] == 0 and cover[-1][1] == a.nchunks and all(x[1] == y[0] for x, y in zip(cover, cover[1:]))
+        a.g.fill_(1.0)
+        ex.begin_step()
+        ex.layer_done(12)                                   # a layer without weights: nothing happens
+        assert updates == []
+        for li in (16, 8, 4, 0):
+            ex.layer_done(li)
+        assert updates == [(b["cb"], b["ce"]) for b in ex.buckets]
+        assert float(a.g.sum()) == float(a.g.numel())       # one rank: the sum over ranks is the gradient itself
+        assert all(b["pending"] for b in ex.buckets)
+        ex.wait_layer(8)
+        assert [b["pending"] for b in ex.buckets] == [True, False, True, True]
+        ex.wait_all()
+        assert not any(b["pending"] for b in ex.buckets)
+        assert ex.check_replicas() == 0.0
+        ex.broadcast_weights()
+        ex.publish_pending(); ex.after_replayed_step(); ex.gather_master()
+    finally:
+        dist.destroy_process_group()
