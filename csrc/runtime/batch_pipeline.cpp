@@ -152,10 +152,16 @@ int cxnio_decode_augment_batch(const CxnioAugItem* items, int n, int C, int H, i
       }
       int w = 0, h = 0, comps = 0;
       int r = cxnio_image_info(it.buf, it.size, &w, &h, &comps);
-      if (r == 0 && (w != it.src_w || h != it.src_h || C != 3)) r = -12;
+      if (r == 0 && (w != it.src_w || h != it.src_h || (C != 3 && C != 1))) r = -12;
       if (r == 0) {
         tmp.resize(size_t(3) * h * w);
         r = cxnio_image_decode_planar_f32(it.buf, it.size, tmp.data(), w, h);
+      }
+      if (r == 0 && C == 1) {
+        // a single-channel net: the mean of the three decoded planes (for a grey-scale file, the image)
+        const size_t plane = size_t(h) * w;
+        float* t = tmp.data();
+        for (size_t i = 0; i < plane; ++i) t[i] = ((t[i] + t[plane + i]) + t[2 * plane + i]) / 3.0f;
       }
       if (r == 0) r = ProcessOne(tmp.data(), C, h, w, it, H, W, mean_mode, mean, mean_h, mean_w, scale, slot, dst_bf16, win);
       status[i] = r;

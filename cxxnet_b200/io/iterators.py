@@ -850,7 +850,7 @@ class BatchAdaptIterator(IIterator):
             return False
         if native.lib() is None or not hasattr(native.lib(), "cxnio_decode_augment_batch"):
             return False
-        return not (len(self.shape) != 3 or self.shape[0] != 3 or self.shape[1] == 1)
+        return not (len(self.shape) != 3 or self.shape[0] not in (1, 3) or self.shape[1] == 1)
 
     def init(self):
         chain = self._native_chain()
@@ -861,7 +861,8 @@ class BatchAdaptIterator(IIterator):
             self.base.base.raw_mode = True
         self.base.init()
         aug = self.base
-        self._native = chain and not (aug.mean_mode() == 2 and (aug.meanimg is None or aug.meanimg.shape[0] != 3))
+        self._native = chain and not (aug.mean_mode() == 2 and (aug.meanimg is None
+                                                                 or aug.meanimg.shape[0] != self.shape[0]))
         self.out.alloc_dense((self.batch_size,) + tuple(self.shape), self.batch_size, self.label_width, pin=True)
         self._data_np = self.out.data.numpy()
         self._label_np = self.out.label.numpy()
@@ -916,6 +917,8 @@ class BatchAdaptIterator(IIterator):
             pixels = None
             if info is None:                               # neither a JPEG the native decoder takes nor a raw record
                 pixels = _decode_image(blob, native_first=False)
+                if self.shape[0] == 1 and pixels.shape[0] == 3:
+                    pixels = pixels.mean(axis=0, keepdims=True, dtype=np.float32)
                 h, w = pixels.shape[1], pixels.shape[2]
             else:
                 w, h = info[0], info[1]
@@ -951,6 +954,8 @@ class BatchAdaptIterator(IIterator):
             if st != 0:                                    # e.g. a damaged file: the library decoders get a try
                 blob, pixels, h, w = items[k][:4]
                 data = pixels if pixels is not None else _decode_image(blob, native_first=False)
+                if self.shape[0] == 1 and data.shape[0] == 3:
+                    data = data.mean(axis=0, keepdims=True, dtype=np.float32)
                 if items[k][9] is not None:
                     Ai, new_h, new_w, wy, wx, _ = items[k][9]
                     data = aug.aug.warp(data, (Ai, new_h, new_w, wy, wx, True))

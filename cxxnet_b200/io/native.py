@@ -222,7 +222,7 @@ def jpeg_decode_many(bufs: List[bytes], nthreads: int = 0) -> list:
 def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, dst_bf16: bool,
                          nthreads: int = 0) -> List[int]:
     """Decode, crop, mean-subtract, jitter, mirror and scale ``len(items)`` images into the rows of ``dst``
-    (a contiguous torch tensor [n, 3, H, W], fp32 or bf16) on native worker threads.
+    (a contiguous torch tensor [n, C, H, W], C = 3 or 1, fp32 or bf16) on native worker threads.
 
     items: tuples ``(encoded bytes, decoded planar float array or None, src_h, src_w, y0, x0, flip, contrast,
     illum[, affine])`` where ``affine`` is None or ``(Ai, warp_h, warp_w, warp_y, warp_x, fill)`` as drawn by

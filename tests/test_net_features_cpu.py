@@ -244,5 +244,24 @@ def test_single_channel_net_reads_image_sources(tmp_path):
     it.before_first()
     assert it.next()
     b = it.value()
-    assert tuple(b.data.shape) == (2, 1, 12, 14)
+    assert tuple(b.data.shape) == (2, 1, 12, 14) and it._native
     assert np.allclose(b.data[1, 0].numpy(), arrs[1].astype(np.float32) - 10.0)
+    # colour JPEGs into a single-channel net: native batch path == Python stages
+    for i in range(4):
+        a = (np.random.RandomState(10 + i).rand(12, 14, 3) * 255).astype(np.uint8)
+        Image.fromarray(a).save(tmp_path / ("c%d.jpg" % i), quality=92)
+    (tmp_path / "c.lst").write_text("".join("%d\t0\tc%d.jpg\n" % (i, i) for i in range(4)))
+
+    def run(native_pipeline):
+        jt = create_iterator(parse_config_string(
+            'iter = img\n image_list = "%s"\n image_root = "%s/"\n batch_size = 2\n input_shape = 1,10,12\n'
+            ' rand_crop = 1\n rand_mirror = 1\n mean_value = 100\n divideby = 16\n native_pipeline = %d\n silent = 1\n'
+            'iter = end\n' % (tmp_path / "c.lst", tmp_path, native_pipeline)))
+        jt.init()
+        jt.before_first()
+        out = []
+        while jt.next():
+            out.append(jt.value().data.clone())
+        return out
+    a0, a1 = run(0), run(1)
+    assert len(a0) == 2 and all(torch.equal(x, y) for x, y in zip(a0, a1))
