@@ -72,3 +72,42 @@ def test_kaggle_resize_and_submission_scripts(tmp_path):
         tmp_path / "probs.txt", tmp_path / "out.csv")
     out = (tmp_path / "out.csv").read_text().strip().split("\n")
     assert out[0] == "image,acantharia,copepod" and len(out) == 7 and out[1].endswith(",0.25,0.75")
+
+
+def test_make_image_list_resizes_splits_and_packs(tmp_path):
+    """tools/make_image_list.py on a class-per-directory tree, then bin/im2bin raw=1 and an imgbin read-back"""
+    import subprocess
+    import sys
+    import numpy as np
+    from PIL import Image
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.io.data import create_iterator
+    for ci, cls in enumerate(("n01", "n02", "n03")):
+        os.makedirs(tmp_path / "raw" / cls)
+        for i in range(8):
+            a = np.full((40 + 3 * i, 50, 3), 60 * ci + 20, dtype=np.uint8)
+            Image.fromarray(a).save(tmp_path / "raw" / cls / ("im%d.%s" % (i, "png" if i % 2 else "jpg")))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_image_list.py"), str(tmp_path / "raw"),
+                        str(tmp_path / "train.lst"), "--val-fraction", "0.25", "--resize", "32", "--resized-root",
+                        str(tmp_path / "small"), "--synsets", str(tmp_path / "synsets.txt")],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout
+    assert (tmp_path / "synsets.txt").read_text().split() == ["n01", "n02", "n03"]
+    tr = (tmp_path / "train.lst").read_text().strip().split("\n")
+    va = (tmp_path / "train.val.lst").read_text().strip().split("\n")
+    assert len(tr) + len(va) == 24 and len(va) >= 1 and [ln.split("\t")[0] for ln in tr] == [str(i) for i in range(len(tr))]
+    assert Image.open(tmp_path / "small" / tr[0].split("\t")[2]).size == (32, 32)
+    im2bin = os.path.join(ROOT, "bin", "im2bin")
+    if not os.path.exists(im2bin):
+        pytest.skip("bin/im2bin not built")
+    subprocess.run([im2bin, str(tmp_path / "train.lst"), str(tmp_path / "small") + "/", str(tmp_path / "train.bin"), "raw=1"],
+                   check=True, stdout=subprocess.PIPE, timeout=120)
+    it = create_iterator(parse_config_string(
+        'iter = imgbin\n image_list = "%s"\n image_bin = "%s"\n batch_size = 4\n input_shape = 3,32,32\n silent = 1\niter = end\n'
+        % (tmp_path / "train.lst", tmp_path / "train.bin")))
+    it.init()
+    it.before_first()
+    assert it.next()
+    b = it.value()
+    for row in range(4):                                       # pixel level = 60 * label + 20 (flat images survive JPEG)
+        assert abs(float(b.data[row].mean()) - (60 * float(b.label[row, 0]) + 20)) < 3
