@@ -158,7 +158,11 @@ def run_ours(args, rank, world, local):
         b = DataBatch()
         # the input pipeline delivers bf16 batches (`input_dtype = bf16` of the batch iterator): the model
         # computes in bf16, so rounding on the host instead of on the device halves the PCIe bytes
-        b.data = torch.randn((B, 3, 227, 227), generator=g).to(torch.bfloat16).pin_memory()
+        if args.input == "u8":
+            b.data = torch.randint(0, 256, (B, 3, 227, 227), generator=g, dtype=torch.uint8).pin_memory()
+            b.norm = ([104.0, 117.0, 123.0], 1.0 / 64)
+        else:
+            b.data = torch.randn((B, 3, 227, 227), generator=g).to(torch.bfloat16).pin_memory()
         b.label = torch.randint(0, 1000, (B, 1), generator=g).float().pin_memory()
         b.batch_size = B
         host.append(b)
@@ -166,6 +170,7 @@ def run_ours(args, rank, world, local):
     devb = DataBatch()
     devb.data = host[0].data.cuda(non_blocking=True)
     devb.label = host[0].label.cuda(non_blocking=True)
+    devb.norm = host[0].norm
     devb.batch_size = B
 
     def step_dev(i):
@@ -201,7 +206,8 @@ def run_ours(args, rank, world, local):
         "metric": METRIC, "value": B * args.steps / (ms / 1e3), "unit": "images/sec", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": args.scaling, "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
-        "config": {"model": "AlexNet (example/ImageNet/ImageNet.conf)", "global_batch": B, "input": "3x227x227 (bf16 NCHW batches from the iterator, fp32 labels)",
+        "config": {"model": "AlexNet (example/ImageNet/ImageNet.conf)", "global_batch": B,
+                   "input": "3x227x227 (%s NCHW batches from the iterator, fp32 labels)" % args.input,
                    "per_gpu_batch": hi - lo, "parallelism": "dp%d" % world, "updater": "sgd momentum 0.9 wd 5e-4",
                    "l2": "no flush: per-step working set (activations + im2col + 244 MB weights) far exceeds "
                          "the 126 MB L2; e2e rotates 3 distinct 79 MB (bf16) input batches",
@@ -282,6 +288,9 @@ def main():
                     help="strong (default, the reference's semantics): --batch is the global batch, split over the "
                          "GPUs; weak: --batch images per GPU, global batch = batch x GPUs (secondary series)")
     ap.add_argument("--extra", default="", help="extra config lines for the ours arm, ';' separated")
+    ap.add_argument("--input", default="bf16", choices=["bf16", "u8"],
+                    help="host batches of the end-to-end measurement: bf16 (default, normalised on the host) or u8 "
+                         "(raw pixels, normalised on the device: half the bf16 bytes over PCIe)")
     args = ap.parse_args()
     args.extra = args.extra.replace(";", "\n")
     args.warmup = max(args.warmup, 3)

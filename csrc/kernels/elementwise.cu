@@ -75,6 +75,35 @@ __global__ void nchw_to_nhwc4_pitched_kernel(const TS* __restrict__ src, bf16* _
     *reinterpret_cast<uint4*>(dst + i * 8) = o;
   }
 }
+// The same from raw 8-bit pixels (a data pipeline that ships a quarter of the fp32 bytes over PCIe): the
+// normalisation the host would have done, (pixel - mean[c]) * scale in fp32, happens here before the bf16
+// rounding, so the result is bit-identical to a bf16 batch prepared on the host.  Pad pixels stay zero.
+__global__ void nchw_u8_to_nhwc4_pitched_kernel(const uint8_t* __restrict__ src, bf16* __restrict__ dst, long long total,
+                                                int C, int H, int W, int Wp, float m0, float m1, float m2, float m3,
+                                                float scale) {
+  const int wp2 = Wp >> 1;
+  const float mean[4] = {m0, m1, m2, m3};
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / wp2;             // n * H + y
+    const int j = (int)(i - row * wp2);
+    const long long n = row / H;
+    const int y = (int)(row - n * H);
+    const uint8_t* s = src + (n * C * H + y) * (long long)W + 2 * j;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (c < C) {
+        if (2 * j < W) v[c] = ((float)s[(long long)c * H * W] - mean[c]) * scale;
+        if (2 * j + 1 < W) v[4 + c] = ((float)s[(long long)c * H * W + 1] - mean[c]) * scale;
+      }
+    uint4 o;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) h[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+    *reinterpret_cast<uint4*>(dst + i * 8) = o;
+  }
+}
 // src bf16 [N][HW][ldc] -> dst fp32 [N][C][HW]
 __global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ src, float* __restrict__ dst, int N, int C, int HW,
                                     int ldc) {
@@ -294,6 +323,17 @@ CXN_API int cxn_nchw_bf16_to_nhwc4_pitched(const void* src, void* dst, int N, in
   if (C > 4 || (Wp & 1) || Wp < W || (reinterpret_cast<uintptr_t>(dst) & 15)) return -1;
   const long long total = (long long)N * H * (Wp / 2);
   nchw_to_nhwc4_pitched_kernel<bf16><<<ew_grid(total, 256, 16), 256, 0, st>>>((const bf16*)src, (bf16*)dst, total, C, H, W, Wp);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+// ... and from 8-bit pixels with the input normalisation (pixel - mean[c]) * scale folded in
+CXN_API int cxn_nchw_u8_to_nhwc4_pitched(const void* src, void* dst, int N, int C, int H, int W, int Wp, float mean0,
+                                         float mean1, float mean2, float mean3, float scale, cudaStream_t st) {
+  if (N <= 0 || C <= 0 || H <= 0 || W <= 0) return 0;
+  if (C > 4 || (Wp & 1) || Wp < W || (reinterpret_cast<uintptr_t>(dst) & 15)) return -1;
+  const long long total = (long long)N * H * (Wp / 2);
+  nchw_u8_to_nhwc4_pitched_kernel<<<ew_grid(total, 256, 16), 256, 0, st>>>((const uint8_t*)src, (bf16*)dst, total, C, H, W,
+                                                                           Wp, mean0, mean1, mean2, mean3, scale);
   CXN_CHECK_LAUNCH();
   return 0;
 }

@@ -4,7 +4,8 @@
 // done for a whole batch in one call.  The caller (cxxnet_b200/io/iterators.py) draws the random decisions
 // in instance order - so results do not depend on the number of threads - and hands over encoded images;
 // each worker decodes one image (jpeg_decoder.cpp) and writes its crop, mean-subtracted, jittered, mirrored
-// and scaled, straight into that instance's slot of the (pinned) batch buffer, as fp32 or bf16.
+// and scaled, straight into that instance's slot of the (pinned) batch buffer, as fp32, bf16 (dst_bf16 = 1) or -
+// cropped and mirrored only, normalisation left to the device - 8-bit pixels (dst_bf16 = 2).
 //
 //   mean_mode 0: out = v * scale                                   (no mean configured)
 //             1: out = ((v - mean[c]) * contrast + illum) * scale  (mean_value: one number per channel)
@@ -64,6 +65,7 @@ CXNIO_CLONES static int AugmentOne(const float* src, int C, int sh, int sw, cons
   if (mean_mode == 3 && (mean_h != H || mean_w != W)) return -11;
   float* df = static_cast<float*>(dst);
   uint16_t* dh = static_cast<uint16_t*>(dst);
+  uint8_t* db = static_cast<uint8_t*>(dst);
   const float contrast = it.contrast, illum = it.illum;
   for (int c = 0; c < C; ++c) {
     for (int y = 0; y < H; ++y) {
@@ -79,7 +81,9 @@ CXNIO_CLONES static int AugmentOne(const float* src, int C, int sh, int sw, cons
         else if (mean_mode == 2) v = (v - mrow[xs]) * contrast + illum;
         else if (mean_mode == 3) v = (v - mrow[x]) * contrast + illum;
         v = v * scale;
-        if (dst_bf16) dh[o + x] = F32ToBf16(v); else df[o + x] = v;
+        if (dst_bf16 == 1) dh[o + x] = F32ToBf16(v);
+        else if (dst_bf16 == 2) db[o + x] = uint8_t(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v + 0.5f));   // raw pixels
+        else df[o + x] = v;
       }
     }
   }
@@ -136,7 +140,7 @@ int cxnio_decode_augment_batch(const CxnioAugItem* items, int n, int C, int H, i
   if (n <= 0) return 0;
   if (nthreads < 1) nthreads = 1;
   if (nthreads > n) nthreads = n;
-  const size_t inst = size_t(C) * H * W * (dst_bf16 ? 2 : 4);
+  const size_t inst = size_t(C) * H * W * (dst_bf16 == 1 ? 2 : dst_bf16 == 2 ? 1 : 4);
   std::atomic<int> next{0};
   auto work = [&]() {
     std::vector<float> tmp, win;

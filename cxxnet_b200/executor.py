@@ -68,6 +68,9 @@ class NeuralNet:
         self.exchange = None
         self.need_update = True
         self.accumulate_grads = False
+        # (per-channel means, scale) of 8-bit input batches: x = (pixel - mean[c]) * scale, applied where the batch
+        # enters the net (DataBatch.norm, set by the batch iterator); None = pixels are used as they are
+        self.input_norm = None
         self.num_sms = 148
         self.step_counter = None
         self.in_stage = None
@@ -335,6 +338,7 @@ class NeuralNet:
         # bf16 batches (a data pipeline that ships half the bytes over PCIe) get their own pair of slots,
         # allocated when the first one arrives
         self.in_stage_bf16 = None
+        self.in_stage_u8 = None       # 8-bit batches (`input_dtype = u8`): normalised on the device, see input_norm
         self.stage_dtype = [torch.float32, torch.float32]
         self.hyper_prepared = False
         self.hyper_slot = 0
@@ -499,13 +503,25 @@ class NeuralNet:
             for c in self.connections:
                 c.layer.on_batch_size_changed(c.nodes_in, c.nodes_out)
 
+    def _norm(self, channels: int):
+        """(means per channel, scale) for an 8-bit batch"""
+        if self.input_norm is None:
+            return [0.0] * channels, 1.0
+        mean, scale = self.input_norm
+        mean = [float(v) for v in mean][:channels]
+        return mean + [0.0] * (channels - len(mean)), float(scale)
+
     def set_input(self, batch: torch.Tensor, extra: Optional[List[torch.Tensor]] = None) -> None:
         """copy one (already device-sliced) host batch into node 0 (+ extra data nodes)."""
         b = batch.shape[0]
         self.adjust_batch_size(b)
         extra = extra or []
         if self.backend == "ref":
-            self.nodes[0].data = batch.to(self.device, non_blocking=True).float().reshape(self.nodes[0].shape)
+            x = batch.to(self.device, non_blocking=True).float().reshape(self.nodes[0].shape)
+            if batch.dtype == torch.uint8:
+                mean, scale = self._norm(x.shape[1])
+                x = (x - torch.tensor(mean, dtype=torch.float32, device=self.device).view(1, -1, 1, 1)) * scale
+            self.nodes[0].data = x
             for i, e in enumerate(extra):
                 self.nodes[i + 1].data = e.to(self.device, non_blocking=True).float().reshape(self.nodes[i + 1].shape)
             return
@@ -528,6 +544,10 @@ class NeuralNet:
             if self.in_stage_bf16 is None:
                 self.in_stage_bf16 = [torch.zeros_like(t, dtype=torch.bfloat16) for t in self.in_stage]
             st = self.in_stage_bf16[slot][:b]
+        elif batch.dtype == torch.uint8:
+            if self.in_stage_u8 is None:
+                self.in_stage_u8 = [torch.zeros_like(t, dtype=torch.uint8) for t in self.in_stage]
+            st = self.in_stage_u8[slot][:b]
         else:
             st = self.in_stage[slot][:b]
         self.stage_dtype[slot] = st.dtype
@@ -545,6 +565,26 @@ class NeuralNet:
         """staging slot (fp32 NCHW) -> node 0 in the backend's layout"""
         n = self.nodes[0]
         b = n.shape[0]
+        if self.stage_dtype[slot] == torch.uint8:
+            src = self.in_stage_u8[slot][:b]
+            _, c, h, w = n.shape
+            mean, scale = self._norm(c)
+            if n.wpitch and not n.is_mat and hasattr(ops.lib(), "cxn_nchw_u8_to_nhwc4_pitched"):
+                m = list(mean) + [0.0] * (4 - len(mean))
+                ops.check(ops.lib().cxn_nchw_u8_to_nhwc4_pitched(src.data_ptr(), n.act.ptr, b, c, h, w, n.wpitch, m[0], m[1],
+                                                                 m[2], m[3], scale, ops.stream()),
+                          "nchw_u8_to_nhwc4_pitched")
+                return
+            # other layouts: widen and normalise on the device, then the fp32 path
+            f = self.in_stage[slot][:b]
+            f.copy_(src)
+            key = (tuple(mean), scale)
+            if getattr(self, "_norm_key", None) != key:       # device copy of the means, made once (not under capture)
+                self._norm_key = key
+                self._norm_mean = torch.tensor(mean, dtype=torch.float32, device=self.device).view(1, c, 1, 1)
+            f.sub_(self._norm_mean).mul_(scale)
+            self._convert_in(n, f)
+            return
         if self.stage_dtype[slot] == torch.bfloat16:
             src = self.in_stage_bf16[slot][:b]
             if n.wpitch and not n.is_mat:

@@ -41,6 +41,9 @@ class DataBatch:
         self.label: Optional[torch.Tensor] = None
         self.data: Optional[torch.Tensor] = None
         self.extra_data: List[torch.Tensor] = []
+        # 8-bit batches (`input_dtype = u8`): (per-channel means, scale) the net applies on entry,
+        # x = (pixel - mean[c]) * scale; None for float batches, which arrive normalised
+        self.norm = None
 
     def alloc_dense(self, shape, batch_size, label_width, pin=False, dtype=torch.float32):
         self.data = torch.zeros(tuple(shape), dtype=dtype)
@@ -60,6 +63,7 @@ class DataBatch:
             self.inst_index[:] = o.inst_index
         self.batch_size = o.batch_size
         self.num_batch_padd = o.num_batch_padd
+        self.norm = getattr(o, "norm", None)
         self.extra_data = [e.clone() for e in o.extra_data]
 
 

@@ -823,8 +823,8 @@ class BatchAdaptIterator(IIterator):
     def set_param(self, name, val):
         self.base.set_param(name, val)
         if name == "input_dtype":
-            if val not in ("fp32", "bf16"):
-                raise ValueError("input_dtype must be fp32 or bf16")
+            if val not in ("fp32", "bf16", "u8"):
+                raise ValueError("input_dtype must be fp32, bf16 or u8")
             self.input_dtype = val
         if name == "batch_size": self.batch_size = int(val)
         if name == "input_shape": self.shape = tuple(int(x) for x in val.split(","))
@@ -866,6 +866,22 @@ class BatchAdaptIterator(IIterator):
         self.out.alloc_dense((self.batch_size,) + tuple(self.shape), self.batch_size, self.label_width, pin=True)
         self._data_np = self.out.data.numpy()
         self._label_np = self.out.label.numpy()
+        self._u8 = None
+        if self.input_dtype == "u8":
+            # 8-bit batches: cropped / mirrored raw pixels cross PCIe (a quarter of the fp32 bytes), the net applies
+            # (pixel - mean[c]) * scale on entry (DataBatch.norm).  That is only the same thing when the rest of the
+            # augmentation is the identity on pixel values.
+            ok = (self._native and self.shape[0] == 3 and aug.mean_mode() in (0, 1) and not aug.aug.need_process()
+                  and aug.max_random_contrast == 0 and aug.max_random_illumination == 0)
+            if not ok:
+                raise ValueError("input_dtype = u8 needs the native batch path (img / imgbin source, 3 channels), "
+                                 "mean_value or no mean, and no contrast / illumination / affine augmentation")
+            self._u8 = DataBatch()
+            self._u8.alloc_dense((self.batch_size,) + tuple(self.shape), self.batch_size, self.label_width, pin=True,
+                                 dtype=torch.uint8)
+            mean = [aug.mean_b, aug.mean_g, aug.mean_r] if aug.mean_mode() == 1 else [0.0, 0.0, 0.0]
+            self._u8.norm = (mean, float(aug.scale))
+            self._u8.label, self._u8.inst_index = self.out.label, self.out.inst_index
         if self.input_dtype == "bf16":
             self._half = DataBatch()
             self._half.alloc_dense((self.batch_size,) + tuple(self.shape), self.batch_size, self.label_width, pin=True,
@@ -946,9 +962,12 @@ class BatchAdaptIterator(IIterator):
             mean = aug.meanimg
         to_half = self._half is not None
         dst = self._half.data if to_half else self.out.data
+        scale = aug.scale
+        if self._u8 is not None:                           # raw pixels: the net normalises them (DataBatch.norm)
+            dst, mode, mean, scale = self._u8.data, 0, None, 1.0
         first = tops[0]
         assert tops == list(range(first, first + len(items)))
-        status = native.decode_augment_batch(items, self.shape, mode, mean, aug.scale, dst[first:first + len(items)],
+        status = native.decode_augment_batch(items, self.shape, mode, mean, scale, dst[first:first + len(items)],
                                              to_half, self.decode_threads)
         for k, st in enumerate(status):
             if st != 0:                                    # e.g. a damaged file: the library decoders get a try
@@ -956,6 +975,12 @@ class BatchAdaptIterator(IIterator):
                 data = pixels if pixels is not None else _decode_image(blob, native_first=False)
                 if self.shape[0] == 1 and data.shape[0] == 3:
                     data = data.mean(axis=0, keepdims=True, dtype=np.float32)
+                if self._u8 is not None:
+                    y0, x0, flip = items[k][4:7]
+                    img = data[:, y0:y0 + self.shape[1], x0:x0 + self.shape[2]]
+                    img = img[:, :, ::-1] if flip else img
+                    dst[first + k].copy_(torch.from_numpy(np.ascontiguousarray(np.clip(img + 0.5, 0, 255.5)).astype(np.uint8)))
+                    continue
                 if items[k][9] is not None:
                     Ai, new_h, new_w, wy, wx, _ = items[k][9]
                     data = aug.aug.warp(data, (Ai, new_h, new_w, wy, wx, True))
@@ -992,6 +1017,10 @@ class BatchAdaptIterator(IIterator):
 
     def value(self):
         assert self.head == 0, "must call Next to get value"
+        if self._u8 is not None:
+            self._u8.batch_size, self._u8.num_batch_padd = self.out.batch_size, self.out.num_batch_padd
+            self._u8.extra_data = self.out.extra_data
+            return self._u8
         if self._half is not None and self._native:
             # the native path wrote bf16 straight into the pinned half-precision batch
             self._half.batch_size, self._half.num_batch_padd = self.out.batch_size, self.out.num_batch_padd

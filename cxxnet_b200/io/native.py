@@ -269,7 +269,10 @@ def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, 
             mode = 3
         groups.setdefault(mode, []).append(i)
     assert dst.is_contiguous() and tuple(dst.shape[1:]) == (c, H, W) and dst.shape[0] >= n
-    inst_bytes = c * H * W * (2 if dst_bf16 else 4)
+    import torch
+    kind = {torch.float32: 0, torch.bfloat16: 1, torch.uint8: 2}[dst.dtype]      # what the C side calls dst_bf16
+    assert kind == (1 if dst_bf16 else kind) and (kind != 2 or (mean_mode == 0 and scale == 1.0))
+    inst_bytes = c * H * W * dst.element_size()
     nthreads = nthreads or default_threads()
     for mode, idx in groups.items():
         # contiguous runs of instances that share a mode go down in one call
@@ -282,7 +285,7 @@ def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, 
             lib().cxnio_decode_augment_batch(
                 ctypes.addressof(arr) + i0 * ctypes.sizeof(AugItem), cnt, c, H, W, mode, mean_ptr,
                 mean_h if mode == 2 else H, mean_w if mode == 2 else W, scale,
-                dst.data_ptr() + i0 * inst_bytes, 1 if dst_bf16 else 0,
+                dst.data_ptr() + i0 * inst_bytes, kind,
                 ctypes.cast(ctypes.addressof(status) + 4 * i0, ctypes.POINTER(ctypes.c_int)), nthreads)
             run_start = run_end + 1
     return list(status)

@@ -72,6 +72,8 @@ def lib():
     _sig(L.cxn_conv_wgrad_masked, [P, I, I, I, I, I, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, I, I, I, P])
     _sig(L.cxn_nchw_f32_to_nhwc4_pitched, [P, P, I, I, I, I, I, P])
     _sig(L.cxn_nchw_bf16_to_nhwc4_pitched, [P, P, I, I, I, I, I, P])
+    if hasattr(L, "cxn_nchw_u8_to_nhwc4_pitched"):
+        _sig(L.cxn_nchw_u8_to_nhwc4_pitched, [P, P, I, I, I, I, I, F, F, F, F, F, P])
     _sig(L.cxn_conv_fprop_masked, [P, I, I, I, I, I, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, P, P])
     _sig(L.cxn_conv_fprop_view, [P, I, I, I, I, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, P, I, LL, LL, LL, P])
     _sig(L.cxn_conv_wgrad_view, [P, I, I, I, I, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, I, I, I, LL, LL, LL, P])

@@ -310,6 +310,7 @@ class NetTrainer:
         begin, end = self._slice(batch.batch_size)
         net.label_info.fields = self._label_fields(label, begin, end, self.device)
         net.accumulate_grads = self.sample_counter != 0
+        net.input_norm = getattr(batch, "norm", None)
         net.set_input(data[begin:end], [self._as_tensor(e)[begin:end] for e in batch.extra_data])
         net.forward(True)
         self._eval_train()
@@ -383,12 +384,14 @@ class NetTrainer:
             t.copy_(label[begin:end, a:b], non_blocking=True)
         net.label_info.fields = self._graph_labels
         net.accumulate_grads = False
+        net.input_norm = getattr(batch, "norm", None)
         slot = net.stage_input(data[begin:end])
         # host half of the per-step hyper parameters (rewrites the pinned table only when it changed)
         net.arena.prepare_hyper(self.epoch_counter, slot)
         net.hyper_prepared, net.hyper_slot = True, slot
         try:
-            gkey = (slot, net.stage_dtype[slot])
+            norm = net.input_norm       # baked into a captured conversion kernel's arguments
+            gkey = (slot, net.stage_dtype[slot], None if norm is None else (tuple(float(v) for v in norm[0]), float(norm[1])))
             entry = self._graphs.get(gkey)
             if entry is not None:
                 g, launches, cnt = entry
@@ -461,11 +464,13 @@ class NetTrainer:
                 part = DataBatch()
                 part.data = self._as_tensor(batch.data)[lo:hi]
                 part.extra_data = [self._as_tensor(e)[lo:hi] for e in batch.extra_data]
+                part.norm = getattr(batch, "norm", None)
                 part.batch_size = hi - lo
                 pieces.append(self._forward_to(node_ids, part))
             return [torch.cat([p[i] for p in pieces], dim=0) for i in range(len(node_ids))]
         data = self._as_tensor(batch.data)
         begin, end = self._slice(batch.batch_size)
+        net.input_norm = getattr(batch, "norm", None)
         net.set_input(data[begin:end], [self._as_tensor(e)[begin:end] for e in batch.extra_data])
         net.forward(False)
         outs = []

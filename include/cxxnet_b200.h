@@ -96,6 +96,10 @@ int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C, int HW,
 /* C <= 4 input image -> NHWC bf16 with pixel pitch 4 and an even row pitch Wp >= W (pad pixels zero) */
 int cxn_nchw_f32_to_nhwc4_pitched(const float* src, void* dst, int N, int C, int H, int W, int Wp, cudaStream_t stream);
 int cxn_nchw_bf16_to_nhwc4_pitched(const void* src, void* dst, int N, int C, int H, int W, int Wp, cudaStream_t stream);
+/* the same from 8-bit pixels, with the input normalisation (pixel - mean[c]) * scale applied in fp32 before the bf16
+ * rounding (`input_dtype = u8` batches; no reference counterpart) */
+int cxn_nchw_u8_to_nhwc4_pitched(const void* src, void* dst, int N, int C, int H, int W, int Wp, float mean0, float mean1,
+                                 float mean2, float mean3, float scale, cudaStream_t stream);
 int cxn_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int N, int C, int HW, int ldc, cudaStream_t stream);
 /* flatten in (c,h,w) order and its inverse.  Reference: src/layer/flatten_layer-inl.hpp:10-39. */
 int cxn_bf16_hwc_chw(const void* src, void* dst, int N, int C, int HW, long long src_img, long long dst_img,

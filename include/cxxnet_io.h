@@ -65,7 +65,8 @@ typedef struct CxnioAugItem {
   double ai[6];          /* inverse affine map, two rows: source x = ai[0] x + ai[1] y + ai[2], source y = ai[3..5] */
 } CxnioAugItem;
 /* mean_mode 0 none | 1 mean[c] per channel | 2 mean image of the decoded size (subtracted before crop / mirror) |
- * 3 mean image of the crop size (after).  dst: [n][C][H][W], fp32 or (dst_bf16 = 1) bf16.  status[i] = 0 when
+ * 3 mean image of the crop size (after).  dst: [n][C][H][W], fp32, (dst_bf16 = 1) bf16 or (dst_bf16 = 2) uint8 - the
+ * last for mean_mode 0 / scale 1 only: cropped and mirrored raw pixels.  status[i] = 0 when
  * instance i was written.  Returns the number of instances that were not. */
 int cxnio_decode_augment_batch(const CxnioAugItem* items, int n, int C, int H, int W, int mean_mode, const float* mean,
                                int mean_h, int mean_w, float scale, void* dst, int dst_bf16, int* status, int nthreads);

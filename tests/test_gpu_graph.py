@@ -1,6 +1,8 @@
 """`cuda_graph = 1`: a training step captured into a CUDA graph must train exactly like the eager
 step (same kernels, same order), keep the train metric's device accumulator and host count going,
 and fall back to the eager path for a short last batch."""
+import os
+
 import pytest
 import torch
 
@@ -101,3 +103,39 @@ def test_bf16_batches_train_exactly_like_fp32_batches():
             wb, _ = b.net.get_weight(i, tag)
             assert rel_err(wa, wb) < 2e-2, "layer %d %s diverged" % (i, tag)
     assert a.train_metric.evals[0].cnt_inst == b.train_metric.evals[0].cnt_inst == 8 * 16
+
+
+@pytest.mark.skipif(os.environ.get("CXN_TEST_U8", "0") != "1",
+                    reason="8-bit input batches on the device: written without access to a GPU, opt-in with CXN_TEST_U8=1 "
+                           "until the path has run on hardware")
+def test_u8_batches_train_like_host_normalised_bf16_batches():
+    """`input_dtype = u8`: raw pixels cross PCIe and cxn_nchw_u8_to_nhwc4_pitched applies (pixel - mean) * scale before
+    the bf16 rounding, so the first layer sees the bits of a bf16 batch normalised on the host"""
+    a = make_trainer(CONF, cuda_graph=1)
+    b = make_trainer(CONF, cuda_graph=1)
+    copy_weights(a, b)
+    mean, scale = [100.0, 110.0, 120.0], 1.0 / 32
+    g = torch.Generator().manual_seed(5)
+    raws, halves = [], []
+    for s in range(3):
+        lab = make_batch((16, 3, 33, 33), seed=s, pin=True)
+        px = torch.randint(0, 256, (16, 3, 33, 33), generator=g, dtype=torch.uint8)
+        r = make_batch((16, 3, 33, 33), seed=s, pin=True)
+        r.data, r.label, r.norm = px.pin_memory(), lab.label, (mean, scale)
+        h = make_batch((16, 3, 33, 33), seed=s, pin=True)
+        h.data = ((px.float() - torch.tensor(mean).view(1, 3, 1, 1)) * scale).to(torch.bfloat16).pin_memory()
+        h.label = lab.label
+        raws.append(r)
+        halves.append(h)
+    for i in range(8):
+        a.update(halves[i % 3])
+        b.update(raws[i % 3])
+    torch.cuda.synchronize()
+    assert b.net.in_stage_u8 is not None and len(b._graphs) == 2
+    for i, c in enumerate(a.net.connections):
+        for tag, _, _ in c.layer.weights():
+            wa, _ = a.net.get_weight(i, tag)
+            wb, _ = b.net.get_weight(i, tag)
+            assert rel_err(wa, wb) < 2e-2, "layer %d %s diverged" % (i, tag)
+    # prediction takes the same route
+    assert (a.predict(halves[0]) == b.predict(raws[0])).all()

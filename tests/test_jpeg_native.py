@@ -516,3 +516,65 @@ def test_png_interlaced_or_damaged_falls_back():
     out = native.image_decode(bytes(flipped))
     assert out is None or out.shape == (3, 10, 20)                   # zlib / filter damage is reported, never a crash
     assert np.array_equal(_decode_image(good), np.asarray(_picture(20, 10)).transpose(2, 0, 1).astype(np.float32))
+
+
+def test_u8_batches_carry_raw_pixels_and_their_normalisation(tmp_path):
+    """input_dtype = u8: cropped / mirrored 8-bit pixels plus DataBatch.norm; (pixel - mean) * scale reproduces the
+    fp32 batch exactly, through a thread buffer too; configurations whose augmentation changes pixel values are
+    refused; the CPU backend trains to the same weights from either kind of batch"""
+    import torch
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.io.data import create_iterator
+    _jpeg_bin(tmp_path, n=10)
+    base = ('iter = imgbin\n image_list = "%s"\n image_bin = "%s"\n batch_size = 4\n input_shape = 3,24,26\n rand_crop = 1\n'
+            ' rand_mirror = 1\n mean_value = 100,110,120\n divideby = 32\n round_batch = 1\n seed_data = 2\n silent = 1\n'
+            % (tmp_path / "j.lst", tmp_path / "j.bin"))
+
+    def batches(extra):
+        it = create_iterator(parse_config_string(base + extra + "iter = threadbuffer\n silent = 1\niter = end\n"))
+        it.init()
+        it.before_first()
+        out = []
+        while it.next():
+            b = it.value()
+            out.append((b.data.clone(), b.norm, b.label.clone()))
+        it.close()
+        return out
+    f32, u8 = batches(""), batches(" input_dtype = u8\n")
+    assert len(f32) == len(u8) == 3
+    for (d0, n0, l0), (d1, n1, l1) in zip(f32, u8):
+        assert n0 is None and d1.dtype == torch.uint8 and torch.equal(l0, l1)
+        mean, scale = n1
+        assert mean == [100.0, 110.0, 120.0] and scale == 1.0 / 32
+        assert torch.equal((d1.float() - torch.tensor(mean).view(1, 3, 1, 1)) * scale, d0)
+    with pytest.raises(ValueError, match="u8"):
+        create_iterator(parse_config_string(base + " input_dtype = u8\n max_random_contrast = 0.2\niter = end\n")).init()
+
+    # the reference-math backend trains identically from 8-bit and from float batches
+    sys_path = __import__("os").path.join(__import__("os").path.dirname(__file__))
+    __import__("sys").path.insert(0, sys_path)
+    from util import make_trainer
+    conf = """
+netconfig=start
+layer[+1] = flatten
+layer[+1] = fullc:fc
+  nhidden = 5
+  init_sigma = 0.01
+layer[+0] = softmax
+netconfig=end
+input_shape = 3,24,26
+batch_size = 4
+dev = cpu
+eta = 0.01
+metric = error
+"""
+    ta, tb = make_trainer(conf), make_trainer(conf)
+    tb.set_weight(ta.get_weight("fc", "wmat")[0], "fc", "wmat")
+    for kind, tr in (("", ta), (" input_dtype = u8\n", tb)):
+        it = create_iterator(parse_config_string(base + kind + "iter = end\n"))
+        it.init()
+        it.before_first()
+        while it.next():
+            tr.update(it.value())
+        it.close()
+    assert np.array_equal(ta.get_weight("fc", "wmat")[0], tb.get_weight("fc", "wmat")[0])

@@ -8,6 +8,7 @@
 # Opt-in experiments that have not yet run on hardware (each under its own timeout, failures do not stop the rest):
 #   CXN_TEST_CLUSTER=1      CTA-pair cluster convolution (tests/test_gpu_conv.py)
 #   CXN_TEST_COLLECTIVE=1   torch.distributed exchange on GPUs (tests/test_gpu_multi.py, needs 2 GPUs)
+#   CXN_TEST_U8=1           8-bit input batches normalised on the device (tests/test_gpu_graph.py)
 set -u
 N=${1:-1}
 OUT=gpurun_out
@@ -21,6 +22,9 @@ echo "pytest exit $?"; tail -3 $OUT/pytest_gpu.log
 echo "== opt-in experiments"
 CXN_TEST_CLUSTER=1 timeout 300 python -m pytest tests/test_gpu_conv.py -q -k cluster > $OUT/pytest_cluster.log 2>&1
 echo "cluster conv exit $?"; tail -3 $OUT/pytest_cluster.log
+CXN_TEST_U8=1 timeout 300 python -m pytest tests/test_gpu_graph.py -q -k u8 > $OUT/pytest_u8.log 2>&1
+echo "u8 input batches exit $?"; tail -3 $OUT/pytest_u8.log
+timeout 300 python bench.py --input u8 --steps 20 --warmup 5 > $OUT/bench_u8.json 2>/dev/null && python -c "import json;d=json.load(open('$OUT/bench_u8.json'));print('u8 input: e2e', round(d['e2e']['value']), 'img/s, device', round(d['value']))"
 timeout 120 python bench/desc_probe.py > $OUT/desc_probe.txt 2>&1
 echo "descriptor probe exit $?"; tail -18 $OUT/desc_probe.txt
 if [ "$N" -ge 2 ]; then
