@@ -51,7 +51,7 @@ static inline uint16_t F32ToBf16(float f) {
   return uint16_t(u >> 16);
 }
 
-#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__)
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__) && !defined(CXNIO_NO_CLONES)
 #define CXNIO_CLONES __attribute__((target_clones("avx2", "default")))
 #else
 #define CXNIO_CLONES

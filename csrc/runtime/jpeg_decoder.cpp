@@ -133,7 +133,7 @@ static const float kAanScale[8] = {1.0f, 1.387039845f, 1.306562965f, 1.175875602
                                    0.275899379f};
 
 // Hot loops are compiled twice (AVX2 and baseline x86-64) and chosen at load time.
-#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__)
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__) && !defined(CXNIO_NO_CLONES)
 #define CXNIO_CLONES __attribute__((target_clones("avx2", "default")))
 #else
 #define CXNIO_CLONES

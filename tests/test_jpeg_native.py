@@ -578,3 +578,28 @@ metric = error
             tr.update(it.value())
         it.close()
     assert np.array_equal(ta.get_weight("fc", "wmat")[0], tb.get_weight("fc", "wmat")[0])
+
+
+def test_pipeline_threads_are_race_free_under_thread_sanitizer(tmp_path):
+    """tools/io_tsan.cpp built with -fsanitize=thread: page reader thread (record and page interfaces, rewind in
+    mid-page) and concurrent batch calls with their worker threads"""
+    import os
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cxx = shutil.which("g++")
+    if cxx is None:
+        pytest.skip("no g++")
+    exe = tmp_path / "io_tsan"
+    srcs = [os.path.join(root, "tools", "io_tsan.cpp")] + [os.path.join(root, "csrc", "runtime", f) for f in
+            ("page_reader.cpp", "jpeg_decoder.cpp", "png_decoder.cpp", "raw_image.cpp", "batch_pipeline.cpp")]
+    r = subprocess.run([cxx, "-O1", "-g", "-std=c++17", "-fsanitize=thread", "-DCXNIO_NO_CLONES", "-pthread", "-o", str(exe)]
+                       + srcs + ["-lz"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    if r.returncode != 0 and "sanitize" in r.stdout:
+        pytest.skip("sanitizer runtime not available: " + r.stdout[-200:])
+    assert r.returncode == 0, r.stdout[-2000:]
+    r = subprocess.run([str(exe), str(tmp_path / "scratch.bin")], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                       timeout=600)
+    if r.returncode != 0 and "unexpected memory mapping" in r.stdout:
+        pytest.skip("thread sanitizer cannot map its shadow memory on this kernel")
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout[-3000:]
