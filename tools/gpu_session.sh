@@ -21,7 +21,13 @@ echo "pytest exit $?"; tail -3 $OUT/pytest_gpu.log
 
 echo "== opt-in experiments"
 CXN_TEST_CLUSTER=1 timeout 300 python -m pytest tests/test_gpu_conv.py -q -k cluster > $OUT/pytest_cluster.log 2>&1
-echo "cluster conv exit $?"; tail -3 $OUT/pytest_cluster.log
+rc_cluster=$?
+echo "cluster conv exit $rc_cluster"; tail -3 $OUT/pytest_cluster.log
+if [ $rc_cluster -eq 0 ]; then
+  CXN_CONV_CLUSTER=2 timeout 300 python bench.py --steps 20 --warmup 5 > $OUT/bench_cluster.json 2>/dev/null && \
+    python -c "import json;d=json.load(open('$OUT/bench_cluster.json'));print('CXN_CONV_CLUSTER=2:', round(d['value']), 'img/s', round(d['ms_per_step'],4), 'ms')"
+  EXTRA=1 WHICH=fprop timeout 600 python bench/conv_sweep.py > $OUT/conv_sweep_extra.txt 2>&1; tail -12 $OUT/conv_sweep_extra.txt
+fi
 CXN_TEST_U8=1 timeout 300 python -m pytest tests/test_gpu_graph.py -q -k u8 > $OUT/pytest_u8.log 2>&1
 echo "u8 input batches exit $?"; tail -3 $OUT/pytest_u8.log
 timeout 300 python bench.py --input u8 --steps 20 --warmup 5 > $OUT/bench_u8.json 2>/dev/null && python -c "import json;d=json.load(open('$OUT/bench_u8.json'));print('u8 input: e2e', round(d['e2e']['value']), 'img/s, device', round(d['value']))"
