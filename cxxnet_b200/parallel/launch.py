@@ -31,11 +31,39 @@ def relaunch_per_device(argv: List[str], devs: List[int]) -> int:
         env.update({"RANK": str(r), "LOCAL_RANK": str(r), "WORLD_SIZE": str(n), "LOCAL_WORLD_SIZE": str(n),
                     "MASTER_ADDR": "127.0.0.1", "MASTER_PORT": str(port)})
         procs.append(subprocess.Popen([sys.executable, "-m", "cxxnet_b200"] + list(argv), env=env))
-    rc = 0
-    for p in procs:
-        p.wait()
-        rc = rc or p.returncode
-    return rc
+    return wait_all(procs)
+
+
+def wait_all(procs, poll_seconds: float = 0.2, grace_seconds: float = 5.0) -> int:
+    """Wait for the ranks.  When one of them fails, the others - which would otherwise sit in a collective or in
+    the exchange kernel's bounded wait until a timeout - are stopped (the processes this launcher started, by PID):
+    the job ends promptly with the failing rank's exit code.  The reference has no failure handling at all
+    (errors call exit(-1) in the failing thread's process)."""
+    import time
+    failed = 0
+    pending = list(procs)
+    while pending and not failed:
+        for p in list(pending):
+            rc = p.poll()
+            if rc is None:
+                continue
+            pending.remove(p)
+            if rc != 0:
+                failed = rc
+                break
+        if pending and not failed:
+            time.sleep(poll_seconds)
+    if failed:
+        for p in pending:
+            p.terminate()
+        deadline = time.time() + grace_seconds
+        for p in pending:
+            try:
+                p.wait(timeout=max(0.1, deadline - time.time()))
+            except subprocess.TimeoutExpired:
+                p.kill()
+                p.wait()
+    return failed
 
 
 def main() -> int:

@@ -149,3 +149,18 @@ silent = 1
     a = np.frombuffer((tmp_path / "m1" / "0002.model").read_bytes()[-1500 * 4:], dtype=np.float32)
     b = np.frombuffer((tmp_path / "m2" / "0002.model").read_bytes()[-1500 * 4:], dtype=np.float32)
     assert np.abs(a - b).max() < 1e-5
+
+
+def test_launcher_stops_the_other_ranks_when_one_fails(tmp_path):
+    """parallel/launch.py wait_all: a failing rank ends the job promptly with its exit code instead of leaving the
+    others waiting"""
+    import time
+    from cxxnet_b200.parallel.launch import wait_all
+    sleeper = subprocess.Popen([sys.executable, "-c", "import time; time.sleep(120)"])
+    failing = subprocess.Popen([sys.executable, "-c", "import sys, time; time.sleep(0.5); sys.exit(7)"])
+    t0 = time.time()
+    rc = wait_all([sleeper, failing], grace_seconds=3.0)
+    assert rc == 7 and time.time() - t0 < 30
+    assert sleeper.poll() is not None                       # stopped by the launcher
+    ok = [subprocess.Popen([sys.executable, "-c", "pass"]) for _ in range(3)]
+    assert wait_all(ok) == 0
