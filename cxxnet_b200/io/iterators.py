@@ -814,6 +814,7 @@ class BatchAdaptIterator(IIterator):
         self.out = DataBatch()
         self.input_dtype = "fp32"     # bf16: batches leave the iterator as bf16 (half the H2D bytes; the b200
         self._half = None             # backend computes in bf16 anyway).  Not a reference option.
+        self._u8 = None               # u8: raw pixels + DataBatch.norm, normalised where the batch enters the net
         self.native_pipeline = 1      # decode + augment + batch assembly on native threads where applicable
         self.decode_threads = 0       # 0 = min(8, cores)
         self._native = False
