@@ -111,3 +111,32 @@ def test_make_image_list_resizes_splits_and_packs(tmp_path):
     b = it.value()
     for row in range(4):                                       # pixel level = 60 * label + 20 (flat images survive JPEG)
         assert abs(float(b.data[row].mean()) - (60 * float(b.label[row, 0]) + 20)) < 3
+
+
+def test_check_conf_knows_every_documented_key_and_flags_typos(tmp_path):
+    """python -m cxxnet_b200.tools.check_conf: the shipped examples are clean, every key of the user guide's tables is
+    known to it, misspelt keys are reported with a suggestion"""
+    import re
+    from cxxnet_b200.config import parse_config_file
+    from cxxnet_b200.tools import check_conf
+    for path in CONFS:
+        assert check_conf.check(list(parse_config_file(path))) == [], path
+    documented = set()
+    for md in glob.glob(os.path.join(ROOT, "doc", "*.md")):
+        in_key_table = False
+        for line in open(md):
+            if not line.startswith("|"):
+                in_key_table = False
+            elif line.startswith("| Key"):
+                in_key_table = True
+            elif in_key_table:
+                documented.update(re.findall(r"`([a-z_:0-9@]+)`", line.split("|")[1]))
+    assert len(documented) > 50
+    unknown = sorted(k for k in documented if not check_conf.known(k) and k not in ("fp32", "bf16", "u8"))
+    assert unknown == [], unknown
+    bad = tmp_path / "bad.conf"
+    bad.write_text("slient = 1\ntrain_eval = 3\nlayer[+1] = fullc:fc\n  nhiden = 3\nwmat:lr = 0.1\n")
+    found = check_conf.check(list(parse_config_file(str(bad))))
+    assert [(f[0], f[3]) for f in found] == [("slient", "silent"), ("train_eval", "eval_train"), ("nhiden", "nhidden")]
+    assert found[2][2].startswith("layer[+1]")
+    assert check_conf.main([str(bad)]) == 1
