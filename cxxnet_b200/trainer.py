@@ -81,6 +81,7 @@ class NetTrainer:
         # then only stages the batch and launches one graph per step
         self.cuda_graph = 0
         self.test_on_server = 0
+        self.check_nan = 0
         self.layer_timing = 0
         self.graph_warmup = 3
         self._graphs = {}            # staging slot -> (torch.cuda.CUDAGraph, launches inside)
@@ -105,6 +106,9 @@ class NetTrainer:
         # round.  Here: every round all ranks compare their replicas with rank 0's (collective).
         if name == "test_on_server": self.test_on_server = int(val)
         if name == "layer_timing": self.layer_timing = int(val)     # per-layer timers, see utils/timing.py
+        # check_nan = 1: every round starts with a look at the weights; a NaN / Inf stops the run and names the
+        # layer (the reference only notices inside the logloss metric, src/utils/metric.h:128)
+        if name == "check_nan": self.check_nan = int(val)
         # Parameter-server tuning keys of the reference (async_updater-inl.hpp:155-184, fullc_layer-inl.hpp) that
         # have nothing to act on here - there is no server, pulls are not deferred, arrays are not chunked by
         # the transport: accepted and ignored, like every key a consumer does not know.
@@ -258,8 +262,33 @@ class NetTrainer:
                     buf.seek(0)
                     self.net.copy_layer(j, buf)
 
+    def find_non_finite(self):
+        """(layer name, tag) of the first weight tensor holding a NaN or an infinity, else None"""
+        net = self.net
+        if net.backend == "b200" and net.arena is not None:
+            if net.exchange is not None:
+                net.exchange.wait_all()
+            if bool(torch.isfinite(net.arena.w[:max(net.arena.total, 1)]).all()):
+                return None
+            for s in net.arena.segments:
+                if not bool(torch.isfinite(net.arena.w_view(s)).all()):
+                    return self.net_cfg.layers[s.layer_index].name or str(s.layer_index), s.tag
+            return None
+        for i, c in enumerate(net.connections):
+            if c.type == 0:          # shared layer: its weights belong to the primary
+                continue
+            for tag, w, _ in c.layer.weights():
+                if not bool(torch.isfinite(w).all()):
+                    return self.net_cfg.layers[i].name or str(i), tag
+        return None
+
     def start_round(self, r: int) -> None:
         self.net.start_round(r)
+        if self.check_nan:
+            bad = self.find_non_finite()
+            if bad is not None:
+                raise RuntimeError("check_nan: non-finite weights in layer %s (%s) at the start of round %d - lower the "
+                                   "learning rate or set clip_gradient" % (bad[0], bad[1], r))
         ex = getattr(self.net, "exchange", None)
         if self.test_on_server and ex is not None:
             d = ex.check_replicas()

@@ -249,3 +249,24 @@ def test_finetune_and_model_info_on_a_net_with_weightless_layers(tmp_path):
     assert info.returncode == 0, info.stdout
     assert "input 1x28x28" in info.stdout and "MaxPooling" in info.stdout and "wmat  (1, 4, 9)" in info.stdout
     assert "parameters: %d" % (4 * 9 + 4 + 10 * 4 * 6 * 6 + 10) in info.stdout
+
+
+def test_check_nan_names_the_layer():
+    from cxxnet_b200.trainer import NetTrainer
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.models import mlp_conf
+    tr = NetTrainer()
+    for k, v in parse_config_string(mlp_conf(dev="cpu", batch_size=10)):
+        tr.set_param(k, v)
+    tr.set_param("check_nan", "1")
+    tr.set_param("silent", "1")
+    tr.init_model()
+    tr.start_round(1)                                         # fine
+    assert tr.find_non_finite() is None
+    w, _ = tr.get_weight("fc2", "wmat")
+    w = w.copy()
+    w.reshape(-1)[3] = float("nan")
+    tr.set_weight(w, "fc2", "wmat")
+    assert tr.find_non_finite() == ("fc2", "wmat")
+    with pytest.raises(RuntimeError, match="fc2"):
+        tr.start_round(2)
