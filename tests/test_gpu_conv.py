@@ -118,9 +118,6 @@ def test_conv_im2col_tma_and_gather_routes_agree_with_reference(atma):
         L.cxn_conv_tune(6, -1)
 
 
-@pytest.mark.skipif(os.environ.get("CXN_TEST_CLUSTER", "0") != "1",
-                    reason="CTA-pair cluster route (multicast filter tile): written without access to a GPU, "
-                           "opt-in with CXN_TEST_CLUSTER=1 until it has been run on hardware")
 def test_conv_cluster_pairs_share_the_filter_tile():
     """cxn_conv_tune(7, 2): forward layers on the im2col-TMA route run as clusters of two CTAs that fetch half of
     the filter tile each and multicast it to both.  Odd and even tile counts, groups, two tile widths, the

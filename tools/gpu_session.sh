@@ -6,9 +6,7 @@
 #   gpurun --gpus 2 --timeout 1500 -- 'bash tools/gpu_session.sh 2'  # also the 2-GPU tests and bench
 # Everything lands in gpurun_out/ (scratch); copy what should be judged into profiles/.
 # Opt-in experiments that have not yet run on hardware (each under its own timeout, failures do not stop the rest):
-#   CXN_TEST_CLUSTER=1      CTA-pair cluster convolution (tests/test_gpu_conv.py)
 #   CXN_TEST_COLLECTIVE=1   torch.distributed exchange on GPUs (tests/test_gpu_multi.py, needs 2 GPUs)
-#   CXN_TEST_U8=1           8-bit input batches normalised on the device (tests/test_gpu_graph.py)
 set -u
 N=${1:-1}
 OUT=gpurun_out
@@ -20,7 +18,7 @@ timeout 1200 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1
 echo "pytest exit $?"; tail -3 $OUT/pytest_gpu.log
 
 echo "== opt-in experiments"
-CXN_TEST_CLUSTER=1 timeout 300 python -m pytest tests/test_gpu_conv.py -q -k cluster > $OUT/pytest_cluster.log 2>&1
+timeout 300 python -m pytest tests/test_gpu_conv.py -q -k cluster > $OUT/pytest_cluster.log 2>&1
 rc_cluster=$?
 echo "cluster conv exit $rc_cluster"; tail -3 $OUT/pytest_cluster.log
 if [ $rc_cluster -eq 0 ]; then
@@ -28,7 +26,7 @@ if [ $rc_cluster -eq 0 ]; then
     python -c "import json;d=json.load(open('$OUT/bench_cluster.json'));print('CXN_CONV_CLUSTER=2:', round(d['value']), 'img/s', round(d['ms_per_step'],4), 'ms')"
   EXTRA=1 WHICH=fprop timeout 600 python bench/conv_sweep.py > $OUT/conv_sweep_extra.txt 2>&1; tail -12 $OUT/conv_sweep_extra.txt
 fi
-CXN_TEST_U8=1 timeout 300 python -m pytest tests/test_gpu_graph.py -q -k u8 > $OUT/pytest_u8.log 2>&1
+timeout 300 python -m pytest tests/test_gpu_graph.py -q -k u8 > $OUT/pytest_u8.log 2>&1
 echo "u8 input batches exit $?"; tail -3 $OUT/pytest_u8.log
 timeout 300 python bench.py --input u8 --steps 20 --warmup 5 > $OUT/bench_u8.json 2>/dev/null && python -c "import json;d=json.load(open('$OUT/bench_u8.json'));print('u8 input: e2e', round(d['e2e']['value']), 'img/s, device', round(d['value']))"
 timeout 120 python bench/desc_probe.py > $OUT/desc_probe.txt 2>&1
