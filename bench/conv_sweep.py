@@ -29,7 +29,9 @@ CONFIGS = [("gather 128-row", dict(atma=0, mh=1, stages=-1)),
            # opt-in routes (EXTRA=1): CTA pairs sharing the filter tile by multicast; narrower tiles for small grids
            ("auto + cluster", dict(atma=-1, mh=0, stages=0, cluster=2, extra=1)),
            ("tma 128-row + cluster", dict(atma=1, mh=1, stages=-1, cluster=2, extra=1)),
-           ("auto + fill", dict(atma=-1, mh=0, stages=0, fill=1, extra=1))]
+           ("auto + fill", dict(atma=-1, mh=0, stages=0, fill=1, extra=1)),
+           ("halo 2 halves", dict(atma=-1, mh=0, stages=0, halo=1, extra=1)),
+           ("halo 1 half", dict(atma=-1, mh=0, stages=0, halo=2, extra=1))]
 if os.environ.get("EXTRA", "0") != "1":
     CONFIGS = [c for c in CONFIGS if not c[1].get("extra")]
 WCONFIGS = [("gather", dict(atma=0)), ("tma", dict(atma=1))]
@@ -46,6 +48,7 @@ def set_knobs(c, ocg):
     L.cxn_conv_tune(6, c.get("atma", -1))
     L.cxn_conv_tune(7, c.get("cluster", 0))
     L.cxn_conv_tune(8, c.get("fill", 0))
+    L.cxn_conv_tune(9, c.get("halo", 0))
 
 
 def reset_knobs():
@@ -53,6 +56,7 @@ def reset_knobs():
         L.cxn_conv_tune(k_, 0 if k_ in (0, 1, 4, 5) else -1)
     L.cxn_conv_tune(7, 0)
     L.cxn_conv_tune(8, 0)
+    L.cxn_conv_tune(9, 0)
 
 
 def timeit(run, iters=10):

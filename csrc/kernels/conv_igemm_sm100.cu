@@ -914,6 +914,267 @@ conv_fprop_cluster_kernel(const __grid_constant__ CUtensorMap tmHalf, const __gr
   }
 }
 
+// ===================================================================================================
+// Halo-tile variant of the forward kernel for stride-1 convolutions with few output columns (opt-in:
+// cxn_conv_tune(9, 1) or CXN_CONV_HALO=1; built for conv2's backward-data problem: 5x5, 128 -> 48 channels).
+// The im2col routes fetch every input element once per filter tap.  Here the GEMM rows enumerate the output over the
+// PADDED-width grid (Wp = W + 2 pad_x columns per output row), where tap (kh, kw) is a constant shift of kh Wp + kw
+// pixels: one tiled TMA load brings the patch of a tile - (rows + KH - 1) x Wp pixels x 64 channels, zero-filled
+// outside the image - and every tap reads it through a descriptor whose start address is moved by that many
+// 128-byte rows (a 128B-swizzled operand may start at any row: profiles/r1_desc_probe.txt).  A tile is MH halves of
+// R = 128 / Wp output rows; the Wp - OW junk columns and the rows past the image are computed and not stored.
+// Patch traffic drops by KH KW at the price of Wp / OW more tensor work; the filter tiles stream through their own
+// ring, one {64 x bn} tile per (tap, 64-channel chunk).
+//
+// warps: 0 TMA producer | 1 MMA issuer + TMEM owner | 2-5 epilogue.
+struct HaloGeom {
+  int wp;        // padded width = GEMM rows per output row
+  int rows_half; // output rows per 128-row half
+  int tiles_img; // tiles per image
+  int patch_h;   // input rows of one patch: MH * rows_half + KH - 1
+  int a_stage_bytes, na, nb;   // patch stage size (1024-aligned), patch ring depth, filter ring depth
+};
+
+constexpr int kHaloThreads = 192;
+constexpr int kHaloBN = 64;          // accumulator columns per half (bn <= 64)
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2,
+                                            int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+template <int MH>
+__global__ void __launch_bounds__(kHaloThreads, 1)
+conv_fprop_halo_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_constant__ CUtensorMap tmTile,
+                       const Params p, const HaloGeom hg) {
+  constexpr int kAcc = 2;
+  constexpr int kTmemCols = kAcc * MH * kHaloBN;       // 128 or 256
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int na = hg.na, nb = hg.nb;
+  const uint32_t b_bytes = (uint32_t)p.bn * BK * 2;                 // one filter tile (bn % 8 == 0: 1024-aligned)
+  const uint32_t a_base = smem_base, b_base = smem_base + (uint32_t)na * hg.a_stage_bytes;
+  const uint32_t bar_base = b_base + (uint32_t)nb * ((b_bytes + 1023u) & ~1023u);
+  const uint32_t b_stride = (b_bytes + 1023u) & ~1023u;
+  auto fulla = [&](int s) { return bar_base + 8u * s; };
+  auto emptya = [&](int s) { return bar_base + 8u * (na + s); };
+  auto fullb = [&](int s) { return bar_base + 8u * (2 * na + s); };
+  auto emptyb = [&](int s) { return bar_base + 8u * (2 * na + nb + s); };
+  auto tfull = [&](int a) { return bar_base + 8u * (2 * na + 2 * nb + a); };
+  auto tempty = [&](int a) { return bar_base + 8u * (2 * na + 2 * nb + kAcc + a); };
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + (bar_base - smem_base) + 8 * (2 * na + 2 * nb + 2 * kAcc));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int cpk = p.Cg >> 6;                         // 64-channel chunks
+  const int taps = p.KH * p.KW;
+  const long long total_tiles = (long long)p.N * hg.tiles_img * p.G;
+  const int rows_tile = MH * hg.rows_half;           // output rows per tile
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < na; ++s) { mbar_init(fulla(s), 1); mbar_init(emptya(s), 1); }
+    for (int s = 0; s < nb; ++s) { mbar_init(fullb(s), 1); mbar_init(emptyb(s), 1); }
+    for (int a = 0; a < kAcc; ++a) { mbar_init(tfull(a), 1); mbar_init(tempty(a), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmDense) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmTile) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32((const void*)tmem_ptr_smem)),
+                 "n"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  auto decode_tile = [&](long long t, int& n, int& ti, int& g) {
+    ti = (int)(t % hg.tiles_img);
+    const long long r = t / hg.tiles_img;
+    n = (int)(r % p.N);
+    g = (int)(r / p.N);
+  };
+
+  if (warp == 0) {
+    // =========================== TMA producer ===========================
+    // items: (tile, chunk) pairs of this CTA in order; the patch of item q + 1 is requested before the filter
+    // tiles of item q, so that it is in flight while q's taps run
+    long long ntile_cta = 0;
+    for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) ++ntile_cta;
+    const long long items = ntile_cta * cpk;
+    int sb = 0;
+    uint32_t pb = 0;
+    auto issue_a = [&](long long q) {
+      const int s = (int)(q % na);
+      const uint32_t ph = (uint32_t)((q / na) & 1);
+      mbar_wait_warp(emptya(s), ph ^ 1u);
+      if (elect_one()) {
+        const long long t = blockIdx.x + (q / cpk) * (long long)gridDim.x;
+        const int chunk = (int)(q % cpk);
+        int n, ti, g;
+        decode_tile(t, n, ti, g);
+        mbar_expect_tx(fulla(s), (uint32_t)(64 * hg.wp * hg.patch_h * 2));
+        tma_load_4d(a_base + (uint32_t)s * hg.a_stage_bytes, &tmTile, fulla(s), g * p.Cg + chunk * 64, -p.pad_x,
+                    ti * rows_tile - p.pad_y, n);
+      }
+      __syncwarp();
+    };
+    if (items > 0) issue_a(0);
+    for (long long q = 0; q < items; ++q) {
+      if (q + 1 < items) issue_a(q + 1);
+      const long long t = blockIdx.x + (q / cpk) * (long long)gridDim.x;
+      const int chunk = (int)(q % cpk);
+      const int g = (int)(t / ((long long)hg.tiles_img * p.N));
+      for (int tap = 0; tap < taps; ++tap) {
+        mbar_wait_warp(emptyb(sb), pb ^ 1u);
+        if (elect_one()) {
+          mbar_expect_tx(fullb(sb), b_bytes);
+          tma_load_3d(b_base + (uint32_t)sb * b_stride, &tmDense, fullb(sb), tap * p.Cg + chunk * 64, 0, g);
+        }
+        __syncwarp();
+        if (++sb == nb) { sb = 0; pb ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA issuer ===========================
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+    const uint64_t desc_hi = make_desc(0, 0u, 1024u);
+    int sb = 0;
+    uint32_t pb = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    long long q = 0;
+    for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      mbar_wait_warp(tempty(acc), acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * MH * kHaloBN);
+      for (int chunk = 0; chunk < cpk; ++chunk, ++q) {
+        const int sa = (int)(q % na);
+        mbar_wait_warp(fulla(sa), (uint32_t)((q / na) & 1));
+        const uint32_t patch = a_base + (uint32_t)sa * hg.a_stage_bytes;
+        for (int tap = 0; tap < taps; ++tap) {
+          mbar_wait_warp(fullb(sb), pb);
+          tc_fence_after();
+          if (elect_one()) {
+            const int kh = tap / p.KW, kw = tap - kh * p.KW;
+            const uint32_t sbt = b_base + (uint32_t)sb * b_stride;
+            const uint64_t b0 = desc_hi | (uint64_t)((sbt >> 4) & 0x3FFF);
+#pragma unroll
+            for (int h = 0; h < MH; ++h) {
+              // rows of half h start (h R + kh) Wp + kw pixels into the patch; one pixel = one 128-byte row
+              const uint32_t sat = patch + (uint32_t)(((h * hg.rows_half + kh) * hg.wp + kw) * 128);
+              const uint64_t a0 = desc_hi | (uint64_t)((sat >> 4) & 0x3FFF);
+#pragma unroll
+              for (int k = 0; k < BK / UMMA_K; ++k)
+                umma_bf16(d_tmem + (uint32_t)(h * kHaloBN), a0 + (uint64_t)((k * UMMA_K * 2) >> 4),
+                          b0 + (uint64_t)((k * UMMA_K * 2) >> 4), idesc, (chunk > 0 || tap > 0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit(emptyb(sb));
+            if (tap == taps - 1) {
+              umma_commit(emptya(sa));
+              if (chunk == cpk - 1) umma_commit(tfull(acc));
+            }
+          }
+          __syncwarp();
+          if (++sb == nb) { sb = 0; pb ^= 1u; }
+        }
+      }
+      if (++acc == kAcc) { acc = 0; acc_phase ^= 1u; }
+    }
+  } else {
+    // =========================== epilogue ===========================
+    const int quad = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const int r = quad * 32 + lane;                 // GEMM row inside a half = position on the padded grid
+    const int orow = r / hg.wp, ow = r - orow * hg.wp;
+    for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      int n, ti, g;
+      decode_tile(t, n, ti, g);
+      mbar_wait_warp(tfull(acc), acc_phase);
+      tc_fence_after();
+      const float* bias = p.bias != nullptr ? p.bias + (long long)g * p.Ng : nullptr;
+#pragma unroll 1
+      for (int hc = 0; hc < MH * kHaloBN; hc += 32) {
+        const int h = hc / kHaloBN, c0 = hc - h * kHaloBN;
+        if (c0 >= p.bn || c0 >= p.Ng) continue;                        // warp-uniform
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * MH * kHaloBN + hc);
+        tmem_ld32(taddr, v);
+        tmem_ld_wait();
+        const int oh = ti * rows_tile + h * hg.rows_half + orow;
+        if (orow >= hg.rows_half || ow >= p.OW || oh >= p.OH) continue;   // junk column / row of the padded grid
+        const int lim = min(32, p.Ng - c0);
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        const long long row = ((long long)n * p.OH + oh) * p.OW + ow;
+        const long long off = (long long)g * p.strideD + row * p.ldd + c0;
+        if (bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < lim) f[j] += __ldg(bias + c0 + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+        }
+        if (p.mask != nullptr) {
+          const bf16* mk = p.mask + off;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < lim && !(__bfloat162float(mk[j]) > 0.0f)) f[j] = 0.0f;
+        }
+        bf16* d = reinterpret_cast<bf16*>(p.D) + off;
+        if ((reinterpret_cast<uintptr_t>(d) & 15) == 0 && (lim & 7) == 0) {
+          uint4* d4 = reinterpret_cast<uint4*>(d);
+#pragma unroll
+          for (int q8 = 0; q8 < 4; ++q8) {
+            if (q8 * 8 < lim) {
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(f[q8 * 8 + 0], f[q8 * 8 + 1]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(f[q8 * 8 + 2], f[q8 * 8 + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(f[q8 * 8 + 4], f[q8 * 8 + 5]);
+              __nv_bfloat162 h3 = __floats2bfloat162_rn(f[q8 * 8 + 6], f[q8 * 8 + 7]);
+              uint4 u;
+              u.x = *reinterpret_cast<uint32_t*>(&h0);
+              u.y = *reinterpret_cast<uint32_t*>(&h1);
+              u.z = *reinterpret_cast<uint32_t*>(&h2);
+              u.w = *reinterpret_cast<uint32_t*>(&h3);
+              d4[q8] = u;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < lim) d[j] = __float2bfloat16(f[j]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty(acc));
+      if (++acc == kAcc) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
+  }
+}
+
 // W[g][oc][kh][kw][ic] (ld_in) -> Wt[g][ic][KH-1-kh][KW-1-kw][oc] (ld_out): the filter of the equivalent
 // forward convolution that computes backward-data of a stride-1 convolution.  Per (group, tap) this is
 // the transpose of an ocg x icg block: 32 x 32 tiles through shared memory, both sides coalesced.
@@ -983,6 +1244,8 @@ static int g_tune_cluster = -1;    // 2: forward layers on the im2col-TMA route 
                                    // filter tile by multicast (conv_fprop_cluster_kernel); -1 = read CXN_CONV_CLUSTER
 static int g_tune_fill = -1;       // 1: forward layers with fewer tiles than SMs take narrower column tiles until
                                    // the grid fills the machine (small per-GPU batches); -1 = read CXN_CONV_FILL
+static int g_tune_halo = -1;       // 1: stride-1 forward problems with <= 64 output columns per group run as halo
+                                   // tiles (conv_fprop_halo_kernel); 2: the same with single-half tiles; -1 = CXN_CONV_HALO
 static long long* g_prof = nullptr;
 
 typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -1074,6 +1337,70 @@ static int launch_cluster(const CUtensorMap& tm_half, const CUtensorMap& tmp, co
     max_set = smem;
   }
   conv_fprop_cluster_kernel<BNMAX, MH><<<grid, kClusterThreads, smem, st>>>(tm_half, tmp, p);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+// NHWC tensor as a tiled 4-D map: box {64 channels, box_w pixels, box_h rows, 1 image}, zero fill outside
+static int encode_tile4d(CUtensorMap* out, const Params& p, int box_w, int box_h) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return -2;
+  if (box_w > 256 || box_h > 256 || box_w < 1 || box_h < 1) return -6;
+  cuuint64_t gdim[4] = {(cuuint64_t)p.Cs, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
+  cuuint64_t gstr[3] = {(cuuint64_t)p.Cs * 2, (cuuint64_t)p.W * p.Cs * 2, (cuuint64_t)p.H * p.W * p.Cs * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)box_w, (cuuint32_t)box_h, 1}, estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<bf16*>(p.src), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr, "[cxxnet_b200] cuTensorMapEncodeTiled (4-D) failed: %d\n", (int)r);
+    return -5;
+  }
+  return 0;
+}
+static int halo_mode() {
+  if (g_tune_halo < 0) {
+    const char* e = getenv("CXN_CONV_HALO");
+    g_tune_halo = e ? atoi(e) : 0;
+  }
+  return g_tune_halo;
+}
+// Does the problem fit the halo-tile kernel?  Fills the geometry for `mh` halves per tile.
+static bool halo_plan(const Params& p, int mh, HaloGeom* hg, int* smem_bytes) {
+  if (p.stride_x != 1 || p.stride_y != 1 || p.gran != 8 || p.Cg % 64 || p.view_cdim) return false;
+  if (p.KH * p.KW < 4 || p.Ng > kHaloBN || p.bn > kHaloBN || (p.bn & 7)) return false;
+  const int wp = p.W + 2 * p.pad_x;
+  if (wp > 128 || wp < p.OW + p.KW - 1 || p.OW != wp - p.KW + 1 || p.OH != p.H + 2 * p.pad_y - p.KH + 1) return false;
+  if ((reinterpret_cast<uintptr_t>(p.src) & 15) || (p.Cs % 8)) return false;
+  hg->wp = wp;
+  hg->rows_half = 128 / wp;
+  if (hg->rows_half < 1) return false;
+  const int rows_tile = mh * hg->rows_half;
+  hg->tiles_img = ceil_div(p.OH, rows_tile);
+  hg->patch_h = rows_tile + p.KH - 1;
+  if (hg->patch_h > 256) return false;
+  // pixels a descriptor may touch: the last half's last tap starts ((mh-1) R + KH-1) Wp + KW-1 rows in and spans 128
+  int pixels = ((mh - 1) * hg->rows_half + p.KH - 1) * wp + p.KW - 1 + 128;
+  if (pixels < wp * hg->patch_h) pixels = wp * hg->patch_h;
+  hg->a_stage_bytes = (pixels * 128 + 1023) & ~1023;
+  const int b_stride = (p.bn * BK * 2 + 1023) & ~1023;
+  const int budget = 232448 - 1024 - 512;
+  hg->nb = 8;
+  hg->na = (budget - hg->nb * b_stride) / hg->a_stage_bytes;
+  if (hg->na > 3) hg->na = 3;
+  if (hg->na < 2) return false;
+  *smem_bytes = hg->na * hg->a_stage_bytes + hg->nb * b_stride + 512 + 1024;
+  return true;
+}
+template <int MH>
+static int launch_halo(const CUtensorMap& tm, const CUtensorMap& tmt, const Params& p, const HaloGeom& hg, int smem, int grid,
+                       cudaStream_t st) {
+  static int max_set = 0;
+  if (smem > max_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_fprop_halo_kernel<MH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    max_set = smem;
+  }
+  conv_fprop_halo_kernel<MH><<<grid, kHaloThreads, smem, st>>>(tm, tmt, p, hg);
   CXN_CHECK_LAUNCH();
   return 0;
 }
@@ -1205,6 +1532,19 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
     rc = encode_im2col(&tmp, p, mh * BM);
     if (rc) return rc;
   }
+  if (halo_mode() > 0 && atma) {     // (takes precedence over the resident-filter variant when asked for)
+    HaloGeom hg;
+    int smem_h = 0;
+    const int hmh = halo_mode() == 2 ? 1 : 2;
+    if (halo_plan(p, hmh, &hg, &smem_h)) {
+      CUtensorMap tmt;
+      rc = encode_tile4d(&tmt, p, hg.wp, hg.patch_h);
+      if (rc) return rc;
+      const long long htiles = (long long)N * hg.tiles_img * G;
+      const int hgrid = (int)(htiles < num_sms() ? htiles : num_sms());
+      return hmh == 2 ? launch_halo<2>(tm, tmt, p, hg, smem_h, hgrid, st) : launch_halo<1>(tm, tmt, p, hg, smem_h, hgrid, st);
+    }
+  }
   const long long tiles_m = ceil_div_ll(rows, mh * BM);
   if (cluster_mode() == 2 && atma && !p.b_resident && tiles_m >= 2 && num_sms() >= 2) {
     // CTA pairs on two pixel tiles of the same output columns: each fetches half of the filter tile and
@@ -1226,6 +1566,7 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
 //   0: row halves per forward tile   1: ring stages   2: gather through L1   3: tap-inner order   4: tile-width class
 //   5: timing experiments   6: im2col TMA on / off   7: 2 = CTA-pair clusters with a multicast filter tile (forward)
 //   8: 1 = narrower column tiles when the forward grid would not fill the machine
+//   9: 1 | 2 = halo-tile kernel (two | one 128-row halves per tile) for stride-1 problems with <= 64 output columns
 // Role profiling of the forward kernel: buf = device array of [148][16] int64 (null switches it off).
 // slots: 0 TMA wait-empty, 1 TMA total | 2 MMA wait-full, 3 MMA wait-tmem-empty, 4 MMA total |
 // 5 gather wait-empty, 6 gather tile setup, 7 gather total | 8 epilogue wait-tmem-full, 9 epilogue body, 10 total
@@ -1245,6 +1586,7 @@ CXN_API int cxn_conv_tune(int key, int value) {
     case 6: g_tune_atma = value; break;
     case 7: g_tune_cluster = value; break;
     case 8: g_tune_fill = value; break;
+    case 9: g_tune_halo = value; break;
     default: return -1;
   }
   return 0;

@@ -74,7 +74,8 @@ int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int 
  * 3 unused, 4 forward tile-width class (128|256), 5 timing-experiment bits,
  * 6 im2col-mode TMA for the patch operand (0|1), 7 = 2: forward layers on the im2col-TMA route run as clusters of
  * two CTAs that multicast the filter tile to each other (also CXN_CONV_CLUSTER=2), 8 = 1: narrower column tiles when
- * a forward grid would leave SMs idle (also CXN_CONV_FILL=1).  No reference counterpart. */
+ * a forward grid would leave SMs idle (also CXN_CONV_FILL=1), 9 = 1|2: halo-tile kernel for stride-1 problems with at
+ * most 64 output columns per group (also CXN_CONV_HALO).  No reference counterpart. */
 int cxn_conv_tune(int key, int value);
 /* hardware probe, not on any training path (csrc/kernels/probe_sm100.cu): one tcgen05.mma whose 128B-swizzled
  * operand starts `shift_rows` rows (0..32) into a shared-memory patch; out = device float [128][16];

@@ -133,3 +133,24 @@ def test_conv_cluster_pairs_share_the_filter_tile():
         _case(64, 64, 32, 32, 64, 1, 3, 3, 1, 1)                 # many pairs per cluster (persistent loop)
     finally:
         L.cxn_conv_tune(7, 0)
+
+
+@pytest.mark.skipif(os.environ.get("CXN_TEST_HALO", "0") != "1",
+                    reason="halo-tile convolution: written without access to a GPU, opt-in with CXN_TEST_HALO=1 until it "
+                           "has run on hardware")
+@pytest.mark.parametrize("mode", [1, 2])
+def test_conv_halo_tiles_shift_the_taps_through_one_patch(mode):
+    """cxn_conv_tune(9, mode): stride-1 problems with <= 64 output columns per group load one padded-width patch per
+    tile and 64-channel chunk and read every filter tap as a row-shifted view of it (mode 1: two 128-row halves per
+    tile, 2: one).  Forward and backward-data uses, groups, image heights that do not divide by the tile."""
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    L.cxn_conv_tune(9, mode)
+    try:
+        _case(3, 96, 27, 27, 256, 2, 5, 5, 1, 2)                 # AlexNet conv2: its backward-data is the target (128 -> 48)
+        _case(2, 128, 27, 27, 96, 2, 5, 5, 1, 2)                 # forward with 64-channel groups and 48 outputs
+        _case(3, 64, 13, 13, 48, 1, 3, 3, 1, 1)                  # 3x3, Wp = 15: eight output rows per half
+        _case(2, 64, 9, 11, 32, 1, 3, 2, 1, 1, relu=False)       # asymmetric filter, odd extents
+        _case(5, 128, 20, 20, 64, 1, 3, 3, 1, 1)                 # 64 output columns, two channel chunks
+    finally:
+        L.cxn_conv_tune(9, 0)
