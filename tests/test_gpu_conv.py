@@ -135,9 +135,6 @@ def test_conv_cluster_pairs_share_the_filter_tile():
         L.cxn_conv_tune(7, 0)
 
 
-@pytest.mark.skipif(os.environ.get("CXN_TEST_HALO", "0") != "1",
-                    reason="halo-tile convolution: written without access to a GPU, opt-in with CXN_TEST_HALO=1 until it "
-                           "has run on hardware")
 @pytest.mark.parametrize("mode", [1, 2])
 def test_conv_halo_tiles_shift_the_taps_through_one_patch(mode):
     """cxn_conv_tune(9, mode): stride-1 problems with <= 64 output columns per group load one padded-width patch per

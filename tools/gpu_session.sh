@@ -7,7 +7,6 @@
 # Everything lands in gpurun_out/ (scratch); copy what should be judged into profiles/.
 # Opt-in experiments that have not yet run on hardware (each under its own timeout, failures do not stop the rest):
 #   CXN_TEST_COLLECTIVE=1   torch.distributed exchange on GPUs (tests/test_gpu_multi.py, needs 2 GPUs)
-#   CXN_TEST_HALO=1         halo-tile convolution (tests/test_gpu_conv.py)
 set -u
 N=${1:-1}
 OUT=gpurun_out
@@ -30,7 +29,7 @@ fi
 timeout 300 python -m pytest tests/test_gpu_graph.py -q -k u8 > $OUT/pytest_u8.log 2>&1
 echo "u8 input batches exit $?"; tail -3 $OUT/pytest_u8.log
 timeout 300 python bench.py --input u8 --steps 20 --warmup 5 > $OUT/bench_u8.json 2>/dev/null && python -c "import json;d=json.load(open('$OUT/bench_u8.json'));print('u8 input: e2e', round(d['e2e']['value']), 'img/s, device', round(d['value']))"
-CXN_TEST_HALO=1 timeout 300 python -m pytest tests/test_gpu_conv.py -q -k halo > $OUT/pytest_halo.log 2>&1
+timeout 300 python -m pytest tests/test_gpu_conv.py -q -k halo > $OUT/pytest_halo.log 2>&1
 rc_halo=$?
 echo "halo-tile conv exit $rc_halo"; tail -3 $OUT/pytest_halo.log
 if [ $rc_halo -eq 0 ]; then
