@@ -665,29 +665,6 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
 // empty barrier (2 arrivals) = tcgen05.commit of BOTH CTAs' MMA warps (multicast commit), because a
 // producer writes into its peer's stage as well as its own.  Both CTAs run the same (n, group, k) loop,
 // so the barriers of a pair advance in lock step; every wait is bounded (mbar_wait traps).
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tma_load_3d_mc(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
-                                               int c2, uint16_t mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster"
-      " [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(dst),
-      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "h"(mask)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
-  asm volatile(
-      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-      "h"(mask)
-      : "memory");
-}
-
 constexpr int kClusterThreads = 192;   // warp 0 TMA | warp 1 MMA + TMEM | warps 2-5 epilogue
 
 template <int BNMAX, int MH>

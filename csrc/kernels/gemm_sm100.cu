@@ -346,6 +346,234 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 }
 
+// ===================================================================================================
+// Cluster variant for skinny K-major-A problems (opt-in: CXN_GEMM_CLUSTER=2|4).  The fully connected forward and
+// backward-data GEMMs have M = batch rows and thousands of output columns: with 128 x BN tiles every column tile
+// re-reads the same activation tile (fc6 forward fetches its 4.7 MB activation matrix 64 times from L2).  Here the CL
+// CTAs of a cluster take CL neighbouring column tiles of one row tile; each fetches 128 / CL rows of the activation
+// tile and multicasts them into every CTA's ring, and fetches its own weight tile.  Same barrier protocol as
+// conv_fprop_cluster_kernel (full = own loads + the peers' slices, empty = multicast tcgen05.commit of all CL MMA
+// warps, producer tail + cluster barrier before exit), which has run on hardware.  No split-K, one batch, no atomics.
+template <int BN, bool B_MN, int CL>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_cluster_kernel(const __grid_constant__ CUtensorMap tmASlice, const __grid_constant__ CUtensorMap tmB, const Params p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t bar_base = smem_base + C::kStages * C::kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + kAccStages + a); };
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + C::kStages * C::kStageBytes + 8 * (2 * C::kStages + 2 * kAccStages));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t crank = cluster_ctarank();
+  constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1u);
+  constexpr int kSliceRows = BM / CL;
+
+  const int tiles_m = ceil_div(p.M, BM);
+  const int tiles_n = ceil_div(p.N, BN);
+  const int groups_n = ceil_div(tiles_n, CL);
+  const int num_kb = ceil_div(p.K, BK);
+  const long long total_groups = (long long)tiles_m * groups_n;
+  const long long cluster_id = blockIdx.x / CL, num_clusters = gridDim.x / CL;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), CL);
+    }
+    for (int a = 0; a < kAccStages; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmASlice) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32((const void*)tmem_ptr_smem)),
+                 "n"(C::kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  auto decode = [&](long long t, int& m_blk, int& n_blk) {
+    const int ng = (int)(t % groups_n);
+    m_blk = (int)(t / groups_n);
+    n_blk = ng * CL + (int)crank;            // may be >= tiles_n in the last group: computed, not stored
+  };
+
+  if (warp == 0) {
+    // =========================== TMA producer ===========================
+    int stage = 0;
+    uint32_t phase = 0;
+    for (long long t = cluster_id; t < total_groups; t += num_clusters) {
+      int m_blk, n_blk;
+      decode(t, m_blk, n_blk);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait_warp(empty_bar(stage), phase ^ 1u);
+        const uint32_t sa = smem_base + stage * C::kStageBytes;
+        const uint32_t sb = sa + C::kABytes;
+        if (elect_one()) {
+          mbar_expect_tx(full_bar(stage), C::kStageBytes);
+          // this CTA's slice of the activation tile, into every CTA of the cluster
+          tma_load_3d_mc(sa + crank * (uint32_t)(kSliceRows * BK * 2), &tmASlice, full_bar(stage), kb * BK,
+                         m_blk * BM + (int)crank * kSliceRows, 0, kMask);
+          if (!B_MN) {
+            tma_load_3d(sb, &tmB, full_bar(stage), kb * BK, n_blk * BN, 0);
+          } else {
+#pragma unroll
+            for (int h = 0; h < BN / 64; ++h)
+              tma_load_3d(sb + h * (64 * BK * 2), &tmB, full_bar(stage), n_blk * BN + h * 64, kb * BK, 0);
+          }
+        }
+        __syncwarp();
+        if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+      }
+    }
+    for (int i = 0; i < C::kStages; ++i) {        // tail: every stage released by all MMA warps of the cluster
+      mbar_wait_warp(empty_bar(stage), phase ^ 1u);
+      if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA issuer =============================
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) |
+                           ((uint32_t)(BM >> 4) << 24);
+    constexpr uint32_t kLboMN = 64 * BK * 2;
+    constexpr uint32_t kSbo = 1024;
+    constexpr uint32_t kAStep = UMMA_K * 2;
+    constexpr uint32_t kBStep = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+    const uint64_t adesc_hi = make_desc(0, 0u, kSbo);
+    const uint64_t bdesc_hi = make_desc(0, B_MN ? kLboMN : 0u, kSbo);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (long long t = cluster_id; t < total_groups; t += num_clusters) {
+      mbar_wait_warp(tempty_bar(acc), acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait_warp(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t sa = smem_base + stage * C::kStageBytes;
+        const uint32_t sb = sa + C::kABytes;
+        if (elect_one()) {
+          const uint64_t a0 = adesc_hi | (uint64_t)((sa >> 4) & 0x3FFF), b0 = bdesc_hi | (uint64_t)((sb >> 4) & 0x3FFF);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma_bf16(d_tmem, a0 + (uint64_t)((k * kAStep) >> 4), b0 + (uint64_t)((k * kBStep) >> 4), idesc,
+                      (kb > 0 || k > 0) ? 1u : 0u);
+          umma_commit_mc(empty_bar(stage), kMask);          // frees the slot in every CTA of the cluster
+          if (kb == num_kb - 1) umma_commit(tfull_bar(acc));
+        }
+        __syncwarp();
+        if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+      }
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  } else {
+    // =========================== epilogue ===============================
+    const int quad = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    const bool relu = p.flags & kFlagRelu;
+    const bool out_bf16 = p.flags & kFlagOutBf16;
+    for (long long t = cluster_id; t < total_groups; t += num_clusters) {
+      int m_blk, n_blk;
+      decode(t, m_blk, n_blk);
+      mbar_wait_warp(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const int row = m_blk * BM + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        const int n0 = n_blk * BN + c0;
+        if (n0 >= p.N) break;  // warp-uniform (covers the tiles past the last column tile)
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
+        tmem_ld32(taddr, v);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        const bool full = (n0 + 32 <= p.N);
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (full || n0 + j < p.N) f[j] += __ldg(p.bias + n0 + j);
+        }
+        if (relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+        }
+        const long long off = (long long)row * p.ldd + n0;
+        if (out_bf16) {
+          bf16* d = reinterpret_cast<bf16*>(p.D) + off;
+          if (full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+            uint4* d4 = reinterpret_cast<uint4*>(d);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(f[q * 8 + 0], f[q * 8 + 1]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(f[q * 8 + 2], f[q * 8 + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(f[q * 8 + 4], f[q * 8 + 5]);
+              __nv_bfloat162 h3 = __floats2bfloat162_rn(f[q * 8 + 6], f[q * 8 + 7]);
+              uint4 u;
+              u.x = *reinterpret_cast<uint32_t*>(&h0);
+              u.y = *reinterpret_cast<uint32_t*>(&h1);
+              u.z = *reinterpret_cast<uint32_t*>(&h2);
+              u.w = *reinterpret_cast<uint32_t*>(&h3);
+              d4[q] = u;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (n0 + j < p.N) d[j] = __float2bfloat16(f[j]);
+          }
+        } else {
+          float* d = reinterpret_cast<float*>(p.D) + off;
+          if (full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+            float4* d4 = reinterpret_cast<float4*>(d);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) d4[q] = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (n0 + j < p.N) d[j] = f[j];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::kTmemCols)
+                 : "memory");
+  }
+}
+
 // Second half of an internally split GEMM: D = act(ws + bias) (+ D), ws (fp32 [M][ldw]) is left zeroed
 // for the next call.
 __global__ void splitk_finish_kernel(float* __restrict__ ws, int ldw, void* __restrict__ D, long long ldd,
@@ -474,6 +702,29 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p,
   return 0;
 }
 
+template <int BN, bool B_MN, int CL>
+static int launch_cluster(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int grid, cudaStream_t st) {
+  using C = Cfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_cluster_kernel<BN, B_MN, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         C::kSmemBytes);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  gemm_cluster_kernel<BN, B_MN, CL><<<grid, kThreads, C::kSmemBytes, st>>>(ta, tb, p);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+static int g_gemm_cluster = -1;    // 2 | 4: cluster size of the activation-multicast route; -1 = read CXN_GEMM_CLUSTER
+static int gemm_cluster_mode() {
+  if (g_gemm_cluster < 0) {
+    const char* e = getenv("CXN_GEMM_CLUSTER");
+    g_gemm_cluster = e ? atoi(e) : 0;
+  }
+  return g_gemm_cluster;
+}
+
 // fp32 scratch of the internally split GEMMs: one zeroed buffer per device, grown on demand (never
 // while a stream is capturing - the first, eager, steps size it).  Different streams using it are
 // ordered through an event; inside a stream capture neither the wait nor the record is issued (the
@@ -527,6 +778,13 @@ static void splitk_release(cudaStream_t st) {
 
 }  // namespace gemm
 }  // namespace cxn
+
+// experiment knob: cluster size (0 | 2 | 4) of the activation-multicast route; -1 re-reads CXN_GEMM_CLUSTER
+CXN_API int cxn_gemm_cluster(int cl) {
+  if (cl != -1 && cl != 0 && cl != 2 && cl != 4) return -1;
+  cxn::gemm::g_gemm_cluster = cl;
+  return 0;
+}
 
 // D[z] = A[z] * B[z]^T.  All leading dimensions / strides are in elements.
 //   a_mn / b_mn: 0 = operand stored [rows=MN][K] (K contiguous), 1 = stored [K][MN] (MN contiguous)
@@ -594,6 +852,25 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   p.M = M; p.N = N; p.K = K; p.batch = batch; p.splits = splits; p.kb_per_split = kbps;
   p.D = D; p.ldd = ldd; p.strideD = strideD; p.bias = bias; p.strideBias = strideBias; p.flags = flags;
   CUtensorMap ta, tb;
+  const int cl = gemm_cluster_mode();
+  if ((cl == 2 || cl == 4) && !a_mn && batch == 1 && splits == 1 && !(flags & (kFlagAtomic | kFlagBeta1)) && bn <= 128 &&
+      ceil_div(N, bn) >= cl && sms >= cl) {
+    // skinny problem, many column tiles: clusters of `cl` column tiles share the activation tile by multicast
+    int rc2 = make_map(&ta, A, M, K, lda, 1, strideA, false, BM / cl);
+    if (rc2) return rc2;
+    rc2 = make_map(&tb, B, N, K, ldb, 1, strideB, b_mn != 0, bn);
+    if (rc2) return rc2;
+    const long long groups = (long long)ceil_div(M, BM) * ceil_div(ceil_div(N, bn), cl);
+    const long long max_clusters = sms / cl;
+    const int gridc = cl * (int)(groups < max_clusters ? groups : max_clusters);
+#define CXN_CL_DISPATCH(BN_, CL_)                                                          \
+  return b_mn ? launch_cluster<BN_, true, CL_>(ta, tb, p, gridc, stream)                  \
+              : launch_cluster<BN_, false, CL_>(ta, tb, p, gridc, stream);
+    if (bn == 128) { if (cl == 4) { CXN_CL_DISPATCH(128, 4) } CXN_CL_DISPATCH(128, 2) }
+    if (cl == 4) { CXN_CL_DISPATCH(64, 4) }
+    CXN_CL_DISPATCH(64, 2)
+#undef CXN_CL_DISPATCH
+  }
   int rc = make_map(&ta, A, M, K, lda, batch, strideA, a_mn != 0, BM);
   if (rc) return rc;
   rc = make_map(&tb, B, N, K, ldb, batch, strideB, b_mn != 0, bn);

@@ -32,6 +32,10 @@ int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a_mn, con
                   long long strideB, int b_mn, void* D, long long ldd, long long strideD, const float* bias,
                   long long strideBias, int M, int N, int K, int batch, int splits, int flags, int bn,
                   cudaStream_t stream);
+/* experiment knob: skinny K-major-A problems (the fully connected forward / backward-data GEMMs) run as clusters of
+ * cl = 2 | 4 column tiles that share the activation tile by TMA multicast (0 = off, -1 = re-read CXN_GEMM_CLUSTER).
+ * No reference counterpart. */
+int cxn_gemm_cluster(int cl);
 
 /* K1 (and K2 for stride-1 layers): implicit-GEMM convolution forward, bias (+ReLU) fused.
  * Reference: src/layer/convolution_layer-inl.hpp:79-105. */

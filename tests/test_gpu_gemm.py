@@ -105,3 +105,25 @@ def test_gemm_many_tiles_persistent():
     # more tiles than SMs: exercises the persistent loop and both TMEM accumulator stages
     _run(128 * 20, 128 * 12, 256, False, False, bn=128)
     _run(128 * 40, 256, 192, False, False, bn=64, bias=True)
+
+
+@pytest.mark.skipif(__import__("os").environ.get("CXN_TEST_GEMM_CLUSTER", "0") != "1",
+                    reason="activation-multicast GEMM clusters: written without access to a GPU, opt-in with "
+                           "CXN_TEST_GEMM_CLUSTER=1 until the route has run on hardware")
+@pytest.mark.parametrize("cl", [2, 4])
+def test_gemm_clusters_share_the_activation_tile(cl):
+    """cxn_gemm_cluster(cl): skinny K-major-A problems run as clusters of cl column tiles that multicast the
+    activation tile; fully connected forward (K-major weights, bias + ReLU, bf16) and backward-data (MN-major
+    weights) shapes, column-tile counts that do not divide by the cluster size, M below a tile"""
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    L.cxn_gemm_cluster(cl)
+    try:
+        _run(256, 4096, 1024, 0, 0, relu=True, bias=True)         # fc forward: 2 row tiles x 64 column tiles
+        _run(256, 4096, 1024, 0, 1)                               # fc backward-data: weights MN-major
+        _run(256, 64 * 7, 512, 0, 0, bias=True)                   # 7 column tiles: the last cluster is partly empty
+        _run(100, 640, 320, 0, 0, relu=True)                      # M below one tile
+        _run(256, 2048, 768, 0, 0, out_bf16=False)                # fp32 output
+        _run(384, 1000, 512, 0, 1, bias=True)                     # N not a multiple of the tile
+    finally:
+        L.cxn_gemm_cluster(0)

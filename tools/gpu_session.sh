@@ -7,6 +7,7 @@
 # Everything lands in gpurun_out/ (scratch); copy what should be judged into profiles/.
 # Opt-in experiments that have not yet run on hardware (each under its own timeout, failures do not stop the rest):
 #   CXN_TEST_COLLECTIVE=1   torch.distributed exchange on GPUs (tests/test_gpu_multi.py, needs 2 GPUs)
+#   CXN_TEST_GEMM_CLUSTER=1 activation-multicast GEMM clusters (tests/test_gpu_gemm.py)
 set -u
 N=${1:-1}
 OUT=gpurun_out
@@ -35,6 +36,15 @@ echo "halo-tile conv exit $rc_halo"; tail -3 $OUT/pytest_halo.log
 if [ $rc_halo -eq 0 ]; then
   CXN_CONV_HALO=1 timeout 300 python bench.py --steps 20 --warmup 5 > $OUT/bench_halo.json 2>/dev/null && \
     python -c "import json;d=json.load(open('$OUT/bench_halo.json'));print('CXN_CONV_HALO=1:', round(d['value']), 'img/s', round(d['ms_per_step'],4), 'ms')"
+fi
+CXN_TEST_GEMM_CLUSTER=1 timeout 300 python -m pytest tests/test_gpu_gemm.py -q -k clusters > $OUT/pytest_gemm_cluster.log 2>&1
+rc_gc=$?
+echo "cluster GEMM exit $rc_gc"; tail -3 $OUT/pytest_gemm_cluster.log
+if [ $rc_gc -eq 0 ]; then
+  for cl in 2 4; do
+    CXN_GEMM_CLUSTER=$cl timeout 300 python bench.py --steps 20 --warmup 5 > $OUT/bench_gemm_cl$cl.json 2>/dev/null && \
+      python -c "import json;d=json.load(open('$OUT/bench_gemm_cl$cl.json'));print('CXN_GEMM_CLUSTER=$cl:', round(d['value']), 'img/s', round(d['ms_per_step'],4), 'ms')"
+  done
 fi
 timeout 120 python bench/desc_probe.py > $OUT/desc_probe.txt 2>&1
 echo "descriptor probe exit $?"; tail -18 $OUT/desc_probe.txt
