@@ -1,6 +1,7 @@
-"""Executable model of the barrier protocol of ``conv_fprop_cluster_kernel`` (csrc/kernels/conv_igemm_sm100.cu).
+"""Executable model of the barrier protocol of ``conv_fprop_cluster_kernel`` (csrc/kernels/conv_igemm_sm100.cu) and
+``gemm_cluster_kernel`` (csrc/kernels/gemm_sm100.cu).
 
-Two CTAs of a cluster, each with a TMA producer, an MMA issuer and an epilogue, a ring of shared-memory stages
+Two (or four) CTAs of a cluster, each with a TMA producer, an MMA issuer and an epilogue, a ring of shared-memory stages
 and two accumulator stages.  A producer fills its own patch tile and multicasts its half of the filter tile into
 BOTH CTAs; an MMA warp releases a stage in BOTH CTAs (multicast commit).  TMA writes and MMA executions complete
 asynchronously, in issue order per engine.  The model runs the agents under many random schedules and checks
@@ -45,34 +46,33 @@ class Barrier:
 
 
 class CTA:
-    def __init__(self, rank, nst, nacc):
+    def __init__(self, rank, nst, nacc, ncta=2):
         self.rank, self.alive = rank, True
         self.full = [Barrier(1) for _ in range(nst)]
-        self.empty = [Barrier(2) for _ in range(nst)]          # released by BOTH MMA warps
+        self.empty = [Barrier(ncta) for _ in range(nst)]       # released by the MMA warps of ALL CTAs
         self.tfull = [Barrier(1) for _ in range(nacc)]
         self.tempty = [Barrier(1) for _ in range(nacc)]
         self.a = [None] * nst                                  # patch tile tag per stage
-        self.b = [[None, None] for _ in range(nst)]            # filter halves per stage
+        self.b = [[None] * ncta for _ in range(nst)]           # multicast slices per stage, one from every CTA
         self.acc = [None] * nacc                               # (tile, k-blocks accumulated)
         self.tma, self.mma = [], []                            # in-flight asynchronous operations (FIFO per engine)
 
 
-def run(seed, nst, tiles, num_kb, drain=True, release_both=True, nacc=2):
+def run(seed, nst, tiles, num_kb, drain=True, release_both=True, nacc=2, ncta=2):
     rnd = random.Random(seed)
-    ctas = [CTA(0, nst, nacc), CTA(1, nst, nacc)]
+    ctas = [CTA(r, nst, nacc, ncta) for r in range(ncta)]
     A_BYTES, H_BYTES = 16, 4
 
     def touch(cta, what):
         assert cta.alive, "%s reached CTA %d after it had left" % (what, cta.rank)
 
     def producer(me):
-        other = ctas[1 - me.rank]
         stage, phase = 0, 0
         for t in range(tiles):
             for kb in range(num_kb):
                 while not me.empty[stage].passed(phase ^ 1):
                     yield
-                me.full[stage].expect_tx(A_BYTES + 2 * H_BYTES)
+                me.full[stage].expect_tx(A_BYTES + ncta * H_BYTES)
                 s = stage
 
                 def load_a(s=s, t=t, kb=kb):
@@ -80,8 +80,8 @@ def run(seed, nst, tiles, num_kb, drain=True, release_both=True, nacc=2):
                     me.full[s].complete_tx(A_BYTES)
 
                 def load_half(s=s, t=t, kb=kb):               # multicast: lands in both CTAs
-                    for c in (me, other):
-                        touch(c, "multicast filter half")
+                    for c in ctas:
+                        touch(c, "multicast slice")
                         c.b[s][me.rank] = (t, kb)
                         c.full[s].complete_tx(H_BYTES)
                 me.tma.append(load_a)
@@ -99,7 +99,6 @@ def run(seed, nst, tiles, num_kb, drain=True, release_both=True, nacc=2):
                     stage, phase = 0, phase ^ 1
 
     def mma(me):
-        other = ctas[1 - me.rank]
         stage, phase, acc, acc_phase = 0, 0, 0, 0
         for t in range(tiles):
             while not me.tempty[acc].passed(acc_phase ^ 1):
@@ -111,15 +110,13 @@ def run(seed, nst, tiles, num_kb, drain=True, release_both=True, nacc=2):
 
                 def execute(s=s, t=t, kb=kb, a_=a_):
                     assert me.a[s] == (me.rank, t, kb), "MMA read patch tile %r, wanted %r" % (me.a[s], (me.rank, t, kb))
-                    assert me.b[s] == [(t, kb), (t, kb)], "MMA read filter halves %r, wanted %r" % (me.b[s], (t, kb))
+                    assert me.b[s] == [(t, kb)] * ncta, "MMA read multicast slices %r, wanted %r" % (me.b[s], (t, kb))
                     me.acc[a_] = (t, kb + 1) if kb else (t, 1)
 
                 def release(s=s):
-                    for c in ((me, other) if release_both else (me,)):
+                    for c in (ctas if release_both else [me] * ncta):   # (broken variant: all arrivals stay local)
                         touch(c, "stage release")
                         c.empty[s].arrive()
-                    if not release_both:
-                        me.empty[s].arrive()                   # (broken variant: both arrivals from the local warp)
                 me.mma.append(execute)
                 me.mma.append(release)
                 if kb == num_kb - 1:
@@ -154,7 +151,7 @@ def run(seed, nst, tiles, num_kb, drain=True, release_both=True, nacc=2):
     while True:
         choices = [k for k in agents if k not in done]
         engines = [(c, q) for c in ctas for q in (c.tma, c.mma) if q]
-        if not choices and not engines and len(at_cluster_barrier) == 2:
+        if not choices and not engines and len(at_cluster_barrier) == ncta:
             break
         steps += 1
         assert steps < 200000, "deadlock: agents %s never finish" % sorted(choices)
@@ -173,7 +170,7 @@ def run(seed, nst, tiles, num_kb, drain=True, release_both=True, nacc=2):
         for c in ctas:
             if all((c.rank, n) in done for n in "PME"):
                 at_cluster_barrier.add(c.rank)
-        if len(at_cluster_barrier) == 2:
+        if len(at_cluster_barrier) == ncta:
             for c in ctas:
                 c.alive = False
     return steps
@@ -183,6 +180,14 @@ def run(seed, nst, tiles, num_kb, drain=True, release_both=True, nacc=2):
 def test_protocol_holds_under_random_schedules(nst, tiles, num_kb):
     for seed in range(150):
         run(seed, nst, tiles, num_kb)
+
+
+@pytest.mark.parametrize("nst,tiles,num_kb", [(2, 2, 5), (8, 2, 9), (3, 1, 16)])
+def test_protocol_holds_for_clusters_of_four(nst, tiles, num_kb):
+    """gemm_cluster_kernel with CL = 4: every CTA multicasts a quarter of the shared tile, a stage is released by four
+    multicast commits"""
+    for seed in range(60):
+        run(seed, nst, tiles, num_kb, ncta=4)
 
 
 def test_model_catches_a_missing_tail_or_a_local_only_release():
