@@ -1539,6 +1539,26 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   return bnmax == 256 ? launch<256, false, 1>(tm, tmp, atma, p, grid_final, st) : launch<128, false, 1>(tm, tmp, atma, p, grid_final, st);
 }
 
+// Host-only: would the halo-tile kernel take this forward problem, and with which geometry?  Returns 1 and fills
+// out[0..7] = {padded width, output rows per half, tiles per image, patch rows, patch stage bytes, patch stages,
+// filter stages, dynamic shared memory} or returns 0.  (Lets the planning be tested without a GPU.)
+CXN_API int cxn_conv_halo_plan(int N, int H, int W, int Cs, int Cg, int G, int Ng, int KH, int KW, int stride, int pad_y,
+                               int pad_x, int OH, int OW, int halves, int* out) {
+  Params p;
+  memset(&p, 0, sizeof(p));
+  static bf16 aligned_dummy[8] __attribute__((aligned(16)));
+  p.src = aligned_dummy; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
+  p.stride_y = p.stride_x = stride; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
+  p.gran = 8; p.Ng = Ng;
+  p.bn = pick_bn(Ng, Ng > 128 ? 256 : 128);
+  HaloGeom hg;
+  int smem = 0;
+  if (halves < 1 || halves > 2 || !halo_plan(p, halves, &hg, &smem)) return 0;
+  out[0] = hg.wp; out[1] = hg.rows_half; out[2] = hg.tiles_img; out[3] = hg.patch_h; out[4] = hg.a_stage_bytes;
+  out[5] = hg.na; out[6] = hg.nb; out[7] = smem;
+  return 1;
+}
+
 // Tuning / experiment knobs; value 0 (or -1 for the switches) restores the automatic choice.
 //   0: row halves per forward tile   1: ring stages   2: gather through L1   3: tap-inner order   4: tile-width class
 //   5: timing experiments   6: im2col TMA on / off   7: 2 = CTA-pair clusters with a multicast filter tile (forward)

@@ -81,6 +81,11 @@ int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int 
  * a forward grid would leave SMs idle (also CXN_CONV_FILL=1), 9 = 1|2: halo-tile kernel for stride-1 problems with at
  * most 64 output columns per group (also CXN_CONV_HALO).  No reference counterpart. */
 int cxn_conv_tune(int key, int value);
+/* host-only planning query of the halo-tile kernel (key 9): 1 and out[0..7] = {padded width, output rows per half, tiles
+ * per image, patch rows, patch stage bytes, patch stages, filter stages, dynamic shared memory}, or 0 if the kernel
+ * would not take the problem.  No reference counterpart. */
+int cxn_conv_halo_plan(int N, int H, int W, int Cs, int Cg, int G, int Ng, int KH, int KW, int stride, int pad_y, int pad_x,
+                       int OH, int OW, int halves, int* out);
 /* hardware probe, not on any training path (csrc/kernels/probe_sm100.cu): one tcgen05.mma whose 128B-swizzled
  * operand starts `shift_rows` rows (0..32) into a shared-memory patch; out = device float [128][16];
  * base_offset_mode 0 | 1 = descriptor base-offset field left 0 | set from the start address.

@@ -151,3 +151,27 @@ def test_collective_exchange_buckets_and_calls_on_a_mocked_device(monkeypatch):
         ex.publish_pending(); ex.after_replayed_step(); ex.gather_master()
     finally:
         dist.destroy_process_group()
+
+
+def test_halo_tile_planning_takes_conv2_backward_data():
+    """host side of conv_fprop_halo_kernel (cxn_conv_halo_plan, no GPU needed): AlexNet conv2's backward-data problem
+    (dy 27x27x256 in two groups of 128, 5x5 flipped filter, pad 2, 48 outputs per group) is taken with the geometry the
+    kernel's comments describe; problems it is not meant for are refused"""
+    import ctypes
+    L = ops.lib()
+    L.cxn_conv_halo_plan.argtypes = [ctypes.c_int] * 15 + [ctypes.POINTER(ctypes.c_int)]
+    L.cxn_conv_halo_plan.restype = ctypes.c_int
+    out = (ctypes.c_int * 8)()
+    # N, H, W, Cs, Cg, G, Ng, KH, KW, stride, pad_y, pad_x, OH, OW, halves
+    assert L.cxn_conv_halo_plan(256, 27, 27, 256, 128, 2, 48, 5, 5, 1, 2, 2, 27, 27, 2, out) == 1
+    wp, rows_half, tiles_img, patch_h, a_bytes, na, nb, smem = list(out)
+    assert (wp, rows_half, tiles_img, patch_h) == (31, 4, 4, 12)
+    assert a_bytes % 1024 == 0 and a_bytes >= ((4 + 4) * 31 + 4 + 128) * 128 and a_bytes >= 31 * 12 * 128
+    assert na in (2, 3) and nb == 8 and smem <= 232448
+    assert L.cxn_conv_halo_plan(256, 27, 27, 256, 128, 2, 48, 5, 5, 1, 2, 2, 27, 27, 1, out) == 1
+    assert list(out)[:4] == [31, 4, 7, 8]                                      # single-half tiles: 4 rows each
+    # refused: strided, channel groups that are not multiples of 64, more than 64 outputs, rows wider than a tile
+    assert L.cxn_conv_halo_plan(8, 27, 27, 256, 128, 2, 48, 5, 5, 2, 2, 2, 14, 14, 2, out) == 0
+    assert L.cxn_conv_halo_plan(8, 27, 27, 96, 48, 2, 128, 5, 5, 1, 2, 2, 27, 27, 2, out) == 0
+    assert L.cxn_conv_halo_plan(8, 13, 13, 256, 256, 1, 384, 3, 3, 1, 1, 1, 13, 13, 2, out) == 0
+    assert L.cxn_conv_halo_plan(8, 200, 200, 64, 64, 1, 32, 3, 3, 1, 1, 1, 200, 200, 2, out) == 0
