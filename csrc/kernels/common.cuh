@@ -41,6 +41,13 @@ inline int num_sms() {
   return n;
 }
 
+// True when [p, p + bytes) is memory of the CURRENT device that this process allocated itself: not a mapping of
+// another GPU's memory (CUDA IPC, peer access, cuMemMap), not host memory.  The cluster-multicast TMA routes ask
+// this before building a multicast tensor map: TMA multicast loads here read only this GPU's memory, since on
+// B200 a TMA multicast load from another GPU's memory hung the GPU.  Anything not provably local answers false.
+// (defined in fused_exchange.cu, which also records every range it maps from a peer)
+bool memory_is_local(const void* p, size_t bytes);
+
 // grid size for a grid-stride elementwise kernel: enough CTAs to fill the chip
 // a few times over, never more than the work needs.
 inline int ew_grid(long long n_items, int threads, int waves = 8) {

@@ -1523,7 +1523,8 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
     }
   }
   const long long tiles_m = ceil_div_ll(rows, mh * BM);
-  if (cluster_mode() == 2 && atma && !p.b_resident && tiles_m >= 2 && num_sms() >= 2) {
+  if (cluster_mode() == 2 && atma && !p.b_resident && tiles_m >= 2 && num_sms() >= 2 &&
+      memory_is_local(w, (size_t)G * (size_t)Ng * (size_t)ldw * sizeof(bf16))) {   // multicast map: own memory only
     // CTA pairs on two pixel tiles of the same output columns: each fetches half of the filter tile and
     // multicasts it to both (tensor map over this GPU's weights)
     CUtensorMap tmh;

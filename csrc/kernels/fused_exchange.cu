@@ -19,6 +19,7 @@
 // deadlock; every wait is bounded and traps on timeout.
 #include "common.cuh"
 #include <mutex>
+#include <vector>
 #include <stdlib.h>
 #include <string.h>
 
@@ -507,6 +508,65 @@ CXN_API int cxn_symm_allgather(const unsigned long long* peers, int nranks, int 
 }
 
 // ------------------------------------------------------------------ CUDA IPC helpers
+// ---- locality registry: every range this library maps from another GPU is recorded here, and memory_is_local()
+// refuses those ranges (as well as anything the driver does not report as plain device memory of the current GPU).
+namespace cxn {
+namespace {
+struct PeerRange { uintptr_t lo, hi; };
+std::mutex g_peer_mu;
+std::vector<PeerRange> g_peer_ranges;
+}  // namespace
+static void note_peer_range(const void* p, size_t bytes) {
+  std::lock_guard<std::mutex> g(g_peer_mu);
+  g_peer_ranges.push_back({reinterpret_cast<uintptr_t>(p), reinterpret_cast<uintptr_t>(p) + bytes});
+}
+static void forget_peer_range(const void* p) {
+  std::lock_guard<std::mutex> g(g_peer_mu);
+  for (size_t i = 0; i < g_peer_ranges.size(); ++i)
+    if (g_peer_ranges[i].lo == reinterpret_cast<uintptr_t>(p)) { g_peer_ranges.erase(g_peer_ranges.begin() + i); return; }
+}
+bool memory_is_local(const void* p, size_t bytes) {
+  if (p == nullptr) return false;
+  const uintptr_t lo = reinterpret_cast<uintptr_t>(p), hi = lo + (bytes ? bytes : 1);
+  {
+    std::lock_guard<std::mutex> g(g_peer_mu);
+    for (const PeerRange& r : g_peer_ranges)
+      if (lo < r.hi && r.lo < hi) return false;
+  }
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  // both ends of the range must be ordinary device allocations of the current device
+  const void* ends[2] = {p, reinterpret_cast<const void*>(hi - 1)};
+  for (int i = 0; i < 2; ++i) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, ends[i]) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (a.type != cudaMemoryTypeDevice || a.device != dev) return false;
+    // an IPC / VMM import of a peer allocation reports the exporting device; a mapping the driver attributes to
+    // this device but whose base is a recorded peer range was caught above
+    CUdeviceptr base = 0; size_t sz = 0;
+    typedef CUresult (*RangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
+    static RangeFn range_fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+      void* q = nullptr;
+      cudaDriverEntryPointQueryResult r;
+      if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &q, cudaEnableDefault, &r) == cudaSuccess &&
+          r == cudaDriverEntryPointSuccess)
+        range_fn = reinterpret_cast<RangeFn>(q);
+    });
+    if (range_fn && range_fn(&base, &sz, (CUdeviceptr)ends[i]) == CUDA_SUCCESS) {
+      std::lock_guard<std::mutex> g(g_peer_mu);
+      for (const PeerRange& r : g_peer_ranges)
+        if ((uintptr_t)base < r.hi && r.lo < (uintptr_t)base + sz) return false;
+    }
+  }
+  return true;
+}
+}  // namespace cxn
+
+// 1 = the range is plain memory of the current device (eligible for the cluster-multicast routes), 0 = not
+CXN_API int cxn_memory_is_local(const void* p, unsigned long long bytes) { return cxn::memory_is_local(p, (size_t)bytes) ? 1 : 0; }
+
 CXN_API int cxn_ipc_alloc(unsigned long long bytes, unsigned long long* ptr, unsigned char* handle64) {
   void* d = nullptr;
   cudaError_t e = cudaMalloc(&d, bytes);
@@ -527,8 +587,23 @@ CXN_API int cxn_ipc_open(const unsigned char* handle64, unsigned long long* ptr)
   void* d = nullptr;
   cudaError_t e = cudaIpcOpenMemHandle(&d, h, cudaIpcMemLazyEnablePeerAccess);
   if (e != cudaSuccess) return (int)e;
+  // record the mapping's extent so that no multicast tensor map is ever built over it
+  size_t sz = 0;
+  {
+    CUdeviceptr base = 0;
+    typedef CUresult (*RangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
+    void* q = nullptr;
+    cudaDriverEntryPointQueryResult r;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &q, cudaEnableDefault, &r) == cudaSuccess &&
+        r == cudaDriverEntryPointSuccess && q)
+      if (reinterpret_cast<RangeFn>(q)(&base, &sz, (CUdeviceptr)d) != CUDA_SUCCESS) sz = 0;
+  }
+  cxn::note_peer_range(d, sz ? sz : ((size_t)1 << 40));
   *ptr = reinterpret_cast<unsigned long long>(d);
   return 0;
 }
-CXN_API int cxn_ipc_close(unsigned long long ptr) { return (int)cudaIpcCloseMemHandle(reinterpret_cast<void*>(ptr)); }
+CXN_API int cxn_ipc_close(unsigned long long ptr) {
+  cxn::forget_peer_range(reinterpret_cast<void*>(ptr));
+  return (int)cudaIpcCloseMemHandle(reinterpret_cast<void*>(ptr));
+}
 CXN_API int cxn_ipc_free(unsigned long long ptr) { return (int)cudaFree(reinterpret_cast<void*>(ptr)); }

@@ -854,8 +854,11 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   CUtensorMap ta, tb;
   const int cl = gemm_cluster_mode();
   if ((cl == 2 || cl == 4) && !a_mn && batch == 1 && splits == 1 && !(flags & (kFlagAtomic | kFlagBeta1)) && bn <= 128 &&
-      ceil_div(N, bn) >= cl && sms >= cl) {
-    // skinny problem, many column tiles: clusters of `cl` column tiles share the activation tile by multicast
+      ceil_div(N, bn) >= cl && sms >= cl &&
+      memory_is_local(A, ((size_t)(M - 1) * (size_t)lda + (size_t)K) * sizeof(bf16))) {
+    // skinny problem, many column tiles: clusters of `cl` column tiles share the activation tile by multicast.
+    // The multicast tensor map must cover this GPU's own memory only (memory_is_local, common.cuh); any other
+    // operand takes the ordinary kernel below.
     int rc2 = make_map(&ta, A, M, K, lda, 1, strideA, false, BM / cl);
     if (rc2) return rc2;
     rc2 = make_map(&tb, B, N, K, ldb, 1, strideB, b_mn != 0, bn);

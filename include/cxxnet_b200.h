@@ -244,6 +244,11 @@ int cxn_ipc_alloc(unsigned long long bytes, unsigned long long* ptr, unsigned ch
 int cxn_ipc_open(const unsigned char* handle64, unsigned long long* ptr);
 int cxn_ipc_close(unsigned long long ptr);
 int cxn_ipc_free(unsigned long long ptr);
+/* 1 when [p, p + bytes) is plain device memory of the current GPU allocated by this process (not an IPC / peer /
+ * VMM mapping of another GPU's memory, not host memory), else 0.  cxn_gemm_bf16 and cxn_conv_fprop* consult it
+ * before taking a cluster-multicast route: a multicast tensor map must cover this GPU's memory alone; every
+ * other operand runs on the non-cluster kernels.  No reference counterpart. */
+int cxn_memory_is_local(const void* p, unsigned long long bytes);
 
 /* number of kernel launches issued by this library in this process */
 unsigned long long cxn_launch_count(void);

@@ -10,6 +10,13 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: test needs a CUDA device (run on the B200 box)")
+    # every oracle in this suite is plain fp32 PyTorch: no TF32 in cuDNN convolutions or cuBLAS matmuls
+    try:
+        import torch
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+    except Exception:
+        pass
 
 
 def pytest_collection_modifyitems(config, items):

@@ -127,3 +127,18 @@ def test_gemm_clusters_share_the_activation_tile(cl):
         _run(384, 1000, 512, 0, 1, bias=True)                     # N not a multiple of the tile
     finally:
         L.cxn_gemm_cluster(0)
+
+
+def test_memory_is_local_guard():
+    """cxn_memory_is_local: device tensors of the current GPU qualify for the multicast routes, pinned host memory
+    and null pointers do not (the multicast tensor maps must cover this GPU's own memory only)"""
+    import ctypes
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    L.cxn_memory_is_local.argtypes = [ctypes.c_void_p, ctypes.c_ulonglong]
+    L.cxn_memory_is_local.restype = ctypes.c_int
+    t = torch.zeros(1 << 20, dtype=torch.bfloat16, device="cuda")
+    assert L.cxn_memory_is_local(t.data_ptr(), t.numel() * 2) == 1
+    h = torch.zeros(1 << 16).pin_memory()
+    assert L.cxn_memory_is_local(h.data_ptr(), h.numel() * 4) == 0
+    assert L.cxn_memory_is_local(None, 16) == 0
