@@ -220,7 +220,75 @@ def run_ours(args, rank, world, local):
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8},
         "gpu_launches": int(launches), "clocks": clocks, "train_error_running": err,
     }
+    if world > 1:
+        # outside the timed regions: are the replicas of the timed trainer identical, and does a multi-rank run
+        # reproduce a single-GPU run of the same batches?
+        out["replica_max_diff"] = tr.net.exchange.check_replicas()
+        if not args.no_verify:
+            rep, rel_w, rel_dw = verify_multi(args, rank, world, local, extra)
+            out["verify"] = {"replica_max_diff_after_3_steps": rep, "max_rel_err_vs_1gpu": rel_w,
+                             "max_rel_err_of_updates_vs_1gpu": rel_dw,
+                             "note": "fresh nets, dropout off, 3 global batches; relative L1 per weight tensor of the "
+                                     "weights and of (w - w0); bf16 rounding differs with the batch split"}
     return out
+
+
+def verify_multi(args, rank, world, local, extra):
+    """Correctness of the multi-GPU path, outside every timed region (the reference's `test_on_server` idea,
+    src/updater/async_updater-inl.hpp:144-154, plus a single-GPU twin): a fresh multi-rank trainer and, on every
+    rank's own device, a single-process twin start from identical weights (dropout off: its masks depend on the
+    batch split) and take the same 3 global batches.  Returns (max |w_rank - w_rank0| over all weights after the
+    steps, max relative L1 difference of any weight tensor against the twin)."""
+    import torch
+    from cxxnet_b200.config import parse_config_string
+    from cxxnet_b200.io.data import DataBatch
+    from cxxnet_b200.models import alexnet_conf
+    from cxxnet_b200.trainer import NetTrainer
+    B = args.batch
+
+    def make(dev, **over):
+        t = NetTrainer()
+        conf = alexnet_conf(batch_size=B, dev=dev, extra=extra).replace("threshold = 0.5", "threshold = 0.0")
+        for k, v in parse_config_string(conf):
+            t.set_param(k, v)
+        for k, v in over.items():
+            t.set_param(k, v)
+        t.set_param("silent", "1")
+        t.init_model()
+        return t
+    multi = make("gpu:" + ",".join(str(i) for i in range(world)))
+    single = make("gpu:%d" % local, param_server="NONE")
+    names = [(i, tag) for i, c in enumerate(multi.net.connections) for tag, _, _ in c.layer.weights()]
+    w0 = {}
+    for i, tag in names:
+        w, _ = multi.net.get_weight(i, tag)
+        single.net.set_weight(i, w, tag)
+        w0[(i, tag)] = w.double()
+    g = torch.Generator().manual_seed(4321)
+    for s_ in range(3):
+        b = DataBatch()
+        b.data = torch.randn((B, 3, 227, 227), generator=g).to(torch.bfloat16)
+        b.label = torch.randint(0, 1000, (B, 1), generator=g).float()
+        b.batch_size = B
+        multi.update(b)
+        single.update(b)
+    torch.cuda.synchronize()
+    replica = multi.net.exchange.check_replicas()
+    worst_w, worst_dw = 0.0, 0.0
+    for i, tag in names:
+        a, _ = multi.net.get_weight(i, tag)
+        c, _ = single.net.get_weight(i, tag)
+        a, c = a.double(), c.double()
+        denom = float(c.abs().sum())
+        worst_w = max(worst_w, float((a - c).abs().sum()) / denom if denom > 0 else float((a - c).abs().sum()))
+        # what moved: w - w0 is small against w, so the weights alone would hide a wrong update
+        da, dc = a - w0[(i, tag)], c - w0[(i, tag)]
+        denom = float(dc.abs().sum())
+        worst_dw = max(worst_dw, float((da - dc).abs().sum()) / denom if denom > 0 else float((da - dc).abs().sum()))
+    t = torch.tensor([worst_w, worst_dw], dtype=torch.float64, device="cuda")
+    import torch.distributed as dist
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return replica, float(t[0].item()), float(t[1].item())
 
 
 def run_library(args, rank, world, local):
@@ -288,6 +356,8 @@ def main():
                     help="strong (default, the reference's semantics): --batch is the global batch, split over the "
                          "GPUs; weak: --batch images per GPU, global batch = batch x GPUs (secondary series)")
     ap.add_argument("--extra", default="", help="extra config lines for the ours arm, ';' separated")
+    ap.add_argument("--no-verify", action="store_true",
+                    help="skip the multi-GPU correctness check against a single-GPU twin (after the timed regions)")
     ap.add_argument("--input", default="bf16", choices=["bf16", "u8"],
                     help="host batches of the end-to-end measurement: bf16 (default, normalised on the host) or u8 "
                          "(raw pixels, normalised on the device: half the bf16 bytes over PCIe)")

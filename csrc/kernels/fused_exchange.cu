@@ -30,7 +30,7 @@ constexpr int kMaxRanks = 16;
 constexpr int kMaxSlots = 256;
 constexpr int kChunk = 1024;
 constexpr int kThreads = 256;
-constexpr int kMaxBucketSegs = 8;
+constexpr int kMaxBucketSegs = 16;   // segments cached in shared memory; buckets may hold more (load_seg)
 
 struct Segment {   // must match loss_update.cu
   long long start, n, shadow_off;
@@ -107,14 +107,13 @@ __device__ __forceinline__ float clip_grad(float g, float c) {
   return fminf(fmaxf(g, -c), c);
 }
 
-// segment of chunk `ch`: the bucket's few segments are cached in shared memory, so no dependent
-// global loads sit on the critical path of every chunk
-__device__ __forceinline__ int find_seg(const Segment* sseg, int nseg, long long e) {
-  int k = 0;
-#pragma unroll 1
-  for (int i = 1; i < nseg; ++i)
-    if (e >= sseg[i].start) k = i;
-  return k;
+// Segment of a chunk: segments are aligned to chunks, so the chunk table names it.  The first kMaxBucketSegs
+// segments of the bucket are cached in shared memory; a bucket with more (many small layers merged into one
+// launch) reads the rest from the global table.  The lookup is off the critical path: the peer loads of a chunk
+// do not depend on it (the arenas are padded to whole chunks, padding gradients are zero).
+__device__ __forceinline__ Segment load_seg(const Params& p, const Segment* sseg, int seg_lo, long long ch) {
+  const int k = __ldg(p.chunk_seg + ch) - seg_lo;
+  return k < kMaxBucketSegs ? sseg[k] : p.segs[seg_lo + k];
 }
 
 template <int NR, int U>   // NR: compile-time upper bound on ranks per load group, U: chunks in flight
@@ -143,13 +142,10 @@ fused_rs_update_ag_kernel(const Params p) {
   for (long long ch0 = my0 + (long long)blockIdx.x * U; ch0 < my1; ch0 += (long long)gridDim.x * U) {
     float4 acc[U];
     bool live[U];
-    int sidx[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const long long e = (ch0 + u) * kChunk + threadIdx.x * 4;
       acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      sidx[u] = find_seg(sseg, nseg, e);
-      live[u] = (ch0 + u < my1) && (e - sseg[sidx[u]].start) < sseg[sidx[u]].n;
+      live[u] = ch0 + u < my1;
     }
     // issue every load of a group of up to NR ranks before consuming any of them
     for (int r0 = 0; r0 < p.nranks; r0 += NR) {
@@ -178,8 +174,9 @@ fused_rs_update_ag_kernel(const Params p) {
     for (int u = 0; u < U; ++u) {
       if (!live[u]) continue;
       const long long e = (ch0 + u) * kChunk + threadIdx.x * 4;
-      const Segment& s = sseg[sidx[u]];
+      const Segment s = load_seg(p, sseg, seg_lo, ch0 + u);
       const long long rel = e - s.start;
+      if (rel >= s.n) continue;             // chunk padding behind the segment's last element
       float4 wv = *reinterpret_cast<const float4*>(w + e);
       float4 mv = *reinterpret_cast<const float4*>(m + e);
       float4 m2v = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -235,21 +232,20 @@ fused_rs_update_ag_kernel(const Params p) {
   constexpr int V = 4;
   for (long long ch0 = p.cb + (long long)blockIdx.x * V; ch0 < p.ce && !(p.dbg & 4); ch0 += (long long)gridDim.x * V) {
     float4 wv[V];
-    int sidx[V];
     bool live[V];
 #pragma unroll
     for (int u = 0; u < V; ++u) {
       const long long e = (ch0 + u) * kChunk + threadIdx.x * 4;
-      sidx[u] = find_seg(sseg, nseg, e);
-      live[u] = (ch0 + u < p.ce) && (e - sseg[sidx[u]].start) < sseg[sidx[u]].n;
-      wv[u] = (live[u] && sseg[sidx[u]].shadow_off >= 0) ? ld_sys_f4(w + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+      live[u] = ch0 + u < p.ce;
+      wv[u] = live[u] ? ld_sys_f4(w + e) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
     for (int u = 0; u < V; ++u) {
       if (!live[u]) continue;
       const long long e = (ch0 + u) * kChunk + threadIdx.x * 4;
-      const Segment& s = sseg[sidx[u]];
+      const Segment s = load_seg(p, sseg, seg_lo, ch0 + u);
       const long long rel = e - s.start;
+      if (rel >= s.n) continue;
       *reinterpret_cast<float4*>(g + e) = make_float4(0.f, 0.f, 0.f, 0.f);
       if (s.shadow_off >= 0) {
         const float* wp = reinterpret_cast<const float*>(&wv[u]);

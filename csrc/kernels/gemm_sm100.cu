@@ -725,10 +725,13 @@ static int gemm_cluster_mode() {
   return g_gemm_cluster;
 }
 
-// fp32 scratch of the internally split GEMMs: one zeroed buffer per device, grown on demand (never
-// while a stream is capturing - the first, eager, steps size it).  Different streams using it are
-// ordered through an event; inside a stream capture neither the wait nor the record is issued (the
-// capture begins after a device synchronisation and its streams are ordered by the graph itself).
+// fp32 scratch of the internally split GEMMs: zeroed buffers per device, grown on demand (never while a stream is
+// capturing - the first, eager, steps size them).  A device has kWsLanes independent buffers ("lanes"); the calling
+// thread picks one with cxn_gemm_workspace_lane (default 0).  Work that may run CONCURRENTLY - e.g. the main-stream
+// and exchange-stream branches of a captured step - must use different lanes, otherwise two split GEMMs would
+// accumulate into, and re-zero, the same buffer.  Within a lane, different streams are ordered through an event;
+// inside a stream capture neither the wait nor the record is issued (sequential use of one lane inside a graph is
+// ordered by the graph's own dependencies).
 struct SplitWs {
   float* p = nullptr;
   size_t n = 0;
@@ -736,8 +739,10 @@ struct SplitWs {
   cudaStream_t last = nullptr;
   bool used = false;
 };
+constexpr int kWsLanes = 4;
 static std::mutex g_ws_mu;
-static SplitWs g_ws[64];
+static SplitWs g_ws[64][kWsLanes];
+static thread_local int t_ws_lane = 0;
 
 static bool stream_capturing(cudaStream_t st) {
   cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
@@ -750,18 +755,20 @@ static float* splitk_workspace(size_t bytes, cudaStream_t st) {
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) return nullptr;
   std::lock_guard<std::mutex> g(g_ws_mu);
-  SplitWs& w = g_ws[dev];
+  SplitWs& w = g_ws[dev][t_ws_lane];
   const bool capturing = stream_capturing(st);
   if (w.n < bytes) {
     if (capturing) return nullptr;            // cannot allocate now: the caller falls back to the unsplit kernel
     if (w.p) { cudaDeviceSynchronize(); cudaFree(w.p); }
     w.p = nullptr; w.n = 0;
     const size_t want = bytes < (16u << 20) ? (16u << 20) : bytes;
-    if (cudaMalloc(&w.p, want) != cudaSuccess) { w.p = nullptr; return nullptr; }
+    if (cudaMalloc(&w.p, want) != cudaSuccess) { w.p = nullptr; cudaGetLastError(); return nullptr; }
     if (cudaMemsetAsync(w.p, 0, want, st) != cudaSuccess) return nullptr;
     w.n = want;
     if (!w.ev) cudaEventCreateWithFlags(&w.ev, cudaEventDisableTiming);
-    w.last = st; w.used = false;
+    // the zero fill counts as a use: another stream must wait for it
+    cudaEventRecord(w.ev, st);
+    w.last = st; w.used = true;
   }
   if (!capturing && w.used && w.last != st && w.ev) cudaStreamWaitEvent(st, w.ev, 0);
   return w.p;
@@ -771,13 +778,21 @@ static void splitk_release(cudaStream_t st) {
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) return;
   std::lock_guard<std::mutex> g(g_ws_mu);
-  SplitWs& w = g_ws[dev];
+  SplitWs& w = g_ws[dev][t_ws_lane];
   if (!stream_capturing(st) && w.ev) cudaEventRecord(w.ev, st);
   w.last = st; w.used = true;
 }
 
 }  // namespace gemm
 }  // namespace cxn
+
+// Split-K scratch lane (0..3) used by this thread's following cxn_gemm_bf16 calls; returns the previous lane or -1.
+CXN_API int cxn_gemm_workspace_lane(int lane) {
+  if (lane < 0 || lane >= cxn::gemm::kWsLanes) return -1;
+  const int prev = cxn::gemm::t_ws_lane;
+  cxn::gemm::t_ws_lane = lane;
+  return prev;
+}
 
 // experiment knob: cluster size (0 | 2 | 4) of the activation-multicast route; -1 re-reads CXN_GEMM_CLUSTER
 CXN_API int cxn_gemm_cluster(int cl) {

@@ -93,7 +93,12 @@ class ParamArena:
         if self.device.type == "cuda":
             self.seg_host = [t.pin_memory() for t in self.seg_host]
         self.seg_dev = torch.zeros_like(self.seg_host[0], device=self.device)
+        # initial table: schedule_epoch is stateful under momentum_schedule (it ADDS to the momentum, as the
+        # reference's ScheduleEpoch does), and this evaluation is not an update - put the momenta back afterwards
+        saved = [s.param.momentum for s in self.segments]
         self.refresh_hyper(0)
+        for s, mom in zip(self.segments, saved):
+            s.param.momentum = mom
 
     # ------------------------------------------------------------------ views
     def w_view(self, s: Segment) -> torch.Tensor:

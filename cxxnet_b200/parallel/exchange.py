@@ -226,8 +226,13 @@ class GradExchange:
                 # gW[row0:row0+my_rows] = GY_all[:, shard]^T . X_all  over the global batch
                 gy_ptr = sh.gy_all.data_ptr() + sh.row0 * 2
                 g_ptr = a.g.data_ptr() + (sh.wseg.start + sh.row0 * nin) * 4
-                ops.gemm(gy_ptr, sh.ld_out, 0, 1, sh.x_all.data_ptr(), sh.ld_in, 0, 1, g_ptr, nin, 0, None, 0,
-                         sh.my_rows, nin, total_b, flags=ops.GEMM_BETA1 if acc else 0)
+                # (split-K scratch lane 1: this GEMM runs concurrently with the main stream's backward GEMMs)
+                prev_lane = ops.lib().cxn_gemm_workspace_lane(1)
+                try:
+                    ops.gemm(gy_ptr, sh.ld_out, 0, 1, sh.x_all.data_ptr(), sh.ld_in, 0, 1, g_ptr, nin, 0, None, 0,
+                             sh.my_rows, nin, total_b, flags=ops.GEMM_BETA1 if acc else 0)
+                finally:
+                    ops.lib().cxn_gemm_workspace_lane(max(prev_lane, 0))
             if sh.bseg is not None:
                 ops.check(ops.lib().cxn_colsum_bf16(sh.gy_all.data_ptr(), total_b, nout, sh.ld_out,
                                                      a.g.data_ptr() + sh.bseg.start * 4, 1 if acc else 0,
@@ -281,11 +286,11 @@ class GradExchange:
 
     def gather_master(self) -> None:
         """refresh the fp32 masters of foreign weight shards from their owners (collective)."""
+        self.wait_all()          # bucket kernels still pending on the exchange stream write arena.w
         if not self.shards:
             return
         import torch.distributed as dist
         from .symm import _RawCudaBuffer
-        self.wait_all()
         torch.cuda.synchronize(self.device)
         dist.barrier()
         a = self.arena

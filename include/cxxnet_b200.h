@@ -36,6 +36,11 @@ int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a_mn, con
  * cl = 2 | 4 column tiles that share the activation tile by TMA multicast (0 = off, -1 = re-read CXN_GEMM_CLUSTER).
  * No reference counterpart. */
 int cxn_gemm_cluster(int cl);
+/* The internally split GEMMs (skinny fully connected shapes) meet in a zeroed fp32 scratch buffer; a device has
+ * four independent ones ("lanes").  Selects the lane used by the calling thread's following cxn_gemm_bf16 calls
+ * (default 0) and returns the previous one, -1 for an invalid lane.  GEMMs that can run concurrently (different
+ * streams, or parallel branches of a captured graph) must use different lanes.  No reference counterpart. */
+int cxn_gemm_workspace_lane(int lane);
 
 /* K1 (and K2 for stride-1 layers): implicit-GEMM convolution forward, bias (+ReLU) fused.
  * Reference: src/layer/convolution_layer-inl.hpp:79-105. */

@@ -175,3 +175,20 @@ def test_halo_tile_planning_takes_conv2_backward_data():
     assert L.cxn_conv_halo_plan(8, 27, 27, 96, 48, 2, 128, 5, 5, 1, 2, 2, 27, 27, 2, out) == 0
     assert L.cxn_conv_halo_plan(8, 13, 13, 256, 256, 1, 384, 3, 3, 1, 1, 1, 13, 13, 2, out) == 0
     assert L.cxn_conv_halo_plan(8, 200, 200, 64, 64, 1, 32, 3, 3, 1, 1, 1, 200, 200, 2, out) == 0
+
+
+def test_momentum_schedule_is_evaluated_once_per_update():
+    """schedule_epoch ADDS to the momentum under momentum_schedule (reference param.h:76-94): building the arena
+    must not count as an update, so the trajectory equals one evaluation per update like the ref backend's"""
+    from cxxnet_b200.parallel.arena import ParamArena
+    kv = dict(lr=0.01, momentum=0.5, momentum_schedule=1, base_momentum=0.5, final_momentum=0.9, saturation_epoch=10)
+    a = ParamArena(torch.device("cpu"), "sgd")
+    s = a.add(None, 0, "wmat", 4, 256, 256, _param("wmat", **kv))
+    a.upload_hyper = lambda slot=0: None
+    a.finalize()
+    twin = _param("wmat", **kv)
+    assert s.param.momentum == twin.momentum          # untouched by finalize()
+    for epoch in range(4):
+        a.prepare_hyper(epoch, epoch & 1)
+        twin.schedule_epoch(epoch)
+        assert s.param.momentum == twin.momentum

@@ -10,7 +10,8 @@ the library image instead and refuses bucket slots beyond that.
 
 The test drives both entry points through the plain C ABI (ctypes on the shared library, raw
 device pointers), as a single-rank exchange so one GPU is enough, and requires identical
-results on two consecutive calls.  It lives in its own file, collected last, so that a
+results on two consecutive calls - identical to each other and to the sgd step written out in plain
+fp32 PyTorch.  It lives in its own file, collected last, so that a
 `pytest -x` run has already executed every other test if this one fails; it does not depend on
 state left by them (fresh buffers, and the entry point clears its scratch word before use).
 """
@@ -91,8 +92,11 @@ def test_no_alloc_entry_point_matches_regular_entry_point():
     counter = torch.zeros(4, dtype=torch.int32, device="cuda")       # the scratch the regular entry point needs
     stream = torch.cuda.current_stream().cuda_stream
     slot = 3
+    w_ref, m_ref = w0.clone(), torch.zeros_like(w0)                  # closed-form sgd: lr 0.05, wd 0.001, momentum 0.9
     for call in range(2):                                            # two calls in a row
         g = torch.randn(a.total, device="cuda")
+        m_ref = 0.9 * m_ref - 0.05 * (g + 0.001 * w_ref)
+        w_ref = w_ref + m_ref
         a.g.copy_(g)
         b.g.copy_(g)
         seq = call + 1
@@ -105,6 +109,9 @@ def test_no_alloc_entry_point_matches_regular_entry_point():
             assert torch.allclose(a.w[st:st + n], b.w[st:st + n], atol=1e-6, rtol=0), "weights differ (call %d)" % call
             assert torch.allclose(a.m[st:st + n], b.m[st:st + n], atol=1e-6, rtol=0), "momentum differs (call %d)" % call
             assert float(a.g[st:st + n].abs().max()) == 0.0 and float(b.g[st:st + n].abs().max()) == 0.0  # consumed
+            # both entry points against the update written out in plain fp32 PyTorch
+            assert torch.allclose(b.w[st:st + n], w_ref[st:st + n], atol=1e-5, rtol=1e-5), "closed form (call %d)" % call
+            assert torch.allclose(a.w[st:st + n], w_ref[st:st + n], atol=1e-5, rtol=1e-5)
         assert torch.equal(a.shadow, b.shadow)
         assert not torch.equal(b.w, w0)                                             # and something happened
     assert int(counter[0]) == 0                                      # the regular entry point left its scratch zeroed
