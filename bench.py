@@ -144,8 +144,10 @@ def run_ours(args, rank, world, local):
     extra = args.extra
     if "cuda_graph" not in extra:
         extra += "\ncuda_graph = 1\n"        # one captured graph per step instead of ~80 launches
-    if world > 1 and "fullc_gather" not in extra:
-        extra += "\nfullc_gather = 1\n"      # the reference's own option for fully connected layers on several GPUs
+    if world > 1 and "fullc_gather" not in extra and "fullc_shard" not in extra:
+        # fully connected layers sharded by output columns over the ranks (weights never cross a link); the
+        # reference's own option for these layers, `fullc_gather = 1`, remains available through --extra
+        extra += "\nfullc_shard = 1\n"
     for k, v in parse_config_string(alexnet_conf(batch_size=B, dev=dev, extra=extra)):
         tr.set_param(k, v)
     tr.set_param("silent", "1")
@@ -208,7 +210,9 @@ def run_ours(args, rank, world, local):
         "scaling": args.scaling, "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
         "config": {"model": "AlexNet (example/ImageNet/ImageNet.conf)", "global_batch": B,
                    "input": "3x227x227 (%s NCHW batches from the iterator, fp32 labels)" % args.input,
-                   "per_gpu_batch": hi - lo, "parallelism": "dp%d" % world, "updater": "sgd momentum 0.9 wd 5e-4",
+                   "per_gpu_batch": hi - lo,
+                   "parallelism": ("dp%d" % world) if (world == 1 or "fullc_shard" not in extra) else
+                                  ("dp%d (conv) + tp%d (fc6-8 column-sharded)" % (world, world)), "updater": "sgd momentum 0.9 wd 5e-4",
                    "l2": "no flush: per-step working set (activations + im2col + 244 MB weights) far exceeds "
                          "the 126 MB L2; e2e rotates 3 distinct 79 MB (bf16) input batches",
                    "timing": "CUDA events around K steps, barrier+synchronize both sides, max over ranks",
@@ -284,7 +288,12 @@ def verify_multi(args, rank, world, local, extra):
         # what moved: w - w0 is small against w, so the weights alone would hide a wrong update
         da, dc = a - w0[(i, tag)], c - w0[(i, tag)]
         denom = float(dc.abs().sum())
-        worst_dw = max(worst_dw, float((da - dc).abs().sum()) / denom if denom > 0 else float((da - dc).abs().sum()))
+        e_dw = float((da - dc).abs().sum()) / denom if denom > 0 else float((da - dc).abs().sum())
+        worst_dw = max(worst_dw, e_dw)
+        if rank == 0:
+            sys.stderr.write("verify %s.%s: |w| %.4g  rel err w %.3g  rel err (w - w0) %.3g\n" % (
+                multi.net_cfg.layers[i].name or i, tag, float(c.abs().sum()),
+                float((a - c).abs().sum()) / max(float(c.abs().sum()), 1e-30), e_dw))
     t = torch.tensor([worst_w, worst_dw], dtype=torch.float64, device="cuda")
     import torch.distributed as dist
     dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -30,6 +30,7 @@ CONFIGS = [("gather 128-row", dict(atma=0, mh=1, stages=-1)),
            ("auto + cluster", dict(atma=-1, mh=0, stages=0, cluster=2, extra=1)),
            ("tma 128-row + cluster", dict(atma=1, mh=1, stages=-1, cluster=2, extra=1)),
            ("auto + fill", dict(atma=-1, mh=0, stages=0, fill=1, extra=1)),
+           ("cta pairs", dict(atma=-1, mh=0, stages=0, pair=2, extra=1)),
            ("halo 2 halves", dict(atma=-1, mh=0, stages=0, halo=1, extra=1)),
            ("halo 1 half", dict(atma=-1, mh=0, stages=0, halo=2, extra=1))]
 if os.environ.get("EXTRA", "0") != "1":
@@ -49,6 +50,7 @@ def set_knobs(c, ocg):
     L.cxn_conv_tune(7, c.get("cluster", 0))
     L.cxn_conv_tune(8, c.get("fill", 0))
     L.cxn_conv_tune(9, c.get("halo", 0))
+    L.cxn_conv_tune(10, c.get("pair", 0))
 
 
 def reset_knobs():
@@ -57,6 +59,7 @@ def reset_knobs():
     L.cxn_conv_tune(7, 0)
     L.cxn_conv_tune(8, 0)
     L.cxn_conv_tune(9, 0)
+    L.cxn_conv_tune(10, 0)
 
 
 def timeit(run, iters=10):

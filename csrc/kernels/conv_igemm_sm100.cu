@@ -892,6 +892,247 @@ conv_fprop_cluster_kernel(const __grid_constant__ CUtensorMap tmHalf, const __gr
 }
 
 // ===================================================================================================
+// CTA-pair variant of the forward kernel (tcgen05 cta_group::2; cxn_conv_tune(10, 1) or CXN_CONV_PAIR2=1).
+// The large stride-1 layers run at the chip-wide L2 -> SM throughput ceiling (profiles/): per k-block a 128 x bn
+// tile pulls 16 KB of patches and bn x 128 B of filter into its SM.  Here the two CTAs of a cluster (the two SMs of
+// a TPC) compute ONE 256-row x bn tile with M = 256 MMAs: each CTA fetches its own 128 output positions (im2col TMA)
+// and HALF of the filter tile (bn / 2 rows), the tensor core reads both halves across the pair, and each CTA
+// receives its 128 rows of the accumulator in its own tensor memory.  Filter bytes per SM halve; nothing is
+// multicast.  Protocol as gemm_pair_kernel (gemm_sm100.cu): full barriers in the leader armed with both CTAs'
+// bytes, empty / tfull by multicast commit, tempty in the leader with arrivals from both CTAs' epilogue warps.
+template <int BNMAX>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kClusterThreads, 1)
+conv_fprop_pair_kernel(const __grid_constant__ CUtensorMap tmHalf, const __grid_constant__ CUtensorMap tmPatch,
+                       const Params p) {
+  constexpr int kAccStages = 2;
+  constexpr int kABytes = BM * BK * 2;
+  constexpr int kBHalfBytes = (BNMAX / 2) * BK * 2;
+  constexpr int kStageBytes = kABytes + kBHalfBytes;
+  constexpr int kTmemCols = kAccStages * BNMAX;
+  constexpr int BMT = 2 * BM;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int nst = p.stages;
+  const uint32_t bar_base = smem_base + (uint32_t)p.ring_bytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (nst + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * nst + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * nst + kAccStages + a); };
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + p.ring_bytes + 8 * (2 * nst + 2 * kAccStages + 1));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t crank = cluster_ctarank();
+  const bool leader = crank == 0;
+  const long long rows = (long long)p.N * p.OH * p.OW;
+  const int tiles_m = (int)ceil_div_ll(rows, BMT);
+  const int tiles_n = ceil_div(p.Ng, p.bn);
+  const int num_kb = ceil_div(p.Kg, BK);
+  const long long total_tiles = (long long)tiles_m * tiles_n * p.G;
+  const long long pair0 = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const int half_rows = p.bn >> 1;               // filter rows each CTA stages
+  const int cpk = p.Cg >> 6;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < nst; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < kAccStages; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 8);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmHalf) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmPatch) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32((const void*)tmem_ptr_smem)),
+                 "n"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  auto decode_tile = [&](long long t, int& n_blk, int& m_blk, int& g) {
+    n_blk = (int)(t % tiles_n);
+    const long long r = t / tiles_n;
+    m_blk = (int)(r % tiles_m);
+    g = (int)(r / tiles_m);
+  };
+
+  if (warp == 0) {
+    // =========================== TMA producer (both CTAs) ===========================
+    int stage = 0;
+    uint32_t phase = 0;
+    const int ohw = p.OH * p.OW;
+    for (long long t = pair0; t < total_tiles; t += npairs) {
+      int n_blk, m_blk, g;
+      decode_tile(t, n_blk, m_blk, g);
+      // first output position of this CTA's 128 rows -> (w, h, n) of its tap-(0,0) input pixel; a position past the
+      // last image reads out of bounds = zeros
+      const long long m0 = (long long)m_blk * BMT + (long long)crank * BM;
+      const int pn = (int)(m0 / ohw);
+      const int r = (int)(m0 - (long long)pn * ohw);
+      const int oh = r / p.OW;
+      const int pw = (r - oh * p.OW) * p.stride_x - p.pad_x;
+      const int ph = oh * p.stride_y - p.pad_y;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait_warp(empty_bar(stage), phase ^ 1u);
+        const uint32_t sa = smem_base + stage * (uint32_t)kStageBytes;
+        const uint32_t sb = sa + kABytes;
+        if (elect_one()) {
+          if (leader) mbar_expect_tx(full_bar(stage), 2u * ((uint32_t)kABytes + (uint32_t)half_rows * BK * 2));
+          const int tap = kb / cpk, chunk = kb - tap * cpk;
+          const int kh = tap / p.KW, kw = tap - kh * p.KW;
+          tma_load_im2col_4d_2cta(sa, &tmPatch, full_bar(stage), g * p.Cg + chunk * 64, pw, ph, pn, kw, kh);
+          tma_load_3d_2cta(sb, &tmHalf, full_bar(stage), kb * BK, n_blk * p.bn + (int)crank * half_rows, g);
+        }
+        __syncwarp();
+        if (++stage == nst) { stage = 0; phase ^= 1u; }
+      }
+    }
+    for (int i = 0; i < nst; ++i) {     // tail: the multicast commits for everything this CTA staged have arrived
+      mbar_wait_warp(empty_bar(stage), phase ^ 1u);
+      if (++stage == nst) { stage = 0; phase ^= 1u; }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA issuer (leader only) ===========================
+    if (leader) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(BMT >> 4) << 24);
+      constexpr uint32_t kSbo = 1024;
+      constexpr uint32_t kStep = UMMA_K * 2;
+      const uint64_t desc_hi = make_desc(0, 0u, kSbo);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (long long t = pair0; t < total_tiles; t += npairs) {
+        mbar_wait_warp(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BNMAX);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait_warp(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * (uint32_t)kStageBytes;
+          const uint32_t sb = sa + kABytes;
+          if (elect_one()) {
+            const uint64_t a0 = desc_hi | (uint64_t)((sa >> 4) & 0x3FFF), b0 = desc_hi | (uint64_t)((sb >> 4) & 0x3FFF);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma_bf16_2cta(d_tmem, a0 + (uint64_t)((k * kStep) >> 4), b0 + (uint64_t)((k * kStep) >> 4), idesc,
+                             (kb > 0 || k > 0) ? 1u : 0u);
+            umma_commit_2cta(empty_bar(stage), (uint16_t)0x3);
+            if (kb == num_kb - 1) umma_commit_2cta(tfull_bar(acc), (uint16_t)0x3);
+          }
+          __syncwarp();
+          if (++stage == nst) { stage = 0; phase ^= 1u; }
+        }
+        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // =========================== epilogue (both CTAs, own 128 rows) ===========================
+    const int quad = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (long long t = pair0; t < total_tiles; t += npairs) {
+      int n_blk, m_blk, g;
+      decode_tile(t, n_blk, m_blk, g);
+      mbar_wait_warp(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const float* bias = p.bias != nullptr ? p.bias + (long long)g * p.Ng : nullptr;
+      const long long row = (long long)m_blk * BMT + (long long)crank * BM + quad * 32 + lane;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BNMAX; c0 += 32) {
+        if (c0 >= p.bn) break;
+        const int n0 = n_blk * p.bn + c0;
+        if (n0 >= p.Ng) break;
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BNMAX + c0);
+        tmem_ld32(taddr, v);
+        tmem_ld_wait();
+        if (row >= rows) continue;
+        const int lim = min(32, min(p.bn - c0, p.Ng - n0));
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        const long long off = (long long)g * p.strideD + row * p.ldd + n0;
+        if (bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < lim) f[j] += __ldg(bias + n0 + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+        }
+        if (p.mask != nullptr) {
+          const bf16* mk = p.mask + off;
+          if (lim == 32 && ((reinterpret_cast<uintptr_t>(mk) & 15) == 0)) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint4 mv = *reinterpret_cast<const uint4*>(mk + 8 * q);
+              const __nv_bfloat162* mh2 = reinterpret_cast<const __nv_bfloat162*>(&mv);
+#pragma unroll
+              for (int tt = 0; tt < 4; ++tt) {
+                const float2 m2 = __bfloat1622float2(mh2[tt]);
+                if (!(m2.x > 0.0f)) f[q * 8 + 2 * tt] = 0.0f;
+                if (!(m2.y > 0.0f)) f[q * 8 + 2 * tt + 1] = 0.0f;
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < lim && !(__bfloat162float(mk[j]) > 0.0f)) f[j] = 0.0f;
+          }
+        }
+        bf16* d = reinterpret_cast<bf16*>(p.D) + off;
+        if (lim == 32 && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+          uint4* d4 = reinterpret_cast<uint4*>(d);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(f[q * 8 + 0], f[q * 8 + 1]);
+            __nv_bfloat162 h1 = __floats2bfloat162_rn(f[q * 8 + 2], f[q * 8 + 3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(f[q * 8 + 4], f[q * 8 + 5]);
+            __nv_bfloat162 h3 = __floats2bfloat162_rn(f[q * 8 + 6], f[q * 8 + 7]);
+            uint4 u;
+            u.x = *reinterpret_cast<uint32_t*>(&h0);
+            u.y = *reinterpret_cast<uint32_t*>(&h1);
+            u.z = *reinterpret_cast<uint32_t*>(&h2);
+            u.w = *reinterpret_cast<uint32_t*>(&h3);
+            d4[q] = u;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < lim) d[j] = __float2bfloat16(f[j]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
+  }
+}
+
+// ===================================================================================================
 // Halo-tile variant of the forward kernel for stride-1 convolutions with few output columns (opt-in:
 // cxn_conv_tune(9, 1) or CXN_CONV_HALO=1; built for conv2's backward-data problem: 5x5, 128 -> 48 channels).
 // The im2col routes fetch every input element once per filter tap.  Here the GEMM rows enumerate the output over the
@@ -1317,6 +1558,32 @@ static int launch_cluster(const CUtensorMap& tm_half, const CUtensorMap& tmp, co
   CXN_CHECK_LAUNCH();
   return 0;
 }
+template <int BNMAX>
+static int launch_pair(const CUtensorMap& tm_half, const CUtensorMap& tmp, const Params& p, int grid, cudaStream_t st) {
+  constexpr int kStageBytes = BM * BK * 2 + (BNMAX / 2) * BK * 2;
+  if (p.stages < 2 || p.stages > 8 || (grid & 1)) return -20;
+  if (p.ring_bytes < p.stages * kStageBytes || (p.ring_bytes & 1023)) return -22;
+  const int smem = p.ring_bytes + 1024 + 256;
+  if (smem > 232448) return -23;
+  static int max_set = 0;
+  if (smem > max_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_fprop_pair_kernel<BNMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return (int)e;
+    max_set = smem;
+  }
+  conv_fprop_pair_kernel<BNMAX><<<grid, kClusterThreads, smem, st>>>(tm_half, tmp, p);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+static int g_tune_pair = -1;       // 1: CTA pairs (cta_group::2) for forward problems on the im2col-TMA route with
+                                   // more than 128 output columns per group; -1 = read CXN_CONV_PAIR2
+static int pair_mode() {
+  if (g_tune_pair < 0) {
+    const char* e = getenv("CXN_CONV_PAIR2");
+    g_tune_pair = e ? atoi(e) : 0;
+  }
+  return g_tune_pair;
+}
 // NHWC tensor as a tiled 4-D map: box {64 channels, box_w pixels, box_h rows, 1 image}, zero fill outside
 static int encode_tile4d(CUtensorMap* out, const Params& p, int box_w, int box_h) {
   EncodeTiledFn enc = get_encode();
@@ -1522,6 +1789,27 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
       return hmh == 2 ? launch_halo<2>(tm, tmt, p, hg, smem_h, hgrid, st) : launch_halo<1>(tm, tmt, p, hg, smem_h, hgrid, st);
     }
   }
+  if (pair_mode() >= 1 && atma && !(p.bn & 15) && num_sms() >= 2 &&
+      (pair_mode() == 2 || (!p.b_resident && Ng > 128 && ceil_div_ll(rows, 2 * BM) * ceil_div(Ng, p.bn) * G >= num_sms() / 2))) {
+    // CTA pairs: one 256-row x bn tile per pair, every CTA stages its own 128 positions and half of the filter tile
+    Params pp = p;
+    const int pbn = p.bn;
+    const int bnmax_p = pbn > 128 ? 256 : 128;
+    const int stage_b = BM * BK * 2 + (bnmax_p / 2) * BK * 2;
+    int st_fit = (232448 - 1024 - 256) / stage_b;
+    if (st_fit > 8) st_fit = 8;
+    pp.stages = g_tune_stages ? (g_tune_stages < st_fit ? g_tune_stages : st_fit) : st_fit;
+    pp.ring_bytes = pp.stages * stage_b;
+    CUtensorMap tmh, tmp1;
+    rc = encode3d(&tmh, w, (uint64_t)p.Kg, (uint64_t)Ng, (uint64_t)G, (uint64_t)ldw, (uint64_t)Ng * ldw, BK, pbn / 2);
+    if (rc) return rc;
+    rc = encode_im2col(&tmp1, pp, BM);
+    if (rc) return rc;
+    const long long ptiles = ceil_div_ll(rows, 2 * BM) * ceil_div(Ng, pbn) * G;
+    const long long max_pairs = num_sms() / 2;
+    const int grid_p = 2 * (int)(ptiles < max_pairs ? ptiles : max_pairs);
+    return bnmax_p == 256 ? launch_pair<256>(tmh, tmp1, pp, grid_p, st) : launch_pair<128>(tmh, tmp1, pp, grid_p, st);
+  }
   const long long tiles_m = ceil_div_ll(rows, mh * BM);
   if (cluster_mode() == 2 && atma && !p.b_resident && tiles_m >= 2 && num_sms() >= 2 &&
       memory_is_local(w, (size_t)G * (size_t)Ng * (size_t)ldw * sizeof(bf16))) {   // multicast map: own memory only
@@ -1565,6 +1853,8 @@ CXN_API int cxn_conv_halo_plan(int N, int H, int W, int Cs, int Cg, int G, int N
 //   5: timing experiments   6: im2col TMA on / off   7: 2 = CTA-pair clusters with a multicast filter tile (forward)
 //   8: 1 = narrower column tiles when the forward grid would not fill the machine
 //   9: 1 | 2 = halo-tile kernel (two | one 128-row halves per tile) for stride-1 problems with <= 64 output columns
+//  10: 1 = CTA pairs (cta_group::2 MMAs, each CTA stages half of the filter tile) for im2col-TMA forward problems with
+//      more than 128 output columns per group and at least one tile per SM pair; 2 = whenever legal; -1 = CXN_CONV_PAIR2
 // Role profiling of the forward kernel: buf = device array of [148][16] int64 (null switches it off).
 // slots: 0 TMA wait-empty, 1 TMA total | 2 MMA wait-full, 3 MMA wait-tmem-empty, 4 MMA total |
 // 5 gather wait-empty, 6 gather tile setup, 7 gather total | 8 epilogue wait-tmem-full, 9 epilogue body, 10 total
@@ -1585,6 +1875,7 @@ CXN_API int cxn_conv_tune(int key, int value) {
     case 7: g_tune_cluster = value; break;
     case 8: g_tune_fill = value; break;
     case 9: g_tune_halo = value; break;
+    case 10: g_tune_pair = value; break;
     default: return -1;
   }
   return 0;

@@ -62,6 +62,122 @@ struct Cfg {
 
 using namespace cxn::tc;
 
+// One 32-column chunk of an accumulator tile, held one row per lane (v[j] = column n0 + j of row row0 + lane):
+// bias / ReLU / conversion and the store, reduction or read-modify-write into D.  `warp_stage` is this warp's
+// 32 x 36 float staging area (fp32 results pass through a shared-memory transpose so that every store instruction
+// covers complete 128-byte row segments).
+__device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&v)[32], int row0, int lane, int n0,
+                                               bool has_work, const float* bias, int z, float* warp_stage) {
+  const bool relu = p.flags & kFlagRelu;
+  const bool out_bf16 = p.flags & kFlagOutBf16;
+  const bool atomic = p.flags & kFlagAtomic;
+  const bool beta1 = p.flags & kFlagBeta1;
+  const int row = row0 + lane;
+  const bool row_ok = row < p.M;
+  const bool full = (n0 + 32 <= p.N);
+  // fp32 results (weight gradients) go through a shared-memory transpose: a thread owns a row of the
+  // accumulator, so direct stores put 32 rows x 16 bytes into every instruction; staged, each
+  // instruction writes four complete 128-byte row segments.
+  if (!out_bf16 && !atomic && full && bias == nullptr && !relu && (p.ldd & 3) == 0 &&
+      ((reinterpret_cast<uintptr_t>(p.D) & 15) == 0) && (p.strideD & 3) == 0) {
+    float* sm = warp_stage;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      float4 o4;
+      o4.x = has_work ? __uint_as_float(v[4 * q]) : 0.0f;
+      o4.y = has_work ? __uint_as_float(v[4 * q + 1]) : 0.0f;
+      o4.z = has_work ? __uint_as_float(v[4 * q + 2]) : 0.0f;
+      o4.w = has_work ? __uint_as_float(v[4 * q + 3]) : 0.0f;
+      *reinterpret_cast<float4*>(sm + lane * 36 + 4 * q) = o4;
+    }
+    __syncwarp();
+    const int rsub = lane >> 3, cq = (lane & 7) * 4;
+    float* dbase = reinterpret_cast<float*>(p.D) + (long long)z * p.strideD + n0 + cq;
+    
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int r = it * 4 + rsub;
+      if (row0 + r < p.M) {
+        float4 o4 = *reinterpret_cast<const float4*>(sm + r * 36 + cq);
+        float4* dp = reinterpret_cast<float4*>(dbase + (long long)(row0 + r) * p.ldd);
+        if (beta1) {
+          const float4 c4 = *dp;
+          o4.x += c4.x; o4.y += c4.y; o4.z += c4.z; o4.w += c4.w;
+        }
+        *dp = o4;
+      }
+    }
+    __syncwarp();
+    return;
+  }
+  if (!row_ok) return;
+  float f[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) f[j] = has_work ? __uint_as_float(v[j]) : 0.0f;
+  if (bias != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (full || n0 + j < p.N) f[j] += __ldg(bias + n0 + j);
+  }
+  if (relu) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+  }
+  const long long off = (long long)z * p.strideD + (long long)row * p.ldd + n0;
+  if (out_bf16) {
+    bf16* d = reinterpret_cast<bf16*>(p.D) + off;
+    if (full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+      uint4* d4 = reinterpret_cast<uint4*>(d);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(f[q * 8 + 0], f[q * 8 + 1]);
+        __nv_bfloat162 h1 = __floats2bfloat162_rn(f[q * 8 + 2], f[q * 8 + 3]);
+        __nv_bfloat162 h2 = __floats2bfloat162_rn(f[q * 8 + 4], f[q * 8 + 5]);
+        __nv_bfloat162 h3 = __floats2bfloat162_rn(f[q * 8 + 6], f[q * 8 + 7]);
+        uint4 u;
+        u.x = *reinterpret_cast<uint32_t*>(&h0);
+        u.y = *reinterpret_cast<uint32_t*>(&h1);
+        u.z = *reinterpret_cast<uint32_t*>(&h2);
+        u.w = *reinterpret_cast<uint32_t*>(&h3);
+        d4[q] = u;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (n0 + j < p.N) d[j] = __float2bfloat16(f[j]);
+    }
+  } else {
+    float* d = reinterpret_cast<float*>(p.D) + off;
+    if (atomic && full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+      // 128-bit reductions: a quarter of the L2 atomic operations of the scalar form
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + 4 * q), "f"(f[4 * q]),
+                     "f"(f[4 * q + 1]), "f"(f[4 * q + 2]), "f"(f[4 * q + 3])
+                     : "memory");
+    } else if (atomic) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (full || n0 + j < p.N) atomicAdd(d + j, f[j]);
+    } else if (full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+      float4* d4 = reinterpret_cast<float4*>(d);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        float4 o = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
+        if (beta1) {
+          const float4 c = d4[q];
+          o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
+        }
+        d4[q] = o;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (n0 + j < p.N) d[j] = beta1 ? d[j] + f[j] : f[j];
+    }
+  }
+}
+
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
@@ -201,10 +317,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int quad = warp & 3;  // TMEM lane quadrant this warp may read
     int acc = 0;
     uint32_t acc_phase = 0;
-    const bool relu = p.flags & kFlagRelu;
-    const bool out_bf16 = p.flags & kFlagOutBf16;
-    const bool atomic = p.flags & kFlagAtomic;
-    const bool beta1 = p.flags & kFlagBeta1;
     for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       long long r = t;
       const int n_blk = (int)(r % tiles_n); r /= tiles_n;
@@ -215,8 +327,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int kb1 = min(num_kb, kb0 + p.kb_per_split);
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
-      const int row = m_blk * BM + quad * 32 + lane;
-      const bool row_ok = row < p.M;
       const bool has_work = kb1 > kb0;
       const float* bias = (p.bias != nullptr && split == 0) ? p.bias + (long long)z * p.strideBias : nullptr;
 #pragma unroll 1
@@ -227,108 +337,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
         tmem_ld32(taddr, v);
         tmem_ld_wait();
-        const bool full = (n0 + 32 <= p.N);
-        // fp32 results (weight gradients) go through a shared-memory transpose: a thread owns a row of the
-        // accumulator, so direct stores put 32 rows x 16 bytes into every instruction; staged, each
-        // instruction writes four complete 128-byte row segments.
-        if (!out_bf16 && !atomic && full && bias == nullptr && !relu && (p.ldd & 3) == 0 &&
-            ((reinterpret_cast<uintptr_t>(p.D) & 15) == 0) && (p.strideD & 3) == 0) {
-          float* sm = stage_out + (warp - 2) * (32 * 36);
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            float4 o4;
-            o4.x = has_work ? __uint_as_float(v[4 * q]) : 0.0f;
-            o4.y = has_work ? __uint_as_float(v[4 * q + 1]) : 0.0f;
-            o4.z = has_work ? __uint_as_float(v[4 * q + 2]) : 0.0f;
-            o4.w = has_work ? __uint_as_float(v[4 * q + 3]) : 0.0f;
-            *reinterpret_cast<float4*>(sm + lane * 36 + 4 * q) = o4;
-          }
-          __syncwarp();
-          const int rsub = lane >> 3, cq = (lane & 7) * 4;
-          float* dbase = reinterpret_cast<float*>(p.D) + (long long)z * p.strideD + n0 + cq;
-          const int row0 = m_blk * BM + quad * 32;
-#pragma unroll
-          for (int it = 0; it < 8; ++it) {
-            const int r = it * 4 + rsub;
-            if (row0 + r < p.M) {
-              float4 o4 = *reinterpret_cast<const float4*>(sm + r * 36 + cq);
-              float4* dp = reinterpret_cast<float4*>(dbase + (long long)(row0 + r) * p.ldd);
-              if (beta1) {
-                const float4 c4 = *dp;
-                o4.x += c4.x; o4.y += c4.y; o4.z += c4.z; o4.w += c4.w;
-              }
-              *dp = o4;
-            }
-          }
-          __syncwarp();
-          continue;
-        }
-        if (!row_ok) continue;
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = has_work ? __uint_as_float(v[j]) : 0.0f;
-        if (bias != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (full || n0 + j < p.N) f[j] += __ldg(bias + n0 + j);
-        }
-        if (relu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
-        }
-        const long long off = (long long)z * p.strideD + (long long)row * p.ldd + n0;
-        if (out_bf16) {
-          bf16* d = reinterpret_cast<bf16*>(p.D) + off;
-          if (full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
-            uint4* d4 = reinterpret_cast<uint4*>(d);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              __nv_bfloat162 h0 = __floats2bfloat162_rn(f[q * 8 + 0], f[q * 8 + 1]);
-              __nv_bfloat162 h1 = __floats2bfloat162_rn(f[q * 8 + 2], f[q * 8 + 3]);
-              __nv_bfloat162 h2 = __floats2bfloat162_rn(f[q * 8 + 4], f[q * 8 + 5]);
-              __nv_bfloat162 h3 = __floats2bfloat162_rn(f[q * 8 + 6], f[q * 8 + 7]);
-              uint4 u;
-              u.x = *reinterpret_cast<uint32_t*>(&h0);
-              u.y = *reinterpret_cast<uint32_t*>(&h1);
-              u.z = *reinterpret_cast<uint32_t*>(&h2);
-              u.w = *reinterpret_cast<uint32_t*>(&h3);
-              d4[q] = u;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (n0 + j < p.N) d[j] = __float2bfloat16(f[j]);
-          }
-        } else {
-          float* d = reinterpret_cast<float*>(p.D) + off;
-          if (atomic && full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
-            // 128-bit reductions: a quarter of the L2 atomic operations of the scalar form
-#pragma unroll
-            for (int q = 0; q < 8; ++q)
-              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d + 4 * q), "f"(f[4 * q]),
-                           "f"(f[4 * q + 1]), "f"(f[4 * q + 2]), "f"(f[4 * q + 3])
-                           : "memory");
-          } else if (atomic) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (full || n0 + j < p.N) atomicAdd(d + j, f[j]);
-          } else if (full && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
-            float4* d4 = reinterpret_cast<float4*>(d);
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-              float4 o = make_float4(f[q * 4], f[q * 4 + 1], f[q * 4 + 2], f[q * 4 + 3]);
-              if (beta1) {
-                const float4 c = d4[q];
-                o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w;
-              }
-              d4[q] = o;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (n0 + j < p.N) d[j] = beta1 ? d[j] + f[j] : f[j];
-          }
-        }
+        epilogue_chunk(p, v, m_blk * BM + quad * 32, lane, n0, has_work, bias, z, stage_out + (warp - 2) * (32 * 36));
       }
       tc_fence_before();
       __syncwarp();
@@ -343,6 +352,213 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::kTmemCols)
                  : "memory");
+  }
+}
+
+// ===================================================================================================
+// CTA-pair variant (tcgen05 cta_group::2) for large problems: the two CTAs of a cluster - the two SMs of one TPC -
+// compute one 256 x 256 tile with ONE stream of M = 256 MMAs.  Each CTA loads its own 128 rows of A and HALF of the
+// B tile (128 of the 256 columns) and receives its 128 rows of the accumulator in its own tensor memory: per SM and
+// k-block 32 KB arrive from L2 for 128 x 256 outputs where the single-CTA 128 x 256 tile needs 48 KB.  The large
+// layers sit on the chip-wide L2 -> SM throughput ceiling (profiles/), so bytes per FLOP is what this buys.
+//
+// Protocol (CTA 0 of the pair = leader):
+//   full[s]   lives in the leader.  Its producer arms it with the bytes of BOTH CTAs' loads; every load of either CTA
+//             (cp.async.bulk.tensor ... .cta_group::2, barrier address with the peer bit cleared) reports there.
+//   empty[s]  one per CTA, count 1: the leader's tcgen05.commit.cta_group::2 ... multicast arrives on both.
+//   tfull[a]  one per CTA, count 1: the same multicast commit after a tile's last MMA; each CTA's epilogue warps read
+//             their own tensor memory.
+//   tempty[a] in the leader, count 8: four epilogue warps of each CTA arrive (the peer's through shared::cluster).
+// Tensor memory is allocated and freed by warp 1 of both CTAs (cta_group::2); cluster barriers bracket the kernel
+// so that neither CTA's shared memory, barriers or tensor memory is touched after it has gone.
+template <bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
+  constexpr int BN = 256;            // tile width of the pair; each CTA stages BN / 2 columns of B
+  constexpr int BNH = BN / 2;
+  constexpr int BM2 = 2 * BM;
+  using C = Cfg<BNH>;                // per-CTA ring: 128 x 64 of A + 128 x 64 of B per stage
+  constexpr int kTmemCols = kAccStages * BN;     // 512: two 256-column accumulators
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t bar_base = smem_base + C::kStages * C::kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (C::kStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * C::kStages + kAccStages + a); };
+  volatile uint32_t* tmem_ptr_smem =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + C::kStages * C::kStageBytes + 8 * (2 * C::kStages + 2 * kAccStages));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t crank = cluster_ctarank();
+  const bool leader = crank == 0;
+  float* stage_out = reinterpret_cast<float*>(smem_gen + C::kStages * C::kStageBytes + 256);
+
+  const int tiles_m = ceil_div(p.M, BM2);
+  const int tiles_n = ceil_div(p.N, BN);
+  const int num_kb = ceil_div(p.K, BK);
+  const long long total_tiles = (long long)tiles_m * tiles_n * p.batch * p.splits;
+  const long long pair0 = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < kAccStages; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 8);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmB) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32((const void*)tmem_ptr_smem)),
+                 "n"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();              // both CTAs' barriers exist before anything arrives on them
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // =========================== TMA producer (both CTAs) ===========================
+    int stage = 0;
+    uint32_t phase = 0;
+    for (long long t = pair0; t < total_tiles; t += npairs) {
+      long long r = t;
+      const int n_blk = (int)(r % tiles_n); r /= tiles_n;
+      const int m_blk = (int)(r % tiles_m); r /= tiles_m;
+      const int split = (int)(r % p.splits);
+      const int z = (int)(r / p.splits);
+      const int kb0 = split * p.kb_per_split;
+      const int kb1 = min(num_kb, kb0 + p.kb_per_split);
+      const int m0 = m_blk * BM2 + (int)crank * BM;
+      const int n0 = n_blk * BN + (int)crank * BNH;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const uint32_t sa = smem_base + stage * C::kStageBytes;
+        const uint32_t sb = sa + C::kABytes;
+        if (elect_one()) {
+          if (leader) mbar_expect_tx(full_bar(stage), 2 * C::kStageBytes);
+          if (!A_MN) {
+            tma_load_3d_2cta(sa, &tmA, full_bar(stage), kb * BK, m0, z);
+          } else {
+#pragma unroll
+            for (int h = 0; h < BM / 64; ++h)
+              tma_load_3d_2cta(sa + h * (64 * BK * 2), &tmA, full_bar(stage), m0 + h * 64, kb * BK, z);
+          }
+          if (!B_MN) {
+            tma_load_3d_2cta(sb, &tmB, full_bar(stage), kb * BK, n0, z);
+          } else {
+#pragma unroll
+            for (int h = 0; h < BNH / 64; ++h)
+              tma_load_3d_2cta(sb + h * (64 * BK * 2), &tmB, full_bar(stage), n0 + h * 64, kb * BK, z);
+          }
+        }
+        __syncwarp();
+        if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+      }
+    }
+    // tail: every stage this CTA filled has been consumed (the multicast commits have arrived here) before the
+    // CTA may leave - a commit must not find this CTA's barriers gone
+    for (int i = 0; i < C::kStages; ++i) {
+      mbar_wait(empty_bar(stage), phase ^ 1u);
+      if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+    }
+  } else if (warp == 1) {
+    // =========================== MMA issuer (leader only) =============================
+    if (leader) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
+                             ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM2 >> 4) << 24);
+      constexpr uint32_t kLboMN = 64 * BK * 2;
+      constexpr uint32_t kSbo = 1024;
+      constexpr uint32_t kAStep = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+      constexpr uint32_t kBStep = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+      const uint64_t adesc_hi = make_desc(0, A_MN ? kLboMN : 0u, kSbo);
+      const uint64_t bdesc_hi = make_desc(0, B_MN ? kLboMN : 0u, kSbo);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (long long t = pair0; t < total_tiles; t += npairs) {
+        long long r = t / ((long long)tiles_n * tiles_m);
+        const int split = (int)(r % p.splits);
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(num_kb, kb0 + p.kb_per_split);
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * C::kStageBytes;
+          const uint32_t sb = sa + C::kABytes;
+          if (elect_one()) {
+            const uint64_t a0 = adesc_hi | (uint64_t)((sa >> 4) & 0x3FFF), b0 = bdesc_hi | (uint64_t)((sb >> 4) & 0x3FFF);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma_bf16_2cta(d_tmem, a0 + (uint64_t)((k * kAStep) >> 4), b0 + (uint64_t)((k * kBStep) >> 4), idesc,
+                             (kb > kb0 || k > 0) ? 1u : 0u);
+            umma_commit_2cta(empty_bar(stage), 3);                   // frees the slot in both CTAs
+            if (kb == kb1 - 1) umma_commit_2cta(tfull_bar(acc), 3);  // accumulator halves complete in both CTAs
+          }
+          __syncwarp();
+          if (++stage == C::kStages) { stage = 0; phase ^= 1u; }
+        }
+        if (kb1 <= kb0 && elect_one()) umma_commit_2cta(tfull_bar(acc), 3);   // empty split: nothing to wait for
+        __syncwarp();
+        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // =========================== epilogue (both CTAs, own accumulator rows) ===============================
+    const int quad = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (long long t = pair0; t < total_tiles; t += npairs) {
+      long long r = t;
+      const int n_blk = (int)(r % tiles_n); r /= tiles_n;
+      const int m_blk = (int)(r % tiles_m); r /= tiles_m;
+      const int split = (int)(r % p.splits);
+      const int z = (int)(r / p.splits);
+      const int kb0 = split * p.kb_per_split;
+      const int kb1 = min(num_kb, kb0 + p.kb_per_split);
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const bool has_work = kb1 > kb0;
+      const float* bias = (p.bias != nullptr && split == 0) ? p.bias + (long long)z * p.strideBias : nullptr;
+      const int row0 = m_blk * BM2 + (int)crank * BM + quad * 32;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        const int n0 = n_blk * BN + c0;
+        if (n0 >= p.N) break;  // warp-uniform
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
+        tmem_ld32(taddr, v);
+        tmem_ld_wait();
+        if (row0 < p.M) epilogue_chunk(p, v, row0, lane, n0, has_work, bias, z, stage_out + (warp - 2) * (32 * 36));
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_leader(tempty_bar(acc));
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(kTmemCols) : "memory");
   }
 }
 
@@ -702,6 +918,29 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p,
   return 0;
 }
 
+template <bool A_MN, bool B_MN>
+static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int grid, cudaStream_t st) {
+  using C = Cfg<128>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_pair_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         C::kSmemBytes);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  gemm_pair_kernel<A_MN, B_MN><<<grid, kThreads, C::kSmemBytes, st>>>(ta, tb, p);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+static int g_gemm_pair = -1;       // CTA pairs (cta_group::2, 256 x 256 tiles): 1 auto (default), 0 off, 2 whenever legal
+static int gemm_pair_mode() {
+  if (g_gemm_pair < 0) {
+    const char* e = getenv("CXN_GEMM_PAIR");
+    g_gemm_pair = e ? atoi(e) : 0;   // (off until measured; see profiles/)
+  }
+  return g_gemm_pair;
+}
+
 template <int BN, bool B_MN, int CL>
 static int launch_cluster(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int grid, cudaStream_t st) {
   using C = Cfg<BN>;
@@ -786,6 +1025,14 @@ static void splitk_release(cudaStream_t st) {
 }  // namespace gemm
 }  // namespace cxn
 
+// CTA-pair route (cta_group::2): 1 = automatic (large problems), 0 = never, 2 = whenever the shape allows,
+// -1 = re-read CXN_GEMM_PAIR
+CXN_API int cxn_gemm_pair(int mode) {
+  if (mode < -1 || mode > 2) return -1;
+  cxn::gemm::g_gemm_pair = mode;
+  return 0;
+}
+
 // Split-K scratch lane (0..3) used by this thread's following cxn_gemm_bf16 calls; returns the previous lane or -1.
 CXN_API int cxn_gemm_workspace_lane(int lane) {
   if (lane < 0 || lane >= cxn::gemm::kWsLanes) return -1;
@@ -857,6 +1104,29 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   }
   int kbps = ceil_div(num_kb, splits);
   splits = ceil_div(num_kb, kbps);
+  // CTA pairs: 256 x 256 tiles computed by two SMs with M = 256 MMAs (gemm_pair_kernel) when the problem has at least
+  // one tile per pair of SMs - two thirds of the L2 -> SM bytes of the 128 x 256 single-CTA tile
+  {
+    const int pm = gemm_pair_mode();
+    const long long t256 = (long long)ceil_div(M, 256) * ceil_div(N, 256) * batch * splits;
+    const bool legal = (bn == 0 || bn == 256) && M > 128 && N > 128 && sms >= 2;
+    if (legal && (pm == 2 || (pm == 1 && t256 >= sms / 2))) {
+      Params pp;
+      pp.M = M; pp.N = N; pp.K = K; pp.batch = batch; pp.splits = splits; pp.kb_per_split = kbps;
+      pp.D = D; pp.ldd = ldd; pp.strideD = strideD; pp.bias = bias; pp.strideBias = strideBias; pp.flags = flags;
+      CUtensorMap pa, pb;
+      int rc2 = make_map(&pa, A, M, K, lda, batch, strideA, a_mn != 0, BM);
+      if (rc2) return rc2;
+      rc2 = make_map(&pb, B, N, K, ldb, batch, strideB, b_mn != 0, 128);
+      if (rc2) return rc2;
+      const long long max_pairs = sms / 2;
+      const int gridp = 2 * (int)(t256 < max_pairs ? t256 : max_pairs);
+      if (!a_mn && !b_mn) return launch_pair<false, false>(pa, pb, pp, gridp, stream);
+      if (!a_mn && b_mn) return launch_pair<false, true>(pa, pb, pp, gridp, stream);
+      if (a_mn && b_mn) return launch_pair<true, true>(pa, pb, pp, gridp, stream);
+      return launch_pair<true, false>(pa, pb, pp, gridp, stream);
+    }
+  }
   if (bn == 0) {
     auto tiles = [&](int b) { return (long long)ceil_div(M, BM) * ceil_div(N, b) * batch * splits; };
     if (N > 128 && tiles(256) >= sms) bn = 256;

@@ -66,6 +66,7 @@ class NeuralNet:
         self.arena = None
         self.arena_alloc = arena_alloc
         self.exchange = None
+        self.tp = None           # parallel.tensor_parallel.TensorParallel when fully connected layers are column-sharded
         self.need_update = True
         self.accumulate_grads = False
         # (per-channel means, scale) of 8-bit input batches: x = (pixel - mean[c]) * scale, applied where the batch
@@ -242,6 +243,15 @@ class NeuralNet:
                     want, x.wpitch = want
                 if want:
                     pitch[x.index] = want
+        # column-sharded fully connected layers (several ranks over peer-mapped memory): planned before the node
+        # buffers exist, because the nodes between two sharded layers are stored [global batch][own columns]
+        peer_mapped = self.world_size > 1 and self.arena_alloc is None and self.exchange_kind == "nvlink"
+        if peer_mapped:
+            from .parallel.tensor_parallel import TensorParallel
+            tp = TensorParallel(self)
+            tp.plan(consumers)
+            if tp.active():
+                self.tp = tp
         # node buffers
         for n in self.nodes:
             b, ch, h, w = n.shape
@@ -251,6 +261,10 @@ class NeuralNet:
                 rows += 64     # zeroed slack: the last span of the last image row reads a few pixels past the image
             cols = w if n.is_mat else ch
             ld = ops.round_up(cols, 8) if n.is_mat else pitch.get(n.index, cols)
+            if self.tp is not None and n.index in self.tp.shard_nodes:
+                n.tp_rows = rows = self.tp.total_rows()
+                cols = self.tp.shard_width(n.index)
+                ld = ops.round_up(cols, 8)
             n.act = ops.DevMat(rows, cols, ld, device=self.device)
             n.grad = ops.DevMat(rows, cols, ld, device=self.device)
             if n.loss_input:
@@ -319,13 +333,14 @@ class NeuralNet:
                                               (isinstance(c.layer, (native.FullConnectLayer, native.ConvolutionLayer))
                                                and tag == "bias")))
                 self._seg_of[(i, tag)] = s
-        peer_mapped = self.world_size > 1 and self.arena_alloc is None and self.exchange_kind == "nvlink"
         if peer_mapped:
             self._plan_fc_shards()
             self._alloc_symmetric()
         self.arena.finalize()
         if peer_mapped:
             self._finish_fc_shards()
+            if self.tp is not None:
+                self.tp.finish(self.symm_block, consumers)
         self._bind_arena()
         for c in self.connections:
             if c.native and c.type != nc.kSharedLayer:
@@ -363,7 +378,7 @@ class NeuralNet:
         for i, c in enumerate(self.connections):
             l = c.layer
             if not (c.native and isinstance(l, native.FullConnectLayer) and l.fullc_gather
-                    and c.type != nc.kSharedLayer):
+                    and c.type != nc.kSharedLayer) or l.tp is not None:
                 continue
             p = l.param
             nin, nout = p.num_input_node, p.num_hidden
@@ -398,6 +413,8 @@ class NeuralNet:
         total = nbuf * (n * 4 + 4096) + max(a.shadow_total, 128) * 2 + 4096 + flag_bytes + 65536
         for sh in getattr(self, "fc_shards", {}).values():
             total += self.max_batch * self.world_size * (sh.ld_in + sh.ld_out) * 2 + 4096
+        if self.tp is not None:
+            total += self.tp.symmetric_bytes()
         self.symm_block = SymmetricBlock(total, self.device)
         off, _ = self.symm_block.carve(flag_bytes)
         self.symm_offsets["flags"] = off
@@ -433,7 +450,7 @@ class NeuralNet:
         if self.arena is None:
             return
         if self.exchange is not None:
-            self.exchange.gather_master()
+            self.exchange.gather_master()      # (includes the column-sharded layers of self.tp)
         for (i, tag), s in self._seg_of.items():
             c = self.connections[i]
             if not c.native:
@@ -449,6 +466,9 @@ class NeuralNet:
 
     # ------------------------------------------------------------------ layout bridge (b200)
     def _node_load(self, n: Node, grad: bool = False) -> torch.Tensor:
+        if n.tp_rows:
+            raise ValueError("node %s lies between two column-sharded fully connected layers (fullc_shard = 1): every "
+                             "rank holds only its columns of it; extract it from a run without fullc_shard" % n.name)
         b, c, h, w = n.shape
         if n.loss_input and not grad:
             return n.f32[:b, :w].reshape(b, 1, 1, w).clone()
@@ -630,6 +650,8 @@ class NeuralNet:
         for i, c in enumerate(self.connections):
             if self.exchange is not None:
                 self.exchange.wait_layer(i)   # UpdateWait: this layer's weights from the last exchange
+            if self.tp is not None:
+                self.tp.wait_layer(i)
             t0 = tm.begin() if tm else None
             if c.native:
                 c.layer.b200_forward(self, is_train)
@@ -678,6 +700,8 @@ class NeuralNet:
                 self.exchange.layer_done(i)
         if need_update and self.exchange is None:
             self.arena.update()
+        if self.tp is not None:
+            self.tp.end_step()
         ops.check(ops.lib().cxn_counter_add(self.step_counter.data_ptr(), 1, ops.stream()), "counter_add")
 
     def update_all(self, epoch: int) -> None:

@@ -18,6 +18,8 @@ from .base import Node
 
 
 def _rows(node: Node) -> int:
+    if node.tp_rows:          # stored [global batch][this rank's columns]
+        return node.tp_rows
     b, c, h, w = node.shape
     return b if node.is_mat else b * h * w
 
@@ -40,6 +42,7 @@ class FullConnectLayer(zoo.FullConnectLayer):
         self.fuse_relu = False
         self.bind = {}
         self.shard = None     # parallel.exchange.FcShard when trained with fullc_gather on several ranks
+        self.tp = None        # parallel.tensor_parallel.TpLayer when sharded by output columns (fullc_shard)
 
     def b200_shadow(self, tag):
         p = self.param
@@ -48,6 +51,9 @@ class FullConnectLayer(zoo.FullConnectLayer):
         return None
 
     def b200_forward(self, ex, is_train):
+        if self.tp is not None:
+            ex.tp.fc_forward(self, is_train)
+            return
         p = self.param
         x, y = self.nodes_in[0], self.nodes_out[0]
         b = x.shape[0]
@@ -63,6 +69,9 @@ class FullConnectLayer(zoo.FullConnectLayer):
                  b, p.num_hidden, p.num_input_node, flags=flags)
 
     def b200_backprop(self, ex, prop_grad):
+        if self.tp is not None:
+            ex.tp.fc_backward(self, prop_grad)
+            return
         p = self.param
         x, y = self.nodes_in[0], self.nodes_out[0]
         b = x.shape[0]

@@ -25,12 +25,15 @@ class FullConnectLayer(Layer):
     def __init__(self):
         super().__init__()
         self.fullc_gather = 0
+        self.fullc_shard = 0      # b200, several ranks: shard the layer by output columns (parallel/tensor_parallel.py)
         self.wmat = self.bias = self.gwmat = self.gbias = None
 
     def set_param(self, name, val):
         super().set_param(name, val)
         if name == "fullc_gather":
             self.fullc_gather = int(val)
+        if name == "fullc_shard":
+            self.fullc_shard = int(val)
 
     def weights(self):
         out = [("wmat", self.wmat, self.gwmat)]

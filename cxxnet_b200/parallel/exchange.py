@@ -80,8 +80,9 @@ class GradExchange:
         self.shards: Dict[int, FcShard] = getattr(net, "fc_shards", {})
         # buckets over the non-sharded weighted layers, merged in backward order
         by_layer: Dict[int, List[int]] = {}
+        tp_layers = net.tp.layers if getattr(net, "tp", None) is not None else {}
         for si, s in enumerate(a.segments):
-            if s.layer_index not in self.shards:
+            if s.layer_index not in self.shards and s.layer_index not in tp_layers:
                 by_layer.setdefault(s.layer_index, []).append(si)
         self.buckets: List[Dict] = []
         cur = None
@@ -187,6 +188,8 @@ class GradExchange:
             self.wait_layer(b["trigger"])
         for li in self.shards:
             self.wait_layer(li)
+        if getattr(self.net, "tp", None) is not None:
+            self.net.tp.wait_all()
 
     # ------------------------------------------------------------------ K18: sharded fully connected layers
     def _allgather(self, pieces, slot, counter, stream) -> None:
@@ -287,6 +290,8 @@ class GradExchange:
     def gather_master(self) -> None:
         """refresh the fp32 masters of foreign weight shards from their owners (collective)."""
         self.wait_all()          # bucket kernels still pending on the exchange stream write arena.w
+        if getattr(self.net, "tp", None) is not None:
+            self.net.tp.gather_master()      # column-sharded layers: owners' rows of W and bias entries
         if not self.shards:
             return
         import torch.distributed as dist

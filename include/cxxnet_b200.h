@@ -36,6 +36,10 @@ int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a_mn, con
  * cl = 2 | 4 column tiles that share the activation tile by TMA multicast (0 = off, -1 = re-read CXN_GEMM_CLUSTER).
  * No reference counterpart. */
 int cxn_gemm_cluster(int cl);
+/* CTA-pair route of cxn_gemm_bf16 (tcgen05 cta_group::2: two SMs compute one 256 x 256 tile, each staging its own
+ * rows of A and half of the B tile): 1 = automatic for problems with at least one tile per pair of SMs (default),
+ * 0 = never, 2 = whenever the shape allows, -1 = re-read CXN_GEMM_PAIR.  No reference counterpart. */
+int cxn_gemm_pair(int mode);
 /* The internally split GEMMs (skinny fully connected shapes) meet in a zeroed fp32 scratch buffer; a device has
  * four independent ones ("lanes").  Selects the lane used by the calling thread's following cxn_gemm_bf16 calls
  * (default 0) and returns the previous one, -1 for an invalid lane.  GEMMs that can run concurrently (different

@@ -46,12 +46,44 @@ metric = error
 %s
 """ % (batch_size, dev, extra)
     SHAPE = (64, 1, 1, 1024)
+elif MODE == "shard":
+    # three fully connected layers sharded by output columns (fullc_shard = 1, parallel/tensor_parallel.py):
+    # row gather -> column gathers -> all-to-all forward, all-to-all -> pull reductions backward
+    def lenet_conf(batch_size=64, dev="gpu", extra=""):
+        return """
+netconfig=start
+layer[+1] = fullc:cv1
+  nhidden = 128
+layer[+1] = relu
+layer[+0] = dropout
+  threshold = 0.0
+layer[+1] = fullc:fc1
+  nhidden = 64
+layer[+1] = sigmoid
+layer[+1] = fullc:fc2
+  nhidden = 32
+layer[+0] = softmax
+netconfig=end
+input_shape = 1,1,1024
+batch_size = %d
+dev = %s
+random_type = xavier
+eta = 0.1
+momentum = 0.9
+metric = error
+fullc_shard = 1
+%s
+""" % (batch_size, dev, extra)
+    SHAPE = (64, 1, 1, 1024)
 else:
     SHAPE = (64, 1, 28, 28)
 tr = make_trainer(lenet_conf(batch_size=64, dev="gpu:" + ",".join(str(i) for i in range(world)),
                              extra=extra + ("cuda_graph = 1\n" if GRAPH else "")))
 if MODE == "gather":
     assert len(tr.net.fc_shards) == 1, "first layer should be sharded"
+if MODE == "shard":
+    assert tr.net.tp is not None and len(tr.net.tp.chains) == 1 and len(tr.net.tp.chains[0]) == 3, "three sharded layers"
+    assert not tr.net.exchange.buckets, "no gradient buckets: every weighted layer is column-sharded"
 assert tr.net.exchange is not None and tr.world_size == world
 assert (type(tr.net.exchange).__name__ == "CollectiveExchange") == COLLECTIVE
 os.environ.pop("CXN_EXCHANGE", None)

@@ -142,3 +142,24 @@ def test_memory_is_local_guard():
     h = torch.zeros(1 << 16).pin_memory()
     assert L.cxn_memory_is_local(h.data_ptr(), h.numel() * 4) == 0
     assert L.cxn_memory_is_local(None, 16) == 0
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1), (1, 0)])
+def test_gemm_cta_pairs(a_mn, b_mn):
+    """cxn_gemm_pair(2): 256 x 256 tiles computed by CTA pairs with cta_group::2 MMAs (each CTA stages its rows of A
+    and half of the B tile) in every operand layout: more tiles than pairs (persistent loop, both accumulator stages),
+    M / N / K tails, bias + ReLU, fp32 output, batches, split-K with fp32 reductions"""
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    L.cxn_gemm_pair.argtypes = [__import__("ctypes").c_int]
+    assert L.cxn_gemm_pair(2) == 0
+    try:
+        _run(512, 512, 256, a_mn, b_mn)
+        _run(256 * 14, 256 * 9, 192, a_mn, b_mn, relu=True, bias=True)      # 126 tiles on 74 pairs
+        _run(300, 333, 200, a_mn, b_mn, bias=True)                          # tails in M, N and K
+        _run(384, 1000, 512, a_mn, b_mn, out_bf16=False)
+        _run(256, 512, 320, a_mn, b_mn, batch=3, out_bf16=False)
+        _run(256, 768, 4096, a_mn, b_mn, splits=4, out_bf16=False, atomic=True)
+        _run(129, 130, 64, a_mn, b_mn)                                       # barely two CTAs' worth of rows
+    finally:
+        L.cxn_gemm_pair(-1)

@@ -19,7 +19,8 @@ def _run(nproc, script_args, timeout=300):
 
 @pytest.mark.skipif(torch.cuda.is_available() and torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 @pytest.mark.parametrize("updater,mode,graph", [("sgd", "lenet", ""), ("nag", "lenet", ""), ("sgd", "gather", ""),
-                                                ("sgd", "lenet", "graph"), ("sgd", "gather", "graph")])
+                                                ("sgd", "lenet", "graph"), ("sgd", "gather", "graph"),
+                                                ("sgd", "shard", ""), ("nag", "shard", "graph")])
 def test_fused_exchange_matches_single_gpu(updater, mode, graph):
     script = os.path.join(ROOT, "tests", "mp_exchange_worker.py")
     r = _run(2, [script, updater, mode] + ([graph] if graph else []))
