@@ -1580,7 +1580,7 @@ static int g_tune_pair = -1;       // 1: CTA pairs (cta_group::2) for forward pr
 static int pair_mode() {
   if (g_tune_pair < 0) {
     const char* e = getenv("CXN_CONV_PAIR2");
-    g_tune_pair = e ? atoi(e) : 0;
+    g_tune_pair = e ? atoi(e) : 1;
   }
   return g_tune_pair;
 }

@@ -292,6 +292,41 @@ __global__ void fill_f32_kernel(float* __restrict__ p, long long n, float v) {
 using namespace cxn;
 
 extern "C" { unsigned long long cxn_launch_counter_ = 0; }
+
+// ---- launch-site histogram (CXN_LAUNCH_LOG=1): which kernels make up a step, without a profiler attached.  Launches
+// replayed from a CUDA graph are counted once, at capture - i.e. the composition of one captured step.
+#include <map>
+#include <mutex>
+#include <string>
+#include <stdlib.h>
+namespace {
+std::mutex g_ll_mu;
+std::map<std::string, unsigned long long>* g_ll = nullptr;
+void ll_dump() {
+  if (!g_ll) return;
+  fprintf(stderr, "[cxxnet_b200] launches per call site (graph replays not included):\n");
+  for (const auto& kv : *g_ll) fprintf(stderr, "  %8llu  %s\n", kv.second, kv.first.c_str());
+}
+int ll_init() {
+  const char* e = getenv("CXN_LAUNCH_LOG");
+  if (e && atoi(e) > 0) {
+    g_ll = new std::map<std::string, unsigned long long>();
+    atexit(ll_dump);
+    return 1;
+  }
+  return 0;
+}
+}  // namespace
+extern "C" {
+int cxn_launch_log_on_ = ll_init();
+void cxn_note_launch_(const char* file, int line) {
+  std::lock_guard<std::mutex> g(g_ll_mu);
+  if (!g_ll) return;
+  const char* base = file;
+  for (const char* q = file; *q; ++q) if (*q == '/') base = q + 1;
+  ++(*g_ll)[std::string(base) + ":" + std::to_string(line)];
+}
+}
 CXN_API unsigned long long cxn_launch_count() { return cxn_launch_counter_; }
 // launches replayed from a captured CUDA graph never pass through this library's entry points
 CXN_API unsigned long long cxn_launch_count_add(unsigned long long n) { return cxn_launch_counter_ += n; }

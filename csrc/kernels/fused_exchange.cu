@@ -30,7 +30,8 @@ constexpr int kMaxRanks = 16;
 constexpr int kMaxSlots = 256;
 constexpr int kChunk = 1024;
 constexpr int kThreads = 256;
-constexpr int kMaxBucketSegs = 16;   // segments cached in shared memory; buckets may hold more (load_seg)
+constexpr int kMaxBucketSegs = 8;    // segments cached in shared memory (512 B: the kernel must fit beside the GEMM /
+                                     // convolution CTAs it overlaps); buckets may hold more (load_seg)
 
 struct Segment {   // must match loss_update.cu
   long long start, n, shadow_off;
@@ -84,8 +85,8 @@ __device__ __forceinline__ void wait_all(const Params& p, int which, unsigned se
     const long long t0 = clock64();
     unsigned spins = 0;
     while ((int)(ld_acquire_sys(f) - seq) < 0) {
-      __nanosleep(64);
-      if ((++spins & 4095u) == 0 && clock64() - t0 > 20000000000LL) {
+      if (++spins > 32) __nanosleep(32);      // the first polls back to back: a peer is usually within a few us
+      if ((spins & 4095u) == 0 && clock64() - t0 > 20000000000LL) {
         printf("[cxxnet_b200 exchange] rank %d timed out waiting for rank %d (slot %d phase %d seq %u)\n", p.rank,
                (int)threadIdx.x, p.slot, which, seq);
         __trap();

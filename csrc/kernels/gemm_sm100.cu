@@ -27,7 +27,8 @@ namespace gemm {
 constexpr int BM = 128;
 constexpr int BK = 64;           // 64 bf16 = 128 bytes = one swizzle span
 constexpr int UMMA_K = 16;
-constexpr int kThreads = 192;
+constexpr int kThreads = 192;        // pair / cluster kernels: TMA warp, MMA warp, 4 epilogue warps
+constexpr int kThreadsWide = 320;    // gemm_kernel: 8 epilogue warps (two per TMEM lane quadrant, half of the columns each)
 constexpr int kAccStages = 2;
 
 enum : int {
@@ -54,9 +55,9 @@ struct Cfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kTmemCols = kAccStages * BN;  // 128 / 256 / 512
-  // epilogue staging: per epilogue warp a 32 x 32 fp32 chunk, rows padded to 36 floats (conflict-free
-  // 128-bit shared accesses both ways)
-  static constexpr int kStageOutBytes = 4 * 32 * 36 * 4;
+  // epilogue staging: per epilogue warp a 32 x 32 fp32 chunk whose 16-byte columns are XOR-swizzled with the row
+  // (conflict-free 128-bit shared accesses both ways, no padding); room for 8 epilogue warps
+  static constexpr int kStageOutBytes = 8 * 32 * 32 * 4;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kStageOutBytes;
 };
 
@@ -64,7 +65,7 @@ using namespace cxn::tc;
 
 // One 32-column chunk of an accumulator tile, held one row per lane (v[j] = column n0 + j of row row0 + lane):
 // bias / ReLU / conversion and the store, reduction or read-modify-write into D.  `warp_stage` is this warp's
-// 32 x 36 float staging area (fp32 results pass through a shared-memory transpose so that every store instruction
+// 32 x 32 float staging area (fp32 results pass through a shared-memory transpose so that every store instruction
 // covers complete 128-byte row segments).
 __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&v)[32], int row0, int lane, int n0,
                                                bool has_work, const float* bias, int z, float* warp_stage) {
@@ -88,7 +89,7 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&v)[32
       o4.y = has_work ? __uint_as_float(v[4 * q + 1]) : 0.0f;
       o4.z = has_work ? __uint_as_float(v[4 * q + 2]) : 0.0f;
       o4.w = has_work ? __uint_as_float(v[4 * q + 3]) : 0.0f;
-      *reinterpret_cast<float4*>(sm + lane * 36 + 4 * q) = o4;
+      *reinterpret_cast<float4*>(sm + lane * 32 + 4 * (q ^ (lane & 7))) = o4;
     }
     __syncwarp();
     const int rsub = lane >> 3, cq = (lane & 7) * 4;
@@ -98,7 +99,7 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&v)[32
     for (int it = 0; it < 8; ++it) {
       const int r = it * 4 + rsub;
       if (row0 + r < p.M) {
-        float4 o4 = *reinterpret_cast<const float4*>(sm + r * 36 + cq);
+        float4 o4 = *reinterpret_cast<const float4*>(sm + r * 32 + 4 * ((lane & 7) ^ (r & 7)));
         float4* dp = reinterpret_cast<float4*>(dbase + (long long)(row0 + r) * p.ldd);
         if (beta1) {
           const float4 c4 = *dp;
@@ -179,7 +180,7 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&v)[32
 }
 
 template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreadsWide, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
@@ -210,7 +211,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int a = 0; a < kAccStages; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 4);
+      mbar_init(tempty_bar(a), 8);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -314,7 +315,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else {
     // =========================== epilogue ===============================
-    const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+    // eight warps: warp w reads TMEM lane quadrant w & 3 (a hardware rule) and takes the lower or upper half of the
+    // tile's columns - the accumulator drains twice as fast as with one warp per quadrant
+    const int quad = warp & 3;
+    const int chalf = (warp - 2) >> 2;
+    constexpr int kColsPerWarp = BN / 2;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -330,14 +335,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const bool has_work = kb1 > kb0;
       const float* bias = (p.bias != nullptr && split == 0) ? p.bias + (long long)z * p.strideBias : nullptr;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = chalf * kColsPerWarp; c0 < (chalf + 1) * kColsPerWarp; c0 += 32) {
         const int n0 = n_blk * BN + c0;
         if (n0 >= p.N) break;  // warp-uniform
         uint32_t v[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
         tmem_ld32(taddr, v);
         tmem_ld_wait();
-        epilogue_chunk(p, v, m_blk * BM + quad * 32, lane, n0, has_work, bias, z, stage_out + (warp - 2) * (32 * 36));
+        epilogue_chunk(p, v, m_blk * BM + quad * 32, lane, n0, has_work, bias, z, stage_out + (warp - 2) * (32 * 32));
       }
       tc_fence_before();
       __syncwarp();
@@ -545,7 +550,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
         tmem_ld32(taddr, v);
         tmem_ld_wait();
-        if (row0 < p.M) epilogue_chunk(p, v, row0, lane, n0, has_work, bias, z, stage_out + (warp - 2) * (32 * 36));
+        if (row0 < p.M) epilogue_chunk(p, v, row0, lane, n0, has_work, bias, z, stage_out + (warp - 2) * (32 * 32));
       }
       tc_fence_before();
       __syncwarp();
@@ -913,7 +918,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p,
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
-  gemm_kernel<BN, A_MN, B_MN><<<grid, kThreads, C::kSmemBytes, st>>>(ta, tb, p);
+  gemm_kernel<BN, A_MN, B_MN><<<grid, kThreadsWide, C::kSmemBytes, st>>>(ta, tb, p);
   CXN_CHECK_LAUNCH();
   return 0;
 }
@@ -936,7 +941,7 @@ static int g_gemm_pair = -1;       // CTA pairs (cta_group::2, 256 x 256 tiles):
 static int gemm_pair_mode() {
   if (g_gemm_pair < 0) {
     const char* e = getenv("CXN_GEMM_PAIR");
-    g_gemm_pair = e ? atoi(e) : 0;   // (off until measured; see profiles/)
+    g_gemm_pair = e ? atoi(e) : 1;
   }
   return g_gemm_pair;
 }
@@ -1110,7 +1115,9 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
     const int pm = gemm_pair_mode();
     const long long t256 = (long long)ceil_div(M, 256) * ceil_div(N, 256) * batch * splits;
     const bool legal = (bn == 0 || bn == 256) && M > 128 && N > 128 && sms >= 2;
-    if (legal && (pm == 2 || (pm == 1 && t256 >= sms / 2))) {
+    // (automatic: only long reductions - with few k-blocks the tile is epilogue-bound and the single-CTA kernel's eight
+    // epilogue warps win; measured in profiles/r2_gemm_sweep.txt)
+    if (legal && (pm == 2 || (pm == 1 && t256 >= sms / 2 && num_kb >= 16))) {
       Params pp;
       pp.M = M; pp.N = N; pp.K = K; pp.batch = batch; pp.splits = splits; pp.kb_per_split = kbps;
       pp.D = D; pp.ldd = ldd; pp.strideD = strideD; pp.bias = bias; pp.strideBias = strideBias; pp.flags = flags;

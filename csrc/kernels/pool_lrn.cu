@@ -347,6 +347,89 @@ __global__ void __launch_bounds__(256) pool_bwd_row_kernel(const bf16* __restric
   *reinterpret_cast<uint4*>(dx + xoff) = o;
 }
 
+// The same with the bias gradient of the layer in front fused in: when the pooled node is the (ReLU-masked) output
+// of a convolution, dx IS that convolution's output gradient and its bias gradient is the column sum of dx over all
+// pixels - a separate pass over the largest gradient tensors of the net otherwise (reference: the convolution's
+// gbias = sum_rows(grad), src/layer/convolution_layer-inl.hpp:127-129).  A block walks `rows_per_block` image rows
+// and keeps per-thread fp32 sums of the bf16 values it stores; one shared-memory reduction and 8 atomics per channel
+// vector per block end it.  bias_grad must be zeroed (or hold the value to accumulate onto) before the launch.
+template <int SH>
+__global__ void __launch_bounds__(256) pool_bwd_row_bias_kernel(const bf16* __restrict__ x, const bf16* __restrict__ y,
+                                                                const bf16* __restrict__ dy, bf16* __restrict__ dx,
+                                                                float* __restrict__ bias_grad, int rows_per_block,
+                                                                PoolGeom g) {
+  __shared__ float red[256 * 8];
+  const int xx = blockIdx.x * blockDim.y + threadIdx.y;
+  const bool active = xx < g.W;
+  const int n = blockIdx.z, c = threadIdx.x << 3;
+  auto div_s = [&](int v) { return SH >= 0 ? (v >> SH) : v / g.stride; };
+  const int px0 = xx < g.K_x ? 0 : div_s(xx - g.K_x + g.stride);
+  const int px1 = min(div_s(xx) + 1, g.OW);
+  const bool ok01 = px0 + 1 < px1;
+  const __nv_bfloat162 z = __float2bfloat162_rn(0.0f);
+  float bs[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) bs[j] = 0.0f;
+  const int y_begin = blockIdx.y * rows_per_block, y_end = min(g.H, y_begin + rows_per_block);
+  for (int yy = y_begin; active && yy < y_end; ++yy) {
+    const int py0 = yy < g.K_y ? 0 : div_s(yy - g.K_y + g.stride);
+    const int py1 = min(div_s(yy) + 1, g.OH);
+    const long long xoff = (((long long)n * g.H + yy) * g.W + xx) * g.C + c;
+    const uint4 xr = *reinterpret_cast<const uint4*>(x + xoff);
+    const long long pbase = (((long long)n * g.OH + py0) * g.OW + px0) * g.C + c;
+    const bool ok10 = py0 + 1 < py1;
+    const bool okv[4] = {py0 < py1 && px0 < px1, py0 < py1 && ok01, ok10 && px0 < px1, ok10 && ok01};
+    const long long offv[4] = {0, (long long)g.C, (long long)g.OW * g.C, (long long)(g.OW + 1) * g.C};
+    uint4 pv[4], gv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      pv[k] = okv[k] ? *reinterpret_cast<const uint4*>(y + pbase + offv[k]) : make_uint4(0, 0, 0, 0);
+      gv[k] = okv[k] ? *reinterpret_cast<const uint4*>(dy + pbase + offv[k]) : make_uint4(0, 0, 0, 0);
+    }
+    const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&xr);
+    __nv_bfloat162 xm[4], am[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      xm[j] = g.relu ? __hmax2(hx[j], z) : hx[j];
+      am[j] = z;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&pv[k]);
+      const __nv_bfloat162* hg = reinterpret_cast<const __nv_bfloat162*>(&gv[k]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) am[j] = __hfma2(__heq2(xm[j], hp[j]), hg[j], am[j]);
+    }
+    if (g.relu) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) am[j] = __hmul2(am[j], __hgt2(hx[j], z));
+    }
+    uint4 o;
+    __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      ho[j] = am[j];
+      const float2 f = __bfloat1622float2(am[j]);
+      bs[2 * j] += f.x;
+      bs[2 * j + 1] += f.y;
+    }
+    *reinterpret_cast<uint4*>(dx + xoff) = o;
+  }
+  // block reduction over the pixel dimension, then one atomic per channel
+  const int cw = blockDim.x * 8;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y * cw + c + j] = bs[j];
+  __syncthreads();
+  if (threadIdx.y == 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float sum = 0.0f;
+      for (int r = 0; r < (int)blockDim.y; ++r) sum += red[r * cw + c + j];
+      atomicAdd(bias_grad + c + j, sum);
+    }
+  }
+}
+
 // dx[n][y][x][c] = sum over covering windows of  partial(x, pooled) * dy   (* 1/k^2 for avg)
 // With relu fused, x is compared after relu and the result is masked by x>0.
 template <int V>
@@ -620,6 +703,35 @@ CXN_API int cxn_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int
   CXN_CHECK_LAUNCH();
   return 0;
 }
+// Max-pool backward that also accumulates the column sums of dx (over all N*H*W pixels) into bias_grad[C] (fp32,
+// zeroed or holding the value to add to): the bias gradient of a convolution whose ReLU-masked output is the pooled
+// node.  Returns -8 when the shape is outside the fused kernel's range (the caller then runs cxn_pool_bwd and a
+// column sum).
+CXN_API int cxn_pool_bwd_bias(const void* x, const void* y, const void* dy, void* dx, float* bias_grad, int N, int H, int W,
+                              int C, int ky, int kx, int stride, int OH, int OW, int mode, int relu, cudaStream_t st) {
+  PoolGeom g{N, H, W, C, ky, kx, stride, OH, OW, mode, relu};
+  if ((long long)N * H * W * C <= 0) return 0;
+  const bool v = pool_vec(x, y, C) && pool_vec(dy, dx, C);
+  if (!(v && mode == 0 && N <= 65535 && H <= 65535 && ky <= 2 * stride && kx <= 2 * stride && C / 8 <= 256) || !bias_grad)
+    return -8;
+  const int cv = C / 8;
+  const int py = 256 / cv > 0 ? 256 / cv : 1;
+  const int segs = ceil_div(W, py);
+  // about eight blocks per SM, each walking a band of image rows
+  long long bands = ceil_div_ll(8LL * num_sms(), (long long)segs * N);
+  if (bands < 1) bands = 1;
+  if (bands > H) bands = H;
+  const int rpb = ceil_div(H, (int)bands);
+  dim3 block(cv, py), grid(segs, ceil_div(H, rpb), N);
+  const bf16 *xp = (const bf16*)x, *yp = (const bf16*)y, *gp = (const bf16*)dy;
+  if (stride == 1) pool_bwd_row_bias_kernel<0><<<grid, block, 0, st>>>(xp, yp, gp, (bf16*)dx, bias_grad, rpb, g);
+  else if (stride == 2) pool_bwd_row_bias_kernel<1><<<grid, block, 0, st>>>(xp, yp, gp, (bf16*)dx, bias_grad, rpb, g);
+  else if (stride == 4) pool_bwd_row_bias_kernel<2><<<grid, block, 0, st>>>(xp, yp, gp, (bf16*)dx, bias_grad, rpb, g);
+  else pool_bwd_row_bias_kernel<-1><<<grid, block, 0, st>>>(xp, yp, gp, (bf16*)dx, bias_grad, rpb, g);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+
 CXN_API int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, int ky,
                          int kx, int stride, int OH, int OW, int mode, int relu, cudaStream_t st) {
   PoolGeom g{N, H, W, C, ky, kx, stride, OH, OW, mode, relu};

@@ -294,6 +294,15 @@ class NeuralNet:
                         and consumers.get(x.index, 0) == 1 and x.grad is x.alias_of.grad):
                     l.mask_relu = True
                     p.layer.skip_bwd = True
+                    # ... and if that ReLU was folded into a convolution with a bias, this pooling layer's input
+                    # gradient is the convolution's output gradient: it accumulates the bias gradient as well
+                    pc = producer.get(x.alias_of.index)
+                    if (pc is not None and pc.native and isinstance(pc.layer, native.ConvolutionLayer)
+                            and pc.type != nc.kSharedLayer and pc.layer.param.no_bias == 0 and p.layer.fused
+                            and type(l) is native.MaxPoolingLayer and x.grad.ld == x.grad.cols
+                            and __import__("os").environ.get("CXN_FUSE_BIAS_GRAD", "0") == "1"):
+                        l.bias_of = pc.layer
+                        pc.layer.bias_grad_fused = True
         # ... or into the backward-data kernel of the convolution that consumes it
         for c in self.connections:
             l = c.layer

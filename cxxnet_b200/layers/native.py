@@ -127,6 +127,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         self.span = False       # cin_pad input read through im2col TMA as overlapping 16-pixel (64-channel) positions
         self.igemm_fwd = False
         self.igemm_dgrad = False
+        self.bias_grad_fused = False   # the pooling layer behind this one accumulates the bias gradient (_NativePool.bias_of)
 
     def b200_supported(self):
         p = self.param
@@ -275,7 +276,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         L = ops.lib()
         W = self.bind["wmat"]
         b, c, h, w = x.shape
-        if p.no_bias == 0:
+        if p.no_bias == 0 and not self.bias_grad_fused:
             ops.check(L.cxn_colsum_bf16(gy.ptr, rows, p.num_channel, gy.ld, self.bind["bias"].g.data_ptr(),
                                         1 if ex.accumulate_grads else 0, ops.stream()), "colsum")
         # weight gradient (accumulates into the arena gradient, which the updater leaves zeroed)
@@ -379,6 +380,8 @@ class _NativePool:
     has_b200 = True
     pool_mode = ops.POOL_MAX
     mask_relu = False   # backward also applies the mask of the ReLU that produced the input node
+    bias_of = None      # convolution whose (ReLU-masked) output this layer pools: its bias gradient = column sums of the
+                        # input gradient computed here, accumulated by the same kernel (set by the executor)
 
     def _args(self, bwd=False):
         p = self.param
@@ -399,8 +402,22 @@ class _NativePool:
         if not prop_grad:
             return
         x, y = self.nodes_in[0], self.nodes_out[0]
-        ops.check(ops.lib().cxn_pool_bwd(x.act.ptr, y.act.ptr, y.grad.ptr, x.grad.ptr, *self._args(True), ops.stream()),
+        L = ops.lib()
+        conv = self.bias_of
+        if conv is not None:
+            gb = conv.bind["bias"].g
+            if not ex.accumulate_grads:
+                ops.check(L.cxn_fill_f32(gb.data_ptr(), gb.numel(), 0.0, ops.stream()), "fill")
+            rc = L.cxn_pool_bwd_bias(x.act.ptr, y.act.ptr, y.grad.ptr, x.grad.ptr, gb.data_ptr(), *self._args(True), ops.stream())
+            if rc == 0:
+                return
+            if rc != -8:
+                ops.check(rc, "pool_bwd_bias")
+        ops.check(L.cxn_pool_bwd(x.act.ptr, y.act.ptr, y.grad.ptr, x.grad.ptr, *self._args(True), ops.stream()),
                   "pool_bwd")
+        if conv is not None:      # shape outside the fused kernel: the separate column sum after all
+            ops.check(L.cxn_colsum_bf16(x.grad.ptr, _rows(x), conv.param.num_channel, x.grad.ld, conv.bind["bias"].g.data_ptr(),
+                                        1, ops.stream()), "colsum")
 
 
 class MaxPoolingLayer(_NativePool, zoo.MaxPoolingLayer):

@@ -92,6 +92,7 @@ def lib():
     _sig(L.cxn_conv_set_prof, [P])
     _sig(L.cxn_pool_fwd, [P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(L.cxn_pool_bwd, [P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])
+    _sig(L.cxn_pool_bwd_bias, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, I, P])
     _sig(L.cxn_lrn_fwd, [P, P, LL, I, I, F, F, F, P])
     _sig(L.cxn_lrn_bwd, [P, P, P, LL, I, I, F, F, F, P])
     _sig(L.cxn_metric_error, [P, LL, P, LL, I, I, P, P])

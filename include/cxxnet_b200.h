@@ -180,6 +180,11 @@ int cxn_pool_fwd(const void* x, void* y, int N, int H, int W, int C, int ky, int
                  int mode, int relu, cudaStream_t stream);
 int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W, int C, int ky, int kx,
                  int stride, int OH, int OW, int mode, int relu, cudaStream_t stream);
+/* K9 + K4: max-pool backward that also accumulates the column sums of dx into bias_grad[C] (fp32; zeroed, or the
+ * value to add to) - the bias gradient of the convolution whose ReLU-masked output is the pooled node
+ * (src/layer/convolution_layer-inl.hpp:127-129).  -8 = shape outside the fused kernel (use cxn_pool_bwd + a column sum). */
+int cxn_pool_bwd_bias(const void* x, const void* y, const void* dy, void* dx, float* bias_grad, int N, int H, int W, int C,
+                      int ky, int kx, int stride, int OH, int OW, int mode, int relu, cudaStream_t stream);
 /* ---- K10/K11 local response normalisation across channels.  src/layer/lrn_layer-inl.hpp:53-75. */
 int cxn_lrn_fwd(const void* x, void* y, long long pixels, int C, int nsize, float alpha, float beta, float knorm,
                 cudaStream_t stream);

@@ -1,5 +1,6 @@
 """Implicit-GEMM convolution kernels (csrc/kernels/conv_igemm_sm100.cu) against torch conv2d in
-fp32 (TF32 off, tests/conftest.py) on the same bf16-rounded operands.
+fp64 on the same bf16-rounded operands (the fp32 path of the oracle library has TF32 switched off in
+tests/conftest.py as well).
 
 Tolerances: products of bf16 operands are exact in fp32 and both sides accumulate in fp32, so what is left is the
 rounding of the bf16 OUTPUT (half an ulp = 2^-9 of the value; bounded here by 2^-7 of the largest output) and, for
@@ -45,8 +46,10 @@ def _case(N, C, H, W, OC, G, KH, KW, stride, pad, relu=True, c_pitch=None):
     ops.check(L.cxn_conv_fprop(xs.data_ptr(), N, H, W, Cs, icg_int, G, gran, wsh.data_ptr(), kpad, ocg, KH, KW, stride,
                                pad, pad, OH, OW, y.data_ptr(), OC, bias.data_ptr(), 1 if relu else 0, ops.stream()),
               "fprop")
-    xr = x.float().permute(0, 3, 1, 2)
-    ref = F.conv2d(xr, w.float(), bias, stride=stride, padding=pad, groups=G)
+    # oracle in fp64 (a plain direct convolution; cuDNN's fp32 algorithms - FFT / Winograd tiles - carry errors of
+    # their own around 1e-3 that would otherwise be charged to the kernel under test)
+    xr = x.double().permute(0, 3, 1, 2)
+    ref = F.conv2d(xr, w.double(), bias.double(), stride=stride, padding=pad, groups=G).float()
     if relu:
         ref = torch.relu(ref)
     got = y.float().view(N, OH, OW, OC).permute(0, 3, 1, 2)
@@ -57,7 +60,8 @@ def _case(N, C, H, W, OC, G, KH, KW, stride, pad, relu=True, c_pitch=None):
     dw = torch.zeros(G * ocg, kg, dtype=torch.float32, device="cuda")
     ops.check(L.cxn_conv_wgrad(xs.data_ptr(), N, H, W, Cs, icg_int, G, gran, dy.data_ptr(), OC, ocg, KH, KW, stride,
                                pad, pad, OH, OW, dw.data_ptr(), kg, 0, ops.stream()), "wgrad")
-    dwr = torch.nn.grad.conv2d_weight(xr, w.shape, dy.float().permute(0, 3, 1, 2), stride=stride, padding=pad, groups=G)
+    dwr = torch.nn.grad.conv2d_weight(xr, w.shape, dy.double().permute(0, 3, 1, 2), stride=stride, padding=pad,
+                                      groups=G).float()
     gotw = dw.view(G, ocg, KH, KW, icg_int)[..., :C // G].permute(0, 1, 4, 2, 3).reshape(OC, C // G, KH, KW)
     errw = float((gotw - dwr).abs().max())
     assert errw <= TOL_F32_SUM * max(1.0, float(dwr.abs().max())), "wgrad err %g (max %g)" % (errw, float(dwr.abs().max()))
@@ -74,8 +78,8 @@ def _case(N, C, H, W, OC, G, KH, KW, stride, pad, relu=True, c_pitch=None):
         dx = torch.zeros(N * H * W, C, dtype=torch.bfloat16, device="cuda")
         ops.check(L.cxn_conv_fprop(dy.data_ptr(), N, OH, OW, OC, ocg, G, 8, wt.data_ptr(), kfpad, icg, KH, KW, 1,
                                    KH - 1 - pad, KW - 1 - pad, H, W, dx.data_ptr(), C, None, 0, ops.stream()), "dgrad")
-        dxr = torch.nn.grad.conv2d_input(xr.shape, w.float(), dy.float().permute(0, 3, 1, 2), stride=1, padding=pad,
-                                         groups=G)
+        dxr = torch.nn.grad.conv2d_input(xr.shape, w.double(), dy.double().permute(0, 3, 1, 2), stride=1, padding=pad,
+                                         groups=G).float()
         gotx = dx.float().view(N, H, W, C).permute(0, 3, 1, 2)
         errx = float((gotx - dxr).abs().max())
         assert errx <= TOL_BF16_OUT * max(1.0, float(dxr.abs().max())), "dgrad err %g" % errx

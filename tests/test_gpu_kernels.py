@@ -46,6 +46,37 @@ def test_pool_fwd_bwd(mode, name, shape, k, s):
     assert torch.allclose(gotdx, dxref, atol=2e-2, rtol=2e-2)
 
 
+@pytest.mark.parametrize("shape,k,s", [((6, 96, 55, 55), 3, 2), ((5, 256, 27, 27), 3, 2), ((4, 256, 13, 13), 3, 2),
+                                       ((3, 16, 9, 8), 2, 2)])
+def test_pool_bwd_with_fused_bias_gradient(shape, k, s):
+    """cxn_pool_bwd_bias: the same dx as cxn_pool_bwd (ReLU-masked max pooling) and, in the same pass, the column
+    sums of dx = the bias gradient of the convolution in front (plain fp32 PyTorch sum of the stored bf16 values);
+    a second call accumulates onto the first"""
+    from cxxnet_b200 import ops
+    from cxxnet_b200.layers.zoo import pool_forward
+    L = ops.lib()
+    torch.manual_seed(7)
+    n, c, h, w = shape
+    x = bf(torch.randn(shape, device="cuda")).float()
+    xr = nhwc(x)
+    yref = pool_forward(torch.relu(x), k, k, s, "max")
+    oh, ow = yref.shape[2:]
+    y = torch.zeros(n * oh * ow, c, dtype=torch.bfloat16, device="cuda")
+    ops.check(L.cxn_pool_fwd(xr.data_ptr(), y.data_ptr(), n, h, w, c, k, k, s, oh, ow, 0, 1, ops.stream()), "pool")
+    g = nhwc(bf(torch.randn_like(yref)).float())
+    dx0, dx1 = torch.zeros_like(xr), torch.zeros_like(xr)
+    ops.check(L.cxn_pool_bwd(xr.data_ptr(), y.data_ptr(), g.data_ptr(), dx0.data_ptr(), n, h, w, c, k, k, s, oh, ow, 0, 1,
+                             ops.stream()), "pool_bwd")
+    gb = torch.zeros(c, device="cuda")
+    for rep in range(2):
+        ops.check(L.cxn_pool_bwd_bias(xr.data_ptr(), y.data_ptr(), g.data_ptr(), dx1.data_ptr(), gb.data_ptr(), n, h, w, c, k,
+                                      k, s, oh, ow, 0, 1, ops.stream()), "pool_bwd_bias")
+        torch.cuda.synchronize()
+        assert torch.equal(dx0, dx1)
+        want = (rep + 1) * dx0.float().sum(dim=0)
+        assert torch.allclose(gb, want, atol=1e-3 * max(1.0, float(want.abs().max())), rtol=1e-4), (rep, float((gb - want).abs().max()))
+
+
 def test_pool_relu_mask_variants():
     from cxxnet_b200 import ops
     from cxxnet_b200.layers.zoo import pool_backward, pool_forward
