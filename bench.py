@@ -145,9 +145,12 @@ def run_ours(args, rank, world, local):
     if "cuda_graph" not in extra:
         extra += "\ncuda_graph = 1\n"        # one captured graph per step instead of ~80 launches
     if world > 1 and "fullc_gather" not in extra and "fullc_shard" not in extra:
-        # fully connected layers sharded by output columns over the ranks (weights never cross a link); the
-        # reference's own option for these layers, `fullc_gather = 1`, remains available through --extra
-        extra += "\nfullc_shard = 1\n"
+        # Fully connected layers on several GPUs.  Four or more: sharded by output columns (`fullc_shard = 1`, weights
+        # never cross a link, activations move on the critical path).  Two: the reference's own option,
+        # `fullc_gather = 1` (row-sharded weight gradient / update, new bf16 rows published on a side stream) - with
+        # two ranks that publish hides under the convolution backward pass and beats the sharded layers' nine
+        # barriers per step (profiles/r2_scaling.md).  Either can be forced through --extra.
+        extra += "\nfullc_shard = 1\n" if world >= 4 else "\nfullc_gather = 1\n"
     for k, v in parse_config_string(alexnet_conf(batch_size=B, dev=dev, extra=extra)):
         tr.set_param(k, v)
     tr.set_param("silent", "1")
@@ -211,10 +214,14 @@ def run_ours(args, rank, world, local):
         "config": {"model": "AlexNet (example/ImageNet/ImageNet.conf)", "global_batch": B,
                    "input": "3x227x227 (%s NCHW batches from the iterator, fp32 labels)" % args.input,
                    "per_gpu_batch": hi - lo,
-                   "parallelism": ("dp%d" % world) if (world == 1 or "fullc_shard" not in extra) else
-                                  ("dp%d (conv) + tp%d (fc6-8 column-sharded)" % (world, world)), "updater": "sgd momentum 0.9 wd 5e-4",
-                   "l2": "no flush: per-step working set (activations + im2col + 244 MB weights) far exceeds "
-                         "the 126 MB L2; e2e rotates 3 distinct 79 MB (bf16) input batches",
+                   "parallelism": ("dp%d" % world) if world == 1 else
+                                  ("dp%d (conv) + tp%d (fc6-8 column-sharded)" % (world, world)) if "fullc_shard" in extra
+                                  else ("dp%d (fc6-8: fullc_gather, row-sharded weight gradient and update)" % world),
+                   "updater": "sgd momentum 0.9 wd 5e-4",
+                   "l2": "no flush: per-step working set (activations + gradients + 244 MB of fp32 weights, 122 MB of "
+                         "bf16 weights, optimiser state) far exceeds the 126 MB L2; e2e rotates 3 distinct %d MB "
+                         "(%s) input batches" % (B * 3 * 227 * 227 * (1 if args.input == "u8" else 2) // 1000000,
+                                                args.input),
                    "timing": "CUDA events around K steps, barrier+synchronize both sides, max over ranks",
                    "host_enqueue_note": "with cuda_graph the host runs exactly one step ahead (it waits for step N-1 "
                                         "before rewriting that step's pinned hyper-parameter table), so its enqueue "
@@ -367,9 +374,10 @@ def main():
     ap.add_argument("--extra", default="", help="extra config lines for the ours arm, ';' separated")
     ap.add_argument("--no-verify", action="store_true",
                     help="skip the multi-GPU correctness check against a single-GPU twin (after the timed regions)")
-    ap.add_argument("--input", default="bf16", choices=["bf16", "u8"],
-                    help="host batches of the end-to-end measurement: bf16 (default, normalised on the host) or u8 "
-                         "(raw pixels, normalised on the device: half the bf16 bytes over PCIe)")
+    ap.add_argument("--input", default="u8", choices=["bf16", "u8"],
+                    help="host batches of the end-to-end measurement: u8 (default: raw pixels as the image iterators "
+                         "decode them, mean / scale applied on the device - a quarter of the fp32 bytes over PCIe) or "
+                         "bf16 (normalised on the host)")
     args = ap.parse_args()
     args.extra = args.extra.replace(";", "\n")
     args.warmup = max(args.warmup, 3)

@@ -13,13 +13,13 @@ extern "C" unsigned long long cxn_launch_counter_;
 
 // Optional histogram of launches per call site (CXN_LAUNCH_LOG=1: printed to stderr at exit; elementwise.cu).
 extern "C" int cxn_launch_log_on_;
-extern "C" void cxn_note_launch_(const char* file, int line);
+extern "C" void cxxnet_note_launch_(const char* file, int line);
 
 // Every launcher returns 0 on success or a cudaError_t / negative framework error.
 #define CXN_CHECK_LAUNCH()                                                     \
   do {                                                                         \
     ++cxn_launch_counter_;                                                     \
-    if (cxn_launch_log_on_) cxn_note_launch_(__FILE__, __LINE__);              \
+    if (cxn_launch_log_on_) cxxnet_note_launch_(__FILE__, __LINE__);              \
     cudaError_t e__ = cudaGetLastError();                                      \
     if (e__ != cudaSuccess) {                                                  \
       fprintf(stderr, "[cxxnet_b200] %s:%d launch failed: %s\n", __FILE__,     \

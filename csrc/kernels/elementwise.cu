@@ -319,7 +319,7 @@ int ll_init() {
 }  // namespace
 extern "C" {
 int cxn_launch_log_on_ = ll_init();
-void cxn_note_launch_(const char* file, int line) {
+void cxxnet_note_launch_(const char* file, int line) {
   std::lock_guard<std::mutex> g(g_ll_mu);
   if (!g_ll) return;
   const char* base = file;

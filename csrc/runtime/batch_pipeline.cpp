@@ -41,6 +41,8 @@ struct CxnioAugItem {
   int32_t warp_h, warp_w, warp_y, warp_x;
   float fill;
   double ai[6];
+  int32_t interp;         // 0 bilinear, 1 bicubic (Keys kernel, a = -0.75: cv::INTER_CUBIC of the reference)
+  int32_t pad_;
 };
 
 static inline uint16_t F32ToBf16(float f) {
@@ -90,6 +92,17 @@ CXNIO_CLONES static int AugmentOne(const float* src, int C, int sh, int sw, cons
   return 0;
 }
 
+// the four Keys (a = -0.75) weights of taps -1, 0, 1, 2 for fraction t; the expressions of ImageAugmenter.cubic_weights
+static inline void CubicWeights(float t, float* c) {
+  const float A = -0.75f;
+  const float t1 = t + 1.0f;
+  c[0] = ((A * t1 - 5.0f * A) * t1 + 8.0f * A) * t1 - 4.0f * A;
+  c[1] = ((A + 2.0f) * t - (A + 3.0f)) * t * t + 1.0f;
+  const float u = 1.0f - t;
+  c[2] = ((A + 2.0f) * u - (A + 3.0f)) * u * u + 1.0f;
+  c[3] = 1.0f - c[0] - c[1] - c[2];
+}
+
 // the H x W window at (wy, wx) of the affine-warped image, channel by channel, into `out` (C x H x W)
 CXNIO_CLONES static void WarpWindow(const float* src, int C, int sh, int sw, const CxnioAugItem& it, int H, int W,
                                     float* out) {
@@ -105,6 +118,29 @@ CXNIO_CLONES static void WarpWindow(const float* src, int C, int sh, int sw, con
       const float fx = float(sx - fxd), fy = float(sy - fyd);
       const bool okx0 = x0 >= 0 && x0 < sw, okx1 = x0 + 1 >= 0 && x0 + 1 < sw;
       const bool oky0 = y0 >= 0 && y0 < sh, oky1 = y0 + 1 >= 0 && y0 + 1 < sh;
+      if (it.interp == 1) {
+        // bicubic: 4 x 4 taps around (y0, x0), weights and summation order as ImageAugmenter.warp (io/iterators.py)
+        float cx[4], cy[4];
+        CubicWeights(fx, cx);
+        CubicWeights(fy, cy);
+        for (int c = 0; c < C; ++c) {
+          const float* pl = src + size_t(c) * sh * sw;
+          float v = 0.0f;
+          for (int j = 0; j < 4; ++j) {
+            const long yr = y0 - 1 + j;
+            const bool oky = yr >= 0 && yr < sh;
+            float t[4];
+            for (int i = 0; i < 4; ++i) {
+              const long xc = x0 - 1 + i;
+              t[i] = (oky && xc >= 0 && xc < sw) ? pl[yr * sw + xc] : fill;
+            }
+            const float r = ((t[0] * cx[0] + t[1] * cx[1]) + t[2] * cx[2]) + t[3] * cx[3];
+            v = j == 0 ? r * cy[0] : v + r * cy[j];
+          }
+          out[(size_t(c) * H + y) * W + x] = v;
+        }
+        continue;
+      }
       const float w00 = (1 - fx), w01 = fx;
       for (int c = 0; c < C; ++c) {
         const float* pl = src + size_t(c) * sh * sw;

@@ -67,6 +67,7 @@ class NeuralNet:
         self.arena_alloc = arena_alloc
         self.exchange = None
         self.tp = None           # parallel.tensor_parallel.TensorParallel when fully connected layers are column-sharded
+        self._shared_ids = set() # ids of layer objects used by several connections (share[tag])
         self.need_update = True
         self.accumulate_grads = False
         # (per-channel means, scale) of 8-bit input batches: x = (pixel - mean[c]) * scale, applied where the batch
@@ -221,12 +222,32 @@ class NeuralNet:
                 if not (c.layer.self_loop and n in c.nodes_out):
                     consumers[n.index] = consumers.get(n.index, 0) + 1
         producer: Dict[int, Connection] = {}
-        # a layer object used by several connections keeps per-layer scratch (im2col buffers),
-        # so weight-shared layers run through the bridge
+        # Weight sharing (`share[tag]`, reference neural_net-inl.hpp:238-244): one layer object serves several
+        # connections.  Fully connected and convolution layers (same shapes at every use, ordinary channel counts)
+        # and the element-wise activations stay native: the executor binds the connection's nodes to the layer before
+        # each call and makes the later uses of a backward pass ACCUMULATE into the one weight gradient; no epilogue /
+        # mask fusion is planned around a shared layer (a fused flag would apply to every use).  Other shared layer
+        # kinds keep per-layer state and run through the bridge.
         shared = set(id(c.layer) for c in self.connections if c.type == nc.kSharedLayer)
+        self._shared_ids = shared
+
+        def share_ok(layer):
+            uses = [k for k in self.connections if k.layer is layer]
+            first = uses[0]
+            same = all([n.shape[1:] for n in k.nodes_in] == [n.shape[1:] for n in first.nodes_in] and
+                       [n.shape[1:] for n in k.nodes_out] == [n.shape[1:] for n in first.nodes_out] for k in uses)
+            if isinstance(layer, native.FullConnectLayer):
+                return same
+            if isinstance(layer, native.ConvolutionLayer):
+                p = layer.param
+                return same and (p.num_input_channel // p.num_group) % 8 == 0 and all(k.nodes_in[0].index != 0 for k in uses)
+            return isinstance(layer, native._NativeAct)
         for c in self.connections:
-            c.native = bool(c.layer.has_b200) and id(c.layer) not in shared
+            c.native = bool(c.layer.has_b200) and (id(c.layer) not in shared or share_ok(c.layer))
             if c.native and hasattr(c.layer, "b200_supported"):
+                if id(c.layer) in shared:      # (the layer's own node binding is the primary's; shapes are the same at every use)
+                    prim = next(k for k in self.connections if k.layer is c.layer)
+                    c.layer.nodes_in, c.layer.nodes_out = prim.nodes_in, prim.nodes_out
                 c.native = bool(c.layer.b200_supported())
             if not c.layer.self_loop:
                 for n in c.nodes_out:
@@ -236,7 +257,7 @@ class NeuralNet:
         # kernel-path planning (may ask for a padded channel pitch on the input node)
         pitch: Dict[int, int] = {}
         for c in self.connections:
-            if c.native and hasattr(c.layer, "b200_plan"):
+            if c.native and hasattr(c.layer, "b200_plan") and c.type != nc.kSharedLayer:
                 x = c.nodes_in[0]
                 want = c.layer.b200_plan(self, x.index == 0, consumers.get(x.index, 0) == 1)
                 if isinstance(want, tuple):          # (channel pitch, row pitch in pixels)
@@ -272,7 +293,7 @@ class NeuralNet:
         # relu folding / aliasing
         for c in self.connections:
             l = c.layer
-            if c.native and isinstance(l, native._NativeAct) and l.alias_ok and c.type != nc.kSharedLayer:
+            if c.native and isinstance(l, native._NativeAct) and l.alias_ok and id(l) not in shared:
                 x, y = c.nodes_in[0], c.nodes_out[0]
                 if x is y or consumers.get(x.index, 0) != 1 or y.loss_input or x.loss_input:
                     continue
@@ -281,13 +302,14 @@ class NeuralNet:
                 p = producer.get(x.index)
                 if (p is not None and p.native and isinstance(l, native.ReluLayer)
                         and isinstance(p.layer, (native.FullConnectLayer, native.ConvolutionLayer))
-                        and consumers.get(x.index, 0) == 1):
+                        and id(p.layer) not in shared and consumers.get(x.index, 0) == 1):
                     p.layer.fuse_relu = True
                     l.fused = True
         # fold the backward mask of an aliased ReLU into the pooling layer that consumes it
         for c in self.connections:
             l = c.layer
-            if c.native and isinstance(l, native._NativePool) and not isinstance(l, native.InsanityPoolingLayer):
+            if c.native and isinstance(l, native._NativePool) and not isinstance(l, native.InsanityPoolingLayer) \
+                    and id(l) not in shared:
                 x = c.nodes_in[0]
                 p = producer.get(x.index)
                 if (p is not None and p.native and isinstance(p.layer, native.ReluLayer) and x.alias_of is not None
@@ -306,7 +328,7 @@ class NeuralNet:
         # ... or into the backward-data kernel of the convolution that consumes it
         for c in self.connections:
             l = c.layer
-            if c.native and isinstance(l, native.ConvolutionLayer) and l.igemm_dgrad:
+            if c.native and isinstance(l, native.ConvolutionLayer) and l.igemm_dgrad and id(l) not in shared:
                 x = c.nodes_in[0]
                 p = producer.get(x.index)
                 if (p is not None and p.native and isinstance(p.layer, native.ReluLayer) and x.alias_of is not None
@@ -387,7 +409,7 @@ class NeuralNet:
         for i, c in enumerate(self.connections):
             l = c.layer
             if not (c.native and isinstance(l, native.FullConnectLayer) and l.fullc_gather
-                    and c.type != nc.kSharedLayer) or l.tp is not None:
+                    and c.type != nc.kSharedLayer and id(l) not in self._shared_ids) or l.tp is not None:
                 continue
             p = l.param
             nin, nout = p.num_input_node, p.num_hidden
@@ -663,6 +685,8 @@ class NeuralNet:
                 self.tp.wait_layer(i)
             t0 = tm.begin() if tm else None
             if c.native:
+                if id(c.layer) in self._shared_ids:       # a shared layer works on this connection's nodes
+                    c.layer.nodes_in, c.layer.nodes_out = c.nodes_in, c.nodes_out
                 c.layer.b200_forward(self, is_train)
             else:
                 self._bridge_forward(c, is_train)
@@ -695,12 +719,20 @@ class NeuralNet:
                 self.arena.refresh_hyper(epoch)
         if self.exchange is not None:
             self.exchange.begin_step()
+        base_acc = self.accumulate_grads
+        seen = set()
         for i in range(n - 1, -1, -1):
             c = self.connections[i]
             prop = i != 0 or prop_to_input
             t0 = tm.begin() if tm else None
             if c.native:
+                if id(c.layer) in self._shared_ids:
+                    # every use after the first one of this pass adds to the shared weight gradient
+                    c.layer.nodes_in, c.layer.nodes_out = c.nodes_in, c.nodes_out
+                    self.accumulate_grads = base_acc or id(c.layer) in seen
+                    seen.add(id(c.layer))
                 c.layer.b200_backprop(self, prop)
+                self.accumulate_grads = base_acc
             else:
                 self._bridge_backprop(c, prop)
             if tm:

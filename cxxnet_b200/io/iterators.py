@@ -535,8 +535,10 @@ class ImageBinIterator(IIterator):
 # ----------------------------------------------------------------------------- augmentation
 class ImageAugmenter:
     """affine rotate / shear / scale / aspect warp + crop (reference ``src/io/image_augmenter-inl.hpp:13-204``).
-    The warp is an inverse-mapped bilinear resample in numpy (the reference calls OpenCV
-    ``warpAffine`` with bicubic interpolation)."""
+    The warp is an inverse-mapped resample in numpy: bicubic by default, as the reference's OpenCV ``warpAffine`` call
+    (``cv::INTER_CUBIC``, ``image_augmenter-inl.hpp:105-108``: the Keys kernel with a = -0.75, constant border =
+    ``fill_value``), in float arithmetic where OpenCV uses 1/32-pixel fixed-point tables; ``warp_interp = bilinear``
+    selects the cheaper two-by-two kernel."""
 
     def __init__(self):
         self.shape = (0, 0, 0)
@@ -550,6 +552,7 @@ class ImageAugmenter:
         self.min_img_size, self.max_img_size = 0.0, 1e10
         self.fill_value = 255
         self.rotate_list: List[int] = []
+        self.bicubic = True
 
     def set_param(self, name, val):
         if name == "input_shape": self.shape = tuple(int(x) for x in val.split(","))
@@ -566,6 +569,10 @@ class ImageAugmenter:
         if name == "fill_value": self.fill_value = int(val)
         if name == "rotate": self.rotate = int(val)
         if name == "rotate_list": self.rotate_list = [int(x) for x in val.split(",") if x]
+        if name == "warp_interp":
+            if val not in ("bicubic", "bilinear"):
+                raise ValueError("warp_interp must be bicubic or bilinear")
+            self.bicubic = val == "bicubic"
 
     def need_process(self) -> bool:
         if self.max_rotate_angle > 0 or self.max_shear_ratio > 0.0 or self.rotate > 0 or self.rotate_list:
@@ -604,8 +611,22 @@ class ImageAugmenter:
             y, x = y // 2, x // 2
         return Ai, new_h, new_w, y, x, True
 
+    @staticmethod
+    def cubic_weights(t):
+        """the four Keys (a = -0.75) weights of taps -1, 0, 1, 2 for fraction t (float32, this operation order - the
+        native stage csrc/runtime/batch_pipeline.cpp evaluates the same expressions)"""
+        A = np.float32(-0.75)
+        one = np.float32(1.0)
+        t1 = t + one
+        c0 = ((A * t1 - np.float32(5.0) * A) * t1 + np.float32(8.0) * A) * t1 - np.float32(4.0) * A
+        c1 = ((A + np.float32(2.0)) * t - (A + np.float32(3.0))) * t * t + one
+        u = one - t
+        c2 = ((A + np.float32(2.0)) * u - (A + np.float32(3.0))) * u * u + one
+        c3 = one - c0 - c1 - c2
+        return c0, c1, c2, c3
+
     def warp(self, data: np.ndarray, params) -> np.ndarray:
-        """bilinear inverse-mapped resample of `data` (c, rows, cols) with the decisions of `draw`"""
+        """inverse-mapped resample (bicubic or bilinear) of `data` (c, rows, cols) with the decisions of `draw`"""
         Ai, new_h, new_w, y, x, cropped = params
         c, rows, cols = data.shape
         ys, xs = np.mgrid[0:new_h, 0:new_w]
@@ -613,13 +634,24 @@ class ImageAugmenter:
         sy = Ai[1, 0] * xs + Ai[1, 1] * ys + Ai[1, 2]
         x0, y0 = np.floor(sx).astype(int), np.floor(sy).astype(int)
         fx, fy = (sx - x0).astype(np.float32), (sy - y0).astype(np.float32)
+        data = np.asarray(data, dtype=np.float32)
+        fill = np.float32(self.fill_value)
 
         def tap(yy, xx):
             ok = (yy >= 0) & (yy < rows) & (xx >= 0) & (xx < cols)
             v = data[:, np.clip(yy, 0, rows - 1), np.clip(xx, 0, cols - 1)]
-            return np.where(ok[None], v, float(self.fill_value))
-        out = (tap(y0, x0) * (1 - fx) * (1 - fy) + tap(y0, x0 + 1) * fx * (1 - fy)
-               + tap(y0 + 1, x0) * (1 - fx) * fy + tap(y0 + 1, x0 + 1) * fx * fy).astype(np.float32)
+            return np.where(ok[None], v, fill)
+        if self.bicubic:
+            cx, cy = self.cubic_weights(fx), self.cubic_weights(fy)
+            out = None
+            for j in range(4):
+                r = ((tap(y0 - 1 + j, x0 - 1) * cx[0] + tap(y0 - 1 + j, x0) * cx[1]) + tap(y0 - 1 + j, x0 + 1) * cx[2]) \
+                    + tap(y0 - 1 + j, x0 + 2) * cx[3]
+                out = r * cy[j] if out is None else out + r * cy[j]
+            out = out.astype(np.float32)
+        else:
+            out = (tap(y0, x0) * (1 - fx) * (1 - fy) + tap(y0, x0 + 1) * fx * (1 - fy)
+                   + tap(y0 + 1, x0) * (1 - fx) * fy + tap(y0 + 1, x0 + 1) * fx * fy).astype(np.float32)
         if not cropped:
             return out
         return out[:, y:y + self.shape[2], x:x + self.shape[1]]
@@ -945,7 +977,7 @@ class BatchAdaptIterator(IIterator):
                 Ai, new_h, new_w, wy, wx, cropped = aug.aug.draw(h, w, aug.rnd)
                 if not cropped:
                     raise ValueError("Data size must be bigger than the input size to net.")
-                affine = (Ai, new_h, new_w, wy, wx, float(aug.aug.fill_value))
+                affine = (Ai, new_h, new_w, wy, wx, float(aug.aug.fill_value), 1 if aug.aug.bicubic else 0)
                 params = tuple(aug.draw_params(self.shape[1], self.shape[2]))
             else:
                 params = tuple(aug.draw_params(h, w))

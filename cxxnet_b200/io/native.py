@@ -67,7 +67,7 @@ class AugItem(ctypes.Structure):
                 ("flip", ctypes.c_int32), ("contrast", ctypes.c_float), ("illum", ctypes.c_float),
                 ("affine", ctypes.c_int32), ("warp_h", ctypes.c_int32), ("warp_w", ctypes.c_int32),
                 ("warp_y", ctypes.c_int32), ("warp_x", ctypes.c_int32), ("fill", ctypes.c_float),
-                ("ai", ctypes.c_double * 6)]
+                ("ai", ctypes.c_double * 6), ("interp", ctypes.c_int32), ("pad_", ctypes.c_int32)]
 
 
 class PageReader:
@@ -249,7 +249,8 @@ def decode_augment_batch(items, shape, mean_mode: int, mean, scale: float, dst, 
         affine = item[9] if len(item) > 9 else None
         a = arr[i]
         if affine is not None:
-            Ai, a.warp_h, a.warp_w, a.warp_y, a.warp_x, a.fill = affine
+            Ai, a.warp_h, a.warp_w, a.warp_y, a.warp_x, a.fill = affine[:6]
+            a.interp = int(affine[6]) if len(affine) > 6 else 0
             a.affine = 1
             for k in range(6):
                 a.ai[k] = float(Ai[k // 3, k % 3])

@@ -58,7 +58,12 @@ class GradExchange:
         self.rank, self.world = net.rank, net.world_size
         self.device = net.device
         self.grid = grid or int(os.environ.get("CXN_XCHG_GRID", "296"))
-        self.min_bucket_bytes = int(float(os.environ.get("CXN_XCHG_MIN_BUCKET_MB", "4")) * (1 << 20))
+        # Bucket size: on four or more ranks every launch costs two all-rank flag barriers whose price is the skew
+        # between the ranks, not bytes - measured on 8 GPUs (profiles/r2_scaling.md) one launch for all convolution
+        # layers of AlexNet (9.3 MB, at the end of backward) beats three overlapped ones by 0.05 ms per step; on two
+        # ranks small buckets overlapped with the backward pass stay ahead.
+        default_mb = "4" if self.world < 4 else "64"
+        self.min_bucket_bytes = int(float(os.environ.get("CXN_XCHG_MIN_BUCKET_MB", default_mb)) * (1 << 20))
         self.seq = 0
         L = ops.lib()
         P, I, LL, U = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_uint

@@ -82,7 +82,8 @@ class TensorParallel:
             c = conns[i]
             l = c.layer
             if not (c.native and isinstance(l, native.FullConnectLayer) and getattr(l, "fullc_shard", 0)
-                    and c.type != 0 and not getattr(l, "fullc_gather", 0)):
+                    and c.type != 0 and not getattr(l, "fullc_gather", 0)
+                    and id(l) not in getattr(net, "_shared_ids", ())):
                 return False
             p = l.param
             ns = ops.round_up((p.num_hidden + self.world - 1) // self.world, 8)

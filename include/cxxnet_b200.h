@@ -253,6 +253,25 @@ int cxn_xchg_set_epoch_ptr(const void* dev_word);
 int cxn_xchg_flag_bytes(void);
 int cxn_xchg_max_ranks(void);
 int cxn_xchg_max_slots(void);
+/* Collectives of the column-sharded (model-parallel) fully connected layers (csrc/kernels/tp_collectives.cu): the
+ * reference moves whole weight gradients / weights of these layers through its parameter server
+ * (src/updater/async_updater-inl.hpp:94-127); here the weights stay with their owner and activations move.
+ *   cxn_tp_push         one 2-D sub-block per destination rank (desc: nranks x {src_off, dst_off, nrows, valid_rows,
+ *                       row_bytes} as long long; rows >= valid_rows are written as zeros) from local memory into every
+ *                       rank's symmetric block by peer stores, then ONE flag barrier (signal, wait for all).
+ *   cxn_tp_reduce_pull  flag barrier ("my partial is complete"), then dst = sum over ranks of the same sub-block of
+ *                       every rank's bf16 partial matrix (peer loads, fp32 sum, bf16 result).
+ * `peers`: HOST array of block base addresses as mapped here; off_flags: cxn_tp_flag_bytes() zeroed bytes inside every
+ * block; counters: cxn_tp_counter_bytes() zeroed LOCAL device bytes (the per-slot sequence numbers live there, so a
+ * launch captured in a CUDA graph replays correctly); all offsets / pitches / row_bytes multiples of 16. */
+int cxn_tp_flag_bytes(void);
+int cxn_tp_counter_bytes(void);
+int cxn_tp_max_slots(void);
+int cxn_tp_push(const unsigned long long* peers, int nranks, int rank, long long off_flags, int slot, unsigned* counters,
+                const void* src, long long src_ld, long long dst_ld, const long long* desc, int grid, cudaStream_t stream);
+int cxn_tp_reduce_pull(const unsigned long long* peers, int nranks, int rank, long long off_flags, int slot,
+                       unsigned* counters, long long part_off, long long part_ld, long long pull_off, int rows,
+                       int row_bytes, void* dst, long long dst_ld, int grid, cudaStream_t stream);
 /* CUDA IPC helpers for the symmetric block (these DO allocate / map device memory). */
 int cxn_ipc_alloc(unsigned long long bytes, unsigned long long* ptr, unsigned char* handle64);
 int cxn_ipc_open(const unsigned char* handle64, unsigned long long* ptr);

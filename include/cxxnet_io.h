@@ -63,6 +63,8 @@ typedef struct CxnioAugItem {
   int32_t warp_h, warp_w, warp_y, warp_x;
   float fill;            /* value outside the decoded image */
   double ai[6];          /* inverse affine map, two rows: source x = ai[0] x + ai[1] y + ai[2], source y = ai[3..5] */
+  int32_t interp;        /* resampling kernel of the warp: 0 bilinear, 1 bicubic (a = -0.75, as cv::INTER_CUBIC) */
+  int32_t pad_;
 } CxnioAugItem;
 /* mean_mode 0 none | 1 mean[c] per channel | 2 mean image of the decoded size (subtracted before crop / mirror) |
  * 3 mean image of the crop size (after).  dst: [n][C][H][W], fp32, (dst_bf16 = 1) bf16 or (dst_bf16 = 2) uint8 - the

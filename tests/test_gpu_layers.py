@@ -313,3 +313,45 @@ layer[+0] = softmax
     assert 0.5 < kept < 0.7                                                 # keep = 0.6
     up = float(((dy == -1) & interior).sum()) / float(interior.sum())
     assert 0.06 < up < 0.14                                                 # (1 - keep) / 4 = 0.1
+
+
+def test_shared_layers_stay_native():
+    """`share[tag]` (reference neural_net-inl.hpp:238-244): a fully connected autoencoder with tied weights and a
+    convolution applied twice.  Both uses run the native kernels (no layout bridge), the weight gradient is the sum
+    over the uses, and the net remains eligible for a captured step."""
+    body = """
+layer[0->1] = fullc:enc
+  nhidden = 64
+layer[1->2] = tanh
+layer[2->3] = share[enc]
+layer[3->4] = relu
+layer[4->5] = fullc:out
+  nhidden = 7
+layer[5->5] = softmax
+"""
+    errs, ref, b2 = compare_backends(_conf(body, 33, "1,1,64"), make_batch((33, 1, 1, 64), nclass=7), return_trainers=True)
+    assert all(c.native for c in b2.net.connections), [c.native for c in b2.net.connections]
+    assert b2.net.connections[2].layer is b2.net.connections[0].layer
+    body = """
+layer[0->1] = conv:stem
+  kernel_size = 3
+  pad = 1
+  nchannel = 16
+layer[1->2] = relu
+layer[2->3] = conv:twice
+  kernel_size = 3
+  pad = 1
+  nchannel = 16
+layer[3->4] = relu
+layer[4->5] = share[twice]
+layer[5->6] = relu
+layer[6->7] = flatten
+layer[7->8] = fullc:out
+  nhidden = 5
+layer[8->8] = softmax
+"""
+    errs, ref, b2 = compare_backends(_conf(body, 9, "3,10,10"), make_batch((9, 3, 10, 10), nclass=5), return_trainers=True)
+    assert all(c.native for c in b2.net.connections), [c.native for c in b2.net.connections]
+    # two updates through the public path: graphs stay possible (nothing forces the eager route)
+    b2._graph_unsafe = None
+    assert b2._graph_applicable(make_batch((9, 3, 10, 10), nclass=5))

@@ -392,7 +392,7 @@ silent = 1
 
 def test_native_affine_stage_equals_the_numpy_warp(tmp_path):
     """rotation / shear / aspect / scale (the kaggle bowl augmentation) on the native batch path: same random
-    decisions, same bilinear arithmetic, bit-identical batches"""
+    decisions, same bicubic (default) / bilinear arithmetic, bit-identical batches"""
     import torch
     from cxxnet_b200.config import parse_config_string
     from cxxnet_b200.io.data import create_iterator
@@ -414,7 +414,8 @@ def test_native_affine_stage_equals_the_numpy_warp(tmp_path):
         return out
 
     for extra in ("", " mean_value = 90,100,110\n divideby = 32\n max_random_contrast = 0.1\n",
-                  ' image_mean = "%s"\n fill_value = 0\n' % (tmp_path / "m.bin")):
+                  ' image_mean = "%s"\n fill_value = 0\n' % (tmp_path / "m.bin"),
+                  " warp_interp = bilinear\n"):      # default: bicubic (cv::INTER_CUBIC of the reference)
         if "image_mean" in extra:
             batches(0, extra)                       # first use creates the mean image
         a, b = batches(0, extra), batches(1, extra)

@@ -265,3 +265,35 @@ def test_single_channel_net_reads_image_sources(tmp_path):
         return out
     a0, a1 = run(0), run(1)
     assert len(a0) == 2 and all(torch.equal(x, y) for x, y in zip(a0, a1))
+
+
+def test_bicubic_warp_reproduces_cubics_and_the_identity():
+    """the affine warp resamples with the Keys kernel (a = -0.75, cv::INTER_CUBIC of the reference,
+    src/io/image_augmenter-inl.hpp:105-108): integer positions return the pixel, the weights sum to one, a linear
+    ramp is reproduced exactly away from the border, and positions outside read fill_value"""
+    from cxxnet_b200.io.iterators import ImageAugmenter
+    aug = ImageAugmenter()
+    aug.set_param("input_shape", "1,8,8")
+    aug.set_param("fill_value", "7")
+    t = np.linspace(0, 1, 11, dtype=np.float32)[:-1]
+    c = aug.cubic_weights(t)
+    assert np.allclose(sum(c), 1.0, atol=1e-6)
+    assert np.allclose([w[0] for w in c], [0.0, 1.0, 0.0, 0.0], atol=1e-7)         # t = 0: the pixel itself
+    assert np.isclose(c[1][5], 0.59375) and np.isclose(c[0][5], -0.09375)        # t = 0.5, a = -0.75: (-3, 19, 19, -3) / 32
+    img = np.arange(12 * 12, dtype=np.float32).reshape(1, 12, 12)
+    shift = np.array([[1.0, 0.0, 2.25], [0.0, 1.0, 1.5], [0.0, 0.0, 1.0]])            # dst(x, y) = src(x + 2.25, y + 1.5)
+    out = aug.warp(img, (shift, 12, 12, 0, 0, False))
+    want = np.fromfunction(lambda y, x: (y + 1.5) * 12 + (x + 2.25), (12, 12))
+    # a = -0.75 (unlike a = -0.5) does not reproduce a ramp exactly: at fraction t the kernel's centroid is
+    # -c0 + c2 + 2 c3 instead of t - the same small bias OpenCV's INTER_CUBIC has
+    def centroid(t):
+        c = [float(v) for v in aug.cubic_weights(np.float32(t))]
+        return -c[0] + c[2] + 2 * c[3]
+    cub = want + (centroid(0.25) - 0.25) + 12 * (centroid(0.5) - 0.5)
+    assert abs(centroid(0.5) - 0.5) < 1e-6 and abs(centroid(0.25) - 0.25) < 0.05
+    assert np.allclose(out[0, 1:8, 1:7], cub[1:8, 1:7], atol=1e-3)
+    assert out[0, 11, 11] != want[11, 11] and np.isfinite(out).all()                  # border taps read the fill value
+    far = aug.warp(img, (np.array([[1.0, 0, 100.0], [0, 1.0, 100.0], [0, 0, 1.0]]), 4, 4, 0, 0, False))
+    assert np.allclose(far, 7.0)
+    aug.set_param("warp_interp", "bilinear")
+    assert np.allclose(aug.warp(img, (shift, 12, 12, 0, 0, False))[0, 1:8, 1:7], want[1:8, 1:7], atol=1e-3)   # exact

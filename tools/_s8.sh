@@ -8,12 +8,16 @@ run() { # name dir extra...
 import json
 try:
     d=json.loads([l for l in open("$OUT/bench_${N}_$name.json") if l.startswith('{')][-1])
-    print("$name", round(d['value']), 'img/s', round(d['ms_per_step'],4), 'ms  e2e', round(d['e2e']['value']), 'host', round(d['host_enqueue_ms_per_step'],3), d.get('replica_max_diff'))
+    print("N=$N $name", round(d['value']), 'img/s', round(d['ms_per_step'],4), 'ms  e2e', round(d['e2e']['value']), round(d['e2e']['ms_per_step'],4), 'launches/step', d['gpu_launches']/d['steps'], d.get('replica_max_diff'))
 except Exception as e:
     print("$name failed", e)
 PY
 }
+if [ "$N" = "4" ]; then
 run r1_gather build/r1
-run cur_gather . --no-verify --extra "fullc_gather = 1"
-run cur_tp . --no-verify
-run r1_gather_again build/r1
+CXN_XCHG_MIN_BUCKET_MB=4 run tp_3buckets . --no-verify
+run tp_1bucket . --no-verify
+run tp_1bucket_u8 . --no-verify --input u8
+else
+run tp_1bucket_u8 . --input u8
+fi
