@@ -231,6 +231,8 @@ def run_ours(args, rank, world, local):
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8},
         "gpu_launches": int(launches), "clocks": clocks, "train_error_running": err,
     }
+    if tr.net.trace_buf is not None:
+        sys.stderr.write("rank %d\n%s\n" % (rank, tr.net.trace_report()))
     if world > 1:
         # outside the timed regions: are the replicas of the timed trainer identical, and does a multi-rank run
         # reproduce a single-GPU run of the same batches?

@@ -1904,8 +1904,9 @@ static int conv_wgrad_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   const int num_kb = (int)ceil_div_ll(rows, BK);
   const long long base_tiles = (long long)ceil_div(Ng, BM) * ceil_div(p.Kg, p.bn) * G;
   if (splits <= 0) {
-    // aim at ~4 tiles per SM so the round-robin tile assignment stays balanced, but keep at least
-    // 8 k-blocks per tile and never exceed a whole number of waves by a few stragglers
+    // aim at ~4 tiles per SM so the round-robin tile assignment stays balanced and the fp32 reduction of one tile
+    // overlaps the main loop of the next (two accumulator stages), but keep at least 8 k-blocks per tile.  (Measured:
+    // fewer, deeper splits - one tile per SM at batch 32..128 - are 1.5-3 % slower per step, profiles/r2_experiments.md.)
     splits = (int)((4LL * num_sms()) / base_tiles);
     const int max_splits = num_kb / 8 > 0 ? num_kb / 8 : 1;
     if (splits > max_splits) splits = max_splits;

@@ -464,6 +464,19 @@ CXN_API int cxn_fill_f32(float* p, long long n, float v, cudaStream_t st) {
   CXN_CHECK_LAUNCH();
   return 0;
 }
+// Step trace: a one-thread kernel that stores the GPU's global nanosecond timer; placed between the layers of a step
+// (also inside a captured graph) it gives a device-side timeline without a profiler - the only kind available for
+// multi-rank runs.  buf[slot] is overwritten at every execution.
+__global__ void timestamp_kernel(unsigned long long* buf, int slot) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  buf[slot] = t;
+}
+CXN_API int cxn_timestamp(unsigned long long* buf, int slot, cudaStream_t st) {
+  timestamp_kernel<<<1, 1, 0, st>>>(buf, slot);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
 CXN_API int cxn_counter_add(unsigned long long* counter, unsigned long long inc, cudaStream_t st) {
   counter_add_kernel<<<1, 1, 0, st>>>(counter, inc);
   CXN_CHECK_LAUNCH();

@@ -68,6 +68,10 @@ class NeuralNet:
         self.exchange = None
         self.tp = None           # parallel.tensor_parallel.TensorParallel when fully connected layers are column-sharded
         self._shared_ids = set() # ids of layer objects used by several connections (share[tag])
+        # step trace (`step_trace = 1` / CXN_STEP_TRACE=1): device timestamps between the layers of a step, also
+        # inside a captured graph; read with trace_report()
+        self.trace_buf = None
+        self.trace_names = []
         self.need_update = True
         self.accumulate_grads = False
         # (per-channel means, scale) of 8-bit input batches: x = (pixel - mean[c]) * scale, applied where the batch
@@ -667,6 +671,31 @@ class NeuralNet:
             ops.check(L.cxn_nchw_f32_to_nhwc_bf16(st.data_ptr(), n.act.ptr, b, c, h * w, n.act.ld, ops.stream()),
                       "nchw_to_nhwc")
 
+    # ------------------------------------------------------------------ step trace
+    def enable_trace(self) -> None:
+        n = len(self.connections)
+        self.trace_names = ["begin"] + ["f%d:%s" % (i, c.layer.type_name) for i, c in enumerate(self.connections)] + \
+                           ["metric"] + ["b%d:%s" % (i, self.connections[i].layer.type_name) for i in range(n - 1, -1, -1)] + ["end"]
+        self.trace_buf = torch.zeros(len(self.trace_names), dtype=torch.int64, device=self.device)
+
+    def _mark(self, slot: int) -> None:
+        if self.trace_buf is not None:
+            ops.check(ops.lib().cxn_timestamp(self.trace_buf.data_ptr(), slot, ops.stream()), "timestamp")
+
+    def trace_report(self) -> str:
+        """time between consecutive marks of the LAST executed step (us): a layer's entry is the stream time from the
+        previous mark to the mark after the layer's last launch, barrier waits included"""
+        if self.trace_buf is None:
+            return ""
+        t = self.trace_buf.cpu().tolist()
+        lines = ["step trace (us, device %globaltimer; last step)"]
+        for k in range(1, len(t)):
+            if t[k] and t[k - 1]:
+                lines.append("%-24s %9.1f" % (self.trace_names[k], (t[k] - t[k - 1]) / 1e3))
+        if t[0] and t[-1]:
+            lines.append("%-24s %9.1f" % ("whole step", (t[-1] - t[0]) / 1e3))
+        return "\n".join(lines)
+
     def forward(self, is_train: bool) -> None:
         tm = self.timer
         if self.backend == "ref":
@@ -678,6 +707,8 @@ class NeuralNet:
             return
         if self.exchange is not None:
             self.exchange.publish_pending()
+        if is_train:
+            self._mark(0)
         for i, c in enumerate(self.connections):
             if self.exchange is not None:
                 self.exchange.wait_layer(i)   # UpdateWait: this layer's weights from the last exchange
@@ -692,6 +723,8 @@ class NeuralNet:
                 self._bridge_forward(c, is_train)
             if tm:
                 tm.end("f", i, t0)
+            if is_train:
+                self._mark(1 + i)
 
     def backprop(self, prop_to_input: bool, need_update: bool, epoch: int) -> None:
         n = len(self.connections)
@@ -719,6 +752,7 @@ class NeuralNet:
                 self.arena.refresh_hyper(epoch)
         if self.exchange is not None:
             self.exchange.begin_step()
+        self._mark(1 + n)          # the train metric and the hyper-parameter upload sit between forward and backward
         base_acc = self.accumulate_grads
         seen = set()
         for i in range(n - 1, -1, -1):
@@ -739,10 +773,15 @@ class NeuralNet:
                 tm.end("b", i, t0)
             if need_update and self.exchange is not None:
                 self.exchange.layer_done(i)
+            self._mark(2 + n + (n - 1 - i))
         if need_update and self.exchange is None:
             self.arena.update()
         if self.tp is not None:
             self.tp.end_step()
+        if self.trace_buf is not None:
+            if self.exchange is not None:
+                self.exchange.wait_all()
+            self._mark(2 + 2 * n)
         ops.check(ops.lib().cxn_counter_add(self.step_counter.data_ptr(), 1, ops.stream()), "counter_add")
 
     def update_all(self, epoch: int) -> None:

@@ -102,6 +102,7 @@ def lib():
     _sig(L.cxn_update, [P, P, P, P, P, P, P, LL, LL, I, P])
     _sig(L.cxn_refresh_shadow, [P, P, P, P, LL, P])
     _sig(L.cxn_counter_add, [P, ULL, P])
+    _sig(L.cxn_timestamp, [P, I, P])
     L.cxn_launch_count.restype = c_ulonglong
     L.cxn_launch_count_add.restype = c_ulonglong
     L.cxn_launch_count_add.argtypes = [c_ulonglong]

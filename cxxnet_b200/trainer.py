@@ -83,6 +83,7 @@ class NetTrainer:
         self.test_on_server = 0
         self.check_nan = 0
         self.layer_timing = 0
+        self.step_trace = int(os.environ.get("CXN_STEP_TRACE", "0"))
         self.graph_warmup = 3
         self._graphs = {}            # staging slot -> (torch.cuda.CUDAGraph, launches inside)
         self._graph_rows = -1
@@ -106,6 +107,7 @@ class NetTrainer:
         # round.  Here: every round all ranks compare their replicas with rank 0's (collective).
         if name == "test_on_server": self.test_on_server = int(val)
         if name == "layer_timing": self.layer_timing = int(val)     # per-layer timers, see utils/timing.py
+        if name == "step_trace": self.step_trace = int(val)         # device timestamps between layers (executor.enable_trace)
         # check_nan = 1: every round starts with a look at the weights; a NaN / Inf stops the run and names the
         # layer (the reference only notices inside the logloss metric, src/utils/metric.h:128)
         if name == "check_nan": self.check_nan = int(val)
@@ -214,6 +216,8 @@ class NetTrainer:
     def _finish_init(self) -> None:
         self.net.init_updaters()
         self.net.init_nodes()
+        if self.step_trace and self.net.backend == "b200":
+            self.net.enable_trace()
 
     # ------------------------------------------------------------------ model
     def init_model(self) -> None:

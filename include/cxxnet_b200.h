@@ -283,6 +283,10 @@ int cxn_ipc_free(unsigned long long ptr);
  * other operand runs on the non-cluster kernels.  No reference counterpart. */
 int cxn_memory_is_local(const void* p, unsigned long long bytes);
 
+/* step trace: stores the GPU's %globaltimer (ns) into buf[slot]; one thread, capturable.  No reference counterpart
+ * (the reference has no profiling facility). */
+int cxn_timestamp(unsigned long long* buf, int slot, cudaStream_t stream);
+
 /* number of kernel launches issued by this library in this process */
 unsigned long long cxn_launch_count(void);
 unsigned long long cxn_launch_count_add(unsigned long long n);   /* account for kernels replayed from a CUDA graph */

@@ -1,12 +1,13 @@
 set -u
 OUT=$PWD/gpurun_out; mkdir -p $OUT
 python build.py > $OUT/build.log 2>&1 || { tail -20 $OUT/build.log; exit 1; }
+echo "== gpu tests"
 timeout 1500 python -m pytest tests -m gpu -q > $OUT/pytest_gpu.log 2>&1; echo "pytest exit $?"; grep -E "passed|failed|^FAILED|Error: " $OUT/pytest_gpu.log | head -20
-timeout 300 python bench.py --steps 20 --warmup 5 > $OUT/b1.json 2>$OUT/b1.err; python -c "
-import json; d=json.loads([l for l in open('$OUT/b1.json') if l.startswith('{')][-1]); print('cur b256', round(d['value']), round(d['ms_per_step'],4), 'ms launches', d['gpu_launches'], 'err', d['train_error_running'])"
-timeout 600 python bench/gemm_sweep.py > $OUT/gemm_sweep.txt 2>&1; python - <<PY
-import json
-for l in open("$OUT/gemm_sweep.txt"):
-    if l.startswith('{'):
-        d=json.loads(l); print(d['shape'], 'auto', d['auto_us'], 'bn256', d['bn256_us'], 'pair', d.get('pair_us'), 'cublas', d['cublas_us'])
-PY
+echo "== bench 1 GPU"
+timeout 300 python bench.py --steps 20 --warmup 5 > $OUT/b1.json 2>$OUT/b1.err; cat $OUT/b1.json | cut -c1-300
+timeout 300 python bench.py --steps 20 --warmup 5 --impl library > $OUT/b1_library.json 2>$OUT/b1_library.err; cat $OUT/b1_library.json | cut -c1-300
+echo "== config benches"
+timeout 300 python bench/config_bench.py --model lenet > $OUT/cfg_lenet_1.json 2>$OUT/cfg_lenet_1.err; cat $OUT/cfg_lenet_1.json | cut -c1-400
+timeout 300 python bench/config_bench.py --model bowl > $OUT/cfg_bowl_1.json 2>$OUT/cfg_bowl_1.err; cat $OUT/cfg_bowl_1.json | cut -c1-400
+echo "== memcheck (small shapes)"
+timeout 900 compute-sanitizer --tool memcheck --error-exitcode 7 python -m pytest tests/test_gpu_gemm.py tests/test_gpu_conv.py tests/test_gpu_exchange_single.py -q -x -k "basic or cta_pairs or odd_shapes or single_rank or 3x3_wide" > $OUT/sanitizer_memcheck.log 2>&1; echo "memcheck exit $?"; grep -E "ERROR SUMMARY|passed|failed|Invalid|error" $OUT/sanitizer_memcheck.log | head -10
