@@ -237,6 +237,7 @@ def run_ours(args, rank, world, local):
         # outside the timed regions: are the replicas of the timed trainer identical, and does a multi-rank run
         # reproduce a single-GPU run of the same batches?
         out["replica_max_diff"] = tr.net.exchange.check_replicas()
+        out["symmetric_memory"] = tr.net.symm_block.kind       # ipc | vmm | nvls (NVSwitch multicast: multimem.*)
         if not args.no_verify:
             rep, rel_w, rel_dw = verify_multi(args, rank, world, local, extra)
             out["verify"] = {"replica_max_diff_after_3_steps": rep, "max_rel_err_vs_1gpu": rel_w,

@@ -50,6 +50,7 @@ struct Params {
   unsigned seq;
   const unsigned* seq_dev;  // optional device word added to seq when the kernel starts (cxn_xchg_set_epoch_ptr)
   int slot;
+  char* mc;                 // NVSwitch multicast address of the symmetric block (null = unicast peer loads / stores)
   unsigned* counter;        // local scratch: CTA completion counter (zero between launches)
   int dbg;                  // profiling aid (CXN_XCHG_DBG): 1 skip peer loads, 2 skip peer stores, 4 skip phase 2
 };
@@ -73,6 +74,21 @@ __device__ __forceinline__ float4 ld_sys_f4(const float* p) {
 }
 __device__ __forceinline__ void st_sys_f4(float* p, float4 v) {
   asm volatile("st.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+// NVLS: one load that returns the SUM of the same 16 bytes of every rank's block (reduced inside the switch), one
+// store that lands in every rank's block.  Plain multimem instructions on the multicast address, not TMA.
+__device__ __forceinline__ float4 mc_ld_reduce_f4(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void mc_st_f4(float* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w)
                : "memory");
 }
 __device__ __forceinline__ unsigned* flag_ptr(char* base, long long off_flags, int which, int slot, int src) {
@@ -148,6 +164,13 @@ fused_rs_update_ag_kernel(const Params p) {
       acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
       live[u] = ch0 + u < my1;
     }
+    if (p.mc != nullptr && !(p.dbg & 1)) {
+      // the switch adds the ranks' gradients: one load per 16 bytes instead of one per rank
+      const float* gmc = reinterpret_cast<const float*>(p.mc + p.off_g);
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (live[u]) acc[u] = mc_ld_reduce_f4(gmc + (ch0 + u) * kChunk + threadIdx.x * 4);
+    } else
     // issue every load of a group of up to NR ranks before consuming any of them
     for (int r0 = 0; r0 < p.nranks; r0 += NR) {
       float4 buf[NR][U];
@@ -207,9 +230,13 @@ fused_rs_update_ag_kernel(const Params p) {
       }
       *reinterpret_cast<float4*>(m + e) = mv;
       if (p.kind == 2) *reinterpret_cast<float4*>(m2 + e) = m2v;
-      for (int r = 0; r < p.nranks; ++r) {
-        const int dst = (p.dbg & 2) ? p.rank : (p.rank + r) % p.nranks;
-        st_sys_f4(reinterpret_cast<float*>(p.peers[dst] + p.off_w) + e, wv);
+      if (p.mc != nullptr && !(p.dbg & 2)) {
+        mc_st_f4(reinterpret_cast<float*>(p.mc + p.off_w) + e, wv);      // one store, every rank's arena
+      } else {
+        for (int r = 0; r < p.nranks; ++r) {
+          const int dst = (p.dbg & 2) ? p.rank : (p.rank + r) % p.nranks;
+          st_sys_f4(reinterpret_cast<float*>(p.peers[dst] + p.off_w) + e, wv);
+        }
       }
     }
   }
@@ -349,6 +376,14 @@ using namespace cxn::xchg;
 // Device word (4-byte aligned, lives as long as exchanges are launched) whose value every exchange
 // kernel adds to its `seq` argument; NULL (the default) = the argument alone.  One GPU per process.
 static const unsigned* g_epoch_ptr = nullptr;
+// Multicast address of the symmetric block (parallel/symm.py, kind "nvls"), or null: the reduce-scatter and the
+// all-gather of the fused exchange then use multimem.ld_reduce / multimem.st.  CXN_XCHG_NVLS=0 keeps the unicast path.
+static char* g_mc_base = nullptr;
+CXN_API int cxn_xchg_set_multicast(void* mc_base) {
+  static const bool off = getenv("CXN_XCHG_NVLS") != nullptr && atoi(getenv("CXN_XCHG_NVLS")) == 0;
+  g_mc_base = off ? nullptr : reinterpret_cast<char*>(mc_base);
+  return 0;
+}
 CXN_API int cxn_xchg_set_epoch_ptr(const void* dev_word) {
   g_epoch_ptr = reinterpret_cast<const unsigned*>(dev_word);
   return 0;
@@ -369,6 +404,7 @@ static int fill_params(Params* p, const unsigned long long* peers, int nranks, i
   p->off_flags = off_flags; p->segs = (const Segment*)segs; p->chunk_seg = chunk_seg; p->cb = cb; p->ce = ce;
   p->rank = rank; p->nranks = nranks; p->kind = kind; p->seq = seq; p->slot = slot; p->counter = counter;
   p->seq_dev = g_epoch_ptr;
+  p->mc = nranks > 1 ? g_mc_base : nullptr;
   static const int dbg = getenv("CXN_XCHG_DBG") ? atoi(getenv("CXN_XCHG_DBG")) : 0;
   p->dbg = dbg;
   return 0;
@@ -560,6 +596,14 @@ bool memory_is_local(const void* p, size_t bytes) {
   return true;
 }
 }  // namespace cxn
+
+// record a range that maps (or multicasts to) another GPU's memory, however it was obtained (VMM imports, multicast
+// addresses of torch's symmetric memory): memory_is_local() answers 0 for anything that overlaps it
+CXN_API int cxn_note_peer_range(const void* p, unsigned long long bytes) {
+  if (p == nullptr || bytes == 0) return -1;
+  cxn::note_peer_range(p, (size_t)bytes);
+  return 0;
+}
 
 // 1 = the range is plain memory of the current device (eligible for the cluster-multicast routes), 0 = not
 CXN_API int cxn_memory_is_local(const void* p, unsigned long long bytes) { return cxn::memory_is_local(p, (size_t)bytes) ? 1 : 0; }

@@ -25,6 +25,7 @@
 // signal of every other rank (see parallel/tensor_parallel.py for the argument per buffer).
 // Every wait is bounded and traps on timeout.
 #include "common.cuh"
+#include <stdlib.h>
 #include <string.h>
 
 namespace cxn {
@@ -57,6 +58,8 @@ struct Params {
   char* dst;                       // local destination
   int pull_rows, pull_row_bytes;
   int rank, nranks, slot;
+  char* mc;                        // NVSwitch multicast address of the symmetric block, or null
+  int bcast;                       // push: every destination receives the same sub-block at the same offset
 };
 
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
@@ -72,6 +75,21 @@ __device__ __forceinline__ uint4 ld_peer_16(const void* p) {
   asm volatile("ld.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
                : "l"(p));
+  return v;
+}
+// NVLS (multicast address of the block): one store reaches every rank's block; one load returns the fp32-accumulated
+// sum of the same eight bf16 values of every rank's block.  Plain multimem instructions, not TMA.
+__device__ __forceinline__ void mc_st_16(void* p, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+               : "memory");
+}
+__device__ __forceinline__ uint4 mc_ld_reduce_bf16x8(const void* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
   return v;
 }
 __device__ __forceinline__ unsigned* flag_ptr(char* base, long long off_flags, int slot, int src) {
@@ -102,6 +120,23 @@ __device__ __forceinline__ void wait_all(const Params& p, unsigned seq) {
 __global__ void __launch_bounds__(kThreads) tp_push_kernel(const Params p) {
   unsigned* done = p.counters + 2 * p.slot;
   const unsigned seq = *reinterpret_cast<volatile unsigned*>(done + 1) + 1u;
+  if (p.mc != nullptr && p.bcast) {
+    // a gather: the same sub-block goes to the same place in every rank's block - one multicast store per 16 bytes
+    const PushDesc d = p.d[p.rank];
+    if (d.nrows > 0 && d.row_bytes > 0) {
+      const int vpr = d.row_bytes >> 4;
+      const long long total = (long long)d.nrows * vpr;
+      const char* s = p.src + d.src_off;
+      char* o = p.mc + d.dst_off;
+      for (long long v = blockIdx.x * (long long)kThreads + threadIdx.x; v < total; v += (long long)gridDim.x * kThreads) {
+        const int r = (int)(v / vpr);
+        const int c = (int)(v - (long long)r * vpr);
+        uint4 val = make_uint4(0u, 0u, 0u, 0u);
+        if (r < d.valid_rows) val = *reinterpret_cast<const uint4*>(s + (long long)r * p.src_ld + ((long long)c << 4));
+        mc_st_16(o + (long long)r * p.dst_ld + ((long long)c << 4), val);
+      }
+    }
+  } else
   for (int i = 0; i < p.nranks; ++i) {
     const int dst = (p.rank + i) % p.nranks;             // own copy first, peers staggered over the links
     const PushDesc d = p.d[dst];
@@ -159,6 +194,11 @@ __global__ void __launch_bounds__(kThreads) tp_reduce_pull_kernel(const Params p
     const int r = (int)(v / vpr);
     const int c = (int)(v - (long long)r * vpr);
     const long long off = p.part_off + p.pull_off + (long long)r * p.part_ld + ((long long)c << 4);
+    if (p.mc != nullptr) {
+      // the switch adds the ranks' partials (fp32 accumulation, bf16 result)
+      *reinterpret_cast<uint4*>(p.dst + (long long)r * p.dst_ld + ((long long)c << 4)) = mc_ld_reduce_bf16x8(p.mc + off);
+      continue;
+    }
     float a[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) a[j] = 0.f;
@@ -194,12 +234,22 @@ CXN_API int cxn_tp_flag_bytes() { return kSlots * kMaxRanks * 4; }
 CXN_API int cxn_tp_counter_bytes() { return kSlots * 2 * 4; }
 CXN_API int cxn_tp_max_slots() { return kSlots; }
 
+// Multicast address of the symmetric block (or null): gathers then use multimem.st, reductions multimem.ld_reduce.
+// CXN_TP_NVLS=0 keeps the unicast path.  One GPU per process.
+static char* g_tp_mc = nullptr;
+CXN_API int cxn_tp_set_multicast(void* mc_base) {
+  static const bool off = getenv("CXN_TP_NVLS") != nullptr && atoi(getenv("CXN_TP_NVLS")) == 0;
+  g_tp_mc = off ? nullptr : reinterpret_cast<char*>(mc_base);
+  return 0;
+}
+
 static int fill_common(Params* p, const unsigned long long* peers, int nranks, int rank, long long off_flags, int slot,
                        unsigned* counters) {
   if (nranks < 1 || nranks > kMaxRanks || rank < 0 || rank >= nranks || slot < 0 || slot >= kSlots || !counters) return -40;
   memset(p, 0, sizeof(*p));
   for (int i = 0; i < nranks; ++i) p->peers[i] = reinterpret_cast<char*>(peers[i]);
   p->off_flags = off_flags; p->counters = counters; p->rank = rank; p->nranks = nranks; p->slot = slot;
+  p->mc = nranks > 1 ? g_tp_mc : nullptr;
   return 0;
 }
 
@@ -223,6 +273,10 @@ CXN_API int cxn_tp_push(const unsigned long long* peers, int nranks, int rank, l
     work += q[2] * (q[4] >> 4);
   }
   p.src = (const char*)src; p.src_ld = src_ld; p.dst_ld = dst_ld;
+  p.bcast = 1;
+  for (int i = 1; i < nranks; ++i)
+    if (memcmp(&p.d[i], &p.d[0], sizeof(PushDesc)) != 0) p.bcast = 0;
+  if (p.bcast) work /= nranks;       // one multicast store instead of a store per rank
   long long need = (work + kThreads - 1) / kThreads;
   if (grid < 1) grid = 1;
   if (grid > num_sms()) grid = num_sms();

@@ -832,6 +832,8 @@ class NeuralNet:
             if t != tag:
                 continue
             if self.arena is not None and c.native:
+                if (layer_index, tag) not in self._seg_of:      # a share[tag] connection: the weights are the primary's
+                    layer_index = next(j for j, k in enumerate(self.connections) if k.layer is c.layer)
                 s = self._seg_of[(layer_index, tag)]
                 return c.layer.weight_from_internal(tag, self.arena.g_view(s)).reshape(w.shape).detach().clone()
             return g.detach().clone()

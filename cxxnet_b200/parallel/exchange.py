@@ -79,6 +79,10 @@ class GradExchange:
             raise ValueError("too many ranks for the fused exchange")
         self.block: SymmetricBlock = net.symm_block
         self.off = net.symm_offsets
+        # NVSwitch multicast address of the block (parallel/symm.py, kind "nvls"): the fused kernel then reduces with
+        # multimem.ld_reduce and publishes with multimem.st (process-wide setting: the newest exchange wins)
+        L.cxn_xchg_set_multicast.argtypes = [P]
+        L.cxn_xchg_set_multicast(self.block.multicast_ptr or None)
         self.counter = torch.zeros(4, dtype=torch.int32, device=self.device)
         self.counter_main = torch.zeros(4, dtype=torch.int32, device=self.device)
         a = self.arena

@@ -185,6 +185,8 @@ class TensorParallel:
         L.cxn_tp_reduce_pull.argtypes = [P, I, I, LL, I, P, LL, LL, LL, I, I, P, LL, I, P]
         L.cxn_tp_reduce_pull.restype = I
         self.block = block
+        L.cxn_tp_set_multicast.argtypes = [P]
+        L.cxn_tp_set_multicast(block.multicast_ptr or None)       # gathers / reductions through the switch when there is one
         self.off_flags, _ = block.carve(L.cxn_tp_flag_bytes())
         self.counters = torch.zeros(L.cxn_tp_counter_bytes() // 4, dtype=torch.int32, device=net.device)
         slot = 0

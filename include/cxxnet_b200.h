@@ -251,6 +251,10 @@ int cxn_symm_allgather(const unsigned long long* peers, int nranks, int rank, lo
  * captured CUDA graph advances the flag barriers on replay); NULL = off.  No reference counterpart. */
 int cxn_xchg_set_epoch_ptr(const void* dev_word);
 int cxn_xchg_flag_bytes(void);
+/* NVSwitch multicast address of the symmetric block (or NULL): with it the fused exchange reduces the gradients with
+ * multimem.ld_reduce (the sum is formed inside the switch) and publishes the weights with one multimem.st per 16 bytes
+ * instead of one load / store per rank.  One GPU per process.  No reference counterpart. */
+int cxn_xchg_set_multicast(void* mc_base);
 int cxn_xchg_max_ranks(void);
 int cxn_xchg_max_slots(void);
 /* Collectives of the column-sharded (model-parallel) fully connected layers (csrc/kernels/tp_collectives.cu): the
@@ -264,6 +268,7 @@ int cxn_xchg_max_slots(void);
  * `peers`: HOST array of block base addresses as mapped here; off_flags: cxn_tp_flag_bytes() zeroed bytes inside every
  * block; counters: cxn_tp_counter_bytes() zeroed LOCAL device bytes (the per-slot sequence numbers live there, so a
  * launch captured in a CUDA graph replays correctly); all offsets / pitches / row_bytes multiples of 16. */
+int cxn_tp_set_multicast(void* mc_base);   /* NVSwitch multicast address of the block (or NULL): multimem.st / ld_reduce */
 int cxn_tp_flag_bytes(void);
 int cxn_tp_counter_bytes(void);
 int cxn_tp_max_slots(void);
@@ -282,6 +287,9 @@ int cxn_ipc_free(unsigned long long ptr);
  * before taking a cluster-multicast route: a multicast tensor map must cover this GPU's memory alone; every
  * other operand runs on the non-cluster kernels.  No reference counterpart. */
 int cxn_memory_is_local(const void* p, unsigned long long bytes);
+/* Report a range that maps, or multicasts to, another GPU's memory (VMM imports, NVSwitch multicast addresses obtained
+ * outside cxn_ipc_open): cxn_memory_is_local answers 0 for everything that overlaps it.  No reference counterpart. */
+int cxn_note_peer_range(const void* p, unsigned long long bytes);
 
 /* step trace: stores the GPU's %globaltimer (ns) into buf[slot]; one thread, capturable.  No reference counterpart
  * (the reference has no profiling facility). */

@@ -350,7 +350,11 @@ layer[7->8] = fullc:out
   nhidden = 5
 layer[8->8] = softmax
 """
-    errs, ref, b2 = compare_backends(_conf(body, 9, "3,10,10"), make_batch((9, 3, 10, 10), nclass=5), return_trainers=True)
+    # (five bf16 layers deep on nine 10 x 10 images: rounding noise is several per cent of these small gradients; a
+    # missing accumulation over the two uses would be an error of ~50 %)
+    errs, ref, b2 = compare_backends(_conf(body, 9, "3,10,10"), make_batch((9, 3, 10, 10), nclass=5), tol_grad=0.12,
+                                     return_trainers=True)
+    assert errs["grad[2:wmat]"] == errs["grad[4:wmat]"]
     assert all(c.native for c in b2.net.connections), [c.native for c in b2.net.connections]
     # two updates through the public path: graphs stay possible (nothing forces the eager route)
     b2._graph_unsafe = None
