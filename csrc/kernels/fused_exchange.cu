@@ -416,7 +416,12 @@ static int fill_params(Params* p, const unsigned long long* peers, int nranks, i
 static int launch_fused(const Params& p, int nranks, int grid, cudaStream_t st) {
   if (grid < 1) grid = 1;
   if (grid > 2 * num_sms()) grid = 2 * num_sms();
-  if (nranks <= 2) fused_rs_update_ag_kernel<2, 4><<<grid, kThreads, 0, st>>>(p);
+  // with the multicast address one load returns the reduced gradient: no per-rank load buffers, so more chunks in flight
+  // per CTA (the switch round trip is several microseconds; bandwidth = bytes in flight / latency)
+  static const int mc_u = getenv("CXN_XCHG_MC_U") ? atoi(getenv("CXN_XCHG_MC_U")) : 1;   // (measured on 8 GPUs, fc6-sized bucket: 1 -> 411 us, 8 -> 456 us)
+  if (p.mc != nullptr && mc_u == 8) fused_rs_update_ag_kernel<1, 8><<<grid, kThreads, 0, st>>>(p);
+  else if (p.mc != nullptr && mc_u == 4) fused_rs_update_ag_kernel<1, 4><<<grid, kThreads, 0, st>>>(p);
+  else if (nranks <= 2) fused_rs_update_ag_kernel<2, 4><<<grid, kThreads, 0, st>>>(p);
   else if (nranks <= 4) fused_rs_update_ag_kernel<4, 2><<<grid, kThreads, 0, st>>>(p);
   else fused_rs_update_ag_kernel<8, 1><<<grid, kThreads, 0, st>>>(p);
   CXN_CHECK_LAUNCH();
