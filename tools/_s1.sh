@@ -1,13 +1,26 @@
 set -u
 OUT=$PWD/gpurun_out; mkdir -p $OUT
 python build.py > $OUT/build.log 2>&1 || { tail -20 $OUT/build.log; exit 1; }
-echo "== gpu tests"
-timeout 1500 python -m pytest tests -m gpu -q > $OUT/pytest_gpu.log 2>&1; echo "pytest exit $?"; grep -E "passed|failed|^FAILED|Error: " $OUT/pytest_gpu.log | head -20
-echo "== bench 1 GPU"
-timeout 300 python bench.py --steps 20 --warmup 5 > $OUT/b1.json 2>$OUT/b1.err; cat $OUT/b1.json | cut -c1-300
-timeout 300 python bench.py --steps 20 --warmup 5 --impl library > $OUT/b1_library.json 2>$OUT/b1_library.err; cat $OUT/b1_library.json | cut -c1-300
-echo "== config benches"
-timeout 300 python bench/config_bench.py --model lenet > $OUT/cfg_lenet_1.json 2>$OUT/cfg_lenet_1.err; cat $OUT/cfg_lenet_1.json | cut -c1-400
-timeout 300 python bench/config_bench.py --model bowl > $OUT/cfg_bowl_1.json 2>$OUT/cfg_bowl_1.err; cat $OUT/cfg_bowl_1.json | cut -c1-400
-echo "== memcheck (small shapes)"
-timeout 900 compute-sanitizer --tool memcheck --error-exitcode 7 python -m pytest tests/test_gpu_gemm.py tests/test_gpu_conv.py tests/test_gpu_exchange_single.py -q -x -k "basic or cta_pairs or odd_shapes or single_rank or 3x3_wide" > $OUT/sanitizer_memcheck.log 2>&1; echo "memcheck exit $?"; grep -E "ERROR SUMMARY|passed|failed|Invalid|error" $OUT/sanitizer_memcheck.log | head -10
+timeout 600 python -m pytest tests/test_gpu_exchange_single.py tests/test_zz_no_alloc.py -q 2>&1 | tail -3
+echo "== new barriers"; timeout 300 python bench/barrier_latency.py 2>&1 | tail -5
+echo "== round-1 tree (old barriers; fused exchange only)"; (cd build/r1 && timeout 300 python - <<'PY'
+import sys, os
+sys.path.insert(0, os.getcwd()); sys.path.insert(0, os.path.join(os.getcwd(), "tests"))
+import ctypes, torch
+from cxxnet_b200 import ops
+import test_zz_no_alloc as Z
+lib = ctypes.CDLL(Z.LIB)
+Pt, I, LL, U = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_uint
+lib.cxn_fused_rs_update_ag.argtypes = [Pt, I, I, LL, LL, LL, LL, LL, LL, Pt, Pt, LL, LL, I, U, I, Pt, I, Pt]
+blk = Z.Block(lib, [65536])
+counter = torch.zeros(4, dtype=torch.int32, device="cuda")
+st = torch.cuda.current_stream().cuda_stream
+def run(n, s0):
+    for i in range(n):
+        lib.cxn_fused_rs_update_ag(*blk.args(s0 + i + 1, 2), counter.data_ptr(), 16, st)
+run(10, 0); torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record(); run(200, 10); e1.record(); torch.cuda.synchronize()
+print("fused exchange, 64 K parameters (round-1 kernel): %.2f us per launch" % (e0.elapsed_time(e1) / 200 * 1e3))
+PY
+)
