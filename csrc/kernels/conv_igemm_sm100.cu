@@ -72,6 +72,11 @@ struct Params {
   // optional strided view for the im2col tensor map (elements; 0 = the dense NHWC tensor): channel
   // extent per position, row stride, image stride.  Cs stays the stride between positions.
   long long view_cdim, view_row, view_img;
+  // optional strided view of the OUTPUT (fprop only; 0 = rows are consecutive): GEMM row r = (image, j, i) of an
+  // o_h x o_w grid lands at element o_base + image * o_img + j * o_row + i * o_pix (+ group / column offsets).  Used by
+  // backward-data of strided convolutions: each stride phase is a stride-1 problem whose results interleave in dx.
+  int o_w, o_hw;
+  long long o_base, o_pix, o_row, o_img;
   long long* prof; // [grid][16] cycle counters of the warp roles (builds with -DCXN_IGEMM_PROF only)
   int dbg;         // timing experiments only (results are garbage): 2 skip the TMA loads, 4 skip the MMAs
 };
@@ -561,7 +566,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-        const long long off = (long long)g * p.strideD + row * p.ldd + n0;
+        long long pix_off = row * p.ldd;
+        if (!WGRAD && p.o_w) {
+          const long long img = row / p.o_hw;
+          const int rr = (int)(row - img * p.o_hw);
+          const int jj = rr / p.o_w;
+          pix_off = p.o_base + img * p.o_img + (long long)jj * p.o_row + (long long)(rr - jj * p.o_w) * p.o_pix;
+        }
+        const long long off = (long long)g * p.strideD + pix_off + n0;
         if (!WGRAD) {
           if (bias != nullptr) {
 #pragma unroll
@@ -1414,6 +1426,30 @@ __global__ void flip_weights_kernel(const bf16* __restrict__ w, bf16* __restrict
   }
 }
 
+// The sub-filter of one stride phase, flipped and channel-transposed (backward-data of a strided convolution):
+//   Wt[g][ic][ty][tx][oc] = W[g][oc][ph + s (KHa - 1 - ty)][pw + s (KWb - 1 - tx)][ic]        ty < KHa, tx < KWb
+// blockIdx.z enumerates (group, ty, tx); per tap a 32 x 32 transpose through shared memory as above.
+__global__ void flip_weights_phase_kernel(const bf16* __restrict__ w, bf16* __restrict__ wt, int ocg, int icg, int KW,
+                                          int s, int ph, int pw, int KHa, int KWb, int ld_in, int ld_out) {
+  __shared__ bf16 tile[32][33];
+  const int taps = KHa * KWb;
+  const int g = blockIdx.z / taps, t = blockIdx.z - g * taps;
+  const int ty = t / KWb, tx = t - ty * KWb;
+  const int kh = ph + s * (KHa - 1 - ty), kw = pw + s * (KWb - 1 - tx);
+  const int oc0 = blockIdx.y * 32, ic0 = blockIdx.x * 32;
+  const bf16* src = w + (long long)g * ocg * ld_in + (long long)(kh * KW + kw) * icg;
+  bf16* dst = wt + (long long)g * icg * ld_out + (long long)t * ocg;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int oc = oc0 + i, ic = ic0 + threadIdx.x;
+    tile[i][threadIdx.x] = (oc < ocg && ic < icg) ? src[(long long)oc * ld_in + ic] : __float2bfloat16(0.0f);
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int ic = ic0 + i, oc = oc0 + threadIdx.x;
+    if (ic < icg && oc < ocg) dst[(long long)ic * ld_out + oc] = tile[threadIdx.x][i];
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -1694,6 +1730,10 @@ using namespace cxn::igemm;
 //        gran 4: single group, Cg = Cs = 4 = RGB padded to 4)
 //   w    bf16 [G][Ng][ldw >= KH*KW*Cg] with the reduction ordered (kh, kw, c)
 //   y    NHWC bf16 [N*OH*OW][ldy], group g writes columns [g*Ng, (g+1)*Ng)
+// output view of the next conv_fprop_impl call of this thread (set by cxn_conv_dgrad_strided)
+struct OutView { int w, h; long long base, pix, row, img; };
+static thread_local OutView t_oview = {0, 0, 0, 0, 0, 0};
+
 static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
                            long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW,
                            void* y, long long ldy, const float* bias, int relu, const void* mask, long long view_cdim,
@@ -1706,6 +1746,11 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   p.gran = gran; p.Ng = Ng; p.D = y; p.ldd = ldy; p.strideD = Ng; p.bias = bias; p.relu = relu;
   p.mask = (const bf16*)mask;
   p.splits = 1; p.kb_per_split = 0;
+  const bool oview = t_oview.w > 0;
+  if (oview) {
+    if (t_oview.w != OW || t_oview.h != OH) return -19;
+    p.o_w = OW; p.o_hw = OH * OW; p.o_base = t_oview.base; p.o_pix = t_oview.pix; p.o_row = t_oview.row; p.o_img = t_oview.img;
+  }
   int rc = check_geom(p);
   if (rc) return rc;
   const long long rows = (long long)N * OH * OW;
@@ -1768,7 +1813,7 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   }
   const long long tiles_final = ceil_div_ll(rows, mh * BM) * ceil_div(Ng, p.bn) * G;
   const int grid_final = (int)(tiles_final < num_sms() ? tiles_final : num_sms());
-  bool atma = atma_ok(p);
+  bool atma = atma_ok(p) && !oview;        // (only the generic kernel knows the output view)
   if (g_tune_atma >= 0 && !p.view_cdim) atma = atma && g_tune_atma;
   if (p.view_cdim && !atma) return -17;    // a strided view only exists as a tensor map
   CUtensorMap tmp = tm;
@@ -1987,6 +2032,96 @@ CXN_API int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int i
   dim3 grid(ceil_div(icg, 32), ceil_div(ocg, 32), G * KH * KW), block(32, 8);
   flip_weights_kernel<<<grid, block, 0, st>>>((const bf16*)w, (bf16*)wt, ocg, icg, KH * KW, ld_in, ld_out);
   CXN_CHECK_LAUNCH();
+  return 0;
+}
+
+// K2 for strided convolutions, without an im2col buffer: backward-data as stride*stride implicit-GEMM problems.
+// Input positions with (ih + pad_y) % s == ph, (iw + pad_x) % s == pw only meet the filter taps kh = ph (mod s),
+// kw = pw (mod s), and over that sub-grid the layer is a STRIDE-1 correlation of dy with the flipped sub-filter - the
+// forward kernel, run once per phase on dy, writing through a strided view of dx.  No multiplication by an inserted
+// zero is ever made (the dilated-dy formulation does s*s times the work).  Reference: the col2im path of
+// src/layer/convolution_layer-inl.hpp:140-153.
+//   dy [N][OH][OW][lddy] (group g: channels [g*ocg, (g+1)*ocg)), w: the forward filter [G][ocg][KH][KW][icg] (ldw),
+//   dx [N][H][W][lddx], mask: optional tensor laid out like dx (outputs whose mask element is <= 0 become zero),
+//   scratch: bf16 room for the phase filters, cxn_conv_dgrad_strided_scratch() elements.
+// Returns -24 when a phase would need a negative padding (pad >= stride with short filters): use the explicit path.
+CXN_API long long cxn_conv_dgrad_strided_scratch(int G, int ocg, int icg, int KH, int KW, int stride) {
+  long long total = 0;
+  for (int ph = 0; ph < stride; ++ph)
+    for (int pw = 0; pw < stride; ++pw) {
+      const int KHa = ph < KH ? ceil_div(KH - ph, stride) : 0, KWb = pw < KW ? ceil_div(KW - pw, stride) : 0;
+      if (KHa * KWb) total += (long long)G * icg * (((long long)KHa * KWb * ocg + 7) / 8 * 8);
+    }
+  return total;
+}
+// 1 when every stride phase of this geometry has a non-negative padding (cxn_conv_dgrad_strided would not return -24)
+CXN_API int cxn_conv_dgrad_strided_ok(int KH, int KW, int stride, int pad_y, int pad_x) {
+  if (stride < 2) return 0;
+  for (int ph = 0; ph < stride; ++ph) {
+    const int KHa = ph < KH ? ceil_div(KH - ph, stride) : 0;
+    const int ih0 = ((ph - pad_y) % stride + stride) % stride;
+    if (KHa && KHa - 1 - (ih0 + pad_y - ph) / stride < 0) return 0;
+  }
+  for (int pw = 0; pw < stride; ++pw) {
+    const int KWb = pw < KW ? ceil_div(KW - pw, stride) : 0;
+    const int iw0 = ((pw - pad_x) % stride + stride) % stride;
+    if (KWb && KWb - 1 - (iw0 + pad_x - pw) / stride < 0) return 0;
+  }
+  return 1;
+}
+CXN_API int cxn_conv_dgrad_strided(const void* dy, int N, int OH, int OW, long long lddy, int ocg, int G, const void* w,
+                                   long long ldw, int icg, int KH, int KW, int stride, int pad_y, int pad_x, int H, int W,
+                                   void* dx, long long lddx, const void* mask, void* scratch, cudaStream_t st) {
+  if (stride < 2 || (ocg % 8) || (lddy % 8)) return -25;
+  bool any_empty = false;
+  for (int ph = 0; ph < stride; ++ph) {
+    const int KHa = ph < KH ? ceil_div(KH - ph, stride) : 0;
+    const int ih0 = ((ph - pad_y) % stride + stride) % stride;
+    if (KHa && KHa - 1 - (ih0 + pad_y - ph) / stride < 0) return -24;
+    if (!KHa) any_empty = true;
+  }
+  for (int pw = 0; pw < stride; ++pw) {
+    const int KWb = pw < KW ? ceil_div(KW - pw, stride) : 0;
+    const int iw0 = ((pw - pad_x) % stride + stride) % stride;
+    if (KWb && KWb - 1 - (iw0 + pad_x - pw) / stride < 0) return -24;
+    if (!KWb) any_empty = true;
+  }
+  if (any_empty) {   // stride larger than the filter: some input positions receive nothing
+    cudaError_t e = cudaMemsetAsync(dx, 0, (size_t)N * H * W * lddx * sizeof(bf16), st);
+    if (e != cudaSuccess) return (int)e;
+  }
+  bf16* wt = (bf16*)scratch;
+  for (int ph = 0; ph < stride; ++ph)
+    for (int pw = 0; pw < stride; ++pw) {
+      const int KHa = ph < KH ? ceil_div(KH - ph, stride) : 0, KWb = pw < KW ? ceil_div(KW - pw, stride) : 0;
+      if (KHa * KWb == 0) continue;
+      const int ih0 = ((ph - pad_y) % stride + stride) % stride, iw0 = ((pw - pad_x) % stride + stride) % stride;
+      const int ld_out = (KHa * KWb * ocg + 7) / 8 * 8;
+      bf16* wt_phase = wt;
+      wt += (long long)G * icg * ld_out;
+      if (ih0 >= H || iw0 >= W) continue;
+      const int IHp = ceil_div(H - ih0, stride), IWp = ceil_div(W - iw0, stride);
+      if ((long long)G * KHa * KWb > 65535) return -1;
+      // rows of the phase filter are padded to 8 elements; the padding must read as zero
+      if (ld_out != KHa * KWb * ocg) {
+        cudaError_t e = cudaMemsetAsync(wt_phase, 0, (size_t)G * icg * ld_out * sizeof(bf16), st);
+        if (e != cudaSuccess) return (int)e;
+      }
+      dim3 grid(ceil_div(icg, 32), ceil_div(ocg, 32), G * KHa * KWb), block(32, 8);
+      flip_weights_phase_kernel<<<grid, block, 0, st>>>((const bf16*)w, wt_phase, ocg, icg, KW, stride, ph, pw, KHa, KWb,
+                                                        (int)ldw, ld_out);
+      CXN_CHECK_LAUNCH();
+      const int pad_py = KHa - 1 - (ih0 + pad_y - ph) / stride, pad_px = KWb - 1 - (iw0 + pad_x - pw) / stride;
+      t_oview.w = IWp; t_oview.h = IHp;
+      t_oview.base = ((long long)ih0 * W + iw0) * lddx;
+      t_oview.pix = (long long)stride * lddx;
+      t_oview.row = (long long)stride * W * lddx;
+      t_oview.img = (long long)H * W * lddx;
+      const int rc = conv_fprop_impl(dy, N, OH, OW, (int)lddy, ocg, G, 8, wt_phase, ld_out, icg, KHa, KWb, 1, pad_py, pad_px, IHp,
+                                     IWp, dx, lddx, nullptr, 0, mask, 0, 0, 0, st);
+      t_oview.w = 0;
+      if (rc) return rc;
+    }
   return 0;
 }
 

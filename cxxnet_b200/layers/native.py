@@ -128,6 +128,8 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         self.igemm_fwd = False
         self.igemm_dgrad = False
         self.bias_grad_fused = False   # the pooling layer behind this one accumulates the bias gradient (_NativePool.bias_of)
+        self.dgrad_phases = False      # strided backward-data as stride*stride implicit-GEMM problems (cxn_conv_dgrad_strided)
+        self.phase_scratch = None
 
     def b200_supported(self):
         p = self.param
@@ -225,7 +227,15 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         p = self.param
         g, icg, ocg, kg, kpad = self._geom()
         y = self.nodes_out[0]
-        if not self.igemm_fwd or not self.igemm_dgrad:
+        L = ops.lib()
+        if (self.igemm_fwd and not self.igemm_dgrad and not self.cin_pad and p.stride > 1 and ocg % 8 == 0 and icg % 8 == 0
+                and y.grad.ld % 8 == 0 and os.environ.get("CXN_CONV_DGRAD_PHASES", "1") != "0"
+                and L.cxn_conv_dgrad_strided_ok(p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x) == 1):
+            # strided layer: backward-data by stride phases, no patch buffer
+            self.dgrad_phases = True
+            n = int(L.cxn_conv_dgrad_strided_scratch(g, ocg, icg, p.kernel_height, p.kernel_width, p.stride))
+            self.phase_scratch = torch.zeros((max(n, 8),), dtype=torch.bfloat16, device=ex.device)
+        if (not self.igemm_fwd or not self.igemm_dgrad) and not (self.dgrad_phases and self.igemm_fwd):
             max_rows = ex.max_batch * y.shape[2] * y.shape[3]
             self.col = torch.empty((g * max_rows * kpad,), dtype=torch.bfloat16, device=ex.device)
         if self.igemm_dgrad:
@@ -313,9 +323,12 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
                                               x.grad.ptr, x.grad.ld, x.act.ptr if self.mask_relu_in else None,
                                               ops.stream()), "conv_dgrad")
             return
-        if self.igemm_fwd:
-            # strided backward-data: explicit dcol = gy . W, then scatter
-            pass
+        if self.dgrad_phases:
+            ops.check(L.cxn_conv_dgrad_strided(gy.ptr, b, y.shape[2], y.shape[3], gy.ld, ocg, g, W.shadow.data_ptr(), kpad, icg,
+                                               p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x, h, w, x.grad.ptr,
+                                               x.grad.ld, None, self.phase_scratch.data_ptr(), ops.stream()), "conv_dgrad_strided")
+            return
+        # strided backward-data the explicit way: dcol = gy . W, then scatter
         ops.gemm(gy.ptr, gy.ld, ocg, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 1, self.col.data_ptr(), kpad,
                  rows * kpad, None, 0, rows, kg, ocg, batch=g, flags=ops.GEMM_OUT_BF16)
         # pair mode: (kh, kw2, 8) columns are (kh, 2*kw2, 4) in the pixel domain of the pitched image

@@ -51,6 +51,18 @@ int cxn_gemm_workspace_lane(int lane);
 int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* w,
                    long long ldw, int Ng, int KH, int KW, int stride, int pad_y, int pad_x, int OH, int OW, void* y,
                    long long ldy, const float* bias, int relu, cudaStream_t stream);
+/* K2 for strided layers: backward-data as stride * stride implicit-GEMM problems, one per stride phase - the positions
+ * (ih + pad) % s == ph only meet the taps kh = ph (mod s), and over that sub-grid the layer is a stride-1 correlation
+ * of dy with the flipped sub-filter, written through a strided view of dx; no im2col buffer, no multiplication by an
+ * inserted zero.  `w` is the forward filter [G][ocg][KH][KW][icg] (row pitch ldw), `mask` an optional tensor laid out
+ * like dx (results become zero where it is <= 0), `scratch` bf16 room of cxn_conv_dgrad_strided_scratch() elements.
+ * -24: a phase would need negative padding (cxn_conv_dgrad_strided_ok answers 0) - use the explicit path.
+ * Reference: src/layer/convolution_layer-inl.hpp:140-153. */
+long long cxn_conv_dgrad_strided_scratch(int G, int ocg, int icg, int KH, int KW, int stride);
+int cxn_conv_dgrad_strided_ok(int KH, int KW, int stride, int pad_y, int pad_x);
+int cxn_conv_dgrad_strided(const void* dy, int N, int OH, int OW, long long lddy, int ocg, int G, const void* w,
+                           long long ldw, int icg, int KH, int KW, int stride, int pad_y, int pad_x, int H, int W, void* dx,
+                           long long lddx, const void* mask, void* scratch, cudaStream_t stream);
 /* K3: implicit-GEMM weight gradient, split-K over pixels, fp32 atomics into dw.
  * Reference: src/layer/convolution_layer-inl.hpp:121-138. */
 int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,

@@ -180,3 +180,41 @@ def test_conv_cta_pairs_split_the_filter_tile():
         _case(64, 64, 32, 32, 64, 1, 3, 3, 1, 1)                 # 256 pair tiles on 74 pairs
     finally:
         L.cxn_conv_tune(10, 0)
+
+
+@pytest.mark.parametrize("C,OC,G,H,W,k,s,pad", [(16, 32, 1, 13, 13, 3, 2, 1), (32, 64, 2, 16, 14, 5, 2, 2), (8, 16, 1, 9, 9, 2, 2, 0),
+                                                (64, 64, 1, 12, 12, 4, 2, 1), (16, 16, 1, 11, 10, 2, 3, 0),
+                                                (24, 48, 1, 23, 23, 7, 4, 3), (64, 128, 1, 28, 28, 3, 2, 0)])
+def test_conv_strided_backward_data_by_stride_phases(C, OC, G, H, W, k, s, pad):
+    """cxn_conv_dgrad_strided: backward-data of a strided convolution as stride x stride stride-1 implicit-GEMM problems
+    written through a strided view of dx (no patch buffer, no inserted zeros), against conv2d_input in fp64.  Odd
+    extents, groups, stride larger than the filter (positions that receive nothing), padding, a ReLU mask."""
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    torch.manual_seed(C * 7 + k * 3 + s)
+    N = 3
+    icg, ocg = C // G, OC // G
+    OH, OW = (H + 2 * pad - k) // s + 1, (W + 2 * pad - k) // s + 1
+    w = _bf(torch.randn(OC, icg, k, k, device="cuda") * (1.0 / (icg * k * k) ** 0.5))
+    dy = _bf(torch.randn(N, OH, OW, OC, device="cuda"))
+    kg = k * k * icg
+    kpad = ops.round_up(kg, 8)
+    wsh = torch.zeros(G * ocg, kpad, dtype=torch.bfloat16, device="cuda")
+    wsh[:, :kg] = w.view(G, ocg, icg, k, k).permute(0, 1, 3, 4, 2).reshape(G * ocg, kg)
+    assert L.cxn_conv_dgrad_strided_ok(k, k, s, pad, pad) == 1
+    scratch = torch.zeros(int(L.cxn_conv_dgrad_strided_scratch(G, ocg, icg, k, k, s)) + 8, dtype=torch.bfloat16, device="cuda")
+    dxr = torch.nn.grad.conv2d_input((N, C, H, W), w.double(), dy.double().permute(0, 3, 1, 2), stride=s, padding=pad,
+                                     groups=G).float()
+    for use_mask in (False, True):
+        dx = torch.full((N * H * W, C), 3.0, dtype=torch.bfloat16, device="cuda")     # stale values must all be overwritten
+        mask = _bf(torch.randn(N * H * W, C, device="cuda")) if use_mask else None
+        ops.check(L.cxn_conv_dgrad_strided(dy.data_ptr(), N, OH, OW, OC, ocg, G, wsh.data_ptr(), kpad, icg, k, k, s, pad, pad,
+                                           H, W, dx.data_ptr(), C, mask.data_ptr() if use_mask else None,
+                                           scratch.data_ptr(), ops.stream()), "dgrad_strided")
+        torch.cuda.synchronize()
+        want = dxr
+        if use_mask:
+            want = dxr * (mask.float().view(N, H, W, C).permute(0, 3, 1, 2) > 0)
+        got = dx.float().view(N, H, W, C).permute(0, 3, 1, 2)
+        err = float((got - want).abs().max())
+        assert err <= TOL_BF16_OUT * max(1.0, float(dxr.abs().max())), "strided dgrad err %g (mask %s)" % (err, use_mask)

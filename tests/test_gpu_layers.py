@@ -359,3 +359,33 @@ layer[8->8] = softmax
     # two updates through the public path: graphs stay possible (nothing forces the eager route)
     b2._graph_unsafe = None
     assert b2._graph_applicable(make_batch((9, 3, 10, 10), nclass=5))
+
+
+def test_inner_strided_convolution_backpropagates_by_stride_phases():
+    """a strided convolution that is not the first layer: its backward-data runs as stride-phase implicit GEMMs
+    (ConvolutionLayer.dgrad_phases), no patch buffer is allocated, gradients match the reference backend"""
+    body = """
+layer[+1] = conv:stem
+  kernel_size = 3
+  pad = 1
+  nchannel = 16
+layer[+1] = relu
+layer[+1] = conv:down
+  kernel_size = 3
+  pad = 1
+  stride = 2
+  nchannel = 32
+layer[+1] = relu
+layer[+1] = conv:down2
+  kernel_size = 2
+  stride = 2
+  nchannel = 32
+layer[+1] = flatten
+layer[+1] = fullc:out
+  nhidden = 6
+layer[+0] = softmax
+"""
+    errs, ref, b2 = compare_backends(_conf(body, 10, "3,17,17"), make_batch((10, 3, 17, 17), nclass=6), tol_grad=0.08,
+                                     return_trainers=True)
+    down = [c.layer for c in b2.net.connections if c.layer.type_name == "conv"][1:]
+    assert all(l.dgrad_phases and l.col is None for l in down)
