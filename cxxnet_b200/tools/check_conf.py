@@ -17,7 +17,7 @@ from ..config import parse_cli_overrides, parse_config_file
 
 TASK = """task dev model_in model_dir continue start_counter num_round max_round save_model print_step silent test_io
 extract_node_name output_format net_type reset_net_type data eval pred iter""".split()
-TRAINER = """batch_size update_period eval_train seed param_server metric backend cuda_graph test_on_server layer_timing
+TRAINER = """batch_size update_period eval_train seed param_server metric backend cuda_graph test_on_server layer_timing step_trace
 input_shape updater sync netconfig extra_data_num label_vec extra_data_shape check_nan
 pull_at_backprop bigarray_bound update_on_server init_on_worker force_contiguous fullc_gather fullc_shard""".split()
 LAYER = """init_sigma init_uniform init_bias init_sparse random_type nhidden nchannel ngroup kernel_size kernel_height
@@ -31,7 +31,7 @@ image_bin image_conf_prefix image_conf_ids dist_num_worker dist_worker_rank labe
 source_shape num_inst num_class value_scale
 rand_crop rand_mirror mirror crop_x_start crop_y_start divideby scale image_mean mean_value max_random_contrast
 max_random_illumination max_rotate_angle max_shear_ratio max_aspect_ratio min_crop_size max_crop_size min_random_scale
-max_random_scale min_img_size max_img_size fill_value rotate rotate_list
+max_random_scale min_img_size max_img_size fill_value rotate rotate_list warp_interp
 round_batch test_skipread input_dtype native_pipeline decode_threads slice_world slice_rank buffer_size max_nbatch
 filename""".split()
 KNOWN = set(TASK + TRAINER + LAYER + UPDATER + ITER)
