@@ -1730,6 +1730,9 @@ using namespace cxn::igemm;
 //        gran 4: single group, Cg = Cs = 4 = RGB padded to 4)
 //   w    bf16 [G][Ng][ldw >= KH*KW*Cg] with the reduction ordered (kh, kw, c)
 //   y    NHWC bf16 [N*OH*OW][ldy], group g writes columns [g*Ng, (g+1)*Ng)
+// CTA cap of this thread's weight-gradient launches (cxn_conv_wgrad_grid_cap); 0 = the whole GPU
+static thread_local int t_wgrad_cap = 0;
+
 // output view of the next conv_fprop_impl call of this thread (set by cxn_conv_dgrad_strided)
 struct OutView { int w, h; long long base, pix, row, img; };
 static thread_local OutView t_oview = {0, 0, 0, 0, 0, 0};
@@ -1965,7 +1968,10 @@ static int conv_wgrad_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   rc = encode3d(&tm, dy, (uint64_t)Ng, (uint64_t)rows, (uint64_t)G, (uint64_t)lddy, (uint64_t)Ng, 64, BK);
   if (rc) return rc;
   const long long tiles = base_tiles * p.splits;
-  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  // (t_wgrad_cap: the caller runs this launch beside another kernel - a sub-wave backward-data problem on another
+  // stream - and leaves that kernel its SMs: both are persistent with one CTA per SM)
+  const int sms_here = (t_wgrad_cap > 0 && t_wgrad_cap < num_sms()) ? t_wgrad_cap : num_sms();
+  const int grid = (int)(tiles < sms_here ? tiles : sms_here);
   p.stages = g_tune_stages ? g_tune_stages : 4;
   p.ring_bytes = p.stages * (BM + 256) * BK * 2;
   p.dbg = g_tune_dbg;
@@ -2123,6 +2129,16 @@ CXN_API int cxn_conv_dgrad_strided(const void* dy, int N, int OH, int OW, long l
       if (rc) return rc;
     }
   return 0;
+}
+
+// Limit the grid of this thread's following weight-gradient launches to `ctas` CTAs (0 = no limit) and return the
+// previous value.  The kernels here are persistent with one CTA per SM; a weight gradient launched beside a
+// backward-data problem that fills only part of the GPU (small per-GPU batches) takes the remaining SMs, and the two
+// run side by side instead of one after the other.
+CXN_API int cxn_conv_wgrad_grid_cap(int ctas) {
+  const int prev = t_wgrad_cap;
+  t_wgrad_cap = ctas < 0 ? 0 : ctas;
+  return prev;
 }
 
 CXN_API int cxn_conv_wgrad(const void* src, int N, int H, int W, int Cs, int Cg, int G, int gran, const void* dy,

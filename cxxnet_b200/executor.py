@@ -68,6 +68,7 @@ class NeuralNet:
         self.exchange = None
         self.tp = None           # parallel.tensor_parallel.TensorParallel when fully connected layers are column-sharded
         self._shared_ids = set() # ids of layer objects used by several connections (share[tag])
+        self.wgrad_stream = None
         # step trace (`step_trace = 1` / CXN_STEP_TRACE=1): device timestamps between the layers of a step, also
         # inside a captured graph; read with trace_report()
         self.trace_buf = None
@@ -393,6 +394,13 @@ class NeuralNet:
         self.hyper_prepared = False
         self.hyper_slot = 0
         self.copy_stream = torch.cuda.Stream(device=self.device)
+        # side stream for weight gradients that run beside a sub-wave backward-data kernel (layers/native.py)
+        import os
+        # (a captured step with more than one stream launches every node a little slower - measured on one GPU at batch
+        # 32: the layers gain 10 us, the step loses 17 - so by default only where the step has side streams anyway)
+        want = os.environ.get("CXN_OVERLAP_WGRAD", "auto")
+        on = want == "1" or (want == "auto" and self.world_size > 1 and self.exchange_kind == "nvlink")
+        self.wgrad_stream = torch.cuda.Stream(device=self.device) if on else None
         self.stage_free = [torch.cuda.Event(), torch.cuda.Event()]
         self.stage_ready = [torch.cuda.Event(), torch.cuda.Event()]
         self.stage_idx = 0

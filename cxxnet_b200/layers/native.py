@@ -238,6 +238,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         if (not self.igemm_fwd or not self.igemm_dgrad) and not (self.dgrad_phases and self.igemm_fwd):
             max_rows = ex.max_batch * y.shape[2] * y.shape[3]
             self.col = torch.empty((g * max_rows * kpad,), dtype=torch.bfloat16, device=ex.device)
+        self.ev_dy, self.ev_wg = torch.cuda.Event(), torch.cuda.Event()
         if self.igemm_dgrad:
             self.wflip_ld = ops.round_up(p.kernel_height * p.kernel_width * ocg, 8)
             self.wflip = torch.zeros((g * icg * self.wflip_ld,), dtype=torch.bfloat16, device=ex.device)
@@ -277,7 +278,8 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         ops.gemm(self.col.data_ptr(), kpad, rows * kpad, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 0,
                  y.act.ptr, y.act.ld, ocg, bias, ocg, rows, ocg, kg, batch=g, flags=flags)
 
-    def b200_backprop(self, ex, prop_grad):
+    def _weight_gradient(self, ex):
+        """accumulates into the arena gradient, which the updater leaves zeroed"""
         p = self.param
         x, y = self.nodes_in[0], self.nodes_out[0]
         g, icg, ocg, kg, kpad = self._geom()
@@ -286,10 +288,6 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         L = ops.lib()
         W = self.bind["wmat"]
         b, c, h, w = x.shape
-        if p.no_bias == 0 and not self.bias_grad_fused:
-            ops.check(L.cxn_colsum_bf16(gy.ptr, rows, p.num_channel, gy.ld, self.bind["bias"].g.data_ptr(),
-                                        1 if ex.accumulate_grads else 0, ops.stream()), "colsum")
-        # weight gradient (accumulates into the arena gradient, which the updater leaves zeroed)
         if self.span:
             wp = x.wpitch
             ops.check(L.cxn_conv_wgrad_view(x.act.ptr, b, h, y.shape[3], p.stride * 4, 64, 1, gy.ptr, gy.ld, ocg,
@@ -308,10 +306,51 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             kb = (rows + 63) // 64
             tiles = ((ocg + 127) // 128) * ((kg + 127) // 128) * g
             splits = max(1, min(kb // 4 if kb >= 8 else 1, (2 * ex.num_sms + tiles - 1) // tiles))
-            if prop_grad and not self.igemm_dgrad:
-                pass  # col still holds the forward patches
+            # (col still holds the forward patches)
             ops.gemm(gy.ptr, gy.ld, ocg, 1, self.col.data_ptr(), kpad, rows * kpad, 1, W.g.data_ptr(), kg, ocg * kg,
                      None, 0, ocg, kg, rows, batch=g, splits=splits, flags=ops.GEMM_ATOMIC)
+
+    def _dgrad_tiles(self, x) -> int:
+        """CTAs the stride-1 backward-data launch occupies (one 128-row tile each; the kernels are persistent, one CTA per SM)"""
+        p = self.param
+        b, c, h, w = x.shape
+        icg = p.num_input_channel // p.num_group
+        bnmax = 256 if icg > 128 else 128
+        return ((b * h * w + 127) // 128) * ((icg + bnmax - 1) // bnmax) * p.num_group
+
+    def b200_backprop(self, ex, prop_grad):
+        p = self.param
+        x, y = self.nodes_in[0], self.nodes_out[0]
+        g, icg, ocg, kg, kpad = self._geom()
+        rows = _rows(y)
+        gy = y.grad
+        L = ops.lib()
+        W = self.bind["wmat"]
+        b, c, h, w = x.shape
+        if p.no_bias == 0 and not self.bias_grad_fused:
+            ops.check(L.cxn_colsum_bf16(gy.ptr, rows, p.num_channel, gy.ld, self.bind["bias"].g.data_ptr(),
+                                        1 if ex.accumulate_grads else 0, ops.stream()), "colsum")
+        # Weight gradient.  When the backward-data problem of this layer fills only part of the GPU (small per-GPU
+        # batches: conv3 of AlexNet at 32 images is 43 tiles on 148 SMs) the two independent kernels run SIDE BY SIDE:
+        # the weight gradient goes to a side stream with its grid capped to the SMs backward-data leaves free.
+        side = None
+        if (prop_grad and self.igemm_dgrad and self.igemm_fwd and not self.span and ex.wgrad_stream is not None):
+            tiles = self._dgrad_tiles(x)
+            if tiles * 4 <= ex.num_sms * 3:
+                side = ex.num_sms - tiles
+        if side is not None:
+            main = torch.cuda.current_stream(ex.device)
+            self.ev_dy.record(main)
+            ex.wgrad_stream.wait_event(self.ev_dy)
+            with torch.cuda.stream(ex.wgrad_stream):
+                prev = L.cxn_conv_wgrad_grid_cap(side)
+                try:
+                    self._weight_gradient(ex)
+                finally:
+                    L.cxn_conv_wgrad_grid_cap(prev)
+                self.ev_wg.record(ex.wgrad_stream)
+        else:
+            self._weight_gradient(ex)
         if not prop_grad:
             return
         if self.igemm_dgrad:
@@ -322,6 +361,8 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
                                               self.wflip_ld, icg, kh, kw, 1, kh - 1 - p.pad_y, kw - 1 - p.pad_x, h, w,
                                               x.grad.ptr, x.grad.ld, x.act.ptr if self.mask_relu_in else None,
                                               ops.stream()), "conv_dgrad")
+            if side is not None:
+                torch.cuda.current_stream(ex.device).wait_event(self.ev_wg)      # join: the layer is done when both are
             return
         if self.dgrad_phases:
             ops.check(L.cxn_conv_dgrad_strided(gy.ptr, b, y.shape[2], y.shape[3], gy.ld, ocg, g, W.shadow.data_ptr(), kpad, icg,

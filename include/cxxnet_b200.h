@@ -58,6 +58,10 @@ int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg, int G, 
  * like dx (results become zero where it is <= 0), `scratch` bf16 room of cxn_conv_dgrad_strided_scratch() elements.
  * -24: a phase would need negative padding (cxn_conv_dgrad_strided_ok answers 0) - use the explicit path.
  * Reference: src/layer/convolution_layer-inl.hpp:140-153. */
+/* Limit the grid of the calling thread's following weight-gradient launches to `ctas` CTAs (0 = the whole GPU);
+ * returns the previous limit.  For running a weight gradient on one stream beside a backward-data problem that fills
+ * only part of the GPU on another (both kernels are persistent, one CTA per SM).  No reference counterpart. */
+int cxn_conv_wgrad_grid_cap(int ctas);
 long long cxn_conv_dgrad_strided_scratch(int G, int ocg, int icg, int KH, int KW, int stride);
 int cxn_conv_dgrad_strided_ok(int KH, int KW, int stride, int pad_y, int pad_x);
 int cxn_conv_dgrad_strided(const void* dy, int N, int OH, int OW, long long lddy, int ocg, int G, const void* w,

@@ -8,12 +8,10 @@ run() { # name extra...
 import json
 try:
     d=json.loads([l for l in open("$OUT/bench_${N}_$name.json") if l.startswith('{')][-1])
-    print("N=$N $name", round(d['value']), 'img/s', round(d['ms_per_step'],4), 'ms', 'e2e', round(d.get('e2e',{}).get('value',0)), d.get('symmetric_memory'), d.get('replica_max_diff'), d.get('verify'))
+    print("N=$N $name", round(d['value']), 'img/s', round(d['ms_per_step'],4), 'ms', 'e2e', round(d.get('e2e',{}).get('value',0)), d.get('symmetric_memory'), d.get('replica_max_diff'))
 except Exception as e:
     print("$name failed", e)
 PY
 }
-CXN_SYMM=ipc run ipc --no-verify
-run nvls
-CXN_XCHG_NVLS=0 run nvls_tp_only --no-verify
-CXN_TP_NVLS=0 run nvls_xchg_only --no-verify
+CXN_OVERLAP_WGRAD=0 run seq --no-verify
+run overlap --no-verify
