@@ -36,6 +36,22 @@ enum : int {
   kFlagOutBf16 = 2,   // D is bf16 (else fp32)
   kFlagAtomic = 4,    // fp32 D += partial via red.global.add (split-K or accumulate)
   kFlagBeta1 = 8,     // fp32 D = D + result (non atomic read-modify-write)
+  kFlagUpdate = 16,   // the result is a weight gradient that is consumed on the spot: the epilogue applies the updater
+                      // to the fp32 master / momentum at D's coordinates and refreshes the bf16 copy; D is not written
+};
+
+// Operands of the fused updater epilogue (kFlagUpdate).  w / m / m2 are addressed like D (row * ldd + column);
+// hyper points at {lr, wd, momentum, clip, adam_lr_t, beta1, beta2} of the layer's entry in the per-step device
+// table (loss_update.cu Segment, refreshed before the backward pass) - read at run time, so a captured step follows
+// the schedules.  kind: 0 sgd, 1 nag, 2 adam, the arithmetic of update_kernel.
+struct UpdArgs {
+  float* w;
+  float* m;
+  float* m2;
+  bf16* shadow;
+  long long shadow_ld;
+  const float* hyper;
+  int kind;
 };
 
 struct Params {
@@ -46,7 +62,29 @@ struct Params {
   const float* bias;
   long long strideBias;
   int flags;
+  UpdArgs u;
 };
+
+struct UpdHyper {
+  float lr, wd, momentum, clip, adam_lr_t, beta1, beta2;
+};
+
+__device__ __forceinline__ void update_one(float& w, float& m, float& m2, float g, const UpdHyper& h, int kind) {
+  if (kind == 0) {
+    if (h.clip != 0.0f) g = (g != g) ? 0.0f : fminf(fmaxf(g, -h.clip), h.clip);
+    m = h.momentum * m - h.lr * (g + h.wd * w);
+    w += m;
+  } else if (kind == 1) {
+    const float old = m;
+    m = h.momentum * old - h.lr * (g + h.wd * w);
+    w += (1.0f + h.momentum) * m - h.momentum * old;
+  } else {
+    if (h.wd > 0.0f) g -= h.wd * w;
+    m += h.beta1 * (g - m);
+    m2 += h.beta2 * (g * g - m2);
+    w -= h.adam_lr_t * (m / (sqrtf(m2) + 1e-8f));
+  }
+}
 
 template <int BN>
 struct Cfg {
@@ -67,8 +105,92 @@ using namespace cxn::tc;
 // bias / ReLU / conversion and the store, reduction or read-modify-write into D.  `warp_stage` is this warp's
 // 32 x 32 float staging area (fp32 results pass through a shared-memory transpose so that every store instruction
 // covers complete 128-byte row segments).
+template <bool UPD = false>
 __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&v)[32], int row0, int lane, int n0,
                                                bool has_work, const float* bias, int z, float* warp_stage) {
+  if constexpr (UPD) {
+    // fused updater: the accumulator IS the weight gradient of rows [row0, row0 + 32) x columns [n0, n0 + 32)
+    UpdHyper h;
+    h.lr = __ldg(p.u.hyper); h.wd = __ldg(p.u.hyper + 1); h.momentum = __ldg(p.u.hyper + 2);
+    h.clip = __ldg(p.u.hyper + 3); h.adam_lr_t = __ldg(p.u.hyper + 4); h.beta1 = __ldg(p.u.hyper + 5);
+    h.beta2 = __ldg(p.u.hyper + 6);
+    const int kind = p.u.kind;
+    if (n0 + 32 <= p.N && (p.ldd & 3) == 0 && (p.u.shadow_ld & 3) == 0) {
+      float* sm = warp_stage;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        float4 o4;
+        o4.x = has_work ? __uint_as_float(v[4 * q]) : 0.0f;
+        o4.y = has_work ? __uint_as_float(v[4 * q + 1]) : 0.0f;
+        o4.z = has_work ? __uint_as_float(v[4 * q + 2]) : 0.0f;
+        o4.w = has_work ? __uint_as_float(v[4 * q + 3]) : 0.0f;
+        *reinterpret_cast<float4*>(sm + lane * 32 + 4 * (q ^ (lane & 7))) = o4;
+      }
+      __syncwarp();
+      const int rsub = lane >> 3, cq = (lane & 7) * 4;
+      const long long col = n0 + cq;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        // all loads of four row segments first (w, m: 8 x 16 bytes in flight per thread), then the arithmetic
+        float4 wv[4], mv[4], m2v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = (half * 4 + i) * 4 + rsub;
+          wv[i] = mv[i] = m2v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (row0 + r < p.M) {
+            const long long off = (long long)(row0 + r) * p.ldd + col;
+            wv[i] = *reinterpret_cast<const float4*>(p.u.w + off);
+            mv[i] = *reinterpret_cast<const float4*>(p.u.m + off);
+            if (kind == 2) m2v[i] = *reinterpret_cast<const float4*>(p.u.m2 + off);
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = (half * 4 + i) * 4 + rsub;
+          if (row0 + r < p.M) {
+            const float4 g4 = *reinterpret_cast<const float4*>(sm + r * 32 + 4 * ((lane & 7) ^ (r & 7)));
+            update_one(wv[i].x, mv[i].x, m2v[i].x, g4.x, h, kind);
+            update_one(wv[i].y, mv[i].y, m2v[i].y, g4.y, h, kind);
+            update_one(wv[i].z, mv[i].z, m2v[i].z, g4.z, h, kind);
+            update_one(wv[i].w, mv[i].w, m2v[i].w, g4.w, h, kind);
+            const long long off = (long long)(row0 + r) * p.ldd + col;
+            *reinterpret_cast<float4*>(p.u.w + off) = wv[i];
+            *reinterpret_cast<float4*>(p.u.m + off) = mv[i];
+            if (kind == 2) *reinterpret_cast<float4*>(p.u.m2 + off) = m2v[i];
+            if (p.u.shadow != nullptr) {
+              const __nv_bfloat162 h0 = __floats2bfloat162_rn(wv[i].x, wv[i].y);
+              const __nv_bfloat162 h1 = __floats2bfloat162_rn(wv[i].z, wv[i].w);
+              uint2 u2;
+              u2.x = *reinterpret_cast<const uint32_t*>(&h0);
+              u2.y = *reinterpret_cast<const uint32_t*>(&h1);
+              *reinterpret_cast<uint2*>(p.u.shadow + (long long)(row0 + r) * p.u.shadow_ld + col) = u2;
+            }
+          }
+        }
+      }
+      __syncwarp();
+      return;
+    }
+    // ragged edge: one row per lane, element by element
+    const int row = row0 + lane;
+    if (row >= p.M) return;
+#pragma unroll 1
+    for (int j = 0; j < 32; ++j) {
+      if (n0 + j >= p.N) break;
+      const long long off = (long long)row * p.ldd + n0 + j;
+      float w = p.u.w[off], m = p.u.m[off], m2 = (kind == 2) ? p.u.m2[off] : 0.0f;
+      float g = 0.0f;
+#pragma unroll
+      for (int jj = 0; jj < 32; ++jj)
+        if (jj == j) g = has_work ? __uint_as_float(v[jj]) : 0.0f;
+      update_one(w, m, m2, g, h, kind);
+      p.u.w[off] = w;
+      p.u.m[off] = m;
+      if (kind == 2) p.u.m2[off] = m2;
+      if (p.u.shadow != nullptr) p.u.shadow[(long long)row * p.u.shadow_ld + n0 + j] = __float2bfloat16(w);
+    }
+    return;
+  }
   const bool relu = p.flags & kFlagRelu;
   const bool out_bf16 = p.flags & kFlagOutBf16;
   const bool atomic = p.flags & kFlagAtomic;
@@ -179,7 +301,7 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&v)[32
   }
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool UPD = false>
 __global__ void __launch_bounds__(kThreadsWide, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
   using C = Cfg<BN>;
@@ -342,7 +464,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
         tmem_ld32(taddr, v);
         tmem_ld_wait();
-        epilogue_chunk(p, v, m_blk * BM + quad * 32, lane, n0, has_work, bias, z, stage_out + (warp - 2) * (32 * 32));
+        epilogue_chunk<UPD>(p, v, m_blk * BM + quad * 32, lane, n0, has_work, bias, z,
+                            stage_out + (warp - 2) * (32 * 32));
       }
       tc_fence_before();
       __syncwarp();
@@ -908,17 +1031,17 @@ static int make_map(CUtensorMap* out, const void* ptr, int mn, int k, long long 
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool UPD = false>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int grid, cudaStream_t st) {
   using C = Cfg<BN>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN, A_MN, B_MN, UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          C::kSmemBytes);
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
-  gemm_kernel<BN, A_MN, B_MN><<<grid, kThreadsWide, C::kSmemBytes, st>>>(ta, tb, p);
+  gemm_kernel<BN, A_MN, B_MN, UPD><<<grid, kThreadsWide, C::kSmemBytes, st>>>(ta, tb, p);
   CXN_CHECK_LAUNCH();
   return 0;
 }
@@ -987,6 +1110,7 @@ constexpr int kWsLanes = 4;
 static std::mutex g_ws_mu;
 static SplitWs g_ws[64][kWsLanes];
 static thread_local int t_ws_lane = 0;
+static thread_local UpdArgs t_upd = {};   // operands of the next kFlagUpdate call (set by cxn_gemm_wgrad_update)
 
 static bool stream_capturing(cudaStream_t st) {
   cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
@@ -1077,7 +1201,7 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   static const bool auto_split = getenv("CXN_GEMM_NO_AUTOSPLIT") == nullptr;
   // (measured: worth it only while even 64-wide tiles would leave a quarter of the SMs idle)
   const long long tiles64 = (long long)ceil_div(M, BM) * ceil_div(N, 64);
-  if (auto_split && splits == 1 && batch == 1 && bn == 0 && !(flags & kFlagAtomic) && num_kb >= 16 &&
+  if (auto_split && splits == 1 && batch == 1 && bn == 0 && !(flags & (kFlagAtomic | kFlagUpdate)) && num_kb >= 16 &&
       tiles64 * 4 < 3LL * sms) {
     int best_bn = 0, best_splits = 1;
     const int cand[3] = {256, 128, 64};
@@ -1114,13 +1238,14 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   {
     const int pm = gemm_pair_mode();
     const long long t256 = (long long)ceil_div(M, 256) * ceil_div(N, 256) * batch * splits;
-    const bool legal = (bn == 0 || bn == 256) && M > 128 && N > 128 && sms >= 2;
+    const bool legal = (bn == 0 || bn == 256) && M > 128 && N > 128 && sms >= 2 && !(flags & kFlagUpdate);
     // (automatic: only long reductions - with few k-blocks the tile is epilogue-bound and the single-CTA kernel's eight
     // epilogue warps win; measured in profiles/r2_gemm_sweep.txt)
     if (legal && (pm == 2 || (pm == 1 && t256 >= sms / 2 && num_kb >= 16))) {
       Params pp;
       pp.M = M; pp.N = N; pp.K = K; pp.batch = batch; pp.splits = splits; pp.kb_per_split = kbps;
       pp.D = D; pp.ldd = ldd; pp.strideD = strideD; pp.bias = bias; pp.strideBias = strideBias; pp.flags = flags;
+      pp.u = UpdArgs{};
       CUtensorMap pa, pb;
       int rc2 = make_map(&pa, A, M, K, lda, batch, strideA, a_mn != 0, BM);
       if (rc2) return rc2;
@@ -1143,6 +1268,13 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   Params p;
   p.M = M; p.N = N; p.K = K; p.batch = batch; p.splits = splits; p.kb_per_split = kbps;
   p.D = D; p.ldd = ldd; p.strideD = strideD; p.bias = bias; p.strideBias = strideBias; p.flags = flags;
+  p.u = UpdArgs{};
+  if (flags & kFlagUpdate) {
+    // fused updater epilogue: weight-gradient operand layout only (both operands stored [K][MN]), one pass over K
+    if (!a_mn || !b_mn || batch != 1 || splits != 1 || bias != nullptr || (flags & ~kFlagUpdate)) return -7;
+    p.u = t_upd;
+    if (p.u.w == nullptr || p.u.m == nullptr || p.u.hyper == nullptr || (p.u.kind == 2 && p.u.m2 == nullptr)) return -7;
+  }
   CUtensorMap ta, tb;
   const int cl = gemm_cluster_mode();
   if ((cl == 2 || cl == 4) && !a_mn && batch == 1 && splits == 1 && !(flags & (kFlagAtomic | kFlagBeta1)) && bn <= 128 &&
@@ -1172,6 +1304,11 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   if (rc) return rc;
   const long long total = (long long)ceil_div(M, BM) * ceil_div(N, bn) * batch * splits;
   const int grid = (int)(total < sms ? total : sms);
+  if (flags & kFlagUpdate) {
+    if (bn == 256) return launch<256, true, true, true>(ta, tb, p, grid, stream);
+    if (bn == 128) return launch<128, true, true, true>(ta, tb, p, grid, stream);
+    return launch<64, true, true, true>(ta, tb, p, grid, stream);
+  }
 #define CXN_DISPATCH(BN_)                                                                      \
   if (!a_mn && !b_mn) return launch<BN_, false, false>(ta, tb, p, grid, stream);              \
   if (!a_mn && b_mn) return launch<BN_, false, true>(ta, tb, p, grid, stream);                \
@@ -1181,4 +1318,22 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   if (bn == 128) { CXN_DISPATCH(128) }
   { CXN_DISPATCH(64) }
 #undef CXN_DISPATCH
+}
+
+// Weight gradient of a fully connected layer with the updater applied in the epilogue (K6 + K15 in one kernel):
+//   g = A^T-stored . B^T-stored as in cxn_gemm_bf16(a_mn = 1, b_mn = 1), M x N over K (= batch rows), then per element
+//   the sgd / nag / adam step of update_kernel on w / m (/ m2) at [row * ldw + column] and the bf16 copy at
+//   [row * shadow_ld + column].  The gradient itself is never stored: 18 bytes of traffic per parameter instead of the
+//   26 of GEMM + multi-tensor update.  `hyper` = &segment.lr of the layer's entry in the device table.
+//   Returns -7 for arguments the fused path does not take (the caller then runs GEMM + cxn_update).
+CXN_API int cxn_gemm_wgrad_update(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K,
+                                  float* w, float* m, float* m2, void* shadow, long long ldw, long long shadow_ld,
+                                  const float* hyper, int kind, cudaStream_t stream) {
+  using namespace cxn::gemm;
+  if (kind < 0 || kind > 2) return -7;
+  t_upd.w = w; t_upd.m = m; t_upd.m2 = m2; t_upd.shadow = (cxn::bf16*)shadow; t_upd.shadow_ld = shadow_ld;
+  t_upd.hyper = hyper; t_upd.kind = kind;
+  const int rc = cxn_gemm_bf16(A, lda, 0, 1, B, ldb, 0, 1, w, ldw, 0, nullptr, 0, M, N, K, 1, 1, kFlagUpdate, 0, stream);
+  t_upd = UpdArgs{};
+  return rc;
 }

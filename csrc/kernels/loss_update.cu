@@ -111,6 +111,7 @@ struct Segment {
   float lr, wd, momentum, clip;   // refreshed every step
   float adam_lr_t, beta1, beta2;
   int flags;              // bit 0: the producer overwrites this gradient every step - the updater need not zero it
+                          // bit 1: this step's update was applied by the producer (cxn_gemm_wgrad_update): skip
 };
 constexpr int kChunk = 1024;
 
@@ -127,6 +128,7 @@ __global__ void update_kernel(float* __restrict__ w, float* __restrict__ g, floa
                               int kind) {
   for (long long ch = chunk_begin + blockIdx.x; ch < chunk_end; ch += gridDim.x) {
     const Segment s = segs[chunk_seg[ch]];
+    if (s.flags & 2) continue;
     const long long base = ch * kChunk;
 #pragma unroll
     for (int it = 0; it < kChunk / 256 / 4; ++it) {

@@ -69,6 +69,8 @@ class NeuralNet:
         self.tp = None           # parallel.tensor_parallel.TensorParallel when fully connected layers are column-sharded
         self._shared_ids = set() # ids of layer objects used by several connections (share[tag])
         self.wgrad_stream = None
+        self.fuse_update = False
+        self.fuse_now = False
         # step trace (`step_trace = 1` / CXN_STEP_TRACE=1): device timestamps between the layers of a step, also
         # inside a captured graph; read with trace_report()
         self.trace_buf = None
@@ -378,6 +380,18 @@ class NeuralNet:
             if self.tp is not None:
                 self.tp.finish(self.symm_block, consumers)
         self._bind_arena()
+        # CXN_FUSE_UPDATE=1: the weight-gradient GEMM of a fully connected layer applies the updater in its epilogue
+        # (cxn_gemm_wgrad_update) and cxn_update skips those segments - the gradient never round-trips through HBM.
+        # Off by default: measured slower (AlexNet, one GPU: 2.617 vs 2.590 ms/step).  The epilogue touches memory in
+        # 128-byte pieces 4 * nin bytes apart and streams w / m at 3.8 TB/s, where the multi-tensor kernel runs at the
+        # copy roofline - 8 bytes per parameter saved, more than that lost (profiles/r2_experiments.md).
+        import os
+        self.fuse_update = os.environ.get("CXN_FUSE_UPDATE", "0") == "1"
+        for (i, tag), s in self._seg_of.items():
+            l = self.connections[i].layer
+            s.fused = bool(self.connections[i].native and isinstance(l, native.FullConnectLayer) and tag == "wmat"
+                           and id(l) not in shared and l.shard is None and l.tp is None
+                           and l.param.num_input_node % 4 == 0)
         for c in self.connections:
             if c.native and c.type != nc.kSharedLayer:
                 c.layer.b200_setup(self)
@@ -480,7 +494,7 @@ class NeuralNet:
             wv, gv = a.w_view(s), a.g_view(s)
             if c.native:
                 wv.copy_(layer.weight_to_internal(tag, w_ref.to(self.device)).reshape(-1))
-                layer.bind[tag] = _ParamBinding(wv, gv, a.shadow_view(s), s.shadow_ld, s.rows, s.cols)
+                layer.bind[tag] = _ParamBinding(wv, gv, a.shadow_view(s), s.shadow_ld, s.rows, s.cols, s)
             else:
                 if w_ref.data_ptr() != wv.data_ptr():
                     wv.copy_(w_ref.reshape(-1))
@@ -753,11 +767,16 @@ class NeuralNet:
                         u.update(epoch)
             return
         self.need_update = need_update
+        self.fuse_now = False
         if need_update:
+            fuse = self.fuse_update_ok() and not self.accumulate_grads
             if self.hyper_prepared:          # the host half already ran (captured step)
+                fuse = fuse and self.arena.fused_on
                 self.arena.upload_hyper(self.hyper_slot)
             else:
+                self.arena.fused_on = fuse
                 self.arena.refresh_hyper(epoch)
+            self.fuse_now = fuse
         if self.exchange is not None:
             self.exchange.begin_step()
         self._mark(1 + n)          # the train metric and the hyper-parameter upload sit between forward and backward
@@ -798,8 +817,13 @@ class NeuralNet:
                 for u in us:
                     u.update(epoch)
         else:
+            self.arena.fused_on = False
             self.arena.refresh_hyper(epoch)
             self.arena.update()
+
+    def fuse_update_ok(self) -> bool:
+        """whether a step that updates may leave the fully connected weight matrices to their weight-gradient kernel"""
+        return bool(self.fuse_update and self.exchange is None and self.tp is None and self.world_size == 1)
 
     def start_round(self, r: int) -> None:
         for us in self.updaters:

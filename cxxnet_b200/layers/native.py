@@ -26,10 +26,11 @@ def _rows(node: Node) -> int:
 
 class _ParamBinding:
     """Arena views handed to a native layer for one tag."""
-    __slots__ = ("w", "g", "shadow", "shadow_ld", "rows", "cols")
+    __slots__ = ("w", "g", "shadow", "shadow_ld", "rows", "cols", "seg")
 
-    def __init__(self, w, g, shadow, shadow_ld, rows, cols):
+    def __init__(self, w, g, shadow, shadow_ld, rows, cols, seg=None):
         self.w, self.g, self.shadow, self.shadow_ld, self.rows, self.cols = w, g, shadow, shadow_ld, rows, cols
+        self.seg = seg        # the arena segment (optimiser state, entry of the per-step hyper-parameter table)
 
 
 # ----------------------------------------------------------------------------- fullc
@@ -84,7 +85,10 @@ class FullConnectLayer(zoo.FullConnectLayer):
                          b, p.num_input_node, p.num_hidden, flags=ops.GEMM_OUT_BF16)
             ex.exchange.fc_backward(self, ex.need_update)
             return
-        if True:
+        # the updater fused into the weight-gradient epilogue (this step updates, nothing accumulates, one GPU):
+        # the gradient matrix never reaches memory; backward-data goes first because it reads the old weights
+        fuse = ex.fuse_now and W.seg is not None and W.seg.fused
+        if not fuse:
             # gW (nout x nin) += gy^T . x   : A = gy stored [K=b][M=nout], B = x stored [K=b][N=nin]
             ops.gemm(gy.ptr, gy.ld, 0, 1, x.act.ptr, x.act.ld, 0, 1, W.g.data_ptr(), p.num_input_node, 0, None, 0,
                      p.num_hidden, p.num_input_node, b, flags=ops.GEMM_BETA1 if ex.accumulate_grads else 0)
@@ -95,6 +99,13 @@ class FullConnectLayer(zoo.FullConnectLayer):
             # gx (b x nin) = gy (b x nout) . W (nout x nin) : B = W stored [K=nout][N=nin]
             ops.gemm(gy.ptr, gy.ld, 0, 0, W.shadow.data_ptr(), W.shadow_ld, 0, 1, x.grad.ptr, x.grad.ld, 0, None, 0,
                      b, p.num_input_node, p.num_hidden, flags=ops.GEMM_OUT_BF16)
+        if fuse:
+            a, sg = ex.arena, W.seg
+            ops.check(ops.lib().cxn_gemm_wgrad_update(
+                gy.ptr, gy.ld, x.act.ptr, x.act.ld, p.num_hidden, p.num_input_node, b,
+                W.w.data_ptr(), a.m.data_ptr() + 4 * sg.start, (a.m2.data_ptr() + 4 * sg.start) if a.m2 is not None else None,
+                W.shadow.data_ptr(), p.num_input_node, W.shadow_ld, a.hyper_ptr(sg), a.kind, ops.stream()),
+                "cxn_gemm_wgrad_update")
 
 
 # ----------------------------------------------------------------------------- conv

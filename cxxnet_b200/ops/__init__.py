@@ -56,6 +56,7 @@ def lib():
     L = ctypes.CDLL(_LIB_PATH)
     P, I, LL, F, ULL = c_void_p, c_int, c_longlong, c_float, c_ulonglong
     _sig(L.cxn_gemm_bf16, [P, LL, LL, I, P, LL, LL, I, P, LL, LL, P, LL, I, I, I, I, I, I, I, P])
+    _sig(L.cxn_gemm_wgrad_update, [P, LL, P, LL, I, I, I, P, P, P, P, LL, LL, P, I, P])
     if hasattr(L, "cxn_gemm_cluster"):
         _sig(L.cxn_gemm_cluster, [I])
     _sig(L.cxn_nchw_f32_to_nhwc_bf16, [P, P, I, I, I, I, P])

@@ -33,7 +33,7 @@ SEG_DTYPE = np.dtype([
 
 class Segment:
     __slots__ = ("layer_index", "tag", "start", "n", "rows", "cols", "shadow_off", "shadow_ld", "param", "layer",
-                 "beta1", "beta2", "nozero")
+                 "beta1", "beta2", "nozero", "fused")
 
 
 class ParamArena:
@@ -54,6 +54,7 @@ class ParamArena:
         self.chunk_seg = None
         self.nchunks = 0
         self._hyper_arr = None
+        self.fused_on = False   # this step's table tells cxn_update to skip the segments their producer updates
 
     # ------------------------------------------------------------------ layout
     def add(self, layer, layer_index: int, tag: str, rows: int, cols: int, shadow_ld: int, param: UpdaterParam,
@@ -71,6 +72,7 @@ class ParamArena:
             s.shadow_off = -1
         s.param, s.beta1, s.beta2 = param, beta1, beta2
         s.nozero = False
+        s.fused = False       # the layer's weight-gradient kernel can apply the update itself (cxn_gemm_wgrad_update)
         self.segments.append(s)
         return s
 
@@ -106,6 +108,11 @@ class ParamArena:
 
     def g_view(self, s: Segment) -> torch.Tensor:
         return self.g[s.start:s.start + s.n]
+
+    def hyper_ptr(self, s: Segment) -> int:
+        """device address of ``{lr, wd, momentum, clip, adam_lr_t, beta1, beta2}`` of segment ``s`` in the per-step table"""
+        i = self.segments.index(s)
+        return self.seg_dev.data_ptr() + i * SEG_DTYPE.itemsize + SEG_DTYPE.fields["lr"][1]
 
     def shadow_view(self, s: Segment) -> Optional[torch.Tensor]:
         if s.shadow_off < 0:
@@ -144,7 +151,9 @@ class ParamArena:
             arr["wd"][:n] = [s.param.wd for s in segs]
             arr["momentum"][:n] = [s.param.momentum for s in segs]
             arr["clip"][:n] = [s.param.clip_gradient for s in segs]
-            arr["flags"][:n] = [1 if s.nozero else 0 for s in segs]   # the producing kernel overwrites this gradient
+            # bit 0: the producing kernel overwrites this gradient; bit 1: it also applies this step's update
+            fz = self.fused_on
+            arr["flags"][:n] = [(1 if s.nozero else 0) | (2 if (fz and s.fused) else 0) for s in segs]
             if self.kind == ops.UPD_ADAM:
                 arr["adam_lr_t"][:n] = [s.param.base_lr * math.sqrt(1.0 - (1.0 - s.beta2) ** (epoch + 1))
                                         / (1.0 - (1.0 - s.beta1) ** (epoch + 1)) for s in segs]

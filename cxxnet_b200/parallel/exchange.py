@@ -234,7 +234,19 @@ class GradExchange:
                                  (y.grad.ptr, sh.gy_off, step * sh.ld_out * 2, b * sh.ld_out * 2)],
                                 sh.slot_gather, self.counter, self.stream.cuda_stream)
             acc = net.accumulate_grads
-            if sh.my_rows > 0 and "fcgemm" not in self._skip:
+            # this step updates and nothing accumulates: the updater runs in the weight-gradient epilogue over the
+            # owned rows (cxn_gemm_wgrad_update) - their gradient never reaches memory
+            fuse = bool(need_update and not acc and net.fuse_update and sh.my_rows > 0 and nin % 4 == 0
+                        and "fcgemm" not in self._skip)
+            if fuse:
+                e0 = sh.wseg.start + sh.row0 * nin
+                sld = sh.wseg.shadow_ld
+                ops.check(ops.lib().cxn_gemm_wgrad_update(
+                    sh.gy_all.data_ptr() + sh.row0 * 2, sh.ld_out, sh.x_all.data_ptr(), sh.ld_in, sh.my_rows, nin, total_b,
+                    a.w.data_ptr() + 4 * e0, a.m.data_ptr() + 4 * e0, (a.m2.data_ptr() + 4 * e0) if a.m2 is not None else None,
+                    a.shadow.data_ptr() + (sh.wseg.shadow_off + sh.row0 * sld) * 2, nin, sld, a.hyper_ptr(sh.wseg), a.kind,
+                    ops.stream()), "cxn_gemm_wgrad_update")
+            elif sh.my_rows > 0 and "fcgemm" not in self._skip:
                 # gW[row0:row0+my_rows] = GY_all[:, shard]^T . X_all  over the global batch
                 gy_ptr = sh.gy_all.data_ptr() + sh.row0 * 2
                 g_ptr = a.g.data_ptr() + (sh.wseg.start + sh.row0 * nin) * 4
@@ -250,7 +262,7 @@ class GradExchange:
                                                      a.g.data_ptr() + sh.bseg.start * 4, 1 if acc else 0,
                                                      ops.stream()), "colsum")
             if need_update:
-                if sh.my_rows > 0:
+                if sh.my_rows > 0 and not fuse:
                     e0 = sh.wseg.start + sh.row0 * nin
                     a.update(e0 // a.chunk, (e0 + sh.my_rows * nin + a.chunk - 1) // a.chunk)
                 if sh.bseg is not None:

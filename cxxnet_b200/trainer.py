@@ -420,6 +420,7 @@ class NetTrainer:
         net.input_norm = getattr(batch, "norm", None)
         slot = net.stage_input(data[begin:end])
         # host half of the per-step hyper parameters (rewrites the pinned table only when it changed)
+        net.arena.fused_on = net.fuse_update_ok()
         net.arena.prepare_hyper(self.epoch_counter, slot)
         net.hyper_prepared, net.hyper_slot = True, slot
         try:

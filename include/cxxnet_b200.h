@@ -45,6 +45,17 @@ int cxn_gemm_pair(int mode);
  * (default 0) and returns the previous one, -1 for an invalid lane.  GEMMs that can run concurrently (different
  * streams, or parallel branches of a captured graph) must use different lanes.  No reference counterpart. */
 int cxn_gemm_workspace_lane(int lane);
+/* K6 + K15 in one kernel: the weight gradient of a fully connected layer, g (M x N) = A . B^T with both operands
+ * stored [K][MN] (dy as [batch][nout], x as [batch][nin]), whose epilogue applies the updater (kind 0 sgd, 1 nag,
+ * 2 adam - the arithmetic of cxn_update) to the fp32 master w and the state m (m2 for adam) at [row * ldw + column] and
+ * rewrites the bf16 copy at [row * shadow_ld + column] (shadow may be NULL).  The gradient is never stored: 18 bytes
+ * per parameter cross HBM instead of 26.  hyper = {lr, wd, momentum, clip, adam_lr_t, beta1, beta2} in device memory
+ * (the layer's entry of the per-step segment table), read when the kernel runs.  Returns -7 when the arguments do not
+ * fit the fused path (the caller then uses cxn_gemm_bf16 + cxn_update).
+ * Reference: src/layer/fullc_layer-inl.hpp:121-123 followed by src/updater/sgd_updater-inl.hpp:73-84. */
+int cxn_gemm_wgrad_update(const void* A, long long lda, const void* B, long long ldb, int M, int N, int K, float* w,
+                          float* m, float* m2, void* shadow, long long ldw, long long shadow_ld, const float* hyper,
+                          int kind, cudaStream_t stream);
 
 /* K1 (and K2 for stride-1 layers): implicit-GEMM convolution forward, bias (+ReLU) fused.
  * Reference: src/layer/convolution_layer-inl.hpp:79-105. */

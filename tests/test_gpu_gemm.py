@@ -163,3 +163,65 @@ def test_gemm_cta_pairs(a_mn, b_mn):
         _run(129, 130, 64, a_mn, b_mn)                                       # barely two CTAs' worth of rows
     finally:
         L.cxn_gemm_pair(-1)
+
+
+@pytest.mark.parametrize("kind", [0, 1, 2])
+@pytest.mark.parametrize("M,N,K", [(256, 512, 64), (4096, 1152, 256), (200, 100, 48), (130, 72, 40)])
+def test_gemm_wgrad_with_fused_updater(kind, M, N, K):
+    """cxn_gemm_wgrad_update: the weight-gradient GEMM whose epilogue applies sgd / nag / adam to the fp32 master and
+    the momentum and rewrites the bf16 copy - against g = dy^T x in fp64 followed by the closed-form updater (full
+    tiles, several tiles per CTA, and ragged rows / columns that take the element-wise path)"""
+    import ctypes
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    gen = torch.Generator().manual_seed(M + 7 * N + K + kind)
+    ldy, ldx = ops.round_up(M, 8), ops.round_up(N, 8)
+    dy = torch.zeros(K, ldy, dtype=torch.bfloat16, device="cuda")
+    x = torch.zeros(K, ldx, dtype=torch.bfloat16, device="cuda")
+    dy[:, :M] = (torch.randn(K, M, generator=gen) * 0.5).cuda().to(torch.bfloat16)
+    x[:, :N] = torch.randn(K, N, generator=gen).cuda().to(torch.bfloat16)
+    w0 = torch.randn(M, N, generator=gen).cuda()
+    m0 = (torch.randn(M, N, generator=gen) * 0.1).cuda()
+    v0 = (torch.rand(M, N, generator=gen) * 0.1).cuda()
+    lr, wd, mom, clip, adam_lr_t, b1, b2 = 0.05, 0.01, 0.9, (2.0 if kind == 0 else 0.0), 0.002, 0.1, 0.001
+    hyper = torch.tensor([lr, wd, mom, clip, adam_lr_t, b1, b2], dtype=torch.float32, device="cuda")
+    sld = ops.round_up(N, 8)
+    for with_shadow in (True, False):
+        w, m, v = w0.clone(), m0.clone(), v0.clone()
+        shadow = torch.zeros(M, sld, dtype=torch.bfloat16, device="cuda")
+        rc = L.cxn_gemm_wgrad_update(dy.data_ptr(), ldy, x.data_ptr(), ldx, M, N, K, w.data_ptr(), m.data_ptr(),
+                                     v.data_ptr() if kind == 2 else None, shadow.data_ptr() if with_shadow else None,
+                                     N, sld, hyper.data_ptr(), kind, ops.stream())
+        assert rc == 0
+        torch.cuda.synchronize()
+        g = (dy[:, :M].double().t() @ x[:, :N].double())
+        wr, mr, vr = w0.double(), m0.double(), v0.double()
+        if kind == 0:
+            g = g.clamp(-clip, clip)
+            mr = mom * mr - lr * (g + wd * wr)
+            wr = wr + mr
+        elif kind == 1:
+            old = mr
+            mr = mom * old - lr * (g + wd * wr)
+            wr = wr + (1 + mom) * mr - mom * old
+        else:
+            g = g - wd * wr
+            mr = mr + b1 * (g - mr)
+            vr = vr + b2 * (g * g - vr)
+            wr = wr - adam_lr_t * (mr / (vr.sqrt() + 1e-8))
+        assert torch.allclose(w.double(), wr, atol=2e-5, rtol=2e-5), (kind, float((w.double() - wr).abs().max()))
+        assert torch.allclose(m.double(), mr, atol=2e-5, rtol=2e-5)
+        if kind == 2:
+            assert torch.allclose(v.double(), vr, atol=2e-5, rtol=2e-5)
+        else:
+            assert torch.equal(v, v0)
+        if with_shadow:
+            assert torch.equal(shadow[:, :N], w.to(torch.bfloat16))
+            assert float(shadow[:, N:].float().abs().max()) == 0.0 if sld > N else True
+        else:
+            assert float(shadow.float().abs().max()) == 0.0
+    # arguments the fused path does not take
+    assert L.cxn_gemm_wgrad_update(dy.data_ptr(), ldy, x.data_ptr(), ldx, M, N, K, w.data_ptr(), m.data_ptr(), None,
+                                   None, N, sld, hyper.data_ptr(), 2, ops.stream()) == -7      # adam without m2
+    assert L.cxn_gemm_wgrad_update(dy.data_ptr(), ldy, x.data_ptr(), ldx, M, N, K, w.data_ptr(), m.data_ptr(), None,
+                                   None, N, sld, None, 0, ops.stream()) == -7                  # no hyper-parameters

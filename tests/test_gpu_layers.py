@@ -389,3 +389,51 @@ layer[+0] = softmax
                                      return_trainers=True)
     down = [c.layer for c in b2.net.connections if c.layer.type_name == "conv"][1:]
     assert all(l.dgrad_phases and l.col is None for l in down)
+
+
+@pytest.mark.parametrize("graph", [0, 1])
+@pytest.mark.parametrize("updater", ["sgd", "nag", "adam"])
+def test_updater_fused_into_weight_gradient_matches_separate_update(updater, graph, monkeypatch):
+    """fully connected weight matrices on one GPU are updated inside their weight-gradient GEMM
+    (cxn_gemm_wgrad_update) - same weights as GEMM + cxn_update after 4 steps of a scheduled learning rate, eagerly
+    and through the captured step, also with gradient accumulation (where the fused path must stand down)"""
+    from util import copy_weights, make_trainer
+    body = """
+layer[+1] = fullc:fc1
+  nhidden = 96
+layer[+1] = relu
+layer[+0] = dropout
+  threshold = 0.3
+layer[+1] = fullc:fc2
+  nhidden = 72
+layer[+1] = tanh
+layer[+1] = fullc:fc3
+  nhidden = 10
+layer[+0] = softmax
+"""
+    conf = (_conf(body, 32, "1,1,64") + "updater = %s\nwmat:wd = 0.001\nbias:lr = 0.2\nlr:schedule = expdecay\n"
+            "lr:gamma = 0.5\nlr:step = 2\nclip_gradient = 0.5\ncuda_graph = %d\nseed = 11\n" % (updater, graph))
+    for period in (1, 2):
+        monkeypatch.setenv("CXN_FUSE_UPDATE", "0")
+        plain = make_trainer(conf, dev="gpu:0", backend="b200", update_period=period)
+        monkeypatch.setenv("CXN_FUSE_UPDATE", "1")
+        fused = make_trainer(conf, dev="gpu:0", backend="b200", update_period=period)
+        assert not plain.net.fuse_update and fused.net.fuse_update
+        assert sum(s.fused for s in fused.net.arena.segments) == 3
+        copy_weights(plain, fused)
+        for s in range(4 * period):
+            batch = make_batch((32, 1, 1, 64), seed=s, pin=True)
+            plain.update(batch)
+            fused.update(batch)
+        assert fused.net.fuse_now == (period == 1)
+        for name in ("fc1", "fc2", "fc3"):
+            for tag in ("wmat", "bias"):
+                wa, _ = plain.get_weight(name, tag)
+                wb, _ = fused.get_weight(name, tag)
+                assert torch.allclose(torch.from_numpy(wa), torch.from_numpy(wb), atol=1e-6, rtol=1e-5), \
+                    (updater, graph, period, name, tag)
+        # the bf16 copies the next forward pass reads follow the masters
+        for s in fused.net.arena.segments:
+            if s.shadow_off >= 0:
+                sh = fused.net.arena.shadow_view(s).view(s.rows, s.shadow_ld)[:, :s.cols]
+                assert torch.equal(sh, fused.net.arena.w_view(s).view(s.rows, s.cols).to(torch.bfloat16))
