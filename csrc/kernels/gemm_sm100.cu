@@ -86,17 +86,23 @@ __device__ __forceinline__ void update_one(float& w, float& m, float& m2, float 
   }
 }
 
-template <int BN>
+// WIDE: the variant for short-K fp32 problems (the fully connected weight gradients: K = batch rows): a two / four
+// stage ring leaves room for every epilogue warp to stage ALL of its columns of a tile (32 rows x BN / 2), so a
+// result row leaves in one 512-byte (BN = 256) or 256-byte (BN = 128) piece instead of four / two 128-byte pieces
+// written microseconds apart.
+template <int BN, bool WIDE = false>
 struct Cfg {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kStages = WIDE ? (BN >= 256 ? 2 : 4) : ((BN >= 256) ? 4 : (BN >= 128 ? 6 : 8));
   static constexpr int kTmemCols = kAccStages * BN;  // 128 / 256 / 512
-  // epilogue staging: per epilogue warp a 32 x 32 fp32 chunk whose 16-byte columns are XOR-swizzled with the row
-  // (conflict-free 128-bit shared accesses both ways, no padding); room for 8 epilogue warps
-  static constexpr int kStageOutBytes = 8 * 32 * 32 * 4;
+  // epilogue staging: per epilogue warp a 32 x 32 fp32 chunk (WIDE: 32 x BN / 2) whose 16-byte columns are
+  // XOR-swizzled with the row (conflict-free 128-bit shared accesses both ways, no padding); 8 epilogue warps
+  static constexpr int kWarpStageFloats = 32 * (WIDE ? BN / 2 : 32);
+  static constexpr int kStageOutBytes = 8 * kWarpStageFloats * 4;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/ + kStageOutBytes;
+  static_assert(kSmemBytes <= 232448, "shared memory budget of one CTA");
 };
 
 using namespace cxn::tc;
@@ -301,10 +307,113 @@ __device__ __forceinline__ void epilogue_chunk(const Params& p, uint32_t (&v)[32
   }
 }
 
-template <int BN, bool A_MN, bool B_MN, bool UPD = false>
+// WIDE epilogue of one warp: its 32 rows x W (= BN / 2) columns of the accumulator go through shared memory and leave
+// row by row - one instruction writes (or, with the fused updater, reads and rewrites) W * 4 contiguous bytes of one
+// or two result rows.  Returns false (nothing done) when the fast path does not apply; the caller then walks the
+// 32-column chunks.  taddr: tensor-memory address of the warp's first column in its lane quadrant.
+template <int W, bool UPD>
+__device__ __forceinline__ bool epilogue_wide(const Params& p, uint32_t taddr, int row0, int lane, int n0w, bool has_work,
+                                              int z, float* sm) {
+  constexpr int C16 = W / 4;            // 16-byte columns per row: 32 or 16
+  constexpr int RPI = 32 / C16;         // rows per instruction: 1 or 2
+  constexpr int ITERS = 32 / RPI;
+  if (n0w + W > p.N || (p.ldd & 3) != 0 || (p.strideD & 3) != 0 || (reinterpret_cast<uintptr_t>(p.D) & 15) != 0 ||
+      (p.flags & (kFlagRelu | kFlagOutBf16 | kFlagAtomic)) != 0 || p.bias != nullptr)
+    return false;
+  if constexpr (UPD) {
+    // (adam keeps a third array: it takes the 32-column chunks)
+    if ((p.u.shadow_ld & 3) != 0 || p.u.kind == 2) return false;
+  }
+#pragma unroll
+  for (int c = 0; c < W / 32; ++c) {
+    uint32_t v[32];
+    tmem_ld32(taddr + (uint32_t)(c * 32), v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      float4 o4;
+      o4.x = has_work ? __uint_as_float(v[4 * q]) : 0.0f;
+      o4.y = has_work ? __uint_as_float(v[4 * q + 1]) : 0.0f;
+      o4.z = has_work ? __uint_as_float(v[4 * q + 2]) : 0.0f;
+      o4.w = has_work ? __uint_as_float(v[4 * q + 3]) : 0.0f;
+      *reinterpret_cast<float4*>(sm + lane * W + 4 * ((c * 8 + q) ^ (lane & 7))) = o4;
+    }
+  }
+  __syncwarp();
+  const int rsub = lane / C16, c16 = lane % C16;
+  const long long col = n0w + 4 * c16;
+  if constexpr (!UPD) {
+    const bool beta1 = p.flags & kFlagBeta1;
+    float* dbase = reinterpret_cast<float*>(p.D) + (long long)z * p.strideD + col;
+#pragma unroll 8
+    for (int it = 0; it < ITERS; ++it) {
+      const int r = it * RPI + rsub;
+      if (row0 + r < p.M) {
+        float4 o4 = *reinterpret_cast<const float4*>(sm + r * W + 4 * (c16 ^ (r & 7)));
+        float4* dp = reinterpret_cast<float4*>(dbase + (long long)(row0 + r) * p.ldd);
+        if (beta1) {
+          const float4 c4 = *dp;
+          o4.x += c4.x; o4.y += c4.y; o4.z += c4.z; o4.w += c4.w;
+        }
+        *dp = o4;
+      }
+    }
+  } else {
+    UpdHyper h;
+    h.lr = __ldg(p.u.hyper); h.wd = __ldg(p.u.hyper + 1); h.momentum = __ldg(p.u.hyper + 2);
+    h.clip = __ldg(p.u.hyper + 3); h.adam_lr_t = __ldg(p.u.hyper + 4); h.beta1 = __ldg(p.u.hyper + 5);
+    h.beta2 = __ldg(p.u.hyper + 6);
+    const int kind = p.u.kind;
+    // groups of G result rows: all (w, m) loads of a group are issued before its arithmetic - 2 x G 16-byte loads
+    // in flight per thread.  Measured on fc6 (37.7 M parameters): G = 8 145 us; a double-buffered G = 4 pipeline 167 us;
+    // the same with streaming (evict-first) hints 172 us - what counts is the number of loads in flight.
+    constexpr int G = (ITERS < 16) ? ITERS : 16;
+#pragma unroll 1
+    for (int g0 = 0; g0 < ITERS; g0 += G) {
+      float4 wv[G], mv[G];
+#pragma unroll
+      for (int i = 0; i < G; ++i) {
+        const int r = (g0 + i) * RPI + rsub;
+        wv[i] = mv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row0 + r < p.M) {
+          const long long off = (long long)(row0 + r) * p.ldd + col;
+          wv[i] = *reinterpret_cast<const float4*>(p.u.w + off);
+          mv[i] = *reinterpret_cast<const float4*>(p.u.m + off);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < G; ++i) {
+        const int r = (g0 + i) * RPI + rsub;
+        if (row0 + r < p.M) {
+          const float4 g4 = *reinterpret_cast<const float4*>(sm + r * W + 4 * (c16 ^ (r & 7)));
+          float unused = 0.0f;
+          update_one(wv[i].x, mv[i].x, unused, g4.x, h, kind);
+          update_one(wv[i].y, mv[i].y, unused, g4.y, h, kind);
+          update_one(wv[i].z, mv[i].z, unused, g4.z, h, kind);
+          update_one(wv[i].w, mv[i].w, unused, g4.w, h, kind);
+          const long long off = (long long)(row0 + r) * p.ldd + col;
+          *reinterpret_cast<float4*>(p.u.w + off) = wv[i];
+          *reinterpret_cast<float4*>(p.u.m + off) = mv[i];
+          if (p.u.shadow != nullptr) {
+            const __nv_bfloat162 h0 = __floats2bfloat162_rn(wv[i].x, wv[i].y);
+            const __nv_bfloat162 h1 = __floats2bfloat162_rn(wv[i].z, wv[i].w);
+            uint2 u2;
+            u2.x = *reinterpret_cast<const uint32_t*>(&h0);
+            u2.y = *reinterpret_cast<const uint32_t*>(&h1);
+            *reinterpret_cast<uint2*>(p.u.shadow + (long long)(row0 + r) * p.u.shadow_ld + col) = u2;
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+  return true;
+}
+
+template <int BN, bool A_MN, bool B_MN, bool UPD = false, bool WIDE = false>
 __global__ void __launch_bounds__(kThreadsWide, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, WIDE>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -456,16 +565,24 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tc_fence_after();
       const bool has_work = kb1 > kb0;
       const float* bias = (p.bias != nullptr && split == 0) ? p.bias + (long long)z * p.strideBias : nullptr;
+      bool done = false;
+      if constexpr (WIDE) {
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + chalf * kColsPerWarp);
+        done = epilogue_wide<kColsPerWarp, UPD>(p, taddr, m_blk * BM + quad * 32, lane, n_blk * BN + chalf * kColsPerWarp,
+                                                has_work, z, stage_out + (warp - 2) * C::kWarpStageFloats);
+      }
+      if (!done) {
 #pragma unroll 1
-      for (int c0 = chalf * kColsPerWarp; c0 < (chalf + 1) * kColsPerWarp; c0 += 32) {
-        const int n0 = n_blk * BN + c0;
-        if (n0 >= p.N) break;  // warp-uniform
-        uint32_t v[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
-        tmem_ld32(taddr, v);
-        tmem_ld_wait();
-        epilogue_chunk<UPD>(p, v, m_blk * BM + quad * 32, lane, n0, has_work, bias, z,
-                            stage_out + (warp - 2) * (32 * 32));
+        for (int c0 = chalf * kColsPerWarp; c0 < (chalf + 1) * kColsPerWarp; c0 += 32) {
+          const int n0 = n_blk * BN + c0;
+          if (n0 >= p.N) break;  // warp-uniform
+          uint32_t v[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * BN + c0);
+          tmem_ld32(taddr, v);
+          tmem_ld_wait();
+          epilogue_chunk<UPD>(p, v, m_blk * BM + quad * 32, lane, n0, has_work, bias, z,
+                              stage_out + (warp - 2) * C::kWarpStageFloats);
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -1031,17 +1148,17 @@ static int make_map(CUtensorMap* out, const void* ptr, int mn, int k, long long 
   return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool UPD = false>
+template <int BN, bool A_MN, bool B_MN, bool UPD = false, bool WIDE = false>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int grid, cudaStream_t st) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, WIDE>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN, A_MN, B_MN, UPD>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         C::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(gemm_kernel<BN, A_MN, B_MN, UPD, WIDE>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
-  gemm_kernel<BN, A_MN, B_MN, UPD><<<grid, kThreadsWide, C::kSmemBytes, st>>>(ta, tb, p);
+  gemm_kernel<BN, A_MN, B_MN, UPD, WIDE><<<grid, kThreadsWide, C::kSmemBytes, st>>>(ta, tb, p);
   CXN_CHECK_LAUNCH();
   return 0;
 }
@@ -1304,11 +1421,22 @@ CXN_API int cxn_gemm_bf16(const void* A, long long lda, long long strideA, int a
   if (rc) return rc;
   const long long total = (long long)ceil_div(M, BM) * ceil_div(N, bn) * batch * splits;
   const int grid = (int)(total < sms ? total : sms);
+  // short-K fp32 problems in the weight-gradient layout (the fully connected weight gradients): WIDE epilogue - whole
+  // result rows of a warp's columns per instruction (Cfg<BN, true>).  CXN_GEMM_WIDE: 1 (default) = with the fused
+  // updater only (measured: 174 -> 145 us on fc6; the plain fp32 store gets slower, 42 -> 44 us), 2 = also plain
+  // stores, 0 = never.
+  static const int wide_mode = []() { const char* e = getenv("CXN_GEMM_WIDE"); return e == nullptr ? 1 : atoi(e); }();
+  const bool wide = (wide_mode >= 2 || (wide_mode == 1 && (flags & kFlagUpdate))) && a_mn && b_mn && bn >= 128 &&
+                    kbps <= 8 && bias == nullptr && !(flags & (kFlagOutBf16 | kFlagAtomic | kFlagRelu));
   if (flags & kFlagUpdate) {
+    if (wide && bn == 256) return launch<256, true, true, true, true>(ta, tb, p, grid, stream);
+    if (wide && bn == 128) return launch<128, true, true, true, true>(ta, tb, p, grid, stream);
     if (bn == 256) return launch<256, true, true, true>(ta, tb, p, grid, stream);
     if (bn == 128) return launch<128, true, true, true>(ta, tb, p, grid, stream);
     return launch<64, true, true, true>(ta, tb, p, grid, stream);
   }
+  if (wide && bn == 256) return launch<256, true, true, false, true>(ta, tb, p, grid, stream);
+  if (wide && bn == 128) return launch<128, true, true, false, true>(ta, tb, p, grid, stream);
 #define CXN_DISPATCH(BN_)                                                                      \
   if (!a_mn && !b_mn) return launch<BN_, false, false>(ta, tb, p, grid, stream);              \
   if (!a_mn && b_mn) return launch<BN_, false, true>(ta, tb, p, grid, stream);                \

@@ -380,13 +380,13 @@ class NeuralNet:
             if self.tp is not None:
                 self.tp.finish(self.symm_block, consumers)
         self._bind_arena()
-        # CXN_FUSE_UPDATE=1: the weight-gradient GEMM of a fully connected layer applies the updater in its epilogue
-        # (cxn_gemm_wgrad_update) and cxn_update skips those segments - the gradient never round-trips through HBM.
-        # Off by default: measured slower (AlexNet, one GPU: 2.617 vs 2.590 ms/step).  The epilogue touches memory in
-        # 128-byte pieces 4 * nin bytes apart and streams w / m at 3.8 TB/s, where the multi-tensor kernel runs at the
-        # copy roofline - 8 bytes per parameter saved, more than that lost (profiles/r2_experiments.md).
+        # The weight-gradient GEMM of a fully connected layer applies the updater in its epilogue
+        # (cxn_gemm_wgrad_update) and cxn_update skips those segments: the gradient never round-trips through HBM
+        # (18 instead of 26 bytes per parameter).  AlexNet, one GPU: 2.580 vs 2.592 ms/step with the WIDE epilogue
+        # (whole 512-byte row pieces per instruction); with 128-byte pieces it lost (2.617) - profiles/r2_experiments.md.
+        # CXN_FUSE_UPDATE=0 keeps GEMM + multi-tensor update.
         import os
-        self.fuse_update = os.environ.get("CXN_FUSE_UPDATE", "0") == "1"
+        self.fuse_update = os.environ.get("CXN_FUSE_UPDATE", "1") != "0"
         for (i, tag), s in self._seg_of.items():
             l = self.connections[i].layer
             s.fused = bool(self.connections[i].native and isinstance(l, native.FullConnectLayer) and tag == "wmat"
