@@ -347,6 +347,74 @@ __global__ void __launch_bounds__(256) pool_bwd_row_kernel(const bf16* __restric
   *reinterpret_cast<uint4*>(dx + xoff) = o;
 }
 
+// Stride-2 max-pool backward, one thread per 2 x 2 block of input pixels (x 8 channels).  The four pixels of a block
+// lie in at most the same four windows - (i-1, j-1), (i-1, j), (i, j-1), (i, j) for the block (i, j), window sizes up to
+// 4 x 4 - so the pooled value and its gradient are fetched once per block: 12 16-byte loads for four results where
+// the per-pixel kernel issues 9 per result (its y / dy re-reads, not DRAM, bound it: 43 % of the copy roofline).
+// Same arithmetic and the same window order as pool_bwd_row_kernel.
+__global__ void __launch_bounds__(256) pool_bwd_quad_kernel(const bf16* __restrict__ x, const bf16* __restrict__ y,
+                                                            const bf16* __restrict__ dy, bf16* __restrict__ dx, PoolGeom g) {
+  const int j = blockIdx.x * blockDim.y + threadIdx.y;
+  if (2 * j >= g.W) return;
+  const int i = blockIdx.y, n = blockIdx.z, c = threadIdx.x << 3;
+  uint4 pv[2][2], gv[2][2];
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      const int p = i - 1 + a, q = j - 1 + b;
+      const bool ok = p >= 0 && p < g.OH && q >= 0 && q < g.OW;
+      const long long off = (((long long)n * g.OH + p) * g.OW + q) * g.C + c;
+      pv[a][b] = ok ? *reinterpret_cast<const uint4*>(y + off) : make_uint4(0, 0, 0, 0);
+      gv[a][b] = ok ? *reinterpret_cast<const uint4*>(dy + off) : make_uint4(0, 0, 0, 0);   // no window: no gradient
+    }
+  const __nv_bfloat162 z = __float2bfloat162_rn(0.0f);
+  uint4 xr[2][2];
+#pragma unroll
+  for (int dr = 0; dr < 2; ++dr)
+#pragma unroll
+    for (int dc = 0; dc < 2; ++dc) {
+      const int r = 2 * i + dr, cc = 2 * j + dc;
+      xr[dr][dc] = (r < g.H && cc < g.W)
+                       ? *reinterpret_cast<const uint4*>(x + (((long long)n * g.H + r) * g.W + cc) * g.C + c)
+                       : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+  for (int dr = 0; dr < 2; ++dr)
+#pragma unroll
+    for (int dc = 0; dc < 2; ++dc) {
+      const int r = 2 * i + dr, cc = 2 * j + dc;
+      if (r >= g.H || cc >= g.W) continue;
+      const __nv_bfloat162* hx = reinterpret_cast<const __nv_bfloat162*>(&xr[dr][dc]);
+      __nv_bfloat162 xm[4], am[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        xm[k] = g.relu ? __hmax2(hx[k], z) : hx[k];
+        am[k] = z;
+      }
+#pragma unroll
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          // window (i - 1 + a, j - 1 + b) starts at row 2 (i - 1 + a): the pixel is dr + 2 (1 - a) rows below its top
+          if (dr + 2 * (1 - a) >= g.K_y || dc + 2 * (1 - b) >= g.K_x) continue;     // (uniform over the grid)
+          const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&pv[a][b]);
+          const __nv_bfloat162* hg = reinterpret_cast<const __nv_bfloat162*>(&gv[a][b]);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) am[k] = __hfma2(__heq2(xm[k], hp[k]), hg[k], am[k]);
+        }
+      if (g.relu) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) am[k] = __hmul2(am[k], __hgt2(hx[k], z));
+      }
+      uint4 o;
+      __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) ho[k] = am[k];
+      *reinterpret_cast<uint4*>(dx + (((long long)n * g.H + r) * g.W + cc) * g.C + c) = o;
+    }
+}
+
 // The same with the bias gradient of the layer in front fused in: when the pooled node is the (ReLU-masked) output
 // of a convolution, dx IS that convolution's output gradient and its bias gradient is the column sum of dx over all
 // pixels - a separate pass over the largest gradient tensors of the net otherwise (reference: the convolution's
@@ -737,7 +805,15 @@ CXN_API int cxn_pool_bwd(const void* x, const void* y, const void* dy, void* dx,
   PoolGeom g{N, H, W, C, ky, kx, stride, OH, OW, mode, relu};
   if ((long long)N * H * W * C <= 0) return 0;
   const bool v = pool_vec(x, y, C) && pool_vec(dy, dx, C);
-  if (v && mode == 0 && N <= 65535 && H <= 65535 && ky <= 2 * stride && kx <= 2 * stride && C / 8 <= 256) {
+  static const bool quad_on = []() { const char* e = getenv("CXN_POOL_QUAD"); return e == nullptr || e[0] != '0'; }();
+  if (quad_on && v && mode == 0 && stride == 2 && ky <= 4 && kx <= 4 && N <= 65535 && H <= 2 * 65535 && C / 8 <= 256) {
+    // stride-2 max pooling: one thread per 2 x 2 input block and 8 channels
+    const int cv = C / 8, qw = (W + 1) / 2;
+    const int py_max = 256 / cv > 0 ? 256 / cv : 1;
+    const int py = ceil_div(qw, ceil_div(qw, py_max));       // equal shares of a row for its blocks
+    dim3 block(cv, py), grid(ceil_div(qw, py), (H + 1) / 2, N);
+    pool_bwd_quad_kernel<<<grid, block, 0, st>>>((const bf16*)x, (const bf16*)y, (const bf16*)dy, (bf16*)dx, g);
+  } else if (v && mode == 0 && N <= 65535 && H <= 65535 && ky <= 2 * stride && kx <= 2 * stride && C / 8 <= 256) {
     // max pooling: one thread per (pixel, 8 channels) with 2-D thread indexing
     const int cv = C / 8;
     const int py = 256 / cv > 0 ? 256 / cv : 1;

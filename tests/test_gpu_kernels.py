@@ -77,6 +77,36 @@ def test_pool_bwd_with_fused_bias_gradient(shape, k, s):
         assert torch.allclose(gb, want, atol=1e-3 * max(1.0, float(want.abs().max())), rtol=1e-4), (rep, float((gb - want).abs().max()))
 
 
+@pytest.mark.parametrize("relu", [0, 1])
+@pytest.mark.parametrize("shape,k", [((2, 16, 10, 12), 3), ((2, 8, 11, 9), 4), ((3, 32, 28, 28), 2), ((2, 96, 55, 55), 3),
+                                     ((2, 256, 13, 13), 3), ((1, 8, 3, 3), 3), ((2, 8, 5, 4), 1)])
+def test_pool_bwd_stride2_blocks_with_ties(shape, k, relu):
+    """stride-2 max-pool backward (one thread per 2 x 2 input block, pool_bwd_quad_kernel): inputs drawn from a few
+    values, so windows hold ties and EVERY maximal input must receive the gradient; odd and even extents, window
+    sizes 1-4, with and without the fused ReLU mask"""
+    from cxxnet_b200 import ops
+    from cxxnet_b200.layers.zoo import pool_backward, pool_forward
+    L = ops.lib()
+    torch.manual_seed(k * 10 + relu)
+    n, c, h, w = shape
+    x = (torch.randint(-2, 3, shape, device="cuda").float() * 0.5)
+    xr = nhwc(x)
+    xin = torch.relu(x) if relu else x
+    yref = pool_forward(xin, k, k, 2, "max")
+    oh, ow = yref.shape[2:]
+    y = torch.zeros(n * oh * ow, c, dtype=torch.bfloat16, device="cuda")
+    ops.check(L.cxn_pool_fwd(xr.data_ptr(), y.data_ptr(), n, h, w, c, k, k, 2, oh, ow, 0, relu, ops.stream()), "pool")
+    assert torch.equal(from_nhwc(y, n, c, oh, ow), yref)
+    g = bf(torch.randint(-4, 5, yref.shape, device="cuda").float() * 0.25).float()       # sums stay exact in bf16
+    dxref = pool_backward(xin, yref, g, k, k, 2, "max")
+    if relu:
+        dxref = dxref * (x > 0)
+    dx = torch.full_like(xr, 7.0)
+    ops.check(L.cxn_pool_bwd(xr.data_ptr(), y.data_ptr(), nhwc(g).data_ptr(), dx.data_ptr(), n, h, w, c, k, k, 2, oh,
+                             ow, 0, relu, ops.stream()), "pool_bwd")
+    assert torch.equal(from_nhwc(dx, n, c, h, w), dxref)
+
+
 def test_pool_relu_mask_variants():
     from cxxnet_b200 import ops
     from cxxnet_b200.layers.zoo import pool_backward, pool_forward
