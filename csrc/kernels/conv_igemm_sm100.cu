@@ -240,6 +240,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
       }
       if (UNI) __syncwarp();
       const int ohw = p.OH * p.OW;
+      const int step_oh = BK / p.OW, step_ow = BK - step_oh * p.OW;     // 64 pixels = step_oh rows + step_ow columns
       for (long long t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         int n_blk, m_blk, split, g;
         decode_tile(t, n_blk, m_blk, split, g);
@@ -253,6 +254,26 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
           const int oh = r / p.OW;
           pw = (r - oh * p.OW) * p.stride_x - p.pad_x;
           ph = oh * p.stride_y - p.pad_y;
+        }
+        // weight gradient on the im2col route: the tile's (up to four) 64-column atoms -> (channel, kw, kh), and the
+        // first pixel of the split -> (ow, oh, n), stepped by 64 pixels per k-block without divisions
+        int wg_c[4] = {0, 0, 0, 0}, wg_kw[4] = {0, 0, 0, 0}, wg_kh[4] = {0, 0, 0, 0};
+        int wg_n = 0, wg_oh = 0, wg_ow = 0;
+        int fp_chunk = 0, fp_kw = 0, fp_kh = 0;     // forward: (64-channel chunk, kw, kh) of k-block kb0 = 0
+        if (ATMA && WGRAD) {
+#pragma unroll
+          for (int a = 0; a < 4; ++a) {
+            const int n0 = n_blk * p.bn + a * 64;
+            const int tap = n0 / p.Cg, c0 = n0 - tap * p.Cg;
+            wg_kh[a] = tap / p.KW;
+            wg_kw[a] = tap - wg_kh[a] * p.KW;
+            wg_c[a] = g * p.Cg + c0;
+          }
+          const long long pix0 = (long long)kb0 * BK;
+          wg_n = (int)(pix0 / ohw);
+          const int r = (int)(pix0 - (long long)wg_n * ohw);
+          wg_oh = r / p.OW;
+          wg_ow = r - wg_oh * p.OW;
         }
         for (int kb = kb0; kb < kb1; ++kb) {
           timed_wait(empty_bar(stage), phase ^ 1u, pw0);
@@ -268,9 +289,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
               if (tx) mbar_expect_tx(full_bar(stage), tx); else mbar_arrive(full_bar(stage));
               if (ATMA) {
                 // A = patches: BMT output positions x 64 channels through tap (kh, kw)
-                const int tap = pk / cpk, chunk = pk - tap * cpk;
-                const int kh = tap / p.KW, kw = tap - kh * p.KW;
-                tma_load_im2col_4d(sa, &tmPatch, full_bar(stage), g * p.Cg + chunk * 64, pw, ph, pn, kw, kh);
+                tma_load_im2col_4d(sa, &tmPatch, full_bar(stage), g * p.Cg + fp_chunk * 64, pw, ph, pn, fp_kw, fp_kh);
               }
               // B = W[g] : K-major box {64 (k), bn (n)}
               if (!bres) tma_load_3d(sb, &tmDense, full_bar(stage), pk * BK, n_blk * p.bn, g);
@@ -287,20 +306,31 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
               for (int h = 0; h < BM / 64; ++h)
                 tma_load_3d(sa + h * (64 * BK * 2), &tmDense, full_bar(stage), m_blk * BM + h * 64, kb * BK, g);
               if (ATMA) {
-                // B = patches, MN-major: per 64-column atom (one tap, 64 channels) the 64 pixels of this k-block
-                const long long pix0 = (long long)kb * BK;
-                const int n = (int)(pix0 / ohw);
-                const int r = (int)(pix0 - (long long)n * ohw);
-                const int oh = r / p.OW;
-                const int w0 = (r - oh * p.OW) * p.stride_x - p.pad_x, h0 = oh * p.stride_y - p.pad_y;
-                for (int a = 0; a < natoms_ld; ++a) {
-                  const int n0 = n_blk * p.bn + a * 64;
-                  const int tap = n0 / p.Cg, c0 = n0 - tap * p.Cg;
-                  const int kh = tap / p.KW, kw = tap - kh * p.KW;
-                  tma_load_im2col_4d(sb + a * (64 * BK * 2), &tmPatch, full_bar(stage), g * p.Cg + c0, w0, h0, n, kw, kh);
-                }
+                // B = patches, MN-major: per 64-column atom (one tap, 64 channels) the 64 pixels of this k-block.
+                // (Everything this needs was decoded outside the k loop: the elected lane's instruction stream is
+                // what paces the loads of this kernel - bench/wgrad_roles.py.)
+                const int w0 = wg_ow * p.stride_x - p.pad_x, h0 = wg_oh * p.stride_y - p.pad_y;
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+                  if (a < natoms_ld)
+                    tma_load_im2col_4d(sb + a * (64 * BK * 2), &tmPatch, full_bar(stage), wg_c[a], w0, h0, wg_n, wg_kw[a],
+                                       wg_kh[a]);
               }
             }
+          }
+          if (ATMA && !WGRAD) {
+            // the next k-block: next 64-channel chunk of the tap, then the next tap
+            if (++fp_chunk == cpk) {
+              fp_chunk = 0;
+              if (++fp_kw == p.KW) { fp_kw = 0; ++fp_kh; }
+            }
+          }
+          if (ATMA && WGRAD) {
+            // the next k-block starts 64 pixels on
+            wg_ow += step_ow;
+            wg_oh += step_oh;
+            if (wg_ow >= p.OW) { wg_ow -= p.OW; ++wg_oh; }
+            while (wg_oh >= p.OH) { wg_oh -= p.OH; ++wg_n; }
           }
           if (UNI) __syncwarp();
           if (++stage == nst) { stage = 0; phase ^= 1u; }
@@ -997,16 +1027,19 @@ conv_fprop_pair_kernel(const __grid_constant__ CUtensorMap tmHalf, const __grid_
       const int oh = r / p.OW;
       const int pw = (r - oh * p.OW) * p.stride_x - p.pad_x;
       const int ph = oh * p.stride_y - p.pad_y;
+      int chunk = 0, kw = 0, kh = 0;
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait_warp(empty_bar(stage), phase ^ 1u);
         const uint32_t sa = smem_base + stage * (uint32_t)kStageBytes;
         const uint32_t sb = sa + kABytes;
         if (elect_one()) {
           if (leader) mbar_expect_tx(full_bar(stage), 2u * ((uint32_t)kABytes + (uint32_t)half_rows * BK * 2));
-          const int tap = kb / cpk, chunk = kb - tap * cpk;
-          const int kh = tap / p.KW, kw = tap - kh * p.KW;
           tma_load_im2col_4d_2cta(sa, &tmPatch, full_bar(stage), g * p.Cg + chunk * 64, pw, ph, pn, kw, kh);
           tma_load_3d_2cta(sb, &tmHalf, full_bar(stage), kb * BK, n_blk * p.bn + (int)crank * half_rows, g);
+        }
+        if (++chunk == cpk) {       // next 64-channel chunk of the tap, then the next tap (no divisions in this loop)
+          chunk = 0;
+          if (++kw == p.KW) { kw = 0; ++kh; }
         }
         __syncwarp();
         if (++stage == nst) { stage = 0; phase ^= 1u; }

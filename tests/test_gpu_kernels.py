@@ -190,7 +190,8 @@ def test_dropout_mask_is_reproducible_and_scaled():
     assert abs(float((y1 > 0).float().mean()) - 0.5) < 0.01
 
 
-@pytest.mark.parametrize("rows,cols", [(100, 10), (30000, 96), (5000, 256), (777, 1000), (256, 4096)])
+@pytest.mark.parametrize("rows,cols", [(100, 10), (30000, 96), (5000, 256), (777, 1000), (256, 4096), (200003, 96),
+                                       (43264, 384)])
 def test_colsum(rows, cols):
     from cxxnet_b200 import ops
     L = ops.lib()
