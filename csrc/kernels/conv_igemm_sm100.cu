@@ -1441,12 +1441,13 @@ conv_fprop_halo_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid
 // W[g][oc][kh][kw][ic] (ld_in) -> Wt[g][ic][KH-1-kh][KW-1-kw][oc] (ld_out): the filter of the equivalent
 // forward convolution that computes backward-data of a stride-1 convolution.  Per (group, tap) this is
 // the transpose of an ocg x icg block: 32 x 32 tiles through shared memory, both sides coalesced.
+// (cpitch: elements between the taps of the source layout - icg, or more when its channels are padded)
 __global__ void flip_weights_kernel(const bf16* __restrict__ w, bf16* __restrict__ wt, int ocg, int icg, int taps,
-                                    int ld_in, int ld_out) {
+                                    int ld_in, int ld_out, int cpitch) {
   __shared__ bf16 tile[32][33];
   const int g = blockIdx.z / taps, t = blockIdx.z - g * taps;
   const int oc0 = blockIdx.y * 32, ic0 = blockIdx.x * 32;
-  const bf16* src = w + (long long)g * ocg * ld_in + (long long)t * icg;
+  const bf16* src = w + (long long)g * ocg * ld_in + (long long)t * cpitch;
   bf16* dst = wt + (long long)g * icg * ld_out + (long long)(taps - 1 - t) * ocg;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
     const int oc = oc0 + i, ic = ic0 + threadIdx.x;
@@ -1561,7 +1562,10 @@ static bool atma_ok(const Params& p) {
   if ((p.W + 2 * p.pad_x - p.KW) / p.stride_x + 1 != p.OW || (p.H + 2 * p.pad_y - p.KH) / p.stride_y + 1 != p.OH) return false;
   if (p.W + 2 * p.pad_x < p.KW || p.H + 2 * p.pad_y < p.KH) return false;
   if ((reinterpret_cast<uintptr_t>(p.src) & 15) || (p.Cs % 8)) return false;
-  if (p.view_cdim && ((p.view_row % 8) || (p.view_img % 8) || p.view_cdim < p.G * p.Cg)) return false;
+  // (a view of ONE group may expose fewer channels than its last 64-channel chunk: the tensor map zero-fills the rest)
+  if (p.view_cdim && ((p.view_row % 8) || (p.view_img % 8) || (p.view_cdim % 8) ||
+                      (p.view_cdim < p.G * p.Cg && (p.G != 1 || p.view_cdim + 63 < p.Cg))))
+    return false;
   return get_encode_im2col() != nullptr;
 }
 
@@ -2069,7 +2073,19 @@ CXN_API int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int i
   if (total <= 0) return 0;
   if ((long long)G * KH * KW > 65535) return -1;
   dim3 grid(ceil_div(icg, 32), ceil_div(ocg, 32), G * KH * KW), block(32, 8);
-  flip_weights_kernel<<<grid, block, 0, st>>>((const bf16*)w, (bf16*)wt, ocg, icg, KH * KW, ld_in, ld_out);
+  flip_weights_kernel<<<grid, block, 0, st>>>((const bf16*)w, (bf16*)wt, ocg, icg, KH * KW, ld_in, ld_out, icg);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+// The same from a filter whose taps are `cpitch` >= icg elements apart (channel-padded internal layout: the padding
+// channels are not part of the backward-data problem).
+CXN_API int cxn_conv_flip_weights_pitch(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in,
+                                        int ld_out, int cpitch, cudaStream_t st) {
+  const long long total = (long long)G * ocg * KH * KW * icg;
+  if (total <= 0) return 0;
+  if ((long long)G * KH * KW > 65535 || cpitch < icg) return -1;
+  dim3 grid(ceil_div(icg, 32), ceil_div(ocg, 32), G * KH * KW), block(32, 8);
+  flip_weights_kernel<<<grid, block, 0, st>>>((const bf16*)w, (bf16*)wt, ocg, icg, KH * KW, ld_in, ld_out, cpitch);
   CXN_CHECK_LAUNCH();
   return 0;
 }

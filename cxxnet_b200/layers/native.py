@@ -141,6 +141,7 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         self.bias_grad_fused = False   # the pooling layer behind this one accumulates the bias gradient (_NativePool.bias_of)
         self.dgrad_phases = False      # strided backward-data as stride*stride implicit-GEMM problems (cxn_conv_dgrad_strided)
         self.phase_scratch = None
+        self.cpad = 0           # internal channels per group, padded up to a multiple of 64 (see b200_plan)
 
     def b200_supported(self):
         p = self.param
@@ -173,13 +174,39 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         pad_ok = p.kernel_height - 1 - p.pad_y >= 0 and p.kernel_width - 1 - p.pad_x >= 0
         self.igemm_dgrad = (self.igemm_fwd and p.stride == 1 and ocg % 8 == 0 and pad_ok
                             and (p.kernel_height * p.kernel_width * ocg) // 8 <= 1024)
+        # Channel-padded groups: the im2col-mode TMA route fetches 64-channel chunks, and a layer with e.g. 48
+        # channels per group (AlexNet conv2) would otherwise build its patch operand with gather warps, which bound
+        # its forward and weight-gradient kernels.  Instead the filter's internal layout pads every tap to 64 channels
+        # with structural zeros and each group runs as a one-group convolution over a channel window that starts at
+        # the group's first channel: what the window reads beyond the group (the next group's channels, or zeros past
+        # the tensor) meets zero weights.  A third more MMA work, no gather instructions.  Stride-1 layers whose
+        # backward-data is the implicit kernel (it works on the unpadded filter) only.
+        b, c, h, w = self.nodes_in[0].shape
+        oh, ow = self.nodes_out[0].shape[2], self.nodes_out[0].shape[3]
+        cp = ops.round_up(icg, 64)
+        if (self.igemm_fwd and self.igemm_dgrad and not self.cin_pad and icg % 64 != 0 and icg % 8 == 0 and 2 * cp <= 3 * icg
+                and (p.kernel_height * p.kernel_width * cp) // 8 <= 1024 and c % 8 == 0
+                and max(p.pad_x, p.pad_y, p.kernel_width - 1 - p.pad_x, p.kernel_height - 1 - p.pad_y) <= 127
+                and (w + 2 * p.pad_x - p.kernel_width) // p.stride + 1 == ow
+                and (h + 2 * p.pad_y - p.kernel_height) // p.stride + 1 == oh
+                and os.environ.get("CXN_CONV_CPAD", "1") != "0"):
+            self.cpad = cp
         if self.pair:
             return (self.cin_pad, ops.round_up(self.nodes_in[0].shape[3], 2))
         return self.cin_pad
 
     def _icg(self):
+        """channels per group of the internal filter layout"""
         p = self.param
-        return self.cin_pad if self.cin_pad else p.num_input_channel // p.num_group
+        return self.cin_pad or self.cpad or p.num_input_channel // p.num_group
+
+    def _group_window(self, x, gi):
+        """(pointer, visible channels, row stride, image stride) of group gi's channel window (cpad layers)"""
+        p = self.param
+        b, c, h, w = x.shape
+        cin = p.num_input_channel // p.num_group
+        ld = x.act.ld
+        return x.act.ptr + 2 * gi * cin, p.num_input_channel - gi * cin, w * ld, h * w * ld
 
     def _kw2(self):
         return (self.param.kernel_width + 1) // 2
@@ -252,7 +279,8 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         self.ev_dy, self.ev_wg = torch.cuda.Event(), torch.cuda.Event()
         if self.igemm_dgrad:
             self.wflip_ld = ops.round_up(p.kernel_height * p.kernel_width * ocg, 8)
-            self.wflip = torch.zeros((g * icg * self.wflip_ld,), dtype=torch.bfloat16, device=ex.device)
+            self.wflip = torch.zeros((g * (p.num_input_channel // g if self.cpad else icg) * self.wflip_ld,),
+                                     dtype=torch.bfloat16, device=ex.device)
 
     def _im2col_args(self, x, y, rows, kpad):
         p = self.param
@@ -275,6 +303,16 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
                                             p.kernel_height, 1, p.stride | (1 << 16), p.pad_y, 0, y.shape[2], y.shape[3],
                                             y.act.ptr, y.act.ld, bias, 1 if self.fuse_relu else 0, 64, wp * 4, h * wp * 4,
                                             ops.stream()), "conv_fprop_view")
+            return
+        if self.cpad:
+            for gi in range(g):
+                ptr, cdim, rstride, istride = self._group_window(x, gi)
+                ops.check(L.cxn_conv_fprop_view(ptr, b, h, w, x.act.ld, self.cpad, 1, W.shadow.data_ptr() + 2 * gi * ocg * kpad,
+                                                kpad, ocg, p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x,
+                                                y.shape[2], y.shape[3], y.act.ptr + 2 * gi * ocg, y.act.ld,
+                                                (bias + 4 * gi * ocg) if bias is not None else None,
+                                                1 if self.fuse_relu else 0, cdim, rstride, istride, ops.stream()),
+                          "conv_fprop_view")
             return
         if self.igemm_fwd:
             gh, gw, gcs, gcg, gran, gkw, gstride, gpad_x = self._gather_args(x)
@@ -305,6 +343,16 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
                                             p.kernel_height, 1, p.stride | (1 << 16), p.pad_y, 0, y.shape[2], y.shape[3],
                                             W.g.data_ptr(), kg, 0, 64, 4 * p.kernel_width, 64, wp * 4, h * wp * 4,
                                             ops.stream()), "conv_wgrad_view")
+        elif self.cpad:
+            # the padding channels of every tap are structural zeros: their gradient (real values of the next group)
+            # must not accumulate (mask period / valid)
+            cin = p.num_input_channel // g
+            for gi in range(g):
+                ptr, cdim, rstride, istride = self._group_window(x, gi)
+                ops.check(L.cxn_conv_wgrad_view(ptr, b, h, w, x.act.ld, self.cpad, 1, gy.ptr + 2 * gi * ocg, gy.ld, ocg,
+                                                p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x, y.shape[2],
+                                                y.shape[3], W.g.data_ptr() + 4 * gi * ocg * kg, kg, 0, self.cpad, cin, cdim,
+                                                rstride, istride, ops.stream()), "conv_wgrad_view")
         elif self.igemm_fwd:
             gh, gw, gcs, gcg, gran, gkw, gstride, gpad_x = self._gather_args(x)
             # pair mode: the odd filter column is a structural zero - its gradient (real pixels!) must not accumulate
@@ -366,8 +414,13 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             return
         if self.igemm_dgrad:
             kh, kw = p.kernel_height, p.kernel_width
-            ops.check(L.cxn_conv_flip_weights(W.shadow.data_ptr(), self.wflip.data_ptr(), g, ocg, icg, kh, kw, kpad,
-                                              self.wflip_ld, ops.stream()), "flip_weights")
+            if self.cpad:
+                icg = p.num_input_channel // g      # backward-data works on the real channels of the group
+                ops.check(L.cxn_conv_flip_weights_pitch(W.shadow.data_ptr(), self.wflip.data_ptr(), g, ocg, icg, kh, kw, kpad,
+                                                        self.wflip_ld, self.cpad, ops.stream()), "flip_weights")
+            else:
+                ops.check(L.cxn_conv_flip_weights(W.shadow.data_ptr(), self.wflip.data_ptr(), g, ocg, icg, kh, kw, kpad,
+                                                  self.wflip_ld, ops.stream()), "flip_weights")
             ops.check(L.cxn_conv_fprop_masked(gy.ptr, b, y.shape[2], y.shape[3], gy.ld, ocg, g, 8, self.wflip.data_ptr(),
                                               self.wflip_ld, icg, kh, kw, 1, kh - 1 - p.pad_y, kw - 1 - p.pad_x, h, w,
                                               x.grad.ptr, x.grad.ld, x.act.ptr if self.mask_relu_in else None,

@@ -109,6 +109,10 @@ int cxn_conv_fprop_masked(const void* src, int N, int H, int W, int Cs, int Cg, 
                           void* y, long long ldy, const void* mask, cudaStream_t stream);
 int cxn_conv_flip_weights(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in, int ld_out,
                           cudaStream_t stream);
+/* The same from a filter whose taps are cpitch >= icg elements apart (channel-padded internal layout; the padding
+ * channels are not part of the backward-data problem).  No reference counterpart. */
+int cxn_conv_flip_weights_pitch(const void* w, void* wt, int G, int ocg, int icg, int KH, int KW, int ld_in, int ld_out,
+                                int cpitch, cudaStream_t st);
 /* experiment / tuning knobs of the implicit-GEMM convolution (0, or -1 for switches, = automatic):
  * key 0 row halves per forward tile (1|2), 1 ring stages, 2 unused,
  * 3 unused, 4 forward tile-width class (128|256), 5 timing-experiment bits,

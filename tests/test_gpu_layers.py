@@ -437,3 +437,88 @@ layer[+0] = softmax
             if s.shadow_off >= 0:
                 sh = fused.net.arena.shadow_view(s).view(s.rows, s.shadow_ld)[:, :s.cols]
                 assert torch.equal(sh, fused.net.arena.w_view(s).view(s.rows, s.cols).to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("cpad", ["1", "0"])
+def test_conv_channel_padded_groups(cpad, monkeypatch, tmp_path):
+    """48 channels per group (AlexNet conv2's shape class): the filter's internal layout pads every tap to 64 channels
+    and each group runs over a channel window through im2col-mode TMA (CXN_CONV_CPAD, default on) - forward, weight
+    gradient (the padding columns stay zero) and backward-data against the reference backend; the weights a user
+    sees, and a checkpoint, keep the unpadded layout"""
+    import io
+    from util import copy_weights, make_trainer
+    monkeypatch.setenv("CXN_CONV_CPAD", cpad)
+    body = """
+layer[+1] = conv:c1
+  kernel_size = 3
+  pad = 1
+  nchannel = 96
+layer[+1] = relu
+layer[+1] = conv:c2
+  kernel_size = 5
+  pad = 2
+  ngroup = 2
+  nchannel = 64
+layer[+1] = relu
+layer[+1] = conv:c3
+  kernel_size = 3
+  pad = 1
+  nchannel = 48
+layer[+1] = relu
+layer[+1] = conv:c4
+  kernel_size = 3
+  nchannel = 16
+layer[+1] = flatten
+layer[+1] = fullc:fc1
+  nhidden = 10
+layer[+0] = softmax
+"""
+    conf = _conf(body, 8, "8,11,10") + "eta = 0.01\nmomentum = 0.5\n"      # small steps: three updates stay comparable
+    _, ref, b2 = compare_backends(conf, make_batch((8, 8, 11, 10)), tol_grad=0.08, return_trainers=True)
+    convs = {c.layer.layer_index: c.layer for c in b2.net.connections if type(c.layer).__name__ == "ConvolutionLayer"}
+    pads = sorted(l.cpad for l in convs.values())
+    assert pads == ([0, 0, 64, 64] if cpad == "1" else [0, 0, 0, 0])       # c2 (2 x 48) and c4 (1 x 48)
+    # three training steps: the structural zeros stay zero; the visible weights follow the reference backend (bf16
+    # drift of a small deep net) and, closely, the same net in the other filter layout
+    monkeypatch.setenv("CXN_CONV_CPAD", "0" if cpad == "1" else "1")
+    twin = make_trainer(conf, dev="gpu:0", backend="b200")
+    monkeypatch.setenv("CXN_CONV_CPAD", cpad)
+    copy_weights(ref, b2)
+    copy_weights(ref, twin)
+    for s in range(3):
+        batch = make_batch((8, 8, 11, 10), seed=10 + s)
+        ref.update(batch)
+        b2.update(batch)
+        twin.update(batch)
+    for name in ("c2", "c4"):
+        wr, _ = ref.get_weight(name, "wmat")
+        wb, shape = b2.get_weight(name, "wmat")
+        wt, _ = twin.get_weight(name, "wmat")
+        assert wb.shape == wr.shape
+        assert rel_err_np(wr, wb) < 2e-2, name
+        assert rel_err_np(wt, wb) < 2e-2, name
+    if cpad == "1":
+        for l in convs.values():
+            if l.cpad:
+                p = l.param
+                cin = p.num_input_channel // p.num_group
+                w5 = l.bind["wmat"].w.view(-1, p.kernel_height, p.kernel_width, l.cpad)
+                assert float(w5[..., cin:].abs().max()) == 0.0
+                g5 = l.bind["wmat"].g.view(-1, p.kernel_height, p.kernel_width, l.cpad)
+                assert float(g5[..., cin:].abs().max()) == 0.0
+    # checkpoint round trip into the other layout
+    buf = io.BytesIO()
+    b2.save_model(buf)
+    monkeypatch.setenv("CXN_CONV_CPAD", "0" if cpad == "1" else "1")
+    other = make_trainer(conf, dev="gpu:0", backend="b200")
+    buf.seek(0)
+    other.load_model(buf)
+    for name in ("c2", "c4"):
+        wa, _ = b2.get_weight(name, "wmat")
+        wo, _ = other.get_weight(name, "wmat")
+        assert (wa == wo).all()
+
+
+def rel_err_np(a, b):
+    import numpy as np
+    return float(np.abs(a - b).sum() / max(np.abs(a).sum(), 1e-12))
