@@ -104,6 +104,70 @@ __global__ void nchw_u8_to_nhwc4_pitched_kernel(const uint8_t* __restrict__ src,
     *reinterpret_cast<uint4*>(dst + i * 8) = o;
   }
 }
+// C <= 4 into the space-to-depth layout the first convolution of a stride-4 net reads as a stride-1 convolution
+// over 64 channels: dst[n][Y][X][(dy*4 + dx)*4 + c] = src[n][c][4Y + dy][4X + dx] (zero for c >= C and past the
+// image).  One 4 x 4 block of pixels = 64 channels = one aligned 128-byte row of the patch operand.  One thread
+// converts the four pixels of one (block, dy): it reads 4 consecutive source pixels per channel and stores 32 bytes.
+// MODE 0: fp32 source, 1: bf16 source, 2: 8-bit source with (pixel - mean[c]) * scale.
+template <typename TS, bool NORM>
+__global__ void nchw_to_s2d4_kernel(const TS* __restrict__ src, bf16* __restrict__ dst, long long total, int C, int H,
+                                    int W, int Hs, int Ws, float m0, float m1, float m2, float m3, float scale) {
+  const float mean[4] = {m0, m1, m2, m3};
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    // i = ((n * Hs + Y) * 4 + dy) * Ws + X : neighbouring threads read neighbouring pixels of one source row
+    const int X = (int)(i % Ws);
+    long long r = i / Ws;
+    const int dy = (int)(r & 3);
+    r >>= 2;
+    const int Y = (int)(r % Hs);
+    const long long n = r / Hs;
+    const int y = 4 * Y + dy;
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = 0.f;
+    if (y < H) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        if (c < C) {
+          const TS* s = src + ((n * C + c) * H + y) * (long long)W + 4 * X;
+#pragma unroll
+          for (int dx = 0; dx < 4; ++dx)
+            if (4 * X + dx < W) {
+              float f;
+              if constexpr (NORM) f = ((float)s[dx] - mean[c]) * scale;
+              else f = ld_as_float(s + dx);
+              v[dx * 4 + c] = f;
+            }
+        }
+      }
+    }
+    uint4 o0, o1;
+    __nv_bfloat162* h0 = reinterpret_cast<__nv_bfloat162*>(&o0);
+    __nv_bfloat162* h1 = reinterpret_cast<__nv_bfloat162*>(&o1);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      h0[k] = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+      h1[k] = __floats2bfloat162_rn(v[8 + 2 * k], v[8 + 2 * k + 1]);
+    }
+    bf16* d = dst + (((n * Hs + Y) * (long long)Ws + X) * 64 + dy * 16);
+    *reinterpret_cast<uint4*>(d) = o0;
+    *reinterpret_cast<uint4*>(d + 8) = o1;
+  }
+}
+__device__ __forceinline__ float ld_as_float(const uint8_t* p) { return (float)*p; }
+
+// g[r][c] *= mask[c]: structural zeros of an internal filter layout must not collect a gradient
+__global__ void mask_cols_kernel(float* __restrict__ g, long long total, int cols, long long ld,
+                                 const float* __restrict__ mask) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cols;
+    const int c = (int)(i - r * cols);
+    if (mask[c] == 0.0f) g[r * ld + c] = 0.0f;
+  }
+}
+
 // src bf16 [N][HW][ldc] -> dst fp32 [N][C][HW]
 __global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ src, float* __restrict__ dst, int N, int C, int HW,
                                     int ldc) {
@@ -369,6 +433,33 @@ CXN_API int cxn_nchw_u8_to_nhwc4_pitched(const void* src, void* dst, int N, int 
   const long long total = (long long)N * H * (Wp / 2);
   nchw_u8_to_nhwc4_pitched_kernel<<<ew_grid(total, 256, 16), 256, 0, st>>>((const uint8_t*)src, (bf16*)dst, total, C, H, W,
                                                                            Wp, mean0, mean1, mean2, mean3, scale);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+// NCHW (C <= 4) -> space-to-depth NHWC bf16 [N][Hs][Ws][64], Hs = ceil(H / 4), Ws = ceil(W / 4); kind 0 fp32,
+// 1 bf16, 2 8-bit pixels normalised as (pixel - mean[c]) * scale.  See nchw_to_s2d4_kernel.
+CXN_API int cxn_nchw_to_s2d4(const void* src, int kind, void* dst, int N, int C, int H, int W, float mean0, float mean1,
+                             float mean2, float mean3, float scale, cudaStream_t st) {
+  if (N <= 0 || C <= 0 || H <= 0 || W <= 0) return 0;
+  if (C > 4 || kind < 0 || kind > 2 || (reinterpret_cast<uintptr_t>(dst) & 15)) return -1;
+  const int Hs = (H + 3) / 4, Ws = (W + 3) / 4;
+  const long long total = (long long)N * Hs * 4 * Ws;
+  const int grid = ew_grid(total, 256, 16);
+  if (kind == 0)
+    nchw_to_s2d4_kernel<float, false><<<grid, 256, 0, st>>>((const float*)src, (bf16*)dst, total, C, H, W, Hs, Ws, 0, 0, 0, 0, 1);
+  else if (kind == 1)
+    nchw_to_s2d4_kernel<bf16, false><<<grid, 256, 0, st>>>((const bf16*)src, (bf16*)dst, total, C, H, W, Hs, Ws, 0, 0, 0, 0, 1);
+  else
+    nchw_to_s2d4_kernel<uint8_t, true><<<grid, 256, 0, st>>>((const uint8_t*)src, (bf16*)dst, total, C, H, W, Hs, Ws, mean0,
+                                                             mean1, mean2, mean3, scale);
+  CXN_CHECK_LAUNCH();
+  return 0;
+}
+// g[r * ld + c] = 0 where mask[c] == 0 (rows x cols fp32)
+CXN_API int cxn_mask_cols_f32(float* g, long long rows, int cols, long long ld, const float* mask, cudaStream_t st) {
+  const long long total = rows * cols;
+  if (total <= 0) return 0;
+  mask_cols_kernel<<<ew_grid(total, 256, 8), 256, 0, st>>>(g, total, cols, ld, mask);
   CXN_CHECK_LAUNCH();
   return 0;
 }

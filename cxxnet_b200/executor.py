@@ -267,7 +267,9 @@ class NeuralNet:
             if c.native and hasattr(c.layer, "b200_plan") and c.type != nc.kSharedLayer:
                 x = c.nodes_in[0]
                 want = c.layer.b200_plan(self, x.index == 0, consumers.get(x.index, 0) == 1)
-                if isinstance(want, tuple):          # (channel pitch, row pitch in pixels)
+                if isinstance(want, tuple) and want[0] == "s2d":      # space-to-depth input node, 64 channels per block
+                    x.s2d, want = want[1], 64
+                elif isinstance(want, tuple):        # (channel pitch, row pitch in pixels)
                     want, x.wpitch = want
                 if want:
                     pitch[x.index] = want
@@ -288,6 +290,8 @@ class NeuralNet:
             if n.wpitch:
                 rows += 64     # zeroed slack: the last span of the last image row reads a few pixels past the image
             cols = w if n.is_mat else ch
+            if n.s2d:
+                rows, cols = self.max_batch * ((h + 3) // 4) * ((w + 3) // 4), 64
             ld = ops.round_up(cols, 8) if n.is_mat else pitch.get(n.index, cols)
             if self.tp is not None and n.index in self.tp.shard_nodes:
                 n.tp_rows = rows = self.tp.total_rows()
@@ -532,6 +536,10 @@ class NeuralNet:
         m = n.grad if grad else n.act
         if n.is_mat:
             return m.t[:b, :w].float().reshape(b, 1, 1, w)
+        if n.s2d:       # [b][Hs][Ws][dy][dx][4] -> [b][c][4 Hs][4 Ws], cropped
+            hs, ws = (h + 3) // 4, (w + 3) // 4
+            t = m.t[:b * hs * ws, :64].reshape(b, hs, ws, 4, 4, 4).permute(0, 5, 1, 3, 2, 4).reshape(b, 4, 4 * hs, 4 * ws)
+            return t[:, :c, :h, :w].float().contiguous()
         wp = n.wpitch or w
         return m.t[:b * h * wp, :c].reshape(b, h, wp, c)[:, :, :w].permute(0, 3, 1, 2).float().contiguous()
 
@@ -543,6 +551,11 @@ class NeuralNet:
         m = n.grad if grad else n.act
         if n.is_mat:
             m.t[:b, :w].copy_(t.reshape(b, w))
+        elif n.s2d:
+            hs, ws = (h + 3) // 4, (w + 3) // 4
+            full = torch.zeros((b, 4, 4 * hs, 4 * ws), dtype=t.dtype, device=t.device)
+            full[:, :c, :h, :w] = t
+            m.t[:b * hs * ws, :64].copy_(full.reshape(b, 4, hs, 4, ws, 4).permute(0, 2, 4, 3, 5, 1).reshape(b * hs * ws, 64))
         else:
             wp = n.wpitch or w
             m.t[:b * h * wp].reshape(b, h, wp, -1)[:, :, :w, :c].copy_(t.permute(0, 2, 3, 1))
@@ -646,6 +659,11 @@ class NeuralNet:
             src = self.in_stage_u8[slot][:b]
             _, c, h, w = n.shape
             mean, scale = self._norm(c)
+            if n.s2d:
+                m = list(mean) + [0.0] * (4 - len(mean))
+                ops.check(ops.lib().cxn_nchw_to_s2d4(src.data_ptr(), 2, n.act.ptr, b, c, h, w, m[0], m[1], m[2], m[3], scale,
+                                                     ops.stream()), "nchw_to_s2d4")
+                return
             if n.wpitch and not n.is_mat and hasattr(ops.lib(), "cxn_nchw_u8_to_nhwc4_pitched"):
                 m = list(mean) + [0.0] * (4 - len(mean))
                 ops.check(ops.lib().cxn_nchw_u8_to_nhwc4_pitched(src.data_ptr(), n.act.ptr, b, c, h, w, n.wpitch, m[0], m[1],
@@ -664,6 +682,11 @@ class NeuralNet:
             return
         if self.stage_dtype[slot] == torch.bfloat16:
             src = self.in_stage_bf16[slot][:b]
+            if n.s2d:
+                _, c, h, w = n.shape
+                ops.check(ops.lib().cxn_nchw_to_s2d4(src.data_ptr(), 1, n.act.ptr, b, c, h, w, 0.0, 0.0, 0.0, 0.0, 1.0,
+                                                     ops.stream()), "nchw_to_s2d4")
+                return
             if n.wpitch and not n.is_mat:
                 _, c, h, w = n.shape
                 ops.check(ops.lib().cxn_nchw_bf16_to_nhwc4_pitched(src.data_ptr(), n.act.ptr, b, c, h, w, n.wpitch,
@@ -686,6 +709,9 @@ class NeuralNet:
         L = ops.lib()
         if n.is_mat:
             ops.check(L.cxn_copy2d(st.data_ptr(), w, n.act.ptr, n.act.ld, b, w, 1, 0, ops.stream()), "copy2d")
+        elif n.s2d:
+            ops.check(L.cxn_nchw_to_s2d4(st.data_ptr(), 0, n.act.ptr, b, c, h, w, 0.0, 0.0, 0.0, 0.0, 1.0, ops.stream()),
+                      "nchw_to_s2d4")
         elif n.wpitch:
             ops.check(L.cxn_nchw_f32_to_nhwc4_pitched(st.data_ptr(), n.act.ptr, b, c, h, w, n.wpitch, ops.stream()),
                       "nchw_to_nhwc4_pitched")

@@ -29,7 +29,7 @@ from .. import model_io as mio
 class Node:
     """One activation node of the graph."""
 
-    __slots__ = ("shape", "data", "name", "index", "act", "grad", "f32", "alias_of", "loss_input", "wpitch", "tp_rows")
+    __slots__ = ("shape", "data", "name", "index", "act", "grad", "f32", "alias_of", "loss_input", "wpitch", "tp_rows", "s2d")
 
     def __init__(self, name: str = "", index: int = 0):
         self.shape: List[int] = [0, 0, 0, 0]  # (b, c, h, w)
@@ -43,6 +43,7 @@ class Node:
         self.alias_of = None
         self.loss_input = False
         self.wpitch = 0    # b200: pixels per stored image row when it differs from shape[3] (0 = dense)
+        self.s2d = 0       # b200: 4 = stored space-to-depth, [N][ceil(H/4)][ceil(W/4)][64] (cxn_nchw_to_s2d4)
         # b200, several ranks: > 0 when the node lives between two column-sharded fully connected layers and is stored
         # as [global batch = tp_rows][this rank's columns] instead of [batch slice][all columns] (parallel/tensor_parallel.py)
         self.tp_rows = 0

@@ -142,6 +142,8 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         self.dgrad_phases = False      # strided backward-data as stride*stride implicit-GEMM problems (cxn_conv_dgrad_strided)
         self.phase_scratch = None
         self.cpad = 0           # internal channels per group, padded up to a multiple of 64 (see b200_plan)
+        self.s2d = False        # stride-4 first layer over a space-to-depth input node (see b200_plan)
+        self.s2d_mask = None
 
     def b200_supported(self):
         p = self.param
@@ -170,6 +172,20 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             # fetches without a single gather instruction; filter columns kw..15 are structural zeros.
             self.span = (self.pair and p.kernel_width <= 16 and p.kernel_height <= 16
                          and os.environ.get("CXN_CONV_SPAN", "1") != "0")
+            # Space to depth: with stride 4 and no padding the layer is a STRIDE-1 convolution with a
+            # ceil(kh/4) x ceil(kw/4) filter over an image of 4 x 4 pixel blocks = 64 channels (4 per pixel).  A patch
+            # row is then one ALIGNED 128-byte line (a span starts every 32 bytes and straddles two lines, which is
+            # what bounds the span route: half the L2 -> SM rate of the aligned layers), the reduction shrinks from
+            # kh * 64 to ceil(kh/4) * ceil(kw/4) * 64, and the layer takes the ordinary im2col-TMA kernels.  Filter
+            # taps past the kh x kw window are structural zeros (masked out of the weight gradient).
+            b_, c_, h_, w_ = self.nodes_in[0].shape
+            k3h, k3w = (p.kernel_height + 3) // 4, (p.kernel_width + 3) // 4
+            self.s2d = (p.stride == 4 and p.pad_x == 0 and p.pad_y == 0 and k3h * k3w * 8 <= 1024
+                        and (h_ + 3) // 4 - k3h + 1 == self.nodes_out[0].shape[2]
+                        and (w_ + 3) // 4 - k3w + 1 == self.nodes_out[0].shape[3]
+                        and p.num_channel % 8 == 0 and os.environ.get("CXN_CONV_S2D", "1") != "0")
+            if self.s2d:
+                self.pair = self.span = False
         ocg = p.num_channel // g
         pad_ok = p.kernel_height - 1 - p.pad_y >= 0 and p.kernel_width - 1 - p.pad_x >= 0
         self.igemm_dgrad = (self.igemm_fwd and p.stride == 1 and ocg % 8 == 0 and pad_ok
@@ -191,6 +207,8 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
                 and (h + 2 * p.pad_y - p.kernel_height) // p.stride + 1 == oh
                 and os.environ.get("CXN_CONV_CPAD", "1") != "0"):
             self.cpad = cp
+        if self.s2d:
+            return ("s2d", 4)
         if self.pair:
             return (self.cin_pad, ops.round_up(self.nodes_in[0].shape[3], 2))
         return self.cin_pad
@@ -198,7 +216,13 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
     def _icg(self):
         """channels per group of the internal filter layout"""
         p = self.param
+        if self.s2d:
+            return 64
         return self.cin_pad or self.cpad or p.num_input_channel // p.num_group
+
+    def _k3(self):
+        """filter extent in 4 x 4 pixel blocks (space-to-depth layers)"""
+        return (self.param.kernel_height + 3) // 4, (self.param.kernel_width + 3) // 4
 
     def _group_window(self, x, gi):
         """(pointer, visible channels, row stride, image stride) of group gi's channel window (cpad layers)"""
@@ -220,6 +244,9 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             kg = 8 * p.kernel_height * self._kw2()
         if self.span:
             kg = 64 * p.kernel_height
+        if self.s2d:
+            k3h, k3w = self._k3()
+            kg = 64 * k3h * k3w
         return g, icg, p.num_channel // g, kg, ops.round_up(kg, 8)
 
     def _gather_args(self, x):
@@ -236,6 +263,12 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         p = self.param
         g, icg, ocg, kg, _ = self._geom()
         cin = p.num_input_channel // g
+        if self.s2d:
+            # (oc, c, kh, kw) -> (oc, ky, kx, dy, dx, c4) with kh = 4 ky + dy, kw = 4 kx + dx; zeros elsewhere
+            k3h, k3w = self._k3()
+            w4 = w.reshape(ocg, cin, p.kernel_height, p.kernel_width)
+            w4 = torch.nn.functional.pad(w4, (0, 4 * k3w - p.kernel_width, 0, 4 * k3h - p.kernel_height, 0, 4 - cin))
+            return w4.reshape(ocg, 4, k3h, 4, k3w, 4).permute(0, 2, 4, 3, 5, 1).reshape(1, ocg, kg)
         w5 = w.reshape(g, ocg, cin, p.kernel_height, p.kernel_width).permute(0, 1, 3, 4, 2)
         if icg != cin:
             w5 = torch.nn.functional.pad(w5, (0, icg - cin))
@@ -251,6 +284,10 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         p = self.param
         g, icg, ocg, kg, _ = self._geom()
         cin = p.num_input_channel // g
+        if self.s2d:
+            k3h, k3w = self._k3()
+            w4 = w.reshape(ocg, k3h, k3w, 4, 4, 4).permute(0, 5, 1, 3, 2, 4).reshape(ocg, 4, 4 * k3h, 4 * k3w)
+            return w4[:, :cin, :p.kernel_height, :p.kernel_width].reshape(1, ocg, cin * p.kernel_height * p.kernel_width)
         kw = 16 if self.span else (2 * self._kw2() if self.pair else p.kernel_width)
         w5 = w.reshape(g, ocg, p.kernel_height, kw, icg)[:, :, :, :p.kernel_width, :cin]
         return w5.permute(0, 1, 4, 2, 3).reshape(g, ocg, cin * p.kernel_height * p.kernel_width)
@@ -273,7 +310,11 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             self.dgrad_phases = True
             n = int(L.cxn_conv_dgrad_strided_scratch(g, ocg, icg, p.kernel_height, p.kernel_width, p.stride))
             self.phase_scratch = torch.zeros((max(n, 8),), dtype=torch.bfloat16, device=ex.device)
-        if (not self.igemm_fwd or not self.igemm_dgrad) and not (self.dgrad_phases and self.igemm_fwd):
+        if self.s2d:
+            # structural zeros of the internal layout, as a 0 / 1 row: applied to the weight gradient
+            ones = torch.ones((1, ocg, (p.num_input_channel // g) * p.kernel_height * p.kernel_width))
+            self.s2d_mask = self.weight_to_internal("wmat", ones)[0, 0].contiguous().to(ex.device, torch.float32)
+        elif (not self.igemm_fwd or not self.igemm_dgrad) and not (self.dgrad_phases and self.igemm_fwd):
             max_rows = ex.max_batch * y.shape[2] * y.shape[3]
             self.col = torch.empty((g * max_rows * kpad,), dtype=torch.bfloat16, device=ex.device)
         self.ev_dy, self.ev_wg = torch.cuda.Event(), torch.cuda.Event()
@@ -297,6 +338,12 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         W = self.bind["wmat"]
         bias = self.bind["bias"].w.data_ptr() if p.no_bias == 0 else None
         b, c, h, w = x.shape
+        if self.s2d:
+            k3h, k3w = self._k3()
+            ops.check(L.cxn_conv_fprop(x.act.ptr, b, (h + 3) // 4, (w + 3) // 4, 64, 64, 1, 8, W.shadow.data_ptr(), kpad, ocg,
+                                       k3h, k3w, 1, 0, 0, y.shape[2], y.shape[3], y.act.ptr, y.act.ld, bias,
+                                       1 if self.fuse_relu else 0, ops.stream()), "conv_fprop")
+            return
         if self.span:
             wp = x.wpitch
             ops.check(L.cxn_conv_fprop_view(x.act.ptr, b, h, y.shape[3], p.stride * 4, 64, 1, W.shadow.data_ptr(), kpad, ocg,
@@ -337,7 +384,13 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
         L = ops.lib()
         W = self.bind["wmat"]
         b, c, h, w = x.shape
-        if self.span:
+        if self.s2d:
+            k3h, k3w = self._k3()
+            ops.check(L.cxn_conv_wgrad(x.act.ptr, b, (h + 3) // 4, (w + 3) // 4, 64, 64, 1, 8, gy.ptr, gy.ld, ocg, k3h, k3w, 1,
+                                       0, 0, y.shape[2], y.shape[3], W.g.data_ptr(), kg, 0, ops.stream()), "conv_wgrad")
+            # filter taps outside the kh x kw window met real pixels: they are structural zeros and stay zero
+            ops.check(L.cxn_mask_cols_f32(W.g.data_ptr(), ocg, kg, kg, self.s2d_mask.data_ptr(), ops.stream()), "mask_cols")
+        elif self.span:
             wp = x.wpitch
             ops.check(L.cxn_conv_wgrad_view(x.act.ptr, b, h, y.shape[3], p.stride * 4, 64, 1, gy.ptr, gy.ld, ocg,
                                             p.kernel_height, 1, p.stride | (1 << 16), p.pad_y, 0, y.shape[2], y.shape[3],
@@ -434,8 +487,15 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
                                                x.grad.ld, None, self.phase_scratch.data_ptr(), ops.stream()), "conv_dgrad_strided")
             return
         # strided backward-data the explicit way: dcol = gy . W, then scatter
+        if self.col is None:      # (space-to-depth first layer: only an input-gradient request ever gets here)
+            self.col = torch.empty((g * ex.max_batch * y.shape[2] * y.shape[3] * kpad,), dtype=torch.bfloat16, device=ex.device)
         ops.gemm(gy.ptr, gy.ld, ocg, 0, W.shadow.data_ptr(), kpad, ocg * kpad, 1, self.col.data_ptr(), kpad,
                  rows * kpad, None, 0, rows, kg, ocg, batch=g, flags=ops.GEMM_OUT_BF16)
+        if self.s2d:
+            k3h, k3w = self._k3()
+            ops.check(L.cxn_col2im_nhwc(self.col.data_ptr(), x.grad.ptr, b, (h + 3) // 4, (w + 3) // 4, 64, 1, k3h, k3w, 1, 0, 0,
+                                        y.shape[2], y.shape[3], kpad, rows * kpad, ops.stream()), "col2im")
+            return
         # pair mode: (kh, kw2, 8) columns are (kh, 2*kw2, 4) in the pixel domain of the pitched image
         cw, ckw = (x.wpitch, 16 if self.span else 2 * self._kw2()) if self.pair else (w, p.kernel_width)
         ops.check(L.cxn_col2im_nhwc(self.col.data_ptr(), x.grad.ptr, b, h, cw, x.act.ld, p.num_group, p.kernel_height,

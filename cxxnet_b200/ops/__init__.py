@@ -82,6 +82,8 @@ def lib():
     _sig(L.cxn_conv_wgrad_view, [P, I, I, I, I, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, I, I, I, LL, LL, LL, P])
     _sig(L.cxn_conv_flip_weights, [P, P, I, I, I, I, I, I, I, P])
     _sig(L.cxn_conv_flip_weights_pitch, [P, P, I, I, I, I, I, I, I, I, P])
+    _sig(L.cxn_nchw_to_s2d4, [P, I, P, I, I, I, I, F, F, F, F, F, P])
+    _sig(L.cxn_mask_cols_f32, [P, LL, I, LL, P, P])
     _sig(L.cxn_conv_dgrad_strided, [P, I, I, I, LL, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, P, P, P])
     _sig(L.cxn_conv_dgrad_strided_ok, [I, I, I, I, I])
     _sig(L.cxn_conv_wgrad_grid_cap, [I])

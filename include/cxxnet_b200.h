@@ -145,6 +145,15 @@ int cxn_col2im_nhwc(const void* col, void* dx, int N, int H, int W, int C, int G
 int cxn_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int N, int C, int HW, int ldc, cudaStream_t stream);
 /* C <= 4 input image -> NHWC bf16 with pixel pitch 4 and an even row pitch Wp >= W (pad pixels zero) */
 int cxn_nchw_f32_to_nhwc4_pitched(const float* src, void* dst, int N, int C, int H, int W, int Wp, cudaStream_t stream);
+/* NCHW input with C <= 4 -> the space-to-depth layout [N][ceil(H/4)][ceil(W/4)][64] (channel (dy*4 + dx)*4 + c of
+ * block (Y, X) = pixel (4Y + dy, 4X + dx), channel c; zero past the image and for c >= C): a stride-4 first layer reads
+ * it as a stride-1 convolution over 64 channels whose patch rows are aligned 128-byte lines.  kind: 0 fp32 source,
+ * 1 bf16, 2 8-bit pixels normalised as (pixel - mean[c]) * scale.  No reference counterpart (the reference unpacks
+ * patches of the NCHW tensor, src/layer/convolution_layer-inl.hpp:88-92). */
+int cxn_nchw_to_s2d4(const void* src, int kind, void* dst, int N, int C, int H, int W, float mean0, float mean1, float mean2,
+                     float mean3, float scale, cudaStream_t stream);
+/* g[r * ld + c] = 0 where mask[c] == 0: the structural zeros of an internal filter layout collect no gradient. */
+int cxn_mask_cols_f32(float* g, long long rows, int cols, long long ld, const float* mask, cudaStream_t stream);
 int cxn_nchw_bf16_to_nhwc4_pitched(const void* src, void* dst, int N, int C, int H, int W, int Wp, cudaStream_t stream);
 /* the same from 8-bit pixels, with the input normalisation (pixel - mean[c]) * scale applied in fp32 before the bf16
  * rounding (`input_dtype = u8` batches; no reference counterpart) */

@@ -76,6 +76,7 @@ def test_conv_first_layer_spans_and_pixel_pairs(k, stride, shape, span, monkeypa
     pitch-4 image are 64-channel positions fetched by im2col-mode TMA; span=0: pixel pairs (16-byte gather
     granules).  Either way the unused filter columns are structural zeros of the internal weight layout."""
     monkeypatch.setenv("CXN_CONV_SPAN", str(span))
+    monkeypatch.setenv("CXN_CONV_S2D", "0")        # (stride-4 layers would otherwise take the space-to-depth route)
     body = """
 layer[+1] = conv:cv1
   kernel_size = %d
@@ -522,3 +523,59 @@ layer[+0] = softmax
 def rel_err_np(a, b):
     import numpy as np
     return float(np.abs(a - b).sum() / max(np.abs(a).sum(), 1e-12))
+
+
+@pytest.mark.parametrize("k,shape", [(11, (3, 67, 67)), (8, (3, 64, 60)), (5, (1, 45, 43)), (11, (3, 227, 227))])
+def test_conv_first_layer_space_to_depth(k, shape, monkeypatch):
+    """stride-4 first layer over the space-to-depth input node ([N][H/4][W/4][64]): a stride-1 convolution with a
+    ceil(k/4)^2 filter through the ordinary im2col-TMA kernels - forward, weight gradient (taps outside the k x k
+    window stay zero), input gradient and the layout bridge of node 0, against the reference backend; 8-bit and bf16
+    batches convert to the same node contents as fp32 batches"""
+    body = """
+layer[+1] = conv:cv1
+  kernel_size = %d
+  stride = 4
+  nchannel = 24
+layer[+1] = relu
+layer[+1] = flatten
+layer[+1] = fullc:fc1
+  nhidden = 10
+layer[+0] = softmax
+""" % k
+    nb = 5 if shape[1] > 100 else 9
+    shp = "%d,%d,%d" % shape
+    errs, ref, b2 = compare_backends(_conf(body, nb, shp), make_batch((nb,) + shape), return_trainers=True, tol_grad=0.1)
+    layer = b2.net.connections[0].layer
+    assert layer.s2d and not layer.span and not layer.pair
+    node0 = b2.net.nodes[0]
+    assert node0.s2d == 4 and node0.act.ld == 64
+    # the structural zeros collected no gradient, the real taps did
+    k3 = (k + 3) // 4
+    g = layer.bind["wmat"].g.reshape(24, k3, k3, 4, 4, 4)          # (oc, ky, kx, dy, dx, c)
+    m = layer.s2d_mask.reshape(k3, k3, 4, 4, 4)
+    assert float((g * (1 - m)).abs().max()) == 0.0
+    assert float((g * m).abs().max()) > 0.0
+    assert int(m.sum()) == k * k * shape[0]
+    # node 0 through the bridge, and the 8-bit / bf16 conversions
+    import torch as T
+    from cxxnet_b200 import ops
+    x = make_batch((nb,) + shape).data
+    got = b2.net._node_load(node0)
+    assert T.equal(got.cpu(), x.to(T.bfloat16).float())
+    keep = node0.act.t.clone()
+    L = ops.lib()
+    xb = x.to(T.bfloat16).cuda()
+    node0.act.t.zero_()
+    ops.check(L.cxn_nchw_to_s2d4(xb.data_ptr(), 1, node0.act.ptr, nb, shape[0], shape[1], shape[2], 0.0, 0.0, 0.0, 0.0, 1.0,
+                                 ops.stream()), "s2d bf16")
+    assert T.equal(node0.act.t, keep)
+    u8 = T.randint(0, 256, (nb,) + shape, dtype=T.uint8)
+    mean = [100.0, 110.0, 120.0, 0.0]
+    ops.check(L.cxn_nchw_to_s2d4(u8.cuda().data_ptr(), 2, node0.act.ptr, nb, shape[0], shape[1], shape[2], mean[0], mean[1],
+                                 mean[2], mean[3], 0.01, ops.stream()), "s2d u8")
+    want = ((u8.float() - T.tensor(mean[:shape[0]]).view(1, -1, 1, 1)) * 0.01).to(T.bfloat16).float()
+    assert T.equal(b2.net._node_load(node0).cpu(), want)
+    # weights a user sees keep the reference layout
+    w, shape_w = b2.get_weight("cv1", "wmat")
+    wr, _ = ref.get_weight("cv1", "wmat")
+    assert w.shape == wr.shape
