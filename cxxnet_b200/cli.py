@@ -64,6 +64,12 @@ class LearnTask:
             return relaunch_per_device(argv, devs)
         self._init_distributed()
         self.init()
+        if self.net_trainer is not None and self.net_trainer.is_server:
+            # update_on_server = 1: this rank owns weights and updaters (parallel/ps_server.py) until the workers finish
+            stats = self.net_trainer.serve()
+            if not self.silent:
+                print("parameter server %d: %s" % (self.rank, stats))
+            return 0
         if not self.silent and self.rank == 0:
             print("initializing end, start working")
         if self.task in ("train", "finetune"):
@@ -78,6 +84,8 @@ class LearnTask:
             self.extract_node_name = self.extract_node_name or "top[-1]"
             self.output_format = 1
             self.task_extract_feature()
+        if self.net_trainer is not None:
+            self.net_trainer.finish()
         self.close()
         return 0
 
@@ -88,9 +96,11 @@ class LearnTask:
             if not dist.is_initialized():
                 kind, devs = parse_devices(self.device)
                 local = int(os.environ.get("LOCAL_RANK", "0"))
-                if kind == "gpu":
+                # a parameter-server run talks point to point through the host (its server ranks own no GPU)
+                ps = any(k == "update_on_server" and v.strip() == "1" for k, v in self.cfg)
+                if kind == "gpu" and not ps:
                     torch.cuda.set_device(devs[local] if local < len(devs) else local)
-                dist.init_process_group("nccl" if kind == "gpu" else "gloo")
+                dist.init_process_group("nccl" if kind == "gpu" and not ps else "gloo")
             self.rank = dist.get_rank()
 
     def set_param(self, name: str, val: str) -> None:
@@ -122,7 +132,8 @@ class LearnTask:
                 raise RuntimeError("Init: Cannot find models for continue training. "
                                    "Please specify it by model_in instead.")
             print("Init: Continue training from round %d" % self.start_counter)
-            self.create_iterators()
+            if not self.net_trainer.is_server:
+                self.create_iterators()
             return
         self.continue_training = 0
         if self.name_model_in == "NULL":
@@ -133,7 +144,8 @@ class LearnTask:
             self.copy_model()
         else:
             self.load_model()
-        self.create_iterators()
+        if not self.net_trainer.is_server:
+            self.create_iterators()
 
     def _model_path(self, counter: int) -> str:
         return "%s/%04d.model" % (self.name_model_dir, counter)
@@ -229,6 +241,8 @@ class LearnTask:
             else:
                 itcfg.append((name, val))
         world = int(os.environ.get("WORLD_SIZE", "1")) if "RANK" in os.environ else 1
+        if self.net_trainer is not None and self.net_trainer.ps_roles is not None:
+            world = self.net_trainer.ps_roles.num_workers        # parameter-server run: the workers share the data
         for it in [self.itr_train, self.itr_pred] + self.itr_evals:
             if it is not None:
                 for k, v in defcfg:

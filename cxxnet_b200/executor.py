@@ -427,7 +427,7 @@ class NeuralNet:
         if self.world_size > 1 and self.exchange_kind == "collective":
             from .parallel.dist_exchange import CollectiveExchange
             self.exchange = CollectiveExchange(self)
-        elif self.world_size > 1:
+        elif self.world_size > 1 and self.exchange_kind != "server":
             from .parallel.exchange import GradExchange
             self.exchange = GradExchange(self)
 
@@ -784,7 +784,10 @@ class NeuralNet:
                 c.layer.backprop(i != 0 or prop_to_input, c.nodes_in, c.nodes_out)
                 if tm:
                     tm.end("b", i, t0)
-                if need_update:
+                if need_update and self.exchange is not None:
+                    # parameter-server run (parallel/ps_server.py): the gradient goes to the server, which updates
+                    self.exchange.layer_done(i)
+                elif need_update:
                     for u in self.updaters[i]:
                         if self.world_size > 1:
                             # reference-backend data parallelism: plain sum over ranks (gloo / nccl)

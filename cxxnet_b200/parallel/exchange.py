@@ -54,6 +54,7 @@ class GradExchange:
         import os
         import torch.distributed as dist
         self.net = net
+        self._fuse_gather = os.environ.get("CXN_FUSE_UPDATE_GATHER", "0") == "1"
         self.arena = net.arena
         self.rank, self.world = net.rank, net.world_size
         self.device = net.device
@@ -236,8 +237,10 @@ class GradExchange:
             acc = net.accumulate_grads
             # this step updates and nothing accumulates: the updater runs in the weight-gradient epilogue over the
             # owned rows (cxn_gemm_wgrad_update) - their gradient never reaches memory
-            fuse = bool(need_update and not acc and net.fuse_update and sh.my_rows > 0 and nin % 4 == 0
-                        and "fcgemm" not in self._skip)
+            # (opt-in here, CXN_FUSE_UPDATE_GATHER=1: on two GPUs the step was slower with it, 1.511-1.517 ms against
+            # 1.494 - this GEMM shares the SMs with the backward pass and the fused epilogue holds them longer)
+            fuse = bool(need_update and not acc and net.fuse_update and self._fuse_gather and sh.my_rows > 0
+                        and nin % 4 == 0 and "fcgemm" not in self._skip)
             if fuse:
                 e0 = sh.wseg.start + sh.row0 * nin
                 sld = sh.wseg.shadow_ld

@@ -81,6 +81,11 @@ class NetTrainer:
         # then only stages the batch and launches one graph per step
         self.cuda_graph = 0
         self.test_on_server = 0
+        self.update_on_server = 0
+        self.num_servers = 1
+        self.is_server = False
+        self.ps_roles = self.ps_group = self.ps_wgroup = self.ps_server = None
+        self.exchange_kind = "nvlink"
         self.check_nan = 0
         self.layer_timing = 0
         self.step_trace = int(os.environ.get("CXN_STEP_TRACE", "0"))
@@ -101,6 +106,11 @@ class NetTrainer:
         if name == "seed": self.seed = int(val)
         if name == "silent": self.silent = int(val)
         if name == "param_server": self.type_pserver = val
+        # param_server = dist with update_on_server = 1: asynchronous parameter server (parallel/ps_server.py) - the
+        # last `num_servers` ranks own the weights and the updaters, the others train (reference
+        # async_updater-inl.hpp:109-113, nnet_ps_server.cpp)
+        if name == "update_on_server": self.update_on_server = int(val)
+        if name == "num_servers": self.num_servers = int(val)
         if name == "backend": self.backend_override = val
         if name == "cuda_graph": self.cuda_graph = int(val)
         # reference async_updater-inl.hpp:148-153: replicate the weights on the server and assert equality every
@@ -114,7 +124,7 @@ class NetTrainer:
         # Parameter-server tuning keys of the reference (async_updater-inl.hpp:155-184, fullc_layer-inl.hpp) that
         # have nothing to act on here - there is no server, pulls are not deferred, arrays are not chunked by
         # the transport: accepted and ignored, like every key a consumer does not know.
-        #   pull_at_backprop, bigarray_bound, update_on_server, init_on_worker, force_contiguous
+        #   pull_at_backprop, bigarray_bound, init_on_worker, force_contiguous
         if name.startswith("metric"):
             m = re.match(r"metric\[([^,]+),([^\]]+)\]", name)
             if m:
@@ -145,6 +155,20 @@ class NetTrainer:
             # param_server = NONE keeps this trainer private to its process (no gradient exchange),
             # as in the reference when a single device is used (nnet_impl-inl.hpp:378-381)
             self.world_size, self.rank = dist.get_world_size(), dist.get_rank()
+        if self.type_pserver == "dist" and self.update_on_server:
+            from .parallel.ps_server import Roles
+            if self.ps_roles is None:
+                self.ps_roles = Roles(dist.get_world_size(), dist.get_rank(), self.num_servers)
+                # (group creation is collective: every rank, once, in this order.)  Requests and weights travel point
+                # to point on host tensors, whatever the job's default backend is; the workers keep a group of their
+                # own for the metric / prediction collectives - the servers are busy serving.
+                self.ps_group = dist.new_group(backend="gloo")
+                self.ps_wgroup = dist.new_group(ranks=list(range(self.ps_roles.num_workers)), backend="gloo")
+            self.exchange_kind = "server"
+            self.world_size = self.ps_roles.num_workers          # the batch is divided among the workers
+            self.is_server = self.ps_roles.is_server
+            if self.is_server:
+                self.dev_kind = "cpu"                            # a server's updaters run on the host, as the reference's
         if self.world_size > 1 and self.dev_kind == "gpu" and self.exchange_kind == "nvlink":
             from .parallel.dist_exchange import ranks_share_one_host
             # peer-mapped memory exists inside one machine only; CXN_EXCHANGE=collective selects the library
@@ -190,11 +214,14 @@ class NetTrainer:
         assert self.net is None, "net must be empty before this"
         self.net_cfg.configure(self.cfg)
         self._resolve_devices()
+        if self.is_server:
+            self._init_server()
+            return
         self.net = NeuralNet(self.net_cfg, self.step, self.rank + self.seed * 100, self.device, self.backend,
                              silent=self.silent or self.rank != 0, world_size=self.world_size, rank=self.rank,
                              exchange_kind=self.exchange_kind)
-        if self.world_size > 1 and self.exchange_kind == "collective":
-            self.cuda_graph = 0          # library collectives stay outside captured steps
+        if self.exchange_kind == "server" or (self.world_size > 1 and self.exchange_kind == "collective"):
+            self.cuda_graph = 0          # library collectives / server round trips stay outside captured steps
         if self.layer_timing:
             from .utils.timing import LayerTimer
             def names():
@@ -214,18 +241,59 @@ class NetTrainer:
                 self.eval_req.append(self.net_cfg.node_name_map[name])
 
     def _finish_init(self) -> None:
+        if self.is_server:
+            return
         self.net.init_updaters()
         self.net.init_nodes()
         if self.step_trace and self.net.backend == "b200":
             self.net.enable_trace()
+        if self.exchange_kind == "server":
+            from .parallel.ps_server import ServerExchange
+            ex = ServerExchange(self.net, self.ps_roles, self.ps_group, self.ps_wgroup)
+            self.net.exchange = ex            # (both backends: the executor reports finished layers to it)
+
+    # ------------------------------------------------------------------ parameter-server role
+    def _init_server(self) -> None:
+        """this rank is a server: no net, one CPU updater per key built from the configuration the workers read
+        (reference nnet_ps_server.cpp:59-82 InitModel)"""
+        from .parallel.ps_server import ParamServer
+        from .updaters import create_updater
+        cfg = self.net_cfg
+        tags = {0: "wmat", 1: "bias"}
+
+        def make_updater(key, w, dw):
+            li, tag = key // 4, tags.get(key % 4, "wmat")
+            if li >= len(cfg.layers):
+                raise RuntimeError("parameter server: key %d names layer %d of a net with %d layers" % (key, li, len(cfg.layers)))
+            u = create_updater(cfg.updater_type, w, dw, tag)
+            for k, v in list(cfg.defcfg) + list(cfg.layercfg[li]):
+                u.set_param(k, v)
+            u.param.silent = 1
+            u.init()
+            return u
+        self.ps_server = ParamServer(self.ps_roles, self.ps_group, make_updater)
+
+    def serve(self):
+        """server ranks: answer the workers until all of them have finished; returns the request counts"""
+        assert self.is_server and self.ps_server is not None, "serve() is for the server ranks of update_on_server = 1"
+        return self.ps_server.serve()
+
+    def finish(self) -> None:
+        """end of the job: a worker of a parameter-server run tells the servers it is done"""
+        if self.exchange_kind == "server" and not self.is_server and self.net is not None and self.net.exchange is not None:
+            self.net.exchange.finish()
 
     # ------------------------------------------------------------------ model
     def init_model(self) -> None:
         self._init_net()
+        if self.is_server:
+            return
         if self.world_size > 1:
             # every rank draws the same initial weights (the reference serialises device 0's model
             # to the others, nnet_impl-inl.hpp:70-81); the exchange re-broadcasts rank 0's arena.
             self.net.rng.manual_seed(self.seed * 100)
+        if self.is_server:
+            return
         self.net.init_model()
         self._finish_init()
         if self.net.exchange is not None:
@@ -244,13 +312,19 @@ class NetTrainer:
         self.net = None
         self._init_net()
         blob = mio.read_bytes(fi)
+        if self.is_server:
+            return
         self.net.load_model(io.BytesIO(blob))
         self._finish_init()
+        if self.exchange_kind == "server":
+            self.net.exchange.broadcast_weights(force=True)      # the servers take the loaded weights
 
     def copy_model_from(self, fi: BinaryIO) -> None:
         """finetune: copy layers whose names match (reference ``nnet_impl-inl.hpp:101-134``)."""
         self.net = None
         self.init_model()
+        if self.is_server:
+            return
         old_cfg = NetConfig()
         old_cfg.load_net(fi)
         mio.read_i64(fi)
@@ -265,6 +339,8 @@ class NetTrainer:
                     old_net.connections[i].layer.save_model(buf)
                     buf.seek(0)
                     self.net.copy_layer(j, buf)
+        if self.exchange_kind == "server":
+            self.net.exchange.broadcast_weights(force=True)
 
     def find_non_finite(self):
         """(layer name, tag) of the first weight tensor holding a NaN or an infinity, else None"""
@@ -520,6 +596,10 @@ class NetTrainer:
         full = torch.zeros((self.world_size * self.step,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
         pad = torch.zeros((self.step,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
         pad[: t.shape[0]] = t
+        if self.ps_wgroup is not None:       # parameter-server run: the workers' own (gloo) group, through the host
+            parts = [torch.zeros_like(pad, device="cpu") for _ in range(self.world_size)]
+            dist.all_gather(parts, pad.cpu(), group=self.ps_wgroup)
+            return torch.cat(parts)[:total].to(t.device)
         dist.all_gather_into_tensor(full, pad)
         return full[:total]
 
@@ -580,7 +660,12 @@ class NetTrainer:
             s = e.sum_metric if e.sum_metric is not None else torch.zeros((), dtype=torch.float64, device=self.device)
             v = torch.stack([s.to(self.device).double(), torch.tensor(float(e.cnt_inst), dtype=torch.float64,
                                                                        device=self.device)])
-            dist.all_reduce(v)
+            if self.ps_wgroup is not None:
+                vc = v.cpu()
+                dist.all_reduce(vc, group=self.ps_wgroup)
+                v = vc.to(self.device)
+            else:
+                dist.all_reduce(v)
             if e.sum_metric is not None:
                 e.sum_metric.copy_(v[0])          # in place: a captured training step accumulates into this tensor
             else:
