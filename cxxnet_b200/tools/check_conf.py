@@ -19,7 +19,7 @@ TASK = """task dev model_in model_dir continue start_counter num_round max_round
 extract_node_name output_format net_type reset_net_type data eval pred iter""".split()
 TRAINER = """batch_size update_period eval_train seed param_server metric backend cuda_graph test_on_server layer_timing step_trace
 input_shape updater sync netconfig extra_data_num label_vec extra_data_shape check_nan
-pull_at_backprop bigarray_bound update_on_server init_on_worker force_contiguous fullc_gather fullc_shard""".split()
+pull_at_backprop bigarray_bound update_on_server num_servers init_on_worker force_contiguous fullc_gather fullc_shard""".split()
 LAYER = """init_sigma init_uniform init_bias init_sparse random_type nhidden nchannel ngroup kernel_size kernel_height
 kernel_width stride pad pad_y pad_x no_bias temp_col_max algo threshold local_size alpha beta knorm b lb ub calm_start
 calm_end keep init_slope random_slope random eps fixconn_weight target grad_scale""".split()
