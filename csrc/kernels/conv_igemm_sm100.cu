@@ -72,6 +72,8 @@ struct Params {
   // optional strided view for the im2col tensor map (elements; 0 = the dense NHWC tensor): channel
   // extent per position, row stride, image stride.  Cs stays the stride between positions.
   long long view_cdim, view_row, view_img;
+  int Cgs;         // channels between the first channels of consecutive groups: Cg, or less when a view's groups are
+                   // channel windows padded up to a multiple of 64 (cxn_conv_view_group_stride)
   // optional strided view of the OUTPUT (fprop only; 0 = rows are consecutive): GEMM row r = (image, j, i) of an
   // o_h x o_w grid lands at element o_base + image * o_img + j * o_row + i * o_pix (+ group / column offsets).  Used by
   // backward-data of strided convolutions: each stride phase is a stride-1 problem whose results interleave in dx.
@@ -267,7 +269,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
             const int tap = n0 / p.Cg, c0 = n0 - tap * p.Cg;
             wg_kh[a] = tap / p.KW;
             wg_kw[a] = tap - wg_kh[a] * p.KW;
-            wg_c[a] = g * p.Cg + c0;
+            wg_c[a] = g * p.Cgs + c0;
           }
           const long long pix0 = (long long)kb0 * BK;
           wg_n = (int)(pix0 / ohw);
@@ -289,7 +291,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
               if (tx) mbar_expect_tx(full_bar(stage), tx); else mbar_arrive(full_bar(stage));
               if (ATMA) {
                 // A = patches: BMT output positions x 64 channels through tap (kh, kw)
-                tma_load_im2col_4d(sa, &tmPatch, full_bar(stage), g * p.Cg + fp_chunk * 64, pw, ph, pn, fp_kw, fp_kh);
+                tma_load_im2col_4d(sa, &tmPatch, full_bar(stage), g * p.Cgs + fp_chunk * 64, pw, ph, pn, fp_kw, fp_kh);
               }
               // B = W[g] : K-major box {64 (k), bn (n)}
               if (!bres) tma_load_3d(sb, &tmDense, full_bar(stage), pk * BK, n_blk * p.bn, g);
@@ -437,7 +439,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
       int n_blk, m_blk, split, g;
       decode_tile(t, n_blk, m_blk, split, g);
       const int kb0 = split * kbps, kb1 = min(num_kb, kb0 + kbps);
-      const bf16* gsrc = p.src + (long long)g * p.Cg;
+      const bf16* gsrc = p.src + (long long)g * p.Cgs;
       const long long tset = prof_on ? clock64() : 0;
       if (!WGRAD) {
         // A tile: MH halves of 128 output pixels x 64 reduction elements; warp wl owns rows
@@ -801,7 +803,7 @@ conv_fprop_cluster_kernel(const __grid_constant__ CUtensorMap tmHalf, const __gr
           mbar_expect_tx(full_bar(stage), (uint32_t)C::kABytes + (uint32_t)p.bn * BK * 2);
           const int tap = kb / cpk, chunk = kb - tap * cpk;
           const int kh = tap / p.KW, kw = tap - kh * p.KW;
-          tma_load_im2col_4d(sa, &tmPatch, full_bar(stage), g * p.Cg + chunk * 64, pw, ph, pn, kw, kh);
+          tma_load_im2col_4d(sa, &tmPatch, full_bar(stage), g * p.Cgs + chunk * 64, pw, ph, pn, kw, kh);
           tma_load_3d_mc(sb + crank * (uint32_t)half_rows * 128u, &tmHalf, full_bar(stage), kb * BK,
                          n_blk * p.bn + (int)crank * half_rows, g, (uint16_t)0x3);
         }
@@ -1034,7 +1036,7 @@ conv_fprop_pair_kernel(const __grid_constant__ CUtensorMap tmHalf, const __grid_
         const uint32_t sb = sa + kABytes;
         if (elect_one()) {
           if (leader) mbar_expect_tx(full_bar(stage), 2u * ((uint32_t)kABytes + (uint32_t)half_rows * BK * 2));
-          tma_load_im2col_4d_2cta(sa, &tmPatch, full_bar(stage), g * p.Cg + chunk * 64, pw, ph, pn, kw, kh);
+          tma_load_im2col_4d_2cta(sa, &tmPatch, full_bar(stage), g * p.Cgs + chunk * 64, pw, ph, pn, kw, kh);
           tma_load_3d_2cta(sb, &tmHalf, full_bar(stage), kb * BK, n_blk * p.bn + (int)crank * half_rows, g);
         }
         if (++chunk == cpk) {       // next 64-channel chunk of the tap, then the next tap (no divisions in this loop)
@@ -1288,7 +1290,7 @@ conv_fprop_halo_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid
         int n, ti, g;
         decode_tile(t, n, ti, g);
         mbar_expect_tx(fulla(s), (uint32_t)(64 * hg.wp * hg.patch_h * 2));
-        tma_load_4d(a_base + (uint32_t)s * hg.a_stage_bytes, &tmTile, fulla(s), g * p.Cg + chunk * 64, -p.pad_x,
+        tma_load_4d(a_base + (uint32_t)s * hg.a_stage_bytes, &tmTile, fulla(s), g * p.Cgs + chunk * 64, -p.pad_x,
                     ti * rows_tile - p.pad_y, n);
       }
       __syncwarp();
@@ -1563,8 +1565,8 @@ static bool atma_ok(const Params& p) {
   if (p.W + 2 * p.pad_x < p.KW || p.H + 2 * p.pad_y < p.KH) return false;
   if ((reinterpret_cast<uintptr_t>(p.src) & 15) || (p.Cs % 8)) return false;
   // (a view of ONE group may expose fewer channels than its last 64-channel chunk: the tensor map zero-fills the rest)
-  if (p.view_cdim && ((p.view_row % 8) || (p.view_img % 8) || (p.view_cdim % 8) ||
-                      (p.view_cdim < p.G * p.Cg && (p.G != 1 || p.view_cdim + 63 < p.Cg))))
+  if (p.view_cdim && ((p.view_row % 8) || (p.view_img % 8) || (p.view_cdim % 8) || (p.Cgs % 8) ||
+                      p.view_cdim + 63 < (long long)(p.G - 1) * p.Cgs + p.Cg))
     return false;
   return get_encode_im2col() != nullptr;
 }
@@ -1648,6 +1650,7 @@ static int launch_pair(const CUtensorMap& tm_half, const CUtensorMap& tmp, const
   CXN_CHECK_LAUNCH();
   return 0;
 }
+static thread_local int t_view_gstride = 0;   // group stride of the NEXT *_view call of this thread (cxn_conv_view_group_stride)
 static int g_tune_pair = -1;       // 1: CTA pairs (cta_group::2) for forward problems on the im2col-TMA route with
                                    // more than 128 output columns per group; -1 = read CXN_CONV_PAIR2
 static int pair_mode() {
@@ -1782,6 +1785,8 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   memset(&p, 0, sizeof(p));
   p.view_cdim = view_cdim; p.view_row = view_row; p.view_img = view_img;
   p.src = (const bf16*)src; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
+  p.Cgs = (view_cdim > 0 && t_view_gstride > 0) ? t_view_gstride : Cg;
+  t_view_gstride = 0;
   p.stride_y = stride & 0xFFFF; p.stride_x = (stride >> 16) ? (stride >> 16) : p.stride_y; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
   p.gran = gran; p.Ng = Ng; p.D = y; p.ldd = ldy; p.strideD = Ng; p.bias = bias; p.relu = relu;
   p.mask = (const bf16*)mask;
@@ -1921,7 +1926,7 @@ CXN_API int cxn_conv_halo_plan(int N, int H, int W, int Cs, int Cg, int G, int N
   Params p;
   memset(&p, 0, sizeof(p));
   static bf16 aligned_dummy[8] __attribute__((aligned(16)));
-  p.src = aligned_dummy; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
+  p.src = aligned_dummy; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.Cgs = Cg; p.KH = KH; p.KW = KW;
   p.stride_y = p.stride_x = stride; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
   p.gran = 8; p.Ng = Ng;
   p.bn = pick_bn(Ng, Ng > 128 ? 256 : 128);
@@ -1977,6 +1982,8 @@ static int conv_wgrad_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   if (mask_period && ((mask_period | mask_valid) & 3)) return -16;
   p.mask_period = mask_period; p.mask_valid = mask_valid;
   p.src = (const bf16*)src; p.N = N; p.H = H; p.W = W; p.Cs = Cs; p.Cg = Cg; p.KH = KH; p.KW = KW;
+  p.Cgs = (view_cdim > 0 && t_view_gstride > 0) ? t_view_gstride : Cg;
+  t_view_gstride = 0;
   p.stride_y = stride & 0xFFFF; p.stride_x = (stride >> 16) ? (stride >> 16) : p.stride_y; p.pad_y = pad_y; p.pad_x = pad_x; p.OH = OH; p.OW = OW; p.G = G; p.Kg = KH * KW * Cg;
   p.gran = gran; p.Ng = Ng; p.D = dw; p.ldd = lddw; p.strideD = (long long)Ng * lddw; p.bias = nullptr; p.relu = 0;
   int rc = check_geom(p);
@@ -2184,6 +2191,15 @@ CXN_API int cxn_conv_dgrad_strided(const void* dy, int N, int OH, int OW, long l
 // previous value.  The kernels here are persistent with one CTA per SM; a weight gradient launched beside a
 // backward-data problem that fills only part of the GPU (small per-GPU batches) takes the remaining SMs, and the two
 // run side by side instead of one after the other.
+// The next cxn_conv_fprop_view / cxn_conv_wgrad_view call of this thread reads group g's channels from channel
+// g * stride on (instead of g * Cg): groups as overlapping channel windows, each padded up to a multiple of 64 channels
+// that meet structural zeros of the filter (AlexNet conv2: Cg = 64, stride = 48).  One launch for all groups.
+CXN_API int cxn_conv_view_group_stride(int stride) {
+  if (stride < 0 || (stride % 8)) return -1;
+  t_view_gstride = stride;
+  return 0;
+}
+
 CXN_API int cxn_conv_wgrad_grid_cap(int ctas) {
   const int prev = t_wgrad_cap;
   t_wgrad_cap = ctas < 0 ? 0 : ctas;

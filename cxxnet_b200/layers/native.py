@@ -352,14 +352,13 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
                                             ops.stream()), "conv_fprop_view")
             return
         if self.cpad:
-            for gi in range(g):
-                ptr, cdim, rstride, istride = self._group_window(x, gi)
-                ops.check(L.cxn_conv_fprop_view(ptr, b, h, w, x.act.ld, self.cpad, 1, W.shadow.data_ptr() + 2 * gi * ocg * kpad,
-                                                kpad, ocg, p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x,
-                                                y.shape[2], y.shape[3], y.act.ptr + 2 * gi * ocg, y.act.ld,
-                                                (bias + 4 * gi * ocg) if bias is not None else None,
-                                                1 if self.fuse_relu else 0, cdim, rstride, istride, ops.stream()),
-                          "conv_fprop_view")
+            # all groups in one launch: group g reads the 64-channel chunks of the window that starts at channel g * cin
+            ptr, cdim, rstride, istride = self._group_window(x, 0)
+            ops.check(L.cxn_conv_view_group_stride(p.num_input_channel // g), "group_stride")
+            ops.check(L.cxn_conv_fprop_view(ptr, b, h, w, x.act.ld, self.cpad, g, W.shadow.data_ptr(), kpad, ocg,
+                                            p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x, y.shape[2], y.shape[3],
+                                            y.act.ptr, y.act.ld, bias, 1 if self.fuse_relu else 0, cdim, rstride, istride,
+                                            ops.stream()), "conv_fprop_view")
             return
         if self.igemm_fwd:
             gh, gw, gcs, gcg, gran, gkw, gstride, gpad_x = self._gather_args(x)
@@ -400,12 +399,12 @@ class ConvolutionLayer(zoo.ConvolutionLayer):
             # the padding channels of every tap are structural zeros: their gradient (real values of the next group)
             # must not accumulate (mask period / valid)
             cin = p.num_input_channel // g
-            for gi in range(g):
-                ptr, cdim, rstride, istride = self._group_window(x, gi)
-                ops.check(L.cxn_conv_wgrad_view(ptr, b, h, w, x.act.ld, self.cpad, 1, gy.ptr + 2 * gi * ocg, gy.ld, ocg,
-                                                p.kernel_height, p.kernel_width, p.stride, p.pad_y, p.pad_x, y.shape[2],
-                                                y.shape[3], W.g.data_ptr() + 4 * gi * ocg * kg, kg, 0, self.cpad, cin, cdim,
-                                                rstride, istride, ops.stream()), "conv_wgrad_view")
+            ptr, cdim, rstride, istride = self._group_window(x, 0)
+            ops.check(L.cxn_conv_view_group_stride(cin), "group_stride")
+            ops.check(L.cxn_conv_wgrad_view(ptr, b, h, w, x.act.ld, self.cpad, g, gy.ptr, gy.ld, ocg, p.kernel_height,
+                                            p.kernel_width, p.stride, p.pad_y, p.pad_x, y.shape[2], y.shape[3],
+                                            W.g.data_ptr(), kg, 0, self.cpad, cin, cdim, rstride, istride, ops.stream()),
+                      "conv_wgrad_view")
         elif self.igemm_fwd:
             gh, gw, gcs, gcg, gran, gkw, gstride, gpad_x = self._gather_args(x)
             # pair mode: the odd filter column is a structural zero - its gradient (real pixels!) must not accumulate

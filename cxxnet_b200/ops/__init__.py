@@ -87,6 +87,7 @@ def lib():
     _sig(L.cxn_conv_dgrad_strided, [P, I, I, I, LL, I, I, P, LL, I, I, I, I, I, I, I, I, P, LL, P, P, P])
     _sig(L.cxn_conv_dgrad_strided_ok, [I, I, I, I, I])
     _sig(L.cxn_conv_wgrad_grid_cap, [I])
+    _sig(L.cxn_conv_view_group_stride, [I])
     L.cxn_conv_dgrad_strided_scratch.argtypes = [I, I, I, I, I, I]
     L.cxn_conv_dgrad_strided_scratch.restype = c_longlong
     _sig(L.cxn_conv_tune, [I, I])

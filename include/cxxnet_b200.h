@@ -73,6 +73,11 @@ int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg, int G, 
  * returns the previous limit.  For running a weight gradient on one stream beside a backward-data problem that fills
  * only part of the GPU on another (both kernels are persistent, one CTA per SM).  No reference counterpart. */
 int cxn_conv_wgrad_grid_cap(int ctas);
+/* The next cxn_conv_fprop_view / cxn_conv_wgrad_view call of the calling thread takes group g's channels from channel
+ * g * stride on instead of g * Cg: groups as overlapping channel windows, each padded up to a multiple of 64 channels
+ * that meet structural zeros of the filter (channel-padded groups; one launch for all groups).  stride % 8 == 0.
+ * No reference counterpart. */
+int cxn_conv_view_group_stride(int stride);
 long long cxn_conv_dgrad_strided_scratch(int G, int ocg, int icg, int KH, int KW, int stride);
 int cxn_conv_dgrad_strided_ok(int KH, int KW, int stride, int pad_y, int pad_x);
 int cxn_conv_dgrad_strided(const void* dy, int N, int OH, int OW, long long lddy, int ocg, int G, const void* w,
