@@ -17,7 +17,8 @@ one server are ordered; the server takes headers from ANY worker (``dist.recv`` 
 
 ==========  =====================================================================================================
 ``INIT``    first writer wins: the weights of ``key`` if the server has none yet (the reference's ``InitModel``,
-            ``nnet_ps_server.cpp:59-82``: "already inited" is not an error); flag = 1 overwrites (a loaded model)
+            ``nnet_ps_server.cpp:59-82``: "already inited" is not an error); flag = 1 overwrites (a loaded model).
+            Acknowledged with the header, so that the sender knows the key exists before it lets other workers ask
 ``PUSH``    gradient of ``key``: ``updater.update(epoch)`` at once (``nnet_ps_server.cpp:83-89``), reply = new weights
 ``PULL``    reply = current weights
 ``DONE``    this worker has finished; a server returns from ``serve()`` when every worker has said so
@@ -98,6 +99,12 @@ class ParamServer:
                 if fresh or int(header[3]) == 1:        # first writer wins, unless the worker insists (a loaded model)
                     w.copy_(buf)
                     self.stats["init"] += 1
+                # acknowledged: the sender may tell the other workers that the key exists only when it does (their
+                # requests travel on other connections, which this loop does not order against this one)
+                dist.send(header, dst=src, group=self.group)
+            elif key not in self.entries:
+                raise RuntimeError("parameter server %d: request %d from rank %d for key %d, which nobody has initialised"
+                                   % (self.roles.rank, op, src, key))
             elif op == OP_PUSH:
                 w, dw, upd = self._entry(key, numel)
                 dist.recv(dw, src=src, group=self.group)
@@ -131,6 +138,8 @@ class ServerClient:
         dst = self.roles.server_of(key)
         self._send_header(OP_INIT, key, w.numel(), dst, 1 if force else 0)
         dist.send(w, dst=dst, group=self.group)
+        ack = torch.zeros(4, dtype=torch.int64)
+        dist.recv(ack, src=dst, group=self.group)        # the server has the key now
 
     def push_pull(self, key: int, grad: torch.Tensor, out_w: torch.Tensor) -> None:
         """gradient up, weights after the server's update down"""

@@ -35,6 +35,8 @@ for name in ("fc1", "fc2"):
     for tag in ("wmat", "bias"):
         single.set_weight(tr.get_weight(name, tag)[0], name, tag)
 assert tr.net.exchange.check_replicas() == 0.0        # what this worker holds is what the servers hold
+if W > 1:
+    dist.barrier(group=tr.ps_wgroup)                  # (... as long as nobody has pushed yet)
 STEPS = 4
 for s in range(STEPS):
     b = make_batch((60, 1, 1, 784), seed=s)
