@@ -79,6 +79,13 @@ struct Params {
   // backward-data of strided convolutions: each stride phase is a stride-1 problem whose results interleave in dx.
   int o_w, o_hw;
   long long o_base, o_pix, o_row, o_img;
+  int o_vh, o_vw;  // valid extent of the view's grid (0 = all of it): positions outside are computed and discarded
+  // FLAT: stride-1 forward problem without padding computed over the INPUT's pixel grid (H x W instead of OH x OW):
+  // there a filter tap is a constant row offset, so a tile's patch rows through tap (kh, kw) are one contiguous 2-D box
+  // fetched in TILED mode at row m0 + kh * W + kw (im2col-mode fetches bound layers with few output columns,
+  // profiles/r2_experiments.md).  The rows with ow >= OW or oh >= OH read across row / image ends and are discarded by
+  // the epilogue through the output view above.
+  int flat;
   long long* prof; // [grid][16] cycle counters of the warp roles (builds with -DCXN_IGEMM_PROF only)
   int dbg;         // timing experiments only (results are garbage): 2 skip the TMA loads, 4 skip the MMAs
 };
@@ -146,7 +153,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const long long rows = (long long)p.N * p.OH * p.OW;
+  const long long rows = p.flat ? (long long)p.N * p.H * p.W : (long long)p.N * p.OH * p.OW;
 
   // GEMM view.  FPROP: M = rows (gathered), N = Ng, K = Kg.   WGRAD: M = Ng, N = Kg (gathered), K = rows.
   const long long gm = WGRAD ? p.Ng : rows;
@@ -202,6 +209,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
 
   const int cpk = p.Cg >> 6;   // 64-channel chunks per filter tap (ATMA)
 
+  // (all lanes of a warp poll: with one polling lane and the rest parked at the reconvergence point the AlexNet step was
+  // 2.242 ms instead of 2.202 - measured at the end of round 2)
   auto wait_bar = [&](uint32_t bar, uint32_t parity) { mbar_wait(bar, parity); };
   auto issue = [&]() -> bool { return UNI ? elect_one() : true; };   // UNI: all lanes run the loop, one issues
   // role profiling: cycles spent inside waits / phases, accumulated per CTA
@@ -289,7 +298,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
               uint32_t tx = bres ? 0u : (uint32_t)p.bn * BK * 2;
               if (ATMA) tx += (uint32_t)C::kABytes;
               if (tx) mbar_expect_tx(full_bar(stage), tx); else mbar_arrive(full_bar(stage));
-              if (ATMA) {
+              if (ATMA && p.flat) {
+                // A = BMT consecutive pixels of the input grid, shifted by the tap: one tiled-mode box
+                tma_load_3d(sa, &tmPatch, full_bar(stage), g * p.Cgs + fp_chunk * 64,
+                            (int)((long long)m_blk * BMT) + fp_kh * p.W + fp_kw, 0);
+              } else if (ATMA) {
                 // A = patches: BMT output positions x 64 channels through tap (kh, kw)
                 tma_load_im2col_4d(sa, &tmPatch, full_bar(stage), g * p.Cgs + fp_chunk * 64, pw, ph, pn, fp_kw, fp_kh);
               }
@@ -603,6 +616,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmDense, const __grid_cons
           const long long img = row / p.o_hw;
           const int rr = (int)(row - img * p.o_hw);
           const int jj = rr / p.o_w;
+          if (p.o_vw && (jj >= p.o_vh || rr - jj * p.o_w >= p.o_vw)) continue;     // outside the valid part of the grid
           pix_off = p.o_base + img * p.o_img + (long long)jj * p.o_row + (long long)(rr - jj * p.o_w) * p.o_pix;
         }
         const long long off = (long long)g * p.strideD + pix_off + n0;
@@ -1650,6 +1664,16 @@ static int launch_pair(const CUtensorMap& tm_half, const CUtensorMap& tmp, const
   CXN_CHECK_LAUNCH();
   return 0;
 }
+static int g_tune_flat = -1;       // forward problems without padding over the input's pixel grid with tiled-mode loads
+                                   // (Params::flat); -1 = CXN_CONV_FLAT, default 0
+static long long g_flat_launches = 0;      // forward launches that took the FLAT route (cxn_conv_flat_launches: tests)
+static int flat_mode() {
+  if (g_tune_flat < 0) {
+    const char* e = getenv("CXN_CONV_FLAT");
+    g_tune_flat = e ? atoi(e) : 0;
+  }
+  return g_tune_flat;
+}
 static thread_local int t_view_gstride = 0;   // group stride of the NEXT *_view call of this thread (cxn_conv_view_group_stride)
 static int g_tune_pair = -1;       // 1: CTA pairs (cta_group::2) for forward problems on the im2col-TMA route with
                                    // more than 128 output columns per group; -1 = read CXN_CONV_PAIR2
@@ -1798,7 +1822,22 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   }
   int rc = check_geom(p);
   if (rc) return rc;
-  const long long rows = (long long)N * OH * OW;
+  // FLAT route (see Params::flat): stride 1, no padding, few output columns per group (such layers are bound by the
+  // im2col-mode fetch rate), at most 15 % of discarded rows
+  bool flat = false;
+  if (flat_mode() && !oview && !p.view_cdim && gran == 8 && p.stride_x == 1 && p.stride_y == 1 && pad_x == 0 && pad_y == 0 &&
+      Ng <= 128 && (long long)H * W * 100 <= (long long)OH * OW * 115 && (long long)N * H * W < (1LL << 31) - 65536) {
+    bool atma_e = atma_ok(p);
+    if (g_tune_atma >= 0) atma_e = atma_e && g_tune_atma;
+    flat = atma_e;
+  }
+  if (flat) {
+    ++g_flat_launches;
+    p.flat = 1;
+    p.o_w = W; p.o_hw = H * W; p.o_base = 0; p.o_pix = ldy; p.o_row = (long long)OW * ldy; p.o_img = (long long)OH * OW * ldy;
+    p.o_vh = OH; p.o_vw = OW;
+  }
+  const long long rows = flat ? (long long)N * H * W : (long long)N * OH * OW;
   if (rows <= 0) return 0;
   // Tile shape: row-paired tiles (256 x <=128, two accumulators sharing the filter tile) when one
   // n-tile covers the group's outputs and there is enough work to fill the machine with them -
@@ -1862,11 +1901,15 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
   if (g_tune_atma >= 0 && !p.view_cdim) atma = atma && g_tune_atma;
   if (p.view_cdim && !atma) return -17;    // a strided view only exists as a tensor map
   CUtensorMap tmp = tm;
-  if (atma) {
+  if (atma && flat) {
+    rc = encode3d(&tmp, src, (uint64_t)Cs, (uint64_t)rows, 1, (uint64_t)Cs, (uint64_t)rows * Cs, 64, mh * BM);
+    if (rc) return rc;
+  } else if (atma) {
     rc = encode_im2col(&tmp, p, mh * BM);
     if (rc) return rc;
   }
-  if (halo_mode() > 0 && atma) {     // (takes precedence over the resident-filter variant when asked for)
+  if (flat && !atma) return -24;
+  if (halo_mode() > 0 && atma && !flat) {     // (takes precedence over the resident-filter variant when asked for)
     HaloGeom hg;
     int smem_h = 0;
     const int hmh = halo_mode() == 2 ? 1 : 2;
@@ -1879,7 +1922,7 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
       return hmh == 2 ? launch_halo<2>(tm, tmt, p, hg, smem_h, hgrid, st) : launch_halo<1>(tm, tmt, p, hg, smem_h, hgrid, st);
     }
   }
-  if (pair_mode() >= 1 && atma && !(p.bn & 15) && num_sms() >= 2 &&
+  if (pair_mode() >= 1 && atma && !flat && !(p.bn & 15) && num_sms() >= 2 &&
       (pair_mode() == 2 || (!p.b_resident && Ng > 128 && ceil_div_ll(rows, 2 * BM) * ceil_div(Ng, p.bn) * G >= num_sms() / 2))) {
     // CTA pairs: one 256-row x bn tile per pair, every CTA stages its own 128 positions and half of the filter tile
     Params pp = p;
@@ -1901,7 +1944,7 @@ static int conv_fprop_impl(const void* src, int N, int H, int W, int Cs, int Cg,
     return bnmax_p == 256 ? launch_pair<256>(tmh, tmp1, pp, grid_p, st) : launch_pair<128>(tmh, tmp1, pp, grid_p, st);
   }
   const long long tiles_m = ceil_div_ll(rows, mh * BM);
-  if (cluster_mode() == 2 && atma && !p.b_resident && tiles_m >= 2 && num_sms() >= 2 &&
+  if (cluster_mode() == 2 && atma && !flat && !p.b_resident && tiles_m >= 2 && num_sms() >= 2 &&
       memory_is_local(w, (size_t)G * (size_t)Ng * (size_t)ldw * sizeof(bf16))) {   // multicast map: own memory only
     // CTA pairs on two pixel tiles of the same output columns: each fetches half of the filter tile and
     // multicasts it to both (tensor map over this GPU's weights)
@@ -1966,6 +2009,7 @@ CXN_API int cxn_conv_tune(int key, int value) {
     case 8: g_tune_fill = value; break;
     case 9: g_tune_halo = value; break;
     case 10: g_tune_pair = value; break;
+    case 12: g_tune_flat = value; break;
     default: return -1;
   }
   return 0;
@@ -2199,6 +2243,9 @@ CXN_API int cxn_conv_view_group_stride(int stride) {
   t_view_gstride = stride;
   return 0;
 }
+
+// how many forward launches of this process took the FLAT route (Params::flat) so far
+CXN_API long long cxn_conv_flat_launches() { return g_flat_launches; }
 
 CXN_API int cxn_conv_wgrad_grid_cap(int ctas) {
   const int prev = t_wgrad_cap;

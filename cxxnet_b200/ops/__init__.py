@@ -88,6 +88,8 @@ def lib():
     _sig(L.cxn_conv_dgrad_strided_ok, [I, I, I, I, I])
     _sig(L.cxn_conv_wgrad_grid_cap, [I])
     _sig(L.cxn_conv_view_group_stride, [I])
+    L.cxn_conv_flat_launches.argtypes = []
+    L.cxn_conv_flat_launches.restype = c_longlong
     L.cxn_conv_dgrad_strided_scratch.argtypes = [I, I, I, I, I, I]
     L.cxn_conv_dgrad_strided_scratch.restype = c_longlong
     _sig(L.cxn_conv_tune, [I, I])

@@ -73,6 +73,11 @@ int cxn_conv_fprop(const void* src, int N, int H, int W, int Cs, int Cg, int G, 
  * returns the previous limit.  For running a weight gradient on one stream beside a backward-data problem that fills
  * only part of the GPU on another (both kernels are persistent, one CTA per SM).  No reference counterpart. */
 int cxn_conv_wgrad_grid_cap(int ctas);
+/* Number of forward launches of this process that took the FLAT route so far: a stride-1 problem without padding and with
+ * at most 128 output columns per group is computed over the INPUT's pixel grid, where a filter tap is a constant row
+ * offset and a tile's patch rows are one tiled-mode TMA box; rows outside the output are discarded (CXN_CONV_FLAT /
+ * cxn_conv_tune(12, v)).  For tests.  No reference counterpart. */
+long long cxn_conv_flat_launches(void);
 /* The next cxn_conv_fprop_view / cxn_conv_wgrad_view call of the calling thread takes group g's channels from channel
  * g * stride on instead of g * Cg: groups as overlapping channel windows, each padded up to a multiple of 64 channels
  * that meet structural zeros of the filter (channel-padded groups; one launch for all groups).  stride % 8 == 0.

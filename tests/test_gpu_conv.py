@@ -110,6 +110,29 @@ def test_conv_many_tiles_persistent():
     _case(64, 32, 32, 32, 64, 1, 3, 3, 1, 1)                    # 65536 rows: 512 m-tiles over 148 SMs
 
 
+def test_conv_flat_route_over_the_input_grid():
+    """cxn_conv_tune(12, 1): stride-1 forward problems without padding and with few output columns run over the
+    input's pixel grid - a tap is a constant row offset, a tile's patch rows one tiled-mode TMA box - and the rows
+    outside the output are discarded: same results as the im2col route, on shapes with row tails, groups, two
+    64-channel chunks per tap and 256-row tiles"""
+    from cxxnet_b200 import ops
+    L = ops.lib()
+    L.cxn_conv_tune(12, 1)
+    try:
+        n0 = L.cxn_conv_flat_launches()
+        _case(3, 64, 57, 57, 96, 1, 3, 3, 1, 0)                    # space-to-depth conv1's shape class
+        assert L.cxn_conv_flat_launches() == n0 + 1
+        _case(2, 128, 30, 29, 48, 2, 2, 2, 1, 0, relu=False)       # groups, 2 x 2 filter
+        _case(40, 128, 40, 40, 64, 1, 3, 3, 1, 0)                  # two chunks per tap; enough rows for 256-row tiles
+        _case(1, 64, 31, 33, 24, 1, 1, 1, 1, 0)                    # 1 x 1: the grid IS the output
+        assert L.cxn_conv_flat_launches() == n0 + 4
+        _case(2, 64, 12, 12, 32, 1, 3, 3, 1, 0)                    # 44 % of the rows would be discarded: im2col route
+        _case(2, 64, 20, 20, 32, 1, 3, 3, 1, 1)                    # padding: im2col route
+        assert L.cxn_conv_flat_launches() == n0 + 4
+    finally:
+        L.cxn_conv_tune(12, -1)
+
+
 @pytest.mark.parametrize("atma", [1, 0])
 def test_conv_im2col_tma_and_gather_routes_agree_with_reference(atma):
     """channels-per-group % 64 == 0 takes the im2col-mode TMA route by default; the same problems through the
