@@ -68,6 +68,8 @@ print("OK", rank)
 
 @pytest.mark.parametrize("workers,servers,extra,atol", [
     (1, 1, "wmat:wd = 0.01\nmomentum = 0.9\n", 1e-6),       # one worker: the server's updater IS the local one
+    (1, 1, "updater = nag\nwmat:wd = 0.01\nlr:schedule = expdecay\nlr:gamma = 0.5\nlr:step = 2\n", 1e-6),
+    (1, 1, "updater = adam\n", 1e-6),
     (2, 1, "momentum = 0\nwd = 0\n", 2e-6),                   # two workers, one server
     (2, 2, "momentum = 0\nwd = 0\n", 2e-6),                   # keys spread over two servers
 ])
@@ -76,7 +78,7 @@ def test_parameter_server_matches_local_training(tmp_path, workers, servers, ext
     script.write_text(WORKER % {"root": ROOT, "servers": servers, "extra": extra, "atol": atol})
     env = dict(os.environ)
     env["MASTER_ADDR"] = "127.0.0.1"
-    port = 29640 + workers * 3 + servers
+    port = 29640 + workers * 3 + servers + (5 if 'nag' in extra else 9 if 'adam' in extra else 0)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(workers + servers),
                         "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)], env=env,
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
