@@ -48,9 +48,10 @@ struct CxnioAugItem {
 static inline uint16_t F32ToBf16(float f) {
   uint32_t u;
   memcpy(&u, &f, 4);
-  if ((u & 0x7fffffffu) > 0x7f800000u) return uint16_t((u >> 16) | 0x40);      // NaN stays NaN
-  u += 0x7fffu + ((u >> 16) & 1u);                                              // round to nearest even
-  return uint16_t(u >> 16);
+  // (branch-free, so that the row loops vectorise: both results are computed and one is selected)
+  const uint32_t nan = (u >> 16) | 0x40u;                                       // NaN stays NaN
+  const uint32_t rne = (u + 0x7fffu + ((u >> 16) & 1u)) >> 16;                  // round to nearest even
+  return uint16_t((u & 0x7fffffffu) > 0x7f800000u ? nan : rne);
 }
 
 #if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__) && !defined(CXNIO_NO_CLONES)
@@ -59,8 +60,46 @@ static inline uint16_t F32ToBf16(float f) {
 #define CXNIO_CLONES
 #endif
 
+extern "C++" {
+// One row of one channel: W outputs.  MODE = mean_mode, DST = 0 fp32 / 1 bf16 / 2 8-bit, FLIP = mirrored read.  All
+// per-instance decisions are template parameters, so the loop body is straight-line code the compiler vectorises
+// (it was one loop with the branches inside: 0.42 ms per 3 x 227 x 227 instance, 0.8 ms with bf16 output).
+// The arithmetic and its order are those of the NumPy path: ((v - mean) * contrast + illum) * scale, single precision,
+// no contraction (-ffp-contract=off).
+template <int MODE, int DST, bool FLIP>
+CXNIO_CLONES static void AugmentRow(const float* srow, const float* mrow, float meanc, float contrast, float illum, float scale,
+                                    int W, float* df, uint16_t* dh, uint8_t* db) {
+  for (int x = 0; x < W; ++x) {
+    const int xs = FLIP ? W - 1 - x : x;
+    float v = srow[xs];
+    if (MODE == 1) v = (v - meanc) * contrast + illum;
+    else if (MODE == 2) v = (v - mrow[xs]) * contrast + illum;
+    else if (MODE == 3) v = (v - mrow[x]) * contrast + illum;
+    v = v * scale;
+    if (DST == 1) dh[x] = F32ToBf16(v);
+    else if (DST == 2) db[x] = uint8_t(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v + 0.5f));   // raw pixels
+    else df[x] = v;
+  }
+}
+typedef void (*AugmentRowFn)(const float*, const float*, float, float, float, float, int, float*, uint16_t*, uint8_t*);
+template <int MODE, int DST>
+static AugmentRowFn PickFlip(bool flip) { return flip ? AugmentRow<MODE, DST, true> : AugmentRow<MODE, DST, false>; }
+template <int MODE>
+static AugmentRowFn PickDst(int dst, bool flip) {
+  return dst == 1 ? PickFlip<MODE, 1>(flip) : dst == 2 ? PickFlip<MODE, 2>(flip) : PickFlip<MODE, 0>(flip);
+}
+static AugmentRowFn PickRow(int mode, int dst, bool flip) {
+  switch (mode) {
+    case 1: return PickDst<1>(dst, flip);
+    case 2: return PickDst<2>(dst, flip);
+    case 3: return PickDst<3>(dst, flip);
+    default: return PickDst<0>(dst, flip);
+  }
+}
+}  // extern "C++"
+
 // one instance: src (C x sh x sw planar float) -> dst slot
-CXNIO_CLONES static int AugmentOne(const float* src, int C, int sh, int sw, const CxnioAugItem& it, int H, int W, int mean_mode,
+static int AugmentOne(const float* src, int C, int sh, int sw, const CxnioAugItem& it, int H, int W, int mean_mode,
                       const float* mean, int mean_h, int mean_w, float scale, void* dst, int dst_bf16) {
   if (it.y0 < 0 || it.x0 < 0 || it.y0 + H > sh || it.x0 + W > sw) return -10;
   if (mean_mode == 2 && (mean_h != sh || mean_w != sw)) return -11;
@@ -68,25 +107,16 @@ CXNIO_CLONES static int AugmentOne(const float* src, int C, int sh, int sw, cons
   float* df = static_cast<float*>(dst);
   uint16_t* dh = static_cast<uint16_t*>(dst);
   uint8_t* db = static_cast<uint8_t*>(dst);
-  const float contrast = it.contrast, illum = it.illum;
+  const AugmentRowFn row = PickRow(mean_mode, dst_bf16, it.flip != 0);
   for (int c = 0; c < C; ++c) {
+    const float meanc = mean_mode == 1 ? mean[c] : 0.0f;
     for (int y = 0; y < H; ++y) {
       const float* srow = src + (size_t(c) * sh + it.y0 + y) * sw + it.x0;
       const float* mrow = nullptr;
       if (mean_mode == 2) mrow = mean + (size_t(c) * sh + it.y0 + y) * sw + it.x0;
       if (mean_mode == 3) mrow = mean + (size_t(c) * H + y) * W;
       const size_t o = (size_t(c) * H + y) * W;
-      for (int x = 0; x < W; ++x) {
-        const int xs = it.flip ? W - 1 - x : x;
-        float v = srow[xs];
-        if (mean_mode == 1) v = (v - mean[c]) * contrast + illum;
-        else if (mean_mode == 2) v = (v - mrow[xs]) * contrast + illum;
-        else if (mean_mode == 3) v = (v - mrow[x]) * contrast + illum;
-        v = v * scale;
-        if (dst_bf16 == 1) dh[o + x] = F32ToBf16(v);
-        else if (dst_bf16 == 2) db[o + x] = uint8_t(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v + 0.5f));   // raw pixels
-        else df[o + x] = v;
-      }
+      row(srow, mrow, meanc, it.contrast, it.illum, scale, W, df + o, dh + o, db + o);
     }
   }
   return 0;
