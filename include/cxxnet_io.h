@@ -33,6 +33,9 @@ long long cxnio_pack(const char* list_path, const char* root, const char* out_pa
 int cxnio_jpeg_info(const uint8_t* buf, size_t n, int* width, int* height, int* components);
 int cxnio_jpeg_decode_rgb(const uint8_t* buf, size_t n, uint8_t* out_hwc, int width, int height);
 int cxnio_jpeg_decode_planar_f32(const uint8_t* buf, size_t n, float* out_chw, int width, int height);
+/* Bytes that differ between the AVX2 inverse DCT and the portable one over nblocks pseudo-random coefficient blocks
+ * (must be 0: the vector code performs the same operations in the same order); -1 on a CPU without AVX2.  For tests. */
+int cxnio_jpeg_idct_selftest(int nblocks, unsigned seed);
 /* `count` images on `nthreads` worker threads; status[i] per image; returns the number of failures */
 int cxnio_jpeg_decode_many(int count, const uint8_t* const* bufs, const size_t* sizes, float* const* outs_chw,
                            const int* widths, const int* heights, int* status, int nthreads);

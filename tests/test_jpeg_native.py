@@ -604,3 +604,21 @@ def test_pipeline_threads_are_race_free_under_thread_sanitizer(tmp_path):
     if r.returncode != 0 and "unexpected memory mapping" in r.stdout:
         pytest.skip("thread sanitizer cannot map its shadow memory on this kernel")
     assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout[-3000:]
+
+
+def test_avx2_idct_is_bit_identical_to_the_portable_one():
+    """the AVX2 inverse DCT performs the portable code's operations in the same order: not one byte may differ over
+    sparse, dense and out-of-range coefficient blocks (skipped on CPUs without AVX2)"""
+    import ctypes
+    from cxxnet_b200.io import native
+    L = ctypes.CDLL(native._LIB_PATH) if hasattr(native, "_LIB_PATH") else None
+    if L is None:
+        import os
+        L = ctypes.CDLL(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(native.__file__))), "lib", "libcxxnet_io.so"))
+    L.cxnio_jpeg_idct_selftest.argtypes = [ctypes.c_int, ctypes.c_uint]
+    L.cxnio_jpeg_idct_selftest.restype = ctypes.c_int
+    for seed in (1, 7, 1234):
+        r = L.cxnio_jpeg_idct_selftest(20000, seed)
+        if r < 0:
+            pytest.skip("no AVX2 on this CPU")
+        assert r == 0
