@@ -69,16 +69,30 @@ extern "C++" {
 template <int MODE, int DST, bool FLIP>
 CXNIO_CLONES static void AugmentRow(const float* srow, const float* mrow, float meanc, float contrast, float illum, float scale,
                                     int W, float* df, uint16_t* dh, uint8_t* db) {
-  for (int x = 0; x < W; ++x) {
-    const int xs = FLIP ? W - 1 - x : x;
-    float v = srow[xs];
-    if (MODE == 1) v = (v - meanc) * contrast + illum;
-    else if (MODE == 2) v = (v - mrow[xs]) * contrast + illum;
-    else if (MODE == 3) v = (v - mrow[x]) * contrast + illum;
-    v = v * scale;
-    if (DST == 1) dh[x] = F32ToBf16(v);
-    else if (DST == 2) db[x] = uint8_t(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v + 0.5f));   // raw pixels
-    else df[x] = v;
+  // bf16 output: the values of a stretch first, then their conversion in a loop of its own (integer operations on a
+  // contiguous array: that one vectorises, the combined loop did not)
+  constexpr int kStretch = 256;
+  float buf[kStretch];
+  for (int x0 = 0; x0 < W; x0 += kStretch) {
+    const int n = W - x0 < kStretch ? W - x0 : kStretch;
+    float* o = DST == 0 ? df + x0 : buf;
+    for (int i = 0; i < n; ++i) {
+      const int x = x0 + i;
+      const int xs = FLIP ? W - 1 - x : x;
+      float v = srow[xs];
+      if (MODE == 1) v = (v - meanc) * contrast + illum;
+      else if (MODE == 2) v = (v - mrow[xs]) * contrast + illum;
+      else if (MODE == 3) v = (v - mrow[x]) * contrast + illum;
+      o[i] = v * scale;
+    }
+    if (DST == 1) {
+      for (int i = 0; i < n; ++i) dh[x0 + i] = F32ToBf16(buf[i]);
+    } else if (DST == 2) {
+      for (int i = 0; i < n; ++i) {
+        const float v = buf[i];
+        db[x0 + i] = uint8_t(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v + 0.5f));   // raw pixels
+      }
+    }
   }
 }
 typedef void (*AugmentRowFn)(const float*, const float*, float, float, float, float, int, float*, uint16_t*, uint8_t*);
